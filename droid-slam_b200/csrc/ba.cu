@@ -1,0 +1,833 @@
+// Dense bundle adjustment (droid_backends.ba) for sm_100a.
+// Reference: src/droid_kernels.cu:176-424 (projective_transform_kernel), :854-998 (accum),
+// :1001-1115 (EEt6x6 / Ev6x1 / EvT6x1), :1117-1311 (host SparseBlock / schur_block, Eigen LLT),
+// :1314-1434 (ba_cuda driver).
+//
+// Design (B200-first, not a translation):
+//  * no host round trips: the edge->source-frame CSR, kx = unique(ii U [t0,t1)) and all index
+//    validation are built by one device kernel (ba_prep_kernel); the reference does >=20 blocking
+//    D2H/H2D copies and an O(P^2 deg^2) host loop per iteration;
+//  * nothing per-edge is materialised in HBM: the reference writes Eii/Eij/Cii/bz/Hs/vs
+//    (76 B per pixel-edge) and re-reads E deg times; here every consumer recomputes the Jacobians
+//    from (target, weight, disp) -- 16 B per pixel-edge of compulsory traffic per pass;
+//  * work is grouped by SOURCE FRAME: all per-pixel depth terms of frame k (C_k, w_k, E_k Q_k E_k^T)
+//    involve only edges with ii == k, so one CTA owns (frame, pixel slab) and needs no inter-CTA
+//    exchange before the reduced camera system; this is also the multi-GPU shard unit;
+//  * the reduced camera system (H - S, v - v_S) is assembled directly in fp64 (the reference sums its
+//    fp32 blocks in double on the host, :1133-1156) as a dense lower-triangular 6P x 6P matrix, then
+//    damped and factorised on the device (chol.cu) -- replaces Eigen::SimplicialLLT on one CPU core.
+#include "common.cuh"
+
+namespace droid {
+
+static constexpr int kThreads = 256;
+static constexpr int kHW_ACC = 96;  // 78 Hessian + 12 gradient values per edge, padded to 96
+
+// ------------------------------------------------------------------------------------------------
+// workspace layout
+// ------------------------------------------------------------------------------------------------
+struct BaWs {
+  int* status;     // [64]   status[0] = DROID_BA_STATUS_* bits, status[1] = |kx|, status[2] = chol info
+  int* kmap;       // [nbuf] frame -> index in kx, or -1
+  int* kx;         // [nbuf] sorted unique source/optimised frames
+  int* eptr;       // [nbuf+1] CSR offsets over kx
+  int* eidx;       // [n_edges] edge ids grouped by source frame, ascending inside a frame
+  int* fill;       // [nbuf] scratch counters
+  float* gij;      // [n_edges][8] relative pose of every edge (tij, qij, pad)
+  float* Q;        // [n_eta][HW]
+  float* W;        // [n_eta][HW]
+  float* dx;       // [P][6]
+  double* A;       // [6P*6P + 6P]  dense system, b appended
+  void* chol;      // workspace of the factorisation
+  size_t total;
+};
+
+static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static BaWs carve(void* base, const droid_ba_params* p, size_t chol_bytes) {
+  BaWs w;
+  const size_t HW = (size_t)p->ht * p->wd;
+  const int P = p->t1 - p->t0;
+  const size_t n6 = (size_t)6 * (P > 0 ? P : 0);
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* q = base ? (void*)((char*)base + off) : nullptr;
+    off += align_up(bytes);
+    return q;
+  };
+  w.status = (int*)take(64 * sizeof(int));
+  w.kmap = (int*)take((size_t)p->nbuf * sizeof(int));
+  w.kx = (int*)take((size_t)p->nbuf * sizeof(int));
+  w.eptr = (int*)take(((size_t)p->nbuf + 1) * sizeof(int));
+  w.eidx = (int*)take((size_t)(p->n_edges > 0 ? p->n_edges : 1) * sizeof(int));
+  w.fill = (int*)take((size_t)p->nbuf * sizeof(int));
+  w.gij = (float*)take((size_t)(p->n_edges > 0 ? p->n_edges : 1) * 8 * sizeof(float));
+  w.Q = (float*)take((size_t)(p->n_eta > 0 ? p->n_eta : 1) * HW * sizeof(float));
+  w.W = (float*)take((size_t)(p->n_eta > 0 ? p->n_eta : 1) * HW * sizeof(float));
+  w.dx = (float*)take((n6 > 0 ? n6 : 1) * sizeof(float));
+  w.A = (double*)take((n6 * n6 + n6 + 1) * sizeof(double));
+  w.chol = take(chol_bytes);
+  w.total = off;
+  return w;
+}
+
+// ------------------------------------------------------------------------------------------------
+// graph bookkeeping on the device (replaces torch::_unique + host argsort/CSR, :1336-1344, :948-986)
+// single CTA, 1024 threads; nbuf and n_edges are small (<= a few 10^3 / 10^5).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) ba_prep_kernel(const int64_t* __restrict__ ii,
+                                                       const int64_t* __restrict__ jj, int n_edges,
+                                                       int nbuf, int n_eta, int t0, int t1,
+                                                       int* status, int* kmap, int* kx, int* eptr,
+                                                       int* eidx, int* fill) {
+  __shared__ int s_scan[1024];
+  __shared__ int s_carry;
+  __shared__ int s_bad;
+  const int tid = threadIdx.x;
+  if (tid == 0) { s_carry = 0; s_bad = 0; }
+  for (int f = tid; f < nbuf; f += 1024) { kmap[f] = (f >= t0 && f < t1) ? 1 : 0; fill[f] = 0; }
+  __syncthreads();
+  for (int e = tid; e < n_edges; e += 1024) {
+    const long long i = ii[e], j = jj[e];
+    if (i < 0 || i >= nbuf || j < 0 || j >= nbuf) { s_bad = 1; continue; }
+    kmap[i] = 1;
+  }
+  __syncthreads();
+  // exclusive scan of the flags in chunks of 1024 -> kx / kmap
+  for (int base = 0; base < nbuf; base += 1024) {
+    const int f = base + tid;
+    const int flag = (f < nbuf) ? kmap[f] : 0;
+    s_scan[tid] = flag;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+      int v = (tid >= o) ? s_scan[tid - o] : 0;
+      __syncthreads();
+      s_scan[tid] += v;
+      __syncthreads();
+    }
+    const int incl = s_scan[tid] + s_carry;
+    if (f < nbuf) {
+      if (flag) { kmap[f] = incl - 1; kx[incl - 1] = f; }
+      else kmap[f] = -1;
+    }
+    __syncthreads();
+    if (tid == 1023) s_carry = incl;
+    __syncthreads();
+  }
+  const int M = s_carry;
+  // out-degree per kx slot
+  for (int e = tid; e < n_edges; e += 1024) {
+    const long long i = ii[e], j = jj[e];
+    if (i < 0 || i >= nbuf || j < 0 || j >= nbuf) continue;
+    atomicAdd(&fill[kmap[i]], 1);
+  }
+  __syncthreads();
+  if (tid == 0) { s_carry = 0; }
+  __syncthreads();
+  for (int base = 0; base < M; base += 1024) {
+    const int m = base + tid;
+    const int c = (m < M) ? fill[m] : 0;
+    s_scan[tid] = c;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+      int v = (tid >= o) ? s_scan[tid - o] : 0;
+      __syncthreads();
+      s_scan[tid] += v;
+      __syncthreads();
+    }
+    const int incl = s_scan[tid] + s_carry;
+    if (m < M) eptr[m] = incl - c;
+    __syncthreads();
+    if (tid == 1023) s_carry = incl;
+    __syncthreads();
+  }
+  if (tid == 0) eptr[M] = s_carry;
+  for (int m = tid; m < M; m += 1024) fill[m] = 0;
+  __syncthreads();
+  for (int e = tid; e < n_edges; e += 1024) {
+    const long long i = ii[e], j = jj[e];
+    if (i < 0 || i >= nbuf || j < 0 || j >= nbuf) continue;
+    const int m = kmap[i];
+    eidx[eptr[m] + atomicAdd(&fill[m], 1)] = e;
+  }
+  __syncthreads();
+  // ascending edge id inside every frame => deterministic accumulation order
+  for (int m = tid; m < M; m += 1024) {
+    const int b = eptr[m], e = eptr[m + 1];
+    for (int a = b + 1; a < e; a++) {
+      const int v = eidx[a];
+      int c = a - 1;
+      while (c >= b && eidx[c] > v) { eidx[c + 1] = eidx[c]; c--; }
+      eidx[c + 1] = v;
+    }
+  }
+  if (tid == 0) {
+    int st = 0;
+    if (M != n_eta) st |= DROID_BA_STATUS_ETA_MISMATCH;
+    if (s_bad) st |= DROID_BA_STATUS_BAD_INDEX;
+    status[0] = st;
+    status[1] = M;
+    status[2] = 0;
+  }
+}
+
+__global__ void ba_edge_pose_kernel(const float* __restrict__ poses, const int64_t* __restrict__ ii,
+                                    const int64_t* __restrict__ jj, int n_edges, int nbuf,
+                                    float* __restrict__ gij) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_edges) return;
+  const long long i = ii[e], j = jj[e];
+  SE3 g;
+  if (i < 0 || i >= nbuf || j < 0 || j >= nbuf) {
+    g.t[0] = g.t[1] = g.t[2] = 0.f; g.q[0] = g.q[1] = g.q[2] = 0.f; g.q[3] = 1.f;
+  } else {
+    g = load_edge_pose(poses, (int)i, (int)j);
+  }
+  float* o = gij + (size_t)e * 8;
+  o[0] = g.t[0]; o[1] = g.t[1]; o[2] = g.t[2];
+  o[3] = g.q[0]; o[4] = g.q[1]; o[5] = g.q[2]; o[6] = g.q[3]; o[7] = 0.f;
+}
+
+// ------------------------------------------------------------------------------------------------
+// per pixel-edge linearisation (src/droid_kernels.cu:283-375)
+// ------------------------------------------------------------------------------------------------
+struct PixLin {
+  float Ji_u[6], Jj_u[6], Ji_v[6], Jj_v[6];
+  float Jz_u, Jz_v;
+  float wu_d, wv_d;  // weights of the depth terms (C, bz)
+  float wu, wv;      // weights of the pose terms (zeroed on stereo edges, :323,:356)
+  float ru, rv;
+};
+
+__device__ __forceinline__ void linearise(const SE3& g, const Intr& K, int wd, int k, float disp,
+                                          float tu, float tv, float wru, float wrv, bool stereo,
+                                          PixLin& L) {
+  const int i = k / wd, j = k - i * wd;
+  const float u = (float)j, v = (float)i;
+  float Xi[4], Xj[4];
+  Xi[0] = (u - K.cx) / K.fx;
+  Xi[1] = (v - K.cy) / K.fy;
+  Xi[2] = 1;
+  Xi[3] = disp;
+  act_se3(g.t, g.q, Xi, Xj);
+  const float x = Xj[0], y = Xj[1], h = Xj[3];
+  const bool behind = Xj[2] < DROID_MIN_DEPTH;
+  const float d = behind ? 0.0f : (float)(1.0 / (double)Xj[2]);
+  const float d2 = d * d;
+  L.wu_d = behind ? 0.0f : (float)(.001 * (double)wru);
+  L.wv_d = behind ? 0.0f : (float)(.001 * (double)wrv);
+  L.ru = tu - (K.fx * d * x + K.cx);
+  L.rv = tv - (K.fy * d * y + K.cy);
+  L.Jj_u[0] = K.fx * (h * d);
+  L.Jj_u[1] = K.fx * 0;
+  L.Jj_u[2] = K.fx * (-x * h * d2);
+  L.Jj_u[3] = K.fx * (-x * y * d2);
+  L.Jj_u[4] = K.fx * (1 + x * x * d2);
+  L.Jj_u[5] = K.fx * (-y * d);
+  L.Jz_u = K.fx * (g.t[0] * d - g.t[2] * (x * d2));
+  adj_se3(g.t, g.q, L.Jj_u, L.Ji_u);
+#pragma unroll
+  for (int n = 0; n < 6; n++) L.Ji_u[n] *= -1;
+  L.Jj_v[0] = K.fy * 0;
+  L.Jj_v[1] = K.fy * (h * d);
+  L.Jj_v[2] = K.fy * (-y * h * d2);
+  L.Jj_v[3] = K.fy * (-1 - y * y * d2);
+  L.Jj_v[4] = K.fy * (x * y * d2);
+  L.Jj_v[5] = K.fy * (x * d);
+  L.Jz_v = K.fy * (g.t[1] * d - g.t[2] * (y * d2));
+  adj_se3(g.t, g.q, L.Jj_v, L.Ji_v);
+#pragma unroll
+  for (int n = 0; n < 6; n++) L.Ji_v[n] *= -1;
+  L.wu = stereo ? 0.f : L.wu_d;
+  L.wv = stereo ? 0.f : L.wv_d;
+}
+
+__device__ __forceinline__ SE3 load_gij(const float* __restrict__ gij, int e) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e * 8));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e * 8 + 4));
+  SE3 g;
+  g.t[0] = a.x; g.t[1] = a.y; g.t[2] = a.z;
+  g.q[0] = a.w; g.q[1] = b.x; g.q[2] = b.y; g.q[3] = b.z;
+  return g;
+}
+
+// Transposing butterfly over 96 per-lane values: lane l ends with the warp sums of 3l..3l+2 in v[0..2].
+__device__ __forceinline__ void transpose_reduce96(float* v, int lane) {
+  int cnt = 96;
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const int half = cnt >> 1;
+    const bool up = lane & off;
+#pragma unroll
+    for (int i = 0; i < 48; i++) {
+      if (i < half) {
+        const float send = up ? v[i] : v[i + half];
+        const float keep = up ? v[i + half] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+      }
+    }
+    cnt = half;
+  }
+}
+
+// Scatter one reduced per-edge value l (0..77 Hessian lower-tri of the 12x12 (i,j) block, 78..89
+// gradient) into the dense lower-triangular system.  pi/pj = pose indices relative to t0 (or -1).
+__device__ __forceinline__ void scatter_edge_value(double* __restrict__ A, double* __restrict__ b,
+                                                   int n6, int l, float val, int pi, int pj) {
+  if (l < 78) {
+    // l = n(n+1)/2 + m, m <= n
+    int n = (int)((sqrtf(8.f * l + 1.f) - 1.f) * 0.5f);
+    while ((n + 1) * (n + 2) / 2 <= l) n++;
+    while (n * (n + 1) / 2 > l) n--;
+    const int m = l - n * (n + 1) / 2;
+    if (n < 6) {  // Hii, lower part of the diagonal block
+      if (pi >= 0) atomicAdd(&A[(size_t)(6 * pi + n) * n6 + 6 * pi + m], (double)val);
+    } else if (m >= 6) {  // Hjj
+      if (pj >= 0) atomicAdd(&A[(size_t)(6 * pj + n - 6) * n6 + 6 * pj + m - 6], (double)val);
+    } else {  // Hji[n-6][m]
+      if (pi >= 0 && pj >= 0) {
+        if (pj > pi) atomicAdd(&A[(size_t)(6 * pj + n - 6) * n6 + 6 * pi + m], (double)val);
+        else if (pj < pi) atomicAdd(&A[(size_t)(6 * pi + m) * n6 + 6 * pj + n - 6], (double)val);
+      }
+    }
+  } else if (l < 84) {
+    if (pi >= 0) atomicAdd(&b[6 * pi + (l - 78)], (double)val);
+  } else if (l < 90) {
+    if (pj >= 0) atomicAdd(&b[6 * pj + (l - 84)], (double)val);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// pass 1: per-edge Hessian/gradient blocks + per-pixel depth terms -> Q = 1/C and w
+// CTA = (pixel slab, source frame m).  Per edge the 90 per-thread partials are reduced with a
+// transposing butterfly and added (fp64 atomics) into the dense system; C and bz are accumulated
+// over the frame's edges in shared memory (each pixel is owned by one thread => no atomics there).
+// ------------------------------------------------------------------------------------------------
+static constexpr int kSlabMax = 3072;
+
+__global__ void __launch_bounds__(kThreads) ba_accum_kernel(
+    const float* __restrict__ disps, const float* __restrict__ intrinsics,
+    const float* __restrict__ disps_sens, const float* __restrict__ targets,
+    const float* __restrict__ weights, const float* __restrict__ eta,
+    const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, const float* __restrict__ gij,
+    const int* __restrict__ status, const int* __restrict__ kx, const int* __restrict__ eptr,
+    const int* __restrict__ eidx, float* __restrict__ Qo, float* __restrict__ Wo,
+    double* __restrict__ A, double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P,
+    int n_eta, int motion_only, int frame_lo, int frame_hi) {
+  __shared__ float Cs[kSlabMax];
+  __shared__ float Bs[kSlabMax];
+  __shared__ float red[kThreads / 32][kHW_ACC];
+  const int m = blockIdx.y;
+  const int M = status[1];
+  if (m >= M || m >= n_eta) return;
+  const int k = kx[m];
+  if (k < frame_lo || k >= frame_hi) return;
+  const int p0 = blockIdx.x * slab;
+  const int p1 = min(HW, p0 + slab);
+  if (p0 >= p1) return;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
+  const int n6 = 6 * P;
+  for (int p = tid; p < p1 - p0; p += kThreads) { Cs[p] = 0.f; Bs[p] = 0.f; }
+  __syncthreads();
+  const float* __restrict__ dmap = disps + (size_t)k * HW;
+  const int e0 = eptr[m], e1 = eptr[m + 1];
+  for (int ei = e0; ei < e1; ei++) {
+    const int e = eidx[ei];
+    const int jx = (int)jj[e];
+    const bool stereo = (jx == k);
+    const SE3 g = load_gij(gij, e);
+    const float* __restrict__ tg = targets + (size_t)e * 2 * HW;
+    const float* __restrict__ wt = weights + (size_t)e * 2 * HW;
+    float acc[kHW_ACC];
+#pragma unroll
+    for (int l = 0; l < kHW_ACC; l++) acc[l] = 0.f;
+    for (int p = p0 + tid; p < p1; p += kThreads) {
+      PixLin L;
+      linearise(g, K, wd, p, dmap[p], tg[p], tg[HW + p], wt[p], wt[HW + p], stereo, L);
+      // depth terms (:320-321, :353-354)
+      float c = L.wu_d * L.Jz_u * L.Jz_u;
+      float bz = L.wu_d * L.ru * L.Jz_u;
+      c += L.wv_d * L.Jz_v * L.Jz_v;
+      bz += L.wv_d * L.rv * L.Jz_v;
+      Cs[p - p0] += c;
+      Bs[p - p0] += bz;
+      if (!stereo) {
+        float Jx[12];
+#pragma unroll
+        for (int n = 0; n < 6; n++) { Jx[n] = L.Ji_u[n]; Jx[6 + n] = L.Jj_u[n]; }
+        int l = 0;
+#pragma unroll
+        for (int n = 0; n < 12; n++) {
+          const float wj = L.wu * Jx[n];
+#pragma unroll
+          for (int q = 0; q <= n; q++) { acc[l] += wj * Jx[q]; l++; }
+        }
+        const float wr = L.wu * L.ru;
+#pragma unroll
+        for (int n = 0; n < 12; n++) acc[78 + n] += wr * Jx[n];
+#pragma unroll
+        for (int n = 0; n < 6; n++) { Jx[n] = L.Ji_v[n]; Jx[6 + n] = L.Jj_v[n]; }
+        l = 0;
+#pragma unroll
+        for (int n = 0; n < 12; n++) {
+          const float wj = L.wv * Jx[n];
+#pragma unroll
+          for (int q = 0; q <= n; q++) { acc[l] += wj * Jx[q]; l++; }
+        }
+        const float wr2 = L.wv * L.rv;
+#pragma unroll
+        for (int n = 0; n < 12; n++) acc[78 + n] += wr2 * Jx[n];
+      }
+    }
+    if (!stereo) {
+      transpose_reduce96(acc, lane);
+      red[warp][3 * lane + 0] = acc[0];
+      red[warp][3 * lane + 1] = acc[1];
+      red[warp][3 * lane + 2] = acc[2];
+      __syncthreads();
+      if (tid < 90) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; w++) s += red[w][tid];
+        int pi = k - t0, pj = jx - t0;
+        if (pi < 0 || pi >= P) pi = -1;
+        if (pj < 0 || pj >= P) pj = -1;
+        scatter_edge_value(A, bvec, n6, tid, s, pi, pj);
+      }
+      __syncthreads();
+    }
+  }
+  if (motion_only) return;
+  // C = sum Cii + m*alpha + (1-m)*eta ; w = sum bz - m*alpha*(disp - disp_sens) ; Q = 1/C   (:1396-1400)
+  const float alpha = 0.05f;
+  const float* __restrict__ ds = disps_sens + (size_t)k * HW;
+  const float* __restrict__ et = eta + (size_t)m * HW;
+  for (int p = p0 + tid; p < p1; p += kThreads) {
+    const float mk = ds[p] > 0.f ? 1.0f : 0.0f;
+    const float C = Cs[p - p0] + mk * alpha + (1 - mk) * et[p];
+    const float w = Bs[p - p0] - mk * alpha * (dmap[p] - ds[p]);
+    Qo[(size_t)m * HW + p] = (float)(1.0 / (double)C);
+    Wo[(size_t)m * HW + p] = w;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// pass 2: Schur complement  S = sum_k E_k diag(Q_k) E_k^T ,  v_S = sum_k E_k (Q_k w_k)
+// (replaces host schur_block :1222-1311 + EEt6x6_kernel :1001-1056 + Ev6x1_kernel :1059-1093).
+// For source frame k the rows of E_k are: block 0 = sum_e E_i^e (pose k), block 1+e = E_j^e (pose jj[e]).
+// CTA = (pixel slab, frame).  Per pixel tile the CTA (a) recomputes the E rows into shared memory,
+// pixel-major [T][R] so that a thread reads one 6-float block as 3 conflict-free LDS.64, (b) runs the
+// Gram product with register tiles of 6x12 (block row a x block columns 2c,2c+1, lower triangle only),
+// accumulating over all tiles of the slab in registers, and (c) subtracts the tiles from the dense fp64
+// system with atomics.  If a frame has more register tiles than threads the CTA makes several passes.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tile_to_ac(int t, int& a, int& c) {
+  // tiles of block row a: c = 0..a/2 ; base(2h) = h(h+1), base(2h+1) = (h+1)^2
+  int h = (int)((sqrtf(4.f * t + 1.f) - 1.f) * 0.5f);
+  while ((h + 1) * (h + 2) <= t) h++;
+  while (h * (h + 1) > t) h--;
+  if (t < (h + 1) * (h + 1)) { a = 2 * h; c = t - h * (h + 1); }
+  else { a = 2 * h + 1; c = t - (h + 1) * (h + 1); }
+}
+
+__device__ __forceinline__ void flush_block(double* __restrict__ A, int n6, const float* blk /*[6][6]*/,
+                                            int pa, int pb, bool same_local) {
+  // blk[n][m] = sum (E_a[n] q) E_b[m]  -> S[pa,pb]; system holds H - S, lower triangle only.
+  if (pa < 0 || pb < 0) return;
+  if (pa > pb) {
+#pragma unroll
+    for (int n = 0; n < 6; n++)
+#pragma unroll
+      for (int m = 0; m < 6; m++)
+        atomicAdd(&A[(size_t)(6 * pa + n) * n6 + 6 * pb + m], -(double)blk[n * 6 + m]);
+  } else if (pa < pb) {
+#pragma unroll
+    for (int n = 0; n < 6; n++)
+#pragma unroll
+      for (int m = 0; m < 6; m++)
+        atomicAdd(&A[(size_t)(6 * pb + m) * n6 + 6 * pa + n], -(double)blk[n * 6 + m]);
+  } else if (same_local) {  // diagonal block of one row block: symmetric, keep the lower part
+#pragma unroll
+    for (int n = 0; n < 6; n++)
+#pragma unroll
+      for (int m = 0; m <= n; m++)
+        atomicAdd(&A[(size_t)(6 * pa + n) * n6 + 6 * pa + m], -(double)blk[n * 6 + m]);
+  } else {  // two different rows of E with the same pose: S[p,p] += blk + blk^T
+#pragma unroll
+    for (int n = 0; n < 6; n++)
+#pragma unroll
+      for (int m = 0; m <= n; m++) {
+        const double v = (n == m) ? 2.0 * (double)blk[n * 6 + n]
+                                  : (double)blk[n * 6 + m] + (double)blk[m * 6 + n];
+        atomicAdd(&A[(size_t)(6 * pa + n) * n6 + 6 * pa + m], -v);
+      }
+  }
+}
+
+static constexpr int kSchurSmemBytes = 200 * 1024;
+
+__global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
+    const float* __restrict__ disps, const float* __restrict__ intrinsics,
+    const float* __restrict__ targets, const float* __restrict__ weights,
+    const int64_t* __restrict__ jj, const float* __restrict__ gij, int* __restrict__ status,
+    const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
+    const float* __restrict__ Qi, const float* __restrict__ Wi, double* __restrict__ A,
+    double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P, int n_eta, int frame_lo,
+    int frame_hi) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int m = blockIdx.y;
+  const int M = status[1];
+  if (m >= M || m >= n_eta) return;
+  const int k = kx[m];
+  if (k < frame_lo || k >= frame_hi) return;
+  const int p0 = blockIdx.x * slab;
+  const int p1 = min(HW, p0 + slab);
+  if (p0 >= p1) return;
+  const int tid = threadIdx.x;
+  const int e0 = eptr[m], e1 = eptr[m + 1];
+  const int deg = e1 - e0;
+  const int D = deg + 1, R = 6 * D;
+  const int stride = (R & 3) == 2 ? R : R + 2;  // == 2 (mod 4): even (LDS.64) and 2-way STS at worst
+  // smem: E[T][stride] | Qs[T] | QWs[T] | vS[R] | pose[D]
+  const int fixed = (R + D + 8) * 4;
+  int T = (kSchurSmemBytes - fixed) / ((stride + 2) * 4);
+  T = min(T, kThreads) & ~31;
+  if (T < 32) {  // out-degree too large for one SM's shared memory
+    if (tid == 0) atomicOr(&status[0], DROID_BA_STATUS_BAD_INDEX);
+    return;
+  }
+  float* Es = reinterpret_cast<float*>(smem_raw);
+  float* Qs = Es + (size_t)T * stride;
+  float* QWs = Qs + T;
+  float* vS = QWs + T;
+  int* pose = reinterpret_cast<int*>(vS + R);
+  const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
+  const int n6 = 6 * P;
+  for (int d = tid; d < D; d += kThreads) {
+    int pz = (d == 0) ? k - t0 : (int)jj[eidx[e0 + d - 1]] - t0;
+    if (pz < 0 || pz >= P) pz = -1;
+    pose[d] = pz;
+  }
+  for (int r = tid; r < R; r += kThreads) vS[r] = 0.f;
+  const int ntiles = (D & 1) ? ((D + 1) / 2) * ((D + 1) / 2) : (D / 2) * (D / 2 + 1);  // base(D)
+  const int G = ntiles >= kThreads ? 1 : min(kThreads / ntiles, 8);
+  const int slots = ntiles >= kThreads ? kThreads : ntiles;
+  const int g = tid / slots, tslot = tid - g * slots;
+  const int npass = (ntiles + slots - 1) / slots;
+  const float* __restrict__ dmap = disps + (size_t)k * HW;
+  __syncthreads();
+
+  for (int pass = 0; pass < npass; pass++) {
+    const int tile = pass * slots + tslot;
+    const bool active = (g < G) && (tile < ntiles);
+    int a = 0, c = 0;
+    if (active) tile_to_ac(tile, a, c);
+    const int b0 = 2 * c, b1 = 2 * c + 1;
+    const bool has1 = active && (b1 <= a);
+    float acc0[36], acc1[36];
+#pragma unroll
+    for (int i = 0; i < 36; i++) { acc0[i] = 0.f; acc1[i] = 0.f; }
+
+    for (int pt = p0; pt < p1; pt += T) {
+      const int np = min(T, p1 - pt);
+      // ---- (a) E rows of this pixel tile ------------------------------------------------------
+      if (tid < np) {
+        const int p = pt + tid;
+        float* Erow = Es + (size_t)tid * stride;
+        float Ei[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        const float dp = dmap[p];
+        for (int ei = e0; ei < e1; ei++) {
+          const int e = eidx[ei];
+          const int jx = (int)jj[e];
+          const SE3 gg = load_gij(gij, e);
+          const float* __restrict__ tg = targets + (size_t)e * 2 * HW;
+          const float* __restrict__ wt = weights + (size_t)e * 2 * HW;
+          PixLin L;
+          linearise(gg, K, wd, p, dp, tg[p], tg[HW + p], wt[p], wt[HW + p], jx == k, L);
+          const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
+          float* Ej = Erow + 6 * (ei - e0 + 1);
+#pragma unroll
+          for (int n = 0; n < 6; n++) {
+            float ei_n = au * L.Ji_u[n];
+            ei_n += av * L.Ji_v[n];
+            Ei[n] += ei_n;
+            float ej_n = au * L.Jj_u[n];
+            ej_n += av * L.Jj_v[n];
+            Ej[n] = ej_n;
+          }
+        }
+#pragma unroll
+        for (int n = 0; n < 6; n++) Erow[n] = Ei[n];
+        const float q = Qi[(size_t)m * HW + p];
+        Qs[tid] = q;
+        QWs[tid] = q * Wi[(size_t)m * HW + p];
+      }
+      __syncthreads();
+      // ---- (b) Gram product over the tile ------------------------------------------------------
+      if (active) {
+        for (int p = g; p < np; p += G) {
+          const float* Erow = Es + (size_t)p * stride;
+          const float q = Qs[p];
+          float ea[6], eb[6], ec[6];
+          {
+            const float2* pa2 = reinterpret_cast<const float2*>(Erow + 6 * a);
+            const float2 x0 = pa2[0], x1 = pa2[1], x2 = pa2[2];
+            ea[0] = x0.x * q; ea[1] = x0.y * q; ea[2] = x1.x * q;
+            ea[3] = x1.y * q; ea[4] = x2.x * q; ea[5] = x2.y * q;
+            const float2* pb2 = reinterpret_cast<const float2*>(Erow + 6 * b0);
+            const float2 y0 = pb2[0], y1 = pb2[1], y2 = pb2[2];
+            eb[0] = y0.x; eb[1] = y0.y; eb[2] = y1.x; eb[3] = y1.y; eb[4] = y2.x; eb[5] = y2.y;
+          }
+#pragma unroll
+          for (int n = 0; n < 6; n++)
+#pragma unroll
+            for (int mm = 0; mm < 6; mm++) acc0[n * 6 + mm] = fmaf(ea[n], eb[mm], acc0[n * 6 + mm]);
+          if (has1) {
+            const float2* pc2 = reinterpret_cast<const float2*>(Erow + 6 * b1);
+            const float2 z0 = pc2[0], z1 = pc2[1], z2 = pc2[2];
+            ec[0] = z0.x; ec[1] = z0.y; ec[2] = z1.x; ec[3] = z1.y; ec[4] = z2.x; ec[5] = z2.y;
+#pragma unroll
+            for (int n = 0; n < 6; n++)
+#pragma unroll
+              for (int mm = 0; mm < 6; mm++) acc1[n * 6 + mm] = fmaf(ea[n], ec[mm], acc1[n * 6 + mm]);
+          }
+        }
+      }
+      // ---- v_S rows (first pass only) -----------------------------------------------------------
+      if (pass == 0) {
+        for (int r = tid; r < R; r += kThreads) {
+          float s = 0.f;
+          for (int p = 0; p < np; p++) s = fmaf(QWs[p], Es[(size_t)p * stride + r], s);
+          vS[r] += s;
+        }
+      }
+      __syncthreads();
+    }
+    // ---- (c) subtract from the dense system ------------------------------------------------------
+    if (active) {
+      flush_block(A, n6, acc0, pose[a], pose[b0], a == b0);
+      if (has1) flush_block(A, n6, acc1, pose[a], pose[b1], a == b1);
+    }
+  }
+  for (int r = tid; r < R; r += kThreads) {
+    const int pz = pose[r / 6];
+    if (pz >= 0) atomicAdd(&bvec[6 * pz + (r % 6)], -(double)vS[r]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// pass 3: depth back-substitution and update  (EvT6x1_kernel :1095-1115, :1417, disp_retr :933-946)
+//   dz_k = Q_k * (w_k - sum_rows E_n^T dx[pose(n)]),  rows whose pose index is <= 0 or >= P are
+//   skipped exactly like the reference (:1105) -- i.e. the first optimised pose t0 never feeds dz.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) ba_dz_kernel(
+    float* __restrict__ disps, const float* __restrict__ intrinsics,
+    const float* __restrict__ targets, const float* __restrict__ weights,
+    const int64_t* __restrict__ jj, const float* __restrict__ gij, const int* __restrict__ status,
+    const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
+    const float* __restrict__ Qi, const float* __restrict__ Wi, const float* __restrict__ dx,
+    float* __restrict__ dz_out, int HW, int wd, int t0, int P, int n_eta, int frame_lo,
+    int frame_hi) {
+  const int m = blockIdx.y;
+  const int M = status[1];
+  if (m >= M || m >= n_eta) return;
+  const int k = kx[m];
+  if (k < frame_lo || k >= frame_hi) return;
+  const int p = blockIdx.x * kThreads + threadIdx.x;
+  if (p >= HW) return;
+  const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
+  float* __restrict__ dmap = disps + (size_t)k * HW;
+  const float dp = dmap[p];
+  const int e0 = eptr[m], e1 = eptr[m + 1];
+  float Ei[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float sum = 0.f;
+  for (int ei = e0; ei < e1; ei++) {
+    const int e = eidx[ei];
+    const int jx = (int)jj[e];
+    const SE3 g = load_gij(gij, e);
+    const float* __restrict__ tg = targets + (size_t)e * 2 * HW;
+    const float* __restrict__ wt = weights + (size_t)e * 2 * HW;
+    PixLin L;
+    linearise(g, K, wd, p, dp, tg[p], tg[HW + p], wt[p], wt[HW + p], jx == k, L);
+    const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
+    const int pj = jx - t0;
+    const bool use = pj > 0 && pj < P;
+    float dw = 0.f;
+#pragma unroll
+    for (int n = 0; n < 6; n++) {
+      float ei_n = au * L.Ji_u[n];
+      ei_n += av * L.Ji_v[n];
+      Ei[n] += ei_n;
+      float ej_n = au * L.Jj_u[n];
+      ej_n += av * L.Jj_v[n];
+      if (use) dw += ej_n * __ldg(&dx[6 * pj + n]);
+    }
+    sum += dw;
+  }
+  const int pk = k - t0;
+  if (pk > 0 && pk < P) {
+    float dw = 0.f;
+#pragma unroll
+    for (int n = 0; n < 6; n++) dw += Ei[n] * __ldg(&dx[6 * pk + n]);
+    sum += dw;
+  }
+  const float dz = Qi[(size_t)m * HW + p] * (Wi[(size_t)m * HW + p] - sum);
+  dz_out[(size_t)m * HW + p] = dz;
+  dmap[p] = dp + dz;
+}
+
+// A.diag += ep + lm * A.diag   (:1197), fp64 like the reference
+__global__ void ba_damp_kernel(double* __restrict__ A, int n6, float lm, float ep) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n6) {
+    double* d = &A[(size_t)i * n6 + i];
+    *d += (double)ep + (double)lm * (*d);
+  }
+}
+
+// dx = float(x) or 0 when the factorisation failed (:1202-1210); then T <- Exp(dx) T (:898-931)
+__global__ void ba_pose_update_kernel(float* __restrict__ poses, const double* __restrict__ x,
+                                      int* __restrict__ status, const int* __restrict__ info,
+                                      float* __restrict__ dx, float* __restrict__ dx_out, int t0,
+                                      int P, int apply) {
+  const int kk = blockIdx.x * blockDim.x + threadIdx.x;
+  if (kk >= P) return;
+  const bool failed = (*info != 0);
+  if (failed && kk == 0) atomicOr(&status[0], DROID_BA_STATUS_CHOL_FAILED);
+  float xi[6];
+#pragma unroll
+  for (int n = 0; n < 6; n++) {
+    xi[n] = failed ? 0.f : (float)x[6 * kk + n];
+    dx[6 * kk + n] = xi[n];
+    dx_out[6 * kk + n] = xi[n];
+  }
+  if (!apply) return;
+  float* p = poses + 7 * (size_t)(t0 + kk);
+  const float t[3] = {p[0], p[1], p[2]};
+  const float q[4] = {p[3], p[4], p[5], p[6]};
+  float t1[3], q1[4];
+  retr_se3(xi, t, q, t1, q1);
+  p[0] = t1[0]; p[1] = t1[1]; p[2] = t1[2];
+  p[3] = q1[0]; p[4] = q1[1]; p[5] = q1[2]; p[6] = q1[3];
+}
+
+__global__ void ba_pose_apply_kernel(float* __restrict__ poses, const float* __restrict__ dx, int t0,
+                                     int P) {
+  const int kk = blockIdx.x * blockDim.x + threadIdx.x;
+  if (kk >= P) return;
+  float xi[6];
+#pragma unroll
+  for (int n = 0; n < 6; n++) xi[n] = dx[6 * kk + n];
+  float* p = poses + 7 * (size_t)(t0 + kk);
+  const float t[3] = {p[0], p[1], p[2]};
+  const float q[4] = {p[3], p[4], p[5], p[6]};
+  float t1[3], q1[4];
+  retr_se3(xi, t, q, t1, q1);
+  p[0] = t1[0]; p[1] = t1[1]; p[2] = t1[2];
+  p[3] = q1[0]; p[4] = q1[1]; p[5] = q1[2]; p[6] = q1[3];
+}
+
+}  // namespace droid
+
+using namespace droid;
+
+extern "C" size_t droid_ba_workspace_bytes(const droid_ba_params* p) {
+  if (!p || p->nbuf <= 0 || p->ht <= 0 || p->wd <= 0 || p->t1 < p->t0 || p->n_edges < 0) return 0;
+  const int n6 = 6 * (p->t1 - p->t0);
+  BaWs w = carve(nullptr, p, droid_chol_workspace_bytes(n6));
+  return w.total + 256;
+}
+
+extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+                        const float* targets, const float* weights, const float* eta,
+                        const int64_t* ii, const int64_t* jj, const droid_ba_params* p,
+                        float* dx_out, float* dz_out, void* workspace, size_t workspace_bytes,
+                        void* stream) {
+  if (!p) return DROID_ERR_INVALID_ARGUMENT;
+  if (p->nbuf <= 0 || p->ht <= 0 || p->wd <= 0 || p->n_edges < 0 || p->n_eta < 0 ||
+      p->t0 < 0 || p->t1 < p->t0 || p->t1 > p->nbuf || p->iterations < 0)
+    return DROID_ERR_INVALID_ARGUMENT;
+  if (!poses || !disps || !intrinsics || !disps_sens || !workspace || !dx_out)
+    return DROID_ERR_INVALID_ARGUMENT;
+  if (p->n_edges > 0 && (!targets || !weights || !ii || !jj)) return DROID_ERR_INVALID_ARGUMENT;
+  if (!p->motion_only && (!eta || !dz_out) && p->n_eta > 0) return DROID_ERR_INVALID_ARGUMENT;
+  if (p->n_eta > 65535) return DROID_ERR_INVALID_ARGUMENT;
+  const int P = p->t1 - p->t0;
+  const int n6 = 6 * P;
+  const size_t chol_bytes = droid_chol_workspace_bytes(n6);
+  if (((uintptr_t)workspace & 255) != 0) {
+    const size_t adj = 256 - ((uintptr_t)workspace & 255);
+    if (workspace_bytes < adj) return DROID_ERR_WORKSPACE_TOO_SMALL;
+    workspace = (char*)workspace + adj;
+    workspace_bytes -= adj;
+  }
+  BaWs w = carve(workspace, p, chol_bytes);
+  if (w.total > workspace_bytes) return DROID_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int HW = p->ht * p->wd;
+  const int frame_lo = p->frame_lo, frame_hi = p->frame_hi > p->frame_lo ? p->frame_hi : 0x7fffffff;
+
+  ba_prep_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->n_eta, p->t0, p->t1, w.status,
+                                     w.kmap, w.kx, w.eptr, w.eidx, w.fill);
+  if (check_launch()) return DROID_ERR_CUDA;
+  if (P == 0 || p->iterations == 0) return DROID_OK;
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(ba_schur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         kSchurSmemBytes);
+    attr_set = true;
+  }
+  // slabs: enough CTAs to fill the 148 SMs twice when there are few frames
+  const int Mrows = p->n_eta > 0 ? p->n_eta : 1;
+  int S = (2 * 148 + Mrows - 1) / Mrows;
+  const int max_s = (HW + kThreads - 1) / kThreads;
+  if (S > max_s) S = max_s;
+  if (S < 1) S = 1;
+  int slab = (HW + S - 1) / S;
+  slab = (slab + 31) & ~31;
+  if (slab > kSlabMax) slab = kSlabMax;
+  S = (HW + slab - 1) / slab;
+  double* bvec = w.A + (size_t)n6 * n6;
+
+  for (int itr = 0; itr < p->iterations; itr++) {
+    if (p->n_edges > 0) {
+      ba_edge_pose_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(poses, ii, jj, p->n_edges,
+                                                                    p->nbuf, w.gij);
+    }
+    cudaMemsetAsync(w.A, 0, ((size_t)n6 * n6 + n6) * sizeof(double), st);
+    if (p->n_edges > 0 && p->n_eta > 0) {
+      ba_accum_kernel<<<dim3(S, p->n_eta), kThreads, 0, st>>>(
+          disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, w.gij, w.status, w.kx,
+          w.eptr, w.eidx, w.Q, w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, p->motion_only,
+          frame_lo, frame_hi);
+      if (!p->motion_only) {
+        ba_schur_kernel<<<dim3(S, p->n_eta), kThreads, kSchurSmemBytes, st>>>(
+            disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q,
+            w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi);
+      }
+    }
+    if (check_launch()) return DROID_ERR_CUDA;
+    if (p->reduce_fn) {
+      int rc = p->reduce_fn(p->reduce_user, w.A, (size_t)n6 * n6 + n6, stream);
+      if (rc != 0) return DROID_ERR_CUDA;
+    }
+    ba_damp_kernel<<<(n6 + 127) / 128, 128, 0, st>>>(w.A, n6, p->lm, p->ep);
+    int rc = droid_chol_solve_f64(w.A, bvec, n6, w.status + 2, w.chol, chol_bytes, stream);
+    if (rc != DROID_OK) return rc;
+    if (p->motion_only || p->n_eta == 0 || p->n_edges == 0) {
+      ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
+                                                             w.dx, dx_out, p->t0, P, 1);
+    } else {
+      ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
+                                                             w.dx, dx_out, p->t0, P, 0);
+      ba_dz_kernel<<<dim3((HW + kThreads - 1) / kThreads, p->n_eta), kThreads, 0, st>>>(
+          disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
+          w.dx, dz_out, HW, p->wd, p->t0, P, p->n_eta, frame_lo, frame_hi);
+      ba_pose_apply_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, w.dx, p->t0, P);
+    }
+    if (check_launch()) return DROID_ERR_CUDA;
+  }
+  return DROID_OK;
+}

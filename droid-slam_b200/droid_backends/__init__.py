@@ -1,0 +1,434 @@
+"""Drop-in replacement of DROID-SLAM's ``droid_backends`` extension module for NVIDIA B200 (sm_100a).
+
+Same nine functions, positional signatures and return structures as the reference's pybind module
+(/root/reference/src/droid.cpp:237-250), so ``droid_slam/modules/corr.py``, ``depth_video.py``,
+``factor_graph.py`` and ``visualization.py`` can ``import droid_backends`` unchanged.
+
+This file is only the host side: it validates arguments, allocates outputs / workspaces with torch on
+the current CUDA stream and calls the C ABI of ``libdroid_b200.so`` (include/droid_b200.h) through
+ctypes.  There is NO CPU or PyTorch fallback: if the shared library is missing or a tensor is not on
+a CUDA device the call raises.
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "..", "lib", "libdroid_b200.so")
+
+_F32, _F16, _F64 = 0, 1, 2
+_DT = {torch.float32: _F32, torch.float16: _F16, torch.float64: _F64}
+
+_ERRORS = {
+    -1: "invalid argument", -2: "unsupported dtype", -3: "workspace too small",
+    -4: "CUDA launch failed", -5: "not implemented",
+}
+
+REDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t,
+                             ctypes.c_void_p)
+
+
+class BaParams(ctypes.Structure):
+    """Mirror of droid_ba_params (include/droid_b200.h)."""
+    _fields_ = [
+        ("n_edges", ctypes.c_int), ("nbuf", ctypes.c_int), ("ht", ctypes.c_int), ("wd", ctypes.c_int),
+        ("n_eta", ctypes.c_int), ("t0", ctypes.c_int), ("t1", ctypes.c_int),
+        ("iterations", ctypes.c_int), ("motion_only", ctypes.c_int),
+        ("lm", ctypes.c_float), ("ep", ctypes.c_float),
+        ("frame_lo", ctypes.c_int), ("frame_hi", ctypes.c_int),
+        ("reduce_fn", REDUCE_FN), ("reduce_user", ctypes.c_void_p),
+    ]
+
+
+def _load():
+    path = os.environ.get("DROID_B200_LIB", _LIB_PATH)
+    if not os.path.exists(path):
+        raise ImportError(
+            "libdroid_b200.so not found at %s -- build it with `python droid-slam_b200/build.py` "
+            "(there is no CPU / PyTorch fallback)" % os.path.abspath(path))
+    lib = ctypes.CDLL(os.path.abspath(path))
+    lib.droid_version.restype = ctypes.c_char_p
+    lib.droid_last_cuda_error.restype = ctypes.c_char_p
+    lib.droid_ba_workspace_bytes.restype = ctypes.c_size_t
+    lib.droid_ba_workspace_bytes.argtypes = [ctypes.POINTER(BaParams)]
+    lib.droid_chol_workspace_bytes.restype = ctypes.c_size_t
+    lib.droid_corr_build_workspace_bytes.restype = ctypes.c_size_t
+    return lib
+
+
+_lib = _load()
+__version__ = _lib.droid_version().decode()
+
+# names every build of the library must export (checked by tests/test_abi.py against the header)
+C_ABI_SYMBOLS = [
+    "droid_version", "droid_last_cuda_error", "droid_corr_index_forward", "droid_corr_index_backward",
+    "droid_corr_index_pyramid", "droid_altcorr_forward", "droid_altcorr_backward",
+    "droid_altcorr_forward_indexed", "droid_corr_build", "droid_corr_build_workspace_bytes",
+    "droid_frame_distance", "droid_projmap", "droid_iproj", "droid_depth_filter",
+    "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_workspace_bytes",
+]
+
+
+def _check(rc, what):
+    if rc != 0:
+        msg = _ERRORS.get(rc, "error %d" % rc)
+        if rc == -4:
+            msg += ": " + _lib.droid_last_cuda_error().decode()
+        raise RuntimeError("droid_backends.%s: %s" % (what, msg))
+
+
+def _contig(what, **tensors):
+    # reference: CHECK_CONTIGUOUS -> TORCH_CHECK -> RuntimeError (src/droid.cpp:84-85)
+    for name, t in tensors.items():
+        if not isinstance(t, torch.Tensor):
+            raise RuntimeError("droid_backends.%s: %s must be a tensor" % (what, name))
+        if not t.is_contiguous():
+            raise RuntimeError("%s must be contiguous" % name)
+        if not t.is_cuda:
+            raise RuntimeError("droid_backends.%s: %s must be a CUDA tensor (no CPU fallback)" % (what, name))
+
+
+def _dtype(what, t, allowed):
+    if t.dtype not in allowed:
+        raise RuntimeError("droid_backends.%s: expected dtype in %s, got %s" % (what, allowed, t.dtype))
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr() if t is not None and t.numel() > 0 else 0)
+
+
+def _stream(t):
+    return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _long(what, **tensors):
+    for name, t in tensors.items():
+        if t.dtype != torch.int64:
+            raise RuntimeError("droid_backends.%s: %s must be int64" % (what, name))
+
+
+# ------------------------------------------------------------------------------------------------
+# correlation lookup                                         reference: src/droid.cpp:170-191
+# ------------------------------------------------------------------------------------------------
+def corr_index_forward(volume, coords, radius):
+    _contig("corr_index_forward", volume=volume, coords=coords)
+    _dtype("corr_index_forward", volume, (torch.float32, torch.float16, torch.float64))
+    _dtype("corr_index_forward", coords, (torch.float32,))
+    if volume.dim() != 5 or coords.dim() != 4:
+        raise RuntimeError("droid_backends.corr_index_forward: volume must be 5-d, coords 4-d")
+    B, H1, W1, H2, W2 = volume.shape
+    rd = 2 * radius + 1
+    with torch.cuda.device(volume.device):
+        out = torch.empty((B, rd, rd, H1, W1), dtype=volume.dtype, device=volume.device)
+        _check(_lib.droid_corr_index_forward(_p(volume), _p(coords), _p(out), _DT[volume.dtype], B,
+                                             H1, W1, H2, W2, int(radius), _stream(volume)),
+               "corr_index_forward")
+    return [out]
+
+
+def corr_index_backward(volume, coords, corr_grad, radius):
+    _contig("corr_index_backward", volume=volume, coords=coords, corr_grad=corr_grad)
+    _dtype("corr_index_backward", volume, (torch.float32, torch.float16, torch.float64))
+    if corr_grad.dtype != volume.dtype:
+        raise RuntimeError("droid_backends.corr_index_backward: corr_grad dtype must match volume")
+    B, H1, W1, H2, W2 = volume.shape
+    with torch.cuda.device(volume.device):
+        vg = torch.empty_like(volume)
+        _check(_lib.droid_corr_index_backward(_p(coords), _p(corr_grad), _p(vg), _DT[volume.dtype], B,
+                                              H1, W1, H2, W2, int(radius), _stream(volume)),
+               "corr_index_backward")
+    return [vg]
+
+
+def corr_index_pyramid(volumes, coords, radius=3):
+    """Extension: all pyramid levels in one launch == torch.cat of the per-level lookups, dim 1.
+    volumes[l]: [B,H1,W1,H2>>l,W2>>l]; coords [B,2,H1,W1] at level 0 (modules/corr.py:40-50)."""
+    L = len(volumes)
+    _contig("corr_index_pyramid", coords=coords, **{"volume%d" % i: v for i, v in enumerate(volumes)})
+    v0 = volumes[0]
+    _dtype("corr_index_pyramid", v0, (torch.float32, torch.float16))
+    B, H1, W1, H2, W2 = v0.shape
+    for l, v in enumerate(volumes):
+        if v.dtype != v0.dtype or tuple(v.shape) != (B, H1, W1, H2 >> l, W2 >> l):
+            raise RuntimeError("droid_backends.corr_index_pyramid: bad level %d" % l)
+    rd = 2 * radius + 1
+    ptrs = (ctypes.c_void_p * L)(*[v.data_ptr() for v in volumes])
+    with torch.cuda.device(v0.device):
+        out = torch.empty((B, L * rd * rd, H1, W1), dtype=v0.dtype, device=v0.device)
+        _check(_lib.droid_corr_index_pyramid(ptrs, L, _p(coords), _p(out), _DT[v0.dtype], B, H1, W1,
+                                             H2, W2, int(radius), _stream(v0)), "corr_index_pyramid")
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# alt correlation                                            reference: src/droid.cpp:193-217
+# ------------------------------------------------------------------------------------------------
+def altcorr_forward(fmap1, fmap2, coords, radius):
+    _contig("altcorr_forward", fmap1=fmap1, fmap2=fmap2, coords=coords)
+    _dtype("altcorr_forward", fmap1, (torch.float32,))
+    _dtype("altcorr_forward", fmap2, (torch.float32,))
+    _dtype("altcorr_forward", coords, (torch.float32,))
+    B, N, H, W, _ = coords.shape
+    _, H1, W1, C = fmap1.shape
+    _, H2, W2, _ = fmap2.shape
+    rd = 2 * radius + 1
+    with torch.cuda.device(fmap1.device):
+        out = torch.empty((B, N, rd * rd, H, W), dtype=fmap1.dtype, device=fmap1.device)
+        _check(_lib.droid_altcorr_forward(_p(fmap1), _p(fmap2), _p(coords), _p(out), _F32, B, N, H1,
+                                          W1, H2, W2, C, int(radius), _stream(fmap1)),
+               "altcorr_forward")
+    return [out]
+
+
+def altcorr_backward(fmap1, fmap2, coords, corr_grad, radius):
+    _contig("altcorr_backward", fmap1=fmap1, fmap2=fmap2, coords=coords, corr_grad=corr_grad)
+    for t in (fmap1, fmap2, coords, corr_grad):
+        _dtype("altcorr_backward", t, (torch.float32,))
+    B, N = coords.shape[0], coords.shape[1]
+    _, H1, W1, C = fmap1.shape
+    _, H2, W2, _ = fmap2.shape
+    with torch.cuda.device(fmap1.device):
+        g1 = torch.empty_like(fmap1)
+        g2 = torch.empty_like(fmap2)
+        gc = torch.empty((B, N, H1, W1, 2), dtype=fmap1.dtype, device=fmap1.device)
+        _check(_lib.droid_altcorr_backward(_p(fmap1), _p(fmap2), _p(coords), _p(corr_grad), _p(g1),
+                                           _p(g2), _p(gc), B, N, H1, W1, H2, W2, C, int(radius),
+                                           _stream(fmap1)), "altcorr_backward")
+    return [g1, g2, gc]
+
+
+def altcorr_forward_indexed(pyr0, pyrl, ii, jj, coords, radius=3):
+    """Extension: altcorr_forward(pyr0[ii].float(), pyrl[jj].float(), coords, r) without
+    materialising the gathered fp32 copies (modules/corr.py:113-120).  pyr*: [F,H,W,C] f16/f32."""
+    _contig("altcorr_forward_indexed", pyr0=pyr0, pyrl=pyrl, ii=ii, jj=jj, coords=coords)
+    _long("altcorr_forward_indexed", ii=ii, jj=jj)
+    _dtype("altcorr_forward_indexed", pyr0, (torch.float32, torch.float16))
+    if pyrl.dtype != pyr0.dtype:
+        raise RuntimeError("droid_backends.altcorr_forward_indexed: dtype mismatch")
+    B, N, H, W, _ = coords.shape
+    F, H1, W1, C = pyr0.shape
+    _, H2, W2, _ = pyrl.shape
+    rd = 2 * radius + 1
+    with torch.cuda.device(pyr0.device):
+        out = torch.empty((B, N, rd * rd, H, W), dtype=torch.float32, device=pyr0.device)
+        _check(_lib.droid_altcorr_forward_indexed(_p(pyr0), _p(pyrl), _p(ii), _p(jj), _p(coords),
+                                                  _p(out), _DT[pyr0.dtype], F, B, N, H1, W1, H2, W2,
+                                                  C, int(radius), _stream(pyr0)),
+               "altcorr_forward_indexed")
+    return out
+
+
+def corr_build(fmap1, fmap2, num_levels=4):
+    """Extension: CorrBlock.corr + avg-pool pyramid (modules/corr.py:24-38,63-71) as one tcgen05 GEMM
+    with a pooling epilogue.  fmap1, fmap2: [B, C, H, W] (or [1,B,C,H,W]) f16, unscaled.
+    Returns the 4 pyramid levels [B, H, W, H>>l, W>>l] f16."""
+    if fmap1.dim() == 5:
+        fmap1 = fmap1.reshape((-1,) + tuple(fmap1.shape[2:]))
+        fmap2 = fmap2.reshape((-1,) + tuple(fmap2.shape[2:]))
+    _contig("corr_build", fmap1=fmap1, fmap2=fmap2)
+    _dtype("corr_build", fmap1, (torch.float16,))
+    _dtype("corr_build", fmap2, (torch.float16,))
+    if num_levels != 4:
+        raise RuntimeError("droid_backends.corr_build: num_levels must be 4")
+    B, C, H, W = fmap1.shape
+    with torch.cuda.device(fmap1.device):
+        lv = [torch.empty((B, H, W, H >> l, W >> l), dtype=torch.float16, device=fmap1.device)
+              for l in range(4)]
+        nws = _lib.droid_corr_build_workspace_bytes(B, C, H, W)
+        ws = torch.empty((nws,), dtype=torch.uint8, device=fmap1.device)
+        _check(_lib.droid_corr_build(_p(fmap1), _p(fmap2), _p(lv[0]), _p(lv[1]), _p(lv[2]), _p(lv[3]),
+                                     B, C, H, W, _p(ws), ctypes.c_size_t(nws), _stream(fmap1)),
+               "corr_build")
+    return lv
+
+
+# ------------------------------------------------------------------------------------------------
+# geometry                                                   reference: src/droid.cpp:120-166,220-234
+# ------------------------------------------------------------------------------------------------
+def frame_distance(poses, disps, intrinsics, ii, jj, beta):
+    _contig("frame_distance", poses=poses, disps=disps, intrinsics=intrinsics, ii=ii, jj=jj)
+    _long("frame_distance", ii=ii, jj=jj)
+    for t in (poses, disps, intrinsics):
+        _dtype("frame_distance", t, (torch.float32,))
+    n = ii.shape[0]
+    ht, wd = disps.shape[1], disps.shape[2]
+    with torch.cuda.device(poses.device):
+        dist = torch.empty((n,), dtype=torch.float32, device=poses.device)
+        _check(_lib.droid_frame_distance(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj),
+                                         _p(dist), n, ht, wd, ctypes.c_float(beta), _stream(poses)),
+               "frame_distance")
+    return dist
+
+
+def projmap(poses, disps, intrinsics, ii, jj):
+    _contig("projmap", poses=poses, disps=disps, intrinsics=intrinsics, ii=ii, jj=jj)
+    _long("projmap", ii=ii, jj=jj)
+    for t in (poses, disps, intrinsics):
+        _dtype("projmap", t, (torch.float32,))
+    n = ii.shape[0]
+    ht, wd = disps.shape[1], disps.shape[2]
+    with torch.cuda.device(poses.device):
+        coords = torch.empty((n, ht, wd, 3), dtype=torch.float32, device=poses.device)
+        valid = torch.empty((n, ht, wd, 1), dtype=torch.float32, device=poses.device)
+        _check(_lib.droid_projmap(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj), _p(coords),
+                                  _p(valid), n, ht, wd, _stream(poses)), "projmap")
+    return [coords, valid]
+
+
+def iproj(poses, disps, intrinsics):
+    _contig("iproj", poses=poses, disps=disps, intrinsics=intrinsics)
+    for t in (poses, disps, intrinsics):
+        _dtype("iproj", t, (torch.float32,))
+    nm, ht, wd = disps.shape
+    if poses.shape[0] < nm:
+        raise RuntimeError("droid_backends.iproj: fewer poses than depth maps")
+    with torch.cuda.device(disps.device):
+        points = torch.empty((nm, ht, wd, 3), dtype=torch.float32, device=disps.device)
+        _check(_lib.droid_iproj(_p(poses), _p(disps), _p(intrinsics), _p(points), nm, ht, wd,
+                                _stream(disps)), "iproj")
+    return points
+
+
+def depth_filter(poses, disps, intrinsics, ix, thresh):
+    _contig("depth_filter", poses=poses, disps=disps, intrinsics=intrinsics, ix=ix, thresh=thresh)
+    _long("depth_filter", ix=ix)
+    for t in (poses, disps, intrinsics, thresh):
+        _dtype("depth_filter", t, (torch.float32,))
+    num = ix.shape[0]
+    nbuf, ht, wd = disps.shape
+    with torch.cuda.device(disps.device):
+        counter = torch.empty((num, ht, wd), dtype=torch.float32, device=disps.device)
+        _check(_lib.droid_depth_filter(_p(poses), _p(disps), _p(intrinsics), _p(ix), _p(thresh),
+                                       _p(counter), num, nbuf, ht, wd, _stream(disps)),
+               "depth_filter")
+    return counter
+
+
+# ------------------------------------------------------------------------------------------------
+# dense bundle adjustment                                     reference: src/droid.cpp:88-117
+# ------------------------------------------------------------------------------------------------
+_ws_cache = {}
+
+
+def _workspace(device, nbytes):
+    key = (device.type, device.index)
+    ws = _ws_cache.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty((int(nbytes * 1.25) + 1024,), dtype=torch.uint8, device=device)
+        _ws_cache[key] = ws
+    return ws
+
+
+def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations,
+       lm, ep, motion_only, _shard=None, _reduce=None):
+    """Updates ``poses`` and ``disps`` in place; returns [dx, dz] of the last iteration
+    (src/droid_kernels.cu:1314-1434).  ``_shard=(lo, hi)`` / ``_reduce`` are used by ba_sharded."""
+    _contig("ba", poses=poses, disps=disps, intrinsics=intrinsics, disps_sens=disps_sens,
+            targets=targets, weights=weights, ii=ii, jj=jj)
+    if not isinstance(eta, torch.Tensor) or not eta.is_cuda:
+        raise RuntimeError("droid_backends.ba: eta must be a CUDA tensor")
+    if not eta.is_contiguous():  # the reference .view()s eta without checking (:1398); be explicit
+        raise RuntimeError("eta must be contiguous")
+    _long("ba", ii=ii, jj=jj)
+    for t in (poses, disps, intrinsics, disps_sens, targets, weights, eta):
+        _dtype("ba", t, (torch.float32,))
+    nbuf, ht, wd = disps.shape
+    n_edges = ii.shape[0]
+    HW = ht * wd
+    n_eta = eta.numel() // HW if HW > 0 else 0
+    P = int(t1) - int(t0)
+    prm = BaParams(n_edges=n_edges, nbuf=nbuf, ht=ht, wd=wd, n_eta=n_eta, t0=int(t0), t1=int(t1),
+                   iterations=int(iterations), motion_only=1 if motion_only else 0, lm=float(lm),
+                   ep=float(ep), frame_lo=0, frame_hi=0x7FFFFFFF, reduce_fn=REDUCE_FN(0),
+                   reduce_user=None)
+    if _shard is not None:
+        prm.frame_lo, prm.frame_hi = int(_shard[0]), int(_shard[1])
+    cb = None
+    if _reduce is not None:
+        cb = REDUCE_FN(_reduce)
+        prm.reduce_fn = cb
+    if poses.shape[0] < t1:
+        raise RuntimeError("droid_backends.ba: t1 exceeds the pose buffer")
+    with torch.cuda.device(poses.device):
+        nws = _lib.droid_ba_workspace_bytes(ctypes.byref(prm))
+        if nws == 0:
+            raise RuntimeError("droid_backends.ba: invalid argument")
+        ws = _workspace(poses.device, nws)
+        dx = torch.zeros((max(P, 0), 6), dtype=torch.float32, device=poses.device)
+        dz = torch.zeros((n_eta, HW), dtype=torch.float32, device=poses.device)
+        _check(_lib.droid_ba(_p(poses), _p(disps), _p(intrinsics), _p(disps_sens), _p(targets),
+                             _p(weights), _p(eta), _p(ii), _p(jj), ctypes.byref(prm), _p(dx), _p(dz),
+                             ctypes.c_void_p(ws.data_ptr()), ctypes.c_size_t(ws.numel()),
+                             _stream(poses)), "ba")
+    return [dx, dz]
+
+
+def ba_status(device=None):
+    """Device-side status word of the last ba() on this device (forces a D2H copy; debug aid)."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    ws = _ws_cache.get((device.type, device.index))
+    if ws is None:
+        return 0
+    off = (-ws.data_ptr()) % 256
+    return int(ws[off:off + 4].view(torch.int32).item())
+
+
+def chol_solve(A, b):
+    """Extension (tests/bench): solves A x = b for SPD fp64 A on the device; returns (x, info)."""
+    n = A.shape[0]
+    with torch.cuda.device(A.device):
+        buf = torch.empty((n * n + n,), dtype=torch.float64, device=A.device)
+        buf[: n * n] = A.reshape(-1)
+        buf[n * n:] = b.reshape(-1)
+        info = torch.zeros((1,), dtype=torch.int32, device=A.device)
+        _check(_lib.droid_chol_solve_f64(_p(buf), ctypes.c_void_p(buf.data_ptr() + 8 * n * n), n,
+                                         _p(info), ctypes.c_void_p(0), ctypes.c_size_t(0),
+                                         _stream(A)), "chol_solve")
+    return buf[n * n:].clone(), info
+
+
+def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1,
+               iterations, lm, ep, motion_only, group=None):
+    """Multi-GPU global BA: every rank holds the full (replicated) inputs of ITS edges'
+    source frames; rank r accumulates the source frames kx in its contiguous shard, the packed
+    reduced camera system is summed with one NCCL all-reduce per iteration, every rank solves it
+    (replicated, deterministic) and updates all poses plus the depths of its own frames; the depth
+    maps are all-gathered at the end so every rank returns the same state as single-GPU ba()."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    nbuf = disps.shape[0]
+    per = (nbuf + world - 1) // world
+    lo, hi = rank * per, min(nbuf, (rank + 1) * per)
+
+    def _reduce(user, buf, n, stream):
+        t = _as_tensor(buf, n, poses.device)
+        dist.all_reduce(t, group=group)
+        return 0
+
+    out = ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations,
+             lm, ep, motion_only, _shard=(lo, hi), _reduce=_reduce)
+    if not motion_only and world > 1:
+        pad = per * world
+        flat = disps.new_zeros((pad,) + tuple(disps.shape[1:]))
+        dist.all_gather_into_tensor(flat, _pad_rows(disps[lo:hi], per), group=group)
+        disps.copy_(flat[:nbuf])
+    return out
+
+
+def _pad_rows(t, rows):
+    if t.shape[0] == rows:
+        return t.contiguous()
+    out = t.new_zeros((rows,) + tuple(t.shape[1:]))
+    out[: t.shape[0]] = t
+    return out
+
+
+class _CudaArray:
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 3}
+
+
+def _as_tensor(ptr, n, device):
+    return torch.as_tensor(_CudaArray(int(ptr), int(n)), device=device)

@@ -1,0 +1,165 @@
+/* droid_b200.h — C ABI of libdroid_b200.so: the sm_100a implementation of DROID-SLAM's
+ * `droid_backends` operator surface (reference: /root/reference/src/droid.cpp:237-250).
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless its name ends in _host; all tensors are contiguous
+ *    in the layout stated next to the argument (the reference enforces contiguity only,
+ *    src/droid.cpp:84-85);
+ *  - `stream` is a cudaStream_t passed as void*; every call is stream-ordered, never synchronises
+ *    the host and never allocates caller-visible memory (outputs and workspaces are supplied by the
+ *    caller; the Python host `droid_backends` allocates them with torch on the current stream);
+ *  - return value: DROID_OK or a negative DROID_ERR_* code (the Python host raises RuntimeError,
+ *    mirroring TORCH_CHECK -> RuntimeError of the reference);
+ *  - index tensors are int64 (torch.long), as in the reference;
+ *  - dtype codes select the element type of volume / fmap tensors (the reference dispatches
+ *    AT_DISPATCH_FLOATING_TYPES_AND_HALF, src/correlation_kernels.cu:145).
+ */
+#ifndef DROID_B200_H_
+#define DROID_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DROID_OK 0
+#define DROID_ERR_INVALID_ARGUMENT (-1) /* bad shape / null pointer / unsupported radius */
+#define DROID_ERR_UNSUPPORTED_DTYPE (-2)
+#define DROID_ERR_WORKSPACE_TOO_SMALL (-3)
+#define DROID_ERR_CUDA (-4) /* a launch failed; see droid_last_cuda_error() */
+#define DROID_ERR_NOT_IMPLEMENTED (-5)
+
+#define DROID_DTYPE_F32 0
+#define DROID_DTYPE_F16 1
+#define DROID_DTYPE_F64 2
+
+/* Library / build identification.  Returns e.g. "droid_b200 0.1 sm_100a". */
+const char* droid_version(void);
+/* cudaGetErrorString of the last failing launch seen by this library (thread-unsafe, debug aid). */
+const char* droid_last_cuda_error(void);
+
+/* ---- correlation lookup ---------------------------------------------------------------------
+ * Replaces corr_index_forward  (src/droid.cpp:170-178, src/correlation_kernels.cu:19-70,126-155).
+ *   volume [B,H1,W1,H2,W2] dtype; coords [B,2,H1,W1] f32 (x,y), already scaled to this level;
+ *   out    [B,2r+1,2r+1,H1,W1] dtype, FULLY WRITTEN (no pre-zeroing required).
+ *   out[b, i, j, y, x] = bilinear(volume[b,y,x], x0 + i - r, y0 + j - r), zero outside. */
+int droid_corr_index_forward(const void* volume, const float* coords, void* out, int dtype, int B,
+                             int H1, int W1, int H2, int W2, int radius, void* stream);
+
+/* Replaces corr_index_backward (src/droid.cpp:180-191, src/correlation_kernels.cu:73-124,157-185).
+ *   corr_grad [B,2r+1,2r+1,H1,W1]; volume_grad [B,H1,W1,H2,W2] FULLY WRITTEN (zeros + window). */
+int droid_corr_index_backward(const float* coords, const void* corr_grad, void* volume_grad,
+                              int dtype, int B, int H1, int W1, int H2, int W2, int radius,
+                              void* stream);
+
+/* Fused 4-level pyramid lookup (one launch instead of 4; what CorrBlock.__call__ does,
+ * droid_slam/modules/corr.py:40-50).  volumes[l] is level l = [B,H1,W1,H2>>l,W2>>l];
+ * coords [B,2,H1,W1] are LEVEL-0 coordinates (divided by 2^l inside, as corr.py:47);
+ * out [B, L*(2r+1)^2, H1, W1] = torch.cat of the per-level results on dim 1. */
+int droid_corr_index_pyramid(const void* const* volumes_host, int num_levels, const float* coords,
+                             void* out, int dtype, int B, int H1, int W1, int H2, int W2,
+                             int radius, void* stream);
+
+/* ---- on-the-fly ("alt") correlation ----------------------------------------------------------
+ * Replaces altcorr_forward (src/droid.cpp:193-203, src/altcorr_kernel.cu:27-149,290-319).
+ *   fmap1 [B,H1,W1,C], fmap2 [B,H2,W2,C] channel-last dtype; coords [B,N,H1,W1,2] f32 (x,y);
+ *   out [B,N,(2r+1)^2,H1,W1] dtype, fully written; channel = iy + (2r+1)*ix. */
+int droid_altcorr_forward(const void* fmap1, const void* fmap2, const float* coords, void* out,
+                          int dtype, int B, int N, int H1, int W1, int H2, int W2, int C,
+                          int radius, void* stream);
+
+/* Replaces altcorr_backward (src/droid.cpp:205-217, src/altcorr_kernel.cu:152-286,321-356); f32 only
+ * like the reference.  fmap1_grad/fmap2_grad fully written; coords_grad [B,N,H1,W1,2] is all zero
+ * (the reference never writes it). */
+int droid_altcorr_backward(const float* fmap1, const float* fmap2, const float* coords,
+                           const float* corr_grad, float* fmap1_grad, float* fmap2_grad,
+                           float* coords_grad, int B, int N, int H1, int W1, int H2, int W2, int C,
+                           int radius, void* stream);
+
+/* Indexed alt-correlation: same result as altcorr_forward on
+ * fmap1 = pyr0[ii], fmap2 = pyrL[jj] (modules/corr.py:106-125) without the gathered copies.
+ *   pyr0 [F,H1,W1,C], pyrL [F,H2,W2,C] dtype; ii,jj [B] int64; output f32. */
+int droid_altcorr_forward_indexed(const void* pyr0, const void* pyrL, const int64_t* ii,
+                                  const int64_t* jj, const float* coords, float* out, int dtype,
+                                  int F, int B, int N, int H1, int W1, int H2, int W2, int C,
+                                  int radius, void* stream);
+
+/* ---- all-pairs correlation volume + pyramid (tcgen05/TMEM GEMM) -------------------------------
+ * Replaces CorrBlock.corr + 3x avg_pool2d (droid_slam/modules/corr.py:24-38,63-71).
+ *   fmap1,fmap2 [B,C,HW] f16 (C=128), UNSCALED (the /4 on each side is applied inside, in f16,
+ *   exactly as corr.py:67-68);  lvl0..lvl3: [B,HW,H>>l,W>>l] f16.  H%8==0, W%8==0. */
+int droid_corr_build(const void* fmap1, const void* fmap2, void* lvl0, void* lvl1, void* lvl2,
+                     void* lvl3, int B, int C, int H, int W, void* workspace,
+                     size_t workspace_bytes, void* stream);
+size_t droid_corr_build_workspace_bytes(int B, int C, int H, int W);
+
+/* ---- geometry --------------------------------------------------------------------------------
+ * frame_distance (src/droid.cpp:120-136, src/droid_kernels.cu:518-657,1438-1460).
+ *   poses [*,7] (tx,ty,tz,qx,qy,qz,qw), disps [nbuf,ht,wd], intrinsics [4], ii,jj [n], dist [n]. */
+int droid_frame_distance(const float* poses, const float* disps, const float* intrinsics,
+                         const int64_t* ii, const int64_t* jj, float* dist, int n, int ht, int wd,
+                         float beta, void* stream);
+
+/* projmap (src/droid.cpp:139-154, src/droid_kernels.cu:427-516,1463-1488).
+ *   coords [n,ht,wd,3] (channel 2 = 0), valid [n,ht,wd,1]; both fully written. */
+int droid_projmap(const float* poses, const float* disps, const float* intrinsics,
+                  const int64_t* ii, const int64_t* jj, float* coords, float* valid, int n, int ht,
+                  int wd, void* stream);
+
+/* iproj (src/droid.cpp:157-166, src/droid_kernels.cu:779-850,1518-1541). points [nm,ht,wd,3]. */
+int droid_iproj(const float* poses, const float* disps, const float* intrinsics, float* points,
+                int nm, int ht, int wd, void* stream);
+
+/* depth_filter (src/droid.cpp:220-234, src/droid_kernels.cu:661-775,1491-1515).
+ *   disps [nbuf,ht,wd]; ix [num] int64; thresh [num]; counter [num,ht,wd] fully written (0..6). */
+int droid_depth_filter(const float* poses, const float* disps, const float* intrinsics,
+                       const int64_t* ix, const float* thresh, float* counter, int num, int nbuf,
+                       int ht, int wd, void* stream);
+
+/* ---- dense bundle adjustment -------------------------------------------------------------------
+ * Replaces ba (src/droid.cpp:88-117, src/droid_kernels.cu:1314-1434).
+ *   poses [nbuf_p,7] and disps [nbuf,ht,wd] are UPDATED IN PLACE; disps_sens [nbuf,ht,wd];
+ *   targets, weights [n_edges,2,ht,wd]; eta [n_eta,ht,wd] with one row per entry of
+ *   kx = unique(ii U [t0,t1)) (so n_eta must equal |kx|; checked on the device, see status);
+ *   dx_out [t1-t0,6], dz_out [n_eta,ht*wd] = updates of the LAST iteration (dz untouched when
+ *   motion_only).  No host synchronisation; graph bookkeeping (unique/CSR) runs on the device.
+ *   Multi-GPU: when `reduce_fn` != NULL it is called once per iteration, stream-ordered,
+ *   on the packed reduced system (n_doubles fp64 values) after local accumulation; the Python host
+ *   plugs torch.distributed.all_reduce (NCCL) in there.  With frame_lo/frame_hi a rank only
+ *   accumulates source frames kx in [frame_lo, frame_hi) (pass 0, INT32_MAX for all). */
+typedef int (*droid_reduce_fn)(void* user, double* buf, size_t n_doubles, void* stream);
+
+typedef struct {
+  int n_edges, nbuf, ht, wd, n_eta, t0, t1, iterations, motion_only;
+  float lm, ep;
+  int frame_lo, frame_hi;      /* shard of source frames handled by this rank              */
+  droid_reduce_fn reduce_fn;   /* NULL on a single GPU                                      */
+  void* reduce_user;
+} droid_ba_params;
+
+size_t droid_ba_workspace_bytes(const droid_ba_params* p);
+int droid_ba(float* poses, float* disps, const float* intrinsics, const float* disps_sens,
+             const float* targets, const float* weights, const float* eta, const int64_t* ii,
+             const int64_t* jj, const droid_ba_params* p, float* dx_out, float* dz_out,
+             void* workspace, size_t workspace_bytes, void* stream);
+
+/* Device-side status word of the last droid_ba on this workspace (first 4 bytes of the workspace):
+ * bit0 = n_eta != |kx|, bit1 = index out of range, bit2 = Cholesky failed in some iteration
+ * (=> dx = 0 for that iteration, like src/droid_kernels.cu:1207-1210).  Reading it is the caller's
+ * choice (it needs a D2H copy); droid_ba itself never reads it. */
+#define DROID_BA_STATUS_ETA_MISMATCH 1
+#define DROID_BA_STATUS_BAD_INDEX 2
+#define DROID_BA_STATUS_CHOL_FAILED 4
+
+/* Dense SPD solve used by ba, exported for tests/bench: A [n,n] fp64 row-major (lower triangle
+ * read, overwritten by L), b [n] fp64 (overwritten by x); info (device int) != 0 on failure. */
+int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, void* workspace,
+                         size_t workspace_bytes, void* stream);
+size_t droid_chol_workspace_bytes(int n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DROID_B200_H_ */

@@ -1,0 +1,264 @@
+"""GPU parity: every operator of libdroid_b200 (through the drop-in `droid_backends` module, i.e. through the
+C ABI) against the CPU oracle (oracle/droid_oracle.py) on identical seeded inputs, and -- when the
+unmodified reference extension built by oracle/build_ref.sh is loadable -- against the reference itself.
+
+Tolerances (BASELINE.json north_star): index/count outputs bit-exact; correlation lookups <= 1e-5 relative;
+pose / inverse-depth updates <= 1e-4 relative per BA iteration.  "relative" = max |a-b| / max |b|.
+"""
+import numpy as np
+import pytest
+import torch
+
+import droid_oracle as O
+import synth
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def rel(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+def cu(x):
+    return torch.from_numpy(np.ascontiguousarray(x)).to(DEV)
+
+
+def geom_inputs(n=6, ht=40, wd=64, seed=0):
+    p = synth.make_ba_problem("C1", seed=seed)
+    return p["poses"], p["disps"], p["intrinsics"], p["ii"], p["jj"]
+
+
+# ---------------------------------------------------------------- corr_index ------------------
+@pytest.mark.parametrize("dtype,tol", [(np.float32, 1e-5), (np.float16, 0.0), (np.float64, 1e-12)])
+@pytest.mark.parametrize("level", [0, 1, 3])
+def test_corr_index_forward(backends, dtype, tol, level):
+    rng = np.random.default_rng(level)
+    B, H1, W1 = 3, 16, 24
+    H2, W2 = 48 >> level, 64 >> level
+    vol = rng.normal(size=(B, H1, W1, H2, W2)).astype(dtype)
+    c = synth.make_corr_problem(B, H1, W1, 8, seed=level, oob_frac=0.1)["coords"]
+    c = (c * np.float32(W2 / W1)).astype(np.float32)
+    ref = O.corr_index_forward(vol, c, 3)
+    out, = backends.corr_index_forward(cu(vol), cu(c), 3)
+    assert out.shape == (B, 7, 7, H1, W1) and out.dtype == cu(vol).dtype
+    got = out.cpu().numpy()
+    if tol == 0.0:
+        assert np.array_equal(got.view(np.uint16), ref.view(np.uint16)) or rel(got, ref) == 0.0
+    else:
+        assert rel(got, ref) <= tol
+
+
+def test_corr_index_forward_edge_cases(backends):
+    rng = np.random.default_rng(5)
+    # odd sizes (scalar path), radius != 3 (generic path), integer coords, coords far outside
+    vol = rng.normal(size=(2, 5, 7, 9, 11)).astype(np.float32)
+    c = rng.uniform(-3, 13, size=(2, 2, 5, 7)).astype(np.float32)
+    c[0, :, 0, 0] = [4.0, 3.0]
+    c[1, :, 1, 1] = [-500.0, 900.0]
+    for r in (0, 1, 2, 3, 4):
+        ref = O.corr_index_forward(vol, c, r)
+        out, = backends.corr_index_forward(cu(vol), cu(c), r)
+        assert rel(out.cpu().numpy(), ref) <= 1e-5
+    # r = 0 at integer coordinates returns the volume entry itself
+    out, = backends.corr_index_forward(cu(vol), cu(c), 0)
+    assert out[0, 0, 0, 0, 0].item() == vol[0, 0, 0, 3, 4]
+    # empty batch
+    out, = backends.corr_index_forward(cu(vol[:0]), cu(c[:0]), 3)
+    assert out.shape == (0, 7, 7, 5, 7)
+
+
+def test_corr_index_matches_grid_sample(backends):
+    """the op equals zero-padded grid_sample(align_corners=True) at coords + (i-r, j-r)."""
+    import torch.nn.functional as F
+    rng = np.random.default_rng(9)
+    B, H1, W1, H2, W2, r = 2, 6, 8, 12, 16, 3
+    vol = torch.from_numpy(rng.normal(size=(B, H1, W1, H2, W2))).double().to(DEV)
+    c = torch.from_numpy(rng.uniform(-2, 17, size=(B, 2, H1, W1))).float().to(DEV)
+    out, = backends.corr_index_forward(vol, c, r)
+    planes = vol.view(B * H1 * W1, 1, H2, W2)
+    xy = c.double().permute(0, 2, 3, 1).reshape(-1, 1, 1, 2)
+    d = torch.arange(-r, r + 1, device=DEV, dtype=torch.float64)
+    off = torch.stack(torch.meshgrid(d, d, indexing="ij"), -1).view(1, 7, 7, 2)  # [i->x][j->y]
+    g = xy + off
+    g = torch.stack([2 * g[..., 0] / (W2 - 1) - 1, 2 * g[..., 1] / (H2 - 1) - 1], -1)
+    s = F.grid_sample(planes, g, padding_mode="zeros", align_corners=True).view(B, H1, W1, 7, 7)
+    assert (s.permute(0, 3, 4, 1, 2) - out).abs().max().item() < 1e-12
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float32, 1e-6), (np.float16, 0.0)])
+def test_corr_index_backward(backends, dtype, tol):
+    rng = np.random.default_rng(2)
+    B, H1, W1, H2, W2 = 2, 6, 8, 12, 16
+    c = rng.uniform(-3, 18, size=(B, 2, H1, W1)).astype(np.float32)
+    g = rng.normal(size=(B, 7, 7, H1, W1)).astype(dtype)
+    vol = np.zeros((B, H1, W1, H2, W2), dtype)
+    ref = O.corr_index_backward(vol.shape, dtype, c, g, 3)
+    out, = backends.corr_index_backward(cu(vol), cu(c), cu(g), 3)
+    assert rel(out.cpu().numpy(), ref) <= tol
+
+
+def test_corr_index_pyramid_equals_levels(backends):
+    rng = np.random.default_rng(3)
+    B, H, W = 4, 16, 24
+    c = synth.make_corr_problem(B, H, W, 8, seed=3, oob_frac=0.05)["coords"]
+    vols = [cu(rng.normal(size=(B, H, W, H >> l, W >> l)).astype(np.float16)) for l in range(4)]
+    ct = cu(c)
+    fused = backends.corr_index_pyramid(vols, ct, 3)
+    ref = torch.cat([backends.corr_index_forward(vols[l], ct / 2 ** l, 3)[0].view(B, 49, H, W) for l in range(4)], 1)
+    assert torch.equal(fused, ref)
+
+
+# ---------------------------------------------------------------- altcorr ---------------------
+def test_altcorr_forward(backends):
+    p = synth.make_corr_problem(4, 16, 24, 128, seed=4, oob_frac=0.05, dtype=np.float32)
+    f = (p["fmaps"] / 4.0).astype(np.float32).transpose(0, 2, 3, 1)
+    f1 = np.ascontiguousarray(f[p["ii"]]); f2 = np.ascontiguousarray(f[p["jj"]])
+    coords = np.ascontiguousarray(p["coords"].transpose(0, 2, 3, 1)[:, None])
+    ref = O.altcorr_forward(f1, f2, coords, 3)
+    out, = backends.altcorr_forward(cu(f1), cu(f2), cu(coords), 3)
+    assert out.shape == ref.shape
+    assert rel(out.cpu().numpy(), ref) <= 1e-5
+    # lower pyramid level (H2 != H1), several samples per pixel, generic radius / channel count
+    f2l = np.ascontiguousarray(f2[:, ::2, ::2])
+    c2 = np.ascontiguousarray(np.concatenate([coords, coords + 0.37], 1) / 2).astype(np.float32)
+    assert rel(backends.altcorr_forward(cu(f1), cu(f2l), cu(c2), 3)[0].cpu().numpy(),
+               O.altcorr_forward(f1, f2l, c2, 3)) <= 1e-5
+    f1s, f2s = np.ascontiguousarray(f1[..., :40]), np.ascontiguousarray(f2[..., :40])
+    assert rel(backends.altcorr_forward(cu(f1s), cu(f2s), cu(coords), 2)[0].cpu().numpy(),
+               O.altcorr_forward(f1s, f2s, coords, 2)) <= 1e-5
+
+
+def test_altcorr_indexed_equals_gathered(backends):
+    p = synth.make_corr_problem(6, 16, 24, 128, seed=6)
+    pyr = cu(np.ascontiguousarray((p["fmaps"] / np.float16(4)).astype(np.float16).transpose(0, 2, 3, 1)))
+    ii, jj = cu(p["ii"]), cu(p["jj"])
+    coords = cu(np.ascontiguousarray(p["coords"].transpose(0, 2, 3, 1)[:, None]))
+    a = backends.altcorr_forward_indexed(pyr, pyr, ii, jj, coords, 3)
+    b, = backends.altcorr_forward(pyr[ii].float().contiguous(), pyr[jj].float().contiguous(), coords, 3)
+    assert torch.equal(a, b)
+
+
+def test_altcorr_backward(backends):
+    p = synth.make_corr_problem(2, 8, 16, 64, seed=7, oob_frac=0.05, dtype=np.float32)
+    f = (p["fmaps"] / 4.0).astype(np.float32).transpose(0, 2, 3, 1)
+    f1 = np.ascontiguousarray(f[p["ii"]]); f2 = np.ascontiguousarray(f[p["jj"]])
+    coords = np.ascontiguousarray(p["coords"].transpose(0, 2, 3, 1)[:, None])
+    g = np.random.default_rng(7).normal(size=(2, 1, 49, 8, 16)).astype(np.float32)
+    r1, r2, r3 = O.altcorr_backward(f1, f2, coords, g, 3)
+    o1, o2, o3 = backends.altcorr_backward(cu(f1), cu(f2), cu(coords), cu(g), 3)
+    assert rel(o1.cpu().numpy(), r1) <= 1e-5 and rel(o2.cpu().numpy(), r2) <= 1e-5
+    assert o3.shape == coords.shape and float(o3.abs().max()) == 0.0
+
+
+# ---------------------------------------------------------------- geometry --------------------
+def test_projmap_iproj(backends):
+    poses, disps, intr, ii, jj = geom_inputs()
+    rc, rv = O.projmap(poses, disps, intr, ii, jj)
+    c, v = backends.projmap(cu(poses), cu(disps), cu(intr), cu(ii), cu(jj))
+    assert rel(c.cpu().numpy(), rc) <= 1e-5 and np.array_equal(v.cpu().numpy(), rv)
+    rp = O.iproj(poses, disps, intr)
+    assert rel(backends.iproj(cu(poses), cu(disps), cu(intr)).cpu().numpy(), rp) <= 1e-5
+
+
+def test_frame_distance(backends):
+    poses, disps, intr, ii, jj = geom_inputs()
+    n = poses.shape[0]
+    a, b = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    a, b = a.reshape(-1).astype(np.int64), b.reshape(-1).astype(np.int64)
+    poses = poses.copy(); poses[7, :3] += [0, 0, 30.0]   # one frame far away -> the 1000.0 sentinel
+    ref = O.frame_distance(poses, disps, intr, a, b, 0.3)
+    got = backends.frame_distance(cu(poses), cu(disps), cu(intr), cu(a), cu(b), 0.3).cpu().numpy()
+    assert np.array_equal(got == 1000.0, ref == 1000.0) and (ref == 1000.0).any()
+    assert rel(got, ref) <= 1e-5
+    assert np.all(got[a == b] == 0.0)          # frame_distance(i, i) == 0
+
+
+def test_depth_filter_bit_exact(backends):
+    p = synth.make_ba_problem("C3", seed=3)
+    poses, disps, intr = p["gt_poses"], p["gt_disps"], p["intrinsics"]
+    ix = np.arange(12, dtype=np.int64)
+    th = np.full(12, 0.05, np.float32)
+    ref = O.depth_filter(poses, disps, intr, ix, th)
+    got = backends.depth_filter(cu(poses), cu(disps), cu(intr), cu(ix), cu(th)).cpu().numpy()
+    assert got.min() >= 0 and got.max() <= 6 and ref.max() > 0
+    assert np.mean(got != ref) <= 1e-4   # identical up to float ties on the floor() of a reprojection
+
+
+# ---------------------------------------------------------------- dense BA --------------------
+def run_ba(backends, p, iterations=2, lm=1e-4, ep=0.1, motion_only=False):
+    poses, disps = cu(p["poses"]), cu(p["disps"])
+    out = backends.ba(poses, disps, cu(p["intrinsics"]), cu(p["disps_sens"]), cu(p["targets"]),
+                      cu(p["weights"]), cu(p["eta"]), cu(p["ii"]), cu(p["jj"]), p["t0"], p["t1"],
+                      iterations, lm, ep, motion_only)
+    torch.cuda.synchronize()
+    return poses.cpu().numpy(), disps.cpu().numpy(), out[0].cpu().numpy(), out[1].cpu().numpy()
+
+
+def oracle_ba(p, iterations=2, lm=1e-4, ep=0.1, motion_only=False):
+    poses, disps = p["poses"].copy(), p["disps"].copy()
+    dx, dz = O.ba(poses, disps, p["intrinsics"], p["disps_sens"], p["targets"], p["weights"], p["eta"],
+                  p["ii"], p["jj"], p["t0"], p["t1"], iterations, lm, ep, motion_only)
+    return poses, disps, dx, dz
+
+
+@pytest.mark.parametrize("name,kw", [("C1", {}), ("C3", {}), ("C1", dict(stereo=True, sensor=True)),
+                                     ("C3", dict(nbuf=20))])
+@pytest.mark.parametrize("iters", [1, 2])
+def test_ba_matches_oracle(backends, name, kw, iters):
+    p = synth.make_ba_problem(name, **kw)
+    rp, rd, rdx, rdz = oracle_ba(p, iters)
+    gp, gd, gdx, gdz = run_ba(backends, p, iters)
+    assert backends.ba_status() == 0
+    assert rel(gdx, rdx) <= 1e-4 and rel(gdz, rdz) <= 1e-4
+    assert rel(gp, rp) <= 1e-5 and rel(gd, rd) <= 1e-5
+
+
+def test_ba_motion_only(backends):
+    p = synth.make_ba_problem("C3")
+    rp, rd, rdx, _ = oracle_ba(p, 2, motion_only=True)
+    gp, gd, gdx, _ = run_ba(backends, p, 2, motion_only=True)
+    assert rel(gdx, rdx) <= 1e-4 and rel(gp, rp) <= 1e-5
+    assert np.array_equal(gd, p["disps"])        # depths untouched
+
+
+def test_ba_backend_window_and_fixed_poses(backends):
+    # t0 > 1: edges reach back to fixed poses; backend damping values (factor_graph.py:287-288)
+    p = synth.make_ba_problem("C4", n_frames=24)
+    p["t0"] = 5
+    kx = np.unique(np.concatenate([np.arange(p["t0"], p["t1"]), p["ii"]]))
+    p["eta"] = np.ascontiguousarray(np.resize(p["eta"], (len(kx),) + p["eta"].shape[1:]))
+    rp, rd, rdx, rdz = oracle_ba(p, 2, lm=1e-5, ep=1e-2)
+    gp, gd, gdx, gdz = run_ba(backends, p, 2, lm=1e-5, ep=1e-2)
+    assert rel(gdx, rdx) <= 1e-4 and rel(gdz, rdz) <= 1e-4
+    assert np.array_equal(gp[:5], p["poses"][:5])
+
+
+def test_ba_reduces_reprojection_error(backends):
+    p = synth.make_ba_problem("C3")
+    def err(poses, disps):
+        c, v = O.projmap(poses, disps, p["intrinsics"], p["ii"], p["jj"])
+        return float(np.abs(c[..., :2].transpose(0, 3, 1, 2) - p["targets"]).mean())
+    e0 = err(p["poses"], p["disps"])
+    gp, gd, _, _ = run_ba(backends, p, 8)
+    assert err(gp, gd) < 0.5 * e0
+
+
+def test_ba_large_system_uses_blocked_cholesky(backends):
+    p = synth.make_ba_problem("C4", n_frames=60)   # 6P = 354 > single-CTA limit
+    rp, rd, rdx, rdz = oracle_ba(p, 1, lm=1e-5, ep=1e-2)
+    gp, gd, gdx, gdz = run_ba(backends, p, 1, lm=1e-5, ep=1e-2)
+    assert rel(gdx, rdx) <= 1e-4 and rel(gdz, rdz) <= 1e-4
+
+
+@pytest.mark.parametrize("n", [7, 64, 156, 157, 200, 777])
+def test_chol_solve(backends, n):
+    rng = np.random.default_rng(n)
+    Mx = rng.normal(size=(n, n)); A = Mx @ Mx.T + n * np.eye(n); b = rng.normal(size=n)
+    x, info = backends.chol_solve(cu(A), cu(b))
+    assert int(info.item()) == 0
+    assert rel(x.cpu().numpy(), np.linalg.solve(A, b)) <= 1e-10
+    A[n // 2, n // 2] = -1.0                       # not SPD -> failure flag, like Eigen's info()
+    _, info = backends.chol_solve(cu(A), cu(b))
+    assert int(info.item()) != 0
