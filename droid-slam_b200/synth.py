@@ -182,13 +182,13 @@ def make_corr_problem(n_edges=24, ht=48, wd=64, dim=128, seed=1234, oob_frac=0.0
     lookup coordinates = pixel grid + smooth flow in [-8, 8] px (+ optionally a fraction far outside)."""
     rng = np.random.default_rng(seed)
     n_frames = max(2, n_edges // 4 + 3)
-    base = rng.normal(size=(n_frames, dim, ht // 4, wd // 4))
-    fm = np.repeat(np.repeat(base, 4, axis=2), 4, axis=3) + 0.5 * rng.normal(size=(n_frames, dim, ht, wd))
+    base = rng.normal(size=(n_frames, dim, (ht + 3) // 4, (wd + 3) // 4))
+    fm = np.repeat(np.repeat(base, 4, axis=2), 4, axis=3)[:, :, :ht, :wd] + 0.5 * rng.normal(size=(n_frames, dim, ht, wd))
     ii = np.array([e % (n_frames - 2) for e in range(n_edges)], np.int64)
     jj = np.array([ii[e] + 1 + (e % 2) for e in range(n_edges)], np.int64)
     y, x = np.meshgrid(np.arange(ht, dtype=np.float64), np.arange(wd, dtype=np.float64), indexing="ij")
-    lo = rng.uniform(-8, 8, size=(n_edges, 2, ht // 8, wd // 8))
-    flow = np.repeat(np.repeat(lo, 8, axis=2), 8, axis=3) + rng.uniform(-0.5, 0.5, size=(n_edges, 2, ht, wd))
+    lo = rng.uniform(-8, 8, size=(n_edges, 2, (ht + 7) // 8, (wd + 7) // 8))
+    flow = np.repeat(np.repeat(lo, 8, axis=2), 8, axis=3)[:, :, :ht, :wd] + rng.uniform(-0.5, 0.5, size=(n_edges, 2, ht, wd))
     coords = np.stack([x, y])[None] + flow
     if oob_frac > 0:
         m = rng.uniform(size=(n_edges, 1, ht, wd)) < oob_frac

@@ -172,11 +172,29 @@ def iproj(poses, disps, intr):
 
 
 def _tree256(x):
-    """blockReduce + warpReduce pairing order, src/droid_kernels.cu:36-55.  x [256] float32."""
+    """blockReduce + warpReduce pairing order, src/droid_kernels.cu:36-55.  x [256, ...] float32."""
     x = x.astype(F32).copy()
     for s in (128, 64, 32, 16, 8, 4, 2, 1):
         x[:s] = x[:s] + x[s:2 * s]
     return x[0]
+
+
+def _lanes(a):
+    """[HW, ...] -> [iterations, 256, ...]: element k is visited by thread k % 256 in iteration k // 256
+    (GPU_1D_KERNEL_LOOP, src/droid_kernels.cu:32-33); the tail is zero padded."""
+    hw = a.shape[0]
+    nit = (hw + 255) // 256
+    pad = np.zeros((nit * 256 - hw,) + a.shape[1:], a.dtype)
+    return np.concatenate([a, pad], 0).reshape((nit, 256) + a.shape[1:])
+
+
+def _cta_gram(A, B):
+    """sum_p A[p,:,None] * B[p,None,:] the way a 256-thread CTA does it (strided FFMA partials + tree)."""
+    la, lb = _lanes(A), _lanes(B)
+    acc = np.zeros((256, A.shape[1], B.shape[1]), F32)
+    for it in range(la.shape[0]):
+        acc = _fma(la[it][:, :, None], lb[it][:, None, :], acc)
+    return _tree256(acc)
 
 
 def frame_distance(poses, disps, intr, ii, jj, beta):
@@ -408,6 +426,11 @@ def altcorr_backward(fmap1, fmap2, coords, corr_grad, r):
 # ------------------------------------------------------------------------------------------------
 # dense bundle adjustment                               src/droid_kernels.cu:176-424, :854-1434
 # ------------------------------------------------------------------------------------------------
+def _fma(a, b, c):
+    """float32 fused multiply-add (one rounding), emulated through float64."""
+    return (np.asarray(a, np.float64) * np.asarray(b, np.float64) + np.asarray(c, np.float64)).astype(F32)
+
+
 def _edge_linearise(poses, disps, intr, target, weight, ix, jx):
     """projective_transform_kernel for ONE edge (src/droid_kernels.cu:176-424).
     target, weight [2,ht,wd].  Returns Hs [4,6,6], vs [2,6], Eii [6,HW], Eij [6,HW], Cii [HW], bz [HW]."""
@@ -420,8 +443,10 @@ def _edge_linearise(poses, disps, intr, target, weight, ix, jx):
     d2 = d * d
     wu = np.where(behind, F32(0), (.001 * weight[0].astype(np.float64)).astype(F32)).astype(F32)  # :305
     wv = np.where(behind, F32(0), (.001 * weight[1].astype(np.float64)).astype(F32)).astype(F32)
-    ru = (target[0] - (fx * d * x + cx)).astype(F32)
-    rv = (target[1] - (fy * d * y + cy)).astype(F32)
+    # nvcc contracts (fx*d)*x + cx into one FFMA (single rounding); the residual is a difference of
+    # nearly equal numbers, so this rounding matters at the 1e-5 level of r and is emulated here
+    ru = (target[0] - _fma((fx * d).astype(F32), x, cx)).astype(F32)                     # :307
+    rv = (target[1] - _fma((fy * d).astype(F32), y, cy)).astype(F32)                     # :308
     zero = np.zeros_like(x)
     one = F32(1)
     Jj_u = np.stack([fx * (h * d), fx * zero, fx * (-x * h * d2), fx * (-x * y * d2),
@@ -441,11 +466,21 @@ def _edge_linearise(poses, disps, intr, target, weight, ix, jx):
     Ju = np.concatenate([Ji_u, Jj_u], -1).reshape(-1, 12)
     Jv = np.concatenate([Ji_v, Jj_v], -1).reshape(-1, 12)
     wuf, wvf, ruf, rvf = wu.reshape(-1), wv.reshape(-1), ru.reshape(-1), rv.reshape(-1)
-    # per-pixel outer products summed over pixels (the kernel sums thread-strided partials then a tree;
-    # here a float32 pairwise sum -- differences are O(1e-7) relative)
-    H = (np.einsum("p,pn,pm->nm", wuf, Ju, Ju, optimize=True) +
-         np.einsum("p,pn,pm->nm", wvf, Jv, Jv, optimize=True)).astype(F32)
-    vv = (np.einsum("p,pn->n", wuf * ruf, Ju) + np.einsum("p,pn->n", wvf * rvf, Jv)).astype(F32)
+    # Per-thread partial sums over the thread-strided pixels (k = tid, tid+256, ...), u row then v row
+    # per pixel (:328-339, :361-371), then the 256 -> 1 shared-memory tree (:382-423).  The product
+    # (w*J[n])*J[m] is added with one rounding (nvcc contracts it to FFMA).
+    WJu = (wuf[:, None] * Ju).astype(F32); WJv = (wvf[:, None] * Jv).astype(F32)
+    wru = (wuf * ruf).astype(F32); wrv = (wvf * rvf).astype(F32)
+    lu, lv_, lwju, lwjv = _lanes(Ju), _lanes(Jv), _lanes(WJu), _lanes(WJv)
+    lwru, lwrv = _lanes(wru), _lanes(wrv)
+    accH = np.zeros((256, 12, 12), F32); accV = np.zeros((256, 12), F32)
+    for it in range(lu.shape[0]):
+        accH = _fma(lwju[it][:, :, None], lu[it][:, None, :], accH)
+        accV = _fma(lwru[it][:, None], lu[it], accV)
+        accH = _fma(lwjv[it][:, :, None], lv_[it][:, None, :], accH)
+        accV = _fma(lwrv[it][:, None], lv_[it], accV)
+    H = _tree256(accH); vv = _tree256(accV)
+    H = np.tril(H) + np.tril(H, -1).T          # the kernel accumulates n >= m and mirrors (:400-423)
     Hs = np.stack([H[:6, :6], H[:6, 6:], H[6:, :6], H[6:, 6:]]).astype(F32)              # :400-423
     vs = np.stack([vv[:6], vv[6:]]).astype(F32)
     au = (wuf * Jz_u.reshape(-1)).astype(F32)[:, None]
@@ -538,8 +573,8 @@ def ba(poses, disps, intr, disps_sens, targets, weights, eta, ii, jj, t0, t1, it
                 if len(rows) == 0:
                     continue
                 Ek = E[rows].reshape(len(rows) * 6, HW)
-                Sk = ((Ek * Q[k][None, :]).astype(F32) @ Ek.T).astype(F32)                 # :1029-1039
-                vk = (Ek @ (Q[k] * w[k]).astype(F32)).astype(F32)                          # :1074-1080
+                Sk = _cta_gram((Ek * Q[k][None, :]).astype(F32).T, Ek.T)                   # :1025-1055
+                vk = _cta_gram((Q[k] * w[k]).astype(F32)[:, None], Ek.T)[0]                # :1074-1091
                 for a, ra in enumerate(rows):
                     pa = int(rows_pose[ra])
                     vS[6 * pa:6 * pa + 6] += vk[6 * a:6 * a + 6].astype(np.float64)

@@ -84,7 +84,7 @@ def test_corr_index_matches_grid_sample(backends):
     g = xy + off
     g = torch.stack([2 * g[..., 0] / (W2 - 1) - 1, 2 * g[..., 1] / (H2 - 1) - 1], -1)
     s = F.grid_sample(planes, g, padding_mode="zeros", align_corners=True).view(B, H1, W1, 7, 7)
-    assert (s.permute(0, 3, 4, 1, 2) - out).abs().max().item() < 1e-12
+    assert (s.permute(0, 3, 4, 1, 2) - out).abs().max().item() < 1e-6   # bilinear weights are float32 by design (:43-44)
 
 
 @pytest.mark.parametrize("dtype,tol", [(np.float32, 1e-6), (np.float16, 0.0)])
@@ -211,7 +211,8 @@ def test_ba_matches_oracle(backends, name, kw, iters):
     rp, rd, rdx, rdz = oracle_ba(p, iters)
     gp, gd, gdx, gdz = run_ba(backends, p, iters)
     assert backends.ba_status() == 0
-    assert rel(gdx, rdx) <= 1e-4 and rel(gdz, rdz) <= 1e-4
+    # <= 1e-4 per Gauss-Newton iteration; iteration 2 starts from a state that already differs at 1e-6
+    assert rel(gdx, rdx) <= (1e-4 if iters == 1 else 5e-4) and rel(gdz, rdz) <= 1e-4
     assert rel(gp, rp) <= 1e-5 and rel(gd, rd) <= 1e-5
 
 
@@ -219,7 +220,8 @@ def test_ba_motion_only(backends):
     p = synth.make_ba_problem("C3")
     rp, rd, rdx, _ = oracle_ba(p, 2, motion_only=True)
     gp, gd, gdx, _ = run_ba(backends, p, 2, motion_only=True)
-    assert rel(gdx, rdx) <= 1e-4 and rel(gp, rp) <= 1e-5
+    assert rel(gdx, rdx) <= 5e-4 and rel(gp, rp) <= 1e-5
+    assert rel(run_ba(backends, p, 1, motion_only=True)[2], oracle_ba(p, 1, motion_only=True)[2]) <= 1e-4
     assert np.array_equal(gd, p["disps"])        # depths untouched
 
 
@@ -231,7 +233,7 @@ def test_ba_backend_window_and_fixed_poses(backends):
     p["eta"] = np.ascontiguousarray(np.resize(p["eta"], (len(kx),) + p["eta"].shape[1:]))
     rp, rd, rdx, rdz = oracle_ba(p, 2, lm=1e-5, ep=1e-2)
     gp, gd, gdx, gdz = run_ba(backends, p, 2, lm=1e-5, ep=1e-2)
-    assert rel(gdx, rdx) <= 1e-4 and rel(gdz, rdz) <= 1e-4
+    assert rel(gdx, rdx) <= 5e-4 and rel(gdz, rdz) <= 1e-4
     assert np.array_equal(gp[:5], p["poses"][:5])
 
 
@@ -262,3 +264,40 @@ def test_chol_solve(backends, n):
     A[n // 2, n // 2] = -1.0                       # not SPD -> failure flag, like Eigen's info()
     _, info = backends.chol_solve(cu(A), cu(b))
     assert int(info.item()) != 0
+
+
+@pytest.mark.parametrize("key", sorted(__import__("golden_cases").BA_CASES))
+def test_ba_matches_reference_golden(backends, key):
+    """Against the stored outputs of the unmodified reference extension (tests/golden/ref_ba_*.npz)."""
+    import os
+    import golden_cases as G
+    p, c = G.ba_case(key)
+    ref = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_" + key + ".npz"))
+    gp, gd, gdx, gdz = run_ba(backends, p, c["iters"], c["lm"], c["ep"], c["motion_only"])
+    assert rel(gdx, ref["dx"]) <= (1e-4 if c["iters"] == 1 else 5e-4)
+    assert rel(gp, ref["poses"]) <= 1e-5
+    if not c["motion_only"]:
+        assert rel(gdz.reshape(ref["dz"].shape), ref["dz"]) <= 1e-4 and rel(gd, ref["disps"]) <= 1e-5
+
+
+def test_against_live_reference_extension(backends, ref_ext):
+    """When oracle/_ref holds the reference extension (built by oracle/build_ref.sh), compare live."""
+    if ref_ext is None:
+        pytest.skip("reference extension not built")
+    import golden_cases as G
+    for dt in (np.float32, np.float16):
+        vol, c, g = G.corr_case(dt)
+        assert torch.equal(backends.corr_index_forward(cu(vol), cu(c), 3)[0], ref_ext.corr_index_forward(cu(vol), cu(c), 3)[0])
+        assert torch.equal(backends.corr_index_backward(cu(vol), cu(c), cu(g), 3)[0],
+                           ref_ext.corr_index_backward(cu(vol), cu(c), cu(g), 3)[0])
+    q = G.geom_case()
+    P, D, K = cu(q["poses"]), cu(q["disps"]), cu(q["intr"])
+    a, b = backends.projmap(P, D, K, cu(q["ii"]), cu(q["jj"])), ref_ext.projmap(P, D, K, cu(q["ii"]), cu(q["jj"]))
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    assert torch.equal(backends.iproj(P, D, K), ref_ext.iproj(P, D, K))
+    GP, GD = cu(q["gt_poses"]), cu(q["gt_disps"])
+    assert torch.equal(backends.depth_filter(GP, GD, K, cu(q["ix"]), cu(q["thresh"])),
+                       ref_ext.depth_filter(GP, GD, K, cu(q["ix"]), cu(q["thresh"])))
+    d1 = backends.frame_distance(P, D, K, cu(q["fa"]), cu(q["fb"]), 0.3)
+    d2 = ref_ext.frame_distance(P, D, K, cu(q["fa"]), cu(q["fb"]), 0.3)
+    assert torch.equal(d1 == 1000.0, d2 == 1000.0) and rel(d1.cpu().numpy(), d2.cpu().numpy()) <= 1e-6
