@@ -224,7 +224,7 @@ static int fwd_common(const void* f1, const void* f2, const int64_t* ii, const i
   const bool aligned = ((uintptr_t)f1 % (4 * esz) == 0) && ((uintptr_t)f2 % (4 * esz) == 0);
   if (radius == 3 && aligned && (C == 128 || C == 256 || (C == 384 && dtype == DROID_DTYPE_F32))) {
 #define ALT_LAUNCH(TF, CPL)                                                                     \
-  altcorr_fwd_r3_kernel<TF, CPL><<<grid, 256, 0, st>>>(reinterpret_cast<const TF*>(f1),          \
+  DROID_LAUNCH altcorr_fwd_r3_kernel<TF, CPL><<<grid, 256, 0, st>>>(reinterpret_cast<const TF*>(f1),          \
                                                         reinterpret_cast<const TF*>(f2), ii, jj, \
                                                         coords, out, N, HW1, H2, W2, C)
     if (dtype == DROID_DTYPE_F32) {
@@ -248,7 +248,7 @@ generic:
     const int rt = 2 * radius + 2;
     size_t smem = (size_t)8 * rt * rt * sizeof(float);
     if (smem > 48 * 1024) return DROID_ERR_INVALID_ARGUMENT;
-    altcorr_fwd_generic_kernel<<<grid, 256, smem, st>>>(reinterpret_cast<const float*>(f1),
+    DROID_LAUNCH altcorr_fwd_generic_kernel<<<grid, 256, smem, st>>>(reinterpret_cast<const float*>(f1),
                                                         reinterpret_cast<const float*>(f2), coords,
                                                         out, N, HW1, H2, W2, C, radius);
   }
@@ -303,7 +303,7 @@ extern "C" int droid_altcorr_backward(const float* fmap1, const float* fmap2, co
   size_t smem = (size_t)8 * rt * rt * sizeof(float);
   if (smem > 48 * 1024) return DROID_ERR_INVALID_ARGUMENT;
   dim3 grid(((int)HW1 + 7) / 8, N, B);
-  altcorr_bwd_kernel<<<grid, 256, smem, st>>>(fmap1, fmap2, coords, corr_grad, fmap1_grad,
+  DROID_LAUNCH altcorr_bwd_kernel<<<grid, 256, smem, st>>>(fmap1, fmap2, coords, corr_grad, fmap1_grad,
                                               fmap2_grad, N, (int)HW1, H2, W2, C, radius);
   return check_launch();
 }

@@ -768,7 +768,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   const int HW = p->ht * p->wd;
   const int frame_lo = p->frame_lo, frame_hi = p->frame_hi > p->frame_lo ? p->frame_hi : 0x7fffffff;
 
-  ba_prep_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->n_eta, p->t0, p->t1, w.status,
+  DROID_LAUNCH ba_prep_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->n_eta, p->t0, p->t1, w.status,
                                      w.kmap, w.kx, w.eptr, w.eidx, w.fill);
   if (check_launch()) return DROID_ERR_CUDA;
   if (P == 0 || p->iterations == 0) return DROID_OK;
@@ -792,40 +792,52 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   double* bvec = w.A + (size_t)n6 * n6;
 
   for (int itr = 0; itr < p->iterations; itr++) {
-    if (p->n_edges > 0) {
-      ba_edge_pose_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(poses, ii, jj, p->n_edges,
-                                                                    p->nbuf, w.gij);
+    {
+      ProfScope ps(DROID_PROF_BA_PREP, st);
+      if (p->n_edges > 0) {
+        DROID_LAUNCH ba_edge_pose_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(poses, ii, jj, p->n_edges,
+                                                                                   p->nbuf, w.gij);
+      }
+      cudaMemsetAsync(w.A, 0, ((size_t)n6 * n6 + n6) * sizeof(double), st);
     }
-    cudaMemsetAsync(w.A, 0, ((size_t)n6 * n6 + n6) * sizeof(double), st);
     if (p->n_edges > 0 && p->n_eta > 0) {
-      ba_accum_kernel<<<dim3(S, p->n_eta), kThreads, 0, st>>>(
-          disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, w.gij, w.status, w.kx,
-          w.eptr, w.eidx, w.Q, w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, p->motion_only,
-          frame_lo, frame_hi);
+      {
+        ProfScope ps(DROID_PROF_BA_ACCUM, st);
+        DROID_LAUNCH ba_accum_kernel<<<dim3(S, p->n_eta), kThreads, 0, st>>>(
+            disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, w.gij, w.status, w.kx,
+            w.eptr, w.eidx, w.Q, w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, p->motion_only,
+            frame_lo, frame_hi);
+      }
       if (!p->motion_only) {
-        ba_schur_kernel<<<dim3(S, p->n_eta), kThreads, kSchurSmemBytes, st>>>(
+        ProfScope ps(DROID_PROF_BA_SCHUR, st);
+        DROID_LAUNCH ba_schur_kernel<<<dim3(S, p->n_eta), kThreads, kSchurSmemBytes, st>>>(
             disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q,
             w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi);
       }
     }
     if (check_launch()) return DROID_ERR_CUDA;
     if (p->reduce_fn) {
+      ProfScope ps(DROID_PROF_BA_REDUCE, st);
       int rc = p->reduce_fn(p->reduce_user, w.A, (size_t)n6 * n6 + n6, stream);
       if (rc != 0) return DROID_ERR_CUDA;
     }
-    ba_damp_kernel<<<(n6 + 127) / 128, 128, 0, st>>>(w.A, n6, p->lm, p->ep);
-    int rc = droid_chol_solve_f64(w.A, bvec, n6, w.status + 2, w.chol, chol_bytes, stream);
-    if (rc != DROID_OK) return rc;
+    {
+      ProfScope ps(DROID_PROF_BA_SOLVE, st);
+      DROID_LAUNCH ba_damp_kernel<<<(n6 + 127) / 128, 128, 0, st>>>(w.A, n6, p->lm, p->ep);
+      int rc = droid_chol_solve_f64(w.A, bvec, n6, w.status + 2, w.chol, chol_bytes, stream);
+      if (rc != DROID_OK) return rc;
+    }
+    ProfScope ps(DROID_PROF_BA_UPDATE, st);
     if (p->motion_only || p->n_eta == 0 || p->n_edges == 0) {
-      ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
-                                                             w.dx, dx_out, p->t0, P, 1);
+      DROID_LAUNCH ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
+                                                                          w.dx, dx_out, p->t0, P, 1);
     } else {
-      ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
-                                                             w.dx, dx_out, p->t0, P, 0);
-      ba_dz_kernel<<<dim3((HW + kThreads - 1) / kThreads, p->n_eta), kThreads, 0, st>>>(
+      DROID_LAUNCH ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
+                                                                          w.dx, dx_out, p->t0, P, 0);
+      DROID_LAUNCH ba_dz_kernel<<<dim3((HW + kThreads - 1) / kThreads, p->n_eta), kThreads, 0, st>>>(
           disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
           w.dx, dz_out, HW, p->wd, p->t0, P, p->n_eta, frame_lo, frame_hi);
-      ba_pose_apply_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, w.dx, p->t0, P);
+      DROID_LAUNCH ba_pose_apply_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, w.dx, p->t0, P);
     }
     if (check_launch()) return DROID_ERR_CUDA;
   }

@@ -260,7 +260,7 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
       attr_set = true;
     }
     const size_t smem = (size_t)(n + 1) * (n + 1) * sizeof(double);
-    chol_small_kernel<<<1, 256, smem, st>>>(A, n, info_dev);
+    DROID_LAUNCH chol_small_kernel<<<1, 256, smem, st>>>(A, n, info_dev);
     return check_launch();
   }
   static bool attr2 = false;
@@ -275,18 +275,18 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
     const int jb = (n - j0) < NB ? (n - j0) : NB;
     const int rem_rows = n + 1 - (j0 + jb);  // >= 1 (the rhs row)
     const int nrb = (rem_rows + NB - 1) / NB;
-    chol_panel_kernel<<<1 + nrb, 256, panel_smem, st>>>(A, n, j0, jb, info_dev);
+    DROID_LAUNCH chol_panel_kernel<<<1 + nrb, 256, panel_smem, st>>>(A, n, j0, jb, info_dev);
     const int ncb = (n - (j0 + jb) + NB - 1) / NB;  // column blocks that remain
     if (ncb > 0) {
       // tiles (bi, bj), bj < ncb, bi >= bj, bi < nrb
       const int ntile = nrb * (nrb + 1) / 2;
-      chol_syrk_kernel<<<ntile, 256, syrk_smem, st>>>(A, n, j0, jb);
+      DROID_LAUNCH chol_syrk_kernel<<<ntile, 256, syrk_smem, st>>>(A, n, j0, jb);
     }
   }
   for (int j0 = ((n - 1) / NB) * NB; j0 >= 0; j0 -= NB) {
     const int jb = (n - j0) < NB ? (n - j0) : NB;
     const int g = j0 > 0 ? (j0 + 255) / 256 : 1;
-    chol_bwd_kernel<<<g, 256, 0, st>>>(A, n, j0, jb);
+    DROID_LAUNCH chol_bwd_kernel<<<g, 256, 0, st>>>(A, n, j0, jb);
   }
   return check_launch();
 }

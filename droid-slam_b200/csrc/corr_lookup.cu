@@ -311,11 +311,11 @@ static int launch_fwd(const void* volume, const float* coords, void* out, int B,
     const bool vec = sizeof(T) <= 4 && (W2 % epc == 0) && ((uintptr_t)volume % 16 == 0) &&
                      (((size_t)H2 * W2) % epc == 0);
     dim3 grid((HW1 + 31) / 32, B);
-    if (vec) corr_index_fwd_r3_kernel<T, true><<<grid, 256, 0, st>>>(vol, coords, o, HW1, H2, W2);
-    else corr_index_fwd_r3_kernel<T, false><<<grid, 256, 0, st>>>(vol, coords, o, HW1, H2, W2);
+    if (vec) DROID_LAUNCH corr_index_fwd_r3_kernel<T, true><<<grid, 256, 0, st>>>(vol, coords, o, HW1, H2, W2);
+    else DROID_LAUNCH corr_index_fwd_r3_kernel<T, false><<<grid, 256, 0, st>>>(vol, coords, o, HW1, H2, W2);
   } else {
     dim3 grid((HW1 + 255) / 256, B);
-    corr_index_fwd_generic_kernel<T><<<grid, 256, 0, st>>>(vol, coords, o, HW1, H2, W2, radius);
+    DROID_LAUNCH corr_index_fwd_generic_kernel<T><<<grid, 256, 0, st>>>(vol, coords, o, HW1, H2, W2, radius);
   }
   return check_launch();
 }
@@ -328,7 +328,7 @@ static int launch_bwd(const float* coords, const void* cg, void* vg, int B, int 
   dim3 grid((HW1 + 7) / 8, B);
   size_t smem = (size_t)8 * rd * rd * sizeof(T);
   if (smem > 48 * 1024) return DROID_ERR_INVALID_ARGUMENT;
-  corr_index_bwd_kernel<T><<<grid, 256, smem, st>>>(coords, reinterpret_cast<const T*>(cg),
+  DROID_LAUNCH corr_index_bwd_kernel<T><<<grid, 256, smem, st>>>(coords, reinterpret_cast<const T*>(cg),
                                                     reinterpret_cast<T*>(vg), HW1, H2, W2, radius);
   return check_launch();
 }
@@ -395,10 +395,10 @@ extern "C" int droid_corr_index_pyramid(const void* const* volumes_host, int num
   dim3 grid((HW1 + 31) / 32, B);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == DROID_DTYPE_F16)
-    corr_index_pyr_r3_kernel<__half><<<grid, 256, 0, st>>>(a, num_levels, coords,
+    DROID_LAUNCH corr_index_pyr_r3_kernel<__half><<<grid, 256, 0, st>>>(a, num_levels, coords,
                                                            reinterpret_cast<__half*>(out), HW1, H2, W2);
   else if (dtype == DROID_DTYPE_F32)
-    corr_index_pyr_r3_kernel<float><<<grid, 256, 0, st>>>(a, num_levels, coords,
+    DROID_LAUNCH corr_index_pyr_r3_kernel<float><<<grid, 256, 0, st>>>(a, num_levels, coords,
                                                           reinterpret_cast<float*>(out), HW1, H2, W2);
   else
     return DROID_ERR_UNSUPPORTED_DTYPE;

@@ -54,6 +54,7 @@ def _load():
     lib.droid_ba_workspace_bytes.argtypes = [ctypes.POINTER(BaParams)]
     lib.droid_chol_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_corr_build_workspace_bytes.restype = ctypes.c_size_t
+    lib.droid_launch_count.restype = ctypes.c_ulonglong
     return lib
 
 
@@ -62,12 +63,33 @@ __version__ = _lib.droid_version().decode()
 
 # names every build of the library must export (checked by tests/test_abi.py against the header)
 C_ABI_SYMBOLS = [
-    "droid_version", "droid_last_cuda_error", "droid_corr_index_forward", "droid_corr_index_backward",
+    "droid_version", "droid_last_cuda_error", "droid_launch_count", "droid_prof_enable", "droid_prof_read", "droid_corr_index_forward", "droid_corr_index_backward",
     "droid_corr_index_pyramid", "droid_altcorr_forward", "droid_altcorr_backward",
     "droid_altcorr_forward_indexed", "droid_corr_build", "droid_corr_build_workspace_bytes",
     "droid_frame_distance", "droid_projmap", "droid_iproj", "droid_depth_filter",
     "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_workspace_bytes",
 ]
+
+
+PROF_PHASES = ["ba_prep", "ba_accum", "ba_schur", "ba_reduce", "ba_solve", "ba_update", "corr_gemm", "spare"]
+
+
+def launch_count():
+    """Kernels launched by libdroid_b200 since load (bench.py's gpu_launches)."""
+    return int(_lib.droid_launch_count())
+
+
+def prof_enable(on=True):
+    _lib.droid_prof_enable(1 if on else 0)
+
+
+def prof_read():
+    """{phase: (milliseconds, intervals)} of the phases recorded since the last read (synchronises)."""
+    n = len(PROF_PHASES)
+    ms = (ctypes.c_double * n)()
+    cnt = (ctypes.c_int * n)()
+    _check(_lib.droid_prof_read(ms, cnt, n), "prof_read")
+    return {PROF_PHASES[i]: (ms[i], cnt[i]) for i in range(n)}
 
 
 def _check(rc, what):

@@ -116,9 +116,10 @@ def edges_global(Rs, ts, rad=2, knn=8, max_factors=None):
     return [p[0] for p in pairs], [p[1] for p in pairs]
 
 
-def make_ba_problem(name="C1", seed=1234, n_frames=None, stereo=False, sensor=False, nbuf=None):
+def make_ba_problem(name="C1", seed=1234, n_frames=None, stereo=False, sensor=False, nbuf=None, knn=8):
     """Returns a dict of float32/int64 numpy arrays: poses, disps, intrinsics, disps_sens, targets,
-    weights, eta, ii, jj, t0, t1 (+ gt_poses, gt_disps)."""
+    weights, eta, ii, jj, t0, t1 (+ gt_poses, gt_disps).  C4 with n_frames=1000, knn=16 is the
+    BASELINE.json backend configuration: 1000 keyframes, 20 862 edges (~20k), 40x64."""
     rng = np.random.default_rng(seed)
     if name == "C1":      # 8 frames, 24 edges, 48x64
         n, ht, wd, intr = 8, 48, 64, TARTAN_INTR
@@ -144,7 +145,7 @@ def make_ba_problem(name="C1", seed=1234, n_frames=None, stereo=False, sensor=Fa
         raise ValueError("n_frames only applies to C4")
     Rs, ts = trajectory(n, loop=loop)
     if ii is None:
-        ii, jj = edges_global(Rs, ts, rad=2, knn=8, max_factors=None)
+        ii, jj = edges_global(Rs, ts, rad=2, knn=knn, max_factors=None)
     if stereo:
         ii = list(ii) + list(range(n)); jj = list(jj) + list(range(n))
     ii = np.asarray(ii, np.int64); jj = np.asarray(jj, np.int64)

@@ -40,6 +40,24 @@ const char* droid_version(void);
 /* cudaGetErrorString of the last failing launch seen by this library (thread-unsafe, debug aid). */
 const char* droid_last_cuda_error(void);
 
+/* Number of kernels this library has launched since it was loaded (bench.py's gpu_launches). */
+unsigned long long droid_launch_count(void);
+
+/* Per-phase device timing for bench.py's roofline: when enabled, the multi-kernel entry points record
+ * CUDA events on the caller's stream around each phase.  droid_prof_read waits for the recorded events,
+ * adds the elapsed milliseconds and interval counts per phase into ms[]/counts[] (nphase entries) and
+ * clears the records.  Phases: */
+#define DROID_PROF_BA_PREP 0    /* graph bookkeeping + edge poses + clearing the system       */
+#define DROID_PROF_BA_ACCUM 1   /* ba_accum_kernel: H, v, C, w                                 */
+#define DROID_PROF_BA_SCHUR 2   /* ba_schur_kernel: S = E Q E^T, v_S                           */
+#define DROID_PROF_BA_REDUCE 3  /* multi-GPU reduction callback                                */
+#define DROID_PROF_BA_SOLVE 4   /* damping + Cholesky factor + solves                          */
+#define DROID_PROF_BA_UPDATE 5  /* dz back-substitution + retractions                          */
+#define DROID_PROF_CORR_GEMM 6  /* corr_build                                                  */
+#define DROID_PROF_NPHASE 8
+int droid_prof_enable(int on);
+int droid_prof_read(double* ms, int* counts, int nphase);
+
 /* ---- correlation lookup ---------------------------------------------------------------------
  * Replaces corr_index_forward  (src/droid.cpp:170-178, src/correlation_kernels.cu:19-70,126-155).
  *   volume [B,H1,W1,H2,W2] dtype; coords [B,2,H1,W1] f32 (x,y), already scaled to this level;
