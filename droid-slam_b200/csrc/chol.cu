@@ -74,126 +74,307 @@ __global__ void __launch_bounds__(256) chol_small_kernel(double* __restrict__ A,
 }
 
 // ------------------------------------------------------------------------------------------------
-// blocked path, step 1: factor the diagonal block (redundantly in every CTA, it is 64^3/3 flops) and
-// solve this CTA's row block  X L_jj^T = A[rows, j0:j0+jb].
-// grid.x = 1 + number of 64-row blocks in rows j0+jb .. n (row n = rhs).
+// blocked path.  Outer panels of PB = 128 columns (depth of the trailing update), each factorised as two
+// sub-panels of NB = 64 columns by chol_panel_kernel; then one trailing SYRK on all SMs.
+//
+// chol_panel_kernel: every CTA holds the 64 rows of the diagonal block (threads 0..63, redundantly in
+// every CTA) plus PR = 192 trailing rows (threads 64..255), ONE MATRIX ROW PER THREAD IN REGISTERS
+// (a[64]).  All rows run the same right-looking elimination in lockstep:
+//     for c:  m = a[c] / d_c ;  a[q] -= m * col_c[q]  (q > c)
+// where col_c[q] = (un-normalised) entry (q, c) of the diagonal block, published through shared memory by
+// the diagonal rows one column ahead, with the reciprocal pivot computed by the publishing thread only.
+// One __syncthreads per column, no triangular-solve phase: the trailing rows finish together with the
+// 64x64 factorisation.  L = a[c] / sqrt(d_c) at the end.  If the sub-panel is the second half of its
+// outer panel (prev = 64), the rows first apply the update by the first half (a -= X_prev Xd_prev^T).
+// The rhs (row n of A) is just one more trailing row, which is how L y = b gets solved for free.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) chol_panel_kernel(double* __restrict__ A, int n, int j0, int jb,
-                                                         int* __restrict__ info) {
+static constexpr int PB = 128;
+static constexpr int PR = 192;
+static constexpr int kPanelSmem = (256 * 65 + 64 * 66 + 2 * 128 + 80 + 80 + 64) * (int)sizeof(double);
+
+// One column of the lockstep elimination.  The 64 columns are processed as 4 blocks of 16: inside a block
+// the step index C is a compile-time constant (a[] stays in registers, static indexing), between blocks
+// the registers are rotated by 16 so that the SAME 16-step code runs four times (a fully unrolled
+// 64-step version is ~7000 straight-line instructions and is instruction-fetch bound).  Register q holds
+// global column cbase + q; registers past column 63 hold don't-care values.
+template <int C>
+struct ElimStep {
+  static __device__ __forceinline__ void run(double (&a)[64], double* col, const double* inv_rd, double* inv,
+                                             double* dv, int tid, int cbase) {
+    __syncthreads();
+    const int c = cbase + C;                              // global column
+    const double* cc = col + (c & 1) * 128 + cbase;       // cc[q] = entry (cbase+q, c) of the diagonal block
+    const double m = a[C] * inv_rd[c];
+    if constexpr (C + 1 < 64) {
+      a[C + 1] = fma(-m, cc[C + 1], a[C + 1]);
+      if (tid < 64 && tid >= c + 1) {                     // diagonal rows publish column c+1
+        col[((c + 1) & 1) * 128 + tid] = a[C + 1];
+        if (tid == c + 1) { inv[c + 1] = 1.0 / a[C + 1]; dv[c + 1] = a[C + 1]; }
+      }
+    }
+    constexpr int Q0 = C + 2;
+    constexpr int QA = (Q0 & 1) ? Q0 + 1 : Q0;
+    if constexpr ((Q0 & 1) && Q0 < 64) a[Q0] = fma(-m, cc[Q0], a[Q0]);
+#pragma unroll
+    for (int q = QA; q < 64; q += 2) {
+      const double2 w = *reinterpret_cast<const double2*>(cc + q);
+      a[q] = fma(-m, w.x, a[q]);
+      a[q + 1] = fma(-m, w.y, a[q + 1]);
+    }
+    ElimStep<C + 1>::run(a, col, inv_rd, inv, dv, tid, cbase);
+  }
+};
+static constexpr int kRot = 64;  // columns per unrolled block (measured: 64 = 4.0 ms/solve, 16 = 4.5 ms at n = 5994)
+template <>
+struct ElimStep<kRot> {
+  static __device__ __forceinline__ void run(double (&)[64], double*, const double*, double*, double*, int, int) {}
+};
+
+__global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__ A, int n, int J, int j0,
+                                                            int jb, int* __restrict__ info) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double (*D)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(smem_raw);
-  double (*X)[NB + 1] = D + NB;
-  __shared__ int fail;
-  const int tid = threadIdx.x;
-  if (tid == 0) fail = 0;
-  for (int e = tid; e < jb * jb; e += 256) {
-    const int r = e / jb, c = e - r * jb;
-    D[r][c] = (c <= r) ? A[(size_t)(j0 + r) * n + j0 + c] : 0.0;
+  double* R = reinterpret_cast<double*>(smem_raw);  // [256][65] row staging
+  double* XdT = R + 256 * 65;                        // [64][66]  Xd^T: [k][c] = A[j0+c][J+k]
+  double* col = XdT + 64 * 66;                       // [2][128]  published column (double-buffered, padded)
+  double* inv = col + 256;                           // [80]      1 / pivot
+  double* dv = inv + 80;                             // [80]      pivots
+  double* rs = dv + 80;                              // [64]      1 / sqrt(pivot)
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int prev = j0 - J;
+  const bool diag = tid < 64;
+  const int trow0 = j0 + jb + blockIdx.x * PR;       // first trailing row of this CTA
+  auto row_of = [&](int t) { return t < 64 ? j0 + t : trow0 + t - 64; };
+  auto row_ok = [&](int t) { return t < 64 ? t < jb : (trow0 + t - 64) <= n; };
+  // R[t][c] = A[row(t)][cbase + c], c < width (zero elsewhere); 16 loads in flight per thread, one
+  // 512-byte row segment per warp-instruction.  `tri`: keep the lower triangle of the diagonal block
+  // only and pad a partial block with the identity.
+  auto stage = [&](int cbase, int width, bool tri) {
+#pragma unroll 1
+    for (int q0 = 0; q0 < 64; q0 += 16) {
+      double v[16];
+#pragma unroll
+      for (int q = 0; q < 16; q++) {
+        const int t = (q0 + q) * 4 + (tid >> 6), c = tid & 63;
+        v[q] = (row_ok(t) && c < width) ? A[(size_t)row_of(t) * n + cbase + c] : 0.0;
+      }
+#pragma unroll
+      for (int q = 0; q < 16; q++) {
+        const int t = (q0 + q) * 4 + (tid >> 6), c = tid & 63;
+        double x = v[q];
+        if (tri && t < 64) {
+          if (c > t) x = 0.0;
+          if (t >= jb && c == t) x = 1.0;
+        }
+        R[t * 65 + c] = x;
+      }
+    }
+  };
+
+  double a[64];
+#pragma unroll
+  for (int c = 0; c < 64; c++) a[c] = 0.0;
+
+  if (prev > 0) {
+    stage(J, prev, false);
+    __syncthreads();
+    for (int e = tid; e < 64 * 64; e += 256) {
+      const int c = e & 63, k = e >> 6;
+      XdT[k * 66 + c] = (c < jb && k < prev) ? R[c * 65 + k] : 0.0;
+    }
+    __syncthreads();
+    for (int k = 0; k < prev; k++) {
+      const double xk = R[tid * 65 + k];
+      const double2* w2 = reinterpret_cast<const double2*>(XdT + k * 66);
+#pragma unroll
+      for (int c = 0; c < 64; c += 2) {
+        const double2 w = w2[c >> 1];
+        a[c] = fma(-xk, w.x, a[c]);
+        a[c + 1] = fma(-xk, w.y, a[c + 1]);
+      }
+    }
+    __syncthreads();
+  }
+  stage(j0, jb, true);
+  __syncthreads();
+#pragma unroll
+  for (int c = 0; c < 64; c++) a[c] += R[tid * 65 + c];
+  // prev-update of the padding rows touched nothing (their x rows are zero)
+  if (tid < 128) { col[tid] = 0.0; col[128 + tid] = 0.0; }
+  if (tid < 80) inv[tid] = 0.0;
+  __syncthreads();
+  if (diag) {
+    col[tid] = a[0];
+    if (tid == 0) { inv[0] = 1.0 / a[0]; dv[0] = a[0]; }
+  }
+#pragma unroll 1
+  for (int cb = 0; cb < 64 / kRot; cb++) {
+    ElimStep<0>::run(a, col, inv, inv, dv, tid, cb * kRot);
+    __syncthreads();                                   // everyone is done with R's staged values / col
+#pragma unroll
+    for (int i = 0; i < kRot; i++) R[tid * 65 + cb * kRot + i] = a[i];
+    if (kRot < 64) {
+#pragma unroll
+      for (int i = 0; i < 64 - kRot; i++) a[i] = a[i + kRot];
+#pragma unroll
+      for (int i = 64 - kRot; i < 64; i++) a[i] = 0.0;
+    }
   }
   __syncthreads();
-  for (int c = 0; c < jb; c++) {
-    const double d = D[c][c];
-    if (!(d > 0.0) && tid == 0) fail = 1;
-    const double sq = sqrt(d), inv = 1.0 / sq;
-    __syncthreads();
-    for (int r = c + tid; r < jb; r += 256) D[r][c] = (r == c) ? sq : D[r][c] * inv;
-    __syncthreads();
-    const int rem = jb - c - 1;
-    for (int e = tid; e < rem * rem; e += 256) {
-      const int rr = e / rem, cc = e - rr * rem;
-      if (cc <= rr) D[c + 1 + rr][c + 1 + cc] -= D[c + 1 + rr][c] * D[c + 1 + cc][c];
-    }
-    __syncthreads();
-  }
-  if (blockIdx.x == 0) {
-    for (int e = tid; e < jb * jb; e += 256) {
-      const int r = e / jb, c = e - r * jb;
-      if (c <= r) A[(size_t)(j0 + r) * n + j0 + c] = D[r][c];
-    }
-    if (tid == 0 && fail) *info = 1;
-    return;
-  }
-  const int i0 = j0 + jb + (blockIdx.x - 1) * NB;
-  const int rows = min(NB, n + 1 - i0);
-  for (int e = tid; e < rows * jb; e += 256) {
-    const int r = e / jb, c = e - r * jb;
-    X[r][c] = A[(size_t)(i0 + r) * n + j0 + c];
+  if (tid < 64) {
+    const double d = dv[tid];
+    if (!(d > 0.0) && blockIdx.x == 0) *info = 1;
+    rs[tid] = 1.0 / sqrt(d);
   }
   __syncthreads();
-  // right-looking triangular solve, one column per step
-  for (int c = 0; c < jb; c++) {
-    const double inv = 1.0 / D[c][c];
-    for (int r = tid; r < rows; r += 256) X[r][c] *= inv;
-    __syncthreads();
-    const int rem = jb - c - 1;
-    for (int e = tid; e < rows * rem; e += 256) {
-      const int r = e / rem, t = c + 1 + (e - r * rem);
-      X[r][t] -= X[r][c] * D[t][c];
-    }
-    __syncthreads();
-  }
-  for (int e = tid; e < rows * jb; e += 256) {
-    const int r = e / jb, c = e - r * jb;
-    A[(size_t)(i0 + r) * n + j0 + c] = X[r][c];
+#pragma unroll 8
+  for (int c = 0; c < 64; c++) R[tid * 65 + c] *= rs[c];
+  __syncthreads();
+  for (int t = warp; t < 256; t += 8) {
+    if (!row_ok(t)) continue;
+    if (t < 64 && blockIdx.x != 0) continue;      // the diagonal block is written once
+    double* dst = A + (size_t)row_of(t) * n + j0;
+    for (int c = lane; c < jb; c += 32)
+      if (t >= 64 || c <= t) dst[c] = R[t * 65 + c];
   }
 }
 
 // ------------------------------------------------------------------------------------------------
-// blocked path, step 2: trailing update  C[bi][bj] -= X_bi X_bj^T  for all 64x64 tiles bi >= bj of
-// rows/cols r0 = j0+jb .. (row n included as a row, never as a column).  One CTA per tile,
-// 256 threads x (4x4) fp64 register tiles, operands staged k-major in shared memory.
+// trailing update  C[bi][bj] -= X_bi X_bj^T over k in [J, J+kb), for all TM x TM tiles bi >= bj of
+// rows/cols r0 = J+kb .. (row n included as a row, never as a column).  One CTA (256 threads) per tile,
+// (TM/16)^2 fp64 accumulators per thread, operands staged k-major in shared memory in chunks of 16 k,
+// double-buffered through registers so that global loads overlap the DFMA stream.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) chol_syrk_kernel(double* __restrict__ A, int n, int j0, int jb) {
+template <int TM, bool VEC>
+__global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
+    chol_syrk_kernel(double* __restrict__ A, int n, int J, int kb) {
+  constexpr int F = TM / 64;
+  constexpr int KC = 16;
+  constexpr int LD = TM + 2;
+  constexpr int LPT = TM / 32;  // double2 loads per thread per operand per chunk
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double (*Xi)[NB + 2] = reinterpret_cast<double (*)[NB + 2]>(smem_raw);  // [k][row]
-  double (*Xj)[NB + 2] = Xi + NB;                                          // [k][col]
-  // decode the lower-triangular tile index
+  double* sm = reinterpret_cast<double*>(smem_raw);  // [2 buffers][2 operands][KC][LD]
   const int t = blockIdx.x;
   int bi = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
   while ((bi + 1) * (bi + 2) / 2 <= t) bi++;
   while (bi * (bi + 1) / 2 > t) bi--;
   const int bj = t - bi * (bi + 1) / 2;
-  const int r0 = j0 + jb;
-  const int i0 = r0 + bi * NB, c0 = r0 + bj * NB;
-  const int rows = min(NB, n + 1 - i0);
-  const int cols = min(NB, n - c0);
+  const int r0 = J + kb;
+  const int i0 = r0 + bi * TM, c0 = r0 + bj * TM;
+  const int rows = min(TM, n + 1 - i0);
+  const int cols = min(TM, n - c0);
   if (cols <= 0 || rows <= 0) return;
   const int tid = threadIdx.x;
-  for (int e = tid; e < NB * NB; e += 256) {
-    const int r = e / NB, k = e - r * NB;
-    Xi[k][r] = (r < rows && k < jb) ? A[(size_t)(i0 + r) * n + j0 + k] : 0.0;
-    Xj[k][r] = (r < cols && k < jb) ? A[(size_t)(c0 + r) * n + j0 + k] : 0.0;
-  }
-  __syncthreads();
   const int ty = tid >> 4, tx = tid & 15;
-  double acc[4][4];
+  double acc[F * 4][F * 4];
 #pragma unroll
-  for (int a = 0; a < 4; a++)
+  for (int a = 0; a < F * 4; a++)
 #pragma unroll
-    for (int b = 0; b < 4; b++) acc[a][b] = 0.0;
-#pragma unroll 8
-  for (int k = 0; k < NB; k++) {
-    const double2 a01 = *reinterpret_cast<const double2*>(&Xi[k][ty * 4]);
-    const double2 a23 = *reinterpret_cast<const double2*>(&Xi[k][ty * 4 + 2]);
-    const double2 b01 = *reinterpret_cast<const double2*>(&Xj[k][tx * 4]);
-    const double2 b23 = *reinterpret_cast<const double2*>(&Xj[k][tx * 4 + 2]);
-    const double av[4] = {a01.x, a01.y, a23.x, a23.y};
-    const double bv[4] = {b01.x, b01.y, b23.x, b23.y};
+    for (int b = 0; b < F * 4; b++) acc[a][b] = 0.0;
+  double2 ra[LPT], rb[LPT];
+  const int nch = (kb + KC - 1) / KC;
+
+  auto gload = [&](int ch) {
 #pragma unroll
-    for (int a = 0; a < 4; a++)
+    for (int q = 0; q < LPT; q++) {
+      const int idx = tid + 256 * q;
+      const int r = idx >> 3, k = ch * KC + 2 * (idx & 7);
+      double2 va = make_double2(0.0, 0.0), vb = make_double2(0.0, 0.0);
+      if (k < kb) {
+        if (r < rows) {
+          const double* p = A + (size_t)(i0 + r) * n + J + k;
+          if (VEC) va = *reinterpret_cast<const double2*>(p);
+          else { va.x = p[0]; if (k + 1 < kb) va.y = p[1]; }
+        }
+        if (r < cols) {
+          const double* p = A + (size_t)(c0 + r) * n + J + k;
+          if (VEC) vb = *reinterpret_cast<const double2*>(p);
+          else { vb.x = p[0]; if (k + 1 < kb) vb.y = p[1]; }
+        }
+      }
+      ra[q] = va; rb[q] = vb;
+    }
+  };
+  auto sstore = [&](int buf) {
+    double* As = sm + (size_t)buf * 2 * KC * LD;
+    double* Bs = As + KC * LD;
 #pragma unroll
-      for (int b = 0; b < 4; b++) acc[a][b] = fma(av[a], bv[b], acc[a][b]);
+    for (int q = 0; q < LPT; q++) {
+      const int idx = tid + 256 * q;
+      const int r = idx >> 3, k = 2 * (idx & 7);
+      As[k * LD + r] = ra[q].x; As[(k + 1) * LD + r] = ra[q].y;
+      Bs[k * LD + r] = rb[q].x; Bs[(k + 1) * LD + r] = rb[q].y;
+    }
+  };
+
+  gload(0);
+  sstore(0);
+  __syncthreads();
+  for (int ch = 0; ch < nch; ch++) {
+    if (ch + 1 < nch) gload(ch + 1);
+    const double* As = sm + (size_t)(ch & 1) * 2 * KC * LD;
+    const double* Bs = As + KC * LD;
+#pragma unroll
+    for (int k = 0; k < KC; k++) {
+      double av[F * 4], bv[F * 4];
+#pragma unroll
+      for (int f = 0; f < F; f++) {
+        // element index e = f*4 + h*2 + {0,1}  <->  row/col  f*64 + h*32 + 2*ty + {0,1}: the 16 lanes of a
+        // half-warp read 16 consecutive 16-byte words (two conflict-free wavefronts per LDS.128)
+        const double2 a01 = *reinterpret_cast<const double2*>(As + k * LD + f * 64 + ty * 2);
+        const double2 a23 = *reinterpret_cast<const double2*>(As + k * LD + f * 64 + 32 + ty * 2);
+        const double2 b01 = *reinterpret_cast<const double2*>(Bs + k * LD + f * 64 + tx * 2);
+        const double2 b23 = *reinterpret_cast<const double2*>(Bs + k * LD + f * 64 + 32 + tx * 2);
+        av[f * 4 + 0] = a01.x; av[f * 4 + 1] = a01.y; av[f * 4 + 2] = a23.x; av[f * 4 + 3] = a23.y;
+        bv[f * 4 + 0] = b01.x; bv[f * 4 + 1] = b01.y; bv[f * 4 + 2] = b23.x; bv[f * 4 + 3] = b23.y;
+      }
+#pragma unroll
+      for (int a = 0; a < F * 4; a++)
+#pragma unroll
+        for (int b = 0; b < F * 4; b++) acc[a][b] = fma(av[a], bv[b], acc[a][b]);
+    }
+    if (ch + 1 < nch) sstore((ch + 1) & 1);
+    __syncthreads();
   }
+  // C -= acc.  The loads of one row are issued together (a load after a store to the same array could not
+  // be hoisted by the compiler, which would serialise 64 round trips to L2).
 #pragma unroll
-  for (int a = 0; a < 4; a++) {
-    const int r = ty * 4 + a;
+  for (int a = 0; a < F * 4; a++) {
+    const int r = (a >> 2) * 64 + ((a >> 1) & 1) * 32 + ty * 2 + (a & 1);
     if (r >= rows) continue;
+    double* dst = A + (size_t)(i0 + r) * n + c0;
+    const int cmax = min(cols - 1, i0 + r - c0);  // lower triangle only
+    double cv[F * 4];
+    if (VEC) {
 #pragma unroll
-    for (int b = 0; b < 4; b++) {
-      const int c = tx * 4 + b;
-      if (c >= cols) continue;
-      if (c0 + c > i0 + r) continue;  // keep to the lower triangle
-      A[(size_t)(i0 + r) * n + c0 + c] -= acc[a][b];
+      for (int b = 0; b < F * 4; b += 2) {
+        const int c = (b >> 2) * 64 + ((b >> 1) & 1) * 32 + tx * 2;
+        if (c + 1 <= cmax) {
+          const double2 v = *reinterpret_cast<const double2*>(dst + c);
+          cv[b] = v.x; cv[b + 1] = v.y;
+        } else if (c <= cmax) {
+          cv[b] = dst[c];
+        }
+      }
+#pragma unroll
+      for (int b = 0; b < F * 4; b += 2) {
+        const int c = (b >> 2) * 64 + ((b >> 1) & 1) * 32 + tx * 2;
+        if (c + 1 <= cmax) {
+          *reinterpret_cast<double2*>(dst + c) = make_double2(cv[b] - acc[a][b], cv[b + 1] - acc[a][b + 1]);
+        } else if (c <= cmax) {
+          dst[c] = cv[b] - acc[a][b];
+        }
+      }
+    } else {
+#pragma unroll
+      for (int b = 0; b < F * 4; b++) {
+        const int c = (b >> 2) * 64 + ((b >> 1) & 1) * 32 + tx * 2 + (b & 1);
+        if (c <= cmax) cv[b] = dst[c];
+      }
+#pragma unroll
+      for (int b = 0; b < F * 4; b++) {
+        const int c = (b >> 2) * 64 + ((b >> 1) & 1) * 32 + tx * 2 + (b & 1);
+        if (c <= cmax) dst[c] = cv[b] - acc[a][b];
+      }
     }
   }
 }
@@ -201,36 +382,56 @@ __global__ void __launch_bounds__(256) chol_syrk_kernel(double* __restrict__ A, 
 // ------------------------------------------------------------------------------------------------
 // backward sweep, one launch per 64-block from the last to the first:
 //   x_j = L_jj^-T y_j  (every CTA redundantly, warp 0), then  y[i] -= sum_r L[j0+r][i] x_j[r], i < j0.
-// y lives in row n of A and is overwritten by x.
+// y lives in row n of A and is overwritten by x.  CTA = 64 columns i x 4 row groups of 16.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) chol_bwd_kernel(double* __restrict__ A, int n, int j0, int jb) {
   __shared__ double D[NB][NB + 1];
   __shared__ double x[NB];
+  __shared__ double rinv[NB];
+  __shared__ double part[4][NB];
   const int tid = threadIdx.x;
   double* y = A + (size_t)n * n;
-  for (int e = tid; e < jb * jb; e += 256) {
-    const int r = e / jb, c = e - r * jb;
-    D[r][c] = (c <= r) ? A[(size_t)(j0 + r) * n + j0 + c] : 0.0;
+  for (int e = tid; e < NB * NB; e += 256) {
+    const int r = e / NB, c = e - r * NB;
+    D[r][c] = (c <= r && r < jb) ? A[(size_t)(j0 + r) * n + j0 + c] : 0.0;
   }
-  if (tid < jb) x[tid] = y[j0 + tid];
+  if (tid < NB) x[tid] = tid < jb ? y[j0 + tid] : 0.0;
+  __syncthreads();
+  if (tid < NB) rinv[tid] = tid < jb ? 1.0 / D[tid][tid] : 0.0;
   __syncthreads();
   if (tid < 32) {
-    for (int c = jb - 1; c >= 0; c--) {
-      double s = 0.0;
-      for (int t = c + 1 + tid; t < jb; t += 32) s += D[t][c] * x[t];
+    // lane holds x[lane] and x[lane+32]; right-looking back substitution with shuffles
+    double x0 = x[tid], x1 = x[tid + 32];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      if (tid == 0) x[c] = (x[c] - s) / D[c][c];
-      __syncwarp();
+    for (int c = NB - 1; c >= 0; c--) {
+      const double src = (c >= 32) ? x1 : x0;
+      const double xc = __shfl_sync(0xffffffffu, src, c & 31) * rinv[c];
+      if (c >= 32) {
+        if (tid == (c & 31)) x1 = xc;
+        else if (tid < (c & 31)) x1 = fma(-D[c][tid + 32], xc, x1);
+        x0 = fma(-D[c][tid], xc, x0);
+      } else {
+        if (tid == c) x0 = xc;
+        else if (tid < c) x0 = fma(-D[c][tid], xc, x0);
+      }
     }
+    x[tid] = x0; x[tid + 32] = x1;
   }
   __syncthreads();
-  const int i = blockIdx.x * 256 + tid;
+  const int i = blockIdx.x * NB + (tid & 63), g = tid >> 6;
+  double s = 0.0;
   if (i < j0) {
-    double s = 0.0;
-#pragma unroll 8
-    for (int r = 0; r < jb; r++) s = fma(A[(size_t)(j0 + r) * n + i], x[r], s);
-    y[i] -= s;
+#pragma unroll
+    for (int r = 0; r < 16; r++) {
+      const int rr = g * 16 + r;
+      if (rr < jb) s = fma(A[(size_t)(j0 + rr) * n + i], x[rr], s);
+    }
+  }
+  part[g][tid & 63] = s;
+  __syncthreads();
+  if (tid < NB) {
+    const int ii = blockIdx.x * NB + tid;
+    if (ii < j0) y[ii] -= part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
   }
   if (blockIdx.x == 0 && tid < jb) y[j0 + tid] = x[tid];
 }
@@ -264,28 +465,44 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
     return check_launch();
   }
   static bool attr2 = false;
-  const size_t panel_smem = 2 * NB * (NB + 1) * sizeof(double);
-  const size_t syrk_smem = 2 * NB * (NB + 2) * sizeof(double);
+  constexpr int kSyrk128 = 2 * 2 * 16 * (128 + 2) * (int)sizeof(double);
+  constexpr int kSyrk64 = 2 * 2 * 16 * (64 + 2) * (int)sizeof(double);
   if (!attr2) {
-    cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem);
-    cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)syrk_smem);
+    cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmem);
+    cudaFuncSetAttribute(chol_syrk_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
+    cudaFuncSetAttribute(chol_syrk_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
+    cudaFuncSetAttribute(chol_syrk_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk64);
+    cudaFuncSetAttribute(chol_syrk_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk64);
     attr2 = true;
   }
-  for (int j0 = 0; j0 < n; j0 += NB) {
-    const int jb = (n - j0) < NB ? (n - j0) : NB;
-    const int rem_rows = n + 1 - (j0 + jb);  // >= 1 (the rhs row)
-    const int nrb = (rem_rows + NB - 1) / NB;
-    DROID_LAUNCH chol_panel_kernel<<<1 + nrb, 256, panel_smem, st>>>(A, n, j0, jb, info_dev);
-    const int ncb = (n - (j0 + jb) + NB - 1) / NB;  // column blocks that remain
-    if (ncb > 0) {
-      // tiles (bi, bj), bj < ncb, bi >= bj, bi < nrb
-      const int ntile = nrb * (nrb + 1) / 2;
-      DROID_LAUNCH chol_syrk_kernel<<<ntile, 256, syrk_smem, st>>>(A, n, j0, jb);
+  const bool vec = (n % 2 == 0) && (((uintptr_t)A & 15) == 0);
+  for (int J = 0; J < n; J += PB) {
+    const int kb = (n - J) < PB ? (n - J) : PB;
+    prof_mark(DROID_PROF_CHOL_PANEL, true, st);
+    for (int j0 = J; j0 < J + kb; j0 += NB) {
+      const int jb = (J + kb - j0) < NB ? (J + kb - j0) : NB;
+      const int rem_rows = n + 1 - (j0 + jb);  // >= 1 (the rhs row)
+      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PR - 1) / PR, 256, kPanelSmem, st>>>(A, n, J, j0, jb, info_dev);
+    }
+    prof_mark(DROID_PROF_CHOL_PANEL, false, st);
+    const int r0 = J + kb;
+    if (r0 < n) {
+      ProfScope ps(DROID_PROF_CHOL_SYRK, st);
+      const int rr = n + 1 - r0;
+      const int t128 = (rr + 127) / 128, t64 = (rr + 63) / 64;
+      if (t128 * (t128 + 1) / 2 >= 148) {
+        if (vec) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb);
+        else DROID_LAUNCH chol_syrk_kernel<128, false><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb);
+      } else {
+        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb);
+        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb);
+      }
     }
   }
+  ProfScope psb(DROID_PROF_CHOL_BWD, st);
   for (int j0 = ((n - 1) / NB) * NB; j0 >= 0; j0 -= NB) {
     const int jb = (n - j0) < NB ? (n - j0) : NB;
-    const int g = j0 > 0 ? (j0 + 255) / 256 : 1;
+    const int g = j0 > 0 ? (j0 + NB - 1) / NB : 1;
     DROID_LAUNCH chol_bwd_kernel<<<g, 256, 0, st>>>(A, n, j0, jb);
   }
   return check_launch();

@@ -71,7 +71,8 @@ C_ABI_SYMBOLS = [
 ]
 
 
-PROF_PHASES = ["ba_prep", "ba_accum", "ba_schur", "ba_reduce", "ba_solve", "ba_update", "corr_gemm", "spare"]
+PROF_PHASES = ["ba_prep", "ba_accum", "ba_schur", "ba_reduce", "ba_solve", "ba_update", "corr_gemm", "spare",
+               "chol_panel", "chol_syrk", "chol_bwd", "spare2"]
 
 
 def launch_count():

@@ -54,7 +54,10 @@ unsigned long long droid_launch_count(void);
 #define DROID_PROF_BA_SOLVE 4   /* damping + Cholesky factor + solves                          */
 #define DROID_PROF_BA_UPDATE 5  /* dz back-substitution + retractions                          */
 #define DROID_PROF_CORR_GEMM 6  /* corr_build                                                  */
-#define DROID_PROF_NPHASE 8
+#define DROID_PROF_CHOL_PANEL 8 /* inside BA_SOLVE: panel factorisations                         */
+#define DROID_PROF_CHOL_SYRK 9  /* inside BA_SOLVE: trailing updates                               */
+#define DROID_PROF_CHOL_BWD 10  /* inside BA_SOLVE: backward substitution                         */
+#define DROID_PROF_NPHASE 12
 int droid_prof_enable(int on);
 int droid_prof_read(double* ms, int* counts, int nphase);
 
