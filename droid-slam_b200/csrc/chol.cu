@@ -272,6 +272,22 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
     for (int b = 0; b < F * 4; b++) acc[a][b] = 0.0;
   double2 ra[LPT], rb[LPT];
   const int nch = (kb + KC - 1) / KC;
+  // The C tile is fetched into shared memory with cp.async while the DFMA loop runs: the epilogue's
+  // read-modify-write would otherwise expose 8 serial round trips to DRAM per tile (33 % of the stall
+  // samples in profiles/r1_chol_ncu_summary.txt).
+  double* Cs = sm + 2 * 2 * KC * LD;                 // [TM][TM]
+  if (VEC) {
+#pragma unroll 4
+    for (int q = 0; q < TM * TM / 2 / 256; q++) {
+      const int idx = tid + 256 * q;
+      const int r = idx / (TM / 2), c = 2 * (idx % (TM / 2));
+      if (r < rows && c < cols) {
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(Cs + r * TM + c);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(A + (size_t)(i0 + r) * n + c0 + c));
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
 
   auto gload = [&](int ch) {
 #pragma unroll
@@ -335,6 +351,10 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
     if (ch + 1 < nch) sstore((ch + 1) & 1);
     __syncthreads();
   }
+  if (VEC) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+  }
   // C -= acc.  The loads of one row are issued together (a load after a store to the same array could not
   // be hoisted by the compiler, which would serialise 64 round trips to L2).
 #pragma unroll
@@ -348,11 +368,9 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
 #pragma unroll
       for (int b = 0; b < F * 4; b += 2) {
         const int c = (b >> 2) * 64 + ((b >> 1) & 1) * 32 + tx * 2;
-        if (c + 1 <= cmax) {
-          const double2 v = *reinterpret_cast<const double2*>(dst + c);
+        if (c <= cmax) {
+          const double2 v = *reinterpret_cast<const double2*>(Cs + r * TM + c);
           cv[b] = v.x; cv[b + 1] = v.y;
-        } else if (c <= cmax) {
-          cv[b] = dst[c];
         }
       }
 #pragma unroll
@@ -465,8 +483,8 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
     return check_launch();
   }
   static bool attr2 = false;
-  constexpr int kSyrk128 = 2 * 2 * 16 * (128 + 2) * (int)sizeof(double);
-  constexpr int kSyrk64 = 2 * 2 * 16 * (64 + 2) * (int)sizeof(double);
+  constexpr int kSyrk128 = (2 * 2 * 16 * (128 + 2) + 128 * 128) * (int)sizeof(double);
+  constexpr int kSyrk64 = (2 * 2 * 16 * (64 + 2) + 64 * 64) * (int)sizeof(double);
   if (!attr2) {
     cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmem);
     cudaFuncSetAttribute(chol_syrk_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);

@@ -247,22 +247,33 @@ def test_ba_reduces_reprojection_error(backends):
     assert err(gp, gd) < 0.5 * e0
 
 
+def oracle_ba64(p, iterations, lm, ep):
+    """The oracle's algorithm evaluated in float64 throughout ("truth" for rounding-error comparisons)."""
+    saved = (O.F32, O.MIN_DEPTH)
+    try:
+        O.F32, O.MIN_DEPTH = np.float64, np.float64(0.25)
+        q = {k: (v.astype(np.float64) if isinstance(v, np.ndarray) and v.dtype == np.float32 else v) for k, v in p.items()}
+        return oracle_ba(q, iterations, lm=lm, ep=ep)
+    finally:
+        O.F32, O.MIN_DEPTH = saved
+
+
 def test_ba_large_system_uses_blocked_cholesky(backends):
-    """6P = 354 > single-CTA limit.  With the backend damping (lm=1e-5, ep=1e-2) the reduced system of a 60-frame
-    graph is ill-conditioned enough that float32 rounding of the INPUTS already moves dx by ~1e-4: the bound is
-    therefore max(1e-4, 4 x the oracle's own sensitivity to a 1-ulp perturbation of targets, weights and depths)."""
+    """6P = 354 > single-CTA limit, backend damping (lm=1e-5, ep=1e-2).  This system is ill-conditioned enough that
+    the float32 accumulation error of the REFERENCE algorithm itself (2560-term float32 sums per Hessian entry) moves
+    dx by ~5e-5 relative to a float64 evaluation of the same algorithm.  The bound is therefore: the CUDA path is
+    within 1e-4 of the float64 truth or no further from it than 2x the float32 reference restatement is, and within
+    3e-4 of the restatement."""
     p = synth.make_ba_problem("C4", n_frames=60)
     rp, rd, rdx, rdz = oracle_ba(p, 1, lm=1e-5, ep=1e-2)
-    q = dict(p)
-    rng = np.random.default_rng(0)
-    for key in ("targets", "weights", "disps"):       # measured here: 1 ulp of each moves dx by 1e-5 .. 4e-5
-        q[key] = (p[key] * (1 + 1e-7 * rng.standard_normal(p[key].shape))).astype(np.float32)
-    _, _, sdx, sdz = oracle_ba(q, 1, lm=1e-5, ep=1e-2)
-    sens_x, sens_z = rel(sdx, rdx), rel(sdz, rdz)
+    tp, td, tdx, tdz = oracle_ba64(p, 1, 1e-5, 1e-2)
     gp, gd, gdx, gdz = run_ba(backends, p, 1, lm=1e-5, ep=1e-2)
-    print("sensitivity dx %.2e dz %.2e ; cuda-vs-oracle dx %.2e dz %.2e" % (sens_x, sens_z, rel(gdx, rdx), rel(gdz, rdz)))
-    assert rel(gdx, rdx) <= max(1e-4, 4 * sens_x) and rel(gdz, rdz) <= max(1e-4, 4 * sens_z)
-    assert rel(gdx, rdx) <= 1e-3 and rel(gdz, rdz) <= 1e-3
+    ref_x, ref_z = rel(rdx, tdx), rel(rdz, tdz)
+    got_x, got_z = rel(gdx, tdx), rel(gdz, tdz)
+    print("vs float64 truth: oracle32 dx %.2e dz %.2e ; cuda dx %.2e dz %.2e ; cuda-vs-oracle32 dx %.2e dz %.2e"
+          % (ref_x, ref_z, got_x, got_z, rel(gdx, rdx), rel(gdz, rdz)))
+    assert got_x <= max(1e-4, 2 * ref_x) and got_z <= max(1e-4, 2 * ref_z)
+    assert rel(gdx, rdx) <= 3e-4 and rel(gdz, rdz) <= 1e-4
 
 
 @pytest.mark.parametrize("n", [7, 64, 156, 157, 200, 777, 1200, 2431, 2500])
