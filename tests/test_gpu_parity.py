@@ -152,6 +152,36 @@ def test_altcorr_backward(backends):
     assert o3.shape == coords.shape and float(o3.abs().max()) == 0.0
 
 
+# ---------------------------------------------------------------- corr build (tcgen05) --------
+@pytest.mark.parametrize("B,H,W", [(3, 48, 64), (2, 40, 64), (2, 16, 32), (1, 24, 48), (2, 8, 16)])
+def test_corr_build_matches_matmul_and_avg_pool(backends, B, H, W):
+    """CorrBlock.corr + pyramid (modules/corr.py:24-38,63-71).  Level 0 against torch.matmul on the /4-scaled fp16
+    maps (cuBLAS accumulates in another order, so a last-place fp16 difference is allowed on a small fraction);
+    levels 1-3 must be BIT-EXACT F.avg_pool2d of the level below; plus the numpy oracle on a small case."""
+    import torch.nn.functional as F
+    p = synth.make_corr_problem(B, H, W, 128, seed=B + H)
+    f1 = cu(p["fmaps"][p["ii"]]); f2 = cu(p["fmaps"][p["jj"]])
+    lv = backends.corr_build(f1, f2)
+    torch.cuda.synchronize()
+    a = (f1 / 4.0).reshape(B, 128, H * W); b = (f2 / 4.0).reshape(B, 128, H * W)
+    ref0 = torch.matmul(a.transpose(1, 2), b).view(B, H, W, H, W)
+    assert lv[0].shape == ref0.shape and lv[0].dtype == torch.float16
+    d = (lv[0].float() - ref0.float()).abs()
+    ulp = torch.maximum(torch.maximum(ref0.float().abs(), lv[0].float().abs()), torch.tensor(2.0 ** -14, device=DEV)) * (1.001 * 2.0 ** -10) + 1e-5   # + float32 accumulation-order noise under cancellation
+    assert bool((d <= ulp).all()) and float((d > 0).float().mean()) < 0.02
+    exact = torch.matmul(a.double().transpose(1, 2), b.double()).view(B, H, W, H, W)
+    assert float((lv[0].double() - exact).abs().max() / exact.abs().max()) < 1e-3
+    for l in range(1, 4):
+        prev = lv[l - 1].reshape(B * H * W, 1, H >> (l - 1), W >> (l - 1))
+        want = F.avg_pool2d(prev, 2, stride=2).view(B, H, W, H >> l, W >> l)
+        assert torch.equal(lv[l], want), "level %d" % l
+    if H * W <= 512:
+        o = O.corr_build(p["fmaps"][p["ii"]], p["fmaps"][p["jj"]])
+        for l in range(4):
+            dd = np.abs(lv[l].float().cpu().numpy() - o[l].astype(np.float32))
+            assert dd.max() <= np.abs(o[l].astype(np.float32)).max() * 2.0 ** -9
+
+
 # ---------------------------------------------------------------- geometry --------------------
 def test_projmap_iproj(backends):
     poses, disps, intr, ii, jj = geom_inputs()
