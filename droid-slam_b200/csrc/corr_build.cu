@@ -103,6 +103,19 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
+// TMA store of one staged level-0 row block: shared [128 pixels][64 columns] (128B-swizzled) -> lvl0[b][m..][h2][:]
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(map), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ float2 unpack_h2(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
+__device__ __forceinline__ uint32_t pool4_h2(uint32_t top_a, uint32_t bot_a, uint32_t top_b, uint32_t bot_b);
+
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
   __half2 h = __floats2half2_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
@@ -113,6 +126,11 @@ __device__ __forceinline__ float pool4(float a, float b, float c, float d) {
   return __half2float(__float2half_rn((((a + b) + c) + d) * 0.25f));
 }
 __device__ __forceinline__ float rnd_h(float x) { return __half2float(__float2half_rn(x)); }
+// two horizontally adjacent 2x2 windows: (top_a, bot_a) and (top_b, bot_b) hold (w, w+1) pairs of two rows
+__device__ __forceinline__ uint32_t pool4_h2(uint32_t top_a, uint32_t bot_a, uint32_t top_b, uint32_t bot_b) {
+  const float2 ta = unpack_h2(top_a), ba = unpack_h2(bot_a), tb = unpack_h2(top_b), bb = unpack_h2(bot_b);
+  return pack_h2(pool4(ta.x, ta.y, ba.x, ba.y), pool4(tb.x, tb.y, bb.x, bb.y));
+}
 
 }  // namespace cb
 }  // namespace droid
@@ -124,14 +142,16 @@ struct Smem {
   // operand buffers first (1024-byte aligned for the 128-byte swizzle)
   static constexpr int kBOff = 0;
   static constexpr int kAOff = kMaxNBoxes * kBoxBytes;          // 128 KB
-  static constexpr int kBarOff = kAOff + 2 * kABytes;           // +64 KB
+  static constexpr int kStageOff = kAOff + 2 * kABytes;         // +64 KB: two 16 KB level-0 row staging buffers
+  static constexpr int kStageBytes = kTileM * 64 * 2;           // 128 pixels x 64 columns fp16
+  static constexpr int kBarOff = kStageOff + 2 * kStageBytes;
   static constexpr int kBytes = kBarOff + 128 + 1024;
 };
 
 template <int W>
 __global__ void __launch_bounds__(kThreads, 1)
 corr_build_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  __half* __restrict__ lvl0, __half* __restrict__ lvl1, __half* __restrict__ lvl2,
+                  const __grid_constant__ CUtensorMap tmOut, __half* __restrict__ lvl0, __half* __restrict__ lvl1, __half* __restrict__ lvl2,
                   __half* __restrict__ lvl3, int H, int HW) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   // the 128-byte swizzle needs 1024-byte aligned atoms; align by hand (1 KB of slack is allocated)
@@ -210,6 +230,87 @@ corr_build_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ---------------- epilogue: one TMEM lane (= one frame-1 pixel) per thread ----------------
     const float scale = 0.0625f;                 // (1/4) * (1/4), exact
     const int H2 = H / 2, W2 = W / 2, H4 = H / 4, W4 = W / 4, H8 = H / 8, W8 = W / 8;
+    if constexpr (W == 64) {
+      // Level 0 (75 % of the bytes) leaves through shared memory and TMA: every thread writes its pixel's 128-byte
+      // row of the staged [128 x 64] block (128B-swizzled: conflict-free), one elected thread issues the bulk store.
+      unsigned char* stage = smem + Smem::kStageOff;
+      const int row_in_tile = warp * 32 + lane;
+      for (int t = 0; t < T; t++) {
+        const int m = t * kTileM + row_in_tile;
+        const bool live = m < HW;
+        const size_t pix = (size_t)b * HW + (live ? m : 0);
+        uint32_t l2keep[2][8];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          mbar_wait(acc_full + h, t & 1);
+          tc_fence_after();
+          const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + h * NHALF;
+          uint32_t prev[32], p1keep[16];
+#pragma unroll
+          for (int r = 0; r < 4; r++) {
+            uint32_t cur[32];
+            {
+              float v[64];
+#pragma unroll
+              for (int j = 0; j < 4; j++) tmem_ld16(taddr + r * 64 + j * 16, v + j * 16);
+              tmem_ld_wait();
+              if (r == 3) {                         // this half of TMEM is drained: let the next tile's MMAs start
+                tc_fence_before();
+                mbar_arrive(acc_empty + h);
+              }
+#pragma unroll
+              for (int i = 0; i < 32; i++) cur[i] = pack_h2(v[2 * i] * scale, v[2 * i + 1] * scale);
+            }
+            unsigned char* buf = stage + (r & 1) * Smem::kStageBytes;
+            if (threadIdx.x == 0) bulk_wait_read<1>();   // the store that last used this buffer has read it
+            epi_barrier();
+            uint4* rowp = reinterpret_cast<uint4*>(buf + row_in_tile * 128);
+#pragma unroll
+            for (int j = 0; j < 8; j++)
+              rowp[j ^ (row_in_tile & 7)] = make_uint4(cur[4 * j], cur[4 * j + 1], cur[4 * j + 2], cur[4 * j + 3]);
+            fence_async_smem();
+            epi_barrier();
+            if (threadIdx.x == 0) {
+              tma_store_4d(&tmOut, buf, 0, nt * 8 + h * 4 + r, t * kTileM, b);
+              bulk_commit();
+            }
+            if (r & 1) {
+              uint32_t p1[16];
+#pragma unroll
+              for (int i = 0; i < 16; i++) p1[i] = pool4_h2(prev[2 * i], cur[2 * i], prev[2 * i + 1], cur[2 * i + 1]);
+              if (live) {
+                uint4* dst = reinterpret_cast<uint4*>(lvl1 + (pix * H2 + (nt * 4 + h * 2 + (r >> 1))) * W2);
+#pragma unroll
+                for (int j = 0; j < 4; j++) dst[j] = make_uint4(p1[4 * j], p1[4 * j + 1], p1[4 * j + 2], p1[4 * j + 3]);
+              }
+              if (r == 1) {
+#pragma unroll
+                for (int i = 0; i < 16; i++) p1keep[i] = p1[i];
+              } else {
+#pragma unroll
+                for (int i = 0; i < 8; i++) l2keep[h][i] = pool4_h2(p1keep[2 * i], p1[2 * i], p1keep[2 * i + 1], p1[2 * i + 1]);
+                if (live) {
+                  uint4* dst = reinterpret_cast<uint4*>(lvl2 + (pix * H4 + (nt * 2 + h)) * W4);
+                  dst[0] = make_uint4(l2keep[h][0], l2keep[h][1], l2keep[h][2], l2keep[h][3]);
+                  dst[1] = make_uint4(l2keep[h][4], l2keep[h][5], l2keep[h][6], l2keep[h][7]);
+                }
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; i++) prev[i] = cur[i];
+            }
+          }
+        }
+        if (live) {
+          uint4* dst = reinterpret_cast<uint4*>(lvl3 + (pix * H8 + nt) * W8);
+          dst[0] = make_uint4(pool4_h2(l2keep[0][0], l2keep[1][0], l2keep[0][1], l2keep[1][1]),
+                              pool4_h2(l2keep[0][2], l2keep[1][2], l2keep[0][3], l2keep[1][3]),
+                              pool4_h2(l2keep[0][4], l2keep[1][4], l2keep[0][5], l2keep[1][5]),
+                              pool4_h2(l2keep[0][6], l2keep[1][6], l2keep[0][7], l2keep[1][7]));
+        }
+      }
+      if (threadIdx.x == 0) bulk_wait_read<0>();
+    } else
     for (int t = 0; t < T; t++) {
       const int m = t * kTileM + warp * 32 + lane;
       const bool live = m < HW;
@@ -311,8 +412,21 @@ static bool make_map(CUtensorMap* m, const void* base, int B, int HW) {
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// lvl0 [B][HW][H][W] fp16 as (w, h2, m, b); box = one image row of 128 consecutive pixels m, 128B swizzle
+static bool make_out_map(CUtensorMap* m, void* base, int B, int HW, int H, int W) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  cuuint64_t dims[4] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)HW, (cuuint64_t)B};
+  cuuint64_t strides[3] = {(cuuint64_t)W * 2, (cuuint64_t)H * W * 2, (cuuint64_t)HW * H * W * 2};
+  cuuint32_t box[4] = {(cuuint32_t)W, 1, kTileM, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            W == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <int W>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, void* l0, void* l1, void* l2, void* l3, int B, int H,
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, void* l0, void* l1, void* l2, void* l3, int B, int H,
                   cudaStream_t st) {
   static bool attr = false;
   if (!attr) {
@@ -321,7 +435,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, void* l0, void* 
   }
   ProfScope ps(DROID_PROF_CORR_GEMM, st);
   DROID_LAUNCH corr_build_kernel<W><<<dim3(H / 8, B), kThreads, Smem::kBytes, st>>>(
-      ta, tb, (__half*)l0, (__half*)l1, (__half*)l2, (__half*)l3, H, H * W);
+      ta, tb, to, (__half*)l0, (__half*)l1, (__half*)l2, (__half*)l3, H, H * W);
   return check_launch();
 }
 
@@ -345,13 +459,15 @@ extern "C" int droid_corr_build(const void* fmap1, const void* fmap2, void* lvl0
   // supported shapes: 128 channels (DroidNet fnet), H % 8 == 0, W in {16,32,48,64}
   if (C != cb::kC || (H % 8) != 0 || (W % 16) != 0 || W > 64) return DROID_ERR_NOT_IMPLEMENTED;
   if (((uintptr_t)fmap1 & 15) || ((uintptr_t)fmap2 & 15) || B > 65535) return DROID_ERR_INVALID_ARGUMENT;
-  CUtensorMap ta, tb;
-  if (!cb::make_map(&ta, fmap1, B, H * W) || !cb::make_map(&tb, fmap2, B, H * W)) return DROID_ERR_CUDA;
+  CUtensorMap ta, tb, to;
+  if (!cb::make_map(&ta, fmap1, B, H * W) || !cb::make_map(&tb, fmap2, B, H * W) ||
+      !cb::make_out_map(&to, lvl0, B, H * W, H, W))
+    return DROID_ERR_CUDA;
   cudaStream_t st = (cudaStream_t)stream;
   switch (W) {
-    case 16: return cb::launch<16>(ta, tb, lvl0, lvl1, lvl2, lvl3, B, H, st);
-    case 32: return cb::launch<32>(ta, tb, lvl0, lvl1, lvl2, lvl3, B, H, st);
-    case 48: return cb::launch<48>(ta, tb, lvl0, lvl1, lvl2, lvl3, B, H, st);
-    default: return cb::launch<64>(ta, tb, lvl0, lvl1, lvl2, lvl3, B, H, st);
+    case 16: return cb::launch<16>(ta, tb, to, lvl0, lvl1, lvl2, lvl3, B, H, st);
+    case 32: return cb::launch<32>(ta, tb, to, lvl0, lvl1, lvl2, lvl3, B, H, st);
+    case 48: return cb::launch<48>(ta, tb, to, lvl0, lvl1, lvl2, lvl3, B, H, st);
+    default: return cb::launch<64>(ta, tb, to, lvl0, lvl1, lvl2, lvl3, B, H, st);
   }
 }
