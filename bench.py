@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-frames", type=int, default=64, help="keyframes of the bounded CPU-baseline sample")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the corr-lookup / frontend-window side metrics")
     return ap.parse_args()
 
 
@@ -279,7 +280,82 @@ def run_b200(args, world, rank, local):
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)
+    if world == 1 and not args.no_extra:
+        try:
+            line["extra"] = extra_metrics(dev, hbm_peak, peaks)
+        except Exception as ex:                                    # noqa: BLE001
+            line["extra"] = {"error": repr(ex)}
     return line
+
+
+def extra_metrics(dev, hbm_peak, peaks):
+    """The other two parts of BASELINE.json's metric, measured in the same run (not the headline `value`):
+    corr build + 4-level radius-3 lookup at configs[1] (24 edges, 48x64x128 fp16) in GB/s against the measured HBM
+    peak, and the frontend-window BA (configs[2]: 12 keyframes, 60 edges, 48x64, iterations=2) as calls/s."""
+    import droid_backends as B
+    import synth
+    out = {}
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def timeit(fn, n=20, warm=3):
+        for _ in range(warm):
+            fn()
+        ts = []
+        for _ in range(n):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        return float(np.median(ts)) * 1e-3
+
+    Bn, H, W, C, r = 24, 48, 64, 128, 3
+    q = synth.make_corr_problem(Bn, H, W, C, seed=1234)
+    f1 = torch.from_numpy(q["fmaps"][q["ii"]]).to(dev)
+    f2 = torch.from_numpy(q["fmaps"][q["jj"]]).to(dev)
+    coords = torch.from_numpy(q["coords"]).to(dev)
+    HW = H * W
+    t = timeit(lambda: B.corr_build(f1, f2))
+    vols = B.corr_build(f1, f2)
+    by = Bn * HW * (HW + HW // 4 + HW // 16 + HW // 64) * 2 + 2 * Bn * C * HW * 2
+    fl = 2.0 * HW * HW * C * Bn
+    tpeak = float(peaks.get("bf16_tflops", 1590.0))
+    out["corr_build"] = {"us": t * 1e6, "GBps": by / t / 1e9, "hbm_frac": by / t / 1e9 / hbm_peak, "TFLOPs": fl / t / 1e12,
+                         "tensor_frac": fl / t / 1e12 / tpeak, "bound": "hbm (write)", "algorithmic_bytes": by,
+                         "workload": "24 edges, 48x64x128 fp16 -> 4-level pyramid", "l2": "flushed between calls"}
+    # lookup: coords (8 B) + up to 64 taps in + 49 out per pixel per level, 2 B elements (SURVEY 8d upper bound)
+    lb = 4 * Bn * HW * (8 + 64 * 2 + 49 * 2)
+    t = timeit(lambda: B.corr_index_pyramid(vols, coords, r))
+    out["corr_lookup_fused"] = {"us": t * 1e6, "GBps": lb / t / 1e9, "hbm_frac": lb / t / 1e9 / hbm_peak,
+                                "algorithmic_bytes": lb, "workload": "4 levels, radius 3, 24 edges, one launch"}
+    cl = [coords / 2 ** l for l in range(4)]
+    t = timeit(lambda: [B.corr_index_forward(vols[l], cl[l], r) for l in range(4)])
+    out["corr_lookup_4calls"] = {"us": t * 1e6, "GBps": lb / t / 1e9, "hbm_frac": lb / t / 1e9 / hbm_peak,
+                                 "workload": "the reference call pattern: 4x corr_index_forward"}
+    try:
+        import droid_backends_ref as R
+        t = timeit(lambda: [R.corr_index_forward(vols[l], cl[l], r) for l in range(4)])
+        out["corr_lookup_4calls_reference_ext"] = {"us": t * 1e6, "GBps": lb / t / 1e9}
+    except Exception:
+        pass
+    p = synth.make_ba_problem("C3")
+    d = {k: torch.from_numpy(np.ascontiguousarray(p[k])).to(dev) for k in KEYS}
+    p0, d0 = d["poses"].clone(), d["disps"].clone()
+
+    def fba(mod):
+        d["poses"].copy_(p0); d["disps"].copy_(d0)
+        mod.ba(d["poses"], d["disps"], d["intrinsics"], d["disps_sens"], d["targets"], d["weights"], d["eta"],
+               d["ii"], d["jj"], p["t0"], p["t1"], 2, 1e-4, 0.1, False)
+    t = timeit(lambda: fba(B), n=50)
+    out["frontend_ba"] = {"us_per_call": t * 1e6, "calls_per_s": 1.0 / t,
+                          "workload": "C3 frontend window: 12 keyframes, 60 edges, 48x64, ba(iterations=2, lm=1e-4, ep=0.1)"}
+    try:
+        import droid_backends_ref as R
+        t = timeit(lambda: fba(R), n=20)
+        out["frontend_ba_reference_ext"] = {"us_per_call": t * 1e6, "calls_per_s": 1.0 / t}
+    except Exception:
+        pass
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
