@@ -304,6 +304,7 @@ __device__ __forceinline__ void scatter_edge_value(double* __restrict__ A, doubl
 // over the frame's edges in shared memory (each pixel is owned by one thread => no atomics there).
 // ------------------------------------------------------------------------------------------------
 static constexpr int kSlabMax = 3072;
+static constexpr int kMetaChunk = 64;  // edges of one source frame staged in shared memory at a time
 
 __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
     const float* __restrict__ disps, const float* __restrict__ intrinsics,
@@ -316,6 +317,7 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
     int n_eta, int motion_only, int frame_lo, int frame_hi) {
   __shared__ float Cs[kSlabMax];
   __shared__ float Bs[kSlabMax];
+  __shared__ float Ds[kSlabMax];   // inverse depths of the slab (re-read for every edge of the frame)
   __shared__ float red[kThreads / 32][kHW_ACC];
   const int m = blockIdx.y;
   const int M = status[1];
@@ -328,74 +330,107 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
   const int n6 = 6 * P;
-  for (int p = tid; p < p1 - p0; p += kThreads) { Cs[p] = 0.f; Bs[p] = 0.f; }
-  __syncthreads();
   const float* __restrict__ dmap = disps + (size_t)k * HW;
+  for (int p = tid; p < p1 - p0; p += kThreads) { Cs[p] = 0.f; Bs[p] = 0.f; Ds[p] = dmap[p0 + p]; }
+  __syncthreads();
   const int e0 = eptr[m], e1 = eptr[m + 1];
-  for (int ei = e0; ei < e1; ei++) {
-    const int e = eidx[ei];
-    const int jx = (int)jj[e];
-    const bool stereo = (jx == k);
-    const SE3 g = load_gij(gij, e);
-    const float* __restrict__ tg = targets + (size_t)e * 2 * HW;
-    const float* __restrict__ wt = weights + (size_t)e * 2 * HW;
-    float acc[kHW_ACC];
-#pragma unroll
-    for (int l = 0; l < kHW_ACC; l++) acc[l] = 0.f;
-    for (int p = p0 + tid; p < p1; p += kThreads) {
-      PixLin L;
-      linearise(g, K, wd, p, dmap[p], tg[p], tg[HW + p], wt[p], wt[HW + p], stereo, L);
-      // depth terms (:320-321, :353-354)
-      float c = L.wu_d * L.Jz_u * L.Jz_u;
-      float bz = L.wu_d * L.ru * L.Jz_u;
-      c += L.wv_d * L.Jz_v * L.Jz_v;
-      bz += L.wv_d * L.rv * L.Jz_v;
-      Cs[p - p0] += c;
-      Bs[p - p0] += bz;
-      if (!stereo) {
-        float Jx[12];
-#pragma unroll
-        for (int n = 0; n < 6; n++) { Jx[n] = L.Ji_u[n]; Jx[6 + n] = L.Jj_u[n]; }
-        int l = 0;
-#pragma unroll
-        for (int n = 0; n < 12; n++) {
-          const float wj = L.wu * Jx[n];
-#pragma unroll
-          for (int q = 0; q <= n; q++) { acc[l] += wj * Jx[q]; l++; }
-        }
-        const float wr = L.wu * L.ru;
-#pragma unroll
-        for (int n = 0; n < 12; n++) acc[78 + n] += wr * Jx[n];
-#pragma unroll
-        for (int n = 0; n < 6; n++) { Jx[n] = L.Ji_v[n]; Jx[6 + n] = L.Jj_v[n]; }
-        l = 0;
-#pragma unroll
-        for (int n = 0; n < 12; n++) {
-          const float wj = L.wv * Jx[n];
-#pragma unroll
-          for (int q = 0; q <= n; q++) { acc[l] += wj * Jx[q]; l++; }
-        }
-        const float wr2 = L.wv * L.rv;
-#pragma unroll
-        for (int n = 0; n < 12; n++) acc[78 + n] += wr2 * Jx[n];
-      }
+  // Edge metadata (edge id, target frame, relative pose) is staged in shared memory in chunks, and the four
+  // input values of the NEXT (edge, pixel) item are fetched before the current item is processed: with ~90
+  // accumulators a thread cannot rely on occupancy to hide the HBM latency of its loads (ncu: 30 % long-scoreboard).
+  __shared__ int s_e[kMetaChunk];
+  __shared__ int s_jx[kMetaChunk];
+  __shared__ __align__(16) float s_g[kMetaChunk][8];
+  for (int eb = e0; eb < e1; eb += kMetaChunk) {
+    const int nE = min(kMetaChunk, e1 - eb);
+    __syncthreads();
+    for (int i = tid; i < nE; i += kThreads) {
+      const int e = eidx[eb + i];
+      s_e[i] = e;
+      s_jx[i] = (int)jj[e];
     }
-    if (!stereo) {
-      transpose_reduce96(acc, lane);
-      red[warp][3 * lane + 0] = acc[0];
-      red[warp][3 * lane + 1] = acc[1];
-      red[warp][3 * lane + 2] = acc[2];
-      __syncthreads();
-      if (tid < 90) {
-        float s = 0.f;
-#pragma unroll
-        for (int w = 0; w < kThreads / 32; w++) s += red[w][tid];
-        int pi = k - t0, pj = jx - t0;
-        if (pi < 0 || pi >= P) pi = -1;
-        if (pj < 0 || pj >= P) pj = -1;
-        scatter_edge_value(A, bvec, n6, tid, s, pi, pj);
+    for (int i = tid; i < nE * 8; i += kThreads) s_g[i >> 3][i & 7] = gij[(size_t)eidx[eb + (i >> 3)] * 8 + (i & 7)];
+    __syncthreads();
+    float n_tu = 0.f, n_tv = 0.f, n_wu = 0.f, n_wv = 0.f;
+    auto fetch = [&](int ei_, int p_) {
+      const size_t base = (size_t)s_e[ei_] * 2 * HW + p_;
+      n_tu = __ldg(targets + base); n_tv = __ldg(targets + base + HW);
+      n_wu = __ldg(weights + base); n_wv = __ldg(weights + base + HW);
+    };
+    if (p0 + tid < p1) fetch(0, p0 + tid);
+    for (int ei = 0; ei < nE; ei++) {
+      const int jx = s_jx[ei];
+      const bool stereo = (jx == k);
+      SE3 g;
+      {
+        const float4 ga = *reinterpret_cast<const float4*>(&s_g[ei][0]);
+        const float4 gb = *reinterpret_cast<const float4*>(&s_g[ei][4]);
+        g.t[0] = ga.x; g.t[1] = ga.y; g.t[2] = ga.z;
+        g.q[0] = ga.w; g.q[1] = gb.x; g.q[2] = gb.y; g.q[3] = gb.z;
       }
-      __syncthreads();
+      float acc[kHW_ACC];
+#pragma unroll
+      for (int l = 0; l < kHW_ACC; l++) acc[l] = 0.f;
+      for (int p = p0 + tid; p < p1; p += kThreads) {
+        const float tu = n_tu, tv = n_tv, wu = n_wu, wv = n_wv;
+        {
+          int pn = p + kThreads, ein = ei;
+          if (pn >= p1) { pn = p0 + tid; ein = ei + 1; }
+          if (ein < nE) fetch(ein, pn);
+        }
+        PixLin L;
+        linearise(g, K, wd, p, Ds[p - p0], tu, tv, wu, wv, stereo, L);
+        // depth terms (:320-321, :353-354)
+        float c = L.wu_d * L.Jz_u * L.Jz_u;
+        float bz = L.wu_d * L.ru * L.Jz_u;
+        c += L.wv_d * L.Jz_v * L.Jz_v;
+        bz += L.wv_d * L.rv * L.Jz_v;
+        Cs[p - p0] += c;
+        Bs[p - p0] += bz;
+        if (!stereo) {
+          float Jx[12];
+#pragma unroll
+          for (int n = 0; n < 6; n++) { Jx[n] = L.Ji_u[n]; Jx[6 + n] = L.Jj_u[n]; }
+          int l = 0;
+#pragma unroll
+          for (int n = 0; n < 12; n++) {
+            const float wj = L.wu * Jx[n];
+#pragma unroll
+            for (int q = 0; q <= n; q++) { acc[l] += wj * Jx[q]; l++; }
+          }
+          const float wr = L.wu * L.ru;
+#pragma unroll
+          for (int n = 0; n < 12; n++) acc[78 + n] += wr * Jx[n];
+#pragma unroll
+          for (int n = 0; n < 6; n++) { Jx[n] = L.Ji_v[n]; Jx[6 + n] = L.Jj_v[n]; }
+          l = 0;
+#pragma unroll
+          for (int n = 0; n < 12; n++) {
+            const float wj = L.wv * Jx[n];
+#pragma unroll
+            for (int q = 0; q <= n; q++) { acc[l] += wj * Jx[q]; l++; }
+          }
+          const float wr2 = L.wv * L.rv;
+#pragma unroll
+          for (int n = 0; n < 12; n++) acc[78 + n] += wr2 * Jx[n];
+        }
+      }
+      if (!stereo) {
+        transpose_reduce96(acc, lane);
+        red[warp][3 * lane + 0] = acc[0];
+        red[warp][3 * lane + 1] = acc[1];
+        red[warp][3 * lane + 2] = acc[2];
+        __syncthreads();
+        if (tid < 90) {
+          float sum = 0.f;
+#pragma unroll
+          for (int w = 0; w < kThreads / 32; w++) sum += red[w][tid];
+          int pi = k - t0, pj = jx - t0;
+          if (pi < 0 || pi >= P) pi = -1;
+          if (pj < 0 || pj >= P) pj = -1;
+          scatter_edge_value(A, bvec, n6, tid, sum, pi, pj);
+        }
+        __syncthreads();
+      }
     }
   }
   if (motion_only) return;
@@ -406,7 +441,7 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
   for (int p = p0 + tid; p < p1; p += kThreads) {
     const float mk = ds[p] > 0.f ? 1.0f : 0.0f;
     const float C = Cs[p - p0] + mk * alpha + (1 - mk) * et[p];
-    const float w = Bs[p - p0] - mk * alpha * (dmap[p] - ds[p]);
+    const float w = Bs[p - p0] - mk * alpha * (Ds[p - p0] - ds[p]);
     Qo[(size_t)m * HW + p] = (float)(1.0 / (double)C);
     Wo[(size_t)m * HW + p] = w;
   }
@@ -488,9 +523,10 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
   const int e0 = eptr[m], e1 = eptr[m + 1];
   const int deg = e1 - e0;
   const int D = deg + 1, R = 6 * D;
-  const int stride = (R & 3) == 2 ? R : R + 2;  // == 2 (mod 4): even (LDS.64) and 2-way STS at worst
-  // smem: E[T][stride] | Qs[T] | QWs[T] | vS[R] | pose[D]
-  const int fixed = (R + D + 8) * 4;
+  const int DP = (D + 1) >> 1, RP = 12 * DP;   // row blocks are processed in pairs (12 rows); odd D is zero-padded
+  const int stride = RP + 2;                    // == 2 (mod 4): even (LDS.64) and spreads the banks
+  // smem: E[T][stride] | Qs[T] | QWs[T] | vS[R] | pose[2*DP] | s_e[deg] | s_jx[deg] | s_g[deg][8]
+  const int fixed = (R + 2 * DP + 8 + 10 * deg + 4) * 4;
   int T = (kSchurSmemBytes - fixed) / ((stride + 2) * 4);
   T = min(T, kThreads) & ~31;
   if (T < 32) {  // out-degree too large for one SM's shared memory
@@ -502,15 +538,31 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
   float* QWs = Qs + T;
   float* vS = QWs + T;
   int* pose = reinterpret_cast<int*>(vS + R);
+  int* s_e = pose + 2 * DP;
+  int* s_jx = s_e + deg;
+  float* s_g = reinterpret_cast<float*>(s_jx + deg);
+  s_g += (4 - ((reinterpret_cast<uintptr_t>(s_g) >> 2) & 3)) & 3;   // 16-byte aligned
   const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
   const int n6 = 6 * P;
-  for (int d = tid; d < D; d += kThreads) {
-    int pz = (d == 0) ? k - t0 : (int)jj[eidx[e0 + d - 1]] - t0;
-    if (pz < 0 || pz >= P) pz = -1;
+  for (int i = tid; i < deg; i += kThreads) {
+    const int e = eidx[e0 + i];
+    s_e[i] = e;
+    s_jx[i] = (int)jj[e];
+  }
+  for (int i = tid; i < deg * 8; i += kThreads) s_g[i] = gij[(size_t)eidx[e0 + (i >> 3)] * 8 + (i & 7)];
+  for (int d = tid; d < 2 * DP; d += kThreads) {
+    int pz = -1;
+    if (d < D) {
+      pz = (d == 0) ? k - t0 : (int)jj[eidx[e0 + d - 1]] - t0;
+      if (pz < 0 || pz >= P) pz = -1;
+    }
     pose[d] = pz;
   }
   for (int r = tid; r < R; r += kThreads) vS[r] = 0.f;
-  const int ntiles = (D & 1) ? ((D + 1) / 2) * ((D + 1) / 2) : (D / 2) * (D / 2 + 1);  // base(D)
+  if (RP > R)  // padding rows of an odd block count stay zero for the whole kernel
+    for (int e = tid; e < T * (RP - R); e += kThreads) Es[(size_t)(e / (RP - R)) * stride + R + e % (RP - R)] = 0.f;
+  // register tiles: 12x12 (a pair of row blocks x a pair of column blocks), lower triangle of pair-blocks
+  const int ntiles = DP * (DP + 1) / 2;
   const int G = ntiles >= kThreads ? 1 : min(kThreads / ntiles, 8);
   const int slots = ntiles >= kThreads ? kThreads : ntiles;
   const int g = tid / slots, tslot = tid - g * slots;
@@ -522,12 +574,17 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
     const int tile = pass * slots + tslot;
     const bool active = (g < G) && (tile < ntiles);
     int a = 0, c = 0;
-    if (active) tile_to_ac(tile, a, c);
-    const int b0 = 2 * c, b1 = 2 * c + 1;
-    const bool has1 = active && (b1 <= a);
-    float acc0[36], acc1[36];
+    if (active) {
+      a = (int)((sqrtf(8.f * tile + 1.f) - 1.f) * 0.5f);
+      while ((a + 1) * (a + 2) / 2 <= tile) a++;
+      while (a * (a + 1) / 2 > tile) a--;
+      c = tile - a * (a + 1) / 2;
+    }
+    float acc[12][12];
 #pragma unroll
-    for (int i = 0; i < 36; i++) { acc0[i] = 0.f; acc1[i] = 0.f; }
+    for (int i = 0; i < 12; i++)
+#pragma unroll
+      for (int j = 0; j < 12; j++) acc[i][j] = 0.f;
 
     for (int pt = p0; pt < p1; pt += T) {
       const int np = min(T, p1 - pt);
@@ -537,14 +594,27 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
         float* Erow = Es + (size_t)tid * stride;
         float Ei[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         const float dp = dmap[p];
+        float n_tu, n_tv, n_wu, n_wv;
+        auto fetch = [&](int i) {
+          const size_t base = (size_t)s_e[i] * 2 * HW + p;
+          n_tu = __ldg(targets + base); n_tv = __ldg(targets + base + HW);
+          n_wu = __ldg(weights + base); n_wv = __ldg(weights + base + HW);
+        };
+        if (deg > 0) fetch(0);
         for (int ei = e0; ei < e1; ei++) {
-          const int e = eidx[ei];
-          const int jx = (int)jj[e];
-          const SE3 gg = load_gij(gij, e);
-          const float* __restrict__ tg = targets + (size_t)e * 2 * HW;
-          const float* __restrict__ wt = weights + (size_t)e * 2 * HW;
+          const int i = ei - e0;
+          const int jx = s_jx[i];
+          const float tu = n_tu, tv = n_tv, wu = n_wu, wv = n_wv;
+          if (i + 1 < deg) fetch(i + 1);     // next edge's inputs are in flight while this one is linearised
+          SE3 gg;
+          {
+            const float4 ga = *reinterpret_cast<const float4*>(s_g + 8 * i);
+            const float4 gb = *reinterpret_cast<const float4*>(s_g + 8 * i + 4);
+            gg.t[0] = ga.x; gg.t[1] = ga.y; gg.t[2] = ga.z;
+            gg.q[0] = ga.w; gg.q[1] = gb.x; gg.q[2] = gb.y; gg.q[3] = gb.z;
+          }
           PixLin L;
-          linearise(gg, K, wd, p, dp, tg[p], tg[HW + p], wt[p], wt[HW + p], jx == k, L);
+          linearise(gg, K, wd, p, dp, tu, tv, wu, wv, jx == k, L);
           const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
           float* Ej = Erow + 6 * (ei - e0 + 1);
 #pragma unroll
@@ -564,34 +634,24 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
         QWs[tid] = q * Wi[(size_t)m * HW + p];
       }
       __syncthreads();
-      // ---- (b) Gram product over the tile ------------------------------------------------------
+      // ---- (b) Gram product over the tile: 144 FFMA per 12 LDS.64 -----------------------------
       if (active) {
         for (int p = g; p < np; p += G) {
           const float* Erow = Es + (size_t)p * stride;
           const float q = Qs[p];
-          float ea[6], eb[6], ec[6];
-          {
-            const float2* pa2 = reinterpret_cast<const float2*>(Erow + 6 * a);
-            const float2 x0 = pa2[0], x1 = pa2[1], x2 = pa2[2];
-            ea[0] = x0.x * q; ea[1] = x0.y * q; ea[2] = x1.x * q;
-            ea[3] = x1.y * q; ea[4] = x2.x * q; ea[5] = x2.y * q;
-            const float2* pb2 = reinterpret_cast<const float2*>(Erow + 6 * b0);
-            const float2 y0 = pb2[0], y1 = pb2[1], y2 = pb2[2];
-            eb[0] = y0.x; eb[1] = y0.y; eb[2] = y1.x; eb[3] = y1.y; eb[4] = y2.x; eb[5] = y2.y;
+          float ea[12], ec[12];
+          const float2* pa2 = reinterpret_cast<const float2*>(Erow + 12 * a);
+          const float2* pc2 = reinterpret_cast<const float2*>(Erow + 12 * c);
+#pragma unroll
+          for (int i = 0; i < 6; i++) {
+            const float2 x = pa2[i], y = pc2[i];
+            ea[2 * i] = x.x * q; ea[2 * i + 1] = x.y * q;
+            ec[2 * i] = y.x; ec[2 * i + 1] = y.y;
           }
 #pragma unroll
-          for (int n = 0; n < 6; n++)
+          for (int i = 0; i < 12; i++)
 #pragma unroll
-            for (int mm = 0; mm < 6; mm++) acc0[n * 6 + mm] = fmaf(ea[n], eb[mm], acc0[n * 6 + mm]);
-          if (has1) {
-            const float2* pc2 = reinterpret_cast<const float2*>(Erow + 6 * b1);
-            const float2 z0 = pc2[0], z1 = pc2[1], z2 = pc2[2];
-            ec[0] = z0.x; ec[1] = z0.y; ec[2] = z1.x; ec[3] = z1.y; ec[4] = z2.x; ec[5] = z2.y;
-#pragma unroll
-            for (int n = 0; n < 6; n++)
-#pragma unroll
-              for (int mm = 0; mm < 6; mm++) acc1[n * 6 + mm] = fmaf(ea[n], ec[mm], acc1[n * 6 + mm]);
-          }
+            for (int j = 0; j < 12; j++) acc[i][j] = fmaf(ea[i], ec[j], acc[i][j]);
         }
       }
       // ---- v_S rows (first pass only) -----------------------------------------------------------
@@ -604,10 +664,22 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
       }
       __syncthreads();
     }
-    // ---- (c) subtract from the dense system ------------------------------------------------------
+    // ---- (c) subtract the four 6x6 blocks of the tile from the dense system ---------------------
     if (active) {
-      flush_block(A, n6, acc0, pose[a], pose[b0], a == b0);
-      if (has1) flush_block(A, n6, acc1, pose[a], pose[b1], a == b1);
+      const int ra = 2 * a, rc = 2 * c;
+      float blk[36];
+#pragma unroll
+      for (int bi = 0; bi < 2; bi++)
+#pragma unroll
+        for (int bj = 0; bj < 2; bj++) {
+          const int rb = ra + bi, cb = rc + bj;   // block row / block column of E
+          if (rb >= D || cb >= D || cb > rb) continue;
+#pragma unroll
+          for (int i = 0; i < 6; i++)
+#pragma unroll
+            for (int j = 0; j < 6; j++) blk[i * 6 + j] = acc[bi * 6 + i][bj * 6 + j];
+          flush_block(A, n6, blk, pose[rb], pose[cb], rb == cb);
+        }
     }
   }
   for (int r = tid; r < R; r += kThreads) {
@@ -642,14 +714,29 @@ __global__ void __launch_bounds__(kThreads) ba_dz_kernel(
   const int e0 = eptr[m], e1 = eptr[m + 1];
   float Ei[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   float sum = 0.f;
+  // one-edge-ahead software prefetch of (edge id, target frame, relative pose, target, weight)
+  int n_jx = 0;
+  float4 n_ga = make_float4(0, 0, 0, 0), n_gb = make_float4(0, 0, 0, 0);
+  float n_tu = 0.f, n_tv = 0.f, n_wu = 0.f, n_wv = 0.f;
+  auto fetch = [&](int ei_) {
+    const int e_ = eidx[ei_];
+    n_jx = (int)jj[e_];
+    n_ga = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e_ * 8));
+    n_gb = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e_ * 8 + 4));
+    const size_t base = (size_t)e_ * 2 * HW + p;
+    n_tu = __ldg(targets + base); n_tv = __ldg(targets + base + HW);
+    n_wu = __ldg(weights + base); n_wv = __ldg(weights + base + HW);
+  };
+  if (e0 < e1) fetch(e0);
   for (int ei = e0; ei < e1; ei++) {
-    const int e = eidx[ei];
-    const int jx = (int)jj[e];
-    const SE3 g = load_gij(gij, e);
-    const float* __restrict__ tg = targets + (size_t)e * 2 * HW;
-    const float* __restrict__ wt = weights + (size_t)e * 2 * HW;
+    const int jx = n_jx;
+    SE3 g;
+    g.t[0] = n_ga.x; g.t[1] = n_ga.y; g.t[2] = n_ga.z;
+    g.q[0] = n_ga.w; g.q[1] = n_gb.x; g.q[2] = n_gb.y; g.q[3] = n_gb.z;
+    const float tu = n_tu, tv = n_tv, wu = n_wu, wv = n_wv;
+    if (ei + 1 < e1) fetch(ei + 1);
     PixLin L;
-    linearise(g, K, wd, p, dp, tg[p], tg[HW + p], wt[p], wt[HW + p], jx == k, L);
+    linearise(g, K, wd, p, dp, tu, tv, wu, wv, jx == k, L);
     const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
     const int pj = jx - t0;
     const bool use = pj > 0 && pj < P;
