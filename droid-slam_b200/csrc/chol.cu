@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(256) chol_small_kernel(double* __restrict__ A,
 // ------------------------------------------------------------------------------------------------
 static constexpr int PB = 128;
 static constexpr int PR = 192;
-static constexpr int kPanelSmem = (256 * 65 + 64 * 66 + 2 * 128 + 80 + 80 + 64) * (int)sizeof(double);
+static constexpr int kPanelSmem = (256 * 65 + 2 * 128 + 80 + 80 + 64) * (int)sizeof(double);
 
 // One column of the lockstep elimination.  The 64 columns are processed as 4 blocks of 16: inside a block
 // the step index C is a compile-time constant (a[] stays in registers, static indexing), between blocks
@@ -130,78 +130,44 @@ struct ElimStep<kRot> {
   static __device__ __forceinline__ void run(double (&)[64], double*, const double*, double*, double*, int, int) {}
 };
 
-__global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__ A, int n, int J, int j0,
-                                                            int jb, int* __restrict__ info) {
+__global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__ A, int n, int j0, int jb,
+                                                            int* __restrict__ info) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* R = reinterpret_cast<double*>(smem_raw);  // [256][65] row staging
-  double* XdT = R + 256 * 65;                        // [64][66]  Xd^T: [k][c] = A[j0+c][J+k]
-  double* col = XdT + 64 * 66;                       // [2][128]  published column (double-buffered, padded)
+  double* col = R + 256 * 65;                        // [2][128]  published column (double-buffered, padded)
   double* inv = col + 256;                           // [80]      1 / pivot
   double* dv = inv + 80;                             // [80]      pivots
   double* rs = dv + 80;                              // [64]      1 / sqrt(pivot)
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int prev = j0 - J;
+  const int tid = threadIdx.x;
   const bool diag = tid < 64;
   const int trow0 = j0 + jb + blockIdx.x * PR;       // first trailing row of this CTA
   auto row_of = [&](int t) { return t < 64 ? j0 + t : trow0 + t - 64; };
   auto row_ok = [&](int t) { return t < 64 ? t < jb : (trow0 + t - 64) <= n; };
-  // R[t][c] = A[row(t)][cbase + c], c < width (zero elsewhere); 16 loads in flight per thread, one
-  // 512-byte row segment per warp-instruction.  `tri`: keep the lower triangle of the diagonal block
-  // only and pad a partial block with the identity.
-  auto stage = [&](int cbase, int width, bool tri) {
-#pragma unroll 1
-    for (int q0 = 0; q0 < 64; q0 += 16) {
-      double v[16];
-#pragma unroll
-      for (int q = 0; q < 16; q++) {
-        const int t = (q0 + q) * 4 + (tid >> 6), c = tid & 63;
-        v[q] = (row_ok(t) && c < width) ? A[(size_t)row_of(t) * n + cbase + c] : 0.0;
-      }
-#pragma unroll
-      for (int q = 0; q < 16; q++) {
-        const int t = (q0 + q) * 4 + (tid >> 6), c = tid & 63;
-        double x = v[q];
-        if (tri && t < 64) {
-          if (c > t) x = 0.0;
-          if (t >= jb && c == t) x = 1.0;
-        }
-        R[t * 65 + c] = x;
-      }
-    }
-  };
 
   double a[64];
+  // stage: all 64 loads of a thread are in flight at once (a[] doubles as the landing zone); a warp-instruction
+  // reads 256 contiguous bytes of one row.  Diagonal block: lower triangle only, partial block padded with I.
+  const int tq = tid >> 6, tc = tid & 63;
 #pragma unroll
-  for (int c = 0; c < 64; c++) a[c] = 0.0;
-
-  if (prev > 0) {
-    stage(J, prev, false);
-    __syncthreads();
-    for (int e = tid; e < 64 * 64; e += 256) {
-      const int c = e & 63, k = e >> 6;
-      XdT[k * 66 + c] = (c < jb && k < prev) ? R[c * 65 + k] : 0.0;
-    }
-    __syncthreads();
-    for (int k = 0; k < prev; k++) {
-      const double xk = R[tid * 65 + k];
-      const double2* w2 = reinterpret_cast<const double2*>(XdT + k * 66);
-#pragma unroll
-      for (int c = 0; c < 64; c += 2) {
-        const double2 w = w2[c >> 1];
-        a[c] = fma(-xk, w.x, a[c]);
-        a[c + 1] = fma(-xk, w.y, a[c + 1]);
-      }
-    }
-    __syncthreads();
+  for (int q = 0; q < 64; q++) {
+    const int t = q * 4 + tq;
+    a[q] = (row_ok(t) && tc < jb) ? A[(size_t)row_of(t) * n + j0 + tc] : 0.0;
   }
-  stage(j0, jb, true);
-  __syncthreads();
 #pragma unroll
-  for (int c = 0; c < 64; c++) a[c] += R[tid * 65 + c];
-  // prev-update of the padding rows touched nothing (their x rows are zero)
+  for (int q = 0; q < 64; q++) {
+    const int t = q * 4 + tq;
+    double x = a[q];
+    if (t < 64) {
+      if (tc > t) x = 0.0;
+      if (t >= jb && tc == t) x = 1.0;
+    }
+    R[t * 65 + tc] = x;
+  }
   if (tid < 128) { col[tid] = 0.0; col[128 + tid] = 0.0; }
   if (tid < 80) inv[tid] = 0.0;
   __syncthreads();
+#pragma unroll
+  for (int c = 0; c < 64; c++) a[c] = R[tid * 65 + c];
   if (diag) {
     col[tid] = a[0];
     if (tid == 0) { inv[0] = 1.0 / a[0]; dv[0] = a[0]; }
@@ -209,10 +175,10 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
 #pragma unroll 1
   for (int cb = 0; cb < 64 / kRot; cb++) {
     ElimStep<0>::run(a, col, inv, inv, dv, tid, cb * kRot);
-    __syncthreads();                                   // everyone is done with R's staged values / col
-#pragma unroll
-    for (int i = 0; i < kRot; i++) R[tid * 65 + cb * kRot + i] = a[i];
     if (kRot < 64) {
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < kRot; i++) R[tid * 65 + cb * kRot + i] = a[i];
 #pragma unroll
       for (int i = 0; i < 64 - kRot; i++) a[i] = a[i + kRot];
 #pragma unroll
@@ -226,15 +192,20 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
     rs[tid] = 1.0 / sqrt(d);
   }
   __syncthreads();
+  if (kRot == 64) {
+#pragma unroll
+    for (int c = 0; c < 64; c++) R[tid * 65 + c] = a[c] * rs[c];
+  } else {
 #pragma unroll 8
-  for (int c = 0; c < 64; c++) R[tid * 65 + c] *= rs[c];
+    for (int c = 0; c < 64; c++) R[tid * 65 + c] *= rs[c];
+  }
   __syncthreads();
-  for (int t = warp; t < 256; t += 8) {
-    if (!row_ok(t)) continue;
-    if (t < 64 && blockIdx.x != 0) continue;      // the diagonal block is written once
-    double* dst = A + (size_t)row_of(t) * n + j0;
-    for (int c = lane; c < jb; c += 32)
-      if (t >= 64 || c <= t) dst[c] = R[t * 65 + c];
+#pragma unroll 16
+  for (int q = 0; q < 64; q++) {
+    const int t = q * 4 + tq;
+    if (!row_ok(t) || tc >= jb) continue;
+    if (t < 64 && (blockIdx.x != 0 || tc > t)) continue;   // the diagonal block is written once, lower part
+    A[(size_t)row_of(t) * n + j0 + tc] = R[t * 65 + tc];
   }
 }
 
@@ -246,7 +217,7 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
 // ------------------------------------------------------------------------------------------------
 template <int TM, bool VEC>
 __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
-    chol_syrk_kernel(double* __restrict__ A, int n, int J, int kb) {
+    chol_syrk_kernel(double* __restrict__ A, int n, int J, int kb, int strip) {
   constexpr int F = TM / 64;
   constexpr int KC = 16;
   constexpr int LD = TM + 2;
@@ -254,14 +225,25 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* sm = reinterpret_cast<double*>(smem_raw);  // [2 buffers][2 operands][KC][LD]
   const int t = blockIdx.x;
-  int bi = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
-  while ((bi + 1) * (bi + 2) / 2 <= t) bi++;
-  while (bi * (bi + 1) / 2 > t) bi--;
-  const int bj = t - bi * (bi + 1) / 2;
+  int bi, bj;
+  if (strip > 0) {   // only the first block column (`strip` columns wide)
+    bi = t; bj = 0;
+  } else if (strip < 0) {   // everything except the first block column (look-ahead split)
+    bi = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
+    while ((bi + 1) * (bi + 2) / 2 <= t) bi++;
+    while (bi * (bi + 1) / 2 > t) bi--;
+    bj = t - bi * (bi + 1) / 2 + 1;
+    bi += 1;
+  } else {
+    bi = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
+    while ((bi + 1) * (bi + 2) / 2 <= t) bi++;
+    while (bi * (bi + 1) / 2 > t) bi--;
+    bj = t - bi * (bi + 1) / 2;
+  }
   const int r0 = J + kb;
   const int i0 = r0 + bi * TM, c0 = r0 + bj * TM;
   const int rows = min(TM, n + 1 - i0);
-  const int cols = min(TM, n - c0);
+  const int cols = min(min(TM, n - c0), strip > 0 ? strip : TM);
   if (cols <= 0 || rows <= 0) return;
   const int tid = threadIdx.x;
   const int ty = tid >> 4, tx = tid & 15;
@@ -494,28 +476,87 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
     attr2 = true;
   }
   const bool vec = (n % 2 == 0) && (((uintptr_t)A & 15) == 0);
+  // Look-ahead: while the bulk of trailing update J runs on the caller's stream, a second (high-priority) stream
+  // updates the next panel's 128 columns first and factorises them, so the serial panel chain hides behind the
+  // SYRK for as long as the SYRK is the longer of the two.
+  //   side : P(0) F(0) P(1) [wait R(0)] F(1) P(2) [wait R(1)] F(2) ...      P = panel, F = first block column
+  //   main :      [wait P(0)] R(0)   [wait P(1)] R(1) ...                    R = rest of the trailing update
+  static cudaStream_t side = nullptr;
+  static cudaEvent_t ev_fork = nullptr, ev_p = nullptr, ev_r = nullptr, ev_join = nullptr;
+  static int side_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (side_dev != dev) {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, hi);
+    cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ev_p, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ev_r, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming);
+    side_dev = dev;
+  }
+  auto lookahead_ok = [&](int J) {
+    const int r0 = J + PB;
+    if (!vec || r0 >= n) return false;
+    const int t128 = (n + 1 - r0 + 127) / 128;
+    return t128 * (t128 + 1) / 2 >= 2 * 148;
+  };
+  bool on_side = lookahead_ok(0);
+  if (on_side) {
+    cudaEventRecord(ev_fork, st);
+    cudaStreamWaitEvent(side, ev_fork, 0);
+  }
   for (int J = 0; J < n; J += PB) {
     const int kb = (n - J) < PB ? (n - J) : PB;
-    prof_mark(DROID_PROF_CHOL_PANEL, true, st);
+    if (on_side && !lookahead_ok(J)) {   // leave look-ahead mode: everything back on the caller's stream
+      cudaEventRecord(ev_join, side);
+      cudaStreamWaitEvent(st, ev_join, 0);
+      on_side = false;
+    }
+    cudaStream_t ps = on_side ? side : st;
+    prof_mark(DROID_PROF_CHOL_PANEL, true, ps);
     for (int j0 = J; j0 < J + kb; j0 += NB) {
       const int jb = (J + kb - j0) < NB ? (J + kb - j0) : NB;
       const int rem_rows = n + 1 - (j0 + jb);  // >= 1 (the rhs row)
-      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PR - 1) / PR, 256, kPanelSmem, st>>>(A, n, J, j0, jb, info_dev);
-    }
-    prof_mark(DROID_PROF_CHOL_PANEL, false, st);
-    const int r0 = J + kb;
-    if (r0 < n) {
-      ProfScope ps(DROID_PROF_CHOL_SYRK, st);
-      const int rr = n + 1 - r0;
-      const int t128 = (rr + 127) / 128, t64 = (rr + 63) / 64;
-      if (t128 * (t128 + 1) / 2 >= 148) {
-        if (vec) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb);
-        else DROID_LAUNCH chol_syrk_kernel<128, false><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb);
-      } else {
-        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb);
-        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb);
+      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PR - 1) / PR, 256, kPanelSmem, ps>>>(A, n, j0, jb, info_dev);
+      const int rest = J + kb - (j0 + jb);     // columns of this outer panel still to factorise
+      if (rest > 0) {
+        // rank-64 update of the panel's remaining columns only (64x64 tiles of one block column, all SMs)
+        const int t64 = (rem_rows + 63) / 64;
+        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest);
+        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest);
       }
     }
+    prof_mark(DROID_PROF_CHOL_PANEL, false, ps);
+    const int r0 = J + kb;
+    if (r0 >= n) break;
+    const int rr = n + 1 - r0;
+    const int t128 = (rr + 127) / 128, t64 = (rr + 63) / 64;
+    if (on_side) {
+      cudaEventRecord(ev_p, side);
+      cudaStreamWaitEvent(side, ev_r, 0);    // R(J-1) (no-op for the first panel)
+      DROID_LAUNCH chol_syrk_kernel<128, true><<<t128, 256, kSyrk128, side>>>(A, n, J, kb, 128);
+      cudaStreamWaitEvent(st, ev_p, 0);
+      {
+        ProfScope ps2(DROID_PROF_CHOL_SYRK, st);
+        DROID_LAUNCH chol_syrk_kernel<128, true><<<(t128 - 1) * t128 / 2, 256, kSyrk128, st>>>(A, n, J, kb, -1);
+      }
+      cudaEventRecord(ev_r, st);
+    } else {
+      ProfScope ps2(DROID_PROF_CHOL_SYRK, st);
+      if (t128 * (t128 + 1) / 2 >= 148) {
+        if (vec) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb, 0);
+        else DROID_LAUNCH chol_syrk_kernel<128, false><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb, 0);
+      } else {
+        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, 0);
+        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, 0);
+      }
+    }
+  }
+  if (on_side) {
+    cudaEventRecord(ev_join, side);
+    cudaStreamWaitEvent(st, ev_join, 0);
   }
   ProfScope psb(DROID_PROF_CHOL_BWD, st);
   for (int j0 = ((n - 1) / NB) * NB; j0 >= 0; j0 -= NB) {
