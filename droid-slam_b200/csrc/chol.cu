@@ -254,23 +254,6 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
     for (int b = 0; b < F * 4; b++) acc[a][b] = 0.0;
   double2 ra[LPT], rb[LPT];
   const int nch = (kb + KC - 1) / KC;
-  // The C tile is fetched into shared memory with cp.async while the DFMA loop runs: the epilogue's
-  // read-modify-write would otherwise expose 8 serial round trips to DRAM per tile (33 % of the stall
-  // samples in profiles/r1_chol_ncu_summary.txt).
-  double* Cs = sm + 2 * 2 * KC * LD;                 // [TM][TM]
-  if (VEC) {
-#pragma unroll 4
-    for (int q = 0; q < TM * TM / 2 / 256; q++) {
-      const int idx = tid + 256 * q;
-      const int r = idx / (TM / 2), c = 2 * (idx % (TM / 2));
-      if (r < rows && c < cols) {
-        const unsigned dst = (unsigned)__cvta_generic_to_shared(Cs + r * TM + c);
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(A + (size_t)(i0 + r) * n + c0 + c));
-      }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  }
-
   auto gload = [&](int ch) {
 #pragma unroll
     for (int q = 0; q < LPT; q++) {
@@ -305,6 +288,23 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
   };
 
   gload(0);
+  // The C tile is fetched into shared memory with cp.async while the DFMA loop runs: the epilogue's
+  // read-modify-write would otherwise expose 8 serial round trips to DRAM per tile (33 % of the stall
+  // samples in profiles/r1_chol_ncu_summary.txt).
+  double* Cs = sm + 2 * 2 * KC * LD;                 // [TM][TM]
+  if (VEC) {
+#pragma unroll 4
+    for (int q = 0; q < TM * TM / 2 / 256; q++) {
+      const int idx = tid + 256 * q;
+      const int r = idx / (TM / 2), c = 2 * (idx % (TM / 2));
+      if (r < rows && c < cols) {
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(Cs + r * TM + c);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(A + (size_t)(i0 + r) * n + c0 + c));
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+
   sstore(0);
   __syncthreads();
   for (int ch = 0; ch < nch; ch++) {
@@ -436,6 +436,109 @@ __global__ void __launch_bounds__(256) chol_bwd_kernel(double* __restrict__ A, i
   if (blockIdx.x == 0 && tid < jb) y[j0 + tid] = x[tid];
 }
 
+// ------------------------------------------------------------------------------------------------
+// backward sweep, two-level version (replaces 94 dependent launches by 2 per 512 rows):
+//   chol_bwd_diag_kernel : ONE CTA solves L_SS^T x_S = y_S for a super-block S of up to 512 rows, walking its
+//                          64-blocks from the last to the first with y_S in shared memory;
+//   chol_bwd_gemv_kernel : y[0:J0] -= L[S, 0:J0]^T x_S on all SMs.
+// ------------------------------------------------------------------------------------------------
+static constexpr int SB = 512;
+static constexpr int kBwdSmem = (NB * (NB + 1) + SB + NB + NB + 4 * (SB - NB)) * (int)sizeof(double);
+
+__global__ void __launch_bounds__(256) chol_bwd_diag_kernel(double* __restrict__ A, int n, int J0, int JB) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double (*D)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(smem_raw);
+  double* ys = &D[NB][0];
+  double* x = ys + SB;
+  double* rinv = x + NB;
+  double (*part)[SB - NB] = reinterpret_cast<double (*)[SB - NB]>(rinv + NB);
+  const int tid = threadIdx.x;
+  double* y = A + (size_t)n * n;
+  for (int i = tid; i < SB; i += 256) ys[i] = i < JB ? y[J0 + i] : 0.0;
+  const int nsb = (JB + NB - 1) / NB;
+  for (int sb = nsb - 1; sb >= 0; sb--) {
+    const int o = sb * NB;                       // offset of this 64-block inside the super-block
+    const int j0 = J0 + o;
+    const int jb = min(NB, JB - o);
+    __syncthreads();
+    {
+      double dv[16];
+#pragma unroll
+      for (int q = 0; q < 16; q++) {
+        const int r = q * 4 + (tid >> 6), c = tid & 63;
+        dv[q] = (c <= r && r < jb) ? A[(size_t)(j0 + r) * n + j0 + c] : 0.0;
+      }
+#pragma unroll
+      for (int q = 0; q < 16; q++) D[q * 4 + (tid >> 6)][tid & 63] = dv[q];
+    }
+    __syncthreads();
+    if (tid < NB) rinv[tid] = tid < jb ? 1.0 / D[tid][tid] : 0.0;
+    __syncthreads();
+    if (tid < 32) {
+      double x0 = ys[o + tid], x1 = (o + tid + 32 < SB) ? ys[o + tid + 32] : 0.0;
+#pragma unroll
+      for (int c = NB - 1; c >= 0; c--) {
+        const double src = (c >= 32) ? x1 : x0;
+        const double xc = __shfl_sync(0xffffffffu, src, c & 31) * rinv[c];
+        if (c >= 32) {
+          if (tid == (c & 31)) x1 = xc;
+          else if (tid < (c & 31)) x1 = fma(-D[c][tid + 32], xc, x1);
+          x0 = fma(-D[c][tid], xc, x0);
+        } else {
+          if (tid == c) x0 = xc;
+          else if (tid < c) x0 = fma(-D[c][tid], xc, x0);
+        }
+      }
+      x[tid] = x0; x[tid + 32] = x1;
+      ys[o + tid] = x0;
+      if (tid + 32 < jb) ys[o + tid + 32] = x1;
+    }
+    __syncthreads();
+    // update the part of y_S above this block: columns J0 .. j0-1 (o of them), 4 row groups of 16
+    const int g = tid >> 6, cl = tid & 63;
+    for (int cb = 0; cb < o; cb += NB) {
+      double sum = 0.0;
+#pragma unroll
+      for (int r = 0; r < 16; r++) {
+        const int rr = g * 16 + r;
+        if (rr < jb) sum = fma(A[(size_t)(j0 + rr) * n + J0 + cb + cl], x[rr], sum);
+      }
+      part[g][cb + cl] = sum;
+    }
+    __syncthreads();
+    for (int i = tid; i < o; i += 256) ys[i] -= part[0][i] + part[1][i] + part[2][i] + part[3][i];
+  }
+  __syncthreads();
+  for (int i = tid; i < JB; i += 256) y[J0 + i] = ys[i];
+}
+
+__global__ void __launch_bounds__(256) chol_bwd_gemv_kernel(double* __restrict__ A, int n, int J0, int JB) {
+  __shared__ double xs[SB];
+  __shared__ double part[4][NB];
+  const int tid = threadIdx.x;
+  double* y = A + (size_t)n * n;
+  for (int i = tid; i < SB; i += 256) xs[i] = i < JB ? y[J0 + i] : 0.0;
+  __syncthreads();
+  const int i = blockIdx.x * NB + (tid & 63), g = tid >> 6;
+  double s0 = 0.0, s1 = 0.0;
+  if (i < J0) {
+    // row group g handles rows g, g+4, g+8, ... of the super-block (two independent chains)
+    int r = g;
+#pragma unroll 4
+    for (; r + 4 < JB; r += 8) {
+      s0 = fma(A[(size_t)(J0 + r) * n + i], xs[r], s0);
+      s1 = fma(A[(size_t)(J0 + r + 4) * n + i], xs[r + 4], s1);
+    }
+    if (r < JB) s0 = fma(A[(size_t)(J0 + r) * n + i], xs[r], s0);
+  }
+  part[g][tid & 63] = s0 + s1;
+  __syncthreads();
+  if (tid < NB) {
+    const int ii = blockIdx.x * NB + tid;
+    if (ii < J0) y[ii] -= part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
+  }
+}
+
 }  // namespace droid
 
 using namespace droid;
@@ -469,6 +572,7 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
   constexpr int kSyrk64 = (2 * 2 * 16 * (64 + 2) + 64 * 64) * (int)sizeof(double);
   if (!attr2) {
     cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmem);
+    cudaFuncSetAttribute(chol_bwd_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem);
     cudaFuncSetAttribute(chol_syrk_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
     cudaFuncSetAttribute(chol_syrk_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
     cudaFuncSetAttribute(chol_syrk_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk64);
@@ -559,10 +663,10 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
     cudaStreamWaitEvent(st, ev_join, 0);
   }
   ProfScope psb(DROID_PROF_CHOL_BWD, st);
-  for (int j0 = ((n - 1) / NB) * NB; j0 >= 0; j0 -= NB) {
-    const int jb = (n - j0) < NB ? (n - j0) : NB;
-    const int g = j0 > 0 ? (j0 + NB - 1) / NB : 1;
-    DROID_LAUNCH chol_bwd_kernel<<<g, 256, 0, st>>>(A, n, j0, jb);
+  for (int J0 = ((n - 1) / SB) * SB; J0 >= 0; J0 -= SB) {
+    const int JB = (n - J0) < SB ? (n - J0) : SB;
+    DROID_LAUNCH chol_bwd_diag_kernel<<<1, 256, kBwdSmem, st>>>(A, n, J0, JB);
+    if (J0 > 0) DROID_LAUNCH chol_bwd_gemv_kernel<<<(J0 + NB - 1) / NB, 256, 0, st>>>(A, n, J0, JB);
   }
   return check_launch();
 }
