@@ -442,71 +442,80 @@ __global__ void __launch_bounds__(256) chol_bwd_kernel(double* __restrict__ A, i
 //                          64-blocks from the last to the first with y_S in shared memory;
 //   chol_bwd_gemv_kernel : y[0:J0] -= L[S, 0:J0]^T x_S on all SMs.
 // ------------------------------------------------------------------------------------------------
-static constexpr int SB = 512;
-static constexpr int kBwdSmem = (NB * (NB + 1) + SB + NB + NB + 4 * (SB - NB)) * (int)sizeof(double);
+static constexpr int SB = 192;                                   // super-block rows (3 blocks of 64)
+static constexpr int kBwdBlocks = (SB / NB) * (SB / NB + 1) / 2;  // lower-triangular 64x64 blocks: 6
+static constexpr int kBwdSmem = (kBwdBlocks * NB * NB + SB + NB + NB + 4 * NB) * (int)sizeof(double);
 
-__global__ void __launch_bounds__(256) chol_bwd_diag_kernel(double* __restrict__ A, int n, int J0, int JB) {
+__global__ void __launch_bounds__(256) chol_bwd_diag_kernel(double* __restrict__ A, int n, int J0, int JB, int vec) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double (*D)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(smem_raw);
-  double* ys = &D[NB][0];
-  double* x = ys + SB;
-  double* rinv = x + NB;
-  double (*part)[SB - NB] = reinterpret_cast<double (*)[SB - NB]>(rinv + NB);
+  double* Lb = reinterpret_cast<double*>(smem_raw);     // [6][64][64]: block (bi,bj) at bi(bi+1)/2 + bj
+  double* ys = Lb + kBwdBlocks * NB * NB;               // [SB]
+  double* x = ys + SB;                                  // [64]
+  double* rinv = x + NB;                                // [64]
+  double* part = rinv + NB;                             // [4][64]
   const int tid = threadIdx.x;
   double* y = A + (size_t)n * n;
+  // The whole lower triangle of the super-block (<= 192 KB) comes in with cp.async, every request in flight at
+  // once: the serial walk below then never waits on DRAM (the per-64-block version paid a round trip per block).
+  for (int e = tid; e < kBwdBlocks * NB * (NB / 2); e += 256) {
+    const int blk = e / (NB * NB / 2), w = e % (NB * NB / 2);
+    const int r = w / (NB / 2), c = 2 * (w % (NB / 2));
+    const int bi = blk >= 3 ? 2 : (blk >= 1 ? 1 : 0), bj = blk - bi * (bi + 1) / 2;
+    const int gr = bi * NB + r, gc = bj * NB + c;
+    double* dst = Lb + (size_t)blk * NB * NB + r * NB + c;
+    if (gr < JB && gc < JB) {
+      const double* src = A + (size_t)(J0 + gr) * n + J0 + gc;
+      if (vec) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src));
+      } else {
+        dst[0] = src[0];
+        dst[1] = (gc + 1 < JB) ? src[1] : 0.0;
+      }
+    } else {
+      dst[0] = 0.0; dst[1] = 0.0;
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
   for (int i = tid; i < SB; i += 256) ys[i] = i < JB ? y[J0 + i] : 0.0;
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   const int nsb = (JB + NB - 1) / NB;
   for (int sb = nsb - 1; sb >= 0; sb--) {
-    const int o = sb * NB;                       // offset of this 64-block inside the super-block
-    const int j0 = J0 + o;
+    const int o = sb * NB;
     const int jb = min(NB, JB - o);
+    const double* D = Lb + (size_t)(sb * (sb + 1) / 2 + sb) * NB * NB;
     __syncthreads();
-    {
-      double dv[16];
-#pragma unroll
-      for (int q = 0; q < 16; q++) {
-        const int r = q * 4 + (tid >> 6), c = tid & 63;
-        dv[q] = (c <= r && r < jb) ? A[(size_t)(j0 + r) * n + j0 + c] : 0.0;
-      }
-#pragma unroll
-      for (int q = 0; q < 16; q++) D[q * 4 + (tid >> 6)][tid & 63] = dv[q];
-    }
-    __syncthreads();
-    if (tid < NB) rinv[tid] = tid < jb ? 1.0 / D[tid][tid] : 0.0;
+    if (tid < NB) rinv[tid] = tid < jb ? 1.0 / D[tid * NB + tid] : 0.0;
     __syncthreads();
     if (tid < 32) {
-      double x0 = ys[o + tid], x1 = (o + tid + 32 < SB) ? ys[o + tid + 32] : 0.0;
+      double x0 = ys[o + tid], x1 = ys[o + tid + 32];
 #pragma unroll
       for (int c = NB - 1; c >= 0; c--) {
         const double src = (c >= 32) ? x1 : x0;
         const double xc = __shfl_sync(0xffffffffu, src, c & 31) * rinv[c];
         if (c >= 32) {
           if (tid == (c & 31)) x1 = xc;
-          else if (tid < (c & 31)) x1 = fma(-D[c][tid + 32], xc, x1);
-          x0 = fma(-D[c][tid], xc, x0);
+          else if (tid < (c & 31)) x1 = fma(-D[c * NB + tid + 32], xc, x1);
+          x0 = fma(-D[c * NB + tid], xc, x0);
         } else {
           if (tid == c) x0 = xc;
-          else if (tid < c) x0 = fma(-D[c][tid], xc, x0);
+          else if (tid < c) x0 = fma(-D[c * NB + tid], xc, x0);
         }
       }
       x[tid] = x0; x[tid + 32] = x1;
-      ys[o + tid] = x0;
-      if (tid + 32 < jb) ys[o + tid + 32] = x1;
+      ys[o + tid] = x0; ys[o + tid + 32] = x1;
     }
     __syncthreads();
-    // update the part of y_S above this block: columns J0 .. j0-1 (o of them), 4 row groups of 16
     const int g = tid >> 6, cl = tid & 63;
-    for (int cb = 0; cb < o; cb += NB) {
+    for (int t = 0; t < sb; t++) {              // y_t -= L(sb,t)^T x_sb
+      const double* Ls = Lb + (size_t)(sb * (sb + 1) / 2 + t) * NB * NB;
       double sum = 0.0;
 #pragma unroll
-      for (int r = 0; r < 16; r++) {
-        const int rr = g * 16 + r;
-        if (rr < jb) sum = fma(A[(size_t)(j0 + rr) * n + J0 + cb + cl], x[rr], sum);
-      }
-      part[g][cb + cl] = sum;
+      for (int r = 0; r < 16; r++) sum = fma(Ls[(g * 16 + r) * NB + cl], x[g * 16 + r], sum);
+      part[g * NB + cl] = sum;
+      __syncthreads();
+      if (tid < NB) ys[t * NB + tid] -= part[tid] + part[NB + tid] + part[2 * NB + tid] + part[3 * NB + tid];
+      __syncthreads();
     }
-    __syncthreads();
-    for (int i = tid; i < o; i += 256) ys[i] -= part[0][i] + part[1][i] + part[2][i] + part[3][i];
   }
   __syncthreads();
   for (int i = tid; i < JB; i += 256) y[J0 + i] = ys[i];
@@ -665,7 +674,7 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
   ProfScope psb(DROID_PROF_CHOL_BWD, st);
   for (int J0 = ((n - 1) / SB) * SB; J0 >= 0; J0 -= SB) {
     const int JB = (n - J0) < SB ? (n - J0) : SB;
-    DROID_LAUNCH chol_bwd_diag_kernel<<<1, 256, kBwdSmem, st>>>(A, n, J0, JB);
+    DROID_LAUNCH chol_bwd_diag_kernel<<<1, 256, kBwdSmem, st>>>(A, n, J0, JB, vec ? 1 : 0);
     if (J0 > 0) DROID_LAUNCH chol_bwd_gemv_kernel<<<(J0 + NB - 1) / NB, 256, 0, st>>>(A, n, J0, JB);
   }
   return check_launch();

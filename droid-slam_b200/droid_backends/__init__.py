@@ -421,9 +421,7 @@ def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, 
     import torch.distributed as dist
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
-    nbuf = disps.shape[0]
-    per = (nbuf + world - 1) // world
-    lo, hi = rank * per, min(nbuf, (rank + 1) * per)
+    lo, hi, per = shard_range(disps.shape[0], world, rank)
 
     def _reduce(user, buf, n, stream):
         t = _as_tensor(buf, n, poses.device)
@@ -433,11 +431,24 @@ def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, 
     out = ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations,
              lm, ep, motion_only, _shard=(lo, hi), _reduce=_reduce)
     if not motion_only and world > 1:
-        pad = per * world
-        flat = disps.new_zeros((pad,) + tuple(disps.shape[1:]))
-        dist.all_gather_into_tensor(flat, _pad_rows(disps[lo:hi], per), group=group)
-        disps.copy_(flat[:nbuf])
+        gather_depth_shards(disps, lo, hi, per, world, group)
     return out
+
+
+def shard_range(nbuf, world, rank):
+    """Contiguous source-frame shard [lo, hi) of rank `rank` and the (padded) shard length."""
+    per = (nbuf + world - 1) // world
+    return min(nbuf, rank * per), min(nbuf, (rank + 1) * per), per
+
+
+def gather_depth_shards(disps, lo, hi, per, world, group=None):
+    """Every rank updated only disps[lo:hi]; all-gather the shards so that all ranks hold the full buffer."""
+    import torch.distributed as dist
+    nbuf = disps.shape[0]
+    flat = disps.new_zeros((per * world,) + tuple(disps.shape[1:]))
+    dist.all_gather_into_tensor(flat, _pad_rows(disps[lo:hi], per), group=group)
+    disps.copy_(flat[:nbuf])
+    return disps
 
 
 def _pad_rows(t, rows):

@@ -1,0 +1,71 @@
+"""N > 1 host logic on CPU: world_size-2 gloo runs of the pieces of droid_backends.ba_sharded that do not need a
+GPU -- the source-frame partition, the all-reduce of the packed fp64 reduced camera system and the all-gather of the
+per-rank depth shards.  The CUDA part of ba_sharded is covered by `bench.py --gpus 2` on the GPU box."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, nbuf, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import droid_backends as B
+    lo, hi, per = B.shard_range(nbuf, world, rank)
+    # (1) partial systems: rank r contributes only the source frames of its shard; the sum must equal the whole
+    rng = np.random.default_rng(7)
+    n6 = 30
+    per_frame = rng.normal(size=(nbuf, n6 * n6 + n6))              # what frame k adds to (H - S | v)
+    part = torch.from_numpy(per_frame[lo:hi].sum(0))
+    dist.all_reduce(part)
+    ok_sum = np.allclose(part.numpy(), per_frame.sum(0), rtol=1e-12, atol=1e-12)
+    # (2) every rank updates only its own depth maps, then the shards are all-gathered
+    disps = torch.zeros(nbuf, 4, 6)
+    full = torch.arange(nbuf * 24, dtype=torch.float32).view(nbuf, 4, 6)
+    disps[lo:hi] = full[lo:hi]
+    B.gather_depth_shards(disps, lo, hi, per, world)
+    ok_gather = torch.equal(disps, full)
+    q.put((rank, lo, hi, per, bool(ok_sum), bool(ok_gather)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("nbuf", [9, 16])
+def test_sharded_host_logic_world2(lib_built, nbuf):
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, nbuf, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    covered = []
+    for rank, lo, hi, per, ok_sum, ok_gather in res:
+        assert ok_sum and ok_gather
+        covered += list(range(lo, hi))
+    assert covered == list(range(nbuf))                            # disjoint, contiguous, complete
+
+
+def test_shard_range_properties(backends):
+    for nbuf in (1, 7, 512, 1000, 1024):
+        for world in (1, 2, 4, 8):
+            seen = []
+            for r in range(world):
+                lo, hi, per = backends.shard_range(nbuf, world, r)
+                assert 0 <= lo <= hi <= nbuf and hi - lo <= per
+                seen += list(range(lo, hi))
+            assert seen == list(range(nbuf))
