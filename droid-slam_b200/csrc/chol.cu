@@ -226,14 +226,16 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
   double* sm = reinterpret_cast<double*>(smem_raw);  // [2 buffers][2 operands][KC][LD]
   const int t = blockIdx.x;
   int bi, bj;
-  if (strip > 0) {   // only the first block column (`strip` columns wide)
-    bi = t; bj = 0;
-  } else if (strip < 0) {   // everything except the first block column (look-ahead split)
+  if (strip > 0) {   // only the first `strip` columns (ceil(strip/TM) block columns)
+    const int nbj = (strip + TM - 1) / TM;
+    bi = t / nbj; bj = t - bi * nbj;
+    if (bj > bi) return;
+  } else if (strip < 0) {   // everything except the first -strip block columns (look-ahead split)
     bi = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
     while ((bi + 1) * (bi + 2) / 2 <= t) bi++;
     while (bi * (bi + 1) / 2 > t) bi--;
-    bj = t - bi * (bi + 1) / 2 + 1;
-    bi += 1;
+    bj = t - bi * (bi + 1) / 2 - strip;
+    bi -= strip;
   } else {
     bi = (int)((sqrtf(8.f * t + 1.f) - 1.f) * 0.5f);
     while ((bi + 1) * (bi + 2) / 2 <= t) bi++;
@@ -243,7 +245,7 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
   const int r0 = J + kb;
   const int i0 = r0 + bi * TM, c0 = r0 + bj * TM;
   const int rows = min(TM, n + 1 - i0);
-  const int cols = min(min(TM, n - c0), strip > 0 ? strip : TM);
+  const int cols = min(min(TM, n - c0), strip > 0 ? strip - bj * TM : TM);
   if (cols <= 0 || rows <= 0) return;
   const int tid = threadIdx.x;
   const int ty = tid >> 4, tx = tid & 15;
@@ -612,8 +614,7 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
   auto lookahead_ok = [&](int J) {
     const int r0 = J + PB;
     if (!vec || r0 >= n) return false;
-    const int t128 = (n + 1 - r0 + 127) / 128;
-    return t128 * (t128 + 1) / 2 >= 2 * 148;
+    return n + 1 - r0 >= 4 * PB;   // at least a few tiles of trailing matrix left to overlap with
   };
   bool on_side = lookahead_ok(0);
   if (on_side) {
@@ -647,13 +648,16 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
     const int rr = n + 1 - r0;
     const int t128 = (rr + 127) / 128, t64 = (rr + 63) / 64;
     if (on_side) {
+      const bool big = t128 * (t128 + 1) / 2 >= 148;
       cudaEventRecord(ev_p, side);
       cudaStreamWaitEvent(side, ev_r, 0);    // R(J-1) (no-op for the first panel)
-      DROID_LAUNCH chol_syrk_kernel<128, true><<<t128, 256, kSyrk128, side>>>(A, n, J, kb, 128);
+      if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128, 256, kSyrk128, side>>>(A, n, J, kb, PB);
+      else DROID_LAUNCH chol_syrk_kernel<64, true><<<2 * t64, 256, kSyrk64, side>>>(A, n, J, kb, PB);
       cudaStreamWaitEvent(st, ev_p, 0);
       {
         ProfScope ps2(DROID_PROF_CHOL_SYRK, st);
-        DROID_LAUNCH chol_syrk_kernel<128, true><<<(t128 - 1) * t128 / 2, 256, kSyrk128, st>>>(A, n, J, kb, -1);
+        if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<(t128 - 1) * t128 / 2, 256, kSyrk128, st>>>(A, n, J, kb, -1);
+        else DROID_LAUNCH chol_syrk_kernel<64, true><<<(t64 - 2) * (t64 - 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, -2);
       }
       cudaEventRecord(ev_r, st);
     } else {
