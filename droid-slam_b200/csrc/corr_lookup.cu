@@ -160,6 +160,41 @@ __device__ __forceinline__ void lookup_tile_r3(const T* __restrict__ vol,
 #pragma unroll
     for (int k = 0; k < 8; k++) m |= ((xs + k >= 0 && xs + k < W2) ? 1u : 0u) << k;
   }
+  if constexpr (sizeof(T) == 2) {
+    // f16: native packed arithmetic.  HMUL2 rounds the (exact) product once and HADD2 the (exact)
+    // sum once, which is bit-identical to c10::Half's float-op-then-round; out-of-plane taps were loaded as
+    // zeros and adding +0 leaves the partial sum unchanged, so no per-tap predicates are needed.
+    (void)m;
+    const __half2 E0 = __halves2half2(t[0], t[1]), E1 = __halves2half2(t[2], t[3]);
+    const __half2 E2 = __halves2half2(t[4], t[5]), E3 = __halves2half2(t[6], t[7]);
+    const unsigned e0 = *reinterpret_cast<const unsigned*>(&E0), e1 = *reinterpret_cast<const unsigned*>(&E1);
+    const unsigned e2 = *reinterpret_cast<const unsigned*>(&E2), e3 = *reinterpret_cast<const unsigned*>(&E3);
+    const unsigned f0 = __shfl_down_sync(0xffffffffu, e0, 1), f1 = __shfl_down_sync(0xffffffffu, e1, 1);
+    const unsigned f2 = __shfl_down_sync(0xffffffffu, e2, 1), f3 = __shfl_down_sync(0xffffffffu, e3, 1);
+    auto H2 = [](unsigned u) { return *reinterpret_cast<const __half2*>(&u); };
+    // odd-aligned pairs (t[2p+1], t[2p+2])
+    const unsigned o0 = __byte_perm(e0, e1, 0x5432), o1 = __byte_perm(e1, e2, 0x5432);
+    const unsigned o2 = __byte_perm(e2, e3, 0x5432), o3 = __byte_perm(e3, 0u, 0x5432);
+    const unsigned g0 = __byte_perm(f0, f1, 0x5432), g1 = __byte_perm(f1, f2, 0x5432);
+    const unsigned g2 = __byte_perm(f2, f3, 0x5432), g3 = __byte_perm(f3, 0u, 0x5432);
+    const __half2 W00 = __float2half2_rn((1.0f - dx) * (1.0f - dy)), W01 = __float2half2_rn((1.0f - dx) * dy);
+    const __half2 W10 = __float2half2_rn(dx * (1.0f - dy)), W11 = __float2half2_rn(dx * dy);
+    auto quad = [&](unsigned ea, unsigned fa, unsigned oa, unsigned ga) {
+      __half2 acc = __hmul2_rn(H2(ea), W00);
+      acc = __hadd2_rn(acc, __hmul2_rn(H2(fa), W01));
+      acc = __hadd2_rn(acc, __hmul2_rn(H2(oa), W10));
+      acc = __hadd2_rn(acc, __hmul2_rn(H2(ga), W11));
+      return acc;
+    };
+    if (row < 7) {
+      const __half2 r0 = quad(e0, f0, o0, g0), r1 = quad(e1, f1, o1, g1);
+      const __half2 r2 = quad(e2, f2, o2, g2), r3 = quad(e3, f3, o3, g3);
+      stage[0 * 7 + row][p] = __low2half(r0); stage[1 * 7 + row][p] = __high2half(r0);
+      stage[2 * 7 + row][p] = __low2half(r1); stage[3 * 7 + row][p] = __high2half(r1);
+      stage[4 * 7 + row][p] = __low2half(r2); stage[5 * 7 + row][p] = __high2half(r2);
+      stage[6 * 7 + row][p] = __low2half(r3);
+    }
+  } else {
   T t2[8];
 #pragma unroll
   for (int k = 0; k < 8; k++) t2[k] = shfl_down1<T>(t[k]);
@@ -178,6 +213,7 @@ __device__ __forceinline__ void lookup_tile_r3(const T* __restrict__ vol,
       if (m2 & (2u << a)) acc = Arith<T>::mad(acc, t2[a + 1], w11);
       stage[a * 7 + row][p] = acc;
     }
+  }
   }
   __syncthreads();
   const int lane = tid & 31, warp = tid >> 5;
