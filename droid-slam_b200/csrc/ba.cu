@@ -37,6 +37,9 @@ struct BaWs {
   float* Q;        // [n_eta][HW]
   float* W;        // [n_eta][HW]
   float* dx;       // [P][6]
+  int* ppos;       // [P]   free pose -> position in the reduced system (fill-reducing order)
+  int* first;      // [6P]  row envelope of the reduced system (first non-zero column per row)
+  int* oscr;       // [5P + 2 nbuf] scratch of ba_order_kernel
   double* A;       // [6P*6P + 6P]  dense system, b appended
   void* chol;      // workspace of the factorisation
   size_t total;
@@ -65,6 +68,9 @@ static BaWs carve(void* base, const droid_ba_params* p, size_t chol_bytes) {
   w.Q = (float*)take((size_t)(p->n_eta > 0 ? p->n_eta : 1) * HW * sizeof(float));
   w.W = (float*)take((size_t)(p->n_eta > 0 ? p->n_eta : 1) * HW * sizeof(float));
   w.dx = (float*)take((n6 > 0 ? n6 : 1) * sizeof(float));
+  w.ppos = (int*)take((n6 > 0 ? n6 : 1) * sizeof(int));
+  w.first = (int*)take((n6 > 0 ? n6 : 1) * sizeof(int));
+  w.oscr = (int*)take((5 * (n6 / 6) + 2 * (size_t)p->nbuf + 8) * sizeof(int));
   w.A = (double*)take((n6 * n6 + n6 + 1) * sizeof(double));
   w.chol = take(chol_bytes);
   w.total = off;
@@ -169,6 +175,145 @@ __global__ void __launch_bounds__(1024) ba_prep_kernel(const int64_t* __restrict
     status[1] = M;
     status[2] = 0;
   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fill-reducing order of the reduced camera system (large systems only).  The reference hands the system to
+// Eigen::SimplicialLLT, which orders and factorises it as a SPARSE matrix (:1192-1201); here the system stays dense
+// in memory but is laid out so that its non-zeros form a narrow band, and chol.cu skips everything outside the
+// row envelopes.  Two poses are coupled in H - E Q E^T iff they occur in the same "star" (a source frame i together
+// with all targets j of its edges), so:
+//   * order  = breadth-first levels of that star graph from the first free pose (level sets of a BFS give a band of
+//     about two level widths), ascending pose index inside a level - deterministic, identical on every rank;
+//   * env[q] = smallest position among all stars containing the pose at position q.
+// The natural order is kept when BFS does not shrink sum (q - env[q])^2 by at least 30 %.
+// One CTA; runs once per ba() call.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int block_scan_excl_1024(int v, int* s_warp, int* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) s_warp[warp] = x;
+  __syncthreads();
+  if (warp == 0) {
+    int w = s_warp[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += y;
+    }
+    s_warp[lane] = w;
+  }
+  __syncthreads();
+  const int base = warp > 0 ? s_warp[warp - 1] : 0;
+  *total = s_warp[31];
+  __syncthreads();
+  return base + x - v;
+}
+
+__global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restrict__ ii,
+                                                        const int64_t* __restrict__ jj, int n_edges, int nbuf,
+                                                        int t0, int P, const int* __restrict__ kmap,
+                                                        int* __restrict__ ppos, int* __restrict__ first,
+                                                        int* __restrict__ scr) {
+  int* pos = scr;              // [P] BFS position of free pose f, -1 = not placed yet
+  int* cur = pos + P;          // [P] current frontier flags
+  int* cand = cur + P;         // [P] next frontier flags; later the envelope of the BFS order
+  int* env = cand + P;         // [P] envelope of the natural order
+  int* starhit = env + P;      // [nbuf]
+  int* starmin = starhit + nbuf;  // [nbuf]
+  __shared__ int s_warp[32];
+  __shared__ int s_seed, s_placed;
+  __shared__ unsigned long long s_prof[2];
+  const int tid = threadIdx.x;
+  auto valid = [&](long long i, long long j) { return i >= 0 && i < nbuf && j >= 0 && j < nbuf; };
+  for (int f = tid; f < P; f += 1024) { pos[f] = -1; cur[f] = 0; cand[f] = 0; }
+  for (int m = tid; m < nbuf; m += 1024) starhit[m] = 0;
+  if (tid == 0) s_placed = 0;
+  __syncthreads();
+  while (true) {
+    if (tid == 0) s_seed = 0x7fffffff;
+    __syncthreads();
+    int best = 0x7fffffff;
+    for (int f = tid; f < P; f += 1024)
+      if (pos[f] < 0) { best = f; break; }
+    if (best != 0x7fffffff) atomicMin(&s_seed, best);
+    __syncthreads();
+    const int seed = s_seed;
+    if (seed == 0x7fffffff) break;
+    if (tid == 0) { pos[seed] = s_placed; cur[seed] = 1; s_placed = s_placed + 1; }
+    __syncthreads();
+    while (true) {
+      for (int e = tid; e < n_edges; e += 1024) {
+        const long long i = ii[e], j = jj[e];
+        if (!valid(i, j)) continue;
+        const int a = (int)i - t0, b = (int)j - t0;
+        if ((a >= 0 && a < P && cur[a]) || (b >= 0 && b < P && cur[b])) starhit[kmap[i]] = 1;
+      }
+      __syncthreads();
+      for (int e = tid; e < n_edges; e += 1024) {
+        const long long i = ii[e], j = jj[e];
+        if (!valid(i, j) || !starhit[kmap[i]]) continue;
+        const int a = (int)i - t0, b = (int)j - t0;
+        if (a >= 0 && a < P && pos[a] < 0) cand[a] = 1;
+        if (b >= 0 && b < P && pos[b] < 0) cand[b] = 1;
+      }
+      __syncthreads();
+      for (int m = tid; m < nbuf; m += 1024) starhit[m] = 0;
+      for (int f = tid; f < P; f += 1024) cur[f] = 0;
+      __syncthreads();
+      const int base = s_placed;
+      int placed = 0;
+      for (int c0 = 0; c0 < P; c0 += 1024) {
+        const int f = c0 + tid;
+        const int flag = (f < P && cand[f]) ? 1 : 0;
+        int total;
+        const int ex = block_scan_excl_1024(flag, s_warp, &total);
+        if (flag) { pos[f] = base + placed + ex; cur[f] = 1; cand[f] = 0; }
+        placed += total;
+      }
+      __syncthreads();
+      if (tid == 0) s_placed = base + placed;
+      __syncthreads();
+      if (placed == 0) break;
+    }
+  }
+  // envelopes + profiles of both orders
+  for (int pass = 0; pass < 2; pass++) {
+    int* en = pass == 0 ? env : cand;
+    for (int m = tid; m < nbuf; m += 1024) starmin[m] = 0x7fffffff;
+    for (int q = tid; q < P; q += 1024) en[q] = q;
+    if (tid == 0) s_prof[pass] = 0ull;
+    __syncthreads();
+    for (int e = tid; e < n_edges; e += 1024) {
+      const long long i = ii[e], j = jj[e];
+      if (!valid(i, j)) continue;
+      const int a = (int)i - t0, b = (int)j - t0, m = kmap[i];
+      if (a >= 0 && a < P) atomicMin(&starmin[m], pass == 0 ? a : pos[a]);
+      if (b >= 0 && b < P) atomicMin(&starmin[m], pass == 0 ? b : pos[b]);
+    }
+    __syncthreads();
+    for (int e = tid; e < n_edges; e += 1024) {
+      const long long i = ii[e], j = jj[e];
+      if (!valid(i, j)) continue;
+      const int a = (int)i - t0, b = (int)j - t0, sm = starmin[kmap[i]];
+      if (a >= 0 && a < P) atomicMin(&en[pass == 0 ? a : pos[a]], sm);
+      if (b >= 0 && b < P) atomicMin(&en[pass == 0 ? b : pos[b]], sm);
+    }
+    __syncthreads();
+    unsigned long long acc = 0ull;
+    for (int q = tid; q < P; q += 1024) { const unsigned long long w = (unsigned long long)(q - en[q]); acc += w * w; }
+    atomicAdd(&s_prof[pass], acc);
+    __syncthreads();
+  }
+  const bool use_bfs = s_prof[1] * 10ull < s_prof[0] * 7ull;
+  const int* en = use_bfs ? cand : env;
+  for (int f = tid; f < P; f += 1024) ppos[f] = use_bfs ? pos[f] : f;
+  for (int r = tid; r < 6 * P; r += 1024) first[r] = 6 * en[r / 6];
 }
 
 __global__ void ba_edge_pose_kernel(const float* __restrict__ poses, const int64_t* __restrict__ ii,
@@ -314,7 +459,7 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
     const int* __restrict__ status, const int* __restrict__ kx, const int* __restrict__ eptr,
     const int* __restrict__ eidx, float* __restrict__ Qo, float* __restrict__ Wo,
     double* __restrict__ A, double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P,
-    int n_eta, int motion_only, int frame_lo, int frame_hi) {
+    int n_eta, int motion_only, int frame_lo, int frame_hi, const int* __restrict__ ppos) {
   __shared__ float Cs[kSlabMax];
   __shared__ float Bs[kSlabMax];
   __shared__ float Ds[kSlabMax];   // inverse depths of the slab (re-read for every edge of the frame)
@@ -427,6 +572,10 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
           int pi = k - t0, pj = jx - t0;
           if (pi < 0 || pi >= P) pi = -1;
           if (pj < 0 || pj >= P) pj = -1;
+          if (ppos != nullptr) {   // position in the (re-ordered) reduced system
+            if (pi >= 0) pi = ppos[pi];
+            if (pj >= 0) pj = ppos[pj];
+          }
           scatter_edge_value(A, bvec, n6, tid, sum, pi, pj);
         }
         __syncthreads();
@@ -509,7 +658,7 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
     const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
     const float* __restrict__ Qi, const float* __restrict__ Wi, double* __restrict__ A,
     double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P, int n_eta, int frame_lo,
-    int frame_hi) {
+    int frame_hi, const int* __restrict__ ppos) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int m = blockIdx.y;
   const int M = status[1];
@@ -555,6 +704,7 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
     if (d < D) {
       pz = (d == 0) ? k - t0 : (int)jj[eidx[e0 + d - 1]] - t0;
       if (pz < 0 || pz >= P) pz = -1;
+      else if (ppos != nullptr) pz = ppos[pz];
     }
     pose[d] = pz;
   }
@@ -777,7 +927,7 @@ __global__ void ba_damp_kernel(double* __restrict__ A, int n6, float lm, float e
 __global__ void ba_pose_update_kernel(float* __restrict__ poses, const double* __restrict__ x,
                                       int* __restrict__ status, const int* __restrict__ info,
                                       float* __restrict__ dx, float* __restrict__ dx_out, int t0,
-                                      int P, int apply) {
+                                      int P, int apply, const int* __restrict__ ppos) {
   const int kk = blockIdx.x * blockDim.x + threadIdx.x;
   if (kk >= P) return;
   const bool failed = (*info != 0);
@@ -785,7 +935,7 @@ __global__ void ba_pose_update_kernel(float* __restrict__ poses, const double* _
   float xi[6];
 #pragma unroll
   for (int n = 0; n < 6; n++) {
-    xi[n] = failed ? 0.f : (float)x[6 * kk + n];
+    xi[n] = failed ? 0.f : (float)x[6 * (ppos != nullptr ? ppos[kk] : kk) + n];
     dx[6 * kk + n] = xi[n];
     dx_out[6 * kk + n] = xi[n];
   }
@@ -859,6 +1009,13 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
                                      w.kmap, w.kx, w.eptr, w.eidx, w.fill);
   if (check_launch()) return DROID_ERR_CUDA;
   if (P == 0 || p->iterations == 0) return DROID_OK;
+  // large systems: fill-reducing order + row envelope for the factorisation (small ones are solved by one CTA)
+  const bool ordered = n6 > kCholSmallMax && p->n_edges > 0;
+  const int* ppos = ordered ? w.ppos : nullptr;
+  const int* first = ordered ? w.first : nullptr;
+  if (ordered)
+    DROID_LAUNCH ba_order_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->t0, P, w.kmap, w.ppos, w.first,
+                                                     w.oscr);
 
   static bool attr_set = false;
   if (!attr_set) {
@@ -893,13 +1050,13 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
         DROID_LAUNCH ba_accum_kernel<<<dim3(S, p->n_eta), kThreads, 0, st>>>(
             disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, w.gij, w.status, w.kx,
             w.eptr, w.eidx, w.Q, w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, p->motion_only,
-            frame_lo, frame_hi);
+            frame_lo, frame_hi, ppos);
       }
       if (!p->motion_only) {
         ProfScope ps(DROID_PROF_BA_SCHUR, st);
         DROID_LAUNCH ba_schur_kernel<<<dim3(S, p->n_eta), kThreads, kSchurSmemBytes, st>>>(
             disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q,
-            w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi);
+            w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos);
       }
     }
     if (check_launch()) return DROID_ERR_CUDA;
@@ -911,16 +1068,16 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     {
       ProfScope ps(DROID_PROF_BA_SOLVE, st);
       DROID_LAUNCH ba_damp_kernel<<<(n6 + 127) / 128, 128, 0, st>>>(w.A, n6, p->lm, p->ep);
-      int rc = droid_chol_solve_f64(w.A, bvec, n6, w.status + 2, w.chol, chol_bytes, stream);
+      int rc = droid_chol_solve_env_f64(w.A, bvec, n6, first, w.status + 2, w.chol, chol_bytes, stream);
       if (rc != DROID_OK) return rc;
     }
     ProfScope ps(DROID_PROF_BA_UPDATE, st);
     if (p->motion_only || p->n_eta == 0 || p->n_edges == 0) {
       DROID_LAUNCH ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
-                                                                          w.dx, dx_out, p->t0, P, 1);
+                                                                          w.dx, dx_out, p->t0, P, 1, ppos);
     } else {
       DROID_LAUNCH ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
-                                                                          w.dx, dx_out, p->t0, P, 0);
+                                                                          w.dx, dx_out, p->t0, P, 0, ppos);
       DROID_LAUNCH ba_dz_kernel<<<dim3((HW + kThreads - 1) / kThreads, p->n_eta), kThreads, 0, st>>>(
           disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
           w.dx, dz_out, HW, p->wd, p->t0, P, p->n_eta, frame_lo, frame_hi);

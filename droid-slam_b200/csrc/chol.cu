@@ -17,59 +17,165 @@
 namespace droid {
 
 static constexpr int NB = 64;
-static constexpr int kSmallMax = 156;  // (n+1)*(n+1)*8 bytes <= ~197 KB of shared memory
+static constexpr int kSmallMax = kCholSmallMax;  // (n+1)*(n+1)*8 bytes <= ~197 KB of shared memory
+__host__ __device__ inline int chol_small_ld(int n) {  // >= n, == 2 (mod 4)
+  return ((n + 1) & ~3) + 2 >= n ? (((n + 1) & ~3) + 2) : (((n + 1) & ~3) + 6);
+}
+static size_t chol_small_smem(int n) {
+  return ((size_t)(n + 1) * chol_small_ld(n) + 8 * 8 + 160 + 160) * sizeof(double);
+}
+static constexpr int kSmallSmemMax = (157 * 158 + 64 + 320) * 8;
 
 // ------------------------------------------------------------------------------------------------
 // small systems: whole solve in one CTA
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) chol_small_kernel(double* __restrict__ A, int n,
+// One CTA, one matrix row per thread (row n = rhs), S [n+1][ld] in shared memory with ld == 2 (mod 4) so that a
+// thread's own row can be read two columns at a time (LDS.128) without bank conflicts.  Left-looking in blocks of
+// KB = 8 columns:
+//   (i)   every row subtracts the contribution of all finished columns from its 8 entries of the block
+//         (a[k] -= sum_{j<c0} L[r][j] L[c0+k][j]; own row vectorised, the 8 diagonal rows are broadcasts);
+//   (ii)  the 8 diagonal rows publish their entries (the updated 8x8 diagonal block);
+//   (iii) EVERY thread factorises that 8x8 block redundantly in registers and eliminates its own row in the same
+//         pass - no communication, no barrier inside the block; the serial chain is 8 x (reciprocal + 2 DFMA);
+//   (iv)  L entries go back to S.
+// Two barriers per 8 columns.  Treating the rhs as row n solves L y = b on the way.  Backward sweep L^T x = y:
+// thread t keeps y_t in a register; 32 columns at a time are solved inside one warp with shuffles, then all
+// earlier threads subtract that block's contribution (row c of L is contiguous in shared memory).
+// A is NOT written back on this path (only x, into row n); the blocked path below leaves L in A.
+static constexpr int KB = 8;
+
+__device__ __forceinline__ double shfl_f64(double v, int src) {
+  return __hiloint2double(__shfl_sync(0xffffffffu, __double2hiint(v), src),
+                          __shfl_sync(0xffffffffu, __double2loint(v), src));
+}
+
+__global__ void __launch_bounds__(160) chol_small_kernel(double* __restrict__ A, int n,
                                                          int* __restrict__ info) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* S = reinterpret_cast<double*>(smem_raw);  // [(n+1)][ld], row n = rhs
-  const int ld = n + 1;
-  const int tid = threadIdx.x;
+  const int R = n + 1;
+  const int ld = chol_small_ld(n);
+  double* S = reinterpret_cast<double*>(smem_raw);
+  double* Dsh = S + (size_t)R * ld;  // [KB][KB]
+  double* rsd = Dsh + KB * KB;       // [160]
+  double* xs = rsd + 160;            // [160]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
   __shared__ int fail;
   if (tid == 0) fail = 0;
-  for (int e = tid; e < (n + 1) * n; e += 256) {
-    const int r = e / n, c = e - r * n;
-    if (c <= r) S[r * ld + c] = A[(size_t)r * n + c];
+  for (int r = warp; r < R; r += nwarps) {
+    const int lim = (r == n) ? n : r + 1;
+    const double* src = A + (size_t)r * n;
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(S + r * ld);
+    for (int c = lane; c < lim; c += 32)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst + c * 8), "l"(src + c));
   }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
-  for (int c = 0; c < n; c++) {
-    const double d = S[c * ld + c];
-    if (!(d > 0.0)) {
-      if (tid == 0) fail = 1;
-    }
-    const double inv = 1.0 / sqrt(d);
-    __syncthreads();
-    // scale column c (rows c..n, row n is the rhs)
-    for (int r = c + tid; r <= n; r += 256) S[r * ld + c] = (r == c) ? sqrt(d) : S[r * ld + c] * inv;
-    __syncthreads();
-    // trailing update of the lower triangle, rows c+1..n
-    const int rem = n - c;  // rows c+1..n  -> rem rows, columns c+1..min(r, n-1)
-    for (int e = tid; e < rem * rem; e += 256) {
-      const int rr = e / rem, cc = e - rr * rem;
-      const int r = c + 1 + rr, q = c + 1 + cc;
-      if (q <= r && q < n) S[r * ld + q] -= S[r * ld + c] * S[q * ld + c];
-    }
-    __syncthreads();
-  }
-  // row n now holds y (L y = b).  Backward: L^T x = y, done by warp 0.
-  if (tid < 32) {
-    for (int c = n - 1; c >= 0; c--) {
-      double s = 0.0;
-      for (int t = c + 1 + tid; t < n; t += 32) s += S[t * ld + c] * S[n * ld + t];
+
+  const bool is_rhs = tid + 0 == n;  // re-evaluated per block below (row index changes with c0)
+  (void)is_rhs;
+  for (int c0 = 0; c0 < n; c0 += KB) {
+    const int kb = min(KB, n - c0);
+    const int r = c0 + tid;
+    const bool active = r < R;
+    double a[KB];
+    if (active) {
+      const double* own = S + r * ld;
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      if (tid == 0) S[n * ld + c] = (S[n * ld + c] - s) / S[c * ld + c];
-      __syncwarp();
+      for (int k = 0; k < KB; k++) a[k] = (k < kb && (c0 + k <= r || r == n)) ? own[c0 + k] : 0.0;
+      // (i) left-looking update with the finished columns 0..c0-1
+      const double2* own2 = reinterpret_cast<const double2*>(own);
+#pragma unroll 2
+      for (int j = 0; j < c0; j += 2) {
+        const double2 o = own2[j >> 1];
+#pragma unroll
+        for (int k = 0; k < KB; k++) {
+          if (k < kb) {
+            const double2 d = *reinterpret_cast<const double2*>(S + (c0 + k) * ld + j);
+            a[k] = fma(-o.x, d.x, a[k]);
+            a[k] = fma(-o.y, d.y, a[k]);
+          }
+        }
+      }
+      // (ii) the diagonal rows publish the updated diagonal block
+      if (tid < kb) {
+#pragma unroll
+        for (int k = 0; k < KB; k++) Dsh[tid * KB + k] = a[k];
+      }
+    }
+    __syncthreads();
+    if (active) {
+      // (iii) redundant factorisation of the 8x8 block + elimination of the own row
+      double D[KB][KB];
+#pragma unroll
+      for (int q = 0; q < KB; q++)
+#pragma unroll
+        for (int k = 0; k <= q; k++) D[q][k] = (q < kb) ? Dsh[q * KB + k] : (q == k ? 1.0 : 0.0);
+      double rs[KB];
+      bool bad = false;
+#pragma unroll
+      for (int C = 0; C < KB; C++) {
+        const double d = D[C][C];
+        bad |= !(d > 0.0);
+        const double inv = 1.0 / d;
+        const double m = a[C] * inv;
+#pragma unroll
+        for (int q = C + 1; q < KB; q++) {
+          const double mq = D[q][C] * inv;
+#pragma unroll
+          for (int k = C + 1; k <= q; k++) D[q][k] = fma(-mq, D[k][C], D[q][k]);
+          a[q] = fma(-m, D[q][C], a[q]);
+        }
+        rs[C] = sqrt(inv);
+      }
+      // (iv) L entries of this block
+      double* own = S + r * ld;
+#pragma unroll
+      for (int k = 0; k < KB; k++)
+        if (k < kb && (c0 + k <= r || r == n)) own[c0 + k] = a[k] * rs[k];
+      if (tid < kb) {
+        double mine = 0.0;
+#pragma unroll
+        for (int k = 0; k < KB; k++) mine = (k == tid) ? rs[k] : mine;
+        rsd[c0 + tid] = mine;
+      }
+      if (tid == 0 && bad) fail = 1;
+    }
+    __syncthreads();
+  }
+
+  // backward sweep
+  double y = (tid < n) ? S[n * ld + tid] : 0.0;
+  const double myrs = (tid < n) ? rsd[tid] : 0.0;
+  double x = 0.0;
+  for (int w = (n - 1) >> 5; w >= 0; w--) {
+    const int b0 = w << 5;
+    if (warp == w) {
+      double Lr[32];
+#pragma unroll
+      for (int c = 0; c < 32; c++) Lr[c] = (b0 + c < n && lane < c) ? S[(b0 + c) * ld + b0 + lane] : 0.0;
+#pragma unroll
+      for (int c = 31; c >= 0; c--) {
+        const double xc = shfl_f64(y * myrs, c);
+        if (lane == c) x = xc;
+        y = fma(-Lr[c], xc, y);
+      }
+      xs[b0 + lane] = x;
+    }
+    __syncthreads();
+    if (warp < w) {
+      const int cend = min(32, n - b0);
+      double y0 = 0.0, y1 = 0.0;
+#pragma unroll 4
+      for (int c = 0; c + 1 < cend; c += 2) {
+        y0 = fma(S[(b0 + c) * ld + tid], xs[b0 + c], y0);
+        y1 = fma(S[(b0 + c + 1) * ld + tid], xs[b0 + c + 1], y1);
+      }
+      if (cend & 1) y0 = fma(S[(b0 + cend - 1) * ld + tid], xs[b0 + cend - 1], y0);
+      y -= y0 + y1;
     }
   }
-  __syncthreads();
-  for (int e = tid; e < (n + 1) * n; e += 256) {
-    const int r = e / n, c = e - r * n;
-    if (c <= r) A[(size_t)r * n + c] = S[r * ld + c];
-  }
+  if (tid < n) A[(size_t)n * n + tid] = x;
   if (tid == 0 && fail) *info = 1;
 }
 
@@ -131,7 +237,9 @@ struct ElimStep<kRot> {
 };
 
 __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__ A, int n, int j0, int jb,
-                                                            int* __restrict__ info) {
+                                                            int* __restrict__ info,
+                                                            const int* __restrict__ hi64,
+                                                            int* __restrict__ arrive) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* R = reinterpret_cast<double*>(smem_raw);  // [256][65] row staging
   double* col = R + 256 * 65;                        // [2][128]  published column (double-buffered, padded)
@@ -141,6 +249,11 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
   const int tid = threadIdx.x;
   const bool diag = tid < 64;
   const int trow0 = j0 + jb + blockIdx.x * PR;       // first trailing row of this CTA
+  // envelope: rows past hi64[] have no entry in these columns (and get none); the CTA holding the rhs row stays
+  if (hi64 != nullptr && blockIdx.x != 0 && trow0 > hi64[(j0 + jb - 1) >> 6] && trow0 + PR <= n) {
+    if (threadIdx.x == 0) atomicAdd(&arrive[j0 >> 6], 1);
+    return;
+  }
   auto row_of = [&](int t) { return t < 64 ? j0 + t : trow0 + t - 64; };
   auto row_ok = [&](int t) { return t < 64 ? t < jb : (trow0 + t - 64) <= n; };
 
@@ -166,6 +279,9 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
   if (tid < 128) { col[tid] = 0.0; col[128 + tid] = 0.0; }
   if (tid < 80) inv[tid] = 0.0;
   __syncthreads();
+  // every CTA has now read the un-factorised diagonal block; CTA 0 overwrites it at the end, but only after all
+  // CTAs of this launch have checked in here (a CTA may be scheduled late when the SMs are busy with the SYRK)
+  if (tid == 0 && blockIdx.x != 0) atomicAdd(&arrive[j0 >> 6], 1);
 #pragma unroll
   for (int c = 0; c < 64; c++) a[c] = R[tid * 65 + c];
   if (diag) {
@@ -199,6 +315,10 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
 #pragma unroll 8
     for (int c = 0; c < 64; c++) R[tid * 65 + c] *= rs[c];
   }
+  if (blockIdx.x == 0 && tid == 0) {
+    volatile int* cnt = arrive + (j0 >> 6);
+    while (*cnt < (int)gridDim.x - 1) {}
+  }
   __syncthreads();
 #pragma unroll 16
   for (int q = 0; q < 64; q++) {
@@ -210,6 +330,158 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------------
+// chol_panel2_kernel: same arithmetic as chol_panel_kernel, laid out for the shared-memory return path.
+// With one row per thread every DFMA needs its own broadcast operand from shared memory (8 B per lane per DFMA):
+// 256 rows x 2016 doubles = 4 MB per sub-panel through 128 B/clk = 32 k cycles, which is what the kernel took.
+//  * register tile 4 rows x 16 columns per thread, columns CYCLIC over the 4 lanes of a quad (lane k owns the
+//    columns == k mod 4): every operand read from shared memory feeds 4 DFMAs, all lanes have the same amount of
+//    work left at every step (no divergence), and the multipliers of the quad's 4 rows travel by shuffle.
+//  * producer / consumer split: the 64 diagonal rows (warps 0-1) run the pivot chain alone, synchronising with a
+//    64-thread named barrier, and publish every column of the diagonal block plus its reciprocal pivot (colS, one
+//    slot per column).  The 192 trailing rows (warps 2-7) never feed back into that chain: they take no barrier,
+//    poll a progress counter once per 8 columns and run 8+ columns behind.
+//  * no staging: a quad reads / writes 32 contiguous bytes of a row, so global loads and stores go straight
+//    between registers and memory at full sector efficiency (no transposition through shared memory).
+// ------------------------------------------------------------------------------------------------
+#ifndef PANEL_EXP
+#define PANEL_EXP 0
+#endif
+#if PANEL_EXP & 8
+__device__ long long g_ts[16];
+#define TS(i) if ((C == 30 || C == 31) && tid == 32) g_ts[(C - 30) * 4 + (i)] = clock64();
+#else
+#define TS(i)
+#endif
+static constexpr int kPanel2Smem = (64 * 64 + 64 + 64 + 64 + 8) * (int)sizeof(double);
+
+template <int C>
+struct ElimStep2 {
+  static __device__ __forceinline__ void run(double (&a)[4][16], double* colS, double* inv, double* dv,
+                                             volatile int* ready, int tid, int k) {
+    constexpr int kC = C & 3, jC = C >> 2;
+    if (tid < 64) {
+      asm volatile("bar.sync 1, 64;" ::: "memory");       // column C and inv[C] are complete
+      if (tid == 0) *ready = C + 1;
+      TS(0)
+    } else if ((C & 7) == 0) {
+      constexpr int need = C + 8 < 64 ? C + 8 : 64;
+      if (!(PANEL_EXP & 4)) while (*ready < need) {}
+      __threadfence_block();
+    }
+    const double* cc = colS + C * 64;                       // cc[q] = entry (q, C) of the diagonal block
+    const double iv = inv[C];
+    const int owner = (tid & 28) | kC;                      // lane of this quad that holds column C
+    double m[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) m[i] = shfl_f64(a[i][jC] * iv, owner);
+    TS(1)
+    if constexpr (C + 1 < 64) {
+      constexpr int k1 = (C + 1) & 3, j1 = (C + 1) >> 2;
+      if (k == k1) {                                        // column C+1 first: it carries the pivot chain
+        const double c1 = cc[C + 1];
+#pragma unroll
+        for (int i = 0; i < 4; i++) a[i][j1] = fma(-m[i], c1, a[i][j1]);
+        if (tid < 64) {
+          double* dst = colS + (C + 1) * 64 + (tid >> 2) * 4;
+          *reinterpret_cast<double2*>(dst) = make_double2(a[0][j1], a[1][j1]);
+          *reinterpret_cast<double2*>(dst + 2) = make_double2(a[2][j1], a[3][j1]);
+          if ((tid >> 2) == ((C + 1) >> 2)) {
+            const double d = a[(C + 1) & 3][j1];
+            inv[C + 1] = 1.0 / d;
+            dv[C + 1] = d;
+          }
+        }
+      }
+    }
+    TS(2)
+    // boundary registers (column 4*jj + k may be <= C, or C+1 which is done): predicated
+    constexpr int jB0 = jC, jB1 = (C + 1) >> 2;
+    if (!((PANEL_EXP & 2) && tid < 64)) {
+#pragma unroll
+    for (int jj = jB0; jj <= jB1 && jj < 16; jj++) {
+      const int col = 4 * jj + k;
+      if (col > C + 1) {
+        const double w = cc[col];
+#pragma unroll
+        for (int i = 0; i < 4; i++) a[i][jj] = fma(-m[i], w, a[i][jj]);
+      }
+    }
+#pragma unroll
+    for (int jj = jB1 + 1; jj < 16; jj++) {
+      const double w = cc[4 * jj + k];
+#pragma unroll
+      for (int i = 0; i < 4; i++) a[i][jj] = fma(-m[i], w, a[i][jj]);
+    }
+    }
+    TS(3)
+    ElimStep2<C + 1>::run(a, colS, inv, dv, ready, tid, k);
+  }
+};
+template <>
+struct ElimStep2<64> {
+  static __device__ __forceinline__ void run(double (&)[4][16], double*, double*, double*, volatile int*, int, int) {}
+};
+
+__global__ void __launch_bounds__(256, 1) chol_panel2_kernel(double* __restrict__ A, int n, int j0, int jb,
+                                                             int* __restrict__ info,
+                                                             const int* __restrict__ hi64) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* colS = reinterpret_cast<double*>(smem_raw);  // [64][64]  published columns
+  double* inv = colS + 64 * 64;                        // [64] 1 / pivot
+  double* dv = inv + 64;                               // [64] pivots
+  double* rs = dv + 64;                                // [64] 1 / sqrt(pivot)
+  volatile int* ready = reinterpret_cast<volatile int*>(rs + 64);
+  const int tid = threadIdx.x, k = tid & 3;
+  const int trow0 = j0 + jb + blockIdx.x * PR;
+  if (hi64 != nullptr && blockIdx.x != 0 && trow0 > hi64[(j0 + jb - 1) >> 6] && trow0 + PR <= n) return;
+  const int t0 = (tid >> 2) * 4;                       // first of this quad's 4 rows (0..63 diagonal, 64.. trailing)
+  const bool diag = tid < 64;
+  double a[4][16];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int t = t0 + i;
+    const int row = diag ? j0 + t : trow0 + t - 64;
+    const bool ok = diag ? t < jb : row <= n;
+    const double* src = A + (size_t)row * n + j0 + k;
+#pragma unroll
+    for (int jj = 0; jj < 16; jj++) {
+      const int col = 4 * jj + k;
+      a[i][jj] = (ok && col < jb && (!diag || col <= t)) ? src[4 * jj] : 0.0;
+      if (diag && t >= jb && col == t) a[i][jj] = 1.0;   // partial block padded with I
+    }
+  }
+  if (tid == 0) *ready = 0;
+  if (diag && k == 0) {
+    *reinterpret_cast<double2*>(colS + t0) = make_double2(a[0][0], a[1][0]);
+    *reinterpret_cast<double2*>(colS + t0 + 2) = make_double2(a[2][0], a[3][0]);
+    if (tid == 0) { inv[0] = 1.0 / a[0][0]; dv[0] = a[0][0]; }
+  }
+  __syncthreads();
+  if ((PANEL_EXP & 1) && tid >= 64) return;
+  ElimStep2<0>::run(a, colS, inv, dv, ready, tid, k);
+  if (diag) {
+    asm volatile("bar.sync 1, 64;" ::: "memory");
+    const double d = dv[tid];
+    if (!(d > 0.0) && blockIdx.x == 0) *info = 1;
+    rs[tid] = 1.0 / sqrt(d);
+  }
+  __syncthreads();
+  if (diag && blockIdx.x != 0) return;                  // the diagonal block is written once (CTA 0), lower part
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int t = t0 + i;
+    const int row = diag ? j0 + t : trow0 + t - 64;
+    const bool ok = diag ? t < jb : row <= n;
+    double* dst = A + (size_t)row * n + j0 + k;
+#pragma unroll
+    for (int jj = 0; jj < 16; jj++) {
+      const int col = 4 * jj + k;
+      if (ok && col < jb && (!diag || col <= t)) dst[4 * jj] = a[i][jj] * rs[col];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // trailing update  C[bi][bj] -= X_bi X_bj^T over k in [J, J+kb), for all TM x TM tiles bi >= bj of
 // rows/cols r0 = J+kb .. (row n included as a row, never as a column).  One CTA (256 threads) per tile,
 // (TM/16)^2 fp64 accumulators per thread, operands staged k-major in shared memory in chunks of 16 k,
@@ -217,7 +489,7 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
 // ------------------------------------------------------------------------------------------------
 template <int TM, bool VEC>
 __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
-    chol_syrk_kernel(double* __restrict__ A, int n, int J, int kb, int strip) {
+    chol_syrk_kernel(double* __restrict__ A, int n, int J, int kb, int strip, const int* __restrict__ hi64) {
   constexpr int F = TM / 64;
   constexpr int KC = 16;
   constexpr int LD = TM + 2;
@@ -247,6 +519,10 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
   const int rows = min(TM, n + 1 - i0);
   const int cols = min(min(TM, n - c0), strip > 0 ? strip - bj * TM : TM);
   if (cols <= 0 || rows <= 0) return;
+  if (hi64 != nullptr) {   // envelope: X_bi or X_bj structurally zero in these kb columns
+    const int hi = hi64[(J + kb - 1) >> 6];
+    if (c0 > hi || (i0 > hi && i0 + rows <= n)) return;
+  }
   const int tid = threadIdx.x;
   const int ty = tid >> 4, tx = tid & 15;
   double acc[F * 4][F * 4];
@@ -523,10 +799,16 @@ __global__ void __launch_bounds__(256) chol_bwd_diag_kernel(double* __restrict__
   for (int i = tid; i < JB; i += 256) y[J0 + i] = ys[i];
 }
 
-__global__ void __launch_bounds__(256) chol_bwd_gemv_kernel(double* __restrict__ A, int n, int J0, int JB) {
+__global__ void __launch_bounds__(256) chol_bwd_gemv_kernel(double* __restrict__ A, int n, int J0, int JB,
+                                                            const int* __restrict__ lo64) {
   __shared__ double xs[SB];
   __shared__ double part[4][NB];
   const int tid = threadIdx.x;
+  if (lo64 != nullptr) {   // envelope: the super-block's rows start at column lo
+    int lo = n;
+    for (int b = J0 >> 6; b <= (J0 + JB - 1) >> 6; b++) lo = min(lo, lo64[b]);
+    if ((int)blockIdx.x * NB + NB - 1 < lo) return;
+  }
   double* y = A + (size_t)n * n;
   for (int i = tid; i < SB; i += 256) xs[i] = i < JB ? y[J0 + i] : 0.0;
   __syncthreads();
@@ -550,18 +832,43 @@ __global__ void __launch_bounds__(256) chol_bwd_gemv_kernel(double* __restrict__
   }
 }
 
+// Envelope summary per 64-block from first[r] = first structurally non-zero column of row r (fill-in of a Cholesky
+// factor stays inside the row envelopes):
+//   hi64[c] = last row with an entry in a column <= 64c+63  (monotone in c; >= the block's own last row)
+//   lo64[b] = first column used by the rows of block b
+__global__ void __launch_bounds__(1024) chol_env_kernel(const int* __restrict__ first, int n, int* __restrict__ hi64,
+                                                        int* __restrict__ lo64) {
+  const int nb = (n + 63) >> 6;
+  for (int c = threadIdx.x; c < nb; c += 1024) { hi64[c] = min(64 * c + 63, n - 1); lo64[c] = 64 * c; }
+  __syncthreads();
+  for (int r = threadIdx.x; r < n; r += 1024) {
+    const int f = max(0, min(first[r], r));
+    atomicMax(&hi64[f >> 6], r);
+    atomicMin(&lo64[r >> 6], f);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = 0;
+    for (int c = 0; c < nb; c++) { run = max(run, hi64[c]); hi64[c] = run; }
+  }
+}
+
 }  // namespace droid
 
 using namespace droid;
 
 extern "C" size_t droid_chol_workspace_bytes(int n) {
-  (void)n;
-  return 256;  // the factorisation is in place; reserved for future use
+  const size_t nb = (size_t)((n > 0 ? n : 0) + 63) / 64;
+  return 256 + 3 * nb * sizeof(int);   // panel check-in counters | hi64 | lo64 of the envelope variant
 }
 
 extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, void* workspace,
                                     size_t workspace_bytes, void* stream) {
-  (void)workspace; (void)workspace_bytes;
+  return droid_chol_solve_env_f64(A, b, n, nullptr, info_dev, workspace, workspace_bytes, stream);
+}
+
+extern "C" int droid_chol_solve_env_f64(double* A, double* b, int n, const int* first_dev, int* info_dev,
+                                        void* workspace, size_t workspace_bytes, void* stream) {
   if (n < 0 || !info_dev) return DROID_ERR_INVALID_ARGUMENT;
   if (n == 0) return DROID_OK;
   if (!A || !b) return DROID_ERR_INVALID_ARGUMENT;
@@ -571,11 +878,11 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
   if (n <= kSmallMax) {
     static bool attr_set = false;
     if (!attr_set) {
-      cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmemMax);
       attr_set = true;
     }
-    const size_t smem = (size_t)(n + 1) * (n + 1) * sizeof(double);
-    DROID_LAUNCH chol_small_kernel<<<1, 256, smem, st>>>(A, n, info_dev);
+    const size_t smem = chol_small_smem(n);
+    DROID_LAUNCH chol_small_kernel<<<1, ((n + 1 + 31) / 32) * 32, smem, st>>>(A, n, info_dev);
     return check_launch();
   }
   static bool attr2 = false;
@@ -583,6 +890,7 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
   constexpr int kSyrk64 = (2 * 2 * 16 * (64 + 2) + 64 * 64) * (int)sizeof(double);
   if (!attr2) {
     cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmem);
+    cudaFuncSetAttribute(chol_panel2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanel2Smem);
     cudaFuncSetAttribute(chol_bwd_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem);
     cudaFuncSetAttribute(chol_syrk_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
     cudaFuncSetAttribute(chol_syrk_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
@@ -591,6 +899,18 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
     attr2 = true;
   }
   const bool vec = (n % 2 == 0) && (((uintptr_t)A & 15) == 0);
+  // Envelope variant: the launches keep their dense shapes (the host never learns the structure), CTAs whose rows
+  // or columns lie outside the envelope return at once.  64x64 tiles throughout: the active window is narrow.
+  int* hi64 = nullptr;
+  int* lo64 = nullptr;
+  if (!workspace || workspace_bytes < droid_chol_workspace_bytes(n)) return DROID_ERR_WORKSPACE_TOO_SMALL;
+  int* arrive = reinterpret_cast<int*>(workspace);
+  cudaMemsetAsync(arrive, 0, (size_t)((n + 63) / 64) * sizeof(int), st);
+  if (first_dev != nullptr) {
+    hi64 = arrive + (n + 63) / 64;
+    lo64 = hi64 + (n + 63) / 64;
+    DROID_LAUNCH chol_env_kernel<<<1, 1024, 0, st>>>(first_dev, n, hi64, lo64);
+  }
   // Look-ahead: while the bulk of trailing update J runs on the caller's stream, a second (high-priority) stream
   // updates the next panel's 128 columns first and factorises them, so the serial panel chain hides behind the
   // SYRK for as long as the SYRK is the longer of the two.
@@ -633,13 +953,13 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
     for (int j0 = J; j0 < J + kb; j0 += NB) {
       const int jb = (J + kb - j0) < NB ? (J + kb - j0) : NB;
       const int rem_rows = n + 1 - (j0 + jb);  // >= 1 (the rhs row)
-      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PR - 1) / PR, 256, kPanelSmem, ps>>>(A, n, j0, jb, info_dev);
+      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PR - 1) / PR, 256, kPanelSmem, ps>>>(A, n, j0, jb, info_dev, hi64, arrive);
       const int rest = J + kb - (j0 + jb);     // columns of this outer panel still to factorise
       if (rest > 0) {
         // rank-64 update of the panel's remaining columns only (64x64 tiles of one block column, all SMs)
         const int t64 = (rem_rows + 63) / 64;
-        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest);
-        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest);
+        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest, hi64);
+        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest, hi64);
       }
     }
     prof_mark(DROID_PROF_CHOL_PANEL, false, ps);
@@ -648,26 +968,26 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
     const int rr = n + 1 - r0;
     const int t128 = (rr + 127) / 128, t64 = (rr + 63) / 64;
     if (on_side) {
-      const bool big = t128 * (t128 + 1) / 2 >= 148;
+      const bool big = hi64 == nullptr && t128 * (t128 + 1) / 2 >= 148;
       cudaEventRecord(ev_p, side);
       cudaStreamWaitEvent(side, ev_r, 0);    // R(J-1) (no-op for the first panel)
-      if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128, 256, kSyrk128, side>>>(A, n, J, kb, PB);
-      else DROID_LAUNCH chol_syrk_kernel<64, true><<<2 * t64, 256, kSyrk64, side>>>(A, n, J, kb, PB);
+      if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128, 256, kSyrk128, side>>>(A, n, J, kb, PB, hi64);
+      else DROID_LAUNCH chol_syrk_kernel<64, true><<<2 * t64, 256, kSyrk64, side>>>(A, n, J, kb, PB, hi64);
       cudaStreamWaitEvent(st, ev_p, 0);
       {
         ProfScope ps2(DROID_PROF_CHOL_SYRK, st);
-        if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<(t128 - 1) * t128 / 2, 256, kSyrk128, st>>>(A, n, J, kb, -1);
-        else DROID_LAUNCH chol_syrk_kernel<64, true><<<(t64 - 2) * (t64 - 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, -2);
+        if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<(t128 - 1) * t128 / 2, 256, kSyrk128, st>>>(A, n, J, kb, -1, hi64);
+        else DROID_LAUNCH chol_syrk_kernel<64, true><<<(t64 - 2) * (t64 - 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, -2, hi64);
       }
       cudaEventRecord(ev_r, st);
     } else {
       ProfScope ps2(DROID_PROF_CHOL_SYRK, st);
-      if (t128 * (t128 + 1) / 2 >= 148) {
-        if (vec) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb, 0);
-        else DROID_LAUNCH chol_syrk_kernel<128, false><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb, 0);
+      if (hi64 == nullptr && t128 * (t128 + 1) / 2 >= 148) {
+        if (vec) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb, 0, hi64);
+        else DROID_LAUNCH chol_syrk_kernel<128, false><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb, 0, hi64);
       } else {
-        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, 0);
-        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, 0);
+        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, 0, hi64);
+        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, 0, hi64);
       }
     }
   }
@@ -679,7 +999,7 @@ extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, 
   for (int J0 = ((n - 1) / SB) * SB; J0 >= 0; J0 -= SB) {
     const int JB = (n - J0) < SB ? (n - J0) : SB;
     DROID_LAUNCH chol_bwd_diag_kernel<<<1, 256, kBwdSmem, st>>>(A, n, J0, JB, vec ? 1 : 0);
-    if (J0 > 0) DROID_LAUNCH chol_bwd_gemv_kernel<<<(J0 + NB - 1) / NB, 256, 0, st>>>(A, n, J0, JB);
+    if (J0 > 0) DROID_LAUNCH chol_bwd_gemv_kernel<<<(J0 + NB - 1) / NB, 256, 0, st>>>(A, n, J0, JB, lo64);
   }
   return check_launch();
 }

@@ -67,7 +67,8 @@ C_ABI_SYMBOLS = [
     "droid_corr_index_pyramid", "droid_altcorr_forward", "droid_altcorr_backward",
     "droid_altcorr_forward_indexed", "droid_corr_build", "droid_corr_build_workspace_bytes",
     "droid_frame_distance", "droid_projmap", "droid_iproj", "droid_depth_filter",
-    "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_workspace_bytes",
+    "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_solve_env_f64",
+    "droid_chol_workspace_bytes",
 ]
 
 
@@ -397,17 +398,26 @@ def ba_status(device=None):
     return int(ws[off:off + 4].view(torch.int32).item())
 
 
-def chol_solve(A, b):
-    """Extension (tests/bench): solves A x = b for SPD fp64 A on the device; returns (x, info)."""
+def chol_solve(A, b, first=None):
+    """Extension (tests/bench): solves A x = b for SPD fp64 A on the device; returns (x, info).
+    first (int32 [n], optional): first non-zero column of every row -> envelope variant."""
     n = A.shape[0]
     with torch.cuda.device(A.device):
         buf = torch.empty((n * n + n,), dtype=torch.float64, device=A.device)
         buf[: n * n] = A.reshape(-1)
         buf[n * n:] = b.reshape(-1)
         info = torch.zeros((1,), dtype=torch.int32, device=A.device)
-        _check(_lib.droid_chol_solve_f64(_p(buf), ctypes.c_void_p(buf.data_ptr() + 8 * n * n), n,
-                                         _p(info), ctypes.c_void_p(0), ctypes.c_size_t(0),
-                                         _stream(A)), "chol_solve")
+        wsb = int(_lib.droid_chol_workspace_bytes(n))
+        ws = torch.empty((wsb,), dtype=torch.uint8, device=A.device)
+        bptr = ctypes.c_void_p(buf.data_ptr() + 8 * n * n)
+        if first is None:
+            _check(_lib.droid_chol_solve_f64(_p(buf), bptr, n, _p(info), _p(ws), ctypes.c_size_t(wsb),
+                                             _stream(A)), "chol_solve")
+        else:
+            if first.dtype != torch.int32 or first.numel() != n or not first.is_cuda:
+                raise RuntimeError("first must be a CUDA int32 tensor of n entries")
+            _check(_lib.droid_chol_solve_env_f64(_p(buf), bptr, n, _p(first.contiguous()), _p(info), _p(ws),
+                                                 ctypes.c_size_t(wsb), _stream(A)), "chol_solve_env")
     return buf[n * n:].clone(), info
 
 

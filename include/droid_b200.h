@@ -175,9 +175,19 @@ int droid_ba(float* poses, float* disps, const float* intrinsics, const float* d
 #define DROID_BA_STATUS_CHOL_FAILED 4
 
 /* Dense SPD solve used by ba, exported for tests/bench: A [n,n] fp64 row-major (lower triangle
- * read, overwritten by L), b [n] fp64 (overwritten by x); info (device int) != 0 on failure. */
+ * read; contents unspecified afterwards: untouched for n <= 156, L for larger n), b [n] fp64
+ * (must be A + n*n; overwritten by x); info (device int) != 0 on failure.
+ * workspace: droid_chol_workspace_bytes(n) bytes of device memory (may be NULL for n <= 156). */
 int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, void* workspace,
                          size_t workspace_bytes, void* stream);
+
+/* Same solve for a matrix with a known row envelope: first_dev[r] (device, int[n]) = first structurally
+ * non-zero column of row r (entries left of it must be exactly 0).  Fill-in stays inside the envelope, so
+ * all tiles outside it are skipped; first_dev == NULL is the dense solve.  Replaces the sparsity that the
+ * reference gets from Eigen::SimplicialLLT on a SparseMatrix (src/droid_kernels.cu:1192-1201).
+ * workspace: droid_chol_workspace_bytes(n) bytes. */
+int droid_chol_solve_env_f64(double* A, double* b, int n, const int* first_dev, int* info_dev,
+                             void* workspace, size_t workspace_bytes, void* stream);
 size_t droid_chol_workspace_bytes(int n);
 
 #ifdef __cplusplus

@@ -306,14 +306,14 @@ def test_ba_large_system_uses_blocked_cholesky(backends):
     assert rel(gdx, rdx) <= 3e-4 and rel(gdz, rdz) <= 1e-4
 
 
-@pytest.mark.parametrize("n", [7, 64, 156, 157, 200, 777, 1200, 2431, 2500])
+@pytest.mark.parametrize("n", [1, 2, 3, 7, 8, 9, 31, 33, 64, 66, 97, 150, 155, 156, 157, 200, 777, 1200, 2431, 2500])
 def test_chol_solve(backends, n):
     rng = np.random.default_rng(n)
     Mx = rng.normal(size=(n, n)); A = Mx @ Mx.T + n * np.eye(n); b = rng.normal(size=n)
     x, info = backends.chol_solve(cu(A), cu(b))
     assert int(info.item()) == 0
     assert rel(x.cpu().numpy(), np.linalg.solve(A, b)) <= 1e-10
-    A[n // 2, n // 2] = -1.0                       # not SPD -> failure flag, like Eigen's info()
+    A[n // 2, n // 2] = -1.0 - n                   # not SPD -> failure flag, like Eigen's info()
     _, info = backends.chol_solve(cu(A), cu(b))
     assert int(info.item()) != 0
 

@@ -17,6 +17,7 @@ e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=Tr
 buf = torch.empty(n * n + n, device="cuda", dtype=torch.float64)
 import ctypes
 inf = torch.zeros(1, dtype=torch.int32, device="cuda")
+wsb = int(B._lib.droid_chol_workspace_bytes(n)); ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
 ts = []
 B.prof_enable(True); B.prof_read()
 for _ in range(reps):
@@ -24,7 +25,7 @@ for _ in range(reps):
     torch.cuda.synchronize()
     e0.record()
     B._lib.droid_chol_solve_f64(ctypes.c_void_p(buf.data_ptr()), ctypes.c_void_p(buf.data_ptr() + 8 * n * n), n,
-                                ctypes.c_void_p(inf.data_ptr()), ctypes.c_void_p(0), ctypes.c_size_t(0),
+                                ctypes.c_void_p(inf.data_ptr()), ctypes.c_void_p(ws.data_ptr()), ctypes.c_size_t(wsb),
                                 ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
     e1.record(); torch.cuda.synchronize()
     ts.append(e0.elapsed_time(e1))
