@@ -17,6 +17,8 @@
 //    fp32 blocks in double on the host, :1133-1156) as a dense lower-triangular 6P x 6P matrix, then
 //    damped and factorised on the device (chol.cu) -- replaces Eigen::SimplicialLLT on one CPU core.
 #include "common.cuh"
+#include "ba_lin.cuh"
+#include <cstdlib>
 
 namespace droid {
 
@@ -333,60 +335,6 @@ __global__ void ba_edge_pose_kernel(const float* __restrict__ poses, const int64
   o[3] = g.q[0]; o[4] = g.q[1]; o[5] = g.q[2]; o[6] = g.q[3]; o[7] = 0.f;
 }
 
-// ------------------------------------------------------------------------------------------------
-// per pixel-edge linearisation (src/droid_kernels.cu:283-375)
-// ------------------------------------------------------------------------------------------------
-struct PixLin {
-  float Ji_u[6], Jj_u[6], Ji_v[6], Jj_v[6];
-  float Jz_u, Jz_v;
-  float wu_d, wv_d;  // weights of the depth terms (C, bz)
-  float wu, wv;      // weights of the pose terms (zeroed on stereo edges, :323,:356)
-  float ru, rv;
-};
-
-__device__ __forceinline__ void linearise(const SE3& g, const Intr& K, int wd, int k, float disp,
-                                          float tu, float tv, float wru, float wrv, bool stereo,
-                                          PixLin& L) {
-  const int i = k / wd, j = k - i * wd;
-  const float u = (float)j, v = (float)i;
-  float Xi[4], Xj[4];
-  Xi[0] = (u - K.cx) / K.fx;
-  Xi[1] = (v - K.cy) / K.fy;
-  Xi[2] = 1;
-  Xi[3] = disp;
-  act_se3(g.t, g.q, Xi, Xj);
-  const float x = Xj[0], y = Xj[1], h = Xj[3];
-  const bool behind = Xj[2] < DROID_MIN_DEPTH;
-  const float d = behind ? 0.0f : (float)(1.0 / (double)Xj[2]);
-  const float d2 = d * d;
-  L.wu_d = behind ? 0.0f : (float)(.001 * (double)wru);
-  L.wv_d = behind ? 0.0f : (float)(.001 * (double)wrv);
-  L.ru = tu - (K.fx * d * x + K.cx);
-  L.rv = tv - (K.fy * d * y + K.cy);
-  L.Jj_u[0] = K.fx * (h * d);
-  L.Jj_u[1] = K.fx * 0;
-  L.Jj_u[2] = K.fx * (-x * h * d2);
-  L.Jj_u[3] = K.fx * (-x * y * d2);
-  L.Jj_u[4] = K.fx * (1 + x * x * d2);
-  L.Jj_u[5] = K.fx * (-y * d);
-  L.Jz_u = K.fx * (g.t[0] * d - g.t[2] * (x * d2));
-  adj_se3(g.t, g.q, L.Jj_u, L.Ji_u);
-#pragma unroll
-  for (int n = 0; n < 6; n++) L.Ji_u[n] *= -1;
-  L.Jj_v[0] = K.fy * 0;
-  L.Jj_v[1] = K.fy * (h * d);
-  L.Jj_v[2] = K.fy * (-y * h * d2);
-  L.Jj_v[3] = K.fy * (-1 - y * y * d2);
-  L.Jj_v[4] = K.fy * (x * y * d2);
-  L.Jj_v[5] = K.fy * (x * d);
-  L.Jz_v = K.fy * (g.t[1] * d - g.t[2] * (y * d2));
-  adj_se3(g.t, g.q, L.Jj_v, L.Ji_v);
-#pragma unroll
-  for (int n = 0; n < 6; n++) L.Ji_v[n] *= -1;
-  L.wu = stereo ? 0.f : L.wu_d;
-  L.wv = stereo ? 0.f : L.wv_d;
-}
-
 __device__ __forceinline__ SE3 load_gij(const float* __restrict__ gij, int e) {
   const float4 a = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e * 8));
   const float4 b = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e * 8 + 4));
@@ -658,7 +606,7 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
     const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
     const float* __restrict__ Qi, const float* __restrict__ Wi, double* __restrict__ A,
     double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P, int n_eta, int frame_lo,
-    int frame_hi, const int* __restrict__ ppos) {
+    int frame_hi, const int* __restrict__ ppos, int tc_max_d) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int m = blockIdx.y;
   const int M = status[1];
@@ -672,6 +620,7 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
   const int e0 = eptr[m], e1 = eptr[m + 1];
   const int deg = e1 - e0;
   const int D = deg + 1, R = 6 * D;
+  if (D <= tc_max_d) return;                    // this frame is handled by ba_schur_tc_kernel (schur_tc.cu)
   const int DP = (D + 1) >> 1, RP = 12 * DP;   // row blocks are processed in pairs (12 rows); odd D is zero-padded
   const int stride = RP + 2;                    // == 2 (mod 4): even (LDS.64) and spreads the banks
   // smem: E[T][stride] | Qs[T] | QWs[T] | vS[R] | pose[2*DP] | s_e[deg] | s_jx[deg] | s_g[deg][8]
@@ -1054,9 +1003,37 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
       }
       if (!p->motion_only) {
         ProfScope ps(DROID_PROF_BA_SCHUR, st);
-        DROID_LAUNCH ba_schur_kernel<<<dim3(S, p->n_eta), kThreads, kSchurSmemBytes, st>>>(
+        // Gram products on the tensor cores for frames with <= 20 edges (schur_tc.cu), CUDA-core kernel for the
+        // rest.  The two kernels touch disjoint frames, so the CUDA-core one runs on a second stream: its few, long
+        // CTAs start first and the tensor-core CTAs fill the SMs around them instead of waiting for its tail.
+        static const bool use_tc = []() { const char* e = getenv("DROID_SCHUR_TC"); return !(e && e[0] == '0'); }();
+        static cudaStream_t s2 = nullptr;
+        static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+        static int s2_dev = -1;
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (use_tc && s2_dev != dev) {
+          cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking);
+          cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming);
+          cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming);
+          s2_dev = dev;
+        }
+        cudaStream_t so = st;
+        if (use_tc) {
+          cudaEventRecord(ev_fork, st);
+          cudaStreamWaitEvent(s2, ev_fork, 0);
+          so = s2;
+        }
+        DROID_LAUNCH ba_schur_kernel<<<dim3(S, p->n_eta), kThreads, kSchurSmemBytes, so>>>(
             disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q,
-            w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos);
+            w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, use_tc ? kSchurTcMaxD : 0);
+        if (use_tc) {
+          cudaEventRecord(ev_join, s2);
+          if (launch_schur_tc(disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
+                              w.A, bvec, HW, p->wd, slab, S, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, st))
+            return DROID_ERR_CUDA;
+          cudaStreamWaitEvent(st, ev_join, 0);
+        }
       }
     }
     if (check_launch()) return DROID_ERR_CUDA;

@@ -13,6 +13,7 @@
 // Failure (non-positive or NaN pivot) sets *info != 0; the caller zeroes dx like the reference
 // (src/droid_kernels.cu:1207-1210).  No host synchronisation anywhere.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace droid {
 
@@ -196,27 +197,50 @@ __global__ void __launch_bounds__(160) chol_small_kernel(double* __restrict__ A,
 // ------------------------------------------------------------------------------------------------
 static constexpr int PB = 128;
 static constexpr int PR = 192;
-static constexpr int kPanelSmem = (256 * 65 + 2 * 128 + 80 + 80 + 64) * (int)sizeof(double);
+#ifdef PANEL_TS
+__device__ long long g_ts[16];
+#define PTS(i) if (blockIdx.x == 0 && threadIdx.x == 0) g_ts[i] = clock64();
+#else
+#define PTS(i)
+#endif
+static constexpr int kRld = 66;   // staging row stride: even (16-byte rows for cp.async / LDS.128), 66*8 B spreads the banks
+static constexpr int kPanelSmem = (256 * kRld + 2 * 128 + 80 + 80 + 64) * (int)sizeof(double);
 
-// One column of the lockstep elimination.  The 64 columns are processed as 4 blocks of 16: inside a block
-// the step index C is a compile-time constant (a[] stays in registers, static indexing), between blocks
-// the registers are rotated by 16 so that the SAME 16-step code runs four times (a fully unrolled
-// 64-step version is ~7000 straight-line instructions and is instruction-fetch bound).  Register q holds
-// global column cbase + q; registers past column 63 hold don't-care values.
+// 1 / d without the IEEE fix-up of the compiler's division: MUFU seed (2^-23) and one third-order step,
+// e = 1 - d x0, x1 = x0 (1 + e + e^2): 4 dependent operations instead of 7, result within ~1 ulp.
+__device__ __forceinline__ double rcp_fast(double d) {
+  double x0;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x0) : "d"(d));
+  const double e = fma(-d, x0, 1.0);
+  const double t = fma(e, e, e);
+  return fma(x0, t, x0);
+}
+
+// One column of the lockstep elimination.  The serial chain of the whole factorisation is
+//   r_c (reciprocal pivot) -> pivot d_{c+1} -> r_{c+1},
+// and fp64 latency on this part is ~40 cycles per dependent operation, so the chain is kept as short as possible:
+// the row that owns the next pivot forms it as d_{c+1} = a[c+1] - a[c]^2 r_c with a[c]^2 computed one step early
+// (off the chain), i.e. ONE fma after r_c arrives, then the 4-operation reciprocal.  It is written without a branch
+// (all diagonal rows compute it, one stores it) so that the compiler can interleave it with the bulk update.
 template <int C>
 struct ElimStep {
-  static __device__ __forceinline__ void run(double (&a)[64], double* col, const double* inv_rd, double* inv,
-                                             double* dv, int tid, int cbase) {
+  static __device__ __forceinline__ void run(double (&a)[64], double& qq, double* col, double* inv, double* dv,
+                                             int tid) {
     __syncthreads();
-    const int c = cbase + C;                              // global column
-    const double* cc = col + (c & 1) * 128 + cbase;       // cc[q] = entry (cbase+q, c) of the diagonal block
-    const double m = a[C] * inv_rd[c];
+    const double* cc = col + (C & 1) * 128;               // cc[q] = entry (q, C) of the diagonal block
+    const double r = inv[C];
+    if constexpr (C + 1 < 64) {
+      if (tid < 64) {
+        const double d = fma(-qq, r, a[C + 1]);           // the pivot d_{C+1} if this is row C+1
+        const double rn = rcp_fast(d);
+        if (tid == C + 1) { inv[C + 1] = rn; dv[C + 1] = d; }
+      }
+    }
+    const double m = a[C] * r;
     if constexpr (C + 1 < 64) {
       a[C + 1] = fma(-m, cc[C + 1], a[C + 1]);
-      if (tid < 64 && tid >= c + 1) {                     // diagonal rows publish column c+1
-        col[((c + 1) & 1) * 128 + tid] = a[C + 1];
-        if (tid == c + 1) { inv[c + 1] = 1.0 / a[C + 1]; dv[c + 1] = a[C + 1]; }
-      }
+      qq = a[C + 1] * a[C + 1];
+      if (tid < 64 && tid >= C + 1) col[((C + 1) & 1) * 128 + tid] = a[C + 1];   // diagonal rows publish column C+1
     }
     constexpr int Q0 = C + 2;
     constexpr int QA = (Q0 & 1) ? Q0 + 1 : Q0;
@@ -227,27 +251,25 @@ struct ElimStep {
       a[q] = fma(-m, w.x, a[q]);
       a[q + 1] = fma(-m, w.y, a[q + 1]);
     }
-    ElimStep<C + 1>::run(a, col, inv_rd, inv, dv, tid, cbase);
+    ElimStep<C + 1>::run(a, qq, col, inv, dv, tid);
   }
 };
-static constexpr int kRot = 64;  // columns per unrolled block (measured: 64 = 4.0 ms/solve, 16 = 4.5 ms at n = 5994)
 template <>
-struct ElimStep<kRot> {
-  static __device__ __forceinline__ void run(double (&)[64], double*, const double*, double*, double*, int, int) {}
+struct ElimStep<64> {
+  static __device__ __forceinline__ void run(double (&)[64], double&, double*, double*, double*, int) {}
 };
 
 __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__ A, int n, int j0, int jb,
                                                             int* __restrict__ info,
                                                             const int* __restrict__ hi64,
-                                                            int* __restrict__ arrive) {
+                                                            int* __restrict__ arrive, int vec) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* R = reinterpret_cast<double*>(smem_raw);  // [256][65] row staging
-  double* col = R + 256 * 65;                        // [2][128]  published column (double-buffered, padded)
+  double* R = reinterpret_cast<double*>(smem_raw);  // [256][kRld] row staging
+  double* col = R + 256 * kRld;                      // [2][128]  published column (double-buffered, padded)
   double* inv = col + 256;                           // [80]      1 / pivot
   double* dv = inv + 80;                             // [80]      pivots
   double* rs = dv + 80;                              // [64]      1 / sqrt(pivot)
   const int tid = threadIdx.x;
-  const bool diag = tid < 64;
   const int trow0 = j0 + jb + blockIdx.x * PR;       // first trailing row of this CTA
   // envelope: rows past hi64[] have no entry in these columns (and get none); the CTA holding the rhs row stays
   if (hi64 != nullptr && blockIdx.x != 0 && trow0 > hi64[(j0 + jb - 1) >> 6] && trow0 + PR <= n) {
@@ -257,24 +279,33 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
   auto row_of = [&](int t) { return t < 64 ? j0 + t : trow0 + t - 64; };
   auto row_ok = [&](int t) { return t < 64 ? t < jb : (trow0 + t - 64) <= n; };
 
-  double a[64];
-  // stage: all 64 loads of a thread are in flight at once (a[] doubles as the landing zone); a warp-instruction
-  // reads 256 contiguous bytes of one row.  Diagonal block: lower triangle only, partial block padded with I.
-  const int tq = tid >> 6, tc = tid & 63;
-#pragma unroll
-  for (int q = 0; q < 64; q++) {
-    const int t = q * 4 + tq;
-    a[q] = (row_ok(t) && tc < jb) ? A[(size_t)row_of(t) * n + j0 + tc] : 0.0;
-  }
-#pragma unroll
-  for (int q = 0; q < 64; q++) {
-    const int t = q * 4 + tq;
-    double x = a[q];
-    if (t < 64) {
-      if (tc > t) x = 0.0;
-      if (t >= jb && tc == t) x = 1.0;
+  PTS(0)
+  // stage: a warp-instruction moves 512 contiguous bytes of one row (16 B per lane) straight into shared memory
+  const int sr = tid >> 5, sc = (tid & 31) * 2;      // row within a group of 8, column pair
+  if (vec && jb == 64) {
+#pragma unroll 8
+    for (int q = 0; q < 32; q++) {
+      const int t = q * 8 + sr;
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(R + t * kRld + sc);
+      if (row_ok(t)) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(A + (size_t)row_of(t) * n + j0 + sc));
+      } else {
+        *reinterpret_cast<double2*>(R + t * kRld + sc) = make_double2(0.0, 0.0);
+      }
     }
-    R[t * 65 + tc] = x;
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  } else {
+    for (int q = 0; q < 32; q++) {
+      const int t = q * 8 + sr;
+      double2 v = make_double2(0.0, 0.0);
+      if (row_ok(t)) {
+        const double* src = A + (size_t)row_of(t) * n + j0 + sc;
+        if (sc < jb) v.x = src[0];
+        if (sc + 1 < jb) v.y = src[1];
+      }
+      *reinterpret_cast<double2*>(R + t * kRld + sc) = v;
+    }
   }
   if (tid < 128) { col[tid] = 0.0; col[128 + tid] = 0.0; }
   if (tid < 80) inv[tid] = 0.0;
@@ -282,203 +313,67 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
   // every CTA has now read the un-factorised diagonal block; CTA 0 overwrites it at the end, but only after all
   // CTAs of this launch have checked in here (a CTA may be scheduled late when the SMs are busy with the SYRK)
   if (tid == 0 && blockIdx.x != 0) atomicAdd(&arrive[j0 >> 6], 1);
+  double a[64];
 #pragma unroll
-  for (int c = 0; c < 64; c++) a[c] = R[tid * 65 + c];
-  if (diag) {
-    col[tid] = a[0];
-    if (tid == 0) { inv[0] = 1.0 / a[0]; dv[0] = a[0]; }
+  for (int c = 0; c < 64; c += 2) {
+    const double2 v = *reinterpret_cast<const double2*>(R + tid * kRld + c);
+    a[c] = v.x; a[c + 1] = v.y;
   }
-#pragma unroll 1
-  for (int cb = 0; cb < 64 / kRot; cb++) {
-    ElimStep<0>::run(a, col, inv, inv, dv, tid, cb * kRot);
-    if (kRot < 64) {
-      __syncthreads();
+  if (tid < 64) {   // diagonal block: lower triangle only, partial block padded with I
 #pragma unroll
-      for (int i = 0; i < kRot; i++) R[tid * 65 + cb * kRot + i] = a[i];
-#pragma unroll
-      for (int i = 0; i < 64 - kRot; i++) a[i] = a[i + kRot];
-#pragma unroll
-      for (int i = 64 - kRot; i < 64; i++) a[i] = 0.0;
+    for (int c = 0; c < 64; c++) {
+      if (c > tid) a[c] = 0.0;
+      if (tid >= jb && c == tid) a[c] = 1.0;
     }
+    col[tid] = a[0];
+    if (tid == 0) { inv[0] = rcp_fast(a[0]); dv[0] = a[0]; }
   }
+  double qq = a[0] * a[0];
+  PTS(1)
+  ElimStep<0>::run(a, qq, col, inv, dv, tid);
   __syncthreads();
+  PTS(2)
   if (tid < 64) {
     const double d = dv[tid];
     if (!(d > 0.0) && blockIdx.x == 0) *info = 1;
     rs[tid] = 1.0 / sqrt(d);
   }
   __syncthreads();
-  if (kRot == 64) {
 #pragma unroll
-    for (int c = 0; c < 64; c++) R[tid * 65 + c] = a[c] * rs[c];
-  } else {
-#pragma unroll 8
-    for (int c = 0; c < 64; c++) R[tid * 65 + c] *= rs[c];
-  }
+  for (int c = 0; c < 64; c += 2)
+    *reinterpret_cast<double2*>(R + tid * kRld + c) = make_double2(a[c] * rs[c], a[c + 1] * rs[c + 1]);
+  PTS(3)
   if (blockIdx.x == 0 && tid == 0) {
     volatile int* cnt = arrive + (j0 >> 6);
     while (*cnt < (int)gridDim.x - 1) {}
   }
   __syncthreads();
-#pragma unroll 16
-  for (int q = 0; q < 64; q++) {
-    const int t = q * 4 + tq;
-    if (!row_ok(t) || tc >= jb) continue;
-    if (t < 64 && (blockIdx.x != 0 || tc > t)) continue;   // the diagonal block is written once, lower part
-    A[(size_t)row_of(t) * n + j0 + tc] = R[t * 65 + tc];
-  }
-}
-
-// ------------------------------------------------------------------------------------------------
-// chol_panel2_kernel: same arithmetic as chol_panel_kernel, laid out for the shared-memory return path.
-// With one row per thread every DFMA needs its own broadcast operand from shared memory (8 B per lane per DFMA):
-// 256 rows x 2016 doubles = 4 MB per sub-panel through 128 B/clk = 32 k cycles, which is what the kernel took.
-//  * register tile 4 rows x 16 columns per thread, columns CYCLIC over the 4 lanes of a quad (lane k owns the
-//    columns == k mod 4): every operand read from shared memory feeds 4 DFMAs, all lanes have the same amount of
-//    work left at every step (no divergence), and the multipliers of the quad's 4 rows travel by shuffle.
-//  * producer / consumer split: the 64 diagonal rows (warps 0-1) run the pivot chain alone, synchronising with a
-//    64-thread named barrier, and publish every column of the diagonal block plus its reciprocal pivot (colS, one
-//    slot per column).  The 192 trailing rows (warps 2-7) never feed back into that chain: they take no barrier,
-//    poll a progress counter once per 8 columns and run 8+ columns behind.
-//  * no staging: a quad reads / writes 32 contiguous bytes of a row, so global loads and stores go straight
-//    between registers and memory at full sector efficiency (no transposition through shared memory).
-// ------------------------------------------------------------------------------------------------
-#ifndef PANEL_EXP
-#define PANEL_EXP 0
-#endif
-#if PANEL_EXP & 8
-__device__ long long g_ts[16];
-#define TS(i) if ((C == 30 || C == 31) && tid == 32) g_ts[(C - 30) * 4 + (i)] = clock64();
-#else
-#define TS(i)
-#endif
-static constexpr int kPanel2Smem = (64 * 64 + 64 + 64 + 64 + 8) * (int)sizeof(double);
-
-template <int C>
-struct ElimStep2 {
-  static __device__ __forceinline__ void run(double (&a)[4][16], double* colS, double* inv, double* dv,
-                                             volatile int* ready, int tid, int k) {
-    constexpr int kC = C & 3, jC = C >> 2;
-    if (tid < 64) {
-      asm volatile("bar.sync 1, 64;" ::: "memory");       // column C and inv[C] are complete
-      if (tid == 0) *ready = C + 1;
-      TS(0)
-    } else if ((C & 7) == 0) {
-      constexpr int need = C + 8 < 64 ? C + 8 : 64;
-      if (!(PANEL_EXP & 4)) while (*ready < need) {}
-      __threadfence_block();
+  if (vec && jb == 64) {
+#pragma unroll 8
+    for (int q = 0; q < 32; q++) {
+      const int t = q * 8 + sr;
+      if (!row_ok(t)) continue;
+      if (t < 64 && (blockIdx.x != 0 || sc > t)) continue;   // the diagonal block is written once, lower part
+      const double2 v = *reinterpret_cast<const double2*>(R + t * kRld + sc);
+      double* dst = A + (size_t)row_of(t) * n + j0 + sc;
+      if (t < 64 && sc + 1 > t) dst[0] = v.x;
+      else *reinterpret_cast<double2*>(dst) = v;
     }
-    const double* cc = colS + C * 64;                       // cc[q] = entry (q, C) of the diagonal block
-    const double iv = inv[C];
-    const int owner = (tid & 28) | kC;                      // lane of this quad that holds column C
-    double m[4];
+  } else {
+    for (int q = 0; q < 32; q++) {
+      const int t = q * 8 + sr;
+      if (!row_ok(t)) continue;
+      double* dst = A + (size_t)row_of(t) * n + j0 + sc;
 #pragma unroll
-    for (int i = 0; i < 4; i++) m[i] = shfl_f64(a[i][jC] * iv, owner);
-    TS(1)
-    if constexpr (C + 1 < 64) {
-      constexpr int k1 = (C + 1) & 3, j1 = (C + 1) >> 2;
-      if (k == k1) {                                        // column C+1 first: it carries the pivot chain
-        const double c1 = cc[C + 1];
-#pragma unroll
-        for (int i = 0; i < 4; i++) a[i][j1] = fma(-m[i], c1, a[i][j1]);
-        if (tid < 64) {
-          double* dst = colS + (C + 1) * 64 + (tid >> 2) * 4;
-          *reinterpret_cast<double2*>(dst) = make_double2(a[0][j1], a[1][j1]);
-          *reinterpret_cast<double2*>(dst + 2) = make_double2(a[2][j1], a[3][j1]);
-          if ((tid >> 2) == ((C + 1) >> 2)) {
-            const double d = a[(C + 1) & 3][j1];
-            inv[C + 1] = 1.0 / d;
-            dv[C + 1] = d;
-          }
-        }
+      for (int u = 0; u < 2; u++) {
+        const int c = sc + u;
+        if (c >= jb) continue;
+        if (t < 64 && (blockIdx.x != 0 || c > t)) continue;
+        dst[u] = R[t * kRld + c];
       }
     }
-    TS(2)
-    // boundary registers (column 4*jj + k may be <= C, or C+1 which is done): predicated
-    constexpr int jB0 = jC, jB1 = (C + 1) >> 2;
-    if (!((PANEL_EXP & 2) && tid < 64)) {
-#pragma unroll
-    for (int jj = jB0; jj <= jB1 && jj < 16; jj++) {
-      const int col = 4 * jj + k;
-      if (col > C + 1) {
-        const double w = cc[col];
-#pragma unroll
-        for (int i = 0; i < 4; i++) a[i][jj] = fma(-m[i], w, a[i][jj]);
-      }
-    }
-#pragma unroll
-    for (int jj = jB1 + 1; jj < 16; jj++) {
-      const double w = cc[4 * jj + k];
-#pragma unroll
-      for (int i = 0; i < 4; i++) a[i][jj] = fma(-m[i], w, a[i][jj]);
-    }
-    }
-    TS(3)
-    ElimStep2<C + 1>::run(a, colS, inv, dv, ready, tid, k);
   }
-};
-template <>
-struct ElimStep2<64> {
-  static __device__ __forceinline__ void run(double (&)[4][16], double*, double*, double*, volatile int*, int, int) {}
-};
-
-__global__ void __launch_bounds__(256, 1) chol_panel2_kernel(double* __restrict__ A, int n, int j0, int jb,
-                                                             int* __restrict__ info,
-                                                             const int* __restrict__ hi64) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* colS = reinterpret_cast<double*>(smem_raw);  // [64][64]  published columns
-  double* inv = colS + 64 * 64;                        // [64] 1 / pivot
-  double* dv = inv + 64;                               // [64] pivots
-  double* rs = dv + 64;                                // [64] 1 / sqrt(pivot)
-  volatile int* ready = reinterpret_cast<volatile int*>(rs + 64);
-  const int tid = threadIdx.x, k = tid & 3;
-  const int trow0 = j0 + jb + blockIdx.x * PR;
-  if (hi64 != nullptr && blockIdx.x != 0 && trow0 > hi64[(j0 + jb - 1) >> 6] && trow0 + PR <= n) return;
-  const int t0 = (tid >> 2) * 4;                       // first of this quad's 4 rows (0..63 diagonal, 64.. trailing)
-  const bool diag = tid < 64;
-  double a[4][16];
-#pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const int t = t0 + i;
-    const int row = diag ? j0 + t : trow0 + t - 64;
-    const bool ok = diag ? t < jb : row <= n;
-    const double* src = A + (size_t)row * n + j0 + k;
-#pragma unroll
-    for (int jj = 0; jj < 16; jj++) {
-      const int col = 4 * jj + k;
-      a[i][jj] = (ok && col < jb && (!diag || col <= t)) ? src[4 * jj] : 0.0;
-      if (diag && t >= jb && col == t) a[i][jj] = 1.0;   // partial block padded with I
-    }
-  }
-  if (tid == 0) *ready = 0;
-  if (diag && k == 0) {
-    *reinterpret_cast<double2*>(colS + t0) = make_double2(a[0][0], a[1][0]);
-    *reinterpret_cast<double2*>(colS + t0 + 2) = make_double2(a[2][0], a[3][0]);
-    if (tid == 0) { inv[0] = 1.0 / a[0][0]; dv[0] = a[0][0]; }
-  }
-  __syncthreads();
-  if ((PANEL_EXP & 1) && tid >= 64) return;
-  ElimStep2<0>::run(a, colS, inv, dv, ready, tid, k);
-  if (diag) {
-    asm volatile("bar.sync 1, 64;" ::: "memory");
-    const double d = dv[tid];
-    if (!(d > 0.0) && blockIdx.x == 0) *info = 1;
-    rs[tid] = 1.0 / sqrt(d);
-  }
-  __syncthreads();
-  if (diag && blockIdx.x != 0) return;                  // the diagonal block is written once (CTA 0), lower part
-#pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const int t = t0 + i;
-    const int row = diag ? j0 + t : trow0 + t - 64;
-    const bool ok = diag ? t < jb : row <= n;
-    double* dst = A + (size_t)row * n + j0 + k;
-#pragma unroll
-    for (int jj = 0; jj < 16; jj++) {
-      const int col = 4 * jj + k;
-      if (ok && col < jb && (!diag || col <= t)) dst[4 * jj] = a[i][jj] * rs[col];
-    }
-  }
+  PTS(4)
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -890,7 +785,6 @@ extern "C" int droid_chol_solve_env_f64(double* A, double* b, int n, const int* 
   constexpr int kSyrk64 = (2 * 2 * 16 * (64 + 2) + 64 * 64) * (int)sizeof(double);
   if (!attr2) {
     cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmem);
-    cudaFuncSetAttribute(chol_panel2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanel2Smem);
     cudaFuncSetAttribute(chol_bwd_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem);
     cudaFuncSetAttribute(chol_syrk_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
     cudaFuncSetAttribute(chol_syrk_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
@@ -934,6 +828,7 @@ extern "C" int droid_chol_solve_env_f64(double* A, double* b, int n, const int* 
   auto lookahead_ok = [&](int J) {
     const int r0 = J + PB;
     if (!vec || r0 >= n) return false;
+    if (hi64 != nullptr && getenv("DROID_ENV_LOOKAHEAD") == nullptr) return false;
     return n + 1 - r0 >= 4 * PB;   // at least a few tiles of trailing matrix left to overlap with
   };
   bool on_side = lookahead_ok(0);
@@ -953,7 +848,7 @@ extern "C" int droid_chol_solve_env_f64(double* A, double* b, int n, const int* 
     for (int j0 = J; j0 < J + kb; j0 += NB) {
       const int jb = (J + kb - j0) < NB ? (J + kb - j0) : NB;
       const int rem_rows = n + 1 - (j0 + jb);  // >= 1 (the rhs row)
-      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PR - 1) / PR, 256, kPanelSmem, ps>>>(A, n, j0, jb, info_dev, hi64, arrive);
+      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PR - 1) / PR, 256, kPanelSmem, ps>>>(A, n, j0, jb, info_dev, hi64, arrive, vec ? 1 : 0);
       const int rest = J + kb - (j0 + jb);     // columns of this outer panel still to factorise
       if (rest > 0) {
         // rank-64 update of the panel's remaining columns only (64x64 tiles of one block column, all SMs)

@@ -1,0 +1,397 @@
+// Schur complement of the per-pixel inverse depths on the tensor cores (tcgen05 / TMEM), sm_100a.
+// Replaces, for source frames with at most 20 outgoing edges, the CUDA-core Gram product of ba_schur_kernel (ba.cu)
+// and with it the reference's EEt6x6 / Ev6x1 kernels (src/droid_kernels.cu:1001-1091).
+//
+// For one source frame k with targets j_1..j_deg the Schur terms are
+//     S[a,b] = sum_p E_a[p] Q[p] E_b[p]^T          (6x6 blocks, a,b in {k, j_1..j_deg})
+//     v_S[a] = sum_p E_a[p] Q[p] w[p]
+// i.e. with F[r][p] = sqrt(Q[p]) * E[r][p] for the R = 6 (deg+1) rows and one extra row F[R][p] = sqrt(Q[p]) w[p]:
+//     G = F F^T  (M x M, M = R + 1 <= 128, K = number of pixels);  S = G[:R,:R],  v_S = G[R,:R].
+// That is a GEMM with K = 3072 .. 5760, which belongs on the tensor pipe.  fp32 accuracy needs two things:
+//  * the 3xTF32 split  F = F_hi + F_lo (both rounded to tf32),  G = F_hi F_hi^T + F_hi F_lo^T + F_lo F_hi^T;
+//  * SHORT accumulation chains: the TMEM accumulator truncates, so the error of a sum grows linearly with the number
+//    of chained MMAs (measured: 1.8e-6 relative over 1152 MMAs, 2.6e-7 over 24).  Every chunk of 32 pixels (12 MMAs)
+//    therefore starts a fresh accumulator, and the chunks are summed with ordinary fp32 adds in registers.
+//
+// Warp roles (512 threads, one CTA per SM, CTA = (pixel slab, source frame)):
+//   warps 0-7   builders: recompute the Jacobians of every (pixel, edge) from (target, weight, disp) like
+//               ba_schur_kernel, stage the chunk's F as plain fp32 in shared memory, then re-pack it (split + 16-byte
+//               stores) into the canonical MN-major UMMA layout for 32-bit operands (SWIZZLE_128B_BASE32B);
+//   warp 13     one thread issues the 12 tcgen05.mma of a chunk into TMEM buffer (chunk & 1);
+//   warps 8-11, 14-15  drainers: TMEM -> registers, fp32 accumulation of half a row of G per thread, and at the end the fp64
+//               atomics into the dense reduced system (same block placement rules as flush_block in ba.cu).
+// Operand stages, fp32 staging and TMEM accumulators are all double-buffered: building chunk c+1, the MMAs of chunk c
+// and the drain of chunk c-1 overlap.
+#include <cstdint>
+
+#include "ba_lin.cuh"
+#include "common.cuh"
+
+namespace droid {
+namespace stc {
+
+static constexpr int kBuild = 256;
+static constexpr int kThreads = 512;             // 8 builder warps, 6 drain warps, 1 MMA warp, 1 spare (128 registers)
+static constexpr int kT = 32;                    // pixels per chunk
+static constexpr int kLbo = kT * 128;            // bytes between consecutive 32-row atoms (4 KB)
+static constexpr int kHalf = 4 * kLbo;           // one operand array (F_hi or F_lo) of one stage: 16 KB
+static constexpr int kStage = 2 * kHalf;
+static constexpr int kELd = 132;                 // fp32 staging row stride (floats): 16-byte rows, spreads the banks
+static constexpr int kTB = 128;                   // pixels per build pass (4 MMA chunks): long enough to pipeline the loads
+static constexpr int kEBytes = kTB * kELd * 4;
+static constexpr int kMetaOff = 2 * kStage + kEBytes;
+static constexpr int kSmem = kMetaOff + 4096 + 1024;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+  } while (!done);
+}
+// same, for the warps that only wait for other warps' work (MMA issuer, drainers): back off between polls so that the
+// polling does not take issue slots from the builder warps on the same scheduler
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+    if (done) break;
+    __nanosleep(100);
+  }
+}
+// shared-memory matrix descriptor: MN-major 32-bit operands use the SWIZZLE_128B_BASE32B layout (type 1; the plain
+// 128-byte swizzle yields zeros for tf32 MN-major): 128-byte rows = 32 consecutive rows of F for one pixel, the four
+// 32-byte chunks of a row XOR-ed with (pixel & 3), atoms of 4 pixels (512 B).
+// LBO = distance between 128-byte-wide atoms along M, SBO = distance between 4-pixel groups along K.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(lbo >> 4) << 16;
+  d |= (uint64_t)(512 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)1 << 61;
+  return d;
+}
+// instruction descriptor, kind::tf32: D = f32, A = B = tf32, both MN-major, M = N = 128
+__device__ __forceinline__ uint32_t umma_idesc() {
+  return (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(128 >> 3) << 17) |
+         ((uint32_t)(128 >> 4) << 24);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr) : "memory");
+#pragma unroll
+  for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// round-to-nearest (ties away) to tf32 = what cvt.rna.tf32.f32 does, with two full-rate integer instructions
+// (the conversion instruction runs at a fraction of the ALU rate and made the pack pass cost as much as the MMAs)
+__device__ __forceinline__ uint32_t tf32_rna(float x) { return (__float_as_uint(x) + 0x1000u) & 0xFFFFE000u; }
+
+__global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
+    const float* __restrict__ disps, const float* __restrict__ intrinsics,
+    const float* __restrict__ targets, const float* __restrict__ weights,
+    const int64_t* __restrict__ jj, const float* __restrict__ gij, int* __restrict__ status,
+    const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
+    const float* __restrict__ Qi, const float* __restrict__ Wi, double* __restrict__ A,
+    double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P, int n_eta, int frame_lo,
+    int frame_hi, const int* __restrict__ ppos) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  const int m = blockIdx.y;
+  const int Mk = status[1];
+  if (m >= Mk || m >= n_eta) return;
+  const int k = kx[m];
+  if (k < frame_lo || k >= frame_hi) return;
+  const int p0 = blockIdx.x * slab;
+  const int p1 = min(HW, p0 + slab);
+  if (p0 >= p1) return;
+  const int e0 = eptr[m], e1 = eptr[m + 1];
+  const int deg = e1 - e0;
+  const int D = deg + 1;
+  if (deg == 0 || D > kSchurTcMaxD) return;     // nothing to do / handled by ba_schur_kernel
+  const int R = 6 * D;                   // rows of E; row R of F carries sqrt(Q) w
+  const int M = R + 1;
+
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  float* E32 = reinterpret_cast<float*>(smem + 2 * kStage);          // [kTB][kELd]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kMetaOff);
+  uint64_t* full = bars;        // [2]  operands of a chunk in place      (256 builder arrivals)
+  uint64_t* empty = bars + 2;   // [2]  operands consumed                 (tcgen05.commit)
+  uint64_t* gdone = bars + 4;   // [2]  accumulator of a chunk complete   (tcgen05.commit)
+  uint64_t* tfree = bars + 6;   // [2]  accumulator drained               (128 drainer arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  int* s_e = reinterpret_cast<int*>(bars + 10);
+  int* s_jx = s_e + 24;
+  int* pose = s_jx + 24;
+  float* s_g = reinterpret_cast<float*>(bars + 10 + 64);   // 16-byte aligned: [deg][8]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int i = 0; i < 2; i++) {
+      mbar_init(full + i, kBuild);
+      mbar_init(empty + i, 1);
+      mbar_init(gdone + i, 1);
+      mbar_init(tfree + i, 192);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 13) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  // staging columns >= M are never written and must read as zero
+  for (int i = tid; i < kEBytes / 16; i += kThreads) reinterpret_cast<uint4*>(E32)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < deg; i += kThreads) {
+    const int e = eidx[e0 + i];
+    s_e[i] = e;
+    s_jx[i] = (int)jj[e];
+  }
+  for (int i = tid; i < deg * 8; i += kThreads) s_g[i] = gij[(size_t)eidx[e0 + (i >> 3)] * 8 + (i & 7)];
+  for (int d = tid; d < D; d += kThreads) {
+    int pz = (d == 0) ? k - t0 : (int)jj[eidx[e0 + d - 1]] - t0;
+    if (pz < 0 || pz >= P) pz = -1;
+    else if (ppos != nullptr) pz = ppos[pz];
+    pose[d] = pz;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const int nchunk = (p1 - p0 + kT - 1) / kT;
+
+  if (warp == 13) {
+    if (lane == 0) {
+      // ---------------- MMA issuer ----------------
+      const uint32_t idesc = umma_idesc();
+      for (int c = 0; c < nchunk; c++) {
+        const int s = c & 1;
+        mbar_wait_relaxed(full + s, (c >> 1) & 1);
+        if (c >= 2) mbar_wait_relaxed(tfree + s, ((c >> 1) - 1) & 1);     // accumulator (c & 1) drained
+        tc_fence_after();
+        const uint32_t hi = smem_u32(smem + s * kStage), lo = hi + kHalf;
+        const uint32_t d_t = tmem + s * 128;
+#pragma unroll
+        for (int kk = 0; kk < kT / 8; kk++) {
+          const uint64_t f_hi = umma_desc(hi + kk * 1024, kLbo), f_lo = umma_desc(lo + kk * 1024, kLbo);
+          umma_tf32(d_t, f_hi, f_hi, idesc, kk > 0 ? 1u : 0u);
+          umma_tf32(d_t, f_hi, f_lo, idesc, 1u);
+          umma_tf32(d_t, f_lo, f_hi, idesc, 1u);
+        }
+        umma_commit(empty + s);
+        umma_commit(gdone + s);
+      }
+    }
+  } else if (warp < 8) {
+    // ---------------- F builders ----------------
+    // A build pass covers kTB = 128 pixels (two threads per pixel, each taking every other edge, inputs of the next
+    // edge prefetched), then the four 32-pixel chunks of the pass are packed and handed to the MMA issuer.
+    const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
+    const int pl = tid >> 1, g = tid & 1;
+    const float* __restrict__ dmap = disps + (size_t)k * HW;
+    float* Erow = E32 + pl * kELd;
+    const int npass = (p1 - p0 + kTB - 1) / kTB;
+    float n_tu = 0.f, n_tv = 0.f, n_wu = 0.f, n_wv = 0.f, n_dp = 0.f, n_q = 0.f, n_w = 0.f;
+    auto fetch = [&](int i, int p, bool ok) {
+      if (ok) {
+        const size_t base = (size_t)s_e[i] * 2 * HW + p;
+        n_tu = __ldg(targets + base); n_tv = __ldg(targets + base + HW);
+        n_wu = __ldg(weights + base); n_wv = __ldg(weights + base + HW);
+      }
+    };
+    auto fetch_pix = [&](int p, bool ok) {
+      n_dp = ok ? dmap[p] : 0.f;
+      n_q = ok ? Qi[(size_t)m * HW + p] : 0.f;
+      n_w = ok ? Wi[(size_t)m * HW + p] : 0.f;
+    };
+    fetch_pix(p0 + pl, p0 + pl < p1);
+    if (g < deg) fetch(g, p0 + pl, p0 + pl < p1);
+    for (int ps = 0; ps < npass; ps++) {
+      const int p = p0 + ps * kTB + pl;
+      const bool valid = p < p1;
+      const float dp = n_dp, sq = sqrtf(n_q), wv_pix = n_w;
+      float Ei[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int i = g; i < deg; i += 2) {
+        const int jx = s_jx[i];
+        const float tu = n_tu, tv = n_tv, wu = n_wu, wv = n_wv;
+        if (i + 2 < deg) fetch(i + 2, p, valid);
+        else {                                   // last edge of this pixel: start on the next pass
+          const int pn = p + kTB;
+          fetch_pix(pn, pn < p1);
+          if (g < deg) fetch(g, pn, pn < p1);
+        }
+        SE3 gg;
+        {
+          const float4 ga = *reinterpret_cast<const float4*>(s_g + 8 * i);
+          const float4 gb = *reinterpret_cast<const float4*>(s_g + 8 * i + 4);
+          gg.t[0] = ga.x; gg.t[1] = ga.y; gg.t[2] = ga.z;
+          gg.q[0] = ga.w; gg.q[1] = gb.x; gg.q[2] = gb.y; gg.q[3] = gb.z;
+        }
+        PixLin L;
+        linearise(gg, K, wd, valid ? p : p0, dp, tu, tv, wu, wv, jx == k, L);
+        const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
+        float ej[6];
+#pragma unroll
+        for (int n = 0; n < 6; n++) {
+          float ei_n = au * L.Ji_u[n];
+          ei_n += av * L.Ji_v[n];
+          Ei[n] += ei_n;
+          float ej_n = au * L.Jj_u[n];
+          ej_n += av * L.Jj_v[n];
+          ej[n] = valid ? sq * ej_n : 0.f;
+        }
+        float2* dst = reinterpret_cast<float2*>(Erow + 6 * (i + 1));
+        dst[0] = make_float2(ej[0], ej[1]); dst[1] = make_float2(ej[2], ej[3]); dst[2] = make_float2(ej[4], ej[5]);
+      }
+      if (deg == 1 && g == 1) {                  // a thread without edges still has to move its prefetch along
+        const int pn = p + kTB;
+        fetch_pix(pn, pn < p1);
+      }
+      // the source pose's rows: sum over the two threads of this pixel
+#pragma unroll
+      for (int n = 0; n < 6; n++) Ei[n] += __shfl_xor_sync(0xffffffffu, Ei[n], 1);
+      if (g == 0) {
+#pragma unroll
+        for (int n = 0; n < 6; n++) Erow[n] = valid ? sq * Ei[n] : 0.f;
+      } else {
+        Erow[R] = valid ? sq * wv_pix : 0.f;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");      // pass staged
+      // ---- pack: 8 consecutive rows of one pixel = one 32-byte unit of the UMMA layout; 2 units per thread and chunk
+      for (int sub = 0; sub < kTB / kT; sub++) {
+        const int c = ps * (kTB / kT) + sub;
+        if (c >= nchunk) break;
+        const int s = c & 1;
+        if (c >= 2) mbar_wait(empty + s, ((c >> 1) - 1) & 1);
+        unsigned char* stage = smem + s * kStage;
+        const float* Es = E32 + sub * (kT * kELd);
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+          const int task = tid + u * kBuild;          // 512 tasks = 32 pixels x 16 row groups
+          const int px = task & 31, rg = task >> 5;
+          const float4 x0 = *reinterpret_cast<const float4*>(Es + px * kELd + 8 * rg);
+          const float4 x1 = *reinterpret_cast<const float4*>(Es + px * kELd + 8 * rg + 4);
+          uint4 h0, h1, l0, l1;
+          h0.x = tf32_rna(x0.x); h0.y = tf32_rna(x0.y); h0.z = tf32_rna(x0.z); h0.w = tf32_rna(x0.w);
+          h1.x = tf32_rna(x1.x); h1.y = tf32_rna(x1.y); h1.z = tf32_rna(x1.z); h1.w = tf32_rna(x1.w);
+          l0.x = tf32_rna(x0.x - __uint_as_float(h0.x)); l0.y = tf32_rna(x0.y - __uint_as_float(h0.y));
+          l0.z = tf32_rna(x0.z - __uint_as_float(h0.z)); l0.w = tf32_rna(x0.w - __uint_as_float(h0.w));
+          l1.x = tf32_rna(x1.x - __uint_as_float(h1.x)); l1.y = tf32_rna(x1.y - __uint_as_float(h1.y));
+          l1.z = tf32_rna(x1.z - __uint_as_float(h1.z)); l1.w = tf32_rna(x1.w - __uint_as_float(h1.w));
+          const int off = (rg >> 2) * kLbo + px * 128 + (((rg & 3) ^ (px & 3)) << 5);
+          *reinterpret_cast<uint4*>(stage + off) = h0;
+          *reinterpret_cast<uint4*>(stage + off + 16) = h1;
+          *reinterpret_cast<uint4*>(stage + kHalf + off) = l0;
+          *reinterpret_cast<uint4*>(stage + kHalf + off + 16) = l1;
+        }
+        fence_async_smem();
+        mbar_arrive(full + s);
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");      // staging buffer free for the next pass
+    }
+  } else if (warp != 12) {
+    // ---------------- drainers: half a row of G per thread (TMEM lane quarter = warp % 4) ----------------
+    // warps 8-11 take columns 0-63 of quarters 0-3, warps 14-15 columns 64-127 of quarters 2-3 (columns <= row only)
+    const int qd = warp & 3, hh = warp >> 3 & (warp >> 2) & 1;
+    const int r = 32 * qd + lane;
+    float acc[64];
+#pragma unroll
+    for (int j = 0; j < 64; j++) acc[j] = 0.f;
+    for (int c = 0; c < nchunk; c++) {
+      const int s = c & 1;
+      mbar_wait_relaxed(gdone + s, (c >> 1) & 1);
+      tc_fence_after();
+      {
+        const uint32_t taddr = tmem + s * 128 + 64 * hh + ((uint32_t)(32 * qd) << 16);
+#pragma unroll
+        for (int part = 0; part < 4; part++) {
+          float v[16];
+          tmem_ld16(taddr + 16 * part, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; j++) acc[16 * part + j] += v[j];
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(tfree + s);
+    }
+    // ---- flush row r (columns <= r) with fp64 atomics
+    const int n6 = 6 * P;
+    if (r <= R) {
+      const int rb = r / 6, n = r - 6 * rb;
+      const int pa = r < R ? pose[rb] : 0;
+#pragma unroll
+      for (int j = 0; j < 64; j++) {
+        const int c = 64 * hh + j;
+        if (c > r || c >= R) continue;
+        const int cb = c / 6, mm = c - 6 * cb;
+        const int pb = pose[cb];
+        if (pb < 0) continue;
+        const double val = -(double)acc[j];
+        if (r == R) { atomicAdd(&bvec[6 * pb + mm], val); continue; }       // v_S
+        if (pa < 0) continue;
+        if (pa > pb) atomicAdd(&A[(size_t)(6 * pa + n) * n6 + 6 * pb + mm], val);
+        else if (pa < pb) atomicAdd(&A[(size_t)(6 * pb + mm) * n6 + 6 * pa + n], val);
+        else if (rb == cb) atomicAdd(&A[(size_t)(6 * pa + n) * n6 + 6 * pa + mm], val);   // c <= r => mm <= n
+        else atomicAdd(&A[(size_t)(6 * pa + max(n, mm)) * n6 + 6 * pa + min(n, mm)], n == mm ? 2.0 * val : val);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 13) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256) : "memory");
+  }
+}
+
+}  // namespace stc
+
+int launch_schur_tc(const float* disps, const float* intrinsics, const float* targets, const float* weights,
+                    const int64_t* jj, const float* gij, int* status, const int* kx, const int* eptr, const int* eidx,
+                    const float* Qi, const float* Wi, double* A, double* bvec, int HW, int wd, int slab, int S, int t0,
+                    int P, int n_eta, int frame_lo, int frame_hi, const int* ppos, cudaStream_t st) {
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(stc::ba_schur_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, stc::kSmem);
+    attr = true;
+  }
+  DROID_LAUNCH stc::ba_schur_tc_kernel<<<dim3(S, n_eta), stc::kThreads, stc::kSmem, st>>>(
+      disps, intrinsics, targets, weights, jj, gij, status, kx, eptr, eidx, Qi, Wi, A, bvec, HW, wd, slab, t0, P, n_eta,
+      frame_lo, frame_hi, ppos);
+  return check_launch();
+}
+
+}  // namespace droid
