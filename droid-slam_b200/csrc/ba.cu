@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(1024) ba_prep_kernel(const int64_t* __restrict
                                                        const int64_t* __restrict__ jj, int n_edges,
                                                        int nbuf, int n_eta, int t0, int t1,
                                                        int* status, int* kmap, int* kx, int* eptr,
-                                                       int* eidx, int* fill) {
+                                                       int* eidx, int* fill, int clear_sig) {
   __shared__ int s_scan[1024];
   __shared__ int s_carry;
   __shared__ int s_bad;
@@ -176,6 +176,7 @@ __global__ void __launch_bounds__(1024) ba_prep_kernel(const int64_t* __restrict
     status[0] = st;
     status[1] = M;
     status[2] = 0;
+    if (clear_sig) status[8] = 0;   // this call may overwrite the cached pose order of a larger system (see ba_order_kernel)
   }
 }
 
@@ -221,7 +222,8 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
                                                         const int64_t* __restrict__ jj, int n_edges, int nbuf,
                                                         int t0, int P, const int* __restrict__ kmap,
                                                         int* __restrict__ ppos, int* __restrict__ first,
-                                                        int* __restrict__ scr) {
+                                                        int* __restrict__ scr, int* __restrict__ sig, int lay0,
+                                                        int lay1) {
   int* pos = scr;              // [P] BFS position of free pose f, -1 = not placed yet
   int* cur = pos + P;          // [P] current frontier flags
   int* cand = cur + P;         // [P] next frontier flags; later the envelope of the BFS order
@@ -233,6 +235,31 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
   __shared__ unsigned long long s_prof[2];
   const int tid = threadIdx.x;
   auto valid = [&](long long i, long long j) { return i >= 0 && i < nbuf && j >= 0 && j < nbuf; };
+  // The order depends only on the edge list.  The backend calls ba() a dozen times on the same graph
+  // (droid_backend.py: `for itr in range(steps)`), so the result is kept in the workspace together with a signature
+  // (64-bit hash of the edges + every parameter that shapes the workspace layout); sig[] sits in the status block at
+  // a fixed offset and is cleared by any call that does not go through here.
+  __shared__ unsigned long long s_hash;
+  __shared__ int s_hit;
+  if (tid == 0) s_hash = 0ull;
+  __syncthreads();
+  {
+    unsigned long long h = 0ull;
+    for (int e = tid; e < n_edges; e += 1024) {
+      unsigned long long x = ((unsigned long long)ii[e] << 32) ^ (unsigned long long)(jj[e] & 0xffffffffll);
+      x ^= (unsigned long long)(e + 1) * 0x9E3779B97F4A7C15ull;
+      x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+      h += x;
+    }
+    atomicAdd(&s_hash, h);
+  }
+  __syncthreads();
+  const unsigned long long hsh = s_hash;
+  if (tid == 0)
+    s_hit = sig[0] == 0x0b200c0d && sig[1] == (int)(hsh & 0xffffffffull) && sig[2] == (int)(hsh >> 32) &&
+            sig[3] == n_edges && sig[4] == nbuf && sig[5] == t0 && sig[6] == P && sig[7] == lay0 && sig[9] == lay1;
+  __syncthreads();
+  if (s_hit) return;
   for (int f = tid; f < P; f += 1024) { pos[f] = -1; cur[f] = 0; cand[f] = 0; }
   for (int m = tid; m < nbuf; m += 1024) starhit[m] = 0;
   if (tid == 0) s_placed = 0;
@@ -316,6 +343,13 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
   const int* en = use_bfs ? cand : env;
   for (int f = tid; f < P; f += 1024) ppos[f] = use_bfs ? pos[f] : f;
   for (int r = tid; r < 6 * P; r += 1024) first[r] = 6 * en[r / 6];
+  __syncthreads();
+  if (tid == 0) {
+    sig[1] = (int)(hsh & 0xffffffffull); sig[2] = (int)(hsh >> 32);
+    sig[3] = n_edges; sig[4] = nbuf; sig[5] = t0; sig[6] = P; sig[7] = lay0; sig[9] = lay1;
+    __threadfence();
+    sig[0] = 0x0b200c0d;
+  }
 }
 
 __global__ void ba_edge_pose_kernel(const float* __restrict__ poses, const int64_t* __restrict__ ii,
@@ -955,7 +989,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   const int frame_lo = p->frame_lo, frame_hi = p->frame_hi > p->frame_lo ? p->frame_hi : 0x7fffffff;
 
   DROID_LAUNCH ba_prep_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->n_eta, p->t0, p->t1, w.status,
-                                     w.kmap, w.kx, w.eptr, w.eidx, w.fill);
+                                     w.kmap, w.kx, w.eptr, w.eidx, w.fill, (n6 > kCholSmallMax && p->n_edges > 0) ? 0 : 1);
   if (check_launch()) return DROID_ERR_CUDA;
   if (P == 0 || p->iterations == 0) return DROID_OK;
   // large systems: fill-reducing order + row envelope for the factorisation (small ones are solved by one CTA)
@@ -964,7 +998,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   const int* first = ordered ? w.first : nullptr;
   if (ordered)
     DROID_LAUNCH ba_order_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->t0, P, w.kmap, w.ppos, w.first,
-                                                     w.oscr);
+                                                     w.oscr, w.status + 8, p->ht * 65536 + p->wd, p->n_eta);
 
   static bool attr_set = false;
   if (!attr_set) {

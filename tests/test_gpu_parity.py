@@ -306,6 +306,36 @@ def test_ba_large_system_uses_blocked_cholesky(backends):
     assert rel(gdx, rdx) <= 3e-4 and rel(gdz, rdz) <= 1e-4
 
 
+def test_ba_pose_order_cache_follows_the_graph(backends):
+    """Large systems are factorised in a fill-reducing pose order that is cached in the workspace while the edge
+    list stays the same (the backend calls ba() a dozen times per graph).  Same graph twice -> same answer; the same
+    problem with its edges listed in a different sequence (different signature, so the order is recomputed) -> same
+    answer; a different graph of identical shape must not reuse the cached order."""
+    p = synth.make_ba_problem("C4", n_frames=60)
+    assert 6 * (p["t1"] - p["t0"]) > 156
+    a = run_ba(backends, p, 1, lm=1e-5, ep=1e-2)
+    b = run_ba(backends, p, 1, lm=1e-5, ep=1e-2)                       # cache hit
+    assert rel(b[2], a[2]) <= 1e-5 and rel(b[3], a[3]) <= 1e-5
+    q = dict(p)
+    perm = np.roll(np.arange(len(p["ii"])), 7)
+    for k in ("ii", "jj", "targets", "weights"):
+        q[k] = np.ascontiguousarray(p[k][perm])
+    c = run_ba(backends, q, 1, lm=1e-5, ep=1e-2)                       # same problem, new signature
+    assert rel(c[2], a[2]) <= 2e-4 and rel(c[3], a[3]) <= 1e-4
+    # different graph, same shapes: the loop-closure edges are re-pointed, which changes the coupling structure
+    r = dict(p)
+    jj2 = p["jj"].copy()
+    far = np.abs(p["ii"] - p["jj"]) > 4
+    jj2[far] = np.clip(p["ii"][far] + 3, 0, p["poses"].shape[0] - 1)
+    r["jj"] = jj2
+    ref = oracle_ba(r, 1, lm=1e-5, ep=1e-2)
+    d = run_ba(backends, r, 1, lm=1e-5, ep=1e-2)
+    assert backends.ba_status() == 0
+    assert rel(d[2], ref[2]) <= 3e-4 and rel(d[3], ref[3]) <= 1e-4
+    e = run_ba(backends, p, 1, lm=1e-5, ep=1e-2)                       # and back
+    assert rel(e[2], a[2]) <= 1e-5 and rel(e[3], a[3]) <= 1e-5
+
+
 @pytest.mark.parametrize("n", [1, 2, 3, 7, 8, 9, 31, 33, 64, 66, 97, 150, 155, 156, 157, 200, 777, 1200, 2431, 2500])
 def test_chol_solve(backends, n):
     rng = np.random.default_rng(n)
