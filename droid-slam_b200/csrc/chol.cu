@@ -828,7 +828,6 @@ extern "C" int droid_chol_solve_env_f64(double* A, double* b, int n, const int* 
   auto lookahead_ok = [&](int J) {
     const int r0 = J + PB;
     if (!vec || r0 >= n) return false;
-    if (hi64 != nullptr && getenv("DROID_ENV_LOOKAHEAD") == nullptr) return false;
     return n + 1 - r0 >= 4 * PB;   // at least a few tiles of trailing matrix left to overlap with
   };
   bool on_side = lookahead_ok(0);

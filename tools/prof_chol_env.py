@@ -33,7 +33,7 @@ inf = torch.zeros(1, dtype=torch.int32, device="cuda")
 wsb = int(B._lib.droid_chol_workspace_bytes(n)); ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 B.prof_enable(True); B.prof_read()
-for mode in ("env",):
+for mode in ("env", "dense"):
     ts = []
     for _ in range(4):
         buf[: n * n] = At.reshape(-1); buf[n * n:] = bt
