@@ -35,7 +35,8 @@ struct BaWs {
   int* eptr;       // [nbuf+1] CSR offsets over kx
   int* eidx;       // [n_edges] edge ids grouped by source frame, ascending inside a frame
   int* fill;       // [nbuf] scratch counters
-  float* gij;      // [n_edges][8] relative pose of every edge (tij, qij, pad)
+  float* gij;      // [n_edges][kEdgeStride] relative pose of every edge (tij, qij) and N = -Ad(g_ij)^T
+  float* ey;       // [n_edges][8] y_e = N_e^T dx[source pose] for the depth back-substitution
   float* Q;        // [n_eta][HW]
   float* W;        // [n_eta][HW]
   float* dx;       // [P][6]
@@ -66,7 +67,8 @@ static BaWs carve(void* base, const droid_ba_params* p, size_t chol_bytes) {
   w.eptr = (int*)take(((size_t)p->nbuf + 1) * sizeof(int));
   w.eidx = (int*)take((size_t)(p->n_edges > 0 ? p->n_edges : 1) * sizeof(int));
   w.fill = (int*)take((size_t)p->nbuf * sizeof(int));
-  w.gij = (float*)take((size_t)(p->n_edges > 0 ? p->n_edges : 1) * 8 * sizeof(float));
+  w.gij = (float*)take((size_t)(p->n_edges > 0 ? p->n_edges : 1) * kEdgeStride * sizeof(float));
+  w.ey = (float*)take((size_t)(p->n_edges > 0 ? p->n_edges : 1) * 8 * sizeof(float));
   w.Q = (float*)take((size_t)(p->n_eta > 0 ? p->n_eta : 1) * HW * sizeof(float));
   w.W = (float*)take((size_t)(p->n_eta > 0 ? p->n_eta : 1) * HW * sizeof(float));
   w.dx = (float*)take((n6 > 0 ? n6 : 1) * sizeof(float));
@@ -364,14 +366,38 @@ __global__ void ba_edge_pose_kernel(const float* __restrict__ poses, const int64
   } else {
     g = load_edge_pose(poses, (int)i, (int)j);
   }
-  float* o = gij + (size_t)e * 8;
+  float* o = gij + (size_t)e * kEdgeStride;
   o[0] = g.t[0]; o[1] = g.t[1]; o[2] = g.t[2];
   o[3] = g.q[0]; o[4] = g.q[1]; o[5] = g.q[2]; o[6] = g.q[3]; o[7] = 0.f;
+  edge_adjoint(g, o + 8);
+}
+
+// y_e = N_e^T dx[source pose] (0 when the source pose is not updated or is the first optimised pose, :1105)
+__global__ void ba_edge_y_kernel(const float* __restrict__ gij, const int64_t* __restrict__ ii, int n_edges,
+                                 int nbuf, const float* __restrict__ dx, int t0, int P, float* __restrict__ ey) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_edges) return;
+  const long long i = ii[e];
+  const int pk = (i < 0 || i >= nbuf) ? -1 : (int)i - t0;
+  float y[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (pk > 0 && pk < P) {
+    const float* N = gij + (size_t)e * kEdgeStride + 8;
+#pragma unroll
+    for (int n = 0; n < 6; n++) {
+      const float d = dx[6 * pk + n];
+#pragma unroll
+      for (int a = 0; a < 6; a++) y[a] = fmaf(N[n * 6 + a], d, y[a]);
+    }
+  }
+  float* o = ey + (size_t)e * 8;
+#pragma unroll
+  for (int a = 0; a < 6; a++) o[a] = y[a];
+  o[6] = 0.f; o[7] = 0.f;
 }
 
 __device__ __forceinline__ SE3 load_gij(const float* __restrict__ gij, int e) {
-  const float4 a = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e * 8));
-  const float4 b = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e * 8 + 4));
+  const float4 a = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e * kEdgeStride));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e * kEdgeStride + 4));
   SE3 g;
   g.t[0] = a.x; g.t[1] = a.y; g.t[2] = a.z;
   g.q[0] = a.w; g.q[1] = b.x; g.q[2] = b.y; g.q[3] = b.z;
@@ -394,6 +420,20 @@ __device__ __forceinline__ void transpose_reduce96(float* v, int lane) {
       }
     }
     cnt = half;
+  }
+}
+
+// Transposing butterfly over 32 per-lane values: lane l ends with the warp sum of v[l] in v[0] (31 shuffles).
+__device__ __forceinline__ void transpose_reduce32(float* v, int lane) {
+#pragma unroll
+  for (int s = 16, cnt = 32; s >= 1; s >>= 1, cnt >>= 1) {
+    const bool upper = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < cnt / 2; i++) {
+      const float send = upper ? v[i] : v[i + cnt / 2];
+      const float keep = upper ? v[i + cnt / 2] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
   }
 }
 
@@ -426,12 +466,17 @@ __device__ __forceinline__ void scatter_edge_value(double* __restrict__ A, doubl
 
 // ------------------------------------------------------------------------------------------------
 // pass 1: per-edge Hessian/gradient blocks + per-pixel depth terms -> Q = 1/C and w
-// CTA = (pixel slab, source frame m).  Per edge the 90 per-thread partials are reduced with a
-// transposing butterfly and added (fp64 atomics) into the dense system; C and bz are accumulated
-// over the frame's edges in shared memory (each pixel is owned by one thread => no atomics there).
+// CTA = (pixel slab, source frame m).  Only the TARGET-pose blocks are accumulated per pixel,
+//     Hjj = sum_p w Jj Jj^T (21 values),  vj = sum_p w r Jj (6 values);
+// the source-pose blocks follow from Ji = N Jj with the per-edge matrix N (edge_adjoint):
+//     Hii = N Hjj N^T,  Hji = Hjj N^T,  vi = N vj,
+// formed once per edge after the reduction (27 accumulators and no adjoint per pixel-edge instead of 90 and two).
+// The 27 per-thread partials are reduced with a transposing butterfly and the 90 values of the edge are added
+// (fp64 atomics) into the dense system; C and bz are accumulated over the frame's edges in shared memory (each
+// pixel is owned by one thread => no atomics there).
 // ------------------------------------------------------------------------------------------------
 static constexpr int kSlabMax = 3072;
-static constexpr int kMetaChunk = 64;  // edges of one source frame staged in shared memory at a time
+static constexpr int kMetaChunk = 32;  // edges of one source frame staged in shared memory at a time
 
 __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
     const float* __restrict__ disps, const float* __restrict__ intrinsics,
@@ -445,7 +490,8 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
   __shared__ float Cs[kSlabMax];
   __shared__ float Bs[kSlabMax];
   __shared__ float Ds[kSlabMax];   // inverse depths of the slab (re-read for every edge of the frame)
-  __shared__ float red[kThreads / 32][kHW_ACC];
+  __shared__ float red[kThreads / 32][32];
+  __shared__ float s_sum[32];      // Hjj (21, lower triangle row-major) | vj (6)
   const int m = blockIdx.y;
   const int M = status[1];
   if (m >= M || m >= n_eta) return;
@@ -461,12 +507,11 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
   for (int p = tid; p < p1 - p0; p += kThreads) { Cs[p] = 0.f; Bs[p] = 0.f; Ds[p] = dmap[p0 + p]; }
   __syncthreads();
   const int e0 = eptr[m], e1 = eptr[m + 1];
-  // Edge metadata (edge id, target frame, relative pose) is staged in shared memory in chunks, and the four
-  // input values of the NEXT (edge, pixel) item are fetched before the current item is processed: with ~90
-  // accumulators a thread cannot rely on occupancy to hide the HBM latency of its loads (ncu: 30 % long-scoreboard).
+  // Edge metadata (edge id, target frame, relative pose, N) is staged in shared memory in chunks, and the four
+  // input values of the NEXT (edge, pixel) item are fetched before the current item is processed.
   __shared__ int s_e[kMetaChunk];
   __shared__ int s_jx[kMetaChunk];
-  __shared__ __align__(16) float s_g[kMetaChunk][8];
+  __shared__ __align__(16) float s_g[kMetaChunk][kEdgeStride];
   for (int eb = e0; eb < e1; eb += kMetaChunk) {
     const int nE = min(kMetaChunk, e1 - eb);
     __syncthreads();
@@ -475,7 +520,8 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
       s_e[i] = e;
       s_jx[i] = (int)jj[e];
     }
-    for (int i = tid; i < nE * 8; i += kThreads) s_g[i >> 3][i & 7] = gij[(size_t)eidx[eb + (i >> 3)] * 8 + (i & 7)];
+    for (int i = tid; i < nE * kEdgeStride; i += kThreads)
+      s_g[i / kEdgeStride][i % kEdgeStride] = gij[(size_t)eidx[eb + i / kEdgeStride] * kEdgeStride + i % kEdgeStride];
     __syncthreads();
     float n_tu = 0.f, n_tv = 0.f, n_wu = 0.f, n_wv = 0.f;
     auto fetch = [&](int ei_, int p_) {
@@ -494,9 +540,9 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
         g.t[0] = ga.x; g.t[1] = ga.y; g.t[2] = ga.z;
         g.q[0] = ga.w; g.q[1] = gb.x; g.q[2] = gb.y; g.q[3] = gb.z;
       }
-      float acc[kHW_ACC];
+      float acc[32];
 #pragma unroll
-      for (int l = 0; l < kHW_ACC; l++) acc[l] = 0.f;
+      for (int l = 0; l < 32; l++) acc[l] = 0.f;
       for (int p = p0 + tid; p < p1; p += kThreads) {
         const float tu = n_tu, tv = n_tv, wu = n_wu, wv = n_wv;
         {
@@ -504,8 +550,8 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
           if (pn >= p1) { pn = p0 + tid; ein = ei + 1; }
           if (ein < nE) fetch(ein, pn);
         }
-        PixLin L;
-        linearise(g, K, wd, p, Ds[p - p0], tu, tv, wu, wv, stereo, L);
+        PixLinJ L;
+        linearise_j(g, K, wd, p, Ds[p - p0], tu, tv, wu, wv, stereo, L);
         // depth terms (:320-321, :353-354)
         float c = L.wu_d * L.Jz_u * L.Jz_u;
         float bz = L.wu_d * L.ru * L.Jz_u;
@@ -514,43 +560,54 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
         Cs[p - p0] += c;
         Bs[p - p0] += bz;
         if (!stereo) {
-          float Jx[12];
-#pragma unroll
-          for (int n = 0; n < 6; n++) { Jx[n] = L.Ji_u[n]; Jx[6 + n] = L.Jj_u[n]; }
           int l = 0;
 #pragma unroll
-          for (int n = 0; n < 12; n++) {
-            const float wj = L.wu * Jx[n];
+          for (int n = 0; n < 6; n++) {
+            const float wju = L.wu * L.Jj_u[n], wjv = L.wv * L.Jj_v[n];
 #pragma unroll
-            for (int q = 0; q <= n; q++) { acc[l] += wj * Jx[q]; l++; }
+            for (int q = 0; q <= n; q++) { acc[l] += wju * L.Jj_u[q]; acc[l] += wjv * L.Jj_v[q]; l++; }
           }
-          const float wr = L.wu * L.ru;
+          const float wr = L.wu * L.ru, wr2 = L.wv * L.rv;
 #pragma unroll
-          for (int n = 0; n < 12; n++) acc[78 + n] += wr * Jx[n];
-#pragma unroll
-          for (int n = 0; n < 6; n++) { Jx[n] = L.Ji_v[n]; Jx[6 + n] = L.Jj_v[n]; }
-          l = 0;
-#pragma unroll
-          for (int n = 0; n < 12; n++) {
-            const float wj = L.wv * Jx[n];
-#pragma unroll
-            for (int q = 0; q <= n; q++) { acc[l] += wj * Jx[q]; l++; }
-          }
-          const float wr2 = L.wv * L.rv;
-#pragma unroll
-          for (int n = 0; n < 12; n++) acc[78 + n] += wr2 * Jx[n];
+          for (int n = 0; n < 6; n++) { acc[21 + n] += wr * L.Jj_u[n]; acc[21 + n] += wr2 * L.Jj_v[n]; }
         }
       }
       if (!stereo) {
-        transpose_reduce96(acc, lane);
-        red[warp][3 * lane + 0] = acc[0];
-        red[warp][3 * lane + 1] = acc[1];
-        red[warp][3 * lane + 2] = acc[2];
+        transpose_reduce32(acc, lane);
+        red[warp][lane] = acc[0];
         __syncthreads();
-        if (tid < 90) {
+        if (tid < 32) {
           float sum = 0.f;
 #pragma unroll
           for (int w = 0; w < kThreads / 32; w++) sum += red[w][tid];
+          s_sum[tid] = sum;
+        }
+        __syncthreads();
+        if (tid < 90) {
+          const float* N = &s_g[ei][8];
+          auto Hjj = [&](int a, int b) { return a >= b ? s_sum[a * (a + 1) / 2 + b] : s_sum[b * (b + 1) / 2 + a]; };
+          float val = 0.f;
+          if (tid < 78) {
+            int n = (int)((sqrtf(8.f * tid + 1.f) - 1.f) * 0.5f);
+            while ((n + 1) * (n + 2) / 2 <= tid) n++;
+            while (n * (n + 1) / 2 > tid) n--;
+            const int mm = tid - n * (n + 1) / 2;
+            if (n < 6) {                 // Hii[n][mm] = sum_ab N[n][a] Hjj[a][b] N[mm][b]
+              for (int a = 0; a < 6; a++) {
+                float t = 0.f;
+                for (int b = 0; b < 6; b++) t = fmaf(Hjj(a, b), N[mm * 6 + b], t);
+                val = fmaf(N[n * 6 + a], t, val);
+              }
+            } else if (mm >= 6) {        // Hjj
+              val = Hjj(n - 6, mm - 6);
+            } else {                     // Hji[n-6][mm] = sum_b Hjj[n-6][b] N[mm][b]
+              for (int b = 0; b < 6; b++) val = fmaf(Hjj(n - 6, b), N[mm * 6 + b], val);
+            }
+          } else if (tid < 84) {         // vi = N vj
+            for (int a = 0; a < 6; a++) val = fmaf(N[(tid - 78) * 6 + a], s_sum[21 + a], val);
+          } else {
+            val = s_sum[21 + tid - 84];
+          }
           int pi = k - t0, pj = jx - t0;
           if (pi < 0 || pi >= P) pi = -1;
           if (pj < 0 || pj >= P) pj = -1;
@@ -558,7 +615,7 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
             if (pi >= 0) pi = ppos[pi];
             if (pj >= 0) pj = ppos[pj];
           }
-          scatter_edge_value(A, bvec, n6, tid, sum, pi, pj);
+          scatter_edge_value(A, bvec, n6, tid, val, pi, pj);
         }
         __syncthreads();
       }
@@ -657,8 +714,8 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
   if (D <= tc_max_d) return;                    // this frame is handled by ba_schur_tc_kernel (schur_tc.cu)
   const int DP = (D + 1) >> 1, RP = 12 * DP;   // row blocks are processed in pairs (12 rows); odd D is zero-padded
   const int stride = RP + 2;                    // == 2 (mod 4): even (LDS.64) and spreads the banks
-  // smem: E[T][stride] | Qs[T] | QWs[T] | vS[R] | pose[2*DP] | s_e[deg] | s_jx[deg] | s_g[deg][8]
-  const int fixed = (R + 2 * DP + 8 + 10 * deg + 4) * 4;
+  // smem: E[T][stride] | Qs[T] | QWs[T] | vS[R] | pose[2*DP] | s_e[deg] | s_jx[deg] | s_g[deg][kEdgeStride]
+  const int fixed = (R + 2 * DP + 8 + (2 + kEdgeStride) * deg + 4) * 4;
   int T = (kSchurSmemBytes - fixed) / ((stride + 2) * 4);
   T = min(T, kThreads) & ~31;
   if (T < 32) {  // out-degree too large for one SM's shared memory
@@ -681,7 +738,8 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
     s_e[i] = e;
     s_jx[i] = (int)jj[e];
   }
-  for (int i = tid; i < deg * 8; i += kThreads) s_g[i] = gij[(size_t)eidx[e0 + (i >> 3)] * 8 + (i & 7)];
+  for (int i = tid; i < deg * kEdgeStride; i += kThreads)
+    s_g[i] = gij[(size_t)eidx[e0 + i / kEdgeStride] * kEdgeStride + i % kEdgeStride];
   for (int d = tid; d < 2 * DP; d += kThreads) {
     int pz = -1;
     if (d < D) {
@@ -741,23 +799,31 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
           if (i + 1 < deg) fetch(i + 1);     // next edge's inputs are in flight while this one is linearised
           SE3 gg;
           {
-            const float4 ga = *reinterpret_cast<const float4*>(s_g + 8 * i);
-            const float4 gb = *reinterpret_cast<const float4*>(s_g + 8 * i + 4);
+            const float4 ga = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i);
+            const float4 gb = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i + 4);
             gg.t[0] = ga.x; gg.t[1] = ga.y; gg.t[2] = ga.z;
             gg.q[0] = ga.w; gg.q[1] = gb.x; gg.q[2] = gb.y; gg.q[3] = gb.z;
           }
-          PixLin L;
-          linearise(gg, K, wd, p, dp, tu, tv, wu, wv, jx == k, L);
+          PixLinJ L;
+          linearise_j(gg, K, wd, p, dp, tu, tv, wu, wv, jx == k, L);
           const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
           float* Ej = Erow + 6 * (ei - e0 + 1);
+          float ej[6];
 #pragma unroll
           for (int n = 0; n < 6; n++) {
-            float ei_n = au * L.Ji_u[n];
-            ei_n += av * L.Ji_v[n];
-            Ei[n] += ei_n;
             float ej_n = au * L.Jj_u[n];
             ej_n += av * L.Jj_v[n];
+            ej[n] = ej_n;
             Ej[n] = ej_n;
+          }
+          // E_i = N E_j (the source-pose Jacobian is a per-edge linear image of the target-pose one)
+          const float* N = s_g + kEdgeStride * i + 8;
+#pragma unroll
+          for (int n = 0; n < 6; n++) {
+            float t = 0.f;
+#pragma unroll
+            for (int a = 0; a < 6; a++) t = fmaf(N[n * 6 + a], ej[a], t);
+            Ei[n] += t;
           }
         }
 #pragma unroll
@@ -829,7 +895,8 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
 __global__ void __launch_bounds__(kThreads) ba_dz_kernel(
     float* __restrict__ disps, const float* __restrict__ intrinsics,
     const float* __restrict__ targets, const float* __restrict__ weights,
-    const int64_t* __restrict__ jj, const float* __restrict__ gij, const int* __restrict__ status,
+    const int64_t* __restrict__ jj, const float* __restrict__ gij, const float* __restrict__ ey,
+    const int* __restrict__ status,
     const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
     const float* __restrict__ Qi, const float* __restrict__ Wi, const float* __restrict__ dx,
     float* __restrict__ dz_out, int HW, int wd, int t0, int P, int n_eta, int frame_lo,
@@ -845,17 +912,20 @@ __global__ void __launch_bounds__(kThreads) ba_dz_kernel(
   float* __restrict__ dmap = disps + (size_t)k * HW;
   const float dp = dmap[p];
   const int e0 = eptr[m], e1 = eptr[m + 1];
-  float Ei[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   float sum = 0.f;
-  // one-edge-ahead software prefetch of (edge id, target frame, relative pose, target, weight)
+  // E_i^T dx_i = (N E_j)^T dx_i = E_j^T y_e with y_e = N_e^T dx_i precomputed per edge (ba_edge_y_kernel; zero when
+  // the source pose index is <= 0 or >= P), so the source-pose Jacobian is never formed here.
+  // one-edge-ahead software prefetch of (edge id, target frame, relative pose, y, target, weight)
   int n_jx = 0;
-  float4 n_ga = make_float4(0, 0, 0, 0), n_gb = make_float4(0, 0, 0, 0);
+  float4 n_ga = make_float4(0, 0, 0, 0), n_gb = make_float4(0, 0, 0, 0), n_ya = n_ga, n_yb = n_ga;
   float n_tu = 0.f, n_tv = 0.f, n_wu = 0.f, n_wv = 0.f;
   auto fetch = [&](int ei_) {
     const int e_ = eidx[ei_];
     n_jx = (int)jj[e_];
-    n_ga = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e_ * 8));
-    n_gb = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e_ * 8 + 4));
+    n_ga = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e_ * kEdgeStride));
+    n_gb = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e_ * kEdgeStride + 4));
+    n_ya = __ldg(reinterpret_cast<const float4*>(ey + (size_t)e_ * 8));
+    n_yb = __ldg(reinterpret_cast<const float4*>(ey + (size_t)e_ * 8 + 4));
     const size_t base = (size_t)e_ * 2 * HW + p;
     n_tu = __ldg(targets + base); n_tv = __ldg(targets + base + HW);
     n_wu = __ldg(weights + base); n_wv = __ldg(weights + base + HW);
@@ -866,30 +936,22 @@ __global__ void __launch_bounds__(kThreads) ba_dz_kernel(
     SE3 g;
     g.t[0] = n_ga.x; g.t[1] = n_ga.y; g.t[2] = n_ga.z;
     g.q[0] = n_ga.w; g.q[1] = n_gb.x; g.q[2] = n_gb.y; g.q[3] = n_gb.z;
+    const float y[6] = {n_ya.x, n_ya.y, n_ya.z, n_ya.w, n_yb.x, n_yb.y};
     const float tu = n_tu, tv = n_tv, wu = n_wu, wv = n_wv;
     if (ei + 1 < e1) fetch(ei + 1);
-    PixLin L;
-    linearise(g, K, wd, p, dp, tu, tv, wu, wv, jx == k, L);
+    PixLinJ L;
+    linearise_j(g, K, wd, p, dp, tu, tv, wu, wv, jx == k, L);
     const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
     const int pj = jx - t0;
     const bool use = pj > 0 && pj < P;
     float dw = 0.f;
 #pragma unroll
     for (int n = 0; n < 6; n++) {
-      float ei_n = au * L.Ji_u[n];
-      ei_n += av * L.Ji_v[n];
-      Ei[n] += ei_n;
       float ej_n = au * L.Jj_u[n];
       ej_n += av * L.Jj_v[n];
       if (use) dw += ej_n * __ldg(&dx[6 * pj + n]);
+      dw += ej_n * y[n];
     }
-    sum += dw;
-  }
-  const int pk = k - t0;
-  if (pk > 0 && pk < P) {
-    float dw = 0.f;
-#pragma unroll
-    for (int n = 0; n < 6; n++) dw += Ei[n] * __ldg(&dx[6 * pk + n]);
     sum += dw;
   }
   const float dz = Qi[(size_t)m * HW + p] * (Wi[(size_t)m * HW + p] - sum);
@@ -1089,8 +1151,10 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     } else {
       DROID_LAUNCH ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
                                                                           w.dx, dx_out, p->t0, P, 0, ppos);
+      DROID_LAUNCH ba_edge_y_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(w.gij, ii, p->n_edges, p->nbuf, w.dx,
+                                                                              p->t0, P, w.ey);
       DROID_LAUNCH ba_dz_kernel<<<dim3((HW + kThreads - 1) / kThreads, p->n_eta), kThreads, 0, st>>>(
-          disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
+          disps, intrinsics, targets, weights, jj, w.gij, w.ey, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
           w.dx, dz_out, HW, p->wd, p->t0, P, p->n_eta, frame_lo, frame_hi);
       DROID_LAUNCH ba_pose_apply_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, w.dx, p->t0, P);
     }

@@ -40,7 +40,7 @@ static constexpr int kELd = 132;                 // fp32 staging row stride (flo
 static constexpr int kTB = 128;                   // pixels per build pass (4 MMA chunks): long enough to pipeline the loads
 static constexpr int kEBytes = kTB * kELd * 4;
 static constexpr int kMetaOff = 2 * kStage + kEBytes;
-static constexpr int kSmem = kMetaOff + 4096 + 1024;
+static constexpr int kSmem = kMetaOff + 8192 + 1024;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
   int* s_e = reinterpret_cast<int*>(bars + 10);
   int* s_jx = s_e + 24;
   int* pose = s_jx + 24;
-  float* s_g = reinterpret_cast<float*>(bars + 10 + 64);   // 16-byte aligned: [deg][8]
+  float* s_g = reinterpret_cast<float*>(bars + 10 + 64);   // 16-byte aligned: [deg][kEdgeStride]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
@@ -180,7 +180,8 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
     s_e[i] = e;
     s_jx[i] = (int)jj[e];
   }
-  for (int i = tid; i < deg * 8; i += kThreads) s_g[i] = gij[(size_t)eidx[e0 + (i >> 3)] * 8 + (i & 7)];
+  for (int i = tid; i < deg * kEdgeStride; i += kThreads)
+    s_g[i] = gij[(size_t)eidx[e0 + i / kEdgeStride] * kEdgeStride + i % kEdgeStride];
   for (int d = tid; d < D; d += kThreads) {
     int pz = (d == 0) ? k - t0 : (int)jj[eidx[e0 + d - 1]] - t0;
     if (pz < 0 || pz >= P) pz = -1;
@@ -255,23 +256,30 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
         }
         SE3 gg;
         {
-          const float4 ga = *reinterpret_cast<const float4*>(s_g + 8 * i);
-          const float4 gb = *reinterpret_cast<const float4*>(s_g + 8 * i + 4);
+          const float4 ga = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i);
+          const float4 gb = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i + 4);
           gg.t[0] = ga.x; gg.t[1] = ga.y; gg.t[2] = ga.z;
           gg.q[0] = ga.w; gg.q[1] = gb.x; gg.q[2] = gb.y; gg.q[3] = gb.z;
         }
-        PixLin L;
-        linearise(gg, K, wd, valid ? p : p0, dp, tu, tv, wu, wv, jx == k, L);
+        PixLinJ L;
+        linearise_j(gg, K, wd, valid ? p : p0, dp, tu, tv, wu, wv, jx == k, L);
         const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
-        float ej[6];
+        float ej[6], ejr[6];
 #pragma unroll
         for (int n = 0; n < 6; n++) {
-          float ei_n = au * L.Ji_u[n];
-          ei_n += av * L.Ji_v[n];
-          Ei[n] += ei_n;
           float ej_n = au * L.Jj_u[n];
           ej_n += av * L.Jj_v[n];
+          ejr[n] = ej_n;
           ej[n] = valid ? sq * ej_n : 0.f;
+        }
+        // E_i = N E_j (per-edge matrix, see ba_lin.cuh)
+        const float* N = s_g + kEdgeStride * i + 8;
+#pragma unroll
+        for (int n = 0; n < 6; n++) {
+          float t = 0.f;
+#pragma unroll
+          for (int a = 0; a < 6; a++) t = fmaf(N[n * 6 + a], ejr[a], t);
+          Ei[n] += t;
         }
         float2* dst = reinterpret_cast<float2*>(Erow + 6 * (i + 1));
         dst[0] = make_float2(ej[0], ej[1]); dst[1] = make_float2(ej[2], ej[3]); dst[2] = make_float2(ej[4], ej[5]);
