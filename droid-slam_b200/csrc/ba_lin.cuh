@@ -5,60 +5,8 @@
 namespace droid {
 
 // ------------------------------------------------------------------------------------------------
-// per pixel-edge linearisation (src/droid_kernels.cu:283-375)
-// ------------------------------------------------------------------------------------------------
-struct PixLin {
-  float Ji_u[6], Jj_u[6], Ji_v[6], Jj_v[6];
-  float Jz_u, Jz_v;
-  float wu_d, wv_d;  // weights of the depth terms (C, bz)
-  float wu, wv;      // weights of the pose terms (zeroed on stereo edges, :323,:356)
-  float ru, rv;
-};
-
-__device__ __forceinline__ void linearise(const SE3& g, const Intr& K, int wd, int k, float disp,
-                                          float tu, float tv, float wru, float wrv, bool stereo,
-                                          PixLin& L) {
-  const int i = k / wd, j = k - i * wd;
-  const float u = (float)j, v = (float)i;
-  float Xi[4], Xj[4];
-  Xi[0] = (u - K.cx) / K.fx;
-  Xi[1] = (v - K.cy) / K.fy;
-  Xi[2] = 1;
-  Xi[3] = disp;
-  act_se3(g.t, g.q, Xi, Xj);
-  const float x = Xj[0], y = Xj[1], h = Xj[3];
-  const bool behind = Xj[2] < DROID_MIN_DEPTH;
-  const float d = behind ? 0.0f : (float)(1.0 / (double)Xj[2]);
-  const float d2 = d * d;
-  L.wu_d = behind ? 0.0f : (float)(.001 * (double)wru);
-  L.wv_d = behind ? 0.0f : (float)(.001 * (double)wrv);
-  L.ru = tu - (K.fx * d * x + K.cx);
-  L.rv = tv - (K.fy * d * y + K.cy);
-  L.Jj_u[0] = K.fx * (h * d);
-  L.Jj_u[1] = K.fx * 0;
-  L.Jj_u[2] = K.fx * (-x * h * d2);
-  L.Jj_u[3] = K.fx * (-x * y * d2);
-  L.Jj_u[4] = K.fx * (1 + x * x * d2);
-  L.Jj_u[5] = K.fx * (-y * d);
-  L.Jz_u = K.fx * (g.t[0] * d - g.t[2] * (x * d2));
-  adj_se3(g.t, g.q, L.Jj_u, L.Ji_u);
-#pragma unroll
-  for (int n = 0; n < 6; n++) L.Ji_u[n] *= -1;
-  L.Jj_v[0] = K.fy * 0;
-  L.Jj_v[1] = K.fy * (h * d);
-  L.Jj_v[2] = K.fy * (-y * h * d2);
-  L.Jj_v[3] = K.fy * (-1 - y * y * d2);
-  L.Jj_v[4] = K.fy * (x * y * d2);
-  L.Jj_v[5] = K.fy * (x * d);
-  L.Jz_v = K.fy * (g.t[1] * d - g.t[2] * (y * d2));
-  adj_se3(g.t, g.q, L.Jj_v, L.Ji_v);
-#pragma unroll
-  for (int n = 0; n < 6; n++) L.Ji_v[n] *= -1;
-  L.wu = stereo ? 0.f : L.wu_d;
-  L.wv = stereo ? 0.f : L.wv_d;
-}
-
-// Same without the Jacobian w.r.t. the SOURCE pose.  Ji = -Ad(g_ij)^T Jj is a LINEAR image of Jj with a matrix that
+// per pixel-edge linearisation (src/droid_kernels.cu:283-375), target-pose Jacobian only.
+// The Jacobian w.r.t. the SOURCE pose is not formed per pixel: Ji = -Ad(g_ij)^T Jj is a LINEAR image of Jj with a matrix that
 // depends on the edge only, not on the pixel, so the kernels keep just Jj per pixel and apply the 6x6 matrix
 // N = -Ad(g_ij)^T (edge_adjoint below, stored next to the relative pose) once per edge / once per 6-vector:
 // the reference evaluates the adjoint twice per pixel-edge (src/droid_kernels.cu:336-338, 368-371), which is
@@ -84,7 +32,9 @@ __device__ __forceinline__ void linearise_j(const SE3& g, const Intr& K, int wd,
   act_se3(g.t, g.q, Xi, Xj);
   const float x = Xj[0], y = Xj[1], h = Xj[3];
   const bool behind = Xj[2] < DROID_MIN_DEPTH;
-  const float d = behind ? 0.0f : (float)(1.0 / (double)Xj[2]);
+  // the reference divides in double and rounds to float (:305); the IEEE-rounded float reciprocal is the same value
+  // except for double-rounding ties (~2^-29 of the inputs) and keeps the slow fp64 pipe off the critical chain
+  const float d = behind ? 0.0f : __frcp_rn(Xj[2]);
   const float d2 = d * d;
   L.wu_d = behind ? 0.0f : (float)(.001 * (double)wru);
   L.wv_d = behind ? 0.0f : (float)(.001 * (double)wrv);

@@ -225,12 +225,18 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
     const float* __restrict__ dmap = disps + (size_t)k * HW;
     float* Erow = E32 + pl * kELd;
     const int npass = (p1 - p0 + kTB - 1) / kTB;
-    float n_tu = 0.f, n_tv = 0.f, n_wu = 0.f, n_wv = 0.f, n_dp = 0.f, n_q = 0.f, n_w = 0.f;
-    auto fetch = [&](int i, int p, bool ok) {
-      if (ok) {
+    // The inputs of a thread's (up to 10) edges live in registers one whole pass ahead: as soon as item i of this
+    // pass has been consumed, the same registers are re-loaded with item i of the next pass, so every global load has
+    // a full pass (~10 linearisations) to arrive.  With 8 builder warps per SM nothing else hides the DRAM latency.
+    constexpr int kMaxI = (kSchurTcMaxD - 1 + 1) / 2;     // edges per thread
+    float r_tu[kMaxI], r_tv[kMaxI], r_wu[kMaxI], r_wv[kMaxI];
+    float n_dp = 0.f, n_q = 0.f, n_w = 0.f;
+    auto fetch = [&](int it, int p, bool ok) {
+      const int i = g + 2 * it;
+      if (ok && i < deg) {
         const size_t base = (size_t)s_e[i] * 2 * HW + p;
-        n_tu = __ldg(targets + base); n_tv = __ldg(targets + base + HW);
-        n_wu = __ldg(weights + base); n_wv = __ldg(weights + base + HW);
+        r_tu[it] = __ldg(targets + base); r_tv[it] = __ldg(targets + base + HW);
+        r_wu[it] = __ldg(weights + base); r_wv[it] = __ldg(weights + base + HW);
       }
     };
     auto fetch_pix = [&](int p, bool ok) {
@@ -238,55 +244,56 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
       n_q = ok ? Qi[(size_t)m * HW + p] : 0.f;
       n_w = ok ? Wi[(size_t)m * HW + p] : 0.f;
     };
+#pragma unroll
+    for (int it = 0; it < kMaxI; it++) { r_tu[it] = 0.f; r_tv[it] = 0.f; r_wu[it] = 0.f; r_wv[it] = 0.f; }
     fetch_pix(p0 + pl, p0 + pl < p1);
-    if (g < deg) fetch(g, p0 + pl, p0 + pl < p1);
+#pragma unroll
+    for (int it = 0; it < kMaxI; it++) fetch(it, p0 + pl, p0 + pl < p1);
     for (int ps = 0; ps < npass; ps++) {
       const int p = p0 + ps * kTB + pl;
       const bool valid = p < p1;
+      const int pn = p + kTB;
+      const bool valid_n = pn < p1;
       const float dp = n_dp, sq = sqrtf(n_q), wv_pix = n_w;
+      fetch_pix(pn, valid_n);
       float Ei[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int i = g; i < deg; i += 2) {
-        const int jx = s_jx[i];
-        const float tu = n_tu, tv = n_tv, wu = n_wu, wv = n_wv;
-        if (i + 2 < deg) fetch(i + 2, p, valid);
-        else {                                   // last edge of this pixel: start on the next pass
-          const int pn = p + kTB;
-          fetch_pix(pn, pn < p1);
-          if (g < deg) fetch(g, pn, pn < p1);
-        }
-        SE3 gg;
-        {
-          const float4 ga = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i);
-          const float4 gb = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i + 4);
-          gg.t[0] = ga.x; gg.t[1] = ga.y; gg.t[2] = ga.z;
-          gg.q[0] = ga.w; gg.q[1] = gb.x; gg.q[2] = gb.y; gg.q[3] = gb.z;
-        }
-        PixLinJ L;
-        linearise_j(gg, K, wd, valid ? p : p0, dp, tu, tv, wu, wv, jx == k, L);
-        const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
-        float ej[6], ejr[6];
 #pragma unroll
-        for (int n = 0; n < 6; n++) {
-          float ej_n = au * L.Jj_u[n];
-          ej_n += av * L.Jj_v[n];
-          ejr[n] = ej_n;
-          ej[n] = valid ? sq * ej_n : 0.f;
-        }
-        // E_i = N E_j (per-edge matrix, see ba_lin.cuh)
-        const float* N = s_g + kEdgeStride * i + 8;
+      for (int it = 0; it < kMaxI; it++) {
+        const int i = g + 2 * it;
+        if (i < deg) {
+          const int jx = s_jx[i];
+          const float tu = r_tu[it], tv = r_tv[it], wu = r_wu[it], wv = r_wv[it];
+          fetch(it, pn, valid_n);
+          SE3 gg;
+          {
+            const float4 ga = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i);
+            const float4 gb = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i + 4);
+            gg.t[0] = ga.x; gg.t[1] = ga.y; gg.t[2] = ga.z;
+            gg.q[0] = ga.w; gg.q[1] = gb.x; gg.q[2] = gb.y; gg.q[3] = gb.z;
+          }
+          PixLinJ L;
+          linearise_j(gg, K, wd, valid ? p : p0, dp, tu, tv, wu, wv, jx == k, L);
+          const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
+          float ej[6], ejr[6];
 #pragma unroll
-        for (int n = 0; n < 6; n++) {
-          float t = 0.f;
+          for (int n = 0; n < 6; n++) {
+            float ej_n = au * L.Jj_u[n];
+            ej_n += av * L.Jj_v[n];
+            ejr[n] = ej_n;
+            ej[n] = valid ? sq * ej_n : 0.f;
+          }
+          // E_i = N E_j (per-edge matrix, see ba_lin.cuh)
+          const float* N = s_g + kEdgeStride * i + 8;
 #pragma unroll
-          for (int a = 0; a < 6; a++) t = fmaf(N[n * 6 + a], ejr[a], t);
-          Ei[n] += t;
+          for (int n = 0; n < 6; n++) {
+            float t = 0.f;
+#pragma unroll
+            for (int a = 0; a < 6; a++) t = fmaf(N[n * 6 + a], ejr[a], t);
+            Ei[n] += t;
+          }
+          float2* dst = reinterpret_cast<float2*>(Erow + 6 * (i + 1));
+          dst[0] = make_float2(ej[0], ej[1]); dst[1] = make_float2(ej[2], ej[3]); dst[2] = make_float2(ej[4], ej[5]);
         }
-        float2* dst = reinterpret_cast<float2*>(Erow + 6 * (i + 1));
-        dst[0] = make_float2(ej[0], ej[1]); dst[1] = make_float2(ej[2], ej[3]); dst[2] = make_float2(ej[4], ej[5]);
-      }
-      if (deg == 1 && g == 1) {                  // a thread without edges still has to move its prefetch along
-        const int pn = p + kTB;
-        fetch_pix(pn, pn < p1);
       }
       // the source pose's rows: sum over the two threads of this pixel
 #pragma unroll
