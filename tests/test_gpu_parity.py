@@ -348,6 +348,56 @@ def test_chol_solve(backends, n):
     assert int(info.item()) != 0
 
 
+@pytest.mark.parametrize("n,bw,wide", [(200, 40, ()), (400, 100, ()), (1200, 200, (700, 1100)), (2431, 130, ()),
+                                       (2500, 384, (2000,)), (2500, 2499, ())])
+def test_chol_solve_envelope(backends, n, bw, wide):
+    """droid_chol_solve_env_f64: banded SPD systems (a few rows with a much wider envelope, and one fully dense
+    'envelope') must give the dense answer -- tiles outside the row envelopes are skipped, fill-in stays inside."""
+    rng = np.random.default_rng(n + bw)
+    first = np.maximum(np.arange(n) - bw, 0)
+    for r in wide:
+        first[r] = rng.integers(0, max(1, r // 4))
+    A = np.zeros((n, n))
+    for r in range(n):
+        A[r, first[r]:r] = rng.normal(size=r - first[r]) * 0.1
+    A = A + A.T + np.diag(np.full(n, 0.2 * min(bw, 400) + 5.0 + 0.1 * n * (len(wide) > 0) + (0.1 * n if bw > 1000 else 0.0)))
+    b = rng.normal(size=n)
+    x, info = backends.chol_solve(cu(A), cu(b), cu(first.astype(np.int32)))
+    assert int(info.item()) == 0
+    assert rel(x.cpu().numpy(), np.linalg.solve(A, b)) <= 1e-10
+    x2, _ = backends.chol_solve(cu(A), cu(b))                      # dense path, same system
+    assert rel(x.cpu().numpy(), x2.cpu().numpy()) <= 1e-10
+    A[n // 2, n // 2] = -1.0 - n
+    _, info = backends.chol_solve(cu(A), cu(b), cu(first.astype(np.int32)))
+    assert int(info.item()) != 0
+
+
+def test_ba_tensor_core_schur_matches_cuda_core_kernel():
+    """The 3xTF32 tcgen05 Schur kernel (default for frames with <= 20 edges) against the fp32 CUDA-core kernel
+    (DROID_SCHUR_TC=0, separate process because the switch is read once): same dx / dz to well inside the 1e-4 budget
+    on the ill-conditioned 60-keyframe backend case."""
+    import os, subprocess, sys, tempfile
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np, torch\n"
+        "sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import synth, droid_backends as B\n"
+        "p = synth.make_ba_problem('C4', n_frames=60)\n"
+        "cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()\n"
+        "po, di = cu(p['poses']), cu(p['disps'])\n"
+        "dx, dz = B.ba(po, di, cu(p['intrinsics']), cu(p['disps_sens']), cu(p['targets']), cu(p['weights']), cu(p['eta']),"
+        " cu(p['ii']), cu(p['jj']), p['t0'], p['t1'], 1, 1e-5, 1e-2, False)\n"
+        "np.savez(sys.argv[1], dx=dx.cpu().numpy(), dz=dz.cpu().numpy())\n"
+    ) % (os.path.join(ROOT, "droid-slam_b200"), os.path.join(ROOT, "oracle"))
+    out = {}
+    with tempfile.TemporaryDirectory() as td:
+        for tc in ("1", "0"):
+            f = os.path.join(td, "o%s.npz" % tc)
+            subprocess.check_call([sys.executable, "-c", code, f], env=dict(os.environ, DROID_SCHUR_TC=tc))
+            out[tc] = dict(np.load(f))
+    assert rel(out["1"]["dx"], out["0"]["dx"]) <= 1e-4 and rel(out["1"]["dz"], out["0"]["dz"]) <= 5e-5
+
+
 @pytest.mark.parametrize("key", sorted(__import__("golden_cases").BA_CASES))
 def test_ba_matches_reference_golden(backends, key):
     """Against the stored outputs of the unmodified reference extension (tests/golden/ref_ba_*.npz)."""
