@@ -259,10 +259,28 @@ struct ElimStep<64> {
   static __device__ __forceinline__ void run(double (&)[64], double&, double*, double*, double*, int) {}
 };
 
+// Chain mode (droid_chol_solve_chains_f64): several column ranges ("chains") that are structurally decoupled from
+// each other are factorised concurrently; they only meet in the separator rows [sep, n].  A launch that works for
+// chain c must not touch the rows / columns of the later chains -- the hole [hole_lo, hole_hi) -- and, except for
+// chain 0, accumulates its update of the separator x separator block into a private scratch copy (row stride lds)
+// that is added to A once all chains are done.
+struct ChainArgs {
+  int hole_lo, hole_hi;   // rows / columns left alone (hole_lo >= hole_hi: none)
+  int sep;                // first separator row
+  double* scr;            // scratch for C[r][c], r >= sep and c >= sep (nullptr: update A in place)
+  int lds;
+};
+static constexpr int kMaxChains = 8;
+struct Ranges {            // range c = [b[c], b[c+1]), c = 0..k; ranges 0..k-1 are the chains, range k the separator
+  int k;
+  int b[kMaxChains + 2];
+};
+
 __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__ A, int n, int j0, int jb,
                                                             int* __restrict__ info,
                                                             const int* __restrict__ hi64,
-                                                            int* __restrict__ arrive, int vec) {
+                                                            int* __restrict__ arrive, int vec, int hole_lo,
+                                                            int hole_hi) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* R = reinterpret_cast<double*>(smem_raw);  // [256][kRld] row staging
   double* col = R + 256 * kRld;                      // [2][128]  published column (double-buffered, padded)
@@ -272,7 +290,8 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
   const int tid = threadIdx.x;
   const int trow0 = j0 + jb + blockIdx.x * PR;       // first trailing row of this CTA
   // envelope: rows past hi64[] have no entry in these columns (and get none); the CTA holding the rhs row stays
-  if (hi64 != nullptr && blockIdx.x != 0 && trow0 > hi64[(j0 + jb - 1) >> 6] && trow0 + PR <= n) {
+  if (hi64 != nullptr && blockIdx.x != 0 &&
+      ((trow0 > hi64[(j0 + jb - 1) >> 6] && trow0 + PR <= n) || (trow0 >= hole_lo && trow0 + PR <= hole_hi))) {
     if (threadIdx.x == 0) atomicAdd(&arrive[j0 >> 6], 1);
     return;
   }
@@ -384,7 +403,8 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
 // ------------------------------------------------------------------------------------------------
 template <int TM, bool VEC>
 __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
-    chol_syrk_kernel(double* __restrict__ A, int n, int J, int kb, int strip, const int* __restrict__ hi64) {
+    chol_syrk_kernel(double* __restrict__ A, int n, int J, int kb, int strip, const int* __restrict__ hi64,
+                     const ChainArgs ca, int tile_na, int tile_skip) {
   constexpr int F = TM / 64;
   constexpr int KC = 16;
   constexpr int LD = TM + 2;
@@ -409,6 +429,9 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
     while (bi * (bi + 1) / 2 > t) bi--;
     bj = t - bi * (bi + 1) / 2;
   }
+  // chain mode: the launch enumerates only the tile rows / columns that are not entirely inside the hole
+  if (bi >= tile_na) bi += tile_skip;
+  if (bj >= tile_na) bj += tile_skip;
   const int r0 = J + kb;
   const int i0 = r0 + bi * TM, c0 = r0 + bj * TM;
   const int rows = min(TM, n + 1 - i0);
@@ -418,6 +441,14 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
     const int hi = hi64[(J + kb - 1) >> 6];
     if (c0 > hi || (i0 > hi && i0 + rows <= n)) return;
   }
+  if ((i0 >= ca.hole_lo && i0 + rows <= ca.hole_hi) || (c0 >= ca.hole_lo && c0 + cols <= ca.hole_hi)) return;
+  auto in_hole = [&](int g) { return g >= ca.hole_lo && g < ca.hole_hi; };
+  // C element (gr, gc), gc even: in A, or in the chain's scratch copy of the separator block
+  auto c_ptr = [&](int gr, int gc) -> double* {
+    if (VEC && ca.scr != nullptr && gr >= ca.sep && gc >= ca.sep)
+      return ca.scr + (size_t)(gr - ca.sep) * ca.lds + (gc - ca.sep);
+    return A + (size_t)gr * n + gc;
+  };
   const int tid = threadIdx.x;
   const int ty = tid >> 4, tx = tid & 15;
   double acc[F * 4][F * 4];
@@ -472,7 +503,7 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
       const int r = idx / (TM / 2), c = 2 * (idx % (TM / 2));
       if (r < rows && c < cols) {
         const unsigned dst = (unsigned)__cvta_generic_to_shared(Cs + r * TM + c);
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(A + (size_t)(i0 + r) * n + c0 + c));
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(c_ptr(i0 + r, c0 + c)));
       }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -515,7 +546,7 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
 #pragma unroll
   for (int a = 0; a < F * 4; a++) {
     const int r = (a >> 2) * 64 + ((a >> 1) & 1) * 32 + ty * 2 + (a & 1);
-    if (r >= rows) continue;
+    if (r >= rows || in_hole(i0 + r)) continue;
     double* dst = A + (size_t)(i0 + r) * n + c0;
     const int cmax = min(cols - 1, i0 + r - c0);  // lower triangle only
     double cv[F * 4];
@@ -531,10 +562,12 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
 #pragma unroll
       for (int b = 0; b < F * 4; b += 2) {
         const int c = (b >> 2) * 64 + ((b >> 1) & 1) * 32 + tx * 2;
+        if (c > cmax || in_hole(c0 + c)) continue;
+        double* d2 = c_ptr(i0 + r, c0 + c);
         if (c + 1 <= cmax) {
-          *reinterpret_cast<double2*>(dst + c) = make_double2(cv[b] - acc[a][b], cv[b + 1] - acc[a][b + 1]);
-        } else if (c <= cmax) {
-          dst[c] = cv[b] - acc[a][b];
+          *reinterpret_cast<double2*>(d2) = make_double2(cv[b] - acc[a][b], cv[b + 1] - acc[a][b + 1]);
+        } else {
+          d2[0] = cv[b] - acc[a][b];
         }
       }
     } else {
@@ -743,7 +776,8 @@ static constexpr int kBwdPThreads = 512;
 static size_t bwd_persist_smem(int n) { return ((size_t)n + 64 + 2 * 64 * 64 + 64 + 64) * sizeof(double); }
 
 __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(double* __restrict__ A, int n,
-                                                                           const int* __restrict__ lo64) {
+                                                                           const int* __restrict__ lo64,
+                                                                           const Ranges rg) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* Dsm = reinterpret_cast<double*>(smem_raw);      // [2][64][64]
   double* xs = Dsm + 2 * 64 * 64;                          // [64]
@@ -801,8 +835,11 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
     }
     __syncthreads();
     // y[c] -= sum_r L[o + r][c] x[r] for the columns left of the block
-    const int lo = lo64 != nullptr ? max(0, min(lo64[blk], o)) & ~1 : 0;
-    for (int c = lo + tid; c < o; c += kBwdPThreads) {
+    for (int sg = 0; sg <= rg.k; sg++) {
+    // columns of range sg that the rows of this block reach into
+    const int hi = min(rg.b[sg + 1], o);
+    const int lo = max(rg.b[sg], min(lo64[sg * nblk + blk], hi)) & ~1;
+    for (int c = lo + tid; c < hi; c += kBwdPThreads) {
       const double* col = A + (size_t)o * n + c;
       double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
       int r = 0;
@@ -816,29 +853,58 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
       for (; r < jb; r++) s0 = fma(col[(size_t)r * n], xs[r], s0);
       ys[c] -= (s0 + s1) + (s2 + s3);
     }
+    }
   }
   __syncthreads();
   for (int i = tid; i < n; i += kBwdPThreads) y[i] = ys[i];
 }
 
-// Envelope summary per 64-block from first[r] = first structurally non-zero column of row r (fill-in of a Cholesky
-// factor stays inside the row envelopes):
-//   hi64[c] = last row with an entry in a column <= 64c+63  (monotone in c; >= the block's own last row)
-//   lo64[b] = first column used by the rows of block b
-__global__ void __launch_bounds__(1024) chol_env_kernel(const int* __restrict__ first, int n, int* __restrict__ hi64,
-                                                        int* __restrict__ lo64) {
+// Envelope summary per 64-block and range.  firstc[c * n + r] = first structurally non-zero column of row r inside
+// range c (fill-in of a Cholesky factor stays inside these per-range row envelopes); a value
+// outside [b[c], min(r, b[c+1] - 1)] means "row r has nothing in range c", except in the row's own range, where it is
+// clamped.
+//   hi64[c * nb + blk] = last row with an entry in a column of range c that is <= 64 blk + 63  (monotone inside c)
+//   lo64[c * nb + blk] = first column of range c used by the rows of block blk  (INT_MAX: none)
+__global__ void __launch_bounds__(1024) chol_env_kernel(const int* __restrict__ firstc, int n, const Ranges rg,
+                                                        int* __restrict__ hi64, int* __restrict__ lo64) {
   const int nb = (n + 63) >> 6;
-  for (int c = threadIdx.x; c < nb; c += 1024) { hi64[c] = min(64 * c + 63, n - 1); lo64[c] = 64 * c; }
-  __syncthreads();
-  for (int r = threadIdx.x; r < n; r += 1024) {
-    const int f = max(0, min(first[r], r));
-    atomicMax(&hi64[f >> 6], r);
-    atomicMin(&lo64[r >> 6], f);
+  for (int e = threadIdx.x; e < (rg.k + 1) * nb; e += 1024) {
+    const int c = e / nb, blk = e - c * nb;
+    hi64[e] = min(64 * blk + 63, rg.b[c + 1] - 1);
+    lo64[e] = 0x7fffffff;
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    int run = 0;
-    for (int c = 0; c < nb; c++) { run = max(run, hi64[c]); hi64[c] = run; }
+  for (int e = threadIdx.x; e < (rg.k + 1) * n; e += 1024) {
+    const int c = e / n, r = e - c * n;
+    int f = firstc[e];
+    const int top = min(r, rg.b[c + 1] - 1);
+    if (r >= rg.b[c] && r < rg.b[c + 1]) f = max(rg.b[c], min(f, r));   // own range: at least the diagonal
+    else if (f < rg.b[c] || f > top) continue;
+    atomicMax(&hi64[c * nb + (f >> 6)], r);
+    atomicMin(&lo64[c * nb + (r >> 6)], f);
+  }
+  __syncthreads();
+  if (threadIdx.x <= rg.k) {
+    const int c = threadIdx.x;
+    if (rg.b[c + 1] > rg.b[c]) {
+      int run = 0;
+      for (int blk = rg.b[c] >> 6; blk <= (rg.b[c + 1] - 1) >> 6; blk++) {
+        run = max(run, hi64[c * nb + blk]);
+        hi64[c * nb + blk] = run;
+      }
+    }
+  }
+}
+
+// A[r][c] += sum of the chains' scratch copies, r in [sep, n], c in [sep, min(r, n - 1)]
+__global__ void chol_merge_kernel(double* __restrict__ A, int n, int sep, const double* __restrict__ scr, int nscr,
+                                  size_t scr_stride, int lds) {
+  const int r = sep + blockIdx.x;
+  const int cmax = min(r, n - 1);
+  for (int c = sep + threadIdx.x; c <= cmax; c += blockDim.x) {
+    double acc = 0.0;
+    for (int q = 0; q < nscr; q++) acc += scr[q * scr_stride + (size_t)(r - sep) * lds + (c - sep)];
+    A[(size_t)r * n + c] += acc;
   }
 }
 
@@ -846,25 +912,58 @@ __global__ void __launch_bounds__(1024) chol_env_kernel(const int* __restrict__ 
 
 using namespace droid;
 
-extern "C" size_t droid_chol_workspace_bytes(int n) {
+static size_t chol_ws_ints(int n, int k) {
   const size_t nb = (size_t)((n > 0 ? n : 0) + 63) / 64;
-  return 256 + 3 * nb * sizeof(int);   // panel check-in counters | hi64 | lo64 of the envelope variant
+  return (size_t)(k + 1) * (3 * nb + 1);   // panel check-in counters | hi64 | lo64, per range
 }
+
+extern "C" size_t droid_chol_chains_workspace_bytes(int n, int nchains, int sep_rows) {
+  const size_t head = (256 + chol_ws_ints(n, nchains > 0 ? nchains : 0) * sizeof(int) + 255) / 256 * 256;
+  const size_t scr = nchains > 1 ? (size_t)(nchains - 1) * (size_t)(sep_rows + 1) * (size_t)sep_rows * sizeof(double) : 0;
+  return head + scr;
+}
+
+extern "C" size_t droid_chol_workspace_bytes(int n) { return droid_chol_chains_workspace_bytes(n, 0, 0); }
 
 extern "C" int droid_chol_solve_f64(double* A, double* b, int n, int* info_dev, void* workspace,
                                     size_t workspace_bytes, void* stream) {
-  return droid_chol_solve_env_f64(A, b, n, nullptr, info_dev, workspace, workspace_bytes, stream);
+  return droid_chol_solve_chains_f64(A, b, n, nullptr, 0, nullptr, info_dev, workspace, workspace_bytes, stream);
 }
 
 extern "C" int droid_chol_solve_env_f64(double* A, double* b, int n, const int* first_dev, int* info_dev,
                                         void* workspace, size_t workspace_bytes, void* stream) {
+  return droid_chol_solve_chains_f64(A, b, n, first_dev, 0, nullptr, info_dev, workspace, workspace_bytes, stream);
+}
+
+namespace {
+struct ChainCtx {
+  cudaStream_t main = nullptr, side = nullptr;
+  cudaEvent_t fork = nullptr, p = nullptr, r = nullptr, join = nullptr, done = nullptr;
+};
+struct ChainState {
+  int J, Jend;
+  bool on_side, finished;
+  cudaStream_t main;
+  ChainCtx* cx;
+  ChainArgs ca;
+  const int* hi64;
+  int* arrive;
+  bool prof;
+};
+}  // namespace
+
+extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const int* firstc_dev, int nchains,
+                                           const int* chain_end, int* info_dev, void* workspace,
+                                           size_t workspace_bytes, void* stream) {
   if (n < 0 || !info_dev) return DROID_ERR_INVALID_ARGUMENT;
   if (n == 0) return DROID_OK;
   if (!A || !b) return DROID_ERR_INVALID_ARGUMENT;
   if (b != A + (size_t)n * n) return DROID_ERR_INVALID_ARGUMENT;  // rhs must be row n of A
+  if (nchains < 0 || nchains > kMaxChains || (nchains > 0 && (!chain_end || !firstc_dev))) return DROID_ERR_INVALID_ARGUMENT;
   cudaStream_t st = (cudaStream_t)stream;
   cudaMemsetAsync(info_dev, 0, sizeof(int), st);
   if (n <= kSmallMax) {
+    if (nchains > 0) return DROID_ERR_INVALID_ARGUMENT;
     static bool attr_set = false;
     if (!attr_set) {
       cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmemMax);
@@ -884,115 +983,205 @@ extern "C" int droid_chol_solve_env_f64(double* A, double* b, int n, const int* 
     cudaFuncSetAttribute(chol_syrk_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
     cudaFuncSetAttribute(chol_syrk_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk64);
     cudaFuncSetAttribute(chol_syrk_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk64);
+    cudaFuncSetAttribute(chol_bwd_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)bwd_persist_smem(kBwdPersistMax));
     attr2 = true;
   }
   const bool vec = (n % 2 == 0) && (((uintptr_t)A & 15) == 0);
-  // Envelope variant: the launches keep their dense shapes (the host never learns the structure), CTAs whose rows
-  // or columns lie outside the envelope return at once.  64x64 tiles throughout: the active window is narrow.
+  const int nb = (n + 63) / 64;
+  // ranges: chains [chain_end[c-1], chain_end[c]) and the separator [chain_end[nchains-1], n)
+  Ranges rg;
+  rg.k = nchains;
+  rg.b[0] = 0;
+  for (int c = 0; c < nchains; c++) {
+    const int e = chain_end[c];
+    if (e <= rg.b[c] || e >= n || (e & 1)) return DROID_ERR_INVALID_ARGUMENT;
+    rg.b[c + 1] = e;
+  }
+  rg.b[nchains + 1] = n;
+  const int sep = rg.b[nchains], seprows = n - sep;
+  if (nchains > 0 && (!vec || n > kBwdPersistMax)) return DROID_ERR_INVALID_ARGUMENT;
+  if (!workspace || workspace_bytes < droid_chol_chains_workspace_bytes(n, nchains, nchains > 1 ? seprows : 0))
+    return DROID_ERR_WORKSPACE_TOO_SMALL;
+  // Envelope variant: the launches keep their dense shapes (the host never learns the band structure), CTAs whose
+  // rows or columns lie outside the envelope return at once.  64x64 tiles throughout: the active window is narrow.
+  int* arrive = reinterpret_cast<int*>(workspace);
   int* hi64 = nullptr;
   int* lo64 = nullptr;
-  if (!workspace || workspace_bytes < droid_chol_workspace_bytes(n)) return DROID_ERR_WORKSPACE_TOO_SMALL;
-  int* arrive = reinterpret_cast<int*>(workspace);
-  cudaMemsetAsync(arrive, 0, (size_t)((n + 63) / 64) * sizeof(int), st);
-  if (first_dev != nullptr) {
-    hi64 = arrive + (n + 63) / 64;
-    lo64 = hi64 + (n + 63) / 64;
-    DROID_LAUNCH chol_env_kernel<<<1, 1024, 0, st>>>(first_dev, n, hi64, lo64);
+  cudaMemsetAsync(arrive, 0, (size_t)(nchains + 1) * (nb + 1) * sizeof(int), st);
+  if (firstc_dev != nullptr) {
+    hi64 = arrive + (size_t)(nchains + 1) * (nb + 1);
+    lo64 = hi64 + (size_t)(nchains + 1) * nb;
+    DROID_LAUNCH chol_env_kernel<<<1, 1024, 0, st>>>(firstc_dev, n, rg, hi64, lo64);
   }
-  // Look-ahead: while the bulk of trailing update J runs on the caller's stream, a second (high-priority) stream
+  double* scr = nullptr;
+  const size_t scr_stride = (size_t)(seprows + 1) * (size_t)seprows;
+  if (nchains > 1) {
+    const size_t head = (256 + chol_ws_ints(n, nchains) * sizeof(int) + 255) / 256 * 256;
+    scr = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(workspace) + head);
+    cudaMemsetAsync(scr, 0, (size_t)(nchains - 1) * scr_stride * sizeof(double), st);
+  }
+  // Look-ahead: while the bulk of trailing update J runs on the chain's main stream, a second (high-priority) stream
   // updates the next panel's 128 columns first and factorises them, so the serial panel chain hides behind the
   // SYRK for as long as the SYRK is the longer of the two.
   //   side : P(0) F(0) P(1) [wait R(0)] F(1) P(2) [wait R(1)] F(2) ...      P = panel, F = first block column
   //   main :      [wait P(0)] R(0)   [wait P(1)] R(1) ...                    R = rest of the trailing update
-  static cudaStream_t side = nullptr;
-  static cudaEvent_t ev_fork = nullptr, ev_p = nullptr, ev_r = nullptr, ev_join = nullptr;
-  static int side_dev = -1;
+  // Chain mode runs one such pair of streams per chain, all forked from the caller's stream.
+  static ChainCtx ctx[kMaxChains];
+  static cudaEvent_t ev_start = nullptr;
+  static int ctx_dev = -1;
   int dev = 0;
   cudaGetDevice(&dev);
-  if (side_dev != dev) {
+  if (ctx_dev != dev) {
     int lo = 0, hi = 0;
     cudaDeviceGetStreamPriorityRange(&lo, &hi);
-    cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, hi);
-    cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_p, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_r, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming);
-    side_dev = dev;
-  }
-  auto lookahead_ok = [&](int J) {
-    const int r0 = J + PB;
-    if (!vec || r0 >= n) return false;
-    return n + 1 - r0 >= 4 * PB;   // at least a few tiles of trailing matrix left to overlap with
-  };
-  bool on_side = lookahead_ok(0);
-  if (on_side) {
-    cudaEventRecord(ev_fork, st);
-    cudaStreamWaitEvent(side, ev_fork, 0);
-  }
-  for (int J = 0; J < n; J += PB) {
-    const int kb = (n - J) < PB ? (n - J) : PB;
-    if (on_side && !lookahead_ok(J)) {   // leave look-ahead mode: everything back on the caller's stream
-      cudaEventRecord(ev_join, side);
-      cudaStreamWaitEvent(st, ev_join, 0);
-      on_side = false;
+    for (int c = 0; c < kMaxChains; c++) {
+      cudaStreamCreateWithPriority(&ctx[c].side, cudaStreamNonBlocking, hi);
+      cudaStreamCreateWithFlags(&ctx[c].main, cudaStreamNonBlocking);
+      cudaEventCreateWithFlags(&ctx[c].fork, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&ctx[c].p, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&ctx[c].r, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&ctx[c].join, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&ctx[c].done, cudaEventDisableTiming);
     }
-    cudaStream_t ps = on_side ? side : st;
-    prof_mark(DROID_PROF_CHOL_PANEL, true, ps);
+    cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming);
+    ctx_dev = dev;
+  }
+  // one outer panel (128 columns) of one range: factorise it, update what lies below / to the right
+  auto step = [&](ChainState& cs) {
+    const int J = cs.J;
+    const int kb = (cs.Jend - J) < PB ? (cs.Jend - J) : PB;
+    auto lookahead_ok = [&](int JJ) {
+      const int r0 = JJ + PB;
+      if (!vec || r0 + PB > cs.Jend) return false;   // the next panel is a full one of the same range
+      return n + 1 - r0 >= 4 * PB;   // at least a few tiles of trailing matrix left to overlap with
+    };
+    cudaStream_t m = cs.main;
+    ChainCtx& cx = *cs.cx;
+    if (cs.on_side && !lookahead_ok(J)) {   // leave look-ahead mode: everything back on the main stream
+      cudaEventRecord(cx.join, cx.side);
+      cudaStreamWaitEvent(m, cx.join, 0);
+      cs.on_side = false;
+    }
+    cudaStream_t ps = cs.on_side ? cx.side : m;
+    if (cs.prof) prof_mark(DROID_PROF_CHOL_PANEL, true, ps);
     for (int j0 = J; j0 < J + kb; j0 += NB) {
       const int jb = (J + kb - j0) < NB ? (J + kb - j0) : NB;
       const int rem_rows = n + 1 - (j0 + jb);  // >= 1 (the rhs row)
-      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PR - 1) / PR, 256, kPanelSmem, ps>>>(A, n, j0, jb, info_dev, hi64, arrive, vec ? 1 : 0);
+      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PR - 1) / PR, 256, kPanelSmem, ps>>>(
+          A, n, j0, jb, info_dev, hi64 ? cs.hi64 : nullptr, cs.arrive, vec ? 1 : 0, cs.ca.hole_lo, cs.ca.hole_hi);
       const int rest = J + kb - (j0 + jb);     // columns of this outer panel still to factorise
       if (rest > 0) {
         // rank-64 update of the panel's remaining columns only (64x64 tiles of one block column, all SMs)
         const int t64 = (rem_rows + 63) / 64;
-        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest, hi64);
-        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest, hi64);
+        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest, hi64 ? cs.hi64 : nullptr, cs.ca, 1 << 30, 0);
+        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest, hi64 ? cs.hi64 : nullptr, cs.ca, 1 << 30, 0);
       }
     }
-    prof_mark(DROID_PROF_CHOL_PANEL, false, ps);
+    if (cs.prof) prof_mark(DROID_PROF_CHOL_PANEL, false, ps);
     const int r0 = J + kb;
-    if (r0 >= n) break;
+    cs.J = r0;
+    if (r0 >= cs.Jend) cs.finished = true;
+    if (r0 >= n) return;
     const int rr = n + 1 - r0;
-    const int t128 = (rr + 127) / 128, t64 = (rr + 63) / 64;
-    if (on_side) {
-      const bool big = hi64 == nullptr && t128 * (t128 + 1) / 2 >= 148;
-      cudaEventRecord(ev_p, side);
-      cudaStreamWaitEvent(side, ev_r, 0);    // R(J-1) (no-op for the first panel)
-      if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128, 256, kSyrk128, side>>>(A, n, J, kb, PB, hi64);
-      else DROID_LAUNCH chol_syrk_kernel<64, true><<<2 * t64, 256, kSyrk64, side>>>(A, n, J, kb, PB, hi64);
-      cudaStreamWaitEvent(st, ev_p, 0);
+    const int* hi = hi64 ? cs.hi64 : nullptr;
+    // tiles of 64 rows counted from r0; those entirely inside the hole are not enumerated
+    int t64 = (rr + 63) / 64, na = 1 << 30, nskip = 0;
+    if (cs.ca.hole_hi > cs.ca.hole_lo) {
+      na = cs.ca.hole_lo > r0 ? (cs.ca.hole_lo - r0 + 63) / 64 : 0;
+      nskip = (cs.ca.hole_hi - r0) / 64 - na;
+      if (nskip < 0) nskip = 0;
+      t64 -= nskip;
+    }
+    const int t128 = (rr + 127) / 128;
+    if (cs.on_side) {
+      const bool big = hi == nullptr && t128 * (t128 + 1) / 2 >= 148;
+      cudaEventRecord(cx.p, cx.side);
+      cudaStreamWaitEvent(cx.side, cx.r, 0);    // R(J-1) (no-op for the first panel)
+      if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128, 256, kSyrk128, cx.side>>>(A, n, J, kb, PB, hi, cs.ca, 1 << 30, 0);
+      else DROID_LAUNCH chol_syrk_kernel<64, true><<<2 * t64, 256, kSyrk64, cx.side>>>(A, n, J, kb, PB, hi, cs.ca, na, nskip);
+      cudaStreamWaitEvent(m, cx.p, 0);
       {
-        ProfScope ps2(DROID_PROF_CHOL_SYRK, st);
-        if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<(t128 - 1) * t128 / 2, 256, kSyrk128, st>>>(A, n, J, kb, -1, hi64);
-        else DROID_LAUNCH chol_syrk_kernel<64, true><<<(t64 - 2) * (t64 - 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, -2, hi64);
+        if (cs.prof) prof_mark(DROID_PROF_CHOL_SYRK, true, m);
+        if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<(t128 - 1) * t128 / 2, 256, kSyrk128, m>>>(A, n, J, kb, -1, hi, cs.ca, 1 << 30, 0);
+        else if (t64 > 2) DROID_LAUNCH chol_syrk_kernel<64, true><<<(t64 - 2) * (t64 - 1) / 2, 256, kSyrk64, m>>>(A, n, J, kb, -2, hi, cs.ca, na, nskip);
+        if (cs.prof) prof_mark(DROID_PROF_CHOL_SYRK, false, m);
       }
-      cudaEventRecord(ev_r, st);
+      cudaEventRecord(cx.r, m);
     } else {
-      ProfScope ps2(DROID_PROF_CHOL_SYRK, st);
-      if (hi64 == nullptr && t128 * (t128 + 1) / 2 >= 148) {
-        if (vec) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb, 0, hi64);
-        else DROID_LAUNCH chol_syrk_kernel<128, false><<<t128 * (t128 + 1) / 2, 256, kSyrk128, st>>>(A, n, J, kb, 0, hi64);
+      if (cs.prof) prof_mark(DROID_PROF_CHOL_SYRK, true, m);
+      if (hi == nullptr && t128 * (t128 + 1) / 2 >= 148) {
+        if (vec) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128 * (t128 + 1) / 2, 256, kSyrk128, m>>>(A, n, J, kb, 0, hi, cs.ca, 1 << 30, 0);
+        else DROID_LAUNCH chol_syrk_kernel<128, false><<<t128 * (t128 + 1) / 2, 256, kSyrk128, m>>>(A, n, J, kb, 0, hi, cs.ca, 1 << 30, 0);
       } else {
-        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, 0, hi64);
-        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64 * (t64 + 1) / 2, 256, kSyrk64, st>>>(A, n, J, kb, 0, hi64);
+        if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64 * (t64 + 1) / 2, 256, kSyrk64, m>>>(A, n, J, kb, 0, hi, cs.ca, na, nskip);
+        else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64 * (t64 + 1) / 2, 256, kSyrk64, m>>>(A, n, J, kb, 0, hi, cs.ca, na, nskip);
+      }
+      if (cs.prof) prof_mark(DROID_PROF_CHOL_SYRK, false, m);
+    }
+  };
+  auto open_range = [&](ChainState& cs, int c, cudaStream_t m, ChainCtx* cx, bool prof) {
+    cs.J = rg.b[c]; cs.Jend = rg.b[c + 1];
+    cs.main = m; cs.cx = cx; cs.prof = prof;
+    cs.finished = cs.J >= cs.Jend;
+    cs.ca.hole_lo = cs.ca.hole_hi = 0; cs.ca.sep = sep; cs.ca.scr = nullptr; cs.ca.lds = seprows;
+    if (c < nchains) {
+      cs.ca.hole_lo = rg.b[c + 1]; cs.ca.hole_hi = sep;
+      if (c > 0) cs.ca.scr = scr + (size_t)(c - 1) * scr_stride;
+    }
+    cs.hi64 = hi64 ? hi64 + (size_t)c * nb : nullptr;
+    cs.arrive = arrive + (size_t)c * (nb + 1);
+    const int r0 = cs.J + PB;
+    cs.on_side = vec && r0 + PB <= cs.Jend && n + 1 - r0 >= 4 * PB;
+    if (cs.on_side) {
+      cudaEventRecord(cx->fork, m);
+      cudaStreamWaitEvent(cx->side, cx->fork, 0);
+    }
+  };
+  auto close_range = [&](ChainState& cs) {
+    if (cs.on_side) {
+      cudaEventRecord(cs.cx->join, cs.cx->side);
+      cudaStreamWaitEvent(cs.main, cs.cx->join, 0);
+      cs.on_side = false;
+    }
+  };
+  if (nchains > 0) {
+    ChainState cs[kMaxChains];
+    cudaEventRecord(ev_start, st);
+    for (int c = 0; c < nchains; c++) {
+      cudaStream_t m = c == 0 ? st : ctx[c].main;
+      if (c > 0) cudaStreamWaitEvent(m, ev_start, 0);
+      open_range(cs[c], c, m, &ctx[c], c == 0);
+    }
+    // the chains' launches are issued round-robin so that all of them are in flight from the start
+    for (bool any = true; any;) {
+      any = false;
+      for (int c = 0; c < nchains; c++) {
+        if (cs[c].finished) continue;
+        step(cs[c]);
+        any = true;
       }
     }
+    for (int c = 0; c < nchains; c++) {
+      close_range(cs[c]);
+      if (c > 0) {
+        cudaEventRecord(ctx[c].done, cs[c].main);
+        cudaStreamWaitEvent(st, ctx[c].done, 0);
+      }
+    }
+    if (nchains > 1)
+      DROID_LAUNCH chol_merge_kernel<<<seprows + 1, 256, 0, st>>>(A, n, sep, scr, nchains - 1, scr_stride, seprows);
   }
-  if (on_side) {
-    cudaEventRecord(ev_join, side);
-    cudaStreamWaitEvent(st, ev_join, 0);
+  {
+    ChainState cs;
+    open_range(cs, nchains, st, &ctx[0], true);
+    while (!cs.finished) step(cs);
+    close_range(cs);
   }
   ProfScope psb(DROID_PROF_CHOL_BWD, st);
   // (dense systems of this size keep the multi-CTA sweep: 0.9 ms vs 2.0 ms for one CTA at n = 5994)
   if (vec && lo64 != nullptr && n <= kBwdPersistMax) {
-    static bool attr3 = false;
-    if (!attr3) {
-      cudaFuncSetAttribute(chol_bwd_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           (int)bwd_persist_smem(kBwdPersistMax));
-      attr3 = true;
-    }
-    DROID_LAUNCH chol_bwd_persist_kernel<<<1, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64);
+    DROID_LAUNCH chol_bwd_persist_kernel<<<1, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg);
     return check_launch();
   }
   for (int J0 = ((n - 1) / SB) * SB; J0 >= 0; J0 -= SB) {

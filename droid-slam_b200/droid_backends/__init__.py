@@ -53,6 +53,7 @@ def _load():
     lib.droid_ba_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_ba_workspace_bytes.argtypes = [ctypes.POINTER(BaParams)]
     lib.droid_chol_workspace_bytes.restype = ctypes.c_size_t
+    lib.droid_chol_chains_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_corr_build_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_launch_count.restype = ctypes.c_ulonglong
     return lib
@@ -68,7 +69,7 @@ C_ABI_SYMBOLS = [
     "droid_altcorr_forward_indexed", "droid_corr_build", "droid_corr_build_workspace_bytes",
     "droid_frame_distance", "droid_projmap", "droid_iproj", "droid_depth_filter",
     "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_solve_env_f64",
-    "droid_chol_workspace_bytes",
+    "droid_chol_workspace_bytes", "droid_chol_solve_chains_f64", "droid_chol_chains_workspace_bytes",
 ]
 
 
@@ -398,10 +399,28 @@ def ba_status(device=None):
     return int(ws[off:off + 4].view(torch.int32).item())
 
 
-def chol_solve(A, b, first=None):
+def chol_solve(A, b, first=None, chain_end=None):
     """Extension (tests/bench): solves A x = b for SPD fp64 A on the device; returns (x, info).
-    first (int32 [n], optional): first non-zero column of every row -> envelope variant."""
+    first (int32 [n], optional): first non-zero column of every row -> envelope variant.
+    chain_end (list of ints, optional) + first of shape [len(chain_end) + 1, n]: chains + separator variant
+    (droid_chol_solve_chains_f64)."""
     n = A.shape[0]
+    if chain_end is not None:
+        k = len(chain_end)
+        if first is None or first.dtype != torch.int32 or first.numel() != (k + 1) * n or not first.is_cuda:
+            raise RuntimeError("first must be a CUDA int32 tensor of (len(chain_end) + 1) * n entries")
+        with torch.cuda.device(A.device):
+            buf = torch.empty((n * n + n,), dtype=torch.float64, device=A.device)
+            buf[: n * n] = A.reshape(-1)
+            buf[n * n:] = b.reshape(-1)
+            info = torch.zeros((1,), dtype=torch.int32, device=A.device)
+            wsb = int(_lib.droid_chol_chains_workspace_bytes(n, k, n - int(chain_end[-1])))
+            ws = torch.empty((wsb,), dtype=torch.uint8, device=A.device)
+            ends = (ctypes.c_int * k)(*[int(e) for e in chain_end])
+            _check(_lib.droid_chol_solve_chains_f64(_p(buf), ctypes.c_void_p(buf.data_ptr() + 8 * n * n), n,
+                                                    _p(first.contiguous()), k, ends, _p(info), _p(ws),
+                                                    ctypes.c_size_t(wsb), _stream(A)), "chol_solve_chains")
+        return buf[n * n:].clone(), info
     with torch.cuda.device(A.device):
         buf = torch.empty((n * n + n,), dtype=torch.float64, device=A.device)
         buf[: n * n] = A.reshape(-1)

@@ -190,6 +190,19 @@ int droid_chol_solve_env_f64(double* A, double* b, int n, const int* first_dev, 
                              void* workspace, size_t workspace_bytes, void* stream);
 size_t droid_chol_workspace_bytes(int n);
 
+/* Same solve for a matrix in "chains + separator" form (the nested-dissection shape ba gives the reduced camera
+ * system of long trajectories): the columns split into nchains ranges [chain_end[c-1], chain_end[c]) (chain_end is a
+ * HOST array of even, increasing values, chain_end[-1] = 0) that are structurally decoupled from each other, followed
+ * by the separator [chain_end[nchains-1], n).  The chains are factorised concurrently (one pair of streams each),
+ * then the separator.  firstc_dev (device, int[(nchains+1) * n]): firstc[c*n + r] = first non-zero column of row r
+ * inside range c (range nchains = the separator); a value outside the range, or > r, means "none".  nchains == 0 is
+ * droid_chol_solve_env_f64 (firstc_dev may then be NULL = dense).  n must be even, A 16-byte aligned, n <= 12288.
+ * workspace: droid_chol_chains_workspace_bytes(n, nchains, n - chain_end[nchains-1]) bytes. */
+int droid_chol_solve_chains_f64(double* A, double* b, int n, const int* firstc_dev, int nchains,
+                                const int* chain_end, int* info_dev, void* workspace, size_t workspace_bytes,
+                                void* stream);
+size_t droid_chol_chains_workspace_bytes(int n, int nchains, int sep_rows);
+
 #ifdef __cplusplus
 }
 #endif

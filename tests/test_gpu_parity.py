@@ -372,6 +372,55 @@ def test_chol_solve_envelope(backends, n, bw, wide):
     assert int(info.item()) != 0
 
 
+def chains_system(n, ends, bw, seed):
+    """SPD matrix in chains + separator form: banded chains (half-bandwidth bw), separator rows that reach into a
+    random tail of every chain, dense separator.  Returns A, b, firstc [(k+1), n]."""
+    rng = np.random.default_rng(seed)
+    k = len(ends)
+    b0 = [0] + list(ends) + [n]
+    NONE = np.iinfo(np.int32).max
+    firstc = np.full((k + 1, n), NONE, np.int64)
+    A = np.zeros((n, n))
+    for c in range(k):
+        for r in range(b0[c], b0[c + 1]):
+            f = max(b0[c], r - bw)
+            firstc[c, r] = f
+            A[r, f:r] = rng.normal(size=r - f) * 0.1
+    for r in range(b0[k], n):
+        firstc[k, r] = b0[k]
+        A[r, b0[k]:r] = rng.normal(size=r - b0[k]) * 0.1
+        for c in range(k):
+            u = rng.uniform()
+            if u < 0.3:
+                continue                                            # nothing in this chain
+            f = b0[c] if u > 0.9 else int(rng.integers(max(b0[c], b0[c + 1] - 3 * bw), b0[c + 1]))
+            firstc[c, r] = f
+            A[r, f:b0[c + 1]] = rng.normal(size=b0[c + 1] - f) * 0.1 * (rng.uniform(size=b0[c + 1] - f) < 0.5)
+    A = A + A.T
+    A += np.diag(np.abs(A).sum(1) * 0.6 + 1.0)
+    return A, rng.normal(size=n), firstc.astype(np.int32)
+
+
+@pytest.mark.parametrize("n,ends,bw", [(1200, (500,), 60), (1500, (400, 902), 90), (2500, (600, 1302, 1850), 100),
+                                       (2432, (512, 1024, 1536, 2048), 64), (1000, (130, 300, 640), 200),
+                                       (3000, (700, 1400, 2100, 2700), 130)])
+def test_chol_solve_chains(backends, n, ends, bw):
+    """droid_chol_solve_chains_f64: decoupled chains factorised concurrently, separator last.  Same answer as the
+    dense solve; an indefinite pivot inside any chain or inside the separator is reported."""
+    A, b, firstc = chains_system(n, ends, bw, n + len(ends))
+    want = np.linalg.solve(A, b)
+    x, info = backends.chol_solve(cu(A), cu(b), cu(firstc), chain_end=list(ends))
+    assert int(info.item()) == 0
+    assert rel(x.cpu().numpy(), want) <= 1e-10
+    for _ in range(3):                                              # concurrency: same bits every time
+        x2, _ = backends.chol_solve(cu(A), cu(b), cu(firstc), chain_end=list(ends))
+        assert torch.equal(x, x2)
+    for bad in (ends[-1] // 2, n - 3):
+        A2 = A.copy(); A2[bad, bad] = -5.0 * n
+        _, info = backends.chol_solve(cu(A2), cu(b), cu(firstc), chain_end=list(ends))
+        assert int(info.item()) != 0
+
+
 def test_ba_tensor_core_schur_matches_cuda_core_kernel():
     """The 3xTF32 tcgen05 Schur kernel (default for frames with <= 20 edges) against the fp32 CUDA-core kernel
     (DROID_SCHUR_TC=0, separate process because the switch is read once): same dx / dz to well inside the 1e-4 budget
