@@ -23,6 +23,8 @@
 namespace droid {
 
 static constexpr int kThreads = 256;
+static constexpr int kBaMaxChains = 4;      // concurrent elimination chains of the reduced camera system
+static constexpr int kBaChainMinRows = 1536;   // smaller systems are factorised as one chain
 static constexpr int kHW_ACC = 96;  // 78 Hessian + 12 gradient values per edge, padded to 96
 
 // ------------------------------------------------------------------------------------------------
@@ -41,8 +43,8 @@ struct BaWs {
   float* W;        // [n_eta][HW]
   float* dx;       // [P][6]
   int* ppos;       // [P]   free pose -> position in the reduced system (fill-reducing order)
-  int* first;      // [6P]  row envelope of the reduced system (first non-zero column per row)
-  int* oscr;       // [5P + 2 nbuf] scratch of ba_order_kernel
+  int* first;      // [(kBaMaxChains + 1) * 6P]  row envelopes of the reduced system per column range (chol.cu: firstc)
+  int* oscr;       // [6P + 2 nbuf + 16] scratch of ba_order_kernel
   double* A;       // [6P*6P + 6P]  dense system, b appended
   void* chol;      // workspace of the factorisation
   size_t total;
@@ -73,8 +75,8 @@ static BaWs carve(void* base, const droid_ba_params* p, size_t chol_bytes) {
   w.W = (float*)take((size_t)(p->n_eta > 0 ? p->n_eta : 1) * HW * sizeof(float));
   w.dx = (float*)take((n6 > 0 ? n6 : 1) * sizeof(float));
   w.ppos = (int*)take((n6 > 0 ? n6 : 1) * sizeof(int));
-  w.first = (int*)take((n6 > 0 ? n6 : 1) * sizeof(int));
-  w.oscr = (int*)take((5 * (n6 / 6) + 2 * (size_t)p->nbuf + 8) * sizeof(int));
+  w.first = (int*)take((size_t)(kBaMaxChains + 1) * (n6 > 0 ? n6 : 1) * sizeof(int));
+  w.oscr = (int*)take((6 * (n6 / 6) + 2 * (size_t)p->nbuf + 16) * sizeof(int));
   w.A = (double*)take((n6 * n6 + n6 + 1) * sizeof(double));
   w.chol = take(chol_bytes);
   w.total = off;
@@ -225,15 +227,17 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
                                                         int t0, int P, const int* __restrict__ kmap,
                                                         int* __restrict__ ppos, int* __restrict__ first,
                                                         int* __restrict__ scr, int* __restrict__ sig, int lay0,
-                                                        int lay1) {
+                                                        int lay1, int kreq) {
   int* pos = scr;              // [P] BFS position of free pose f, -1 = not placed yet
   int* cur = pos + P;          // [P] current frontier flags
   int* cand = cur + P;         // [P] next frontier flags; later the envelope of the BFS order
   int* env = cand + P;         // [P] envelope of the natural order
   int* starhit = env + P;      // [nbuf]
   int* starmin = starhit + nbuf;  // [nbuf]
+  int* lvl = starmin + nbuf;      // [P + 1] first BFS position of every level
   __shared__ int s_warp[32];
-  __shared__ int s_seed, s_placed;
+  __shared__ int s_seed, s_placed, s_nlev;
+  __shared__ int s_nch, s_sepl[kBaMaxChains];   // chains: number, BFS level of every separator
   __shared__ unsigned long long s_prof[2];
   const int tid = threadIdx.x;
   auto valid = [&](long long i, long long j) { return i >= 0 && i < nbuf && j >= 0 && j < nbuf; };
@@ -264,7 +268,7 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
   if (s_hit) return;
   for (int f = tid; f < P; f += 1024) { pos[f] = -1; cur[f] = 0; cand[f] = 0; }
   for (int m = tid; m < nbuf; m += 1024) starhit[m] = 0;
-  if (tid == 0) s_placed = 0;
+  if (tid == 0) { s_placed = 0; s_nlev = 0; }
   __syncthreads();
   while (true) {
     if (tid == 0) s_seed = 0x7fffffff;
@@ -276,7 +280,7 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
     __syncthreads();
     const int seed = s_seed;
     if (seed == 0x7fffffff) break;
-    if (tid == 0) { pos[seed] = s_placed; cur[seed] = 1; s_placed = s_placed + 1; }
+    if (tid == 0) { pos[seed] = s_placed; cur[seed] = 1; lvl[s_nlev] = s_placed; s_nlev = s_nlev + 1; s_placed = s_placed + 1; }
     __syncthreads();
     while (true) {
       for (int e = tid; e < n_edges; e += 1024) {
@@ -308,7 +312,10 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
         placed += total;
       }
       __syncthreads();
-      if (tid == 0) s_placed = base + placed;
+      if (tid == 0) {
+        s_placed = base + placed;
+        if (placed > 0) { lvl[s_nlev] = base; s_nlev = s_nlev + 1; }
+      }
       __syncthreads();
       if (placed == 0) break;
     }
@@ -342,11 +349,105 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
     __syncthreads();
   }
   const bool use_bfs = s_prof[1] * 10ull < s_prof[0] * 7ull;
-  const int* en = use_bfs ? cand : env;
-  for (int f = tid; f < P; f += 1024) ppos[f] = use_bfs ? pos[f] : f;
-  for (int r = tid; r < 6 * P; r += 1024) first[r] = 6 * en[r / 6];
+  // Chains (long trajectories): every BFS level is a separator of the star graph (the members of a star lie in two
+  // adjacent levels), so k - 1 levels near the quantiles of the order cut it into k mutually decoupled chains.  The
+  // chains are eliminated concurrently and the separator levels last (chol.cu: droid_chol_solve_chains_f64); the
+  // last chain runs in reverse BFS order so that it, like the first, meets its separator at its end.
+  if (tid == 0) {
+    int nch = 0;
+    const int nlev = s_nlev;
+    lvl[nlev] = P;
+    if (use_bfs) {
+      for (int k = min(kreq, kBaMaxChains); k >= 2 && nch == 0; k--) {
+        bool ok = true;
+        int prev = -1, sepf = 0, cstart = 0;
+        for (int m = 1; m < k && ok; m++) {
+          const int target = (int)((long long)P * m / k);
+          int best = -1, bestd = 0x7fffffff;
+          for (int L = prev + 2; L <= nlev - 2; L++) {          // a level on either side stays with the chains
+            const int d = abs((lvl[L] + lvl[L + 1]) / 2 - target);
+            if (d < bestd) { bestd = d; best = L; }
+          }
+          if (best < 0 || lvl[best] - cstart < 22) { ok = false; break; }
+          s_sepl[m - 1] = best;
+          sepf += lvl[best + 1] - lvl[best];
+          cstart = lvl[best + 1];
+          prev = best;
+        }
+        if (ok && (P - cstart < 22 || 6 * sepf > (6 * P) / 4)) ok = false;
+        if (ok) nch = k;
+      }
+    }
+    s_nch = nch;
+  }
+  __syncthreads();
+  const int nch = s_nch;
+  if (nch == 0) {
+    const int* en = use_bfs ? cand : env;
+    for (int f = tid; f < P; f += 1024) ppos[f] = use_bfs ? pos[f] : f;
+    for (int r = tid; r < 6 * P; r += 1024) first[r] = 6 * en[r / 6];
+  } else {
+    // new position of BFS position q: chains first (the last one reversed), then the separator levels
+    int cs[kBaMaxChains], ce[kBaMaxChains], nbeg[kBaMaxChains + 1], ss[kBaMaxChains], sbeg[kBaMaxChains];
+    {
+      int c0 = 0, acc = 0;
+      for (int c = 0; c < nch; c++) {
+        cs[c] = c0;
+        ce[c] = c + 1 < nch ? lvl[s_sepl[c]] : P;
+        nbeg[c] = acc;
+        acc += ce[c] - cs[c];
+        if (c + 1 < nch) { ss[c] = lvl[s_sepl[c]]; c0 = lvl[s_sepl[c] + 1]; }
+      }
+      nbeg[nch] = acc;                                           // first separator position
+      for (int m = 0; m + 1 < nch; m++) { sbeg[m] = acc; acc += lvl[s_sepl[m] + 1] - ss[m]; }
+    }
+    auto newpos = [&](int q) {
+      for (int c = 0; c < nch; c++)
+        if (q >= cs[c] && q < ce[c]) return c == nch - 1 ? nbeg[c] + (ce[c] - 1 - q) : nbeg[c] + (q - cs[c]);
+      for (int m = 0; m + 1 < nch; m++)
+        if (q >= ss[m] && q < lvl[s_sepl[m] + 1]) return sbeg[m] + (q - ss[m]);
+      return q;
+    };
+    int* fpos = cur;   // [P] new position of free pose f
+    int* en = env;     // [P] envelope inside the current range, by new position
+    for (int f = tid; f < P; f += 1024) { fpos[f] = newpos(pos[f]); ppos[f] = fpos[f]; }
+    const int sep0 = nbeg[nch];
+    const int n6 = 6 * P;
+    __syncthreads();
+    for (int c = 0; c < nch; c++) {
+      const int lo = nbeg[c], hi = nbeg[c] + (ce[c] - cs[c]);
+      for (int m = tid; m < nbuf; m += 1024) starmin[m] = 0x7fffffff;
+      for (int q = tid; q < P; q += 1024) en[q] = 0x7fffffff;
+      __syncthreads();
+      for (int e = tid; e < n_edges; e += 1024) {
+        const long long i = ii[e], j = jj[e];
+        if (!valid(i, j)) continue;
+        const int a = (int)i - t0, b = (int)j - t0, m = kmap[i];
+        if (a >= 0 && a < P && fpos[a] >= lo && fpos[a] < hi) atomicMin(&starmin[m], fpos[a]);
+        if (b >= 0 && b < P && fpos[b] >= lo && fpos[b] < hi) atomicMin(&starmin[m], fpos[b]);
+      }
+      __syncthreads();
+      for (int e = tid; e < n_edges; e += 1024) {
+        const long long i = ii[e], j = jj[e];
+        if (!valid(i, j)) continue;
+        const int a = (int)i - t0, b = (int)j - t0, sm = starmin[kmap[i]];
+        if (a >= 0 && a < P) atomicMin(&en[fpos[a]], sm);
+        if (b >= 0 && b < P) atomicMin(&en[fpos[b]], sm);
+      }
+      __syncthreads();
+      for (int r = tid; r < n6; r += 1024) {
+        const int q = r / 6;
+        const bool mine = (q >= lo && q < hi) || q >= sep0;      // rows of this chain and of the separator
+        first[(size_t)c * n6 + r] = (mine && en[q] != 0x7fffffff) ? 6 * en[q] : 0x7fffffff;
+      }
+      __syncthreads();
+    }
+    for (int r = tid; r < n6; r += 1024) first[(size_t)nch * n6 + r] = r >= 6 * sep0 ? 6 * sep0 : 0x7fffffff;
+    if (tid <= nch && tid > 0) sig[10 + tid] = 6 * nbeg[tid];     // chain ends; the last one = first separator row
+  }
   __syncthreads();
   if (tid == 0) {
+    sig[10] = nch;
     sig[1] = (int)(hsh & 0xffffffffull); sig[2] = (int)(hsh >> 32);
     sig[3] = n_edges; sig[4] = nbuf; sig[5] = t0; sig[6] = P; sig[7] = lay0; sig[9] = lay1;
     __threadfence();
@@ -1014,10 +1115,16 @@ __global__ void ba_pose_apply_kernel(float* __restrict__ poses, const float* __r
 
 using namespace droid;
 
+// chains are only used when the separator holds at most a quarter of the rows (ba_order_kernel)
+static size_t ba_chol_bytes(int n6) {
+  if (n6 < kBaChainMinRows) return droid_chol_workspace_bytes(n6);
+  return droid_chol_chains_workspace_bytes(n6, kBaMaxChains, n6 / 4 + 8);
+}
+
 extern "C" size_t droid_ba_workspace_bytes(const droid_ba_params* p) {
   if (!p || p->nbuf <= 0 || p->ht <= 0 || p->wd <= 0 || p->t1 < p->t0 || p->n_edges < 0) return 0;
   const int n6 = 6 * (p->t1 - p->t0);
-  BaWs w = carve(nullptr, p, droid_chol_workspace_bytes(n6));
+  BaWs w = carve(nullptr, p, ba_chol_bytes(n6));
   return w.total + 256;
 }
 
@@ -1037,7 +1144,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   if (p->n_eta > 65535) return DROID_ERR_INVALID_ARGUMENT;
   const int P = p->t1 - p->t0;
   const int n6 = 6 * P;
-  const size_t chol_bytes = droid_chol_workspace_bytes(n6);
+  const size_t chol_bytes = ba_chol_bytes(n6);
   if (((uintptr_t)workspace & 255) != 0) {
     const size_t adj = 256 - ((uintptr_t)workspace & 255);
     if (workspace_bytes < adj) return DROID_ERR_WORKSPACE_TOO_SMALL;
@@ -1058,9 +1165,33 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   const bool ordered = n6 > kCholSmallMax && p->n_edges > 0;
   const int* ppos = ordered ? w.ppos : nullptr;
   const int* first = ordered ? w.first : nullptr;
-  if (ordered)
+  // long trajectories: the order also cuts the system into up to kBaMaxChains decoupled chains + a separator.  The
+  // chain boundaries are the one thing the host has to know (they shape the launch sequence of the factorisation):
+  // 5 ints read back once per call.  DROID_BA_CHAINS=0/1 turns this off, 2..4 caps the number of chains.
+  static const int chains_req = []() {
+    const char* e = getenv("DROID_BA_CHAINS");
+    const int v = e ? atoi(e) : kBaMaxChains;
+    return v < 2 ? 0 : (v > kBaMaxChains ? kBaMaxChains : v);
+  }();
+  const int kreq = (ordered && n6 >= kBaChainMinRows) ? chains_req : 0;
+  int nchains = 0;
+  int chain_end[kBaMaxChains] = {0, 0, 0, 0};
+  if (ordered) {
     DROID_LAUNCH ba_order_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->t0, P, w.kmap, w.ppos, w.first,
-                                                     w.oscr, w.status + 8, p->ht * 65536 + p->wd, p->n_eta);
+                                                     w.oscr, w.status + 8, p->ht * 65536 + p->wd, p->n_eta, kreq);
+    if (kreq > 0) {
+      static int* h_split = nullptr;
+      if (!h_split && cudaHostAlloc((void**)&h_split, 8 * sizeof(int), cudaHostAllocDefault) != cudaSuccess)
+        return DROID_ERR_CUDA;
+      if (cudaMemcpyAsync(h_split, w.status + 18, (1 + kBaMaxChains) * sizeof(int), cudaMemcpyDeviceToHost, st) !=
+              cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess)
+        return DROID_ERR_CUDA;
+      nchains = h_split[0];
+      if (nchains < 0 || nchains > kBaMaxChains) return DROID_ERR_CUDA;
+      for (int c = 0; c < nchains; c++) chain_end[c] = h_split[1 + c];
+      if (nchains > 0 && n6 - chain_end[nchains - 1] > n6 / 4 + 8) return DROID_ERR_CUDA;
+    }
+  }
 
   static bool attr_set = false;
   if (!attr_set) {
@@ -1141,7 +1272,8 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     {
       ProfScope ps(DROID_PROF_BA_SOLVE, st);
       DROID_LAUNCH ba_damp_kernel<<<(n6 + 127) / 128, 128, 0, st>>>(w.A, n6, p->lm, p->ep);
-      int rc = droid_chol_solve_env_f64(w.A, bvec, n6, first, w.status + 2, w.chol, chol_bytes, stream);
+      int rc = droid_chol_solve_chains_f64(w.A, bvec, n6, first, nchains, chain_end, w.status + 2, w.chol, chol_bytes,
+                                           stream);
       if (rc != DROID_OK) return rc;
     }
     ProfScope ps(DROID_PROF_BA_UPDATE, st);

@@ -399,6 +399,20 @@ def ba_status(device=None):
     return int(ws[off:off + 4].view(torch.int32).item())
 
 
+def ba_chains(device=None):
+    """Chain layout the last large ba() on this device factorised its reduced camera system with: a list of the chain
+    end rows (empty = one chain).  Forces a D2H copy; debug / test aid."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    ws = _ws_cache.get((device.type, device.index))
+    if ws is None:
+        return []
+    off = (-ws.data_ptr()) % 256
+    st = ws[off:off + 256].view(torch.int32).cpu().tolist()
+    if st[8] != 0x0b200c0d:
+        return []
+    return st[19:19 + st[18]]
+
+
 def chol_solve(A, b, first=None, chain_end=None):
     """Extension (tests/bench): solves A x = b for SPD fp64 A on the device; returns (x, info).
     first (int32 [n], optional): first non-zero column of every row -> envelope variant.
