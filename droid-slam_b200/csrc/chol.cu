@@ -775,9 +775,12 @@ static constexpr int kBwdPersistMax = 12288;
 static constexpr int kBwdPThreads = 512;
 static size_t bwd_persist_smem(int n) { return ((size_t)n + 64 + 2 * 64 * 64 + 64 + 64) * sizeof(double); }
 
+// One CTA sweeps one range (rows [b[c], b[c+1]), blocks of 64 rows counted from the range start).  The separator
+// (c0 = k, one CTA) goes first and also subtracts its rows' contributions from the y entries of all chains; the
+// chains (c0 = 0, k CTAs) then run concurrently, each touching only its own columns.
 __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(double* __restrict__ A, int n,
                                                                            const int* __restrict__ lo64,
-                                                                           const Ranges rg) {
+                                                                           const Ranges rg, int c0) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* Dsm = reinterpret_cast<double*>(smem_raw);      // [2][64][64]
   double* xs = Dsm + 2 * 64 * 64;                          // [64]
@@ -785,9 +788,15 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
   double* ys = rinv + 64;                                  // [n (+pad)]
   const int tid = threadIdx.x;
   double* y = A + (size_t)n * n;
-  const int nblk = (n + 63) >> 6;
+  const int nb64 = (n + 63) >> 6;
+  const int rc = c0 + blockIdx.x;                          // the range this CTA sweeps
+  const int rbeg = rg.b[rc], rend = rg.b[rc + 1];
+  if (rend <= rbeg) return;
+  const int sg0 = rc == rg.k ? 0 : rc;                     // column ranges its rows reach into: all / its own
+  const int ylo = rg.b[sg0];
+  const int nblk = (rend - rbeg + 63) >> 6;
   auto load_diag = [&](int blk, int buf) {
-    const int o = blk << 6, jb = min(64, n - o);
+    const int o = rbeg + (blk << 6), jb = min(64, rend - o);
     double* D = Dsm + buf * 4096;
     for (int e = tid; e < 64 * 32; e += kBwdPThreads) {
       const int r = e >> 5, c = 2 * (e & 31);
@@ -801,9 +810,9 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
   load_diag(nblk - 1, (nblk - 1) & 1);
-  for (int i = tid; i < n; i += kBwdPThreads) ys[i] = y[i];
+  for (int i = ylo + tid; i < rend; i += kBwdPThreads) ys[i] = y[i];
   for (int blk = nblk - 1; blk >= 0; blk--) {
-    const int o = blk << 6, jb = min(64, n - o);
+    const int o = rbeg + (blk << 6), jb = min(64, rend - o);
     double* D = Dsm + (blk & 1) * 4096;
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();                                       // diagonal block landed; previous update of ys complete
@@ -830,33 +839,34 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
         }
       }
       xs[tid] = x0; xs[tid + 32] = x1;
-      ys[o + tid] = x0;
+      if (tid < jb) ys[o + tid] = x0;
       if (tid + 32 < jb) ys[o + tid + 32] = x1;
     }
     __syncthreads();
-    // y[c] -= sum_r L[o + r][c] x[r] for the columns left of the block
-    for (int sg = 0; sg <= rg.k; sg++) {
-    // columns of range sg that the rows of this block reach into
-    const int hi = min(rg.b[sg + 1], o);
-    const int lo = max(rg.b[sg], min(lo64[sg * nblk + blk], hi)) & ~1;
-    for (int c = lo + tid; c < hi; c += kBwdPThreads) {
-      const double* col = A + (size_t)o * n + c;
-      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-      int r = 0;
+    // y[c] -= sum_r L[o + r][c] x[r] for the columns left of the block, range by range
+    const int bl0 = o >> 6, bl1 = (o + jb - 1) >> 6;      // the (absolute) 64-blocks of lo64 these rows fall into
+    for (int sg = sg0; sg <= rc; sg++) {
+      const int hi = min(rg.b[sg + 1], o);
+      const int l = min(lo64[sg * nb64 + bl0], lo64[sg * nb64 + bl1]);
+      const int lo = max(rg.b[sg], min(l, hi)) & ~1;
+      for (int c = lo + tid; c < hi; c += kBwdPThreads) {
+        const double* col = A + (size_t)o * n + c;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        int r = 0;
 #pragma unroll 4
-      for (; r + 3 < jb; r += 4) {
-        s0 = fma(col[(size_t)r * n], xs[r], s0);
-        s1 = fma(col[(size_t)(r + 1) * n], xs[r + 1], s1);
-        s2 = fma(col[(size_t)(r + 2) * n], xs[r + 2], s2);
-        s3 = fma(col[(size_t)(r + 3) * n], xs[r + 3], s3);
+        for (; r + 3 < jb; r += 4) {
+          s0 = fma(col[(size_t)r * n], xs[r], s0);
+          s1 = fma(col[(size_t)(r + 1) * n], xs[r + 1], s1);
+          s2 = fma(col[(size_t)(r + 2) * n], xs[r + 2], s2);
+          s3 = fma(col[(size_t)(r + 3) * n], xs[r + 3], s3);
+        }
+        for (; r < jb; r++) s0 = fma(col[(size_t)r * n], xs[r], s0);
+        ys[c] -= (s0 + s1) + (s2 + s3);
       }
-      for (; r < jb; r++) s0 = fma(col[(size_t)r * n], xs[r], s0);
-      ys[c] -= (s0 + s1) + (s2 + s3);
-    }
     }
   }
   __syncthreads();
-  for (int i = tid; i < n; i += kBwdPThreads) y[i] = ys[i];
+  for (int i = ylo + tid; i < rend; i += kBwdPThreads) y[i] = ys[i];
 }
 
 // Envelope summary per 64-block and range.  firstc[c * n + r] = first structurally non-zero column of row r inside
@@ -1181,7 +1191,9 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
   ProfScope psb(DROID_PROF_CHOL_BWD, st);
   // (dense systems of this size keep the multi-CTA sweep: 0.9 ms vs 2.0 ms for one CTA at n = 5994)
   if (vec && lo64 != nullptr && n <= kBwdPersistMax) {
-    DROID_LAUNCH chol_bwd_persist_kernel<<<1, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg);
+    DROID_LAUNCH chol_bwd_persist_kernel<<<1, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg, nchains);
+    if (nchains > 0)
+      DROID_LAUNCH chol_bwd_persist_kernel<<<nchains, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg, 0);
     return check_launch();
   }
   for (int J0 = ((n - 1) / SB) * SB; J0 >= 0; J0 -= SB) {
