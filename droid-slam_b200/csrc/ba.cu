@@ -39,6 +39,7 @@ struct BaWs {
   int* fill;       // [nbuf] scratch counters
   float* gij;      // [n_edges][kEdgeStride] relative pose of every edge (tij, qij) and N = -Ad(g_ij)^T
   float* ey;       // [n_edges][8] y_e = N_e^T dx[source pose] for the depth back-substitution
+  float* ejc;      // [n_edges][5][HW] packed E_j of every pixel-edge (ba_lin.cuh), written by pass 1 for pass 2
   float* Q;        // [n_eta][HW]
   float* W;        // [n_eta][HW]
   float* dx;       // [P][6]
@@ -79,6 +80,8 @@ static BaWs carve(void* base, const droid_ba_params* p, size_t chol_bytes) {
   w.oscr = (int*)take((6 * (n6 / 6) + 2 * (size_t)p->nbuf + 16) * sizeof(int));
   w.A = (double*)take((n6 * n6 + n6 + 1) * sizeof(double));
   w.chol = take(chol_bytes);
+  // last, so that the offsets of everything above (the cached pose order included) do not depend on motion_only
+  w.ejc = (float*)take(p->motion_only ? 16 : (size_t)(p->n_edges > 0 ? p->n_edges : 1) * kEjComp * HW * sizeof(float));
   w.total = off;
   return w;
 }
@@ -587,7 +590,8 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
     const int* __restrict__ status, const int* __restrict__ kx, const int* __restrict__ eptr,
     const int* __restrict__ eidx, float* __restrict__ Qo, float* __restrict__ Wo,
     double* __restrict__ A, double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P,
-    int n_eta, int motion_only, int frame_lo, int frame_hi, const int* __restrict__ ppos) {
+    int n_eta, int motion_only, int frame_lo, int frame_hi, const int* __restrict__ ppos,
+    float* __restrict__ ejc) {
   __shared__ float Cs[kSlabMax];
   __shared__ float Bs[kSlabMax];
   __shared__ float Ds[kSlabMax];   // inverse depths of the slab (re-read for every edge of the frame)
@@ -660,6 +664,13 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
         bz += L.wv_d * L.rv * L.Jz_v;
         Cs[p - p0] += c;
         Bs[p - p0] += bz;
+        if (!motion_only) {   // E_j for the Schur pass (streaming stores, read once by another kernel)
+          float pk[5];
+          ej_pack(L, K, pk);
+          float* dst = ejc + (size_t)s_e[ei] * kEjComp * HW + p;
+#pragma unroll
+          for (int q = 0; q < kEjComp; q++) __stcg(dst + (size_t)q * HW, pk[q]);
+        }
         if (!stereo) {
           int l = 0;
 #pragma unroll
@@ -792,9 +803,7 @@ __device__ __forceinline__ void flush_block(double* __restrict__ A, int n6, cons
 static constexpr int kSchurSmemBytes = 200 * 1024;
 
 __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
-    const float* __restrict__ disps, const float* __restrict__ intrinsics,
-    const float* __restrict__ targets, const float* __restrict__ weights,
-    const int64_t* __restrict__ jj, const float* __restrict__ gij, int* __restrict__ status,
+    const float* __restrict__ ejc, const int64_t* __restrict__ jj, const float* __restrict__ gij, int* __restrict__ status,
     const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
     const float* __restrict__ Qi, const float* __restrict__ Wi, double* __restrict__ A,
     double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P, int n_eta, int frame_lo,
@@ -832,7 +841,6 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
   int* s_jx = s_e + deg;
   float* s_g = reinterpret_cast<float*>(s_jx + deg);
   s_g += (4 - ((reinterpret_cast<uintptr_t>(s_g) >> 2) & 3)) & 3;   // 16-byte aligned
-  const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
   const int n6 = 6 * P;
   for (int i = tid; i < deg; i += kThreads) {
     const int e = eidx[e0 + i];
@@ -859,7 +867,6 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
   const int slots = ntiles >= kThreads ? kThreads : ntiles;
   const int g = tid / slots, tslot = tid - g * slots;
   const int npass = (ntiles + slots - 1) / slots;
-  const float* __restrict__ dmap = disps + (size_t)k * HW;
   __syncthreads();
 
   for (int pass = 0; pass < npass; pass++) {
@@ -885,38 +892,24 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
         const int p = pt + tid;
         float* Erow = Es + (size_t)tid * stride;
         float Ei[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        const float dp = dmap[p];
-        float n_tu, n_tv, n_wu, n_wv;
+        float nx[kEjComp];
         auto fetch = [&](int i) {
-          const size_t base = (size_t)s_e[i] * 2 * HW + p;
-          n_tu = __ldg(targets + base); n_tv = __ldg(targets + base + HW);
-          n_wu = __ldg(weights + base); n_wv = __ldg(weights + base + HW);
+          const float* src = ejc + (size_t)s_e[i] * kEjComp * HW + p;
+#pragma unroll
+          for (int q = 0; q < kEjComp; q++) nx[q] = __ldcs(src + (size_t)q * HW);
         };
         if (deg > 0) fetch(0);
         for (int ei = e0; ei < e1; ei++) {
           const int i = ei - e0;
-          const int jx = s_jx[i];
-          const float tu = n_tu, tv = n_tv, wu = n_wu, wv = n_wv;
-          if (i + 1 < deg) fetch(i + 1);     // next edge's inputs are in flight while this one is linearised
-          SE3 gg;
-          {
-            const float4 ga = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i);
-            const float4 gb = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i + 4);
-            gg.t[0] = ga.x; gg.t[1] = ga.y; gg.t[2] = ga.z;
-            gg.q[0] = ga.w; gg.q[1] = gb.x; gg.q[2] = gb.y; gg.q[3] = gb.z;
-          }
-          PixLinJ L;
-          linearise_j(gg, K, wd, p, dp, tu, tv, wu, wv, jx == k, L);
-          const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
+          float pk[kEjComp];
+#pragma unroll
+          for (int q = 0; q < kEjComp; q++) pk[q] = nx[q];
+          if (i + 1 < deg) fetch(i + 1);     // the next edge's packed E_j is in flight while this one is expanded
           float* Ej = Erow + 6 * (ei - e0 + 1);
           float ej[6];
+          ej_unpack(pk, ej);
 #pragma unroll
-          for (int n = 0; n < 6; n++) {
-            float ej_n = au * L.Jj_u[n];
-            ej_n += av * L.Jj_v[n];
-            ej[n] = ej_n;
-            Ej[n] = ej_n;
-          }
+          for (int n = 0; n < 6; n++) Ej[n] = ej[n];
           // E_i = N E_j (the source-pose Jacobian is a per-edge linear image of the target-pose one)
           const float* N = s_g + kEdgeStride * i + 8;
 #pragma unroll
@@ -1226,7 +1219,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
         DROID_LAUNCH ba_accum_kernel<<<dim3(S, p->n_eta), kThreads, 0, st>>>(
             disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, w.gij, w.status, w.kx,
             w.eptr, w.eidx, w.Q, w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, p->motion_only,
-            frame_lo, frame_hi, ppos);
+            frame_lo, frame_hi, ppos, w.ejc);
       }
       if (!p->motion_only) {
         ProfScope ps(DROID_PROF_BA_SCHUR, st);
@@ -1252,11 +1245,11 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
           so = s2;
         }
         DROID_LAUNCH ba_schur_kernel<<<dim3(S, p->n_eta), kThreads, kSchurSmemBytes, so>>>(
-            disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q,
+            w.ejc, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q,
             w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, use_tc ? kSchurTcMaxD : 0);
         if (use_tc) {
           cudaEventRecord(ev_join, s2);
-          if (launch_schur_tc(disps, intrinsics, targets, weights, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
+          if (launch_schur_tc(w.ejc, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
                               w.A, bvec, HW, p->wd, slab, S, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, st))
             return DROID_ERR_CUDA;
           cudaStreamWaitEvent(st, ev_join, 0);

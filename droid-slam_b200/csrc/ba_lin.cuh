@@ -17,7 +17,33 @@ struct PixLinJ {
   float wu_d, wv_d;
   float wu, wv;
   float ru, rv;
+  float xd, yd, hd;   // x/z, y/z, h/z of the transformed point (what the Jacobian rows are made of)
 };
+
+// The Schur kernels need, per pixel-edge, only the 6-vector E_j = wu Jz_u Jj_u + wv Jz_v Jj_v.  The accumulation
+// kernel has the linearisation in registers anyway and leaves E_j behind in 5 floats,
+//   a = wu Jz_u fx,  b = wv Jz_v fy,  xd,  yd,  hd,
+// from which the six components follow with a dozen flops (Jj_u = fx [hd, 0, -xd hd, -xd yd, 1 + xd^2, -yd],
+// Jj_v = fy [0, hd, -yd hd, -1 - yd^2, xd yd, xd]); the Schur kernels then stream 20 bytes per pixel-edge instead of
+// redoing the projection.  Layout: ejc[(edge * 5 + component) * HW + pixel].
+static constexpr int kEjComp = 5;
+
+__device__ __forceinline__ void ej_pack(const PixLinJ& L, const Intr& K, float (&c)[5]) {
+  c[0] = (L.wu * L.Jz_u) * K.fx;
+  c[1] = (L.wv * L.Jz_v) * K.fy;
+  c[2] = L.xd; c[3] = L.yd; c[4] = L.hd;
+}
+
+__device__ __forceinline__ void ej_unpack(const float (&c)[5], float (&ej)[6]) {
+  const float a = c[0], b = c[1], xd = c[2], yd = c[3], hd = c[4];
+  const float xy = xd * yd;
+  ej[0] = a * hd;
+  ej[1] = b * hd;
+  ej[2] = -(a * xd + b * yd) * hd;
+  ej[3] = -a * xy - b * (1.f + yd * yd);
+  ej[4] = a * (1.f + xd * xd) + b * xy;
+  ej[5] = b * xd - a * yd;
+}
 
 __device__ __forceinline__ void linearise_j(const SE3& g, const Intr& K, int wd, int k, float disp,
                                             float tu, float tv, float wru, float wrv, bool stereo,
@@ -56,6 +82,7 @@ __device__ __forceinline__ void linearise_j(const SE3& g, const Intr& K, int wd,
   L.Jz_v = K.fy * (g.t[1] * d - g.t[2] * (y * d2));
   L.wu = stereo ? 0.f : L.wu_d;
   L.wv = stereo ? 0.f : L.wv_d;
+  L.xd = x * d; L.yd = y * d; L.hd = h * d;
 }
 
 // N[n][a] with Ji[n] = sum_a N[n][a] Jj[a]  (row-major 6x6): column a is -adj_se3(g, e_a)

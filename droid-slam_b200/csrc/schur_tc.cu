@@ -123,9 +123,7 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 __device__ __forceinline__ uint32_t tf32_rna(float x) { return (__float_as_uint(x) + 0x1000u) & 0xFFFFE000u; }
 
 __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
-    const float* __restrict__ disps, const float* __restrict__ intrinsics,
-    const float* __restrict__ targets, const float* __restrict__ weights,
-    const int64_t* __restrict__ jj, const float* __restrict__ gij, int* __restrict__ status,
+    const float* __restrict__ ejc, const int64_t* __restrict__ jj, const float* __restrict__ gij, int* __restrict__ status,
     const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
     const float* __restrict__ Qi, const float* __restrict__ Wi, double* __restrict__ A,
     double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P, int n_eta, int frame_lo,
@@ -220,32 +218,31 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
     // ---------------- F builders ----------------
     // A build pass covers kTB = 128 pixels (two threads per pixel, each taking every other edge, inputs of the next
     // edge prefetched), then the four 32-pixel chunks of the pass are packed and handed to the MMA issuer.
-    const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
     const int pl = tid >> 1, g = tid & 1;
-    const float* __restrict__ dmap = disps + (size_t)k * HW;
     float* Erow = E32 + pl * kELd;
     const int npass = (p1 - p0 + kTB - 1) / kTB;
-    // The inputs of a thread's (up to 10) edges live in registers one whole pass ahead: as soon as item i of this
-    // pass has been consumed, the same registers are re-loaded with item i of the next pass, so every global load has
-    // a full pass (~10 linearisations) to arrive.  With 8 builder warps per SM nothing else hides the DRAM latency.
+    // The packed E_j (ba_lin.cuh: 5 floats per pixel-edge, left behind by ba_accum_kernel) of a thread's (up to 10)
+    // edges live in registers one whole pass ahead: as soon as item i of this pass has been consumed, the same
+    // registers are re-loaded with item i of the next pass, so every global load has a full pass to arrive.
     constexpr int kMaxI = (kSchurTcMaxD - 1 + 1) / 2;     // edges per thread
-    float r_tu[kMaxI], r_tv[kMaxI], r_wu[kMaxI], r_wv[kMaxI];
-    float n_dp = 0.f, n_q = 0.f, n_w = 0.f;
+    float r_c[kMaxI][kEjComp];
+    float n_q = 0.f, n_w = 0.f;
     auto fetch = [&](int it, int p, bool ok) {
       const int i = g + 2 * it;
       if (ok && i < deg) {
-        const size_t base = (size_t)s_e[i] * 2 * HW + p;
-        r_tu[it] = __ldg(targets + base); r_tv[it] = __ldg(targets + base + HW);
-        r_wu[it] = __ldg(weights + base); r_wv[it] = __ldg(weights + base + HW);
+        const float* src = ejc + (size_t)s_e[i] * kEjComp * HW + p;
+#pragma unroll
+        for (int q = 0; q < kEjComp; q++) r_c[it][q] = __ldcs(src + (size_t)q * HW);
       }
     };
     auto fetch_pix = [&](int p, bool ok) {
-      n_dp = ok ? dmap[p] : 0.f;
       n_q = ok ? Qi[(size_t)m * HW + p] : 0.f;
       n_w = ok ? Wi[(size_t)m * HW + p] : 0.f;
     };
 #pragma unroll
-    for (int it = 0; it < kMaxI; it++) { r_tu[it] = 0.f; r_tv[it] = 0.f; r_wu[it] = 0.f; r_wv[it] = 0.f; }
+    for (int it = 0; it < kMaxI; it++)
+#pragma unroll
+      for (int q = 0; q < kEjComp; q++) r_c[it][q] = 0.f;
     fetch_pix(p0 + pl, p0 + pl < p1);
 #pragma unroll
     for (int it = 0; it < kMaxI; it++) fetch(it, p0 + pl, p0 + pl < p1);
@@ -254,34 +251,21 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
       const bool valid = p < p1;
       const int pn = p + kTB;
       const bool valid_n = pn < p1;
-      const float dp = n_dp, sq = sqrtf(n_q), wv_pix = n_w;
+      const float sq = sqrtf(n_q), wv_pix = n_w;
       fetch_pix(pn, valid_n);
       float Ei[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int it = 0; it < kMaxI; it++) {
         const int i = g + 2 * it;
         if (i < deg) {
-          const int jx = s_jx[i];
-          const float tu = r_tu[it], tv = r_tv[it], wu = r_wu[it], wv = r_wv[it];
-          fetch(it, pn, valid_n);
-          SE3 gg;
-          {
-            const float4 ga = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i);
-            const float4 gb = *reinterpret_cast<const float4*>(s_g + kEdgeStride * i + 4);
-            gg.t[0] = ga.x; gg.t[1] = ga.y; gg.t[2] = ga.z;
-            gg.q[0] = ga.w; gg.q[1] = gb.x; gg.q[2] = gb.y; gg.q[3] = gb.z;
-          }
-          PixLinJ L;
-          linearise_j(gg, K, wd, valid ? p : p0, dp, tu, tv, wu, wv, jx == k, L);
-          const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
-          float ej[6], ejr[6];
+          float pk[kEjComp];
 #pragma unroll
-          for (int n = 0; n < 6; n++) {
-            float ej_n = au * L.Jj_u[n];
-            ej_n += av * L.Jj_v[n];
-            ejr[n] = ej_n;
-            ej[n] = valid ? sq * ej_n : 0.f;
-          }
+          for (int q = 0; q < kEjComp; q++) pk[q] = r_c[it][q];
+          fetch(it, pn, valid_n);
+          float ej[6], ejr[6];
+          ej_unpack(pk, ejr);
+#pragma unroll
+          for (int n = 0; n < 6; n++) ej[n] = valid ? sq * ejr[n] : 0.f;
           // E_i = N E_j (per-edge matrix, see ba_lin.cuh)
           const float* N = s_g + kEdgeStride * i + 8;
 #pragma unroll
@@ -394,8 +378,7 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
 
 }  // namespace stc
 
-int launch_schur_tc(const float* disps, const float* intrinsics, const float* targets, const float* weights,
-                    const int64_t* jj, const float* gij, int* status, const int* kx, const int* eptr, const int* eidx,
+int launch_schur_tc(const float* ejc, const int64_t* jj, const float* gij, int* status, const int* kx, const int* eptr, const int* eidx,
                     const float* Qi, const float* Wi, double* A, double* bvec, int HW, int wd, int slab, int S, int t0,
                     int P, int n_eta, int frame_lo, int frame_hi, const int* ppos, cudaStream_t st) {
   static bool attr = false;
@@ -404,7 +387,7 @@ int launch_schur_tc(const float* disps, const float* intrinsics, const float* ta
     attr = true;
   }
   DROID_LAUNCH stc::ba_schur_tc_kernel<<<dim3(S, n_eta), stc::kThreads, stc::kSmem, st>>>(
-      disps, intrinsics, targets, weights, jj, gij, status, kx, eptr, eidx, Qi, Wi, A, bvec, HW, wd, slab, t0, P, n_eta,
+      ejc, jj, gij, status, kx, eptr, eidx, Qi, Wi, A, bvec, HW, wd, slab, t0, P, n_eta,
       frame_lo, frame_hi, ppos);
   return check_launch();
 }
