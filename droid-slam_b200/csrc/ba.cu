@@ -1246,7 +1246,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
         }
         DROID_LAUNCH ba_schur_kernel<<<dim3(S, p->n_eta), kThreads, kSchurSmemBytes, so>>>(
             w.ejc, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q,
-            w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, use_tc ? kSchurTcMaxD : 0);
+            w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, use_tc ? kSchurTcMaxDeg + 1 : 0);
         if (use_tc) {
           cudaEventRecord(ev_join, s2);
           if (launch_schur_tc(w.ejc, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,

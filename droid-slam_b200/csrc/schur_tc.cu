@@ -1,25 +1,34 @@
 // Schur complement of the per-pixel inverse depths on the tensor cores (tcgen05 / TMEM), sm_100a.
-// Replaces, for source frames with at most 20 outgoing edges, the CUDA-core Gram product of ba_schur_kernel (ba.cu)
-// and with it the reference's EEt6x6 / Ev6x1 kernels (src/droid_kernels.cu:1001-1091).
+// Replaces, for source frames with at most kSchurTcMaxDeg = 31 outgoing edges, the CUDA-core Gram product of
+// ba_schur_kernel (ba.cu) and with it the reference's EEt6x6 / Ev6x1 kernels (src/droid_kernels.cu:1001-1091).
 //
 // For one source frame k with targets j_1..j_deg the Schur terms are
 //     S[a,b] = sum_p E_a[p] Q[p] E_b[p]^T          (6x6 blocks, a,b in {k, j_1..j_deg})
 //     v_S[a] = sum_p E_a[p] Q[p] w[p]
-// i.e. with F[r][p] = sqrt(Q[p]) * E[r][p] for the R = 6 (deg+1) rows and one extra row F[R][p] = sqrt(Q[p]) w[p]:
-//     G = F F^T  (M x M, M = R + 1 <= 128, K = number of pixels);  S = G[:R,:R],  v_S = G[R,:R].
-// That is a GEMM with K = 3072 .. 5760, which belongs on the tensor pipe.  fp32 accuracy needs two things:
+// The source pose's rows are a LINEAR image of the edge rows, E_k[p] = sum_e N_e E_{j_e}[p] with the per-edge matrix
+// N_e = -Ad(G_e)^T (ba_lin.cuh), so they never enter the per-pixel work: with F[6e+a][p] = sqrt(Q[p]) E_{j_e}[p][a]
+// and one extra row F[6 deg][p] = sqrt(Q[p]) w[p],
+//     G = F F^T  (M x M, M = 6 deg + 1 <= 128, K = number of pixels)
+// holds every edge-edge block and v_S of the targets, and the source pose's blocks follow once per frame from G:
+//     S[k,j_e'] = sum_e N_e G[e,e'],   S[k,k] = sum_{e,e'} N_e G[e,e'] N_e'^T,   v_S[k] = sum_e N_e G[e,w].
+// Frames with 22..31 edges: the edges are cut into three groups and one CTA takes each PAIR of groups (<= 21 edges);
+// a pair of rows is "owned" by exactly one of the three CTAs (cross-group pairs by the CTA of that pair of groups,
+// pairs inside a group by the CTA that lists the group first), and a CTA adds only what it owns.
+// G is a GEMM with K = 3072 .. 5760, which belongs on the tensor pipe.  fp32 accuracy needs two things:
 //  * the 3xTF32 split  F = F_hi + F_lo (both rounded to tf32),  G = F_hi F_hi^T + F_hi F_lo^T + F_lo F_hi^T;
 //  * SHORT accumulation chains: the TMEM accumulator truncates, so the error of a sum grows linearly with the number
 //    of chained MMAs (measured: 1.8e-6 relative over 1152 MMAs, 2.6e-7 over 24).  Every chunk of 32 pixels (12 MMAs)
 //    therefore starts a fresh accumulator, and the chunks are summed with ordinary fp32 adds in registers.
 //
-// Warp roles (512 threads, one CTA per SM, CTA = (pixel slab, source frame)):
-//   warps 0-7   builders: recompute the Jacobians of every (pixel, edge) from (target, weight, disp) like
-//               ba_schur_kernel, stage the chunk's F as plain fp32 in shared memory, then re-pack it (split + 16-byte
-//               stores) into the canonical MN-major UMMA layout for 32-bit operands (SWIZZLE_128B_BASE32B);
+// Warp roles (512 threads, one CTA per SM, CTA = (pixel slab, source frame, pair of edge groups)):
+//   warps 0-7   builders: stream the packed E_j of every (pixel, edge) (left behind by ba_accum_kernel), stage the
+//               chunk's F as plain fp32 in shared memory, then re-pack it (split + 16-byte stores) into the canonical
+//               MN-major UMMA layout for 32-bit operands (SWIZZLE_128B_BASE32B);
 //   warp 13     one thread issues the 12 tcgen05.mma of a chunk into TMEM buffer (chunk & 1);
-//   warps 8-11, 14-15  drainers: TMEM -> registers, fp32 accumulation of half a row of G per thread, and at the end the fp64
-//               atomics into the dense reduced system (same block placement rules as flush_block in ba.cu).
+//   warps 8-11, 14-15  drainers: TMEM -> registers, fp32 accumulation of half a row of G per thread;
+//   epilogue    (all warps) G goes to shared memory, the source pose's rows are derived from it, and everything is
+//               subtracted from the dense reduced system with fp64 atomics, lanes along a row (same block placement
+//               rules as flush_block in ba.cu).
 // Operand stages, fp32 staging and TMEM accumulators are all double-buffered: building chunk c+1, the MMAs of chunk c
 // and the drain of chunk c-1 overlap.
 #include <cstdint>
@@ -139,10 +148,17 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
   if (p0 >= p1) return;
   const int e0 = eptr[m], e1 = eptr[m + 1];
   const int deg = e1 - e0;
-  const int D = deg + 1;
-  if (deg == 0 || D > kSchurTcMaxD) return;     // nothing to do / handled by ba_schur_kernel
-  const int R = 6 * D;                   // rows of E; row R of F carries sqrt(Q) w
-  const int M = R + 1;
+  if (deg == 0 || deg > kSchurTcMaxDeg) return;     // nothing to do / handled by ba_schur_kernel
+  // edge groups: one group (this CTA takes all edges) or three (this CTA takes groups z and z+1 mod 3)
+  const int z = blockIdx.z;
+  const int ng = deg <= kSchurTcMaxU ? 1 : 3;
+  if (z >= ng) return;
+  const int gbase = deg / 3, grem = deg - 3 * gbase;
+  const int g1 = z, g2 = (z + 1) % 3;
+  const int start1 = ng == 1 ? 0 : g1 * gbase + min(g1, grem), start2 = g2 * gbase + min(g2, grem);
+  const int nfirst = ng == 1 ? deg : gbase + (g1 < grem ? 1 : 0);
+  const int nu = ng == 1 ? deg : nfirst + gbase + (g2 < grem ? 1 : 0);      // edges of this CTA (<= kSchurTcMaxU)
+  const int R = 6 * nu;                  // rows of E; row R of F carries sqrt(Q) w
 
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   float* E32 = reinterpret_cast<float*>(smem + 2 * kStage);          // [kTB][kELd]
@@ -173,15 +189,16 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
   }
   // staging columns >= M are never written and must read as zero
   for (int i = tid; i < kEBytes / 16; i += kThreads) reinterpret_cast<uint4*>(E32)[i] = make_uint4(0, 0, 0, 0);
-  for (int i = tid; i < deg; i += kThreads) {
-    const int e = eidx[e0 + i];
+  auto edge_of = [&](int i) { return eidx[e0 + (i < nfirst ? start1 + i : start2 + (i - nfirst))]; };
+  for (int i = tid; i < nu; i += kThreads) {
+    const int e = edge_of(i);
     s_e[i] = e;
     s_jx[i] = (int)jj[e];
   }
-  for (int i = tid; i < deg * kEdgeStride; i += kThreads)
-    s_g[i] = gij[(size_t)eidx[e0 + i / kEdgeStride] * kEdgeStride + i % kEdgeStride];
-  for (int d = tid; d < D; d += kThreads) {
-    int pz = (d == 0) ? k - t0 : (int)jj[eidx[e0 + d - 1]] - t0;
+  for (int i = tid; i < nu * kEdgeStride; i += kThreads)
+    s_g[i] = gij[(size_t)edge_of(i / kEdgeStride) * kEdgeStride + i % kEdgeStride];
+  for (int d = tid; d <= nu; d += kThreads) {       // pose[0] = source pose, pose[1 + i] = target of edge i
+    int pz = (d == 0) ? k - t0 : (int)jj[edge_of(d - 1)] - t0;
     if (pz < 0 || pz >= P) pz = -1;
     else if (ppos != nullptr) pz = ppos[pz];
     pose[d] = pz;
@@ -224,12 +241,12 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
     // The packed E_j (ba_lin.cuh: 5 floats per pixel-edge, left behind by ba_accum_kernel) of a thread's (up to 10)
     // edges live in registers one whole pass ahead: as soon as item i of this pass has been consumed, the same
     // registers are re-loaded with item i of the next pass, so every global load has a full pass to arrive.
-    constexpr int kMaxI = (kSchurTcMaxD - 1 + 1) / 2;     // edges per thread
+    constexpr int kMaxI = (kSchurTcMaxU + 1) / 2;     // edges per thread
     float r_c[kMaxI][kEjComp];
     float n_q = 0.f, n_w = 0.f;
     auto fetch = [&](int it, int p, bool ok) {
       const int i = g + 2 * it;
-      if (ok && i < deg) {
+      if (ok && i < nu) {
         const float* src = ejc + (size_t)s_e[i] * kEjComp * HW + p;
 #pragma unroll
         for (int q = 0; q < kEjComp; q++) r_c[it][q] = __ldcs(src + (size_t)q * HW);
@@ -251,43 +268,25 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
       const bool valid = p < p1;
       const int pn = p + kTB;
       const bool valid_n = pn < p1;
-      const float sq = sqrtf(n_q), wv_pix = n_w;
+      const float sq = valid ? sqrtf(n_q) : 0.f, wv_pix = n_w;
       fetch_pix(pn, valid_n);
-      float Ei[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int it = 0; it < kMaxI; it++) {
         const int i = g + 2 * it;
-        if (i < deg) {
+        if (i < nu) {
           float pk[kEjComp];
 #pragma unroll
           for (int q = 0; q < kEjComp; q++) pk[q] = r_c[it][q];
           fetch(it, pn, valid_n);
-          float ej[6], ejr[6];
-          ej_unpack(pk, ejr);
-#pragma unroll
-          for (int n = 0; n < 6; n++) ej[n] = valid ? sq * ejr[n] : 0.f;
-          // E_i = N E_j (per-edge matrix, see ba_lin.cuh)
-          const float* N = s_g + kEdgeStride * i + 8;
-#pragma unroll
-          for (int n = 0; n < 6; n++) {
-            float t = 0.f;
-#pragma unroll
-            for (int a = 0; a < 6; a++) t = fmaf(N[n * 6 + a], ejr[a], t);
-            Ei[n] += t;
-          }
-          float2* dst = reinterpret_cast<float2*>(Erow + 6 * (i + 1));
-          dst[0] = make_float2(ej[0], ej[1]); dst[1] = make_float2(ej[2], ej[3]); dst[2] = make_float2(ej[4], ej[5]);
+          float ej[6];
+          ej_unpack(pk, ej);
+          float2* dst = reinterpret_cast<float2*>(Erow + 6 * i);
+          dst[0] = make_float2(sq * ej[0], sq * ej[1]);
+          dst[1] = make_float2(sq * ej[2], sq * ej[3]);
+          dst[2] = make_float2(sq * ej[4], sq * ej[5]);
         }
       }
-      // the source pose's rows: sum over the two threads of this pixel
-#pragma unroll
-      for (int n = 0; n < 6; n++) Ei[n] += __shfl_xor_sync(0xffffffffu, Ei[n], 1);
-      if (g == 0) {
-#pragma unroll
-        for (int n = 0; n < 6; n++) Erow[n] = valid ? sq * Ei[n] : 0.f;
-      } else {
-        Erow[R] = valid ? sq * wv_pix : 0.f;
-      }
+      if (g == 1) Erow[R] = sq * wv_pix;
       asm volatile("bar.sync 1, 256;" ::: "memory");      // pass staged
       // ---- pack: 8 consecutive rows of one pixel = one 32-byte unit of the UMMA layout; 2 units per thread and chunk
       for (int sub = 0; sub < kTB / kT; sub++) {
@@ -347,30 +346,94 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
       tc_fence_before();
       mbar_arrive(tfree + s);
     }
-    // ---- flush row r (columns <= r) with fp64 atomics
-    const int n6 = 6 * P;
-    if (r <= R) {
-      const int rb = r / 6, n = r - 6 * rb;
-      const int pa = r < R ? pose[rb] : 0;
+    // ---- hand the row to the epilogue: G[r][64 hh .. 64 hh + 63] -> shared memory (the fp32 staging buffer is free:
+    // the last chunk's MMAs, which this thread has just waited for, were issued after the builders' last read of it)
+    float4* grow = reinterpret_cast<float4*>(E32 + r * kELd + 64 * hh);
 #pragma unroll
-      for (int j = 0; j < 64; j++) {
-        const int c = 64 * hh + j;
-        if (c > r || c >= R) continue;
-        const int cb = c / 6, mm = c - 6 * cb;
-        const int pb = pose[cb];
-        if (pb < 0) continue;
-        const double val = -(double)acc[j];
-        if (r == R) { atomicAdd(&bvec[6 * pb + mm], val); continue; }       // v_S
-        if (pa < 0) continue;
-        if (pa > pb) atomicAdd(&A[(size_t)(6 * pa + n) * n6 + 6 * pb + mm], val);
-        else if (pa < pb) atomicAdd(&A[(size_t)(6 * pb + mm) * n6 + 6 * pa + n], val);
-        else if (rb == cb) atomicAdd(&A[(size_t)(6 * pa + n) * n6 + 6 * pa + mm], val);   // c <= r => mm <= n
-        else atomicAdd(&A[(size_t)(6 * pa + max(n, mm)) * n6 + 6 * pa + min(n, mm)], n == mm ? 2.0 * val : val);
-      }
-    }
+    for (int j = 0; j < 16; j++) grow[j] = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
   }
   tc_fence_before();
   __syncthreads();
+  // ---------------- epilogue (all warps): G in shared memory (lower triangle valid), operand stages free ----------------
+  {
+    const float* Gs = E32;
+    float* Ts = reinterpret_cast<float*>(smem);       // [4][6][128] partial sums of T = sum_e N_e G[e, :]
+    float* Tf = Ts + 4 * 6 * 128;                     // [6][128]
+    const int n6 = 6 * P;
+    const int ps = pose[0];
+    auto own = [&](int a, int b) { return a < nfirst || b < nfirst; };      // edge indices inside this CTA's list
+    auto place = [&](int pa, int n, int pb, int mm, bool same_rows, double val) {
+      // element (n, mm) of the 6x6 block E_a Q E_b^T -> lower triangle of H - S (flush_block in ba.cu)
+      if (pa > pb) atomicAdd(&A[(size_t)(6 * pa + n) * n6 + 6 * pb + mm], val);
+      else if (pa < pb) atomicAdd(&A[(size_t)(6 * pb + mm) * n6 + 6 * pa + n], val);
+      else if (same_rows) atomicAdd(&A[(size_t)(6 * pa + n) * n6 + 6 * pa + mm], val);          // caller passes mm <= n
+      else atomicAdd(&A[(size_t)(6 * pa + max(n, mm)) * n6 + 6 * pa + min(n, mm)], n == mm ? 2.0 * val : val);
+    };
+    // (1) partial T: thread = (column c, quarter q of the edges)
+    {
+      const int c = tid & 127, q = tid >> 7;
+      float t[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (c <= R) {
+        const int cb = c / 6;
+        for (int e = q; e < nu; e += 4) {
+          if (!(c < R ? own(e, cb) : e < nfirst)) continue;
+          float gv[6];
+#pragma unroll
+          for (int a = 0; a < 6; a++) {
+            const int r = 6 * e + a;
+            gv[a] = r >= c ? Gs[r * kELd + c] : Gs[c * kELd + r];
+          }
+          const float* N = s_g + kEdgeStride * e + 8;
+#pragma unroll
+          for (int n = 0; n < 6; n++)
+#pragma unroll
+            for (int a = 0; a < 6; a++) t[n] = fmaf(N[n * 6 + a], gv[a], t[n]);
+        }
+      }
+#pragma unroll
+      for (int n = 0; n < 6; n++) Ts[(q * 6 + n) * 128 + c] = t[n];
+    }
+    // (2) edge-edge blocks and v_S of the targets: one row of G per warp step, lanes along the row
+    for (int r = warp; r <= R; r += kThreads / 32) {
+      const int rb = r / 6, n = r - 6 * rb;
+      const int pa = r < R ? pose[1 + rb] : 0;
+      for (int c = lane; c <= r && c < R; c += 32) {
+        const int cb = c / 6, mm = c - 6 * cb;
+        const int pb = pose[1 + cb];
+        if (pb < 0) continue;
+        const double val = -(double)Gs[r * kELd + c];
+        if (r == R) { if (cb < nfirst) atomicAdd(&bvec[6 * pb + mm], val); continue; }       // v_S
+        if (pa < 0 || !own(rb, cb)) continue;
+        place(pa, n, pb, mm, rb == cb, val);
+      }
+    }
+    __syncthreads();
+    // (3) the source pose against every target, and its v_S
+    for (int idx = tid; idx < 6 * 128; idx += kThreads) {
+      const int n = idx >> 7, c = idx & 127;
+      const float v = (Ts[n * 128 + c] + Ts[(6 + n) * 128 + c]) + (Ts[(12 + n) * 128 + c] + Ts[(18 + n) * 128 + c]);
+      Tf[n * 128 + c] = v;
+      if (c > R || ps < 0) continue;
+      if (c == R) { atomicAdd(&bvec[6 * ps + n], -(double)v); continue; }
+      const int cb = c / 6, mm = c - 6 * cb;
+      const int pb = pose[1 + cb];
+      if (pb < 0) continue;
+      place(ps, n, pb, mm, false, -(double)v);
+    }
+    __syncthreads();
+    // (4) the source pose's own block: S[k,k] = sum_c T[:, c] N_{e(c)}[:, a(c)]^T  (symmetric; lower triangle)
+    if (tid < 36 && ps >= 0) {
+      const int n = tid / 6, mm = tid - 6 * n;
+      if (mm <= n) {
+        float sacc = 0.f;
+        for (int c = 0; c < R; c++) {
+          const int e = c / 6, a = c - 6 * e;
+          sacc = fmaf(Tf[n * 128 + c], s_g[kEdgeStride * e + 8 + mm * 6 + a], sacc);
+        }
+        atomicAdd(&A[(size_t)(6 * ps + n) * n6 + 6 * ps + mm], -(double)sacc);
+      }
+    }
+  }
   if (warp == 13) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256) : "memory");
   }
@@ -386,7 +449,7 @@ int launch_schur_tc(const float* ejc, const int64_t* jj, const float* gij, int* 
     cudaFuncSetAttribute(stc::ba_schur_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, stc::kSmem);
     attr = true;
   }
-  DROID_LAUNCH stc::ba_schur_tc_kernel<<<dim3(S, n_eta), stc::kThreads, stc::kSmem, st>>>(
+  DROID_LAUNCH stc::ba_schur_tc_kernel<<<dim3(S, n_eta, 3), stc::kThreads, stc::kSmem, st>>>(
       ejc, jj, gij, status, kx, eptr, eidx, Qi, Wi, A, bvec, HW, wd, slab, t0, P, n_eta,
       frame_lo, frame_hi, ppos);
   return check_launch();
