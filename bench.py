@@ -148,18 +148,23 @@ def algorithmic(p):
     M, P = p["eta"].shape[0], p["t1"] - p["t0"]
     deg = np.bincount(p["ii"], minlength=p["n"])
     rows = 6 * (deg[deg > 0] + 1)
+    pe = ne * hw                                                                      # pixel-edges
     return {
         # targets+weights once, disps/disps_sens/eta in, Q/W out, 90 fp64 values per edge into the system
-        "ba_accum_bytes": ne * hw * 16 + M * hw * 20 + ne * 90 * 8,
-        # targets+weights again (E is recomputed, never stored), disps/Q/W in, lower triangle of S out
-        "ba_schur_bytes": ne * hw * 16 + M * hw * 12 + int((rows * (rows + 1) // 2).sum()) * 8,
+        "ba_accum_bytes": pe * 16 + M * hw * 20 + ne * 90 * 8,
+        # + the packed E_j (5 floats per pixel-edge, ba_lin.cuh) that this pass leaves behind for the next two
+        "ba_accum_streamed_bytes": pe * 16 + M * hw * 20 + ne * 90 * 8 + pe * 20,
+        # packed E_j + Q/W in, lower triangle of S out
+        "ba_schur_bytes": pe * 20 + M * hw * 8 + int((rows * (rows + 1) // 2).sum()) * 8,
         "ba_schur_flops": int((rows.astype(np.int64) * (rows + 1)).sum()) * hw,       # lower-triangular Gram
-        # what the tensor-core kernel issues: three 128x128 tf32 MMAs per 8 pixels for frames with <= 20 edges
-        "ba_schur_issued_flops": int((deg[(deg > 0) & (deg <= 20)] > 0).sum()) * 3 * 2 * 128 * 128 * hw,
+        # what the tensor-core kernel issues: three 128x128 tf32 MMAs per 8 pixels and CTA; one CTA for frames with
+        # <= 21 edges, three (one per pair of edge groups) for 22..31 edges
+        "ba_schur_issued_flops": int(((deg > 0) & (deg <= 21)).sum() + 3 * ((deg > 21) & (deg <= 31)).sum()) * 3 * 2 * 128 * 128 * hw,
         "ba_solve_flops": (6 * P) ** 3 // 3 + 2 * (6 * P) ** 2,                        # dense fp64 Cholesky + 2 solves
         "ba_solve_bytes": (6 * P) ** 2 * 8 // 2,
-        "ba_update_bytes": ne * hw * 16 + M * hw * 20,
-        "iter_bytes": ne * hw * 16 + M * hw * 16 + (6 * P) ** 2 * 4,                   # 1.0 GB at C4
+        # packed E_j + Q/W + depth map in, dz + depth map out
+        "ba_update_bytes": pe * 20 + M * hw * 20,
+        "iter_bytes": pe * 16 + M * hw * 16 + (6 * P) ** 2 * 4,                        # 1.0 GB at C4
     }
 
 
@@ -297,15 +302,19 @@ def run_b200(args, world, rank, local):
             g = alg[k + "_bytes"] / (ms_of(k) * 1e-3) / 1e9
             table[k] = {"bound": "hbm", "ms": ms_of(k), "achieved": g, "peak": hbm_peak, "unit": "GB/s", "frac": g / hbm_peak,
                         "algorithmic_bytes": int(alg[k + "_bytes"])}
+            if k + "_streamed_bytes" in alg:          # what the kernel moves by design (intermediate stream included)
+                table[k]["streamed_GBps"] = alg[k + "_streamed_bytes"] / (ms_of(k) * 1e-3) / 1e9
+                table[k]["streamed_bytes"] = int(alg[k + "_streamed_bytes"])
     if "ba_schur" in per_phase:
         t = alg["ba_schur_flops"] / (ms_of("ba_schur") * 1e-3) / 1e12
         table["ba_schur"] = {"bound": "tensor", "ms": ms_of("ba_schur"), "achieved": t, "peak": tf32_peak, "unit": "TFLOP/s",
                              "frac": t / tf32_peak, "algorithmic_flops": int(alg["ba_schur_flops"]),
                              "issued_flops": int(alg["ba_schur_issued_flops"]),
                              "hbm_GBps": alg["ba_schur_bytes"] / (ms_of("ba_schur") * 1e-3) / 1e9,
-                             "note": "3xTF32 tcgen05 Gram product (frames with <= 20 edges) + CUDA-core kernel (rest), run "
-                                     "concurrently; both are limited by the fp32 Jacobian recomputation that feeds them, "
-                                     "not by the tensor pipe or HBM"}
+                             "note": "3xTF32 tcgen05 Gram product of the edge rows (frames with <= 31 edges; > 21 edges: one "
+                                     "CTA per pair of edge groups), source-pose rows derived from the Gram per frame; "
+                                     "CUDA-core kernel only beyond 31 edges.  Limited by the builder warps that unpack, "
+                                     "split (3xTF32) and re-pack the operand tiles, not by the tensor pipe or HBM"}
     if "ba_solve" in per_phase:
         table["ba_solve"] = {"bound": "latency (serial pivot chain, fp64)", "ms": ms_of("ba_solve"),
                              "pivots": int(6 * (p["t1"] - p["t0"])), "ns_per_pivot": ms_of("ba_solve") * 1e6 / max(6 * (p["t1"] - p["t0"]), 1),

@@ -476,13 +476,17 @@ __global__ void ba_edge_pose_kernel(const float* __restrict__ poses, const int64
   edge_adjoint(g, o + 8);
 }
 
-// y_e = N_e^T dx[source pose] (0 when the source pose is not updated or is the first optimised pose, :1105)
-__global__ void ba_edge_y_kernel(const float* __restrict__ gij, const int64_t* __restrict__ ii, int n_edges,
+// u_e = N_e^T dx[source pose] + dx[target pose]: what the depth back-substitution multiplies E_j of the edge with
+// (E_i^T dx_i = (N E_j)^T dx_i = E_j^T N^T dx_i).  A term is 0 when its pose is not updated or is the first
+// optimised pose (:1105).
+__global__ void ba_edge_y_kernel(const float* __restrict__ gij, const int64_t* __restrict__ ii,
+                                 const int64_t* __restrict__ jj, int n_edges,
                                  int nbuf, const float* __restrict__ dx, int t0, int P, float* __restrict__ ey) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_edges) return;
-  const long long i = ii[e];
+  const long long i = ii[e], j = jj[e];
   const int pk = (i < 0 || i >= nbuf) ? -1 : (int)i - t0;
+  const int pj = (j < 0 || j >= nbuf) ? -1 : (int)j - t0;
   float y[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (pk > 0 && pk < P) {
     const float* N = gij + (size_t)e * kEdgeStride + 8;
@@ -492,6 +496,10 @@ __global__ void ba_edge_y_kernel(const float* __restrict__ gij, const int64_t* _
 #pragma unroll
       for (int a = 0; a < 6; a++) y[a] = fmaf(N[n * 6 + a], d, y[a]);
     }
+  }
+  if (pj > 0 && pj < P) {
+#pragma unroll
+    for (int a = 0; a < 6; a++) y[a] += dx[6 * pj + a];
   }
   float* o = ey + (size_t)e * 8;
 #pragma unroll
@@ -987,14 +995,11 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
 //   skipped exactly like the reference (:1105) -- i.e. the first optimised pose t0 never feeds dz.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) ba_dz_kernel(
-    float* __restrict__ disps, const float* __restrict__ intrinsics,
-    const float* __restrict__ targets, const float* __restrict__ weights,
-    const int64_t* __restrict__ jj, const float* __restrict__ gij, const float* __restrict__ ey,
+    float* __restrict__ disps, const float* __restrict__ ejc, const float* __restrict__ ey,
     const int* __restrict__ status,
     const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
-    const float* __restrict__ Qi, const float* __restrict__ Wi, const float* __restrict__ dx,
-    float* __restrict__ dz_out, int HW, int wd, int t0, int P, int n_eta, int frame_lo,
-    int frame_hi) {
+    const float* __restrict__ Qi, const float* __restrict__ Wi,
+    float* __restrict__ dz_out, int HW, int n_eta, int frame_lo, int frame_hi) {
   const int m = blockIdx.y;
   const int M = status[1];
   if (m >= M || m >= n_eta) return;
@@ -1002,55 +1007,36 @@ __global__ void __launch_bounds__(kThreads) ba_dz_kernel(
   if (k < frame_lo || k >= frame_hi) return;
   const int p = blockIdx.x * kThreads + threadIdx.x;
   if (p >= HW) return;
-  const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
-  float* __restrict__ dmap = disps + (size_t)k * HW;
-  const float dp = dmap[p];
   const int e0 = eptr[m], e1 = eptr[m + 1];
-  float sum = 0.f;
-  // E_i^T dx_i = (N E_j)^T dx_i = E_j^T y_e with y_e = N_e^T dx_i precomputed per edge (ba_edge_y_kernel; zero when
-  // the source pose index is <= 0 or >= P), so the source-pose Jacobian is never formed here.
-  // one-edge-ahead software prefetch of (edge id, target frame, relative pose, y, target, weight)
-  int n_jx = 0;
-  float4 n_ga = make_float4(0, 0, 0, 0), n_gb = make_float4(0, 0, 0, 0), n_ya = n_ga, n_yb = n_ga;
-  float n_tu = 0.f, n_tv = 0.f, n_wu = 0.f, n_wv = 0.f;
-  auto fetch = [&](int ei_) {
-    const int e_ = eidx[ei_];
-    n_jx = (int)jj[e_];
-    n_ga = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e_ * kEdgeStride));
-    n_gb = __ldg(reinterpret_cast<const float4*>(gij + (size_t)e_ * kEdgeStride + 4));
-    n_ya = __ldg(reinterpret_cast<const float4*>(ey + (size_t)e_ * 8));
-    n_yb = __ldg(reinterpret_cast<const float4*>(ey + (size_t)e_ * 8 + 4));
-    const size_t base = (size_t)e_ * 2 * HW + p;
-    n_tu = __ldg(targets + base); n_tv = __ldg(targets + base + HW);
-    n_wu = __ldg(weights + base); n_wv = __ldg(weights + base + HW);
-  };
-  if (e0 < e1) fetch(e0);
-  for (int ei = e0; ei < e1; ei++) {
-    const int jx = n_jx;
-    SE3 g;
-    g.t[0] = n_ga.x; g.t[1] = n_ga.y; g.t[2] = n_ga.z;
-    g.q[0] = n_ga.w; g.q[1] = n_gb.x; g.q[2] = n_gb.y; g.q[3] = n_gb.z;
-    const float y[6] = {n_ya.x, n_ya.y, n_ya.z, n_ya.w, n_yb.x, n_yb.y};
-    const float tu = n_tu, tv = n_tv, wu = n_wu, wv = n_wv;
-    if (ei + 1 < e1) fetch(ei + 1);
-    PixLinJ L;
-    linearise_j(g, K, wd, p, dp, tu, tv, wu, wv, jx == k, L);
-    const float au = L.wu * L.Jz_u, av = L.wv * L.Jz_v;
-    const int pj = jx - t0;
-    const bool use = pj > 0 && pj < P;
-    float dw = 0.f;
+  // sum_e E_j^T u_e with the packed E_j that ba_accum_kernel left behind (same linearisation point: poses and depths
+  // are only retracted after this kernel) and the per-edge 6-vector u_e of ba_edge_y_kernel; 20 bytes per pixel-edge,
+  // two edges in flight per thread.
+  float s0 = 0.f, s1 = 0.f;
+  auto term = [&](int ei) {
+    const int e = eidx[ei];
+    const float* src = ejc + (size_t)e * kEjComp * HW + p;
+    float c[kEjComp];
 #pragma unroll
-    for (int n = 0; n < 6; n++) {
-      float ej_n = au * L.Jj_u[n];
-      ej_n += av * L.Jj_v[n];
-      if (use) dw += ej_n * __ldg(&dx[6 * pj + n]);
-      dw += ej_n * y[n];
-    }
-    sum += dw;
+    for (int q = 0; q < kEjComp; q++) c[q] = __ldcs(src + (size_t)q * HW);
+    const float4 ua = __ldg(reinterpret_cast<const float4*>(ey + (size_t)e * 8));
+    const float4 ub = __ldg(reinterpret_cast<const float4*>(ey + (size_t)e * 8 + 4));
+    float ej[6];
+    ej_unpack(c, ej);
+    float d = ej[0] * ua.x;
+    d = fmaf(ej[1], ua.y, d); d = fmaf(ej[2], ua.z, d); d = fmaf(ej[3], ua.w, d);
+    d = fmaf(ej[4], ub.x, d); d = fmaf(ej[5], ub.y, d);
+    return d;
+  };
+  int ei = e0;
+  for (; ei + 1 < e1; ei += 2) {
+    const float a = term(ei), b = term(ei + 1);
+    s0 += a; s1 += b;
   }
-  const float dz = Qi[(size_t)m * HW + p] * (Wi[(size_t)m * HW + p] - sum);
+  if (ei < e1) s0 += term(ei);
+  float* __restrict__ dmap = disps + (size_t)k * HW;
+  const float dz = Qi[(size_t)m * HW + p] * (Wi[(size_t)m * HW + p] - (s0 + s1));
   dz_out[(size_t)m * HW + p] = dz;
-  dmap[p] = dp + dz;
+  dmap[p] += dz;
 }
 
 // A.diag += ep + lm * A.diag   (:1197), fp64 like the reference
@@ -1276,11 +1262,10 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     } else {
       DROID_LAUNCH ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
                                                                           w.dx, dx_out, p->t0, P, 0, ppos);
-      DROID_LAUNCH ba_edge_y_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(w.gij, ii, p->n_edges, p->nbuf, w.dx,
-                                                                              p->t0, P, w.ey);
+      DROID_LAUNCH ba_edge_y_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(w.gij, ii, jj, p->n_edges, p->nbuf,
+                                                                              w.dx, p->t0, P, w.ey);
       DROID_LAUNCH ba_dz_kernel<<<dim3((HW + kThreads - 1) / kThreads, p->n_eta), kThreads, 0, st>>>(
-          disps, intrinsics, targets, weights, jj, w.gij, w.ey, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
-          w.dx, dz_out, HW, p->wd, p->t0, P, p->n_eta, frame_lo, frame_hi);
+          disps, w.ejc, w.ey, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W, dz_out, HW, p->n_eta, frame_lo, frame_hi);
       DROID_LAUNCH ba_pose_apply_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, w.dx, p->t0, P);
     }
     if (check_launch()) return DROID_ERR_CUDA;
