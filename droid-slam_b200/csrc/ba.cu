@@ -48,8 +48,13 @@ struct BaWs {
   int* oscr;       // [6P + 2 nbuf + 16] scratch of ba_order_kernel
   double* A;       // [6P*6P + 6P]  dense system, b appended
   void* chol;      // workspace of the factorisation
+  int* pseg;       // [6P][kPackSegs][2] non-zero column segments of every row   (multi-GPU only)
+  int* poff;       // [6P + 1] offset of every row inside the packed system       (multi-GPU only)
+  double* pack;    // [6P (6P + 1) / 2 + 6P] packed system + rhs                  (multi-GPU only)
   size_t total;
 };
+
+static constexpr int kPackSegs = kBaMaxChains + 1;
 
 static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -80,6 +85,11 @@ static BaWs carve(void* base, const droid_ba_params* p, size_t chol_bytes) {
   w.oscr = (int*)take((6 * (n6 / 6) + 2 * (size_t)p->nbuf + 16) * sizeof(int));
   w.A = (double*)take((n6 * n6 + n6 + 1) * sizeof(double));
   w.chol = take(chol_bytes);
+  // after everything whose offset the cached pose order depends on
+  const bool multi = p->reduce_fn != nullptr;
+  w.pseg = (int*)take(multi ? (n6 > 0 ? n6 : 1) * kPackSegs * 2 * sizeof(int) : 16);
+  w.poff = (int*)take(multi ? (n6 + 1) * sizeof(int) : 16);
+  w.pack = (double*)take(multi ? (n6 * (n6 + 1) / 2 + n6 + 1) * sizeof(double) : 16);
   // last, so that the offsets of everything above (the cached pose order included) do not depend on motion_only
   w.ejc = (float*)take(p->motion_only ? 16 : (size_t)(p->n_edges > 0 ? p->n_edges : 1) * kEjComp * HW * sizeof(float));
   w.total = off;
@@ -458,6 +468,90 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Multi-GPU: the reduced system is summed over the ranks in PACKED form.  Row r of the lower triangle is structurally
+// zero outside at most kPackSegs column segments that follow from the pose order alone (identical on every rank):
+//   no chains:   [first[r], r]
+//   chain rows:  [first[c][r], r]                             (c = the chain holding r)
+//   separator:   [first[c][r], end of chain c) per chain c that the row touches, and [first separator row, r]
+//   unordered (small systems are not packed at all).
+// ba_pack_plan_kernel lists the segments and their offsets (one CTA), ba_pack_kernel / ba_unpack_kernel copy them
+// (one CTA per row; row 6P = the right-hand side).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) ba_pack_plan_kernel(const int* __restrict__ first, const int* __restrict__ sig,
+                                                            int n6, int* __restrict__ seg, int* __restrict__ off,
+                                                            int* __restrict__ total_out) {
+  __shared__ int s_warp[32];
+  __shared__ int s_base;
+  const int tid = threadIdx.x;
+  const int nch = sig[10];
+  int ends[kBaMaxChains + 1];
+  for (int c = 0; c < kBaMaxChains; c++) ends[c] = c < nch ? sig[11 + c] : 0;
+  const int sep0 = nch > 0 ? ends[nch - 1] : 0;
+  if (tid == 0) s_base = 0;
+  __syncthreads();
+  for (int r0 = 0; r0 < n6; r0 += 1024) {
+    const int r = r0 + tid;
+    int len = 0;
+    if (r < n6) {
+      int* sg = seg + (size_t)r * kPackSegs * 2;
+      for (int c = 0; c < kPackSegs; c++) { sg[2 * c] = 0; sg[2 * c + 1] = 0; }
+      if (nch == 0) {
+        int f = first[r];
+        if (f < 0 || f > r) f = r;
+        sg[0] = f; sg[1] = r - f + 1;
+      } else if (r < sep0) {
+        int c = 0;
+        while (c + 1 < nch && r >= ends[c]) c++;
+        int f = first[(size_t)c * n6 + r];
+        if (f < 0 || f > r) f = r;
+        sg[0] = f; sg[1] = r - f + 1;
+      } else {
+        for (int c = 0; c < nch; c++) {
+          const int f = first[(size_t)c * n6 + r];
+          const int lo = c > 0 ? ends[c - 1] : 0;
+          if (f >= lo && f < ends[c]) { sg[2 * c] = f; sg[2 * c + 1] = ends[c] - f; }
+        }
+        sg[2 * nch] = sep0; sg[2 * nch + 1] = r - sep0 + 1;
+      }
+      for (int c = 0; c < kPackSegs; c++) len += sg[2 * c + 1];
+    }
+    int total;
+    const int ex = block_scan_excl_1024(len, s_warp, &total);
+    if (r < n6) off[r] = s_base + ex;
+    __syncthreads();
+    if (tid == 0) s_base += total;
+    __syncthreads();
+  }
+  if (tid == 0) { off[n6] = s_base; *total_out = s_base; }
+}
+
+template <bool kUnpack>
+__global__ void __launch_bounds__(128) ba_pack_kernel(double* __restrict__ A, double* __restrict__ bvec,
+                                                      const int* __restrict__ seg, const int* __restrict__ off,
+                                                      int n6, double* __restrict__ pack) {
+  const int r = blockIdx.x;
+  if (r == n6) {
+    double* pb = pack + off[n6];
+    for (int i = threadIdx.x; i < n6; i += 128) {
+      if (kUnpack) bvec[i] = pb[i]; else pb[i] = bvec[i];
+    }
+    return;
+  }
+  double* pr = pack + off[r];
+  double* ar = A + (size_t)r * n6;
+  const int* sg = seg + (size_t)r * kPackSegs * 2;
+  int o = 0;
+#pragma unroll
+  for (int c = 0; c < kPackSegs; c++) {
+    const int st = sg[2 * c], ln = sg[2 * c + 1];
+    for (int i = threadIdx.x; i < ln; i += 128) {
+      if (kUnpack) ar[st + i] = pr[o + i]; else pr[o + i] = ar[st + i];
+    }
+    o += ln;
+  }
+}
+
 __global__ void ba_edge_pose_kernel(const float* __restrict__ poses, const int64_t* __restrict__ ii,
                                     const int64_t* __restrict__ jj, int n_edges, int nbuf,
                                     float* __restrict__ gij) {
@@ -599,7 +693,7 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
     const int* __restrict__ eidx, float* __restrict__ Qo, float* __restrict__ Wo,
     double* __restrict__ A, double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P,
     int n_eta, int motion_only, int frame_lo, int frame_hi, const int* __restrict__ ppos,
-    float* __restrict__ ejc) {
+    float* __restrict__ ejc, const int* __restrict__ edge_row) {
   __shared__ float Cs[kSlabMax];
   __shared__ float Bs[kSlabMax];
   __shared__ float Ds[kSlabMax];   // inverse depths of the slab (re-read for every edge of the frame)
@@ -638,7 +732,7 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
     __syncthreads();
     float n_tu = 0.f, n_tv = 0.f, n_wu = 0.f, n_wv = 0.f;
     auto fetch = [&](int ei_, int p_) {
-      const size_t base = (size_t)s_e[ei_] * 2 * HW + p_;
+      const size_t base = (size_t)(edge_row ? edge_row[s_e[ei_]] : s_e[ei_]) * 2 * HW + p_;
       n_tu = __ldg(targets + base); n_tv = __ldg(targets + base + HW);
       n_wu = __ldg(weights + base); n_wv = __ldg(weights + base + HW);
     };
@@ -1155,20 +1249,31 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   const int kreq = (ordered && n6 >= kBaChainMinRows) ? chains_req : 0;
   int nchains = 0;
   int chain_end[kBaMaxChains] = {0, 0, 0, 0};
+  int pack_total = -1;          // multi-GPU: doubles of the packed system (without the rhs); -1 = sum the dense buffer
   if (ordered) {
     DROID_LAUNCH ba_order_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->t0, P, w.kmap, w.ppos, w.first,
                                                      w.oscr, w.status + 8, p->ht * 65536 + p->wd, p->n_eta, kreq);
-    if (kreq > 0) {
+    const bool packed = p->reduce_fn != nullptr;
+    if (packed) {
+      DROID_LAUNCH ba_pack_plan_kernel<<<1, 1024, 0, st>>>(w.first, w.status + 8, n6, w.pseg, w.poff, w.status + 24);
+    }
+    if (kreq > 0 || packed) {
       static int* h_split = nullptr;
       if (!h_split && cudaHostAlloc((void**)&h_split, 8 * sizeof(int), cudaHostAllocDefault) != cudaSuccess)
         return DROID_ERR_CUDA;
-      if (cudaMemcpyAsync(h_split, w.status + 18, (1 + kBaMaxChains) * sizeof(int), cudaMemcpyDeviceToHost, st) !=
+      if (cudaMemcpyAsync(h_split, w.status + 18, 7 * sizeof(int), cudaMemcpyDeviceToHost, st) !=
               cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess)
         return DROID_ERR_CUDA;
-      nchains = h_split[0];
-      if (nchains < 0 || nchains > kBaMaxChains) return DROID_ERR_CUDA;
-      for (int c = 0; c < nchains; c++) chain_end[c] = h_split[1 + c];
-      if (nchains > 0 && n6 - chain_end[nchains - 1] > n6 / 4 + 8) return DROID_ERR_CUDA;
+      if (kreq > 0) {
+        nchains = h_split[0];
+        if (nchains < 0 || nchains > kBaMaxChains) return DROID_ERR_CUDA;
+        for (int c = 0; c < nchains; c++) chain_end[c] = h_split[1 + c];
+        if (nchains > 0 && n6 - chain_end[nchains - 1] > n6 / 4 + 8) return DROID_ERR_CUDA;
+      }
+      if (packed) {
+        pack_total = h_split[6];
+        if (pack_total < n6 || (size_t)pack_total > (size_t)n6 * (n6 + 1) / 2) return DROID_ERR_CUDA;
+      }
     }
   }
 
@@ -1205,7 +1310,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
         DROID_LAUNCH ba_accum_kernel<<<dim3(S, p->n_eta), kThreads, 0, st>>>(
             disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, w.gij, w.status, w.kx,
             w.eptr, w.eidx, w.Q, w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, p->motion_only,
-            frame_lo, frame_hi, ppos, w.ejc);
+            frame_lo, frame_hi, ppos, w.ejc, p->edge_row);
       }
       if (!p->motion_only) {
         ProfScope ps(DROID_PROF_BA_SCHUR, st);
@@ -1245,7 +1350,14 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     if (check_launch()) return DROID_ERR_CUDA;
     if (p->reduce_fn) {
       ProfScope ps(DROID_PROF_BA_REDUCE, st);
-      int rc = p->reduce_fn(p->reduce_user, w.A, (size_t)n6 * n6 + n6, stream);
+      int rc;
+      if (pack_total >= 0) {
+        DROID_LAUNCH ba_pack_kernel<false><<<n6 + 1, 128, 0, st>>>(w.A, bvec, w.pseg, w.poff, n6, w.pack);
+        rc = p->reduce_fn(p->reduce_user, w.pack, (size_t)pack_total + n6, stream);
+        DROID_LAUNCH ba_pack_kernel<true><<<n6 + 1, 128, 0, st>>>(w.A, bvec, w.pseg, w.poff, n6, w.pack);
+      } else {
+        rc = p->reduce_fn(p->reduce_user, w.A, (size_t)n6 * n6 + n6, stream);
+      }
       if (rc != 0) return DROID_ERR_CUDA;
     }
     {

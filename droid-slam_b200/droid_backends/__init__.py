@@ -37,7 +37,7 @@ class BaParams(ctypes.Structure):
         ("iterations", ctypes.c_int), ("motion_only", ctypes.c_int),
         ("lm", ctypes.c_float), ("ep", ctypes.c_float),
         ("frame_lo", ctypes.c_int), ("frame_hi", ctypes.c_int),
-        ("reduce_fn", REDUCE_FN), ("reduce_user", ctypes.c_void_p),
+        ("reduce_fn", REDUCE_FN), ("reduce_user", ctypes.c_void_p), ("edge_row", ctypes.c_void_p),
     ]
 
 
@@ -346,9 +346,9 @@ def _workspace(device, nbytes):
 
 
 def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations,
-       lm, ep, motion_only, _shard=None, _reduce=None):
+       lm, ep, motion_only, _shard=None, _reduce=None, _edge_row=None):
     """Updates ``poses`` and ``disps`` in place; returns [dx, dz] of the last iteration
-    (src/droid_kernels.cu:1314-1434).  ``_shard=(lo, hi)`` / ``_reduce`` are used by ba_sharded."""
+    (src/droid_kernels.cu:1314-1434).  ``_shard=(lo, hi)`` / ``_reduce`` / ``_edge_row`` are used by ba_sharded."""
     _contig("ba", poses=poses, disps=disps, intrinsics=intrinsics, disps_sens=disps_sens,
             targets=targets, weights=weights, ii=ii, jj=jj)
     if not isinstance(eta, torch.Tensor) or not eta.is_cuda:
@@ -366,7 +366,14 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, 
     prm = BaParams(n_edges=n_edges, nbuf=nbuf, ht=ht, wd=wd, n_eta=n_eta, t0=int(t0), t1=int(t1),
                    iterations=int(iterations), motion_only=1 if motion_only else 0, lm=float(lm),
                    ep=float(ep), frame_lo=0, frame_hi=0x7FFFFFFF, reduce_fn=REDUCE_FN(0),
-                   reduce_user=None)
+                   reduce_user=None, edge_row=None)
+    if _edge_row is not None:
+        if (_edge_row.dtype != torch.int32 or not _edge_row.is_cuda or not _edge_row.is_contiguous()
+                or _edge_row.numel() != n_edges):
+            raise RuntimeError("droid_backends.ba: edge_row must be a contiguous CUDA int32 tensor with one entry per edge")
+        prm.edge_row = _edge_row.data_ptr()
+    elif targets.shape[0] != n_edges or weights.shape[0] != n_edges:
+        raise RuntimeError("droid_backends.ba: targets / weights need one row per edge")
     if _shard is not None:
         prm.frame_lo, prm.frame_hi = int(_shard[0]), int(_shard[1])
     cb = None
@@ -455,16 +462,24 @@ def chol_solve(A, b, first=None, chain_end=None):
 
 
 def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1,
-               iterations, lm, ep, motion_only, group=None):
-    """Multi-GPU global BA: every rank holds the full (replicated) inputs of ITS edges'
-    source frames; rank r accumulates the source frames kx in its contiguous shard, the packed
-    reduced camera system is summed with one NCCL all-reduce per iteration, every rank solves it
-    (replicated, deterministic) and updates all poses plus the depths of its own frames; the depth
-    maps are all-gathered at the end so every rank returns the same state as single-GPU ba()."""
+               iterations, lm, ep, motion_only, group=None, edge_row=None):
+    """Multi-GPU global BA.  Poses, depth maps and the edge list are replicated; rank r accumulates the
+    source frames kx in its contiguous shard (shard_range), the reduced camera system -- packed to its structural
+    non-zeros -- is summed with one NCCL all-reduce per iteration, every rank solves it (replicated, deterministic) and
+    updates all poses plus the depths of its own frames; the depth maps are all-gathered at the end so every rank
+    returns the same state as single-GPU ba().
+    ``targets`` / ``weights`` hold either one row per edge (replicated), or only the rows of THIS rank's edges
+    (``shard_edges``; in edge order) -- then ``edge_row`` (from ``shard_edge_rows``) maps an edge to its row; it is
+    computed here when omitted."""
     import torch.distributed as dist
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     lo, hi, per = shard_range(disps.shape[0], world, rank)
+    if edge_row is None and targets.shape[0] != ii.shape[0]:
+        edge_row, count = shard_edge_rows(ii, lo, hi)
+        if count != targets.shape[0] or count != weights.shape[0]:
+            raise RuntimeError("droid_backends.ba_sharded: targets / weights must hold one row per edge, or one row per "
+                               "edge of this rank's shard (%d), got %d" % (count, targets.shape[0]))
 
     def _reduce(user, buf, n, stream):
         t = _as_tensor(buf, n, poses.device)
@@ -472,10 +487,23 @@ def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, 
         return 0
 
     out = ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations,
-             lm, ep, motion_only, _shard=(lo, hi), _reduce=_reduce)
+             lm, ep, motion_only, _shard=(lo, hi), _reduce=_reduce, _edge_row=edge_row)
     if not motion_only and world > 1:
         gather_depth_shards(disps, lo, hi, per, world, group)
     return out
+
+
+def shard_edges(ii, lo, hi):
+    """Mask of the edges whose source frame lies in the shard [lo, hi): the rows of targets / weights a rank needs."""
+    return (ii >= lo) & (ii < hi)
+
+
+def shard_edge_rows(ii, lo, hi):
+    """(edge_row, count): edge_row[e] (int32) = row of edge e among the shard's edges (meaningless for edges outside
+    the shard, which the kernels never touch), count = number of edges in the shard (one D2H read)."""
+    mask = shard_edges(ii, lo, hi)
+    rows = torch.cumsum(mask.to(torch.int32), 0, dtype=torch.int32) - 1
+    return rows.clamp_(min=0).contiguous(), int(mask.sum().item())
 
 
 def shard_range(nbuf, world, rank):

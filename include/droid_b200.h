@@ -149,7 +149,13 @@ int droid_depth_filter(const float* poses, const float* disps, const float* intr
  *   Multi-GPU: when `reduce_fn` != NULL it is called once per iteration, stream-ordered,
  *   on the packed reduced system (n_doubles fp64 values) after local accumulation; the Python host
  *   plugs torch.distributed.all_reduce (NCCL) in there.  With frame_lo/frame_hi a rank only
- *   accumulates source frames kx in [frame_lo, frame_hi) (pass 0, INT32_MAX for all). */
+ *   accumulates source frames kx in [frame_lo, frame_hi) (pass 0, INT32_MAX for all).
+ *   The buffer handed to reduce_fn is the reduced system PACKED to its structural non-zeros (the row segments
+ *   inside the envelope of the pose order + the right-hand side; identical layout on every rank because the order
+ *   is a function of the edge list alone) -- 10-20x fewer bytes than the dense lower triangle at 1000 keyframes.
+ *   edge_row (device int[n_edges], or NULL = identity): row of edge e inside `targets` / `weights`, for a rank
+ *   that holds only the rows of the edges whose source frame lies in its shard (entries of other edges are
+ *   never read). */
 typedef int (*droid_reduce_fn)(void* user, double* buf, size_t n_doubles, void* stream);
 
 typedef struct {
@@ -158,6 +164,7 @@ typedef struct {
   int frame_lo, frame_hi;      /* shard of source frames handled by this rank              */
   droid_reduce_fn reduce_fn;   /* NULL on a single GPU                                      */
   void* reduce_user;
+  const int* edge_row;         /* NULL, or row of every edge inside targets / weights       */
 } droid_ba_params;
 
 size_t droid_ba_workspace_bytes(const droid_ba_params* p);

@@ -496,6 +496,60 @@ def test_ba_tensor_core_schur_matches_cuda_core_kernel(knn):
     assert dxx <= 3e-4 and dzz <= 1e-4
 
 
+@pytest.mark.parametrize("name,kw,lm,ep", [("C3", {}, 1e-4, 0.1), ("C4", dict(n_frames=60), 1e-5, 1e-2),
+                                           ("C4", dict(n_frames=280), 1e-5, 1e-2)])
+def test_ba_two_shards_emulated_on_one_gpu(backends, name, kw, lm, ep):
+    """The multi-GPU path of droid_ba on ONE device: source-frame shards [lo, hi), per-rank rows of targets / weights
+    (edge_row) and the PACKED reduced system handed to reduce_fn.  World 2 is played in turns: shard A runs with a
+    callback that keeps its partial packed system, shard B runs with a callback that adds A's -- which is what the
+    all-reduce gives every rank -- and must reproduce the single-GPU dx, poses and the depth maps of its own frames.
+    C3: small system (dense buffer); 60 keyframes: envelope order; 280 keyframes: chains + separator."""
+    p = synth.make_ba_problem(name, **kw)
+    full_p, full_d, full_dx, _ = run_ba(backends, p, 1, lm=lm, ep=ep)
+    nbuf = p["disps"].shape[0]
+    ii = cu(p["ii"])
+    shards = [backends.shard_range(nbuf, 2, r)[:2] for r in range(2)]
+    sizes = {}
+
+    def run(r, cb):
+        lo, hi = shards[r]
+        mask = backends.shard_edges(ii, lo, hi)
+        rows, count = backends.shard_edge_rows(ii, lo, hi)
+        m = mask.cpu().numpy()
+        assert count == int(m.sum())
+        poses, disps = cu(p["poses"]), cu(p["disps"])
+        dx, _ = backends.ba(poses, disps, cu(p["intrinsics"]), cu(p["disps_sens"]), cu(p["targets"][m]),
+                            cu(p["weights"][m]), cu(p["eta"]), ii, cu(p["jj"]), p["t0"], p["t1"], 1, lm, ep, False,
+                            _shard=(lo, hi), _reduce=cb, _edge_row=rows)
+        torch.cuda.synchronize()
+        return poses.cpu().numpy(), disps.cpu().numpy(), dx.cpu().numpy()
+
+    for a, b in ((0, 1), (1, 0)):
+        kept = {}
+
+        def keep(user, buf, n, stream):
+            kept["part"] = backends._as_tensor(buf, n, torch.device(DEV)).clone()
+            sizes[a] = int(n)
+            return 0
+
+        def add(user, buf, n, stream):
+            assert int(n) == kept["part"].numel()            # same packed layout on both "ranks"
+            backends._as_tensor(buf, n, torch.device(DEV)).add_(kept["part"])
+            return 0
+
+        run(a, keep)
+        gp, gd, gdx = run(b, add)
+        lo, hi = shards[b]
+        assert rel(gdx, full_dx) <= 1e-5 and rel(gp, full_p) <= 1e-6
+        assert rel(gd[lo:hi], full_d[lo:hi]) <= 1e-6
+        other = np.ones(nbuf, bool); other[lo:hi] = False
+        assert np.array_equal(gd[other], p["disps"][other])          # depth maps of the other shard untouched
+    n6 = 6 * (p["t1"] - p["t0"])
+    if n6 > 156:                                                     # ordered systems travel packed
+        assert sizes[0] < (n6 * n6 + n6) // 2 + 2 * n6
+        print("packed system: %d doubles instead of %d dense" % (sizes[0], n6 * n6 + n6))
+
+
 @pytest.mark.parametrize("key", sorted(__import__("golden_cases").BA_CASES))
 def test_ba_matches_reference_golden(backends, key):
     """Against the stored outputs of the unmodified reference extension (tests/golden/ref_ba_*.npz)."""
