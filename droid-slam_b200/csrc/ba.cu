@@ -55,6 +55,7 @@ struct BaWs {
 };
 
 static constexpr int kPackSegs = kBaMaxChains + 1;
+static constexpr int kPackTotalWord = 18 + 1 + kBaMaxChains + 1;   // status word behind the chain layout (status[18..])
 
 static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -1248,20 +1249,20 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   }();
   const int kreq = (ordered && n6 >= kBaChainMinRows) ? chains_req : 0;
   int nchains = 0;
-  int chain_end[kBaMaxChains] = {0, 0, 0, 0};
+  int chain_end[kBaMaxChains] = {};
   int pack_total = -1;          // multi-GPU: doubles of the packed system (without the rhs); -1 = sum the dense buffer
   if (ordered) {
     DROID_LAUNCH ba_order_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->t0, P, w.kmap, w.ppos, w.first,
                                                      w.oscr, w.status + 8, p->ht * 65536 + p->wd, p->n_eta, kreq);
     const bool packed = p->reduce_fn != nullptr;
     if (packed) {
-      DROID_LAUNCH ba_pack_plan_kernel<<<1, 1024, 0, st>>>(w.first, w.status + 8, n6, w.pseg, w.poff, w.status + 24);
+      DROID_LAUNCH ba_pack_plan_kernel<<<1, 1024, 0, st>>>(w.first, w.status + 8, n6, w.pseg, w.poff, w.status + kPackTotalWord);
     }
     if (kreq > 0 || packed) {
       static int* h_split = nullptr;
-      if (!h_split && cudaHostAlloc((void**)&h_split, 8 * sizeof(int), cudaHostAllocDefault) != cudaSuccess)
+      if (!h_split && cudaHostAlloc((void**)&h_split, 64 * sizeof(int), cudaHostAllocDefault) != cudaSuccess)
         return DROID_ERR_CUDA;
-      if (cudaMemcpyAsync(h_split, w.status + 18, 7 * sizeof(int), cudaMemcpyDeviceToHost, st) !=
+      if (cudaMemcpyAsync(h_split, w.status + 18, (kPackTotalWord - 18 + 1) * sizeof(int), cudaMemcpyDeviceToHost, st) !=
               cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess)
         return DROID_ERR_CUDA;
       if (kreq > 0) {
@@ -1271,7 +1272,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
         if (nchains > 0 && n6 - chain_end[nchains - 1] > n6 / 4 + 8) return DROID_ERR_CUDA;
       }
       if (packed) {
-        pack_total = h_split[6];
+        pack_total = h_split[kPackTotalWord - 18];
         if (pack_total < n6 || (size_t)pack_total > (size_t)n6 * (n6 + 1) / 2) return DROID_ERR_CUDA;
       }
     }

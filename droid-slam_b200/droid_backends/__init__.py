@@ -462,19 +462,22 @@ def chol_solve(A, b, first=None, chain_end=None):
 
 
 def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1,
-               iterations, lm, ep, motion_only, group=None, edge_row=None):
+               iterations, lm, ep, motion_only, group=None, edge_row=None, bounds=None):
     """Multi-GPU global BA.  Poses, depth maps and the edge list are replicated; rank r accumulates the
-    source frames kx in its contiguous shard (shard_range), the reduced camera system -- packed to its structural
-    non-zeros -- is summed with one NCCL all-reduce per iteration, every rank solves it (replicated, deterministic) and
-    updates all poses plus the depths of its own frames; the depth maps are all-gathered at the end so every rank
-    returns the same state as single-GPU ba().
+    source frames kx in its contiguous shard [bounds[r], bounds[r+1]) (default: shard_bounds, balanced by work), the
+    reduced camera system -- packed to its structural non-zeros -- is summed with one NCCL all-reduce per iteration,
+    every rank solves it (replicated, deterministic) and updates all poses plus the depths of its own frames; the
+    depth maps are all-gathered at the end so every rank returns the same state as single-GPU ba().
     ``targets`` / ``weights`` hold either one row per edge (replicated), or only the rows of THIS rank's edges
     (``shard_edges``; in edge order) -- then ``edge_row`` (from ``shard_edge_rows``) maps an edge to its row; it is
     computed here when omitted."""
     import torch.distributed as dist
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
-    lo, hi, per = shard_range(disps.shape[0], world, rank)
+    nbuf = disps.shape[0]
+    if bounds is None:
+        bounds = shard_bounds(ii, nbuf, world)
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
     if edge_row is None and targets.shape[0] != ii.shape[0]:
         edge_row, count = shard_edge_rows(ii, lo, hi)
         if count != targets.shape[0] or count != weights.shape[0]:
@@ -489,7 +492,7 @@ def ba_sharded(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, 
     out = ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations,
              lm, ep, motion_only, _shard=(lo, hi), _reduce=_reduce, _edge_row=edge_row)
     if not motion_only and world > 1:
-        gather_depth_shards(disps, lo, hi, per, world, group)
+        gather_depth_shards(disps, bounds, rank, group)
     return out
 
 
@@ -507,18 +510,42 @@ def shard_edge_rows(ii, lo, hi):
 
 
 def shard_range(nbuf, world, rank):
-    """Contiguous source-frame shard [lo, hi) of rank `rank` and the (padded) shard length."""
+    """Contiguous source-frame shard [lo, hi) of rank `rank` and the (padded) shard length: equal frame counts."""
     per = (nbuf + world - 1) // world
     return min(nbuf, rank * per), min(nbuf, (rank + 1) * per), per
 
 
-def gather_depth_shards(disps, lo, hi, per, world, group=None):
-    """Every rank updated only disps[lo:hi]; all-gather the shards so that all ranks hold the full buffer."""
+def shard_bounds(ii, nbuf, world):
+    """Contiguous source-frame shards balanced by WORK instead of by frame count ("greedy balance on
+    out-degree"): frame k costs deg_k * (deg_k + 12) (linearisation ~ deg, Schur Gram ~ deg^2), the cut points are
+    the world-quantiles of the cumulative cost.  Returns world + 1 frame indices; a pure function of the edge list,
+    so every rank computes the same cuts.  ``ii`` may be a CPU or CUDA tensor (one small D2H read)."""
+    deg = torch.bincount(ii.clamp(0, nbuf - 1), minlength=nbuf).to(torch.float64)
+    cost = torch.cumsum(deg * (deg + 12.0), 0)
+    total = float(cost[-1].item()) if nbuf > 0 else 0.0
+    if total <= 0.0:
+        return [shard_range(nbuf, world, r)[0] for r in range(world)] + [nbuf]
+    q = torch.arange(1, world, dtype=torch.float64, device=cost.device) * (total / world)
+    cuts = (torch.searchsorted(cost, q) + 1).clamp(max=nbuf).tolist() if world > 1 else []
+    b = [0] + [int(c) for c in cuts] + [nbuf]
+    for i in range(1, len(b)):                  # monotone
+        b[i] = max(b[i], b[i - 1])
+    return b
+
+
+def gather_depth_shards(disps, bounds, rank, group=None):
+    """Every rank updated only disps[bounds[rank]:bounds[rank+1]]; all-gather the shards (padded to the longest) so
+    that all ranks hold the full buffer."""
     import torch.distributed as dist
-    nbuf = disps.shape[0]
+    world = len(bounds) - 1
+    per = max(1, max(int(bounds[r + 1]) - int(bounds[r]) for r in range(world)))
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
     flat = disps.new_zeros((per * world,) + tuple(disps.shape[1:]))
     dist.all_gather_into_tensor(flat, _pad_rows(disps[lo:hi], per), group=group)
-    disps.copy_(flat[:nbuf])
+    for r in range(world):
+        a, b = int(bounds[r]), int(bounds[r + 1])
+        if r != rank and b > a:
+            disps[a:b].copy_(flat[r * per:r * per + (b - a)])
     return disps
 
 

@@ -22,7 +22,10 @@ def _worker(rank, world, port, nbuf, q):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     import droid_backends as B
-    lo, hi, per = B.shard_range(nbuf, world, rank)
+    ii = torch.from_numpy(np.random.default_rng(3).integers(0, nbuf, size=20 * nbuf))
+    bounds = B.shard_bounds(ii, nbuf, world)
+    lo, hi = bounds[rank], bounds[rank + 1]
+    per = max(bounds[r + 1] - bounds[r] for r in range(world))
     # (1) partial systems: rank r contributes only the source frames of its shard; the sum must equal the whole
     rng = np.random.default_rng(7)
     n6 = 30
@@ -34,7 +37,7 @@ def _worker(rank, world, port, nbuf, q):
     disps = torch.zeros(nbuf, 4, 6)
     full = torch.arange(nbuf * 24, dtype=torch.float32).view(nbuf, 4, 6)
     disps[lo:hi] = full[lo:hi]
-    B.gather_depth_shards(disps, lo, hi, per, world)
+    B.gather_depth_shards(disps, bounds, rank)
     ok_gather = torch.equal(disps, full)
     q.put((rank, lo, hi, per, bool(ok_sum), bool(ok_gather)))
     dist.barrier()
@@ -69,3 +72,19 @@ def test_shard_range_properties(backends):
                 assert 0 <= lo <= hi <= nbuf and hi - lo <= per
                 seen += list(range(lo, hi))
             assert seen == list(range(nbuf))
+
+
+def test_shard_bounds_balance_the_work(backends):
+    """Work-balanced contiguous shards: cuts are monotone, cover every frame once, and no shard carries more than
+    its share of the cost plus one frame's worth."""
+    rng = np.random.default_rng(5)
+    nbuf = 300
+    deg = rng.integers(4, 32, size=nbuf)
+    ii = torch.from_numpy(np.repeat(np.arange(nbuf), deg))
+    cost = (deg * (deg + 12.0))
+    for world in (1, 2, 4, 8):
+        b = backends.shard_bounds(ii, nbuf, world)
+        assert len(b) == world + 1 and b[0] == 0 and b[-1] == nbuf and all(b[i] <= b[i + 1] for i in range(world))
+        share = cost.sum() / world
+        for r in range(world):
+            assert cost[b[r]:b[r + 1]].sum() <= share + cost.max() + 1e-9
