@@ -1315,10 +1315,11 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
       }
       if (!p->motion_only) {
         ProfScope ps(DROID_PROF_BA_SCHUR, st);
-        // Gram products on the tensor cores for frames with <= 20 edges (schur_tc.cu), CUDA-core kernel for the
+        // Gram products on the tensor cores for frames with <= 31 edges (schur_tc.cu), CUDA-core kernel for the
         // rest.  The two kernels touch disjoint frames, so the CUDA-core one runs on a second stream: its few, long
         // CTAs start first and the tensor-core CTAs fill the SMs around them instead of waiting for its tail.
-        static const bool use_tc = []() { const char* e = getenv("DROID_SCHUR_TC"); return !(e && e[0] == '0'); }();
+        static const bool tc_on = []() { const char* e = getenv("DROID_SCHUR_TC"); return !(e && e[0] == '0'); }();
+        const bool use_tc = tc_on && (HW % 4 == 0);      // the tensor-core builders move 4 pixels per 16-byte access
         static cudaStream_t s2 = nullptr;
         static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
         static int s2_dev = -1;

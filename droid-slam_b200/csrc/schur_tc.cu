@@ -39,17 +39,18 @@
 namespace droid {
 namespace stc {
 
-static constexpr int kBuild = 256;
 static constexpr int kThreads = 512;             // 8 builder warps, 6 drain warps, 1 MMA warp, 1 spare (128 registers)
-static constexpr int kT = 32;                    // pixels per chunk
-static constexpr int kLbo = kT * 128;            // bytes between consecutive 32-row atoms (4 KB)
-static constexpr int kHalf = 4 * kLbo;           // one operand array (F_hi or F_lo) of one stage: 16 KB
-static constexpr int kStage = 2 * kHalf;
-static constexpr int kELd = 132;                 // fp32 staging row stride (floats): 16-byte rows, spreads the banks
-static constexpr int kTB = 128;                   // pixels per build pass (4 MMA chunks): long enough to pipeline the loads
-static constexpr int kEBytes = kTB * kELd * 4;
-static constexpr int kMetaOff = 2 * kStage + kEBytes;
+static constexpr int kT = 32;                    // pixels per chunk = one 128-byte row of a K-major operand tile
+static constexpr int kHalf = 128 * kT * 4;       // one operand array (F_hi or F_lo) of one stage: 128 rows x 128 B
+static constexpr int kStage = 2 * kHalf;         // 32 KB
+static constexpr int kStages = 4;                // = chunks of one build pass (128 pixels)
+static constexpr int kTB = kStages * kT;
+static constexpr int kELd = 132;                 // row stride (floats) of G in the epilogue
+static constexpr int kGBytes = 128 * kELd * 4;
+static constexpr int kTsOff = 72 * 1024;         // epilogue scratch behind G, inside the (then idle) operand stages
+static constexpr int kMetaOff = kStages * kStage;
 static constexpr int kSmem = kMetaOff + 8192 + 1024;
+static_assert(kGBytes <= kTsOff && kTsOff + 5 * 6 * 128 * 4 <= kMetaOff, "epilogue scratch must fit in the stages");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -84,23 +85,21 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
     __nanosleep(100);
   }
 }
-// shared-memory matrix descriptor: MN-major 32-bit operands use the SWIZZLE_128B_BASE32B layout (type 1; the plain
-// 128-byte swizzle yields zeros for tf32 MN-major): 128-byte rows = 32 consecutive rows of F for one pixel, the four
-// 32-byte chunks of a row XOR-ed with (pixel & 3), atoms of 4 pixels (512 B).
-// LBO = distance between 128-byte-wide atoms along M, SBO = distance between 4-pixel groups along K.
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo) {
+// shared-memory matrix descriptor, K-major 32-bit operands, SWIZZLE_128B (layout type 2): a tile is [128 rows][32
+// pixels] with 128-byte rows, atoms of 8 rows (1024 B, SBO) whose 16-byte chunks are XOR-ed with (row & 7).  One MMA
+// consumes K = 8 pixels = 32 bytes of every row: the k-th MMA of a chunk starts 32 k bytes into the tile.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
-  d |= (uint64_t)(lbo >> 4) << 16;
-  d |= (uint64_t)(512 >> 4) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)1 << 61;
+  d |= (uint64_t)1 << 16;                  // LBO: unused for swizzled K-major operands
+  d |= (uint64_t)(1024 >> 4) << 32;        // SBO
+  d |= (uint64_t)1 << 46;                  // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                  // SWIZZLE_128B
   return d;
 }
-// instruction descriptor, kind::tf32: D = f32, A = B = tf32, both MN-major, M = N = 128
+// instruction descriptor, kind::tf32: D = f32, A = B = tf32, both K-major, M = N = 128
 __device__ __forceinline__ uint32_t umma_idesc() {
-  return (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(128 >> 3) << 17) |
-         ((uint32_t)(128 >> 4) << 24);
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
 __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
   asm volatile(
@@ -161,23 +160,25 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
   const int R = 6 * nu;                  // rows of E; row R of F carries sqrt(Q) w
 
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  float* E32 = reinterpret_cast<float*>(smem + 2 * kStage);          // [kTB][kELd]
+  float* Gs = reinterpret_cast<float*>(smem);                        // epilogue: G [128][kELd] (stages idle by then)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kMetaOff);
-  uint64_t* full = bars;        // [2]  operands of a chunk in place      (256 builder arrivals)
-  uint64_t* empty = bars + 2;   // [2]  operands consumed                 (tcgen05.commit)
-  uint64_t* gdone = bars + 4;   // [2]  accumulator of a chunk complete   (tcgen05.commit)
-  uint64_t* tfree = bars + 6;   // [2]  accumulator drained               (128 drainer arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
-  int* s_e = reinterpret_cast<int*>(bars + 10);
+  uint64_t* full = bars;        // [4]  operands of a chunk in place      (64 builder arrivals: the 2 warps of a stage)
+  uint64_t* empty = bars + 4;   // [4]  operands consumed                 (tcgen05.commit)
+  uint64_t* gdone = bars + 8;   // [2]  accumulator of a chunk complete   (tcgen05.commit)
+  uint64_t* tfree = bars + 10;  // [2]  accumulator drained               (192 drainer arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+  int* s_e = reinterpret_cast<int*>(bars + 14);
   int* s_jx = s_e + 24;
   int* pose = s_jx + 24;
-  float* s_g = reinterpret_cast<float*>(bars + 10 + 64);   // 16-byte aligned: [deg][kEdgeStride]
+  float* s_g = reinterpret_cast<float*>(bars + 14 + 64);   // 16-byte aligned: [nu][kEdgeStride]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
-    for (int i = 0; i < 2; i++) {
-      mbar_init(full + i, kBuild);
+    for (int i = 0; i < kStages; i++) {
+      mbar_init(full + i, 64);
       mbar_init(empty + i, 1);
+    }
+    for (int i = 0; i < 2; i++) {
       mbar_init(gdone + i, 1);
       mbar_init(tfree + i, 192);
     }
@@ -187,8 +188,8 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  // staging columns >= M are never written and must read as zero
-  for (int i = tid; i < kEBytes / 16; i += kThreads) reinterpret_cast<uint4*>(E32)[i] = make_uint4(0, 0, 0, 0);
+  // operand rows > R are never written and must read as zero
+  for (int i = tid; i < kStages * kStage / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
   auto edge_of = [&](int i) { return eidx[e0 + (i < nfirst ? start1 + i : start2 + (i - nfirst))]; };
   for (int i = tid; i < nu; i += kThreads) {
     const int e = edge_of(i);
@@ -214,111 +215,104 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
       // ---------------- MMA issuer ----------------
       const uint32_t idesc = umma_idesc();
       for (int c = 0; c < nchunk; c++) {
-        const int s = c & 1;
-        mbar_wait_relaxed(full + s, (c >> 1) & 1);
-        if (c >= 2) mbar_wait_relaxed(tfree + s, ((c >> 1) - 1) & 1);     // accumulator (c & 1) drained
+        const int s = c & (kStages - 1), t = c & 1;
+        mbar_wait_relaxed(full + s, (c >> 2) & 1);
+        if (c >= 2) mbar_wait_relaxed(tfree + t, ((c >> 1) - 1) & 1);     // accumulator (c & 1) drained
         tc_fence_after();
         const uint32_t hi = smem_u32(smem + s * kStage), lo = hi + kHalf;
-        const uint32_t d_t = tmem + s * 128;
+        const uint32_t d_t = tmem + t * 128;
 #pragma unroll
         for (int kk = 0; kk < kT / 8; kk++) {
-          const uint64_t f_hi = umma_desc(hi + kk * 1024, kLbo), f_lo = umma_desc(lo + kk * 1024, kLbo);
+          const uint64_t f_hi = umma_desc(hi + kk * 32), f_lo = umma_desc(lo + kk * 32);
           umma_tf32(d_t, f_hi, f_hi, idesc, kk > 0 ? 1u : 0u);
           umma_tf32(d_t, f_hi, f_lo, idesc, 1u);
           umma_tf32(d_t, f_lo, f_hi, idesc, 1u);
         }
         umma_commit(empty + s);
-        umma_commit(gdone + s);
+        umma_commit(gdone + t);
       }
     }
   } else if (warp < 8) {
     // ---------------- F builders ----------------
-    // A build pass covers kTB = 128 pixels (two threads per pixel, each taking every other edge, inputs of the next
-    // edge prefetched), then the four 32-pixel chunks of the pass are packed and handed to the MMA issuer.
-    const int pl = tid >> 1, g = tid & 1;
-    float* Erow = E32 + pl * kELd;
+    // A build pass covers kTB = 128 pixels = 4 chunks = the 4 operand stages.  Warp w builds chunk (w & 3) of every
+    // pass; inside the warp a lane owns 4 consecutive pixels (one 16-byte unit of a K-major row: kq = lane & 7) of the
+    // edges i = slice, slice + 8, slice + 16 with slice = 4 (w >> 2) + (lane >> 3).  Per (4 pixels, edge) the packed
+    // E_j (ba_lin.cuh: 5 floats per pixel-edge, left behind by ba_accum_kernel) arrives as five 16-byte loads, is
+    // unpacked, scaled by sqrt(Q), split into tf32 hi + lo and stored straight into the swizzled operand tile: one
+    // 16-byte store per row and array, a quarter-warp covers one whole 128-byte row (conflict-free).  The loads of a
+    // pass are issued one pass ahead into registers.
+    const int sub = warp & 3, kq = lane & 7, slice = 4 * (warp >> 2) + (lane >> 3);
+    unsigned char* stage = smem + sub * kStage;
     const int npass = (p1 - p0 + kTB - 1) / kTB;
-    // The packed E_j (ba_lin.cuh: 5 floats per pixel-edge, left behind by ba_accum_kernel) of a thread's (up to 10)
-    // edges live in registers one whole pass ahead: as soon as item i of this pass has been consumed, the same
-    // registers are re-loaded with item i of the next pass, so every global load has a full pass to arrive.
-    constexpr int kMaxI = (kSchurTcMaxU + 1) / 2;     // edges per thread
-    float r_c[kMaxI][kEjComp];
-    float n_q = 0.f, n_w = 0.f;
+    constexpr int kMaxI = (kSchurTcMaxU + 7) / 8;     // edges per thread
+    float4 r_c[kMaxI][kEjComp];
+    float4 n_q = make_float4(0.f, 0.f, 0.f, 0.f), n_w = n_q;
     auto fetch = [&](int it, int p, bool ok) {
-      const int i = g + 2 * it;
+      const int i = slice + 8 * it;
       if (ok && i < nu) {
         const float* src = ejc + (size_t)s_e[i] * kEjComp * HW + p;
 #pragma unroll
-        for (int q = 0; q < kEjComp; q++) r_c[it][q] = __ldcs(src + (size_t)q * HW);
+        for (int q = 0; q < kEjComp; q++) r_c[it][q] = __ldcs(reinterpret_cast<const float4*>(src + (size_t)q * HW));
       }
     };
     auto fetch_pix = [&](int p, bool ok) {
-      n_q = ok ? Qi[(size_t)m * HW + p] : 0.f;
-      n_w = ok ? Wi[(size_t)m * HW + p] : 0.f;
+      n_q = ok ? __ldg(reinterpret_cast<const float4*>(Qi + (size_t)m * HW + p)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (slice == 7) n_w = ok ? __ldg(reinterpret_cast<const float4*>(Wi + (size_t)m * HW + p)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    };
+    // 16-byte store of 4 pixels of row r: hi and lo parts
+    auto put_row = [&](int r, float x0, float x1, float x2, float x3) {
+      uint4 h, l;
+      h.x = tf32_rna(x0); h.y = tf32_rna(x1); h.z = tf32_rna(x2); h.w = tf32_rna(x3);
+      l.x = tf32_rna(x0 - __uint_as_float(h.x)); l.y = tf32_rna(x1 - __uint_as_float(h.y));
+      l.z = tf32_rna(x2 - __uint_as_float(h.z)); l.w = tf32_rna(x3 - __uint_as_float(h.w));
+      const int r7 = r & 7;
+      const int off = ((r >> 3) << 10) + (r7 << 7) + ((kq ^ r7) << 4);
+      *reinterpret_cast<uint4*>(stage + off) = h;
+      *reinterpret_cast<uint4*>(stage + kHalf + off) = l;
     };
 #pragma unroll
     for (int it = 0; it < kMaxI; it++)
 #pragma unroll
-      for (int q = 0; q < kEjComp; q++) r_c[it][q] = 0.f;
-    fetch_pix(p0 + pl, p0 + pl < p1);
+      for (int q = 0; q < kEjComp; q++) r_c[it][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int pq = p0 + 32 * sub + 4 * kq;             // this lane's 4 pixels in pass 0
+    fetch_pix(pq, pq < p1);
 #pragma unroll
-    for (int it = 0; it < kMaxI; it++) fetch(it, p0 + pl, p0 + pl < p1);
+    for (int it = 0; it < kMaxI; it++) fetch(it, pq, pq < p1);
     for (int ps = 0; ps < npass; ps++) {
-      const int p = p0 + ps * kTB + pl;
+      const int c = ps * kStages + sub;
+      if (c >= nchunk) break;
+      const int p = pq + ps * kTB;
       const bool valid = p < p1;
       const int pn = p + kTB;
       const bool valid_n = pn < p1;
-      const float sq = valid ? sqrtf(n_q) : 0.f, wv_pix = n_w;
+      const float sq0 = valid ? sqrtf(n_q.x) : 0.f, sq1 = valid ? sqrtf(n_q.y) : 0.f;
+      const float sq2 = valid ? sqrtf(n_q.z) : 0.f, sq3 = valid ? sqrtf(n_q.w) : 0.f;
+      const float4 wv = n_w;
       fetch_pix(pn, valid_n);
+      if (ps > 0) mbar_wait(empty + sub, (ps - 1) & 1);          // the MMAs of the previous pass have read this stage
 #pragma unroll
       for (int it = 0; it < kMaxI; it++) {
-        const int i = g + 2 * it;
+        const int i = slice + 8 * it;
         if (i < nu) {
-          float pk[kEjComp];
+          float4 pk[kEjComp];
 #pragma unroll
           for (int q = 0; q < kEjComp; q++) pk[q] = r_c[it][q];
           fetch(it, pn, valid_n);
-          float ej[6];
-          ej_unpack(pk, ej);
-          float2* dst = reinterpret_cast<float2*>(Erow + 6 * i);
-          dst[0] = make_float2(sq * ej[0], sq * ej[1]);
-          dst[1] = make_float2(sq * ej[2], sq * ej[3]);
-          dst[2] = make_float2(sq * ej[4], sq * ej[5]);
-        }
-      }
-      if (g == 1) Erow[R] = sq * wv_pix;
-      asm volatile("bar.sync 1, 256;" ::: "memory");      // pass staged
-      // ---- pack: 8 consecutive rows of one pixel = one 32-byte unit of the UMMA layout; 2 units per thread and chunk
-      for (int sub = 0; sub < kTB / kT; sub++) {
-        const int c = ps * (kTB / kT) + sub;
-        if (c >= nchunk) break;
-        const int s = c & 1;
-        if (c >= 2) mbar_wait(empty + s, ((c >> 1) - 1) & 1);
-        unsigned char* stage = smem + s * kStage;
-        const float* Es = E32 + sub * (kT * kELd);
+          float e0v[6], e1v[6], e2v[6], e3v[6];
+          {
+            const float c0[5] = {pk[0].x, pk[1].x, pk[2].x, pk[3].x, pk[4].x};
+            const float c1[5] = {pk[0].y, pk[1].y, pk[2].y, pk[3].y, pk[4].y};
+            const float c2[5] = {pk[0].z, pk[1].z, pk[2].z, pk[3].z, pk[4].z};
+            const float c3[5] = {pk[0].w, pk[1].w, pk[2].w, pk[3].w, pk[4].w};
+            ej_unpack(c0, e0v); ej_unpack(c1, e1v); ej_unpack(c2, e2v); ej_unpack(c3, e3v);
+          }
 #pragma unroll
-        for (int u = 0; u < 2; u++) {
-          const int task = tid + u * kBuild;          // 512 tasks = 32 pixels x 16 row groups
-          const int px = task & 31, rg = task >> 5;
-          const float4 x0 = *reinterpret_cast<const float4*>(Es + px * kELd + 8 * rg);
-          const float4 x1 = *reinterpret_cast<const float4*>(Es + px * kELd + 8 * rg + 4);
-          uint4 h0, h1, l0, l1;
-          h0.x = tf32_rna(x0.x); h0.y = tf32_rna(x0.y); h0.z = tf32_rna(x0.z); h0.w = tf32_rna(x0.w);
-          h1.x = tf32_rna(x1.x); h1.y = tf32_rna(x1.y); h1.z = tf32_rna(x1.z); h1.w = tf32_rna(x1.w);
-          l0.x = tf32_rna(x0.x - __uint_as_float(h0.x)); l0.y = tf32_rna(x0.y - __uint_as_float(h0.y));
-          l0.z = tf32_rna(x0.z - __uint_as_float(h0.z)); l0.w = tf32_rna(x0.w - __uint_as_float(h0.w));
-          l1.x = tf32_rna(x1.x - __uint_as_float(h1.x)); l1.y = tf32_rna(x1.y - __uint_as_float(h1.y));
-          l1.z = tf32_rna(x1.z - __uint_as_float(h1.z)); l1.w = tf32_rna(x1.w - __uint_as_float(h1.w));
-          const int off = (rg >> 2) * kLbo + px * 128 + (((rg & 3) ^ (px & 3)) << 5);
-          *reinterpret_cast<uint4*>(stage + off) = h0;
-          *reinterpret_cast<uint4*>(stage + off + 16) = h1;
-          *reinterpret_cast<uint4*>(stage + kHalf + off) = l0;
-          *reinterpret_cast<uint4*>(stage + kHalf + off + 16) = l1;
+          for (int n = 0; n < 6; n++) put_row(6 * i + n, sq0 * e0v[n], sq1 * e1v[n], sq2 * e2v[n], sq3 * e3v[n]);
         }
-        fence_async_smem();
-        mbar_arrive(full + s);
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");      // staging buffer free for the next pass
+      if (slice == 7) put_row(R, sq0 * wv.x, sq1 * wv.y, sq2 * wv.z, sq3 * wv.w);
+      fence_async_smem();
+      mbar_arrive(full + sub);
     }
   } else if (warp != 12) {
     // ---------------- drainers: half a row of G per thread (TMEM lane quarter = warp % 4) ----------------
@@ -346,9 +340,9 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
       tc_fence_before();
       mbar_arrive(tfree + s);
     }
-    // ---- hand the row to the epilogue: G[r][64 hh .. 64 hh + 63] -> shared memory (the fp32 staging buffer is free:
-    // the last chunk's MMAs, which this thread has just waited for, were issued after the builders' last read of it)
-    float4* grow = reinterpret_cast<float4*>(E32 + r * kELd + 64 * hh);
+    // ---- hand the row to the epilogue: G[r][64 hh .. 64 hh + 63] -> shared memory (the operand stages are idle: this
+    // thread has just waited for the commit behind the last chunk's MMAs, which covers every MMA before it)
+    float4* grow = reinterpret_cast<float4*>(Gs + r * kELd + 64 * hh);
 #pragma unroll
     for (int j = 0; j < 16; j++) grow[j] = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
   }
@@ -356,8 +350,7 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
   __syncthreads();
   // ---------------- epilogue (all warps): G in shared memory (lower triangle valid), operand stages free ----------------
   {
-    const float* Gs = E32;
-    float* Ts = reinterpret_cast<float*>(smem);       // [4][6][128] partial sums of T = sum_e N_e G[e, :]
+    float* Ts = reinterpret_cast<float*>(smem + kTsOff);   // [4][6][128] partial sums of T = sum_e N_e G[e, :]
     float* Tf = Ts + 4 * 6 * 128;                     // [6][128]
     const int n6 = 6 * P;
     const int ps = pose[0];
