@@ -24,7 +24,7 @@
 //   warps 0-7   builders: stream the packed E_j of every (pixel, edge) (left behind by ba_accum_kernel), stage the
 //               chunk's F as plain fp32 in shared memory, then re-pack it (split + 16-byte stores) into the canonical
 //               MN-major UMMA layout for 32-bit operands (SWIZZLE_128B_BASE32B);
-//   warp 13     one thread issues the 12 tcgen05.mma of a chunk into TMEM buffer (chunk & 1);
+//   warp 13     one thread issues the 12 tcgen05.mma of a chunk into TMEM accumulator (chunk & 3);
 //   warps 8-11, 14-15  drainers: TMEM -> registers, fp32 accumulation of half a row of G per thread;
 //   epilogue    (all warps) G goes to shared memory, the source pose's rows are derived from it, and everything is
 //               subtracted from the dense reduced system with fp64 atomics, lanes along a row (same block placement
@@ -121,6 +121,19 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
 #pragma unroll
   for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr) : "memory");
+#pragma unroll
+  for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -164,28 +177,26 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kMetaOff);
   uint64_t* full = bars;        // [4]  operands of a chunk in place      (64 builder arrivals: the 2 warps of a stage)
   uint64_t* empty = bars + 4;   // [4]  operands consumed                 (tcgen05.commit)
-  uint64_t* gdone = bars + 8;   // [2]  accumulator of a chunk complete   (tcgen05.commit)
-  uint64_t* tfree = bars + 10;  // [2]  accumulator drained               (192 drainer arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
-  int* s_e = reinterpret_cast<int*>(bars + 14);
+  uint64_t* gdone = bars + 8;   // [4]  accumulator of a chunk complete   (tcgen05.commit)
+  uint64_t* tfree = bars + 12;  // [4]  accumulator drained               (192 drainer arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+  int* s_e = reinterpret_cast<int*>(bars + 18);
   int* s_jx = s_e + 24;
   int* pose = s_jx + 24;
-  float* s_g = reinterpret_cast<float*>(bars + 14 + 64);   // 16-byte aligned: [nu][kEdgeStride]
+  float* s_g = reinterpret_cast<float*>(bars + 18 + 64);   // 16-byte aligned: [nu][kEdgeStride]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
     for (int i = 0; i < kStages; i++) {
       mbar_init(full + i, 64);
       mbar_init(empty + i, 1);
-    }
-    for (int i = 0; i < 2; i++) {
       mbar_init(gdone + i, 1);
       mbar_init(tfree + i, 192);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 13) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   // operand rows > R are never written and must read as zero
@@ -215,12 +226,12 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
       // ---------------- MMA issuer ----------------
       const uint32_t idesc = umma_idesc();
       for (int c = 0; c < nchunk; c++) {
-        const int s = c & (kStages - 1), t = c & 1;
+        const int s = c & (kStages - 1);          // operand stage = accumulator (4 x 128 TMEM columns)
         mbar_wait_relaxed(full + s, (c >> 2) & 1);
-        if (c >= 2) mbar_wait_relaxed(tfree + t, ((c >> 1) - 1) & 1);     // accumulator (c & 1) drained
+        if (c >= kStages) mbar_wait_relaxed(tfree + s, ((c >> 2) - 1) & 1);     // accumulator drained
         tc_fence_after();
         const uint32_t hi = smem_u32(smem + s * kStage), lo = hi + kHalf;
-        const uint32_t d_t = tmem + t * 128;
+        const uint32_t d_t = tmem + s * 128;
 #pragma unroll
         for (int kk = 0; kk < kT / 8; kk++) {
           const uint64_t f_hi = umma_desc(hi + kk * 32), f_lo = umma_desc(lo + kk * 32);
@@ -229,7 +240,7 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
           umma_tf32(d_t, f_lo, f_hi, idesc, 1u);
         }
         umma_commit(empty + s);
-        umma_commit(gdone + t);
+        umma_commit(gdone + s);
       }
     }
   } else if (warp < 8) {
@@ -253,6 +264,10 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
         const float* src = ejc + (size_t)s_e[i] * kEjComp * HW + p;
 #pragma unroll
         for (int q = 0; q < kEjComp; q++) r_c[it][q] = __ldcs(reinterpret_cast<const float4*>(src + (size_t)q * HW));
+        if (p + kTB < p1) {      // and the pass after that on its way into L2
+#pragma unroll
+          for (int q = 0; q < kEjComp; q++) asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (size_t)q * HW + kTB));
+        }
       }
     };
     auto fetch_pix = [&](int p, bool ok) {
@@ -323,18 +338,18 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
 #pragma unroll
     for (int j = 0; j < 64; j++) acc[j] = 0.f;
     for (int c = 0; c < nchunk; c++) {
-      const int s = c & 1;
-      mbar_wait_relaxed(gdone + s, (c >> 1) & 1);
+      const int s = c & (kStages - 1);
+      mbar_wait_relaxed(gdone + s, (c >> 2) & 1);
       tc_fence_after();
       {
         const uint32_t taddr = tmem + s * 128 + 64 * hh + ((uint32_t)(32 * qd) << 16);
 #pragma unroll
-        for (int part = 0; part < 4; part++) {
-          float v[16];
-          tmem_ld16(taddr + 16 * part, v);
+        for (int part = 0; part < 2; part++) {
+          float v[32];
+          tmem_ld32(taddr + 32 * part, v);
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 16; j++) acc[16 * part + j] += v[j];
+          for (int j = 0; j < 32; j++) acc[32 * part + j] += v[j];
         }
       }
       tc_fence_before();
@@ -428,7 +443,7 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
     }
   }
   if (warp == 13) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
   }
 }
 
