@@ -695,9 +695,15 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
     double* __restrict__ A, double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P,
     int n_eta, int motion_only, int frame_lo, int frame_hi, const int* __restrict__ ppos,
     float* __restrict__ ejc, const int* __restrict__ edge_row) {
-  __shared__ float Cs[kSlabMax];
-  __shared__ float Bs[kSlabMax];
-  __shared__ float Ds[kSlabMax];   // inverse depths of the slab (re-read for every edge of the frame)
+  // per pixel of the slab (dynamic shared memory, 5 x slab floats): C and bz sums, inverse depth and the normalised
+  // image coordinates -- the last three are the same for every edge of the frame, so the row/column split of the
+  // pixel index (an integer division) and the two float divisions by fx, fy are paid once per pixel, not per pixel-edge
+  extern __shared__ __align__(16) float accum_dyn[];
+  float* Cs = accum_dyn;
+  float* Bs = Cs + slab;
+  float* Ds = Bs + slab;
+  float* Xs = Ds + slab;
+  float* Ys = Xs + slab;
   __shared__ float red[kThreads / 32][32];
   __shared__ float s_sum[32];      // Hjj (21, lower triangle row-major) | vj (6)
   const int m = blockIdx.y;
@@ -712,7 +718,12 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
   const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
   const int n6 = 6 * P;
   const float* __restrict__ dmap = disps + (size_t)k * HW;
-  for (int p = tid; p < p1 - p0; p += kThreads) { Cs[p] = 0.f; Bs[p] = 0.f; Ds[p] = dmap[p0 + p]; }
+  for (int p = tid; p < p1 - p0; p += kThreads) {
+    Cs[p] = 0.f; Bs[p] = 0.f; Ds[p] = dmap[p0 + p];
+    const int pi = (p0 + p) / wd, pj = (p0 + p) - pi * wd;
+    Xs[p] = ((float)pj - K.cx) / K.fx;
+    Ys[p] = ((float)pi - K.cy) / K.fy;
+  }
   __syncthreads();
   const int e0 = eptr[m], e1 = eptr[m + 1];
   // Edge metadata (edge id, target frame, relative pose, N) is staged in shared memory in chunks, and the four
@@ -759,7 +770,7 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
           if (ein < nE) fetch(ein, pn);
         }
         PixLinJ L;
-        linearise_j(g, K, wd, p, Ds[p - p0], tu, tv, wu, wv, stereo, L);
+        linearise_j_xy(g, K, Xs[p - p0], Ys[p - p0], Ds[p - p0], tu, tv, wu, wv, stereo, L);
         // depth terms (:320-321, :353-354)
         float c = L.wu_d * L.Jz_u * L.Jz_u;
         float bz = L.wu_d * L.ru * L.Jz_u;
@@ -1282,6 +1293,8 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   if (!attr_set) {
     cudaFuncSetAttribute(ba_schur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          kSchurSmemBytes);
+    cudaFuncSetAttribute(ba_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         5 * kSlabMax * (int)sizeof(float));
     attr_set = true;
   }
   // slabs: enough CTAs to fill the 148 SMs twice when there are few frames
@@ -1308,7 +1321,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     if (p->n_edges > 0 && p->n_eta > 0) {
       {
         ProfScope ps(DROID_PROF_BA_ACCUM, st);
-        DROID_LAUNCH ba_accum_kernel<<<dim3(S, p->n_eta), kThreads, 0, st>>>(
+        DROID_LAUNCH ba_accum_kernel<<<dim3(S, p->n_eta), kThreads, 5 * (size_t)slab * sizeof(float), st>>>(
             disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, w.gij, w.status, w.kx,
             w.eptr, w.eidx, w.Q, w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, p->motion_only,
             frame_lo, frame_hi, ppos, w.ejc, p->edge_row);

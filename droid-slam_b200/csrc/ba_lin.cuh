@@ -45,14 +45,13 @@ __device__ __forceinline__ void ej_unpack(const float (&c)[5], float (&ej)[6]) {
   ej[5] = b * xd - a * yd;
 }
 
-__device__ __forceinline__ void linearise_j(const SE3& g, const Intr& K, int wd, int k, float disp,
-                                            float tu, float tv, float wru, float wrv, bool stereo,
-                                            PixLinJ& L) {
-  const int i = k / wd, j = k - i * wd;
-  const float u = (float)j, v = (float)i;
+// x0, y0 = normalised image coordinates (u - cx) / fx, (v - cy) / fy of the pixel
+__device__ __forceinline__ void linearise_j_xy(const SE3& g, const Intr& K, float x0, float y0, float disp,
+                                               float tu, float tv, float wru, float wrv, bool stereo,
+                                               PixLinJ& L) {
   float Xi[4], Xj[4];
-  Xi[0] = (u - K.cx) / K.fx;
-  Xi[1] = (v - K.cy) / K.fy;
+  Xi[0] = x0;
+  Xi[1] = y0;
   Xi[2] = 1;
   Xi[3] = disp;
   act_se3(g.t, g.q, Xi, Xj);
@@ -83,6 +82,13 @@ __device__ __forceinline__ void linearise_j(const SE3& g, const Intr& K, int wd,
   L.wu = stereo ? 0.f : L.wu_d;
   L.wv = stereo ? 0.f : L.wv_d;
   L.xd = x * d; L.yd = y * d; L.hd = h * d;
+}
+
+__device__ __forceinline__ void linearise_j(const SE3& g, const Intr& K, int wd, int k, float disp,
+                                            float tu, float tv, float wru, float wrv, bool stereo,
+                                            PixLinJ& L) {
+  const int i = k / wd, j = k - i * wd;
+  linearise_j_xy(g, K, ((float)j - K.cx) / K.fx, ((float)i - K.cy) / K.fy, disp, tu, tv, wru, wrv, stereo, L);
 }
 
 // N[n][a] with Ji[n] = sum_a N[n][a] Jj[a]  (row-major 6x6): column a is -adj_se3(g, e_a)
