@@ -353,9 +353,20 @@ def run_b200(args, world, rank, local):
                              "note": "envelope Cholesky of the re-ordered reduced camera system; ~1% of the dense flops "
                                      "remain, the time is the dependent chain of 6P pivots (panel -> update -> panel)"}
     # `roofline` itself: the largest THROUGHPUT phase (the solve is a latency chain, see table)
+    # DRAM traffic per launch of the same kernels from the committed ncu --set full capture (same workload only)
+    traffic = {}
+    try:
+        if p["n"] == 1000 and len(p["ii"]) == 20862 and world == 1:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+    except Exception:
+        traffic = {}
+    for k in table:
+        if k in traffic:
+            table[k]["traffic"] = int(traffic[k])
     dom = max((k for k in ("ba_accum", "ba_schur", "ba_update") if k in table), key=lambda k: table[k]["ms"])
     roof = {"kernel": dom, "bound": table[dom]["bound"], "achieved": table[dom]["achieved"], "peak": table[dom]["peak"],
-            "unit": table[dom]["unit"], "frac": table[dom]["frac"], "traffic": None,
+            "unit": table[dom]["unit"], "frac": table[dom]["frac"], "traffic": table[dom].get("traffic"),
+            "traffic_source": traffic.get("source") if table[dom].get("traffic") else None,
             "peak_source": ("measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)") +
                            ("; tf32 = bf16_tflops / 2" if table[dom]["bound"] == "tensor" else ""),
             "ms_per_launch": table[dom]["ms"], "phases": table}
