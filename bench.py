@@ -369,7 +369,12 @@ def run_b200(args, world, rank, local):
             "traffic_source": traffic.get("source") if table[dom].get("traffic") else None,
             "peak_source": ("measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)") +
                            ("; tf32 = bf16_tflops / 2" if table[dom]["bound"] == "tensor" else ""),
-            "ms_per_launch": table[dom]["ms"], "phases": table}
+            "ms_per_launch": table[dom]["ms"], "phases": table,
+            # the whole Gauss-Newton iteration against SURVEY 8(d)'s compulsory traffic (1.0 GB at C4): what an ideal
+            # single-pass BA would be bound by; the Schur Gram product and the fp64 factorisation keep it far from that
+            "iteration": {"algorithmic_bytes": int(alg["iter_bytes"]), "ms": ms / iters,
+                          "achieved": alg["iter_bytes"] / (ms / iters * 1e-3) / 1e9, "unit": "GB/s",
+                          "frac": alg["iter_bytes"] / (ms / iters * 1e-3) / 1e9 / hbm_peak}}
     line = {
         "metric": "global BA iters/s @1000 KF", "value": value, "unit": "iters/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
