@@ -252,9 +252,16 @@ def run_b200(args, world, rank, local):
             host["weights"] = torch.from_numpy(np.ascontiguousarray(p["weights"][mask])).pin_memory()
             host["edge_row"] = torch.from_numpy(np.maximum(np.cumsum(mask) - 1, 0).astype(np.int32)).pin_memory()
             ekeys = KEYS + ("edge_row",)
-            h2d = sum(host[k].numel() * host[k].element_size() for k in ekeys)
+            # per-frame inputs (depth maps, sensor depths, eta): a rank reads only the rows of its own source frames
+            # (the depth maps of the other shards arrive through the all-gather at the end of the call), so it uploads
+            # only those rows.  eta is indexed by slot in kx = unique(ii U [t0,t1)), which here is every frame in order.
+            kx = np.unique(np.concatenate([np.arange(t0, t1), p["ii"]]))
+            rows_ok = len(kx) == p["disps"].shape[0] and np.array_equal(kx, np.arange(len(kx)))
+            row_keys = ("disps", "disps_sens", "eta") if rows_ok else ()
+            h2d = sum(host[k].numel() * host[k].element_size() for k in ekeys if k not in row_keys)
+            h2d += sum(host[k][lo:hi].numel() * host[k].element_size() for k in row_keys)
             h2d = int(sum_over_ranks(float(h2d), world, dev))
-        bufs = [{k: torch.empty(host[k].shape, dtype=host[k].dtype, device=dev) for k in ekeys} for _ in range(2)]
+        bufs = [{k: host[k].to(dev) for k in ekeys} for _ in range(2)]
         outs = [(torch.empty((t1 - t0, 6), dtype=torch.float32).pin_memory(), torch.empty_like(host["poses"]).pin_memory())
                 for _ in range(2)]
         ev_copied = [torch.cuda.Event() for _ in range(2)]
@@ -267,7 +274,10 @@ def run_b200(args, world, rank, local):
             with torch.cuda.stream(copy_stream):
                 copy_stream.wait_event(ev_free[i])
                 for k in ekeys:
-                    bufs[i][k].copy_(host[k], non_blocking=True)
+                    if sharded and k in row_keys:
+                        bufs[i][k][lo:hi].copy_(host[k][lo:hi], non_blocking=True)
+                    else:
+                        bufs[i][k].copy_(host[k], non_blocking=True)
                 ev_copied[i].record(copy_stream)
 
         def run_pipeline(nsteps):
@@ -310,8 +320,9 @@ def run_b200(args, world, rank, local):
         e2e = {"value": iters / (ems * 1e-3), "unit": "iters/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": ems / args.steps,
                "pipeline": "H2D of step s+1 overlaps BA of step s (2 device buffers, copy stream)",
-               "inputs": ("every rank uploads the replicated poses / depth maps / eta / edge list and the targets + weights "
-                          "rows of ITS OWN edges; h2d_bytes_per_step is the sum over ranks") if sharded else "all inputs"}
+               "inputs": ("every rank uploads the replicated poses / edge list and, of targets / weights / depth maps / "
+                          "sensor depths / eta, the rows of ITS OWN edges and source frames; h2d_bytes_per_step is the "
+                          "sum over ranks") if sharded else "all inputs"}
 
     if rank != 0:
         return None

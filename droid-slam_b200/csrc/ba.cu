@@ -1298,7 +1298,9 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     attr_set = true;
   }
   // slabs: enough CTAs to fill the 148 SMs twice when there are few frames
-  const int Mrows = p->n_eta > 0 ? p->n_eta : 1;
+  // (a rank of a sharded call works on the frames of its shard only)
+  int Mrows = p->n_eta > 0 ? p->n_eta : 1;
+  if (p->frame_hi > p->frame_lo && p->frame_hi - p->frame_lo < Mrows) Mrows = p->frame_hi - p->frame_lo;
   int S = (2 * 148 + Mrows - 1) / Mrows;
   const int max_s = (HW + kThreads - 1) / kThreads;
   if (S > max_s) S = max_s;
