@@ -84,7 +84,7 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(done) : "r"(addr), "r"(parity) : "memory");
     if (done) break;
-    __nanosleep(100);
+    __nanosleep(32);
   }
 }
 // shared-memory matrix descriptor, K-major 32-bit operands, SWIZZLE_128B (layout type 2): a tile is [128 rows][32
@@ -231,8 +231,9 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
         const int s = c & (kStages - 1);          // operand stage
         const int g = c / kChain, a = g & 3;      // accumulator group, TMEM accumulator (4 x 128 columns)
         const bool first = (c % kChain) == 0, last = (c % kChain) == kChain - 1 || c == nchunk - 1;
-        mbar_wait_relaxed(full + s, (c >> 2) & 1);
-        if (first && g >= 4) mbar_wait_relaxed(tfree + a, ((g >> 2) - 1) & 1);     // accumulator drained
+        // (no back-off here: with builders and tensor pipe balanced, every hand-off of the issuer is on the critical path)
+        mbar_wait(full + s, (c >> 2) & 1);
+        if (first && g >= 4) mbar_wait(tfree + a, ((g >> 2) - 1) & 1);     // accumulator drained
         tc_fence_after();
         const uint32_t hi = smem_u32(smem + s * kStage), lo = hi + kHalf;
         const uint32_t d_t = tmem + a * 128;
