@@ -67,7 +67,7 @@ C_ABI_SYMBOLS = [
     "droid_version", "droid_last_cuda_error", "droid_launch_count", "droid_prof_enable", "droid_prof_read", "droid_corr_index_forward", "droid_corr_index_backward",
     "droid_corr_index_pyramid", "droid_altcorr_forward", "droid_altcorr_backward",
     "droid_altcorr_forward_indexed", "droid_corr_build", "droid_corr_build_workspace_bytes",
-    "droid_frame_distance", "droid_projmap", "droid_iproj", "droid_depth_filter",
+    "droid_frame_distance", "droid_projmap", "droid_reproject", "droid_iproj", "droid_depth_filter",
     "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_solve_env_f64",
     "droid_chol_workspace_bytes", "droid_chol_solve_chains_f64", "droid_chol_chains_workspace_bytes",
 ]
@@ -299,6 +299,34 @@ def projmap(poses, disps, intrinsics, ii, jj):
         _check(_lib.droid_projmap(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj), _p(coords),
                                   _p(valid), n, ht, wd, _stream(poses)), "projmap")
     return [coords, valid]
+
+
+def reproject(poses, disps, intrinsics, ii, jj, target=None):
+    """Extension: what ``DepthVideo.reproject(ii, jj)`` computes (droid_slam/depth_video.py:139-147,
+    geom/projective_ops.py:96-125) in one launch.  intrinsics [nbuf,4] per frame (like ``video.intrinsics``).
+    Returns [coords [n,ht,wd,2], valid [n,ht,wd,1]]; with ``target`` [n,ht,wd,2] also the motion features of
+    ``FactorGraph.update`` (droid_slam/factor_graph.py:203-204) as a third tensor [n,4,ht,wd]."""
+    _contig("reproject", poses=poses, disps=disps, intrinsics=intrinsics, ii=ii, jj=jj)
+    _long("reproject", ii=ii, jj=jj)
+    for t in (poses, disps, intrinsics):
+        _dtype("reproject", t, (torch.float32,))
+    if intrinsics.dim() != 2 or intrinsics.shape[1] != 4 or intrinsics.shape[0] < disps.shape[0]:
+        raise RuntimeError("droid_backends.reproject: intrinsics must be [nbuf,4] (one row per frame)")
+    n = ii.shape[0]
+    ht, wd = disps.shape[1], disps.shape[2]
+    if target is not None:
+        _contig("reproject", target=target)
+        _dtype("reproject", target, (torch.float32,))
+        if tuple(target.shape) != (n, ht, wd, 2):
+            raise RuntimeError("droid_backends.reproject: target must be [n,ht,wd,2]")
+    with torch.cuda.device(poses.device):
+        coords = torch.empty((n, ht, wd, 2), dtype=torch.float32, device=poses.device)
+        valid = torch.empty((n, ht, wd, 1), dtype=torch.float32, device=poses.device)
+        motn = torch.empty((n, 4, ht, wd), dtype=torch.float32, device=poses.device) if target is not None else None
+        _check(_lib.droid_reproject(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj),
+                                    _p(target) if target is not None else None, _p(coords), _p(valid),
+                                    _p(motn) if motn is not None else None, n, ht, wd, _stream(poses)), "reproject")
+    return [coords, valid] if motn is None else [coords, valid, motn]
 
 
 def iproj(poses, disps, intrinsics):

@@ -129,6 +129,16 @@ int droid_projmap(const float* poses, const float* disps, const float* intrinsic
                   const int64_t* ii, const int64_t* jj, float* coords, float* valid, int n, int ht,
                   int wd, void* stream);
 
+/* reproject -- extension, SURVEY 8f N1: DepthVideo.reproject (droid_slam/depth_video.py:139-147) =
+ * geom/projective_ops.py:96-125 with jacobian=False, i.e. the PYTHON semantics (not projmap's): intrinsics
+ * [nbuf,4] per frame, Z < 0.1 -> 1, valid = Z > 0.2, stereo edges ii == jj use the baseline (-0.1,0,0).
+ *   coords [n,ht,wd,2], valid [n,ht,wd,1]; both fully written.
+ *   target [n,ht,wd,2] and motn [n,4,ht,wd] are both NULL or both given: motn = the motion features of
+ *   FactorGraph.update (droid_slam/factor_graph.py:203-204), clamp(cat(coords - grid, target - coords), -64, 64). */
+int droid_reproject(const float* poses, const float* disps, const float* intrinsics, const int64_t* ii,
+                    const int64_t* jj, const float* target, float* coords, float* valid, float* motn,
+                    int n, int ht, int wd, void* stream);
+
 /* iproj (src/droid.cpp:157-166, src/droid_kernels.cu:779-850,1518-1541). points [nm,ht,wd,3]. */
 int droid_iproj(const float* poses, const float* disps, const float* intrinsics, float* points,
                 int nm, int ht, int wd, void* stream);

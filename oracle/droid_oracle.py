@@ -158,6 +158,51 @@ def projmap(poses, disps, intr, ii, jj):
     return coords, valid
 
 
+def _quat_mul(a, b):
+    """Eigen quaternion product a * b, coefficients (x, y, z, w)."""
+    ax, ay, az, aw = [a[..., k] for k in range(4)]
+    bx, by, bz, bw = [b[..., k] for k in range(4)]
+    return np.stack([aw * bx + ax * bw + ay * bz - az * by,
+                     aw * by + ay * bw + az * bx - ax * bz,
+                     aw * bz + az * bw + ax * by - ay * bx,
+                     aw * bw - ax * bx - ay * by - az * bz], -1).astype(F32)
+
+
+def reproject(poses, disps, intr, ii, jj, target=None):
+    """DepthVideo.reproject (droid_slam/depth_video.py:139-147) = projective_transform with jacobian=False
+    (droid_slam/geom/projective_ops.py:96-125), group arithmetic as in lietorch (thirdparty/lietorch/lietorch/include/
+    se3.h:36-52, so3.h:43-60).  intr [nbuf,4] per frame.  -> coords [n,ht,wd,2], valid [n,ht,wd,1]
+    (+ motn [n,4,ht,wd], the motion features of droid_slam/factor_graph.py:203-204, when target is given)."""
+    n = len(ii)
+    ht, wd = disps.shape[1:]
+    coords = np.zeros((n, ht, wd, 2), F32)
+    valid = np.zeros((n, ht, wd, 1), F32)
+    motn = np.zeros((n, 4, ht, wd), F32) if target is not None else None
+    for e in range(n):
+        ix, jx = int(ii[e]), int(jj[e])
+        u, v, xn, yn = _grid(ht, wd, intr[ix])                                   # iproj, projective_ops.py:18-37
+        X0 = np.stack([xn, yn, np.ones_like(xn), disps[ix].astype(F32)], -1)
+        if ix == jx:                                                             # projective_ops.py:105
+            t, q = np.array([-0.1, 0, 0], F32), np.array([0, 0, 0, 1], F32)
+        else:                                                                    # Gj * Gi.inv()
+            ti, qi, tj, qj = poses[ix, :3].astype(F32), poses[ix, 3:].astype(F32), poses[jx, :3].astype(F32), poses[jx, 3:].astype(F32)
+            qinv = qi * np.array([-1, -1, -1, 1], F32)
+            tinv = -act_so3(qinv, ti)
+            q = _quat_mul(qj, qinv)
+            t = (tj + act_so3(qj, tinv)).astype(F32)
+        X1 = act_se3(t, q, X0)                                                   # actp: act4
+        fx, fy, cx, cy = [F32(a) for a in intr[jx]]
+        Z = np.where(X1[..., 2] < F32(0.1), F32(1.0), X1[..., 2]).astype(F32)   # proj, projective_ops.py:39-53
+        d = (F32(1.0) / Z).astype(F32)
+        coords[e, ..., 0] = fx * (X1[..., 0] * d) + cx
+        coords[e, ..., 1] = fy * (X1[..., 1] * d) + cy
+        valid[e, ..., 0] = (X1[..., 2] > F32(0.2)).astype(F32)                   # X0[...,2] = 1 > 0.2 always
+        if motn is not None:
+            m = np.concatenate([coords[e] - np.stack([u, v], -1), target[e].astype(F32) - coords[e]], -1)
+            motn[e] = np.clip(m, -64.0, 64.0).transpose(2, 0, 1)
+    return (coords, valid) if motn is None else (coords, valid, motn)
+
+
 def iproj(poses, disps, intr):
     """src/droid_kernels.cu:779-850.  -> points [nm,ht,wd,3]."""
     nm, ht, wd = disps.shape

@@ -192,6 +192,34 @@ def test_projmap_iproj(backends):
     assert rel(backends.iproj(cu(poses), cu(disps), cu(intr)).cpu().numpy(), rp) <= 1e-5
 
 
+def test_reproject_matches_oracle(backends):
+    """DepthVideo.reproject in one launch (Python-path semantics: per-frame intrinsics, Z < 0.1 -> 1,
+    valid = Z > 0.2, stereo baseline for ii == jj) + the fused motion features of FactorGraph.update.  Includes a
+    frame pushed behind its neighbours (invalid / Z-fallback pixels), a stereo edge and intrinsics that differ per
+    frame.  Coordinates <= 1e-5 relative (the group arithmetic is ordered as in src/droid_kernels.cu, the oracle's
+    as in lietorch), masks bit-exact."""
+    poses, disps, intr, ii, jj = geom_inputs()
+    poses = poses.copy(); poses[7, :3] += [0, 0, 30.0]
+    n = poses.shape[0]
+    K = np.tile(intr[None], (n, 1)).astype(np.float32)
+    K *= (1.0 + 0.01 * np.arange(n, dtype=np.float32))[:, None]
+    ii = np.concatenate([ii, [3, 7, 6]]).astype(np.int64); jj = np.concatenate([jj, [3, 6, 7]]).astype(np.int64)
+    rng = np.random.default_rng(3)
+    rc, rv = O.reproject(poses, disps, K, ii, jj)
+    tgt = (rc + rng.normal(0, 40.0, size=rc.shape)).astype(np.float32)
+    rc, rv, rm = O.reproject(poses, disps, K, ii, jj, target=tgt)
+    c, v = backends.reproject(cu(poses), cu(disps), cu(K), cu(ii), cu(jj))
+    c2, v2, m = backends.reproject(cu(poses), cu(disps), cu(K), cu(ii), cu(jj), cu(tgt))
+    assert 0.0 < rv.mean() < 1.0 and (np.abs(rm) == 64.0).any()
+    assert torch.equal(c, c2) and torch.equal(v, v2)
+    c, v, m = c.cpu().numpy(), v.cpu().numpy(), m.cpu().numpy()
+    assert np.abs(c - rc).max() <= 1e-5 * np.abs(rc).max()
+    assert (v != rv).mean() <= 1e-4                                   # a pixel exactly on Z = 0.2 may fall either way
+    assert np.abs(m - rm).max() <= 1e-5 * np.abs(rc).max()
+    with pytest.raises(RuntimeError):
+        backends.reproject(cu(poses), cu(disps), cu(intr), cu(ii), cu(jj))     # one intrinsics row per frame
+
+
 def test_frame_distance(backends):
     poses, disps, intr, ii, jj = geom_inputs()
     n = poses.shape[0]

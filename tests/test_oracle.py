@@ -59,6 +59,34 @@ def test_geometry_vs_reference():
     assert np.array_equal(cnt, ref["counter"])                         # integer counts: bit-exact
 
 
+def test_reproject_oracle_pinned_through_projmap():
+    """SURVEY 8f N1.  The Python path behind DepthVideo.reproject (geom/projective_ops.py:96-125) has no reference
+    run that can travel (it needs lietorch), so its restatement is pinned through the reference extension's CUDA twin
+    `projmap`, whose outputs are stored: wherever the point lies in front of the camera (Z > 0.25, valid in both) the
+    two must give the same coordinates; the validity masks may differ only for 0.2 < Z <= 0.25 (MIN_DEPTH 0.2 vs
+    0.25); behind the camera (Z < 0.1) the Python path projects with Z = 1 instead of returning the pixel itself."""
+    q = G.geom_case()
+    ref = gold("ref_geom")
+    n = q["poses"].shape[0]
+    intr = np.tile(q["intr"][None], (n, 1)).astype(np.float32)
+    c, v = O.reproject(q["poses"], q["disps"], intr, q["ii"], q["jj"])
+    both = (ref["valid"][..., 0] > 0) & (v[..., 0] > 0)
+    assert both.mean() > 0.5
+    assert np.abs(c - ref["coords"][..., :2])[both].max() <= 1e-4 * max(1.0, np.abs(ref["coords"]).max())
+    assert not ((ref["valid"] > 0) & (v == 0)).any()                   # Z > 0.25 implies Z > 0.2
+    # stereo edge: fixed baseline, identity rotation -> u shifts by -0.1 fx d, v unchanged
+    ii = np.array([2], np.int64)
+    cs, vs = O.reproject(q["poses"], q["disps"], intr, ii, ii)
+    vg, ug = np.meshgrid(np.arange(cs.shape[1], dtype=np.float32), np.arange(cs.shape[2], dtype=np.float32), indexing="ij")
+    assert np.abs(cs[0, ..., 0] - (ug - 0.1 * intr[2, 0] * q["disps"][2])).max() <= 1e-3
+    assert np.abs(cs[0, ..., 1] - vg).max() <= 1e-3 and vs.min() == 1.0
+    # motion features: clamp(cat(coords - grid, target - coords)), channel-first
+    tgt = (c + 100.0).astype(np.float32)
+    _, _, m = O.reproject(q["poses"], q["disps"], intr, q["ii"], q["jj"], target=tgt)
+    assert m.shape == (len(q["ii"]), 4) + c.shape[1:3] and np.all(m[:, 2:] == 64.0)
+    assert np.allclose(m[:, 0], np.clip(c[..., 0] - ug, -64, 64)) and np.allclose(m[:, 1], np.clip(c[..., 1] - vg, -64, 64))
+
+
 @pytest.mark.parametrize("key", sorted(G.BA_CASES))
 def test_ba_vs_reference(key):
     p, c = G.ba_case(key)
