@@ -459,6 +459,24 @@ def extra_metrics(dev, hbm_peak, peaks):
         out["corr_lookup_4calls_reference_ext"] = {"us": t * 1e6, "GBps": lb / t / 1e9}
     except Exception:
         pass
+    # reproject + motion features on the edge list of a 250-keyframe backend graph: one launch instead of
+    # the ~15 lietorch / elementwise kernels of DepthVideo.reproject; depth in, coords + valid + 4 feature planes out
+    try:
+        pr = synth.make_ba_problem("C4", n_frames=250, knn=16)
+        nb = pr["disps"].shape[0]
+        Kf = torch.from_numpy(np.tile(pr["intrinsics"][None], (nb, 1)).astype(np.float32)).to(dev)
+        rp, rd = torch.from_numpy(pr["poses"]).to(dev), torch.from_numpy(pr["disps"]).to(dev)
+        ri, rj = torch.from_numpy(pr["ii"]).to(dev), torch.from_numpy(pr["jj"]).to(dev)
+        rt = torch.from_numpy(np.ascontiguousarray(pr["targets"].transpose(0, 2, 3, 1))).to(dev)
+        ne, hw = len(pr["ii"]), pr["ht"] * pr["wd"]
+        t = timeit(lambda: B.reproject(rp, rd, Kf, ri, rj, rt), n=10)
+        rb = ne * hw * (4 + 8 + 8 + 4 + 16)
+        out["reproject_motion"] = {"us": t * 1e6, "GBps": rb / t / 1e9, "hbm_frac": rb / t / 1e9 / hbm_peak,
+                                   "algorithmic_bytes": rb, "bound": "hbm",
+                                   "workload": "%d edges, %dx%d: depth + target in, coords + valid + 4 motion planes out" % (ne, pr["ht"], pr["wd"])}
+        del rt
+    except Exception as ex:                                        # noqa: BLE001
+        out["reproject_motion"] = {"error": repr(ex)}
     p = synth.make_ba_problem("C3")
     d = {k: torch.from_numpy(np.ascontiguousarray(p[k])).to(dev) for k in KEYS}
     p0, d0 = d["poses"].clone(), d["disps"].clone()
