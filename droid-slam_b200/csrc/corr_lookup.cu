@@ -127,39 +127,47 @@ __device__ __forceinline__ __half shfl_down1(__half v) { return __shfl_down_sync
 // One level of the radius-3 lookup for the 32-pixel tile of this CTA.  256 threads: 32 pixels x 8 rows.
 //   vol   : [B,HW1,H2,W2] of this level;  scale : 1/2^level applied to the level-0 coords
 //   out   : channel c = i*7 + j of this level goes to out[(b*CH + ch0 + c)*HW1 + pix]
-template <typename T, bool VEC>
-__device__ __forceinline__ void lookup_tile_r3(const T* __restrict__ vol,
-                                               const float* __restrict__ coords, T* __restrict__ out,
-                                               int b, int pix0, int HW1, int H2, int W2, float scale,
-                                               int CH, int ch0, T (*stage)[33]) {
-  const int tid = threadIdx.x;
-  const int p = tid >> 3, row = tid & 7;
-  const int pix = pix0 + p;
-  const bool pv = pix < HW1;
-  float x0 = 0.f, y0 = 0.f;
-  if (pv) {
-    x0 = coords[((size_t)b * 2 + 0) * HW1 + pix] * scale;
-    y0 = coords[((size_t)b * 2 + 1) * HW1 + pix] * scale;
-  }
+// what one thread (pixel p = tid >> 3, window row = tid & 7) holds of one level between the load and the arithmetic
+template <typename T>
+struct RowTaps {
+  T t[8];        // taps (xs .. xs+7, ys), zero outside the plane
+  unsigned m;    // bit k: tap (xs+k, ys) is inside the plane
+  float dx, dy;  // bilinear fractions
+};
+
+// load phase: x0, y0 = the pixel's coordinates at this level (already scaled); pv = pixel inside the image
+template <typename T>
+__device__ __forceinline__ void lookup_load_r3(const T* __restrict__ vol, int b, int pix, bool pv, float x0, float y0,
+                                               int HW1, int H2, int W2, bool vec, RowTaps<T>& R) {
+  const int row = threadIdx.x & 7;
   const float fx0 = floorf(x0), fy0 = floorf(y0);
-  const float dx = x0 - fx0, dy = y0 - fy0;
+  R.dx = x0 - fx0; R.dy = y0 - fy0;
   const int xs = (int)fx0 - 3;
   const int ys = (int)fy0 - 3 + row;
   const bool rv = pv && ys >= 0 && ys < H2;
-  T t[8];
   if (rv) {
     const T* rowp = vol + ((size_t)b * HW1 + pix) * ((size_t)H2 * W2) + (size_t)ys * W2;
-    if (VEC) load_row_vec(rowp, xs, W2, t);
-    else load_row_scalar(rowp, xs, W2, t);
+    if (vec) load_row_vec(rowp, xs, W2, R.t);
+    else load_row_scalar(rowp, xs, W2, R.t);
   } else {
 #pragma unroll
-    for (int k = 0; k < 8; k++) t[k] = Arith<T>::zero();
+    for (int k = 0; k < 8; k++) R.t[k] = Arith<T>::zero();
   }
-  unsigned m = 0;  // bit k: tap (xs+k, ys) is inside the plane
+  R.m = 0;
   if (rv) {
 #pragma unroll
-    for (int k = 0; k < 8; k++) m |= ((xs + k >= 0 && xs + k < W2) ? 1u : 0u) << k;
+    for (int k = 0; k < 8; k++) R.m |= ((xs + k >= 0 && xs + k < W2) ? 1u : 0u) << k;
   }
+}
+
+// arithmetic phase of one level: 49 channels x 32 pixels of this CTA's tile into the staging rows
+template <typename T>
+__device__ __forceinline__ void lookup_finish_r3(const RowTaps<T>& R, T (*stage)[33]) {
+  const int tid = threadIdx.x;
+  const int p = tid >> 3, row = tid & 7;
+  const T* t = R.t;
+  const unsigned m = R.m;
+  const float dx = R.dx, dy = R.dy;
   if constexpr (sizeof(T) == 2) {
     // f16: native packed arithmetic.  HMUL2 rounds the (exact) product once and HADD2 the (exact)
     // sum once, which is bit-identical to c10::Half's float-op-then-round; out-of-plane taps were loaded as
@@ -215,13 +223,40 @@ __device__ __forceinline__ void lookup_tile_r3(const T* __restrict__ vol,
     }
   }
   }
+}
+
+// store phase: nch staged channels of the 32-pixel tile -> out[(b*CH + ch0 + c)*HW1 + pix], 64/128-byte rows per warp
+template <typename T>
+__device__ __forceinline__ void lookup_store_r3(T* __restrict__ out, int b, int pix0, int HW1, int CH, int ch0, int nch,
+                                                T (*stage)[33]) {
   __syncthreads();
-  const int lane = tid & 31, warp = tid >> 5;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (pix0 + lane < HW1) {
-    for (int c = warp; c < 49; c += 8)
+    for (int c = warp; c < nch; c += 8)
       out[((size_t)b * CH + ch0 + c) * HW1 + pix0 + lane] = stage[c][lane];
   }
   __syncthreads();
+}
+
+// One level of the radius-3 lookup for the 32-pixel tile of this CTA.  256 threads: 32 pixels x 8 rows.
+//   vol   : [B,HW1,H2,W2] of this level;  scale : 1/2^level applied to the level-0 coords
+//   out   : channel c = i*7 + j of this level goes to out[(b*CH + ch0 + c)*HW1 + pix]
+template <typename T, bool VEC>
+__device__ __forceinline__ void lookup_tile_r3(const T* __restrict__ vol,
+                                               const float* __restrict__ coords, T* __restrict__ out,
+                                               int b, int pix0, int HW1, int H2, int W2, float scale,
+                                               int CH, int ch0, T (*stage)[33]) {
+  const int pix = pix0 + (threadIdx.x >> 3);
+  const bool pv = pix < HW1;
+  float x0 = 0.f, y0 = 0.f;
+  if (pv) {
+    x0 = coords[((size_t)b * 2 + 0) * HW1 + pix] * scale;
+    y0 = coords[((size_t)b * 2 + 1) * HW1 + pix] * scale;
+  }
+  RowTaps<T> R;
+  lookup_load_r3<T>(vol, b, pix, pv, x0, y0, HW1, H2, W2, VEC, R);
+  lookup_finish_r3<T>(R, stage);
+  lookup_store_r3<T>(out, b, pix0, HW1, CH, ch0, 49, stage);
 }
 
 template <typename T, bool VEC>
@@ -244,18 +279,30 @@ __global__ void __launch_bounds__(256) corr_index_pyr_r3_kernel(PyrArgs a, int L
                                                                 const float* __restrict__ coords,
                                                                 T* __restrict__ out, int HW1, int H2,
                                                                 int W2) {
-  __shared__ T stage[49][33];
+  __shared__ T stage[4 * 49][33];
+  // The four levels read four unrelated planes: all their loads are issued before any arithmetic, so that a CTA pays
+  // the DRAM latency once (coordinates -> rows) instead of once per level.
+  const int b = blockIdx.y, pix0 = blockIdx.x * 32;
+  const int pix = pix0 + (threadIdx.x >> 3);
+  const bool pv = pix < HW1;
+  float x0 = 0.f, y0 = 0.f;
+  if (pv) {
+    x0 = coords[((size_t)b * 2 + 0) * HW1 + pix];
+    y0 = coords[((size_t)b * 2 + 1) * HW1 + pix];
+  }
+  RowTaps<T> R[4];
   float scale = 1.0f;
-  for (int l = 0; l < L; l++) {
-    const T* vol = reinterpret_cast<const T*>(a.vol[l]);
-    if (a.vec[l])
-      lookup_tile_r3<T, true>(vol, coords, out, blockIdx.y, blockIdx.x * 32, HW1, H2 >> l, W2 >> l,
-                              scale, 49 * L, 49 * l, stage);
-    else
-      lookup_tile_r3<T, false>(vol, coords, out, blockIdx.y, blockIdx.x * 32, HW1, H2 >> l, W2 >> l,
-                               scale, 49 * L, 49 * l, stage);
+#pragma unroll
+  for (int l = 0; l < 4; l++) {
+    if (l < L)
+      lookup_load_r3<T>(reinterpret_cast<const T*>(a.vol[l]), b, pix, pv, x0 * scale, y0 * scale, HW1, H2 >> l, W2 >> l,
+                        a.vec[l] != 0, R[l]);
     scale *= 0.5f;
   }
+#pragma unroll
+  for (int l = 0; l < 4; l++)
+    if (l < L) lookup_finish_r3<T>(R[l], stage + 49 * l);
+  lookup_store_r3<T>(out, b, pix0, HW1, 49 * L, 0, 49 * L, stage);
 }
 
 // Generic radius (any r >= 0): one thread per pixel and output row, no staging.  Used only when
