@@ -649,3 +649,52 @@ def ba(poses, disps, intr, disps_sens, targets, weights, eta, ii, jj, t0, t1, it
     if return_debug:
         return dx, dz, dbg
     return dx, dz
+
+
+# ------------------------------------------------------------------------------------------------
+# edge selection
+# ------------------------------------------------------------------------------------------------
+def proximity_edges(d, t, t0, t1, rad, nms, thresh, max_factors, stereo, ii_exist, jj_exist):
+    """FactorGraph.add_proximity_factors (droid_slam/factor_graph.py:305-369) from the point where the distances are
+    known: d = video.distance(ii, jj, beta) over meshgrid(arange(t0, t), arange(t1, t)), row-major.  ii_exist /
+    jj_exist = cat(active, bad, inactive) edges (:322-323).  Returns the edge list handed to add_factors, in order:
+    the mandatory temporal (and stereo) edges, then the accepted pairs (both directions) in ascending distance.
+    Ties in d are taken in index order (the reference's argsort leaves them unspecified)."""
+    d = np.array(d, np.float32, copy=True)
+    W = t - t1
+    gi, gj = np.meshgrid(np.arange(t0, t), np.arange(t1, t), indexing="ij")
+    gi, gj = gi.reshape(-1), gj.reshape(-1)
+    d[gi - rad < gj] = np.inf                                                     # :318
+    d[d > 100] = np.inf                                                           # :319
+
+    def suppress(i, j):                                                           # :324-333, :359-367
+        r = max(min(abs(i - j) - 2, nms), 0)
+        for di in range(-nms, nms + 1):
+            for dj in range(-nms, nms + 1):
+                if abs(di) + abs(dj) <= r:
+                    i1, j1 = i + di, j + dj
+                    if t0 <= i1 < t and t1 <= j1 < t:
+                        d[(i1 - t0) * W + (j1 - t1)] = np.inf
+
+    for i, j in zip(np.asarray(ii_exist, np.int64), np.asarray(jj_exist, np.int64)):
+        suppress(int(i), int(j))
+    es = []
+    for i in range(t0, t):                                                        # :336-345
+        if stereo:
+            es.append((i, i))
+            d[(i - t0) * W + (i - t1)] = np.inf
+        for j in range(max(i - rad - 1, 0), i):
+            es.append((i, j))
+            es.append((j, i))
+            d[(i - t0) * W + (j - t1)] = np.inf
+    for k in np.argsort(d, kind="stable"):                                        # :347-367
+        if d[k] > thresh:
+            continue
+        if len(es) > max_factors:
+            break
+        i, j = int(gi[k]), int(gj[k])
+        es.append((i, j))
+        es.append((j, i))
+        suppress(i, j)
+    e = np.asarray(es, np.int64).reshape(-1, 2)
+    return e[:, 0].copy(), e[:, 1].copy()

@@ -173,3 +173,17 @@ def test_retraction_small_and_large_angle():
         assert abs(np.linalg.norm(q1) - 1) < 1e-6
         R, tt = synth.se3_exp(xi.astype(np.float64))
         assert np.abs(t1 - (R @ t + tt)).max() < 1e-6
+
+
+@pytest.mark.parametrize("key", sorted(__import__("proximity_cases").CASES))
+def test_proximity_edges_vs_reference(key):
+    """the restatement of FactorGraph.add_proximity_factors' edge selection against the edge lists the
+    UNMODIFIED reference method produced on the same seeded inputs (tests/golden/make_golden_proximity.py): bit-exact,
+    order included."""
+    import proximity_cases as PC
+    c = PC.make_case(key)
+    ref = gold("ref_proximity")
+    assert str(ref[key + "_digest"]) == PC.digest(c)
+    ii, jj = O.proximity_edges(c["d"], c["t"], c["t0"], c["t1"], c["rad"], c["nms"], c["thresh"], c["max_factors"],
+                               c["stereo"], c["ii_exist"], c["jj_exist"])
+    assert np.array_equal(ii, ref[key + "_ii"]) and np.array_equal(jj, ref[key + "_jj"])
