@@ -1,0 +1,216 @@
+// Edge selection on the device: the part of FactorGraph.add_proximity_factors
+// (droid_slam/factor_graph.py:305-369) that follows the distance computation.  The reference runs it as Python
+// double loops with an .item() per candidate; at 1000 keyframes that is seconds of host time around kernels that
+// take microseconds.  Here the whole selection stays on the device and is stream-ordered:
+//   1. prox_mask_kernel      d[i - rad < j] = inf, d[d > 100] = inf                                   (:318-319)
+//   2. prox_exist_kernel     non-maximum suppression around the edges the graph already has           (:322-333)
+//   3. prox_mandatory_kernel temporal neighbours (and stereo pairs) go in unconditionally             (:336-345)
+//   4. radix sort of (distance, pair index)  -- cub::DeviceRadixSort, stable: ties in index order     (:347)
+//   5. prox_greedy_kernel    one warp walks the sorted candidates, 32 at a time: accept the first one alive, suppress
+//                            its neighbourhood (arithmetically for the 31 candidates in flight, through a byte map
+//                            for later batches), until the distance exceeds thresh or the graph is full (:348-367)
+// The result is the reference's edge list, in the reference's order (bit-exact against its own output, tests/).
+// Index arithmetic follows Python: d[(i - t0) * W + (j - t1)] with a negative index wraps around.
+#include <cub/device/device_radix_sort.cuh>
+
+#include "common.cuh"
+
+namespace droid {
+namespace {
+
+__device__ __forceinline__ long long wrap_index(long long idx, long long n) { return idx < 0 ? idx + n : idx; }
+
+__global__ void prox_mask_kernel(const float* __restrict__ d, float* __restrict__ dm, int* __restrict__ vals,
+                                 unsigned char* __restrict__ sup, int n, int W, int t0, int t1, int rad) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  const int i = t0 + idx / W, j = t1 + idx % W;
+  const float v = d[idx];
+  dm[idx] = (i - rad < j || v > 100.0f) ? __int_as_float(0x7f800000) : v;
+  vals[idx] = idx;
+  sup[idx] = 0;
+}
+
+// |di| + |dj| <= max(min(|i - j| - 2, nms), 0), inside [t0, t) x [t1, t)
+__device__ __forceinline__ int nms_radius(int i, int j, int nms) { return max(min(abs(i - j) - 2, nms), 0); }
+
+__global__ void prox_exist_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int n_exist,
+                                  float* __restrict__ dm, int W, int t, int t0, int t1, int nms) {
+  const int e = blockIdx.x;
+  if (e >= n_exist) return;
+  const int i = (int)ii[e], j = (int)jj[e];
+  const int r = nms_radius(i, j, nms), side = 2 * nms + 1;
+  for (int c = threadIdx.x; c < side * side; c += blockDim.x) {
+    const int di = c / side - nms, dj = c % side - nms;
+    if (abs(di) + abs(dj) > r) continue;
+    const int i1 = i + di, j1 = j + dj;
+    if (i1 >= t0 && i1 < t && j1 >= t1 && j1 < t) dm[(size_t)(i1 - t0) * W + (j1 - t1)] = __int_as_float(0x7f800000);
+  }
+}
+
+// number of mandatory entries of frames 0 .. x-1: s per frame (stereo) + 2 min(i, rad + 1) temporal neighbours
+__host__ __device__ inline long long mandatory_before(long long x, int rad, int s) {
+  const long long m = rad + 1;
+  const long long tri = x <= m + 1 ? x * (x - 1) / 2 : m * (m + 1) / 2 + (x - m - 1) * m;
+  return s * x + 2 * tri;
+}
+
+__global__ void prox_mandatory_kernel(float* __restrict__ dm, int64_t* __restrict__ out_ii, int64_t* __restrict__ out_jj,
+                                      int* __restrict__ status, int n, int W, int t, int t0, int t1, int rad, int stereo) {
+  const int i = t0 + blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= t) return;
+  long long o = mandatory_before(i, rad, stereo ? 1 : 0) - mandatory_before(t0, rad, stereo ? 1 : 0);
+  auto kill = [&](int j) {
+    const long long idx = wrap_index((long long)(i - t0) * W + (j - t1), n);
+    if (idx < 0 || idx >= n) { atomicOr(status, 1); return; }      // Python would raise IndexError
+    dm[idx] = __int_as_float(0x7f800000);
+  };
+  if (stereo) {
+    out_ii[o] = i; out_jj[o] = i; o++;
+    kill(i);
+  }
+  for (int j = max(i - rad - 1, 0); j < i; j++) {
+    out_ii[o] = i; out_jj[o] = j; o++;
+    out_ii[o] = j; out_jj[o] = i; o++;
+    kill(j);
+  }
+}
+
+__global__ void __launch_bounds__(32) prox_greedy_kernel(const float* __restrict__ keys, const int* __restrict__ vals,
+                                                         unsigned char* sup, int64_t* __restrict__ out_ii,
+                                                         int64_t* __restrict__ out_jj, int* __restrict__ out_count,
+                                                         int* __restrict__ status, int n, int W, int t, int t0, int t1,
+                                                         int nms, float thresh, int max_factors, int mandatory,
+                                                         int capacity) {
+  const int lane = threadIdx.x;
+  const int side = 2 * nms + 1;
+  int count = mandatory;
+  bool stop = false;
+  for (int base = 0; base < n && !stop; base += 32) {
+    const int k = base + lane;
+    const float key = k < n ? keys[k] : __int_as_float(0x7f800000);
+    const int idx = k < n ? vals[k] : 0;
+    const int ci = t0 + idx / W, cj = t1 + idx % W;
+    const bool close = k < n && !(key > thresh);                 // `if d[k] > thresh: continue`
+    bool alive = close && __ldcg(sup + idx) == 0;
+    if (__ballot_sync(0xffffffffu, !close) != 0u) stop = true;   // sorted: nothing behind this batch can pass
+    unsigned live;
+    while ((live = __ballot_sync(0xffffffffu, alive)) != 0u) {
+      if (count > max_factors) { stop = true; break; }           // `if len(es) > max_factors: break`
+      if (count + 2 > capacity) { if (lane == 0) atomicOr(status, 2); stop = true; break; }
+      const int l = __ffs(live) - 1;
+      const int i = __shfl_sync(0xffffffffu, ci, l), j = __shfl_sync(0xffffffffu, cj, l);
+      if (lane == 0) {
+        out_ii[count] = i; out_jj[count] = j;
+        out_ii[count + 1] = j; out_jj[count + 1] = i;
+      }
+      count += 2;
+      const int r = nms_radius(i, j, nms);
+      // candidates of this batch (their flags were read before this acceptance) ...
+      if (alive && abs(ci - i) <= nms && abs(cj - j) <= nms && abs(ci - i) + abs(cj - j) <= r) alive = false;
+      if (lane == l) alive = false;
+      // ... and everything behind it
+      for (int c = lane; c < side * side; c += 32) {
+        const int di = c / side - nms, dj = c % side - nms;
+        if (abs(di) + abs(dj) > r) continue;
+        const int i1 = i + di, j1 = j + dj;
+        if (i1 >= t0 && i1 < t && j1 >= t1 && j1 < t) __stcg(sup + (size_t)(i1 - t0) * W + (j1 - t1), (unsigned char)1);
+      }
+    }
+    __threadfence_block();
+    __syncwarp();
+  }
+  if (lane == 0) *out_count = count;
+}
+
+size_t sort_temp_bytes(int n) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const float*)nullptr, (float*)nullptr, (const int*)nullptr,
+                                  (int*)nullptr, n);
+  return bytes;
+}
+
+struct ProxWs {
+  float* dm; float* keys; int* vals; int* vals_sorted; unsigned char* sup; int* status; void* temp;
+  size_t temp_bytes, total;
+};
+
+ProxWs carve_prox(void* base, int n) {
+  ProxWs w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* q = base ? (void*)((char*)base + off) : nullptr;
+    off += (bytes + 255) & ~(size_t)255;
+    return q;
+  };
+  const size_t nn = n > 0 ? n : 1;
+  w.status = (int*)take(256);
+  w.dm = (float*)take(nn * sizeof(float));
+  w.keys = (float*)take(nn * sizeof(float));
+  w.vals = (int*)take(nn * sizeof(int));
+  w.vals_sorted = (int*)take(nn * sizeof(int));
+  w.sup = (unsigned char*)take(nn);
+  w.temp_bytes = sort_temp_bytes((int)nn);
+  w.temp = take(w.temp_bytes);
+  w.total = off;
+  return w;
+}
+
+}  // namespace
+}  // namespace droid
+
+using namespace droid;
+
+extern "C" size_t droid_proximity_workspace_bytes(int n_pairs) {
+  if (n_pairs < 0) return 0;
+  return carve_prox(nullptr, n_pairs).total + 256;
+}
+
+extern "C" int droid_proximity_mandatory_count(int t, int t0, int rad, int stereo) {
+  if (t < t0 || t0 < 0 || rad < 0) return -1;
+  return (int)(mandatory_before(t, rad, stereo ? 1 : 0) - mandatory_before(t0, rad, stereo ? 1 : 0));
+}
+
+extern "C" int droid_proximity_edges(const float* d, int t, int t0, int t1, int rad, int nms, float thresh,
+                                     int max_factors, int stereo, const int64_t* ii_exist,
+                                     const int64_t* jj_exist, int n_exist, int64_t* out_ii, int64_t* out_jj,
+                                     int capacity, int* out_count, void* workspace, size_t workspace_bytes,
+                                     void* stream) {
+  if (t0 < 0 || t1 < 0 || t < t0 || t < t1 || rad < 0 || nms < 0 || nms > 15 || n_exist < 0 || capacity < 0)
+    return DROID_ERR_INVALID_ARGUMENT;
+  if (!out_ii || !out_jj || !out_count || !workspace) return DROID_ERR_INVALID_ARGUMENT;
+  if (n_exist > 0 && (!ii_exist || !jj_exist)) return DROID_ERR_INVALID_ARGUMENT;
+  const long long nl = (long long)(t - t0) * (t - t1);
+  if (nl > 0x7fffffffLL) return DROID_ERR_INVALID_ARGUMENT;
+  const int n = (int)nl, W = t - t1;
+  if (n > 0 && !d) return DROID_ERR_INVALID_ARGUMENT;
+  const int mandatory = droid_proximity_mandatory_count(t, t0, rad, stereo);
+  if (mandatory > capacity) return DROID_ERR_INVALID_ARGUMENT;
+  if (((uintptr_t)workspace & 255) != 0) {
+    const size_t adj = 256 - ((uintptr_t)workspace & 255);
+    if (workspace_bytes < adj) return DROID_ERR_WORKSPACE_TOO_SMALL;
+    workspace = (char*)workspace + adj;
+    workspace_bytes -= adj;
+  }
+  ProxWs w = carve_prox(workspace, n);
+  if (workspace_bytes < w.total) return DROID_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(w.status, 0, sizeof(int), st);
+  if (n > 0) {
+    DROID_LAUNCH prox_mask_kernel<<<(n + 255) / 256, 256, 0, st>>>(d, w.dm, w.vals, w.sup, n, W, t0, t1, rad);
+    if (n_exist > 0)
+      DROID_LAUNCH prox_exist_kernel<<<n_exist, 64, 0, st>>>(ii_exist, jj_exist, n_exist, w.dm, W, t, t0, t1, nms);
+  }
+  if (t > t0)
+    DROID_LAUNCH prox_mandatory_kernel<<<(t - t0 + 127) / 128, 128, 0, st>>>(w.dm, out_ii, out_jj, w.status, n, W, t, t0,
+                                                                              t1, rad, stereo);
+  if (n > 0) {
+    size_t tb = w.temp_bytes;
+    ++g_launch_count;
+    if (cub::DeviceRadixSort::SortPairs(w.temp, tb, w.dm, w.keys, w.vals, w.vals_sorted, n, 0, 32, st) != cudaSuccess)
+      return DROID_ERR_CUDA;
+  }
+  DROID_LAUNCH prox_greedy_kernel<<<1, 32, 0, st>>>(w.keys, w.vals_sorted, w.sup, out_ii, out_jj, out_count, w.status, n, W,
+                                                    t, t0, t1, nms, thresh, max_factors, mandatory, capacity);
+  return check_launch();
+}

@@ -56,6 +56,7 @@ def _load():
     lib.droid_chol_chains_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_corr_build_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_launch_count.restype = ctypes.c_ulonglong
+    lib.droid_proximity_workspace_bytes.restype = ctypes.c_size_t
     return lib
 
 
@@ -70,6 +71,7 @@ C_ABI_SYMBOLS = [
     "droid_frame_distance", "droid_projmap", "droid_reproject", "droid_iproj", "droid_depth_filter",
     "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_solve_env_f64",
     "droid_chol_workspace_bytes", "droid_chol_solve_chains_f64", "droid_chol_chains_workspace_bytes",
+    "droid_proximity_workspace_bytes", "droid_proximity_mandatory_count", "droid_proximity_edges",
 ]
 
 
@@ -327,6 +329,46 @@ def reproject(poses, disps, intrinsics, ii, jj, target=None):
                                     _p(target) if target is not None else None, _p(coords), _p(valid),
                                     _p(motn) if motn is not None else None, n, ht, wd, _stream(poses)), "reproject")
     return [coords, valid] if motn is None else [coords, valid, motn]
+
+
+def proximity_edges(d, t, t0, t1, rad, nms, thresh, max_factors, stereo, ii_exist, jj_exist):
+    """Extension: the edge selection of ``FactorGraph.add_proximity_factors``
+    (droid_slam/factor_graph.py:305-369) on the device.  ``d`` = ``video.distance(ii, jj, beta)`` over
+    ``meshgrid(arange(t0, t), arange(t1, t))`` (float32 CUDA, row-major, left untouched); ``ii_exist`` / ``jj_exist`` =
+    ``cat(graph.ii, graph.ii_bad, graph.ii_inac)`` and likewise for jj.  Returns ``(ii, jj)`` int64 CUDA tensors: the
+    edge list the reference hands to ``add_factors``, in the same order.  One D2H read (the edge count)."""
+    if not d.is_cuda or d.dtype != torch.float32 or not d.is_contiguous():
+        raise RuntimeError("droid_backends.proximity_edges: d must be a contiguous float32 CUDA tensor")
+    t, t0, t1 = int(t), int(t0), int(t1)
+    n = (t - t0) * (t - t1)
+    if t0 < 0 or t1 < 0 or t < t0 or t < t1 or d.numel() != n:
+        raise RuntimeError("droid_backends.proximity_edges: d must hold (t - t0) * (t - t1) distances")
+    dev = d.device
+    ii_exist = ii_exist.to(device=dev, dtype=torch.long).contiguous()
+    jj_exist = jj_exist.to(device=dev, dtype=torch.long).contiguous()
+    if ii_exist.numel() != jj_exist.numel():
+        raise RuntimeError("droid_backends.proximity_edges: ii_exist / jj_exist differ in length")
+    with torch.cuda.device(dev):
+        mand = int(_lib.droid_proximity_mandatory_count(t, t0, int(rad), 1 if stereo else 0))
+        cap = max(mand, int(max_factors) + 1) + 4
+        out_ii = torch.empty((cap,), dtype=torch.long, device=dev)
+        out_jj = torch.empty((cap,), dtype=torch.long, device=dev)
+        count = torch.zeros((1,), dtype=torch.int32, device=dev)
+        nws = int(_lib.droid_proximity_workspace_bytes(n))
+        ws = torch.empty((nws,), dtype=torch.uint8, device=dev)
+        _check(_lib.droid_proximity_edges(_p(d), t, t0, t1, int(rad), int(nms), ctypes.c_float(float(thresh)),
+                                          int(max_factors), 1 if stereo else 0, _p(ii_exist), _p(jj_exist),
+                                          int(ii_exist.numel()), _p(out_ii), _p(out_jj), cap, _p(count),
+                                          ctypes.c_void_p(ws.data_ptr()), ctypes.c_size_t(nws), _stream(d)),
+               "proximity_edges")
+        k = int(count.item())
+        off = (-ws.data_ptr()) % 256
+        status = int(ws[off:off + 4].view(torch.int32).item())
+    if status & 1:
+        raise IndexError("droid_backends.proximity_edges: index out of range (t0, t1, rad as the Python code would raise)")
+    if status & 2:
+        raise RuntimeError("droid_backends.proximity_edges: edge capacity exhausted")
+    return out_ii[:k], out_jj[:k]
 
 
 def iproj(poses, disps, intrinsics):

@@ -149,6 +149,24 @@ int droid_depth_filter(const float* poses, const float* disps, const float* intr
                        const int64_t* ix, const float* thresh, float* counter, int num, int nbuf,
                        int ht, int wd, void* stream);
 
+/* ---- edge selection (extension) ------------------------------------------------------
+ * The part of FactorGraph.add_proximity_factors (droid_slam/factor_graph.py:305-369) behind the distance
+ * computation, on the device and stream-ordered.
+ *   d [(t-t0)*(t-t1)]: video.distance over meshgrid(arange(t0,t), arange(t1,t)), row-major (not modified);
+ *   ii_exist/jj_exist [n_exist]: cat(active, bad, inactive) edges of the graph (:322-323);
+ *   out_ii/out_jj [capacity]: the edge list handed to add_factors, in the reference's order (mandatory temporal /
+ *   stereo edges, then the accepted pairs in both directions by ascending distance; ties in index order);
+ *   out_count (device int): number of entries written.  capacity >= droid_proximity_mandatory_count(...) and
+ *   >= max_factors + 3 never overflows.  Status word = first int of the workspace: bit0 = an index the Python code
+ *   would have raised IndexError on, bit1 = capacity exhausted.
+ *   workspace: droid_proximity_workspace_bytes((t-t0)*(t-t1)) bytes of device memory. */
+size_t droid_proximity_workspace_bytes(int n_pairs);
+int droid_proximity_mandatory_count(int t, int t0, int rad, int stereo);
+int droid_proximity_edges(const float* d, int t, int t0, int t1, int rad, int nms, float thresh, int max_factors,
+                          int stereo, const int64_t* ii_exist, const int64_t* jj_exist, int n_exist,
+                          int64_t* out_ii, int64_t* out_jj, int capacity, int* out_count, void* workspace,
+                          size_t workspace_bytes, void* stream);
+
 /* ---- dense bundle adjustment -------------------------------------------------------------------
  * Replaces ba (src/droid.cpp:88-117, src/droid_kernels.cu:1314-1434).
  *   poses [nbuf_p,7] and disps [nbuf,ht,wd] are UPDATED IN PLACE; disps_sens [nbuf,ht,wd];

@@ -5,6 +5,8 @@ unmodified reference extension built by oracle/build_ref.sh is loadable -- again
 Tolerances (BASELINE.json north_star): index/count outputs bit-exact; correlation lookups <= 1e-5 relative;
 pose / inverse-depth updates <= 1e-4 relative per BA iteration.  "relative" = max |a-b| / max |b|.
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -617,3 +619,42 @@ def test_against_live_reference_extension(backends, ref_ext):
     d1 = backends.frame_distance(P, D, K, cu(q["fa"]), cu(q["fb"]), 0.3)
     d2 = ref_ext.frame_distance(P, D, K, cu(q["fa"]), cu(q["fb"]), 0.3)
     assert torch.equal(d1 == 1000.0, d2 == 1000.0) and rel(d1.cpu().numpy(), d2.cpu().numpy()) <= 1e-6
+
+
+@pytest.mark.parametrize("key", sorted(__import__("proximity_cases").CASES))
+def test_proximity_edges_bit_exact(backends, key):
+    """the device-side edge selection against the edge lists of the UNMODIFIED reference method
+    (tests/golden/ref_proximity.npz) and against the restatement: same edges, same order."""
+    import proximity_cases as PC
+    c = PC.make_case(key)
+    ref = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_proximity.npz"))
+    assert str(ref[key + "_digest"]) == PC.digest(c)
+    d = cu(c["d"])
+    d0 = d.clone()
+    ii, jj = backends.proximity_edges(d, c["t"], c["t0"], c["t1"], c["rad"], c["nms"], c["thresh"], c["max_factors"],
+                                      c["stereo"], cu(c["ii_exist"]), cu(c["jj_exist"]))
+    assert torch.equal(d, d0)                                           # the distances are the caller's
+    assert ii.dtype == torch.long and np.array_equal(ii.cpu().numpy(), ref[key + "_ii"])
+    assert np.array_equal(jj.cpu().numpy(), ref[key + "_jj"])
+
+
+def test_proximity_edges_large_graph_matches_oracle(backends):
+    """1000 keyframes (10^6 candidate pairs, the backend's size): device selection == restatement, and the
+    size-independent properties of the result: no duplicate edges, both directions present, every accepted pair
+    closer than thresh and at least rad + 1 frames apart."""
+    rng = np.random.default_rng(11)
+    t, rad, nms, thresh = 1000, 2, 3, 22.0
+    s = np.arange(t) * (2 * np.pi / 250.0)
+    pos = np.stack([10 * np.cos(s), 10 * np.sin(s), 0.002 * np.arange(t)], -1) + rng.normal(0, 0.2, size=(t, 3))
+    ii, jj = np.meshgrid(np.arange(t), np.arange(t), indexing="ij")
+    d = (np.linalg.norm(pos[ii.reshape(-1)] - pos[jj.reshape(-1)], axis=-1) * 6.0
+         + rng.uniform(0, 1e-3, size=t * t)).astype(np.float32)
+    empty = np.zeros(0, np.int64)
+    ri, rj = O.proximity_edges(d, t, 0, 0, rad, nms, thresh, 16 * t, False, empty, empty)
+    gi, gj = backends.proximity_edges(cu(d), t, 0, 0, rad, nms, thresh, 16 * t, False, cu(empty), cu(empty))
+    gi, gj = gi.cpu().numpy(), gj.cpu().numpy()
+    assert np.array_equal(gi, ri) and np.array_equal(gj, rj) and len(gi) > 6000
+    pairs = set(zip(gi.tolist(), gj.tolist()))
+    assert len(pairs) == len(gi) and all((b, a) in pairs for a, b in pairs)
+    far = np.abs(gi - gj) > rad + 1
+    assert far.any() and (d[gi[far] * t + gj[far]].reshape(-1, 2).min(axis=1) <= thresh).all()
