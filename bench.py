@@ -477,6 +477,27 @@ def extra_metrics(dev, hbm_peak, peaks):
         del rt
     except Exception as ex:                                        # noqa: BLE001
         out["reproject_motion"] = {"error": repr(ex)}
+    # edge selection at the backend's size: 1000 keyframes = 10^6 candidate pairs, on the device vs the
+    # restatement of the reference's Python loops on one host core
+    try:
+        import droid_oracle as O
+        rng = np.random.default_rng(11)
+        tk = 1000
+        sa = np.arange(tk) * (2 * np.pi / 250.0)
+        pos = np.stack([10 * np.cos(sa), 10 * np.sin(sa), 0.002 * np.arange(tk)], -1) + rng.normal(0, 0.2, size=(tk, 3))
+        gi, gj = np.meshgrid(np.arange(tk), np.arange(tk), indexing="ij")
+        dd = (np.linalg.norm(pos[gi.reshape(-1)] - pos[gj.reshape(-1)], axis=-1) * 6.0
+              + rng.uniform(0, 1e-3, size=tk * tk)).astype(np.float32)
+        ddev = torch.from_numpy(dd).to(dev)
+        none = torch.zeros(0, dtype=torch.long, device=dev)
+        t = timeit(lambda: B.proximity_edges(ddev, tk, 0, 0, 2, 3, 22.0, 16 * tk, False, none, none), n=10)
+        c0 = time.perf_counter()
+        ri, _ = O.proximity_edges(dd, tk, 0, 0, 2, 3, 22.0, 16 * tk, False, np.zeros(0, np.int64), np.zeros(0, np.int64))
+        cpu_s = time.perf_counter() - c0
+        out["proximity_edges"] = {"us": t * 1e6, "edges": int(len(ri)), "cpu_port_s": cpu_s, "speedup_vs_cpu_port": cpu_s / t,
+                                  "workload": "1000 keyframes, 10^6 candidate pairs, rad 2, nms 3, thresh 22 (backend settings)"}
+    except Exception as ex:                                        # noqa: BLE001
+        out["proximity_edges"] = {"error": repr(ex)}
     p = synth.make_ba_problem("C3")
     d = {k: torch.from_numpy(np.ascontiguousarray(p[k])).to(dev) for k in KEYS}
     p0, d0 = d["poses"].clone(), d["disps"].clone()

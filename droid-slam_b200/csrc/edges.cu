@@ -86,10 +86,19 @@ __global__ void __launch_bounds__(32) prox_greedy_kernel(const float* __restrict
   const int side = 2 * nms + 1;
   int count = mandatory;
   bool stop = false;
+  // the (distance, pair) of the next batch are fetched while this one is worked on; only the suppression flags, which
+  // this batch may still change, have to be read at the last moment
+  float nkey = lane < n ? keys[lane] : __int_as_float(0x7f800000);
+  int nidx = lane < n ? vals[lane] : 0;
   for (int base = 0; base < n && !stop; base += 32) {
     const int k = base + lane;
-    const float key = k < n ? keys[k] : __int_as_float(0x7f800000);
-    const int idx = k < n ? vals[k] : 0;
+    const float key = nkey;
+    const int idx = nidx;
+    {
+      const int kn = k + 32;
+      nkey = kn < n ? keys[kn] : __int_as_float(0x7f800000);
+      nidx = kn < n ? vals[kn] : 0;
+    }
     const int ci = t0 + idx / W, cj = t1 + idx % W;
     const bool close = k < n && !(key > thresh);                 // `if d[k] > thresh: continue`
     bool alive = close && __ldcg(sup + idx) == 0;
