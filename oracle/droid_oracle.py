@@ -698,3 +698,25 @@ def proximity_edges(d, t, t0, t1, rad, nms, thresh, max_factors, stereo, ii_exis
         suppress(i, j)
     e = np.asarray(es, np.int64).reshape(-1, 2)
     return e[:, 0].copy(), e[:, 1].copy()
+
+
+# ------------------------------------------------------------------------------------------------
+# convex upsampling
+# ------------------------------------------------------------------------------------------------
+def cvx_upsample(data, mask):
+    """droid_slam/droid_net.py:21-35.  data [batch,ht,wd,dim], mask [batch,9*8*8,ht,wd] logits -> [batch,8ht,8wd,dim]:
+    out[b, 8y+i, 8x+j, :] = sum_k softmax_k(mask[b, k, i, j, y, x]) * data[b, y + k//3 - 1, x + k%3 - 1, :] with zeros
+    outside the image (F.unfold(..., padding=1))."""
+    data = np.asarray(data, F32)
+    batch, ht, wd, dim = data.shape
+    m = np.asarray(mask, F32).reshape(batch, 9, 8, 8, ht, wd)
+    m = m - m.max(axis=1, keepdims=True)
+    e = np.exp(m).astype(F32)
+    w = (e / e.sum(axis=1, keepdims=True, dtype=F32)).astype(F32)                 # softmax over the 9 neighbours
+    pad = np.zeros((batch, ht + 2, wd + 2, dim), F32)
+    pad[:, 1:-1, 1:-1] = data
+    out = np.zeros((batch, ht, 8, wd, 8, dim), F32)
+    for k in range(9):
+        nb = pad[:, k // 3:k // 3 + ht, k % 3:k % 3 + wd]                         # [batch,ht,wd,dim]
+        out += w[:, k].transpose(0, 3, 1, 4, 2)[..., None] * nb[:, :, None, :, None, :]
+    return out.reshape(batch, 8 * ht, 8 * wd, dim)

@@ -187,3 +187,14 @@ def test_proximity_edges_vs_reference(key):
     ii, jj = O.proximity_edges(c["d"], c["t"], c["t0"], c["t1"], c["rad"], c["nms"], c["thresh"], c["max_factors"],
                                c["stereo"], c["ii_exist"], c["jj_exist"])
     assert np.array_equal(ii, ref[key + "_ii"]) and np.array_equal(jj, ref[key + "_jj"])
+
+
+@pytest.mark.parametrize("key", sorted(__import__("upsample_cases").CASES))
+def test_cvx_upsample_vs_reference(key):
+    """restatement of cvx_upsample against outputs of the UNMODIFIED reference function
+    (droid_net.py:21-35, run on CPU by tests/golden/make_golden_upsample.py).  <= 1e-6 relative."""
+    import upsample_cases as UC
+    data, mask = UC.make_case(key)
+    ref = gold("ref_cvx_upsample")
+    assert str(ref[key + "_digest"]) == UC.digest(data, mask)
+    assert rel(O.cvx_upsample(data, mask), ref[key]) <= 1e-6
