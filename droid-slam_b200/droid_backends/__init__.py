@@ -72,6 +72,7 @@ C_ABI_SYMBOLS = [
     "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_solve_env_f64",
     "droid_chol_workspace_bytes", "droid_chol_solve_chains_f64", "droid_chol_chains_workspace_bytes",
     "droid_proximity_workspace_bytes", "droid_proximity_mandatory_count", "droid_proximity_edges",
+    "droid_cvx_upsample",
 ]
 
 
@@ -369,6 +370,25 @@ def proximity_edges(d, t, t0, t1, rad, nms, thresh, max_factors, stereo, ii_exis
     if status & 2:
         raise RuntimeError("droid_backends.proximity_edges: edge capacity exhausted")
     return out_ii[:k], out_jj[:k]
+
+
+def cvx_upsample(data, mask):
+    """Extension: ``cvx_upsample`` of droid_slam/droid_net.py:21-35 in one pass.  data [batch,ht,wd,dim]
+    float32, mask [batch, 9*8*8, ht, wd] (any shape with that many elements; float32 or float16 logits) ->
+    [batch, 8*ht, 8*wd, dim] float32."""
+    _contig("cvx_upsample", data=data, mask=mask)
+    _dtype("cvx_upsample", data, (torch.float32,))
+    _dtype("cvx_upsample", mask, (torch.float32, torch.float16))
+    if data.dim() != 4:
+        raise RuntimeError("droid_backends.cvx_upsample: data must be [batch,ht,wd,dim]")
+    batch, ht, wd, dim = data.shape
+    if mask.numel() != batch * 576 * ht * wd or mask.device != data.device:
+        raise RuntimeError("droid_backends.cvx_upsample: mask must hold batch * 9*8*8 * ht * wd logits on data's device")
+    with torch.cuda.device(data.device):
+        out = torch.empty((batch, 8 * ht, 8 * wd, dim), dtype=torch.float32, device=data.device)
+        _check(_lib.droid_cvx_upsample(_p(data), _p(mask), _p(out), 0 if mask.dtype == torch.float32 else 1,
+                                       batch, ht, wd, dim, _stream(data)), "cvx_upsample")
+    return out
 
 
 def iproj(poses, disps, intrinsics):

@@ -167,6 +167,13 @@ int droid_proximity_edges(const float* d, int t, int t0, int t1, int rad, int nm
                           int64_t* out_ii, int64_t* out_jj, int capacity, int* out_count, void* workspace,
                           size_t workspace_bytes, void* stream);
 
+/* ---- convex upsampling (extension) -----------------------------------------------------
+ * cvx_upsample (droid_slam/droid_net.py:21-35), as DepthVideo.upsample applies it (depth_video.py:123-127).
+ *   data [batch,ht,wd,dim] float32; mask [batch,9*8*8,ht,wd] logits, float32 (mask_dtype 0) or float16 (1);
+ *   out [batch,8*ht,8*wd,dim] float32, fully written. */
+int droid_cvx_upsample(const float* data, const void* mask, float* out, int mask_dtype, int batch, int ht, int wd,
+                       int dim, void* stream);
+
 /* ---- dense bundle adjustment -------------------------------------------------------------------
  * Replaces ba (src/droid.cpp:88-117, src/droid_kernels.cu:1314-1434).
  *   poses [nbuf_p,7] and disps [nbuf,ht,wd] are UPDATED IN PLACE; disps_sens [nbuf,ht,wd];

@@ -658,3 +658,33 @@ def test_proximity_edges_large_graph_matches_oracle(backends):
     assert len(pairs) == len(gi) and all((b, a) in pairs for a, b in pairs)
     far = np.abs(gi - gj) > rad + 1
     assert far.any() and (d[gi[far] * t + gj[far]].reshape(-1, 2).min(axis=1) <= thresh).all()
+
+
+@pytest.mark.parametrize("key", sorted(__import__("upsample_cases").CASES))
+def test_cvx_upsample_matches_reference(backends, key):
+    """one-pass convex upsampling against outputs of the UNMODIFIED reference function
+    (tests/golden/ref_cvx_upsample.npz) and the restatement, float32 mask: <= 1e-5 relative (expf vs torch's exp);
+    float16 mask (what autocast hands DepthVideo.upsample): against the restatement fed the same rounded logits."""
+    import upsample_cases as UC
+    data, mask = UC.make_case(key)
+    ref = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_cvx_upsample.npz"))
+    assert str(ref[key + "_digest"]) == UC.digest(data, mask)
+    out = backends.cvx_upsample(cu(data), cu(mask)).cpu().numpy()
+    assert out.shape == ref[key].shape
+    assert rel(out, ref[key]) <= 1e-5 and rel(out, O.cvx_upsample(data, mask)) <= 1e-5
+    mh = mask.astype(np.float16)
+    outh = backends.cvx_upsample(cu(data), cu(mh)).cpu().numpy()
+    assert rel(outh, O.cvx_upsample(data, mh.astype(np.float32))) <= 2e-3      # weights rounded to half, 9 terms
+
+
+def test_cvx_upsample_full_size_properties(backends):
+    """At the frontend's size (48x64 -> 384x512): a convex combination stays inside the range of its 3x3 neighbourhood,
+    and a constant map is reproduced exactly where no zero padding enters (interior)."""
+    rng = np.random.default_rng(9)
+    data = rng.uniform(0.2, 3.0, size=(4, 48, 64, 1)).astype(np.float32)
+    mask = rng.normal(size=(4, 576, 48, 64)).astype(np.float32) * 3
+    out = backends.cvx_upsample(cu(data), cu(mask)).cpu().numpy()
+    assert out.shape == (4, 384, 512, 1) and out.max() <= data.max() * (1 + 1e-6) and out.min() >= 0.0
+    const = np.full_like(data, 1.25)
+    oc = backends.cvx_upsample(cu(const), cu(mask)).cpu().numpy()
+    assert np.abs(oc[:, 8:-8, 8:-8] - 1.25).max() <= 1e-6
