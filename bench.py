@@ -477,6 +477,18 @@ def extra_metrics(dev, hbm_peak, peaks):
         del rt
     except Exception as ex:                                        # noqa: BLE001
         out["reproject_motion"] = {"error": repr(ex)}
+    # convex upsampling: 64 inverse-depth maps 48x64 -> 384x512, float32 mask (2304 B in, 260 B out per pixel)
+    try:
+        nb_, hh, ww = 64, 48, 64
+        dat = torch.rand((nb_, hh, ww, 1), device=dev) + 0.1
+        msk = torch.randn((nb_, 576, hh, ww), device=dev)
+        t = timeit(lambda: B.cvx_upsample(dat, msk), n=10)
+        ub = nb_ * hh * ww * (576 * 4 + 4 + 256)
+        out["cvx_upsample"] = {"us": t * 1e6, "GBps": ub / t / 1e9, "hbm_frac": ub / t / 1e9 / hbm_peak, "bound": "hbm",
+                               "algorithmic_bytes": ub, "workload": "64 maps 48x64 -> 384x512, float32 mask"}
+        del msk
+    except Exception as ex:                                        # noqa: BLE001
+        out["cvx_upsample"] = {"error": repr(ex)}
     # edge selection at the backend's size: 1000 keyframes = 10^6 candidate pairs, on the device vs the
     # restatement of the reference's Python loops on one host core
     try:
