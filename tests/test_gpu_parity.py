@@ -688,3 +688,29 @@ def test_cvx_upsample_full_size_properties(backends):
     const = np.full_like(data, 1.25)
     oc = backends.cvx_upsample(cu(const), cu(mask)).cpu().numpy()
     assert np.abs(oc[:, 8:-8, 8:-8] - 1.25).max() <= 1e-6
+
+
+def test_extension_ops_empty_and_invalid_inputs(backends):
+    """Edge cases of the SURVEY 8f extensions: empty edge lists / batches give empty outputs without a launch error,
+    wrong dtypes and shapes raise RuntimeError like the nine reference operators do for non-contiguous input."""
+    poses, disps, intr, ii, jj = geom_inputs()
+    n = poses.shape[0]
+    K = cu(np.tile(intr[None], (n, 1)).astype(np.float32))
+    none = torch.zeros(0, dtype=torch.long, device=DEV)
+    c, v = backends.reproject(cu(poses), cu(disps), K, none, none)
+    assert c.shape == (0,) + disps.shape[1:] + (2,) and v.shape == (0,) + disps.shape[1:] + (1,)
+    with pytest.raises(RuntimeError):
+        backends.reproject(cu(poses), cu(disps), K, cu(ii).int(), cu(jj).int())
+    assert backends.cvx_upsample(torch.zeros((0, 4, 6, 1), device=DEV), torch.zeros((0, 576, 4, 6), device=DEV)).shape == (0, 32, 48, 1)
+    with pytest.raises(RuntimeError):
+        backends.cvx_upsample(torch.zeros((1, 4, 6, 1), device=DEV), torch.zeros((1, 64, 4, 6), device=DEV))
+    # no candidate pairs at all (t == t0): nothing mandatory, nothing accepted
+    gi, gj = backends.proximity_edges(torch.zeros(0, device=DEV), 7, 7, 2, 2, 1, 16.0, 48, False, none, none)
+    assert gi.numel() == 0 and gj.numel() == 0
+    # one new frame against a window: only its temporal neighbours when everything else is far away
+    d = torch.full((1 * 6,), 50.0, device=DEV)
+    gi, gj = backends.proximity_edges(d, 8, 7, 2, 2, 1, 16.0, 48, False, none, none)
+    ri, rj = O.proximity_edges(d.cpu().numpy(), 8, 7, 2, 2, 1, 16.0, 48, False, np.zeros(0, np.int64), np.zeros(0, np.int64))
+    assert np.array_equal(gi.cpu().numpy(), ri) and np.array_equal(gj.cpu().numpy(), rj) and len(ri) == 6
+    with pytest.raises(RuntimeError):
+        backends.proximity_edges(d.double(), 8, 7, 2, 2, 1, 16.0, 48, False, none, none)
