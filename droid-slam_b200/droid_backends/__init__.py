@@ -57,6 +57,7 @@ def _load():
     lib.droid_corr_build_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_launch_count.restype = ctypes.c_ulonglong
     lib.droid_proximity_workspace_bytes.restype = ctypes.c_size_t
+    lib.droid_scatter_mean_workspace_bytes.restype = ctypes.c_size_t
     return lib
 
 
@@ -72,7 +73,7 @@ C_ABI_SYMBOLS = [
     "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_solve_env_f64",
     "droid_chol_workspace_bytes", "droid_chol_solve_chains_f64", "droid_chol_chains_workspace_bytes",
     "droid_proximity_workspace_bytes", "droid_proximity_mandatory_count", "droid_proximity_edges",
-    "droid_cvx_upsample",
+    "droid_cvx_upsample", "droid_scatter_mean_workspace_bytes", "droid_scatter_mean",
 ]
 
 
@@ -388,6 +389,35 @@ def cvx_upsample(data, mask):
         out = torch.empty((batch, 8 * ht, 8 * wd, dim), dtype=torch.float32, device=data.device)
         _check(_lib.droid_cvx_upsample(_p(data), _p(mask), _p(out), 0 if mask.dtype == torch.float32 else 1,
                                        batch, ht, wd, dim, _stream(data)), "cvx_upsample")
+    return out
+
+
+def scatter_mean(src, index, dim=1, dim_size=None):
+    """Extension: ``torch_scatter.scatter_mean(src, index, dim=1)`` as ``GraphAgg.forward`` uses it
+    (droid_slam/droid_net.py:67): src [1, n, ...] (batch 1, like everywhere in DROID-SLAM's inference) float32 or
+    float16, index [n] int64 -> [1, dim_size or index.max() + 1, ...].  Accumulates in float32."""
+    if dim != 1 or src.dim() < 2 or src.shape[0] != 1:
+        raise RuntimeError("droid_backends.scatter_mean: only dim=1 of a [1, n, ...] tensor (GraphAgg's use)")
+    _contig("scatter_mean", src=src, index=index)
+    _long("scatter_mean", index=index)
+    _dtype("scatter_mean", src, (torch.float32, torch.float16))
+    n = src.shape[1]
+    if index.numel() != n:
+        raise RuntimeError("droid_backends.scatter_mean: index must have one entry per slice of dim 1")
+    M = int(dim_size) if dim_size is not None else (int(index.max().item()) + 1 if n > 0 else 0)
+    D = 1
+    for s_ in src.shape[2:]:
+        D *= int(s_)
+    V = 4 if src.dtype == torch.float32 else 8
+    if D % V != 0:
+        raise RuntimeError("droid_backends.scatter_mean: trailing size must be a multiple of %d" % V)
+    with torch.cuda.device(src.device):
+        out = torch.empty((1, M) + tuple(src.shape[2:]), dtype=src.dtype, device=src.device)
+        nws = int(_lib.droid_scatter_mean_workspace_bytes(n, M))
+        ws = torch.empty((nws,), dtype=torch.uint8, device=src.device)
+        _check(_lib.droid_scatter_mean(_p(src), _p(index), _p(out), 0 if src.dtype == torch.float32 else 1, n, M,
+                                       ctypes.c_longlong(D), ctypes.c_void_p(ws.data_ptr()), ctypes.c_size_t(nws),
+                                       _stream(src)), "scatter_mean")
     return out
 
 

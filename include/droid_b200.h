@@ -174,6 +174,15 @@ int droid_proximity_edges(const float* d, int t, int t0, int t1, int rad, int nm
 int droid_cvx_upsample(const float* data, const void* mask, float* out, int mask_dtype, int batch, int ht, int wd,
                        int dim, void* stream);
 
+/* ---- segmented mean over edges (extension) -----------------------------------------------
+ * scatter_mean(net, ix, dim=1) of GraphAgg.forward (droid_slam/droid_net.py:59-75; torch_scatter): out[m] = mean of
+ * src[e] over the edges with ix[e] == m.  src [n,D], out [M,D] (every row written; 0 for an empty group), float32
+ * (dtype 0, D % 4 == 0) or float16 (dtype 1, D % 8 == 0), 16-byte aligned; accumulation in float32, ascending edge
+ * order.  Status word = first int of the workspace: bit0 = an index outside [0, M). */
+size_t droid_scatter_mean_workspace_bytes(int n, int M);
+int droid_scatter_mean(const void* src, const int64_t* ix, void* out, int dtype, int n, int M, long long D,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- dense bundle adjustment -------------------------------------------------------------------
  * Replaces ba (src/droid.cpp:88-117, src/droid_kernels.cu:1314-1434).
  *   poses [nbuf_p,7] and disps [nbuf,ht,wd] are UPDATED IN PLACE; disps_sens [nbuf,ht,wd];

@@ -720,3 +720,22 @@ def cvx_upsample(data, mask):
         nb = pad[:, k // 3:k // 3 + ht, k % 3:k % 3 + wd]                         # [batch,ht,wd,dim]
         out += w[:, k].transpose(0, 3, 1, 4, 2)[..., None] * nb[:, :, None, :, None, :]
     return out.reshape(batch, 8 * ht, 8 * wd, dim)
+
+
+# ------------------------------------------------------------------------------------------------
+# segmented mean over edges
+# ------------------------------------------------------------------------------------------------
+def scatter_mean(src, index, dim_size=None):
+    """torch_scatter.scatter_mean(src, index, dim=1) as GraphAgg.forward uses it (droid_slam/droid_net.py:59-75).
+    torch_scatter is not vendored in the reference (conda `pytorch-scatter`, unpinned, environment.yaml:10), so this
+    restates its published algorithm: out = scatter_sum(src) / clamp(scatter_sum(ones), min=1).  src [1, n, ...],
+    index [n] -> [1, M, ...]; sums in float64 here (the checker), result in src's dtype."""
+    src = np.asarray(src)
+    index = np.asarray(index, np.int64)
+    M = int(dim_size) if dim_size is not None else (int(index.max()) + 1 if len(index) else 0)
+    acc = np.zeros((M,) + src.shape[2:], np.float64)
+    cnt = np.zeros(M, np.float64)
+    np.add.at(acc, index, src[0].astype(np.float64))
+    np.add.at(cnt, index, 1.0)
+    out = acc / np.maximum(cnt, 1.0).reshape((M,) + (1,) * (src.ndim - 2))
+    return out.astype(src.dtype)[None]

@@ -714,3 +714,24 @@ def test_extension_ops_empty_and_invalid_inputs(backends):
     assert np.array_equal(gi.cpu().numpy(), ri) and np.array_equal(gj.cpu().numpy(), rj) and len(ri) == 6
     with pytest.raises(RuntimeError):
         backends.proximity_edges(d.double(), 8, 7, 2, 2, 1, 16.0, 48, False, none, none)
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float32, 1e-6), (np.float16, 1e-3)])
+def test_scatter_mean_matches_oracle(backends, dtype, tol):
+    """the segmented mean of GraphAgg.forward (scatter_mean(net, ix, dim=1)) at the frontend's shape
+    (60 edges, 128 channels, 48x64) against the float64 restatement; float16 maps (autocast) accumulate in float32 and
+    round once, so they land within half precision of it.  Includes an empty group and unsorted indices."""
+    rng = np.random.default_rng(8)
+    n, M = 60, 13
+    src = rng.normal(size=(1, n, 128, 48, 64)).astype(dtype)
+    idx = rng.integers(0, M, size=n)
+    idx[idx == 7] = 3
+    want = O.scatter_mean(src, idx, dim_size=M).astype(np.float32)
+    got = backends.scatter_mean(cu(src), cu(idx.astype(np.int64)), dim_size=M)
+    assert got.dtype == (torch.float32 if dtype == np.float32 else torch.float16) and tuple(got.shape) == (1, M, 128, 48, 64)
+    g = got.float().cpu().numpy()
+    assert rel(g, want) <= tol and np.all(g[0, 7] == 0)
+    # default size = index.max() + 1, like torch_scatter
+    assert backends.scatter_mean(cu(src[:, :5]), cu(np.array([2, 0, 2, 1, 0], np.int64))).shape[1] == 3
+    with pytest.raises(RuntimeError):
+        backends.scatter_mean(cu(src[0]), cu(idx.astype(np.int64)))

@@ -198,3 +198,18 @@ def test_cvx_upsample_vs_reference(key):
     ref = gold("ref_cvx_upsample")
     assert str(ref[key + "_digest"]) == UC.digest(data, mask)
     assert rel(O.cvx_upsample(data, mask), ref[key]) <= 1e-6
+
+
+def test_scatter_mean_restatement_against_torch_index_add():
+    """torch_scatter is absent; its scatter_mean is restated (sum / clamp(count, 1)) and checked
+    here against the same definition built from torch.index_add_ (the shim SURVEY 8c names)."""
+    import torch
+    rng = np.random.default_rng(4)
+    src = rng.normal(size=(1, 23, 8, 3, 4)).astype(np.float32)
+    idx = rng.integers(0, 6, size=23)
+    idx[idx == 4] = 5                                               # an empty group in the middle
+    out = O.scatter_mean(src, idx)
+    s = torch.zeros((1, 6, 8, 3, 4), dtype=torch.float64).index_add_(1, torch.from_numpy(idx), torch.from_numpy(src).double())
+    c = torch.zeros(6, dtype=torch.float64).index_add_(0, torch.from_numpy(idx), torch.ones(23, dtype=torch.float64))
+    want = (s / c.clamp(min=1).view(1, 6, 1, 1, 1)).float().numpy()
+    assert out.shape == (1, 6, 8, 3, 4) and rel(out, want) <= 1e-6 and np.all(out[0, 4] == 0)
