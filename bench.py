@@ -489,6 +489,18 @@ def extra_metrics(dev, hbm_peak, peaks):
         del msk
     except Exception as ex:                                        # noqa: BLE001
         out["cvx_upsample"] = {"error": repr(ex)}
+    # segmented mean of GraphAgg: 60 edges x 128 channels x 48x64 float16 -> 12 source frames
+    try:
+        ne_, m_ = 60, 12
+        srcm = torch.randn((1, ne_, 128, 48, 64), device=dev).half()
+        ixm = (torch.arange(ne_, device=dev) % m_).long()
+        t = timeit(lambda: B.scatter_mean(srcm, ixm, dim_size=m_), n=10)
+        sb = (ne_ + m_) * 128 * 48 * 64 * 2
+        out["scatter_mean"] = {"us": t * 1e6, "GBps": sb / t / 1e9, "hbm_frac": sb / t / 1e9 / hbm_peak, "bound": "hbm",
+                               "algorithmic_bytes": sb, "workload": "60 edges x 128 x 48x64 float16 -> 12 frames"}
+        del srcm
+    except Exception as ex:                                        # noqa: BLE001
+        out["scatter_mean"] = {"error": repr(ex)}
     # edge selection at the backend's size: 1000 keyframes = 10^6 candidate pairs, on the device vs the
     # restatement of the reference's Python loops on one host core
     try:
