@@ -430,6 +430,16 @@ def extra_metrics(dev, hbm_peak, peaks):
             ts.append(e0.elapsed_time(e1))
         return float(np.median(ts)) * 1e-3
 
+    # write-only HBM bandwidth of this GPU (a plain fill), measured here: the roof of kernels that only write.  On this
+    # pool's B200s it is ~3.9 TB/s, well below the 6.55 TB/s that a copy (half reads, half writes) moves.
+    fill = torch.empty(1 << 30, dtype=torch.uint8, device=dev)
+    tf = []
+    for _ in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fill.zero_(); e1.record(); torch.cuda.synchronize(); tf.append(e0.elapsed_time(e1))
+    write_peak = (1 << 30) / (sorted(tf)[len(tf) // 2] * 1e-3) / 1e9
+    out["hbm_write_only_fill"] = {"GBps": write_peak, "workload": "torch fill of 1 GiB, median of 6"}
+    del fill
     Bn, H, W, C, r = 24, 48, 64, 128, 3
     q = synth.make_corr_problem(Bn, H, W, C, seed=1234)
     f1 = torch.from_numpy(q["fmaps"][q["ii"]]).to(dev)
@@ -443,6 +453,8 @@ def extra_metrics(dev, hbm_peak, peaks):
     tpeak = float(peaks.get("bf16_tflops", 1590.0))
     out["corr_build"] = {"us": t * 1e6, "GBps": by / t / 1e9, "hbm_frac": by / t / 1e9 / hbm_peak, "TFLOPs": fl / t / 1e12,
                          "tensor_frac": fl / t / 1e12 / tpeak, "bound": "hbm (write)", "algorithmic_bytes": by,
+                         "write_GBps": (by - 2 * Bn * C * HW * 2) / t / 1e9,
+                         "write_roof_frac": (by - 2 * Bn * C * HW * 2) / t / 1e9 / write_peak,
                          "workload": "24 edges, 48x64x128 fp16 -> 4-level pyramid", "l2": "flushed between calls"}
     # lookup: coords (8 B) + up to 64 taps in + 49 out per pixel per level, 2 B elements (SURVEY 8d upper bound)
     lb = 4 * Bn * HW * (8 + 64 * 2 + 49 * 2)

@@ -19,7 +19,8 @@
 //    The two TMEM halves (4 image rows each) are drained and refilled independently so the MMAs of the next tile
 //    overlap the stores of the current one.
 //
-// Warp roles (160 threads): warps 0-3 = epilogue (TMEM lane quarter = warp id), warp 4 = TMA producer + MMA issuer.
+// Warp roles: W == 64 (288 threads): warps 0-3 / 4-7 = the two epilogue groups (TMEM lane quarter = warp & 3, accumulator
+// half = warp >> 2), warp 8 = TMA producer + MMA issuer; W < 64 (160 threads): warps 0-3 = epilogue, warp 4 = producer.
 #include <cuda.h>
 #include <cuda_fp16.h>
 
@@ -34,7 +35,8 @@ static constexpr int kBoxPix = 64;       // pixels per TMA box (128 bytes of fp1
 static constexpr int kBoxBytes = kBoxPix * kC * 2;   // 16 KB
 static constexpr int kABytes = 2 * kBoxBytes;        // 128 pixels
 static constexpr int kMaxNBoxes = 8;                 // 8 rows x 64 columns
-static constexpr int kThreads = 160;
+static constexpr int kThreads = 160;                 // 4 epilogue warps + producer (W < 64)
+static constexpr int kThreads64 = 288;               // 8 epilogue warps + producer (W == 64)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -113,6 +115,8 @@ template <int N>
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+// one named barrier per epilogue group (id 1 / 2), 128 threads each
+__device__ __forceinline__ void epi_barrier_g(int g) { asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory"); }
 __device__ __forceinline__ float2 unpack_h2(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
 __device__ __forceinline__ uint32_t pool4_h2(uint32_t top_a, uint32_t bot_a, uint32_t top_b, uint32_t bot_b);
 
@@ -142,14 +146,17 @@ struct Smem {
   // operand buffers first (1024-byte aligned for the 128-byte swizzle)
   static constexpr int kBOff = 0;
   static constexpr int kAOff = kMaxNBoxes * kBoxBytes;          // 128 KB
-  static constexpr int kStageOff = kAOff + 2 * kABytes;         // +64 KB: two 16 KB level-0 row staging buffers
-  static constexpr int kStageBytes = kTileM * 64 * 2;           // 128 pixels x 64 columns fp16
-  static constexpr int kBarOff = kStageOff + 2 * kStageBytes;
-  static constexpr int kBytes = kBarOff + 128 + 1024;
+  static constexpr int kStageOff = kAOff + kABytes;             // +32 KB: ONE A tile (see the producer)
+  static constexpr int kStageBytes = kTileM * 64 * 2;           // 128 pixels x 64 columns fp16 = one level-0 row block
+  static constexpr int kXchOff = kStageOff + 2 * kStageBytes;   // two staging buffers (W == 64: one per epilogue group)
+  static constexpr int kXchBytes = kTileM * 8 * 4;              // level-2 values of the upper half, one tile
+  static constexpr int kBarOff = kXchOff + 2 * kXchBytes;
+  static constexpr int kBytes = kBarOff + 256 + 1024;
 };
 
+
 template <int W>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(W == 64 ? kThreads64 : kThreads, 1)
 corr_build_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmOut, __half* __restrict__ lvl0, __half* __restrict__ lvl1, __half* __restrict__ lvl2,
                   __half* __restrict__ lvl3, int H, int HW) {
@@ -160,11 +167,14 @@ corr_build_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   unsigned char* As = smem + Smem::kAOff;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Smem::kBarOff);
   uint64_t* b_full = bars + 0;
-  uint64_t* a_full = bars + 1;     // [2]
-  uint64_t* a_empty = bars + 3;    // [2]
-  uint64_t* acc_full = bars + 5;   // [2]
-  uint64_t* acc_empty = bars + 7;  // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* a_full = bars + 1;     // the A tile of this iteration has landed
+  uint64_t* a_empty = bars + 2;    // ... and its MMAs are done
+  uint64_t* acc_full = bars + 3;   // [2]
+  uint64_t* acc_empty = bars + 5;  // [2]
+  uint64_t* x_full = bars + 7;     // [2]  W == 64: level-2 values of the upper half handed to the lower-half group
+  uint64_t* x_empty = bars + 9;    // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  constexpr int kProducer = W == 64 ? 8 : 4;      // warp index of the TMA / MMA warp = number of epilogue warps
 
   constexpr int NHALF = 4 * W;               // accumulator columns per half (4 image rows)
   constexpr int NBOX = 8 * W / kBoxPix;      // TMA boxes of the B tile
@@ -174,15 +184,17 @@ corr_build_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   if (threadIdx.x == 0) {
     mbar_init(b_full, 1);
+    mbar_init(a_full, 1);
+    mbar_init(a_empty, 1);
     for (int i = 0; i < 2; i++) {
-      mbar_init(a_full + i, 1);
-      mbar_init(a_empty + i, 1);
       mbar_init(acc_full + i, 1);
       mbar_init(acc_empty + i, 128);
+      mbar_init(x_full + i, 128);
+      mbar_init(x_empty + i, 128);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 4) {
+  if (warp == kProducer) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -191,22 +203,21 @@ corr_build_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == 4) {
+  if (warp == kProducer) {
     if (lane == 0) {
       // ---------------- TMA producer + MMA issuer (one thread) ----------------
+      // ONE A buffer: the MMAs of a tile take ~1 us and the tile after it cannot start before the epilogue has freed
+      // the accumulator (several us later), so the next A tile is fetched as soon as this one's MMAs are done and is
+      // there long before it is needed; the 32 KB saved pay for the second epilogue group's staging.
       mbar_expect_tx(b_full, NBOX * kBoxBytes);
       for (int i = 0; i < NBOX; i++) tma_load_3d(Bs + i * kBoxBytes, &tmB, b_full, nt * 8 * W + i * kBoxPix, 0, b);
-      for (int t = 0; t < 2 && t < T; t++) {
-        mbar_expect_tx(a_full + t, kABytes);
-        for (int j = 0; j < 2; j++)
-          tma_load_3d(As + t * kABytes + j * kBoxBytes, &tmA, a_full + t, t * kTileM + j * kBoxPix, 0, b);
-      }
+      mbar_expect_tx(a_full, kABytes);
+      for (int j = 0; j < 2; j++) tma_load_3d(As + j * kBoxBytes, &tmA, a_full, j * kBoxPix, 0, b);
       const uint32_t idesc = umma_idesc(NHALF);
       mbar_wait(b_full, 0);
       for (int t = 0; t < T; t++) {
-        const int s = t & 1;
-        mbar_wait(a_full + s, (t >> 1) & 1);
-        const uint64_t adesc = umma_desc(smem_u32(As + s * kABytes));
+        mbar_wait(a_full, t & 1);
+        const uint64_t adesc = umma_desc(smem_u32(As));
         for (int h = 0; h < 2; h++) {
           if (t > 0) mbar_wait(acc_empty + h, (t - 1) & 1);
           tc_fence_after();
@@ -216,12 +227,12 @@ corr_build_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             umma_f16(tmem + h * NHALF, adesc + (uint64_t)(k * 2048 >> 4), bdesc + (uint64_t)(k * 2048 >> 4), idesc, k > 0);
           umma_commit(acc_full + h);
         }
-        umma_commit(a_empty + s);
-        if (t + 2 < T) {
-          mbar_wait(a_empty + s, (t >> 1) & 1);
-          mbar_expect_tx(a_full + s, kABytes);
+        umma_commit(a_empty);
+        if (t + 1 < T) {
+          mbar_wait(a_empty, t & 1);
+          mbar_expect_tx(a_full, kABytes);
           for (int j = 0; j < 2; j++)
-            tma_load_3d(As + s * kABytes + j * kBoxBytes, &tmA, a_full + s, (t + 2) * kTileM + j * kBoxPix, 0, b);
+            tma_load_3d(As + j * kBoxBytes, &tmA, a_full, (t + 1) * kTileM + j * kBoxPix, 0, b);
         }
       }
     }
@@ -233,83 +244,98 @@ corr_build_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if constexpr (W == 64) {
       // Level 0 (75 % of the bytes) leaves through shared memory and TMA: every thread writes its pixel's 128-byte
       // row of the staged [128 x 64] block (128B-swizzled: conflict-free), one elected thread issues the bulk store.
-      unsigned char* stage = smem + Smem::kStageOff;
-      const int row_in_tile = warp * 32 + lane;
+      // TWO epilogue groups of four warps: group g owns accumulator half g (image rows 4g .. 4g+3 of the N tile), its
+      // own staging buffer and named barrier, so both halves are drained at the same time and every scheduler has two
+      // epilogue warps to interleave (with one group the kernel was the latency chain of that group: ~1540 cycles per
+      // row, DRAM 37 % busy).  Levels 0-2 are complete inside a half; level 3 pools across the two, so group 0 hands
+      // its eight level-2 values per pixel to group 1 through shared memory (double-buffered, mbarrier hand-shake).
+      const int g = warp >> 2, q = warp & 3, h = g;
+      unsigned char* buf = smem + Smem::kStageOff + g * Smem::kStageBytes;
+      uint32_t* xch = reinterpret_cast<uint32_t*>(smem + Smem::kXchOff);
+      const int row_in_tile = q * 32 + lane;
+      const bool leader = q == 0 && lane == 0;
       for (int t = 0; t < T; t++) {
         const int m = t * kTileM + row_in_tile;
         const bool live = m < HW;
         const size_t pix = (size_t)b * HW + (live ? m : 0);
-        uint32_t l2keep[2][8];
+        uint32_t l2[8];
+        mbar_wait(acc_full + h, t & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + h * NHALF;
+        uint32_t prev[32], p1keep[16];
 #pragma unroll
-        for (int h = 0; h < 2; h++) {
-          mbar_wait(acc_full + h, t & 1);
-          tc_fence_after();
-          const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + h * NHALF;
-          uint32_t prev[32], p1keep[16];
+        for (int r = 0; r < 4; r++) {
+          uint32_t cur[32];
+          {
+            float v[64];
 #pragma unroll
-          for (int r = 0; r < 4; r++) {
-            uint32_t cur[32];
-            {
-              float v[64];
-#pragma unroll
-              for (int j = 0; j < 4; j++) tmem_ld16(taddr + r * 64 + j * 16, v + j * 16);
-              tmem_ld_wait();
-              if (r == 3) {                         // this half of TMEM is drained: let the next tile's MMAs start
-                tc_fence_before();
-                mbar_arrive(acc_empty + h);
-              }
-#pragma unroll
-              for (int i = 0; i < 32; i++) cur[i] = pack_h2(v[2 * i] * scale, v[2 * i + 1] * scale);
+            for (int j = 0; j < 4; j++) tmem_ld16(taddr + r * 64 + j * 16, v + j * 16);
+            tmem_ld_wait();
+            if (r == 3) {                         // this half of TMEM is drained: let the next tile's MMAs start
+              tc_fence_before();
+              mbar_arrive(acc_empty + h);
             }
-            unsigned char* buf = stage + (r & 1) * Smem::kStageBytes;
-            if (threadIdx.x == 0) bulk_wait_read<1>();   // the store that last used this buffer has read it
-            epi_barrier();
-            uint4* rowp = reinterpret_cast<uint4*>(buf + row_in_tile * 128);
 #pragma unroll
-            for (int j = 0; j < 8; j++)
-              rowp[j ^ (row_in_tile & 7)] = make_uint4(cur[4 * j], cur[4 * j + 1], cur[4 * j + 2], cur[4 * j + 3]);
-            fence_async_smem();
-            epi_barrier();
-            if (threadIdx.x == 0) {
-              tma_store_4d(&tmOut, buf, 0, nt * 8 + h * 4 + r, t * kTileM, b);
-              bulk_commit();
+            for (int i = 0; i < 32; i++) cur[i] = pack_h2(v[2 * i] * scale, v[2 * i + 1] * scale);
+          }
+          if (leader) bulk_wait_read<0>();        // the store of the previous row has read the staging buffer
+          epi_barrier_g(g);
+          uint4* rowp = reinterpret_cast<uint4*>(buf + row_in_tile * 128);
+#pragma unroll
+          for (int j = 0; j < 8; j++)
+            rowp[j ^ (row_in_tile & 7)] = make_uint4(cur[4 * j], cur[4 * j + 1], cur[4 * j + 2], cur[4 * j + 3]);
+          fence_async_smem();
+          epi_barrier_g(g);
+          if (leader) {
+            tma_store_4d(&tmOut, buf, 0, nt * 8 + h * 4 + r, t * kTileM, b);
+            bulk_commit();
+          }
+          if (r & 1) {
+            uint32_t p1[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) p1[i] = pool4_h2(prev[2 * i], cur[2 * i], prev[2 * i + 1], cur[2 * i + 1]);
+            if (live) {
+              uint4* dst = reinterpret_cast<uint4*>(lvl1 + (pix * H2 + (nt * 4 + h * 2 + (r >> 1))) * W2);
+#pragma unroll
+              for (int j = 0; j < 4; j++) dst[j] = make_uint4(p1[4 * j], p1[4 * j + 1], p1[4 * j + 2], p1[4 * j + 3]);
             }
-            if (r & 1) {
-              uint32_t p1[16];
+            if (r == 1) {
 #pragma unroll
-              for (int i = 0; i < 16; i++) p1[i] = pool4_h2(prev[2 * i], cur[2 * i], prev[2 * i + 1], cur[2 * i + 1]);
-              if (live) {
-                uint4* dst = reinterpret_cast<uint4*>(lvl1 + (pix * H2 + (nt * 4 + h * 2 + (r >> 1))) * W2);
-#pragma unroll
-                for (int j = 0; j < 4; j++) dst[j] = make_uint4(p1[4 * j], p1[4 * j + 1], p1[4 * j + 2], p1[4 * j + 3]);
-              }
-              if (r == 1) {
-#pragma unroll
-                for (int i = 0; i < 16; i++) p1keep[i] = p1[i];
-              } else {
-#pragma unroll
-                for (int i = 0; i < 8; i++) l2keep[h][i] = pool4_h2(p1keep[2 * i], p1[2 * i], p1keep[2 * i + 1], p1[2 * i + 1]);
-                if (live) {
-                  uint4* dst = reinterpret_cast<uint4*>(lvl2 + (pix * H4 + (nt * 2 + h)) * W4);
-                  dst[0] = make_uint4(l2keep[h][0], l2keep[h][1], l2keep[h][2], l2keep[h][3]);
-                  dst[1] = make_uint4(l2keep[h][4], l2keep[h][5], l2keep[h][6], l2keep[h][7]);
-                }
-              }
+              for (int i = 0; i < 16; i++) p1keep[i] = p1[i];
             } else {
 #pragma unroll
-              for (int i = 0; i < 32; i++) prev[i] = cur[i];
+              for (int i = 0; i < 8; i++) l2[i] = pool4_h2(p1keep[2 * i], p1[2 * i], p1keep[2 * i + 1], p1[2 * i + 1]);
+              if (live) {
+                uint4* dst = reinterpret_cast<uint4*>(lvl2 + (pix * H4 + (nt * 2 + h)) * W4);
+                dst[0] = make_uint4(l2[0], l2[1], l2[2], l2[3]);
+                dst[1] = make_uint4(l2[4], l2[5], l2[6], l2[7]);
+              }
             }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; i++) prev[i] = cur[i];
           }
         }
-        if (live) {
-          uint4* dst = reinterpret_cast<uint4*>(lvl3 + (pix * H8 + nt) * W8);
-          dst[0] = make_uint4(pool4_h2(l2keep[0][0], l2keep[1][0], l2keep[0][1], l2keep[1][1]),
-                              pool4_h2(l2keep[0][2], l2keep[1][2], l2keep[0][3], l2keep[1][3]),
-                              pool4_h2(l2keep[0][4], l2keep[1][4], l2keep[0][5], l2keep[1][5]),
-                              pool4_h2(l2keep[0][6], l2keep[1][6], l2keep[0][7], l2keep[1][7]));
+        // level 3: one 8x8 window = upper half (group 0) over lower half (group 1)
+        const int xs = t & 1;
+        uint4* xp = reinterpret_cast<uint4*>(xch + xs * (Smem::kXchBytes / 4) + row_in_tile * 8);
+        if (g == 0) {
+          if (t >= 2) mbar_wait(x_empty + xs, ((t >> 1) - 1) & 1);
+          xp[0] = make_uint4(l2[0], l2[1], l2[2], l2[3]);
+          xp[1] = make_uint4(l2[4], l2[5], l2[6], l2[7]);
+          mbar_arrive(x_full + xs);
+        } else {
+          mbar_wait(x_full + xs, (t >> 1) & 1);
+          const uint4 u0 = xp[0], u1 = xp[1];
+          mbar_arrive(x_empty + xs);
+          if (live) {
+            uint4* dst = reinterpret_cast<uint4*>(lvl3 + (pix * H8 + nt) * W8);
+            dst[0] = make_uint4(pool4_h2(u0.x, l2[0], u0.y, l2[1]), pool4_h2(u0.z, l2[2], u0.w, l2[3]),
+                                pool4_h2(u1.x, l2[4], u1.y, l2[5]), pool4_h2(u1.z, l2[6], u1.w, l2[7]));
+          }
         }
       }
-      if (threadIdx.x == 0) bulk_wait_read<0>();
+      if (leader) bulk_wait_read<0>();
     } else
     for (int t = 0; t < T; t++) {
       const int m = t * kTileM + warp * 32 + lane;
@@ -378,7 +404,7 @@ corr_build_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == kProducer) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
   }
 }
@@ -434,7 +460,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
     attr = true;
   }
   ProfScope ps(DROID_PROF_CORR_GEMM, st);
-  DROID_LAUNCH corr_build_kernel<W><<<dim3(H / 8, B), kThreads, Smem::kBytes, st>>>(
+  DROID_LAUNCH corr_build_kernel<W><<<dim3(H / 8, B), W == 64 ? kThreads64 : kThreads, Smem::kBytes, st>>>(
       ta, tb, to, (__half*)l0, (__half*)l1, (__half*)l2, (__half*)l3, H, H * W);
   return check_launch();
 }
