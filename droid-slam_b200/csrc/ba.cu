@@ -555,7 +555,9 @@ __global__ void __launch_bounds__(128) ba_pack_kernel(double* __restrict__ A, do
 
 __global__ void ba_edge_pose_kernel(const float* __restrict__ poses, const int64_t* __restrict__ ii,
                                     const int64_t* __restrict__ jj, int n_edges, int nbuf,
-                                    float* __restrict__ gij) {
+                                    float* __restrict__ gij, double* __restrict__ zero, int nzero) {
+  // frontend-sized systems: the few thousand doubles of the reduced system are cleared here instead of by a memset
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < nzero; k += gridDim.x * blockDim.x) zero[k] = 0.0;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n_edges) return;
   const long long i = ii[e], j = jj[e];
@@ -574,11 +576,9 @@ __global__ void ba_edge_pose_kernel(const float* __restrict__ poses, const int64
 // u_e = N_e^T dx[source pose] + dx[target pose]: what the depth back-substitution multiplies E_j of the edge with
 // (E_i^T dx_i = (N E_j)^T dx_i = E_j^T N^T dx_i).  A term is 0 when its pose is not updated or is the first
 // optimised pose (:1105).
-__global__ void ba_edge_y_kernel(const float* __restrict__ gij, const int64_t* __restrict__ ii,
-                                 const int64_t* __restrict__ jj, int n_edges,
-                                 int nbuf, const float* __restrict__ dx, int t0, int P, float* __restrict__ ey) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n_edges) return;
+__device__ __forceinline__ void edge_y_body(int e, const float* __restrict__ gij, const int64_t* __restrict__ ii,
+                                            const int64_t* __restrict__ jj, int nbuf, const float* dx, int t0, int P,
+                                            float* __restrict__ ey) {
   const long long i = ii[e], j = jj[e];
   const int pk = (i < 0 || i >= nbuf) ? -1 : (int)i - t0;
   const int pj = (j < 0 || j >= nbuf) ? -1 : (int)j - t0;
@@ -600,6 +600,14 @@ __global__ void ba_edge_y_kernel(const float* __restrict__ gij, const int64_t* _
 #pragma unroll
   for (int a = 0; a < 6; a++) o[a] = y[a];
   o[6] = 0.f; o[7] = 0.f;
+}
+
+__global__ void ba_edge_y_kernel(const float* __restrict__ gij, const int64_t* __restrict__ ii,
+                                 const int64_t* __restrict__ jj, int n_edges,
+                                 int nbuf, const float* __restrict__ dx, int t0, int P, float* __restrict__ ey) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_edges) return;
+  edge_y_body(e, gij, ii, jj, nbuf, dx, t0, P, ey);
 }
 
 __device__ __forceinline__ SE3 load_gij(const float* __restrict__ gij, int e) {
@@ -1155,12 +1163,10 @@ __global__ void ba_damp_kernel(double* __restrict__ A, int n6, float lm, float e
 }
 
 // dx = float(x) or 0 when the factorisation failed (:1202-1210); then T <- Exp(dx) T (:898-931)
-__global__ void ba_pose_update_kernel(float* __restrict__ poses, const double* __restrict__ x,
-                                      int* __restrict__ status, const int* __restrict__ info,
-                                      float* __restrict__ dx, float* __restrict__ dx_out, int t0,
-                                      int P, int apply, const int* __restrict__ ppos) {
-  const int kk = blockIdx.x * blockDim.x + threadIdx.x;
-  if (kk >= P) return;
+__device__ __forceinline__ void pose_update_body(int kk, float* __restrict__ poses, const double* __restrict__ x,
+                                                 int* __restrict__ status, const int* __restrict__ info,
+                                                 float* dx, float* __restrict__ dx_out, int t0, int apply,
+                                                 const int* __restrict__ ppos) {
   const bool failed = (*info != 0);
   if (failed && kk == 0) atomicOr(&status[0], DROID_BA_STATUS_CHOL_FAILED);
   float xi[6];
@@ -1178,6 +1184,27 @@ __global__ void ba_pose_update_kernel(float* __restrict__ poses, const double* _
   retr_se3(xi, t, q, t1, q1);
   p[0] = t1[0]; p[1] = t1[1]; p[2] = t1[2];
   p[3] = q1[0]; p[4] = q1[1]; p[5] = q1[2]; p[6] = q1[3];
+}
+
+__global__ void ba_pose_update_kernel(float* __restrict__ poses, const double* __restrict__ x,
+                                      int* __restrict__ status, const int* __restrict__ info,
+                                      float* __restrict__ dx, float* __restrict__ dx_out, int t0,
+                                      int P, int apply, const int* __restrict__ ppos) {
+  const int kk = blockIdx.x * blockDim.x + threadIdx.x;
+  if (kk >= P) return;
+  pose_update_body(kk, poses, x, status, info, dx, dx_out, t0, apply, ppos);
+}
+
+// frontend-sized systems (one CTA): dx of every pose, then the per-edge vectors of the depth back-substitution
+__global__ void __launch_bounds__(256) ba_small_update_kernel(float* __restrict__ poses, const double* __restrict__ x,
+                                                              int* __restrict__ status, const int* __restrict__ info,
+                                                              float* dx, float* __restrict__ dx_out, int t0, int P,
+                                                              const float* __restrict__ gij, const int64_t* __restrict__ ii,
+                                                              const int64_t* __restrict__ jj, int n_edges, int nbuf,
+                                                              float* __restrict__ ey) {
+  for (int kk = threadIdx.x; kk < P; kk += 256) pose_update_body(kk, poses, x, status, info, dx, dx_out, t0, 0, nullptr);
+  __syncthreads();
+  for (int e = threadIdx.x; e < n_edges; e += 256) edge_y_body(e, gij, ii, jj, nbuf, dx, t0, P, ey);
 }
 
 __global__ void ba_pose_apply_kernel(float* __restrict__ poses, const float* __restrict__ dx, int t0,
@@ -1248,6 +1275,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   if (P == 0 || p->iterations == 0) return DROID_OK;
   // large systems: fill-reducing order + row envelope for the factorisation (small ones are solved by one CTA)
   const bool ordered = n6 > kCholSmallMax && p->n_edges > 0;
+  const bool small = n6 <= kCholSmallMax;        // frontend / trajectory-filler windows: one-CTA solver
   const int* ppos = ordered ? w.ppos : nullptr;
   const int* first = ordered ? w.first : nullptr;
   // long trajectories: the order also cuts the system into up to kBaMaxChains decoupled chains + a separator.  The
@@ -1323,11 +1351,20 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   for (int itr = 0; itr < p->iterations; itr++) {
     {
       ProfScope ps(DROID_PROF_BA_PREP, st);
-      if (p->n_edges > 0) {
+      // frontend-sized systems are launch-bound (a dozen small kernels per iteration): the system is cleared by the
+      // edge-pose kernel, damping / info live in the one-CTA solver, dx and the per-edge vectors share a kernel and the
+      // Schur kernels stay on one stream -- 5 launches and 4 event operations less per iteration
+      const size_t nsys = (size_t)n6 * n6 + n6;
+      if (small && p->n_edges > 0) {
         DROID_LAUNCH ba_edge_pose_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(poses, ii, jj, p->n_edges,
-                                                                                   p->nbuf, w.gij);
+                                                                                   p->nbuf, w.gij, w.A, (int)nsys);
+      } else {
+        if (p->n_edges > 0) {
+          DROID_LAUNCH ba_edge_pose_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(poses, ii, jj, p->n_edges,
+                                                                                     p->nbuf, w.gij, nullptr, 0);
+        }
+        cudaMemsetAsync(w.A, 0, nsys * sizeof(double), st);
       }
-      cudaMemsetAsync(w.A, 0, ((size_t)n6 * n6 + n6) * sizeof(double), st);
     }
     if (p->n_edges > 0 && p->n_eta > 0) {
       {
@@ -1344,6 +1381,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
         // CTAs start first and the tensor-core CTAs fill the SMs around them instead of waiting for its tail.
         static const bool tc_on = []() { const char* e = getenv("DROID_SCHUR_TC"); return !(e && e[0] == '0'); }();
         const bool use_tc = tc_on && (HW % 4 == 0);      // the tensor-core builders move 4 pixels per 16-byte access
+        const bool fork = use_tc && !small;              // second stream for the CUDA-core kernel (large systems only)
         static cudaStream_t s2 = nullptr;
         static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
         static int s2_dev = -1;
@@ -1356,7 +1394,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
           s2_dev = dev;
         }
         cudaStream_t so = st;
-        if (use_tc) {
+        if (fork) {
           cudaEventRecord(ev_fork, st);
           cudaStreamWaitEvent(s2, ev_fork, 0);
           so = s2;
@@ -1365,11 +1403,11 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
             w.ejc, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q,
             w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, use_tc ? kSchurTcMaxDeg + 1 : 0);
         if (use_tc) {
-          cudaEventRecord(ev_join, s2);
+          if (fork) cudaEventRecord(ev_join, s2);
           if (launch_schur_tc(w.ejc, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
                               w.A, bvec, HW, p->wd, slab_tc, S_tc, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, st))
             return DROID_ERR_CUDA;
-          cudaStreamWaitEvent(st, ev_join, 0);
+          if (fork) cudaStreamWaitEvent(st, ev_join, 0);
         }
       }
     }
@@ -1388,9 +1426,14 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     }
     {
       ProfScope ps(DROID_PROF_BA_SOLVE, st);
-      DROID_LAUNCH ba_damp_kernel<<<(n6 + 127) / 128, 128, 0, st>>>(w.A, n6, p->lm, p->ep);
-      int rc = droid_chol_solve_chains_f64(w.A, bvec, n6, first, nchains, chain_end, w.status + 2, w.chol, chol_bytes,
-                                           stream);
+      int rc;
+      if (small) {
+        rc = launch_chol_small_damped(w.A, n6, p->lm, p->ep, w.status + 2, st);
+      } else {
+        DROID_LAUNCH ba_damp_kernel<<<(n6 + 127) / 128, 128, 0, st>>>(w.A, n6, p->lm, p->ep);
+        rc = droid_chol_solve_chains_f64(w.A, bvec, n6, first, nchains, chain_end, w.status + 2, w.chol, chol_bytes,
+                                         stream);
+      }
       if (rc != DROID_OK) return rc;
     }
     ProfScope ps(DROID_PROF_BA_UPDATE, st);
@@ -1398,10 +1441,15 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
       DROID_LAUNCH ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
                                                                           w.dx, dx_out, p->t0, P, 1, ppos);
     } else {
-      DROID_LAUNCH ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
-                                                                          w.dx, dx_out, p->t0, P, 0, ppos);
-      DROID_LAUNCH ba_edge_y_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(w.gij, ii, jj, p->n_edges, p->nbuf,
-                                                                              w.dx, p->t0, P, w.ey);
+      if (small) {
+        DROID_LAUNCH ba_small_update_kernel<<<1, 256, 0, st>>>(poses, bvec, w.status, w.status + 2, w.dx, dx_out, p->t0, P,
+                                                              w.gij, ii, jj, p->n_edges, p->nbuf, w.ey);
+      } else {
+        DROID_LAUNCH ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
+                                                                            w.dx, dx_out, p->t0, P, 0, ppos);
+        DROID_LAUNCH ba_edge_y_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(w.gij, ii, jj, p->n_edges, p->nbuf,
+                                                                                w.dx, p->t0, P, w.ey);
+      }
       DROID_LAUNCH ba_dz_kernel<<<dim3((HW + kThreads - 1) / kThreads, p->n_eta), kThreads, 0, st>>>(
           disps, w.ejc, w.ey, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W, dz_out, HW, p->n_eta, frame_lo, frame_hi);
       DROID_LAUNCH ba_pose_apply_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, w.dx, p->t0, P);

@@ -50,8 +50,11 @@ __device__ __forceinline__ double shfl_f64(double v, int src) {
                           __shfl_sync(0xffffffffu, __double2loint(v), src));
 }
 
+// damp != 0: the Levenberg-Marquardt damping of ba (diag += ep + lm * diag, src/droid_kernels.cu:1197) is applied to the
+// copy in shared memory and *info is written in either case (0 / 1), so that ba needs neither a damping kernel nor a
+// memset in front of the solve of a frontend-sized system.
 __global__ void __launch_bounds__(160) chol_small_kernel(double* __restrict__ A, int n,
-                                                         int* __restrict__ info) {
+                                                         int* __restrict__ info, int damp, float lm, float ep) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int R = n + 1;
   const int ld = chol_small_ld(n);
@@ -72,6 +75,13 @@ __global__ void __launch_bounds__(160) chol_small_kernel(double* __restrict__ A,
   asm volatile("cp.async.commit_group;" ::: "memory");
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
+  if (damp) {
+    for (int r = tid; r < n; r += blockDim.x) {
+      double* d = S + r * ld + r;
+      *d += (double)ep + (double)lm * (*d);
+    }
+    __syncthreads();
+  }
 
   const bool is_rhs = tid + 0 == n;  // re-evaluated per block below (row index changes with c0)
   (void)is_rhs;
@@ -177,7 +187,7 @@ __global__ void __launch_bounds__(160) chol_small_kernel(double* __restrict__ A,
     }
   }
   if (tid < n) A[(size_t)n * n + tid] = x;
-  if (tid == 0 && fail) *info = 1;
+  if (tid == 0 && (fail || damp)) *info = fail ? 1 : 0;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -945,6 +955,18 @@ extern "C" int droid_chol_solve_env_f64(double* A, double* b, int n, const int* 
   return droid_chol_solve_chains_f64(A, b, n, first_dev, 0, nullptr, info_dev, workspace, workspace_bytes, stream);
 }
 
+// frontend-sized systems of ba: damping + factorisation + both sweeps + info in ONE launch (no memset, no damping kernel)
+int droid::launch_chol_small_damped(double* A, int n, float lm, float ep, int* info_dev, cudaStream_t st) {
+  if (n <= 0 || n > kSmallMax) return DROID_ERR_INVALID_ARGUMENT;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmemMax);
+    attr_set = true;
+  }
+  DROID_LAUNCH chol_small_kernel<<<1, ((n + 1 + 31) / 32) * 32, chol_small_smem(n), st>>>(A, n, info_dev, 1, lm, ep);
+  return check_launch();
+}
+
 namespace {
 struct ChainCtx {
   cudaStream_t main = nullptr, side = nullptr;
@@ -980,7 +1002,7 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
       attr_set = true;
     }
     const size_t smem = chol_small_smem(n);
-    DROID_LAUNCH chol_small_kernel<<<1, ((n + 1 + 31) / 32) * 32, smem, st>>>(A, n, info_dev);
+    DROID_LAUNCH chol_small_kernel<<<1, ((n + 1 + 31) / 32) * 32, smem, st>>>(A, n, info_dev, 0, 0.f, 0.f);
     return check_launch();
   }
   static bool attr2 = false;
