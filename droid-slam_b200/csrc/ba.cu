@@ -1202,25 +1202,9 @@ __global__ void __launch_bounds__(256) ba_small_update_kernel(float* __restrict_
                                                               const float* __restrict__ gij, const int64_t* __restrict__ ii,
                                                               const int64_t* __restrict__ jj, int n_edges, int nbuf,
                                                               float* __restrict__ ey) {
-  for (int kk = threadIdx.x; kk < P; kk += 256) pose_update_body(kk, poses, x, status, info, dx, dx_out, t0, 0, nullptr);
+  for (int kk = threadIdx.x; kk < P; kk += 256) pose_update_body(kk, poses, x, status, info, dx, dx_out, t0, 1, nullptr);
   __syncthreads();
   for (int e = threadIdx.x; e < n_edges; e += 256) edge_y_body(e, gij, ii, jj, nbuf, dx, t0, P, ey);
-}
-
-__global__ void ba_pose_apply_kernel(float* __restrict__ poses, const float* __restrict__ dx, int t0,
-                                     int P) {
-  const int kk = blockIdx.x * blockDim.x + threadIdx.x;
-  if (kk >= P) return;
-  float xi[6];
-#pragma unroll
-  for (int n = 0; n < 6; n++) xi[n] = dx[6 * kk + n];
-  float* p = poses + 7 * (size_t)(t0 + kk);
-  const float t[3] = {p[0], p[1], p[2]};
-  const float q[4] = {p[3], p[4], p[5], p[6]};
-  float t1[3], q1[4];
-  retr_se3(xi, t, q, t1, q1);
-  p[0] = t1[0]; p[1] = t1[1]; p[2] = t1[2];
-  p[3] = q1[0]; p[4] = q1[1]; p[5] = q1[2]; p[6] = q1[3];
 }
 
 }  // namespace droid
@@ -1446,13 +1430,14 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
                                                               w.gij, ii, jj, p->n_edges, p->nbuf, w.ey);
       } else {
         DROID_LAUNCH ba_pose_update_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, bvec, w.status, w.status + 2,
-                                                                            w.dx, dx_out, p->t0, P, 0, ppos);
+                                                                            w.dx, dx_out, p->t0, P, 1, ppos);
         DROID_LAUNCH ba_edge_y_kernel<<<(p->n_edges + 127) / 128, 128, 0, st>>>(w.gij, ii, jj, p->n_edges, p->nbuf,
                                                                                 w.dx, p->t0, P, w.ey);
       }
       DROID_LAUNCH ba_dz_kernel<<<dim3((HW + kThreads - 1) / kThreads, p->n_eta), kThreads, 0, st>>>(
           disps, w.ejc, w.ey, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W, dz_out, HW, p->n_eta, frame_lo, frame_hi);
-      DROID_LAUNCH ba_pose_apply_kernel<<<(P + 127) / 128, 128, 0, st>>>(poses, w.dx, p->t0, P);
+      // (the poses were retracted together with dx: the depth update reads the packed E_j and the per-edge vectors of
+      //  the OLD linearisation point, not the poses, so nothing has to wait for it any more)
     }
     if (check_launch()) return DROID_ERR_CUDA;
   }
