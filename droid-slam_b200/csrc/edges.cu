@@ -86,22 +86,30 @@ __global__ void __launch_bounds__(32) prox_greedy_kernel(const float* __restrict
   const int side = 2 * nms + 1;
   int count = mandatory;
   bool stop = false;
-  // the (distance, pair) of the next batch are fetched while this one is worked on; only the suppression flags, which
-  // this batch may still change, have to be read at the last moment
-  float nkey = lane < n ? keys[lane] : __int_as_float(0x7f800000);
-  int nidx = lane < n ? vals[lane] : 0;
+  const float kInf = __int_as_float(0x7f800000);
+  // Software pipeline over batches of 32 sorted candidates: while batch b is walked, the (distance, pair) of batch b+2
+  // and the suppression flag of batch b+1 are already on their way.  A flag fetched that early cannot know about the
+  // candidates accepted while batch b is walked, so every acceptance is also tested arithmetically against the lane's
+  // candidate of batch b+1 (like against the other candidates of batch b itself); acceptances of older batches reach
+  // it through the byte map, which is fenced at the end of every batch.
+  auto cand = [&](int k, float& key, int& idx) {
+    key = k < n ? keys[k] : kInf;
+    idx = k < n ? vals[k] : 0;
+  };
+  float key0, key1, key2;
+  int idx0, idx1, idx2;
+  cand(lane, key0, idx0);
+  cand(32 + lane, key1, idx1);
+  unsigned char sup0 = (lane < n && !(key0 > thresh)) ? __ldcg(sup + idx0) : (unsigned char)0;
   for (int base = 0; base < n && !stop; base += 32) {
     const int k = base + lane;
-    const float key = nkey;
-    const int idx = nidx;
-    {
-      const int kn = k + 32;
-      nkey = kn < n ? keys[kn] : __int_as_float(0x7f800000);
-      nidx = kn < n ? vals[kn] : 0;
-    }
-    const int ci = t0 + idx / W, cj = t1 + idx % W;
-    const bool close = k < n && !(key > thresh);                 // `if d[k] > thresh: continue`
-    bool alive = close && __ldcg(sup + idx) == 0;
+    cand(k + 64, key2, idx2);
+    const bool close1 = (k + 32) < n && !(key1 > thresh);
+    unsigned char sup1 = close1 ? __ldcg(sup + idx1) : (unsigned char)0;     // consumed in the next iteration
+    const int ci = t0 + idx0 / W, cj = t1 + idx0 % W;
+    const int ni = t0 + idx1 / W, nj = t1 + idx1 % W;
+    const bool close = k < n && !(key0 > thresh);                // `if d[k] > thresh: continue`
+    bool alive = close && sup0 == 0;
     if (__ballot_sync(0xffffffffu, !close) != 0u) stop = true;   // sorted: nothing behind this batch can pass
     unsigned live;
     while ((live = __ballot_sync(0xffffffffu, alive)) != 0u) {
@@ -115,10 +123,11 @@ __global__ void __launch_bounds__(32) prox_greedy_kernel(const float* __restrict
       }
       count += 2;
       const int r = nms_radius(i, j, nms);
-      // candidates of this batch (their flags were read before this acceptance) ...
-      if (alive && abs(ci - i) <= nms && abs(cj - j) <= nms && abs(ci - i) + abs(cj - j) <= r) alive = false;
+      // candidates of this batch and of the next one (their flags were read before this acceptance) ...
+      if (alive && abs(ci - i) + abs(cj - j) <= r) alive = false;
+      if (abs(ni - i) + abs(nj - j) <= r) sup1 = 1;
       if (lane == l) alive = false;
-      // ... and everything behind it
+      // ... and everything behind them
       for (int c = lane; c < side * side; c += 32) {
         const int di = c / side - nms, dj = c % side - nms;
         if (abs(di) + abs(dj) > r) continue;
@@ -128,6 +137,8 @@ __global__ void __launch_bounds__(32) prox_greedy_kernel(const float* __restrict
     }
     __threadfence_block();
     __syncwarp();
+    key0 = key1; idx0 = idx1; sup0 = sup1;
+    key1 = key2; idx1 = idx2;
   }
   if (lane == 0) *out_count = count;
 }
