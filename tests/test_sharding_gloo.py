@@ -88,3 +88,21 @@ def test_shard_bounds_balance_the_work(backends):
         share = cost.sum() / world
         for r in range(world):
             assert cost[b[r]:b[r + 1]].sum() <= share + cost.max() + 1e-9
+
+
+def test_shard_edge_rows_index_the_ranks_own_rows(backends):
+    """A rank that holds only the targets / weights rows of its own edges: edge_row maps every edge of the shard to
+    its position among the shard's edges, in edge order; together the shards cover every edge exactly once."""
+    rng = np.random.default_rng(2)
+    nbuf, ne, world = 40, 500, 4
+    ii = torch.from_numpy(rng.integers(0, nbuf, size=ne))
+    bounds = backends.shard_bounds(ii, nbuf, world)
+    seen = torch.zeros(ne, dtype=torch.int32)
+    for r in range(world):
+        lo, hi = bounds[r], bounds[r + 1]
+        mask = backends.shard_edges(ii, lo, hi)
+        rows, count = backends.shard_edge_rows(ii, lo, hi)
+        assert rows.dtype == torch.int32 and count == int(mask.sum())
+        assert torch.equal(rows[mask].long(), torch.arange(count))          # dense, ascending edge order
+        seen += mask.int()
+    assert torch.equal(seen, torch.ones(ne, dtype=torch.int32))
