@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-frames", type=int, default=64, help="keyframes of the bounded CPU-baseline sample")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the live comparison with the reference extension")
     ap.add_argument("--no-extra", action="store_true", help="skip the corr-lookup / frontend-window side metrics")
     return ap.parse_args()
 
@@ -324,6 +325,7 @@ def run_b200(args, world, rank, local):
                           "sensor depths / eta, the rows of ITS OWN edges and source frames; h2d_bytes_per_step is the "
                           "sum over ranks") if sharded else "all inputs"}
 
+    parity = parity_check(B, p, d, poses0, disps0, dev, world, rank, bounds) if not args.no_parity else None
     if rank != 0:
         return None
     peaks = {}
@@ -397,8 +399,10 @@ def run_b200(args, world, rank, local):
                    "parallelism": "1 GPU" if world == 1 else "work-balanced source-frame shards x%d + NCCL all-reduce of the packed reduced camera system" % world,
                    "l2": "inputs>L2 (855 MB of targets+weights per pass vs 126 MB L2)"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "phases": per_phase,
-        "ba_status": status, "impl": "b200",
+        "ba_status": status, "impl": "b200", "parity": parity,
     }
+    if status != 0:
+        line["error"] = "device-side BA status word is %d (see DROID_BA_STATUS_* in include/droid_b200.h)" % status
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)
     if world == 1 and not args.no_extra:
@@ -407,6 +411,48 @@ def run_b200(args, world, rank, local):
         except Exception as ex:                                    # noqa: BLE001
             line["extra"] = {"error": repr(ex)}
     return line
+
+
+def parity_check(B, p, d, poses0, disps0, dev, world, rank, bounds):
+    """Outside the timed region: the timed configuration itself (same inputs, ITERS iterations, same LM / EP) against
+    the UNMODIFIED reference extension (oracle/_ref) when it is loadable -- relative errors max|a-b| / max|b| of dx,
+    dz, poses and depth maps -- and, under torchrun, ba_sharded against single-GPU ba on rank 0."""
+    t0, t1 = p["t0"], p["t1"]
+    rel = lambda a, b: float((a.double() - b.double()).abs().max() / b.double().abs().max().clamp(min=1e-30))  # noqa: E731
+
+    def call(fn, **kw):
+        po, di = poses0.clone(), disps0.clone()
+        dx, dz = fn(po, di, d["intrinsics"], d["disps_sens"], d["targets"], d["weights"], d["eta"], d["ii"], d["jj"],
+                    t0, t1, ITERS, LM, EP, False, **kw)
+        torch.cuda.synchronize()
+        return po, di, dx, dz.reshape(-1)
+
+    out = {"tolerance": "north_star: <= 1e-4 relative per Gauss-Newton iteration (tests/test_gpu_parity.py asserts it per "
+                        "iteration at this size); here ONE call of %d iterations, where iteration 2 also carries the "
+                        "1e-6 state difference left by iteration 1" % ITERS}
+    mine = call(B.ba_sharded, bounds=bounds) if world > 1 else call(B.ba)
+    if world > 1:
+        if rank == 0:
+            single = call(B.ba)
+            out["sharded_vs_single_gpu"] = {"dx": rel(mine[2], single[2]), "dz": rel(mine[3], single[3]),
+                                            "poses": rel(mine[0], single[0]), "disps": rel(mine[1], single[1])}
+            mine = single
+    if rank != 0:
+        return None
+    try:
+        import droid_backends_ref as R
+        ref = call(R.ba)
+        out["vs_reference_extension"] = {"dx": rel(mine[2], ref[2]), "dz": rel(mine[3], ref[3]),
+                                         "poses": rel(mine[0], ref[0]), "disps": rel(mine[1], ref[1])}
+        v = out["vs_reference_extension"]
+        out["ok"] = bool(v["poses"] <= 1e-5 and v["disps"] <= 1e-5 and v["dx"] <= 5e-4 and v["dz"] <= 5e-4)
+    except Exception as ex:                                        # noqa: BLE001
+        out["vs_reference_extension"] = {"unavailable": repr(ex)}
+        out["ok"] = None
+    if "sharded_vs_single_gpu" in out:
+        v = out["sharded_vs_single_gpu"]
+        out["sharded_ok"] = bool(v["poses"] <= 1e-5 and v["disps"] <= 1e-5 and v["dx"] <= 5e-4)
+    return out
 
 
 def extra_metrics(dev, hbm_peak, peaks):
@@ -534,6 +580,10 @@ def extra_metrics(dev, hbm_peak, peaks):
                                   "workload": "1000 keyframes, 10^6 candidate pairs, rad 2, nms 3, thresh 22 (backend settings)"}
     except Exception as ex:                                        # noqa: BLE001
         out["proximity_edges"] = {"error": repr(ex)}
+    try:
+        out.update(altcorr_and_geometry_metrics(dev, hbm_peak, timeit))
+    except Exception as ex:                                        # noqa: BLE001
+        out["altcorr_geometry_error"] = repr(ex)
     p = synth.make_ba_problem("C3")
     d = {k: torch.from_numpy(np.ascontiguousarray(p[k])).to(dev) for k in KEYS}
     p0, d0 = d["poses"].clone(), d["disps"].clone()
@@ -551,6 +601,100 @@ def extra_metrics(dev, hbm_peak, peaks):
         out["frontend_ba_reference_ext"] = {"us_per_call": t * 1e6, "calls_per_s": 1.0 / t}
     except Exception:
         pass
+    return out
+
+
+def altcorr_and_geometry_metrics(dev, hbm_peak, timeit):
+    """The other half of BASELINE configs[3] and the geometry operators, L2 flushed between calls, the unmodified
+    reference extension beside every figure where it is loadable:
+      * alt-corr on ONE chunk of the backend's update_lowmem loop (droid_slam/factor_graph.py:262-270): the edges of
+        8 consecutive source frames of a 250-keyframe graph (~160), 40x64, C = 128, 4 pyramid levels, radius 3 --
+        the drop-in signature (float32 gathered copies, modules/corr.py:113-120) and the indexed float16-pyramid
+        extension; flops = B HW 64 C 2 per level, bytes per SURVEY 8(d);
+      * frame_distance on the 10^6 pairs of a 1000-keyframe video (depth_video.py:160-170), pairs/s;
+      * projmap / iproj / depth_filter, one line each."""
+    import droid_backends as B
+    import synth
+    try:
+        import droid_backends_ref as R
+    except Exception:                                              # noqa: BLE001
+        R = None
+    out = {}
+    pr = synth.make_ba_problem("C4", n_frames=250, knn=16)
+    H, W, C, r = pr["ht"], pr["wd"], 128, 3
+    HW = H * W
+    sel = np.nonzero((pr["ii"] >= 120) & (pr["ii"] < 128))[0]
+    ii = torch.from_numpy(pr["ii"][sel]).to(dev)
+    jj = torch.from_numpy(pr["jj"][sel]).to(dev)
+    Bn = len(sel)
+    g = torch.Generator(device="cpu").manual_seed(5)
+    fm = (torch.randn((250, C, H, W), generator=g) * 0.5).to(dev)                # [frames, C, H, W] like video.fmaps / 4
+    pyr = []
+    f = fm
+    for l in range(4):
+        pyr.append(f.permute(0, 2, 3, 1).contiguous().half())
+        f = torch.nn.functional.avg_pool2d(f, 2, stride=2)
+    del fm, f
+    coords = torch.from_numpy(np.ascontiguousarray(pr["targets"][sel].transpose(0, 2, 3, 1))).to(dev)[:, None].contiguous()
+    cl = [(coords / 2 ** l).contiguous() for l in range(4)]
+    f1 = pyr[0][ii].float().contiguous()
+    f2 = [pyr[l][jj].float().contiguous() for l in range(4)]
+    flops = sum(Bn * HW * 64 * C * 2 for l in range(4))
+    by32 = sum(Bn * (HW + (H >> l) * (W >> l)) * C * 4 + Bn * HW * 8 + Bn * 49 * HW * 4 for l in range(4))
+    by16 = sum(Bn * (HW + (H >> l) * (W >> l)) * C * 2 + Bn * HW * 8 + Bn * 49 * HW * 4 for l in range(4))
+
+    def rec(t, by):
+        return {"us": t * 1e6, "GFLOPs": flops / t / 1e9, "GBps": by / t / 1e9, "hbm_frac": by / t / 1e9 / hbm_peak,
+                "algorithmic_bytes": int(by), "flops": int(flops)}
+    wl = "%d edges (8 source frames of a 250-keyframe backend graph), %dx%d, C=128, 4 levels, radius 3" % (Bn, H, W)
+    t = timeit(lambda: [B.altcorr_forward(f1, f2[l], cl[l], r) for l in range(4)], n=10)
+    out["altcorr_forward"] = dict(rec(t, by32), workload=wl + "; drop-in signature, float32 gathered copies, 4 calls")
+    t = timeit(lambda: [B.altcorr_forward_indexed(pyr[0], pyr[l], ii, jj, cl[l], r) for l in range(4)], n=10)
+    out["altcorr_forward_indexed"] = dict(rec(t, by16), workload=wl + "; float16 pyramid indexed by (ii, jj), no gathered copies, 4 calls")
+    t = timeit(lambda: [B.altcorr_forward(pyr[0][ii].float(), pyr[l][jj].float(), cl[l], r) for l in range(4)], n=10)
+    out["altcorr_forward_with_gathers"] = {"us": t * 1e6, "workload": wl + "; as AltCorrBlock.corr_fn calls it: pyramid[l][:, jj].float() gathers + the op"}
+    if R is not None:
+        t = timeit(lambda: [R.altcorr_forward(f1, f2[l], cl[l], r) for l in range(4)], n=5)
+        out["altcorr_forward_reference_ext"] = rec(t, by32)
+        out["altcorr_forward"]["speedup_vs_reference_ext"] = out["altcorr_forward_reference_ext"]["us"] / out["altcorr_forward"]["us"]
+        out["altcorr_forward_indexed"]["speedup_vs_reference_ext"] = out["altcorr_forward_reference_ext"]["us"] / out["altcorr_forward_indexed"]["us"]
+    del f1, f2, pyr, coords, cl
+
+    # ---- frame_distance: every pair of a 1000-keyframe video, one direction (the caller averages two calls)
+    pk = synth.make_ba_problem("C4", n_frames=1000, knn=2)
+    n = 1000
+    P, D, K = (torch.from_numpy(pk[k]).to(dev) for k in ("gt_poses", "gt_disps", "intrinsics"))
+    a, b = torch.meshgrid(torch.arange(n, device=dev), torch.arange(n, device=dev), indexing="ij")
+    a, b = a.reshape(-1).contiguous(), b.reshape(-1).contiguous()
+    t = timeit(lambda: B.frame_distance(P, D, K, a, b, 0.3), n=5, warm=1)
+    fb = n * pk["ht"] * pk["wd"] * 4 + a.numel() * 20
+    out["frame_distance"] = {"us": t * 1e6, "pairs_per_s": a.numel() / t, "pairs": int(a.numel()),
+                             "pixel_pairs_per_s": a.numel() * pk["ht"] * pk["wd"] / t, "algorithmic_bytes": int(fb),
+                             "workload": "10^6 pairs (meshgrid of 1000 keyframes), 40x64, beta 0.3, one direction",
+                             "bound": "ALU / L2 (every pair re-projects 2560 pixels twice; depth maps are L2 resident)"}
+    if R is not None:
+        t2 = timeit(lambda: R.frame_distance(P, D, K, a, b, 0.3), n=3, warm=1)
+        out["frame_distance_reference_ext"] = {"us": t2 * 1e6, "pairs_per_s": a.numel() / t2}
+        out["frame_distance"]["speedup_vs_reference_ext"] = t2 / t
+        out["frame_distance"]["bit_exact_vs_reference_ext"] = bool(torch.equal(B.frame_distance(P, D, K, a, b, 0.3),
+                                                                                R.frame_distance(P, D, K, a, b, 0.3)))
+    # ---- projmap / iproj / depth_filter
+    ei = torch.from_numpy(pr["ii"]).to(dev); ej = torch.from_numpy(pr["jj"]).to(dev)
+    ne = ei.numel()
+    ix = torch.arange(n, device=dev)
+    th = torch.full((n,), 0.05, device=dev)
+    ops = {
+        "projmap": (lambda M: M.projmap(P, D, K, ei, ej), ne * HW * (4 + 12 + 4), "%d edges, 40x64: depth in, coords[3] + valid out" % ne),
+        "iproj": (lambda M: M.iproj(P, D, K), n * HW * (4 + 12), "1000 frames, 40x64: depth in, points[3] out"),
+        "depth_filter": (lambda M: M.depth_filter(P, D, K, ix, th), n * HW * (4 + 4), "1000 frames x 6 temporal neighbours, 40x64 (depth maps L2 resident)"),
+    }
+    for name, (fn, by, wl_) in ops.items():
+        t = timeit(lambda: fn(B), n=10)
+        out[name] = {"us": t * 1e6, "GBps": by / t / 1e9, "hbm_frac": by / t / 1e9 / hbm_peak, "algorithmic_bytes": int(by), "workload": wl_}
+        if R is not None:
+            t2 = timeit(lambda: fn(R), n=5)
+            out[name]["reference_ext_us"] = t2 * 1e6
+            out[name]["speedup_vs_reference_ext"] = t2 / t
     return out
 
 

@@ -105,12 +105,13 @@ __global__ void __launch_bounds__(1024) ba_prep_kernel(const int64_t* __restrict
                                                        const int64_t* __restrict__ jj, int n_edges,
                                                        int nbuf, int n_eta, int t0, int t1,
                                                        int* status, int* kmap, int* kx, int* eptr,
-                                                       int* eidx, int* fill, int clear_sig) {
+                                                       int* eidx, int* fill, int clear_sig, int motion_only) {
   __shared__ int s_scan[1024];
   __shared__ int s_carry;
   __shared__ int s_bad;
+  __shared__ int s_maxdeg;
   const int tid = threadIdx.x;
-  if (tid == 0) { s_carry = 0; s_bad = 0; }
+  if (tid == 0) { s_carry = 0; s_bad = 0; s_maxdeg = 0; }
   for (int f = tid; f < nbuf; f += 1024) { kmap[f] = (f >= t0 && f < t1) ? 1 : 0; fill[f] = 0; }
   __syncthreads();
   for (int e = tid; e < n_edges; e += 1024) {
@@ -153,6 +154,7 @@ __global__ void __launch_bounds__(1024) ba_prep_kernel(const int64_t* __restrict
   for (int base = 0; base < M; base += 1024) {
     const int m = base + tid;
     const int c = (m < M) ? fill[m] : 0;
+    if (c > 0) atomicMax(&s_maxdeg, c);
     s_scan[tid] = c;
     __syncthreads();
     for (int o = 1; o < 1024; o <<= 1) {
@@ -189,11 +191,12 @@ __global__ void __launch_bounds__(1024) ba_prep_kernel(const int64_t* __restrict
   }
   if (tid == 0) {
     int st = 0;
-    if (M != n_eta) st |= DROID_BA_STATUS_ETA_MISMATCH;
+    if (M != n_eta && !motion_only) st |= DROID_BA_STATUS_ETA_MISMATCH;   // the reference ignores eta when motion_only
     if (s_bad) st |= DROID_BA_STATUS_BAD_INDEX;
     status[0] = st;
     status[1] = M;
     status[2] = 0;
+    status[3] = s_maxdeg;
     if (clear_sig) status[8] = 0;   // this call may overwrite the cached pose order of a larger system (see ba_order_kernel)
   }
 }
@@ -716,7 +719,7 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
   __shared__ float s_sum[32];      // Hjj (21, lower triangle row-major) | vj (6)
   const int m = blockIdx.y;
   const int M = status[1];
-  if (m >= M || m >= n_eta) return;
+  if (m >= M || (!motion_only && m >= n_eta)) return;   // eta has no say when motion_only (the reference ignores it)
   const int k = kx[m];
   if (k < frame_lo || k >= frame_hi) return;
   const int p0 = blockIdx.x * slab;
@@ -924,6 +927,18 @@ __device__ __forceinline__ void flush_block(double* __restrict__ A, int n6, cons
 
 static constexpr int kSchurSmemBytes = 200 * 1024;
 
+// Pixels per tile of ba_schur_kernel for a source frame with `deg` edges, or 0 when even a 32-pixel tile of its
+// 6 (deg + 1) rows does not fit one SM's shared memory (deg > ~190): those frames go to ba_schur_big_kernel.
+__host__ __device__ inline int schur_cc_tile(int deg) {
+  const int D = deg + 1, R = 6 * D;
+  const int DP = (D + 1) >> 1, RP = 12 * DP;
+  const int stride = RP + 2;
+  const int fixed = (R + 2 * DP + 8 + (2 + kEdgeStride) * deg + 4) * 4;
+  int T = (kSchurSmemBytes - fixed) / ((stride + 2) * 4);
+  T = (T < kThreads ? T : kThreads) & ~31;
+  return T < 32 ? 0 : T;
+}
+
 __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
     const float* __restrict__ ejc, const int64_t* __restrict__ jj, const float* __restrict__ gij, int* __restrict__ status,
     const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
@@ -947,13 +962,8 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
   const int DP = (D + 1) >> 1, RP = 12 * DP;   // row blocks are processed in pairs (12 rows); odd D is zero-padded
   const int stride = RP + 2;                    // == 2 (mod 4): even (LDS.64) and spreads the banks
   // smem: E[T][stride] | Qs[T] | QWs[T] | vS[R] | pose[2*DP] | s_e[deg] | s_jx[deg] | s_g[deg][kEdgeStride]
-  const int fixed = (R + 2 * DP + 8 + (2 + kEdgeStride) * deg + 4) * 4;
-  int T = (kSchurSmemBytes - fixed) / ((stride + 2) * 4);
-  T = min(T, kThreads) & ~31;
-  if (T < 32) {  // out-degree too large for one SM's shared memory
-    if (tid == 0) atomicOr(&status[0], DROID_BA_STATUS_BAD_INDEX);
-    return;
-  }
+  const int T = schur_cc_tile(deg);
+  if (T == 0) return;                           // out-degree too large for one SM's shared memory: ba_schur_big_kernel
   float* Es = reinterpret_cast<float*>(smem_raw);
   float* Qs = Es + (size_t)T * stride;
   float* QWs = Qs + T;
@@ -1104,6 +1114,119 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_kernel(
 }
 
 // ------------------------------------------------------------------------------------------------
+// Schur complement of source frames whose out-degree exceeds what ba_schur_kernel can stage in one SM's shared memory
+// (schur_cc_tile(deg) == 0, i.e. more than ~190 edges out of ONE keyframe).  No such frame occurs in DROID-SLAM's own
+// graphs (the proximity NMS keeps the degree in the tens), so this is the correct-but-slow path that replaces
+// "silently skip the frame": persistent CTAs walk the frames, and for a big frame every pair (a, b <= a) of its
+// 6-row blocks is one work item -- the CTA forms sum_p E_a[p] q[p] E_b[p]^T (and v_S of row block a when a == b)
+// straight from the packed E_j stream with a block reduction.  Row block 0 (the source pose) is re-derived as
+// sum_e N_e E_j^e for every item that touches it.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void schur_big_row(int a, int p, int HW, int e0, int deg, const int* __restrict__ eidx,
+                                              const float* __restrict__ ejc, const float* __restrict__ gij, float (&E)[6]) {
+  auto load = [&](int e, float (&ej)[6]) {
+    const float* src = ejc + (size_t)e * kEjComp * HW + p;
+    float c[kEjComp];
+#pragma unroll
+    for (int q = 0; q < kEjComp; q++) c[q] = __ldg(src + (size_t)q * HW);
+    ej_unpack(c, ej);
+  };
+  if (a > 0) { load(eidx[e0 + a - 1], E); return; }
+#pragma unroll
+  for (int n = 0; n < 6; n++) E[n] = 0.f;
+  for (int i = 0; i < deg; i++) {
+    const int e = eidx[e0 + i];
+    float ej[6];
+    load(e, ej);
+    const float* N = gij + (size_t)e * kEdgeStride + 8;
+#pragma unroll
+    for (int n = 0; n < 6; n++) {
+      float t = 0.f;
+#pragma unroll
+      for (int b = 0; b < 6; b++) t = fmaf(__ldg(N + n * 6 + b), ej[b], t);
+      E[n] += t;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) ba_schur_big_kernel(
+    const float* __restrict__ ejc, const int64_t* __restrict__ jj, const float* __restrict__ gij,
+    const int* __restrict__ status, const int* __restrict__ kx, const int* __restrict__ eptr,
+    const int* __restrict__ eidx, const float* __restrict__ Qi, const float* __restrict__ Wi, double* __restrict__ A,
+    double* __restrict__ bvec, int HW, int t0, int P, int n_eta, int frame_lo, int frame_hi,
+    const int* __restrict__ ppos, int tc_max_d) {
+  __shared__ float red[kThreads / 32][44];
+  const int M = min(status[1], n_eta);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n6 = 6 * P;
+  for (int m = 0; m < M; m++) {
+    const int e0 = eptr[m], deg = eptr[m + 1] - e0;
+    if (deg + 1 <= tc_max_d || schur_cc_tile(deg) != 0) continue;
+    const int k = kx[m];
+    if (k < frame_lo || k >= frame_hi) continue;
+    const int D = deg + 1;
+    auto pose_of = [&](int a) {
+      int pz = (a == 0) ? k - t0 : (int)jj[eidx[e0 + a - 1]] - t0;
+      if (pz < 0 || pz >= P) return -1;
+      return ppos != nullptr ? ppos[pz] : pz;
+    };
+    const long long items = (long long)D * (D + 1) / 2;
+    for (long long it = blockIdx.x; it < items; it += gridDim.x) {
+      int a = (int)((sqrt(8.0 * (double)it + 1.0) - 1.0) * 0.5);
+      while ((long long)(a + 1) * (a + 2) / 2 <= it) a++;
+      while ((long long)a * (a + 1) / 2 > it) a--;
+      const int b = (int)(it - (long long)a * (a + 1) / 2);
+      const int pa = pose_of(a), pb = pose_of(b);
+      if (pa < 0 || (pb < 0 && a != b)) continue;          // uniform over the CTA
+      float acc[42];
+#pragma unroll
+      for (int i = 0; i < 42; i++) acc[i] = 0.f;
+      for (int p = tid; p < HW; p += kThreads) {
+        float Ea[6], Eb[6];
+        schur_big_row(a, p, HW, e0, deg, eidx, ejc, gij, Ea);
+        if (a == b) {
+#pragma unroll
+          for (int n = 0; n < 6; n++) Eb[n] = Ea[n];
+        } else {
+          schur_big_row(b, p, HW, e0, deg, eidx, ejc, gij, Eb);
+        }
+        const float q = Qi[(size_t)m * HW + p];
+        const float qw = q * Wi[(size_t)m * HW + p];
+#pragma unroll
+        for (int n = 0; n < 6; n++) {
+          const float eq = Ea[n] * q;
+#pragma unroll
+          for (int c = 0; c < 6; c++) acc[n * 6 + c] = fmaf(eq, Eb[c], acc[n * 6 + c]);
+          acc[36 + n] = fmaf(qw, Ea[n], acc[36 + n]);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 42; i++) {
+        const float v = warp_sum(acc[i]);
+        if (lane == 0) red[warp][i] = v;
+      }
+      __syncthreads();
+      if (tid == 0) {
+        float blk[36];
+        for (int i = 0; i < 36; i++) {
+          float v = 0.f;
+          for (int w = 0; w < kThreads / 32; w++) v += red[w][i];
+          blk[i] = v;
+        }
+        flush_block(A, n6, blk, pa, pb, a == b);
+        if (a == b)
+          for (int n = 0; n < 6; n++) {
+            float v = 0.f;
+            for (int w = 0; w < kThreads / 32; w++) v += red[w][36 + n];
+            atomicAdd(&bvec[6 * pa + n], -(double)v);
+          }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // pass 3: depth back-substitution and update  (EvT6x1_kernel :1095-1115, :1417, disp_retr :933-946)
 //   dz_k = Q_k * (w_k - sum_rows E_n^T dx[pose(n)]),  rows whose pose index is <= 0 or >= P are
 //   skipped exactly like the reference (:1105) -- i.e. the first optimised pose t0 never feeds dz.
@@ -1213,8 +1336,18 @@ using namespace droid;
 
 // chains are only used when the separator holds at most a quarter of the rows (ba_order_kernel)
 static size_t ba_chol_bytes(int n6) {
-  if (n6 < kBaChainMinRows) return droid_chol_workspace_bytes(n6);
+  if (n6 < kBaChainMinRows || n6 > kCholChainsMaxRows) return droid_chol_workspace_bytes(n6);
   return droid_chol_chains_workspace_bytes(n6, kBaMaxChains, n6 / 4 + 8);
+}
+
+// The shard of source frames a call works on: [lo, hi).  "All frames" is frame_hi == INT32_MAX or < 0, or the
+// zero-initialised pair (0, 0) of a single-GPU call (no reduce_fn).  Anything else is taken literally, so a rank
+// whose shard is EMPTY (lo == hi; shard_bounds can produce one) accumulates nothing and only joins the reduction.
+static void ba_shard(const droid_ba_params* p, int* lo, int* hi, bool* all) {
+  *all = p->frame_hi == 0x7fffffff || p->frame_hi < 0 ||
+         (p->frame_lo == 0 && p->frame_hi == 0 && p->reduce_fn == nullptr);
+  *lo = *all ? 0 : p->frame_lo;
+  *hi = *all ? 0x7fffffff : (p->frame_hi > p->frame_lo ? p->frame_hi : p->frame_lo);
 }
 
 extern "C" size_t droid_ba_workspace_bytes(const droid_ba_params* p) {
@@ -1237,7 +1370,9 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     return DROID_ERR_INVALID_ARGUMENT;
   if (p->n_edges > 0 && (!targets || !weights || !ii || !jj)) return DROID_ERR_INVALID_ARGUMENT;
   if (!p->motion_only && (!eta || !dz_out) && p->n_eta > 0) return DROID_ERR_INVALID_ARGUMENT;
-  if (p->n_eta > 65535) return DROID_ERR_INVALID_ARGUMENT;
+  // frames of the launch grids: one row of eta per optimised frame; eta has no say when motion_only (:1392-1395)
+  const int Mgrid = p->motion_only ? p->nbuf : p->n_eta;
+  if (Mgrid > 65535) return DROID_ERR_INVALID_ARGUMENT;
   const int P = p->t1 - p->t0;
   const int n6 = 6 * P;
   const size_t chol_bytes = ba_chol_bytes(n6);
@@ -1251,12 +1386,33 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   if (w.total > workspace_bytes) return DROID_ERR_WORKSPACE_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
   const int HW = p->ht * p->wd;
-  const int frame_lo = p->frame_lo, frame_hi = p->frame_hi > p->frame_lo ? p->frame_hi : 0x7fffffff;
+  int frame_lo, frame_hi;
+  bool all_frames;
+  ba_shard(p, &frame_lo, &frame_hi, &all_frames);
+  const bool check = (p->flags & DROID_BA_FLAG_CHECK) != 0;
+  DevCtx& dc = dev_ctx();
+  std::lock_guard<std::recursive_mutex> call_lock(dc.call);   // side stream, events and pinned scratch are per device
 
   DROID_LAUNCH ba_prep_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->n_eta, p->t0, p->t1, w.status,
-                                     w.kmap, w.kx, w.eptr, w.eidx, w.fill, (n6 > kCholSmallMax && p->n_edges > 0) ? 0 : 1);
+                                     w.kmap, w.kx, w.eptr, w.eidx, w.fill, (n6 > kCholSmallMax && p->n_edges > 0) ? 0 : 1,
+                                     p->motion_only);
   if (check_launch()) return DROID_ERR_CUDA;
-  if (P == 0 || p->iterations == 0) return DROID_OK;
+  // device-side validation (status word): read back when the caller asked for it -- for free where the host has to
+  // wait for the chain layout anyway (below), with one small read at the end of the call otherwise
+  int* h_ints = nullptr;
+  auto read_status = [&](int nints) -> int {
+    if (!h_ints) h_ints = dc.pinned_ints();
+    if (!h_ints) return DROID_ERR_CUDA;
+    if (cudaMemcpyAsync(h_ints, w.status, nints * sizeof(int), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+        cudaStreamSynchronize(st) != cudaSuccess)
+      return DROID_ERR_CUDA;
+    return DROID_OK;
+  };
+  auto status_error = [&]() { return (h_ints[0] & (DROID_BA_STATUS_ETA_MISMATCH | DROID_BA_STATUS_BAD_INDEX)) ? DROID_ERR_BA_INPUT : DROID_OK; };
+  if (P == 0 || p->iterations == 0) {
+    if (check) { if (int rc = read_status(4)) return rc; return status_error(); }
+    return DROID_OK;
+  }
   // large systems: fill-reducing order + row envelope for the factorisation (small ones are solved by one CTA)
   const bool ordered = n6 > kCholSmallMax && p->n_edges > 0;
   const bool small = n6 <= kCholSmallMax;        // frontend / trajectory-filler windows: one-CTA solver
@@ -1264,16 +1420,19 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   const int* first = ordered ? w.first : nullptr;
   // long trajectories: the order also cuts the system into up to kBaMaxChains decoupled chains + a separator.  The
   // chain boundaries are the one thing the host has to know (they shape the launch sequence of the factorisation):
-  // 5 ints read back once per call.  DROID_BA_CHAINS=0/1 turns this off, 2..4 caps the number of chains.
+  // a few ints read back once per call.  DROID_BA_CHAINS=0/1 turns this off, 2..4 caps the number of chains.
+  // Systems beyond the chained solver's limit (kCholChainsMaxRows) keep the single-chain envelope path.
   static const int chains_req = []() {
     const char* e = getenv("DROID_BA_CHAINS");
     const int v = e ? atoi(e) : kBaMaxChains;
     return v < 2 ? 0 : (v > kBaMaxChains ? kBaMaxChains : v);
   }();
-  const int kreq = (ordered && n6 >= kBaChainMinRows) ? chains_req : 0;
+  const int kreq = (ordered && n6 >= kBaChainMinRows && n6 <= kCholChainsMaxRows) ? chains_req : 0;
   int nchains = 0;
   int chain_end[kBaMaxChains] = {};
   int pack_total = -1;          // multi-GPU: doubles of the packed system (without the rhs); -1 = sum the dense buffer
+  int max_deg = p->n_edges;     // upper bound until the device's figure is known
+  bool status_read = false;
   if (ordered) {
     DROID_LAUNCH ba_order_kernel<<<1, 1024, 0, st>>>(ii, jj, p->n_edges, p->nbuf, p->t0, P, w.kmap, w.ppos, w.first,
                                                      w.oscr, w.status + 8, p->ht * 65536 + p->wd, p->n_eta, kreq);
@@ -1282,12 +1441,11 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
       DROID_LAUNCH ba_pack_plan_kernel<<<1, 1024, 0, st>>>(w.first, w.status + 8, n6, w.pseg, w.poff, w.status + kPackTotalWord);
     }
     if (kreq > 0 || packed) {
-      static int* h_split = nullptr;
-      if (!h_split && cudaHostAlloc((void**)&h_split, 64 * sizeof(int), cudaHostAllocDefault) != cudaSuccess)
-        return DROID_ERR_CUDA;
-      if (cudaMemcpyAsync(h_split, w.status + 18, (kPackTotalWord - 18 + 1) * sizeof(int), cudaMemcpyDeviceToHost, st) !=
-              cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess)
-        return DROID_ERR_CUDA;
+      if (int rc = read_status(kPackTotalWord + 1)) return rc;
+      status_read = true;
+      max_deg = h_ints[3];
+      if (check) { if (int rc = status_error()) return rc; }
+      const int* h_split = h_ints + 18;
       if (kreq > 0) {
         nchains = h_split[0];
         if (nchains < 0 || nchains > kBaMaxChains) return DROID_ERR_CUDA;
@@ -1301,19 +1459,19 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     }
   }
 
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(ba_schur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         kSchurSmemBytes);
-    cudaFuncSetAttribute(ba_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         5 * kSlabMax * (int)sizeof(float));
-    attr_set = true;
+  if (dc.first(kOnceBa)) {
+    cudaFuncSetAttribute(ba_schur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSchurSmemBytes);
+    cudaFuncSetAttribute(ba_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * kSlabMax * (int)sizeof(float));
+    cudaStreamCreateWithFlags(&dc.ba_s2, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&dc.ba_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&dc.ba_join, cudaEventDisableTiming);
   }
-  // slabs: enough CTAs to fill the 148 SMs twice when there are few frames
+  // slabs: enough CTAs to fill the SMs twice when there are few frames
   // (a rank of a sharded call works on the frames of its shard only)
-  int Mrows = p->n_eta > 0 ? p->n_eta : 1;
-  if (p->frame_hi > p->frame_lo && p->frame_hi - p->frame_lo < Mrows) Mrows = p->frame_hi - p->frame_lo;
-  int S = (2 * 148 + Mrows - 1) / Mrows;
+  const int sms = dc.sm_count;
+  int Mrows = Mgrid > 0 ? Mgrid : 1;
+  if (!all_frames && frame_hi - frame_lo < Mrows) Mrows = frame_hi - frame_lo > 0 ? frame_hi - frame_lo : 1;
+  int S = (2 * sms + Mrows - 1) / Mrows;
   const int max_s = (HW + kThreads - 1) / kThreads;
   if (S > max_s) S = max_s;
   if (S < 1) S = 1;
@@ -1324,7 +1482,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
   // The tensor-core Schur kernel runs one CTA per SM and pays a prologue and an epilogue (fp64 atomics of the whole
   // Gram matrix) per CTA: it cuts a frame into slabs only when there are fewer frames than SMs (measured on a shard
   // of 125 frames: 0.17 ms with whole frames, 0.24 ms with three slabs each).
-  int S_tc = 148 / Mrows;
+  int S_tc = sms / Mrows;
   if (S_tc > S) S_tc = S;
   if (S_tc < 1) S_tc = 1;
   int slab_tc = (HW + S_tc - 1) / S_tc;
@@ -1350,10 +1508,10 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
         cudaMemsetAsync(w.A, 0, nsys * sizeof(double), st);
       }
     }
-    if (p->n_edges > 0 && p->n_eta > 0) {
+    if (p->n_edges > 0 && Mgrid > 0) {
       {
         ProfScope ps(DROID_PROF_BA_ACCUM, st);
-        DROID_LAUNCH ba_accum_kernel<<<dim3(S, p->n_eta), kThreads, 5 * (size_t)slab * sizeof(float), st>>>(
+        DROID_LAUNCH ba_accum_kernel<<<dim3(S, Mgrid), kThreads, 5 * (size_t)slab * sizeof(float), st>>>(
             disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, w.gij, w.status, w.kx,
             w.eptr, w.eidx, w.Q, w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, p->motion_only,
             frame_lo, frame_hi, ppos, w.ejc, p->edge_row);
@@ -1365,33 +1523,31 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
         // CTAs start first and the tensor-core CTAs fill the SMs around them instead of waiting for its tail.
         static const bool tc_on = []() { const char* e = getenv("DROID_SCHUR_TC"); return !(e && e[0] == '0'); }();
         const bool use_tc = tc_on && (HW % 4 == 0);      // the tensor-core builders move 4 pixels per 16-byte access
-        const bool fork = use_tc && !small;              // second stream for the CUDA-core kernel (large systems only)
-        static cudaStream_t s2 = nullptr;
-        static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-        static int s2_dev = -1;
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (use_tc && s2_dev != dev) {
-          cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking);
-          cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming);
-          cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming);
-          s2_dev = dev;
-        }
+        const int tc_max_d = use_tc ? kSchurTcMaxDeg + 1 : 0;
+        // once the device's maximum out-degree is known (large systems), kernels without a frame to work on are not launched
+        const bool need_cc = !status_read || max_deg + 1 > tc_max_d;
+        const bool need_big = schur_cc_tile(max_deg) == 0;
+        const bool fork = use_tc && !small && need_cc;   // second stream for the CUDA-core kernel (large systems only)
         cudaStream_t so = st;
         if (fork) {
-          cudaEventRecord(ev_fork, st);
-          cudaStreamWaitEvent(s2, ev_fork, 0);
-          so = s2;
+          cudaEventRecord(dc.ba_fork, st);
+          cudaStreamWaitEvent(dc.ba_s2, dc.ba_fork, 0);
+          so = dc.ba_s2;
         }
-        DROID_LAUNCH ba_schur_kernel<<<dim3(S, p->n_eta), kThreads, kSchurSmemBytes, so>>>(
-            w.ejc, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q,
-            w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, use_tc ? kSchurTcMaxDeg + 1 : 0);
+        if (need_cc)
+          DROID_LAUNCH ba_schur_kernel<<<dim3(S, p->n_eta), kThreads, kSchurSmemBytes, so>>>(
+              w.ejc, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q,
+              w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, tc_max_d);
+        if (need_big)
+          DROID_LAUNCH ba_schur_big_kernel<<<2 * sms, kThreads, 0, so>>>(
+              w.ejc, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W, w.A, bvec, HW, p->t0, P, p->n_eta,
+              frame_lo, frame_hi, ppos, tc_max_d);
         if (use_tc) {
-          if (fork) cudaEventRecord(ev_join, s2);
+          if (fork) cudaEventRecord(dc.ba_join, dc.ba_s2);
           if (launch_schur_tc(w.ejc, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W,
                               w.A, bvec, HW, p->wd, slab_tc, S_tc, p->t0, P, p->n_eta, frame_lo, frame_hi, ppos, st))
             return DROID_ERR_CUDA;
-          if (fork) cudaStreamWaitEvent(st, ev_join, 0);
+          if (fork) cudaStreamWaitEvent(st, dc.ba_join, 0);
         }
       }
     }
@@ -1440,6 +1596,10 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
       //  the OLD linearisation point, not the poses, so nothing has to wait for it any more)
     }
     if (check_launch()) return DROID_ERR_CUDA;
+  }
+  if (check && !status_read) {
+    if (int rc = read_status(4)) return rc;
+    return status_error();
   }
   return DROID_OK;
 }

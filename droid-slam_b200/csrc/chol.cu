@@ -781,7 +781,7 @@ __global__ void __launch_bounds__(256) chol_bwd_gemv_kernel(double* __restrict__
 //     global memory (row-major L => consecutive threads read consecutive columns; 64 independent loads per thread).
 //     In envelope mode only the columns from the block's first non-zero column on are touched.
 // ------------------------------------------------------------------------------------------------
-static constexpr int kBwdPersistMax = 12288;
+static constexpr int kBwdPersistMax = kCholChainsMaxRows;
 static constexpr int kBwdPThreads = 512;
 static size_t bwd_persist_smem(int n) { return ((size_t)n + 64 + 2 * 64 * 64 + 64 + 64) * sizeof(double); }
 
@@ -958,20 +958,14 @@ extern "C" int droid_chol_solve_env_f64(double* A, double* b, int n, const int* 
 // frontend-sized systems of ba: damping + factorisation + both sweeps + info in ONE launch (no memset, no damping kernel)
 int droid::launch_chol_small_damped(double* A, int n, float lm, float ep, int* info_dev, cudaStream_t st) {
   if (n <= 0 || n > kSmallMax) return DROID_ERR_INVALID_ARGUMENT;
-  static bool attr_set = false;
-  if (!attr_set) {
+  if (dev_ctx().first(kOnceCholSmall))
     cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmemMax);
-    attr_set = true;
-  }
   DROID_LAUNCH chol_small_kernel<<<1, ((n + 1 + 31) / 32) * 32, chol_small_smem(n), st>>>(A, n, info_dev, 1, lm, ep);
   return check_launch();
 }
 
 namespace {
-struct ChainCtx {
-  cudaStream_t main = nullptr, side = nullptr;
-  cudaEvent_t fork = nullptr, p = nullptr, r = nullptr, join = nullptr, done = nullptr;
-};
+using ChainCtx = droid::ChainStreams;
 struct ChainState {
   int J, Jend;
   bool on_side, finished;
@@ -996,19 +990,17 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
   cudaMemsetAsync(info_dev, 0, sizeof(int), st);
   if (n <= kSmallMax) {
     if (nchains > 0) return DROID_ERR_INVALID_ARGUMENT;
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (dev_ctx().first(kOnceCholSmall))
       cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmemMax);
-      attr_set = true;
-    }
     const size_t smem = chol_small_smem(n);
     DROID_LAUNCH chol_small_kernel<<<1, ((n + 1 + 31) / 32) * 32, smem, st>>>(A, n, info_dev, 0, 0.f, 0.f);
     return check_launch();
   }
-  static bool attr2 = false;
+  DevCtx& dc = dev_ctx();
+  std::lock_guard<std::recursive_mutex> call_lock(dc.call);   // the side streams / events below are shared per device
   constexpr int kSyrk128 = (2 * 2 * 16 * (128 + 2) + 128 * 128) * (int)sizeof(double);
   constexpr int kSyrk64 = (2 * 2 * 16 * (64 + 2) + 64 * 64) * (int)sizeof(double);
-  if (!attr2) {
+  if (dc.first(kOnceChol)) {
     cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmem);
     cudaFuncSetAttribute(chol_bwd_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem);
     cudaFuncSetAttribute(chol_syrk_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
@@ -1017,7 +1009,19 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
     cudaFuncSetAttribute(chol_syrk_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk64);
     cudaFuncSetAttribute(chol_bwd_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)bwd_persist_smem(kBwdPersistMax));
-    attr2 = true;
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    for (int c = 0; c < kMaxChains; c++) {
+      ChainStreams& x = dc.chain[c];
+      cudaStreamCreateWithPriority(&x.side, cudaStreamNonBlocking, hi);
+      cudaStreamCreateWithFlags(&x.main, cudaStreamNonBlocking);
+      cudaEventCreateWithFlags(&x.fork, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&x.p, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&x.r, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&x.join, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&x.done, cudaEventDisableTiming);
+    }
+    cudaEventCreateWithFlags(&dc.chol_start, cudaEventDisableTiming);
   }
   const bool vec = (n % 2 == 0) && (((uintptr_t)A & 15) == 0);
   const int nb = (n + 63) / 64;
@@ -1059,26 +1063,8 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
   //   side : P(0) F(0) P(1) [wait R(0)] F(1) P(2) [wait R(1)] F(2) ...      P = panel, F = first block column
   //   main :      [wait P(0)] R(0)   [wait P(1)] R(1) ...                    R = rest of the trailing update
   // Chain mode runs one such pair of streams per chain, all forked from the caller's stream.
-  static ChainCtx ctx[kMaxChains];
-  static cudaEvent_t ev_start = nullptr;
-  static int ctx_dev = -1;
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (ctx_dev != dev) {
-    int lo = 0, hi = 0;
-    cudaDeviceGetStreamPriorityRange(&lo, &hi);
-    for (int c = 0; c < kMaxChains; c++) {
-      cudaStreamCreateWithPriority(&ctx[c].side, cudaStreamNonBlocking, hi);
-      cudaStreamCreateWithFlags(&ctx[c].main, cudaStreamNonBlocking);
-      cudaEventCreateWithFlags(&ctx[c].fork, cudaEventDisableTiming);
-      cudaEventCreateWithFlags(&ctx[c].p, cudaEventDisableTiming);
-      cudaEventCreateWithFlags(&ctx[c].r, cudaEventDisableTiming);
-      cudaEventCreateWithFlags(&ctx[c].join, cudaEventDisableTiming);
-      cudaEventCreateWithFlags(&ctx[c].done, cudaEventDisableTiming);
-    }
-    cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming);
-    ctx_dev = dev;
-  }
+  ChainStreams* ctx = dc.chain;
+  cudaEvent_t ev_start = dc.chol_start;
   // one outer panel (128 columns) of one range: factorise it, update what lies below / to the right
   auto step = [&](ChainState& cs) {
     const int J = cs.J;
@@ -1127,7 +1113,7 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
     }
     const int t128 = (rr + 127) / 128;
     if (cs.on_side) {
-      const bool big = hi == nullptr && t128 * (t128 + 1) / 2 >= 148;
+      const bool big = hi == nullptr && t128 * (t128 + 1) / 2 >= dc.sm_count;
       cudaEventRecord(cx.p, cx.side);
       cudaStreamWaitEvent(cx.side, cx.r, 0);    // R(J-1) (no-op for the first panel)
       if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128, 256, kSyrk128, cx.side>>>(A, n, J, kb, PB, hi, cs.ca, 1 << 30, 0);
@@ -1142,7 +1128,7 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
       cudaEventRecord(cx.r, m);
     } else {
       if (cs.prof) prof_mark(DROID_PROF_CHOL_SYRK, true, m);
-      if (hi == nullptr && t128 * (t128 + 1) / 2 >= 148) {
+      if (hi == nullptr && t128 * (t128 + 1) / 2 >= dc.sm_count) {
         if (vec) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128 * (t128 + 1) / 2, 256, kSyrk128, m>>>(A, n, J, kb, 0, hi, cs.ca, 1 << 30, 0);
         else DROID_LAUNCH chol_syrk_kernel<128, false><<<t128 * (t128 + 1) / 2, 256, kSyrk128, m>>>(A, n, J, kb, 0, hi, cs.ca, 1 << 30, 0);
       } else {

@@ -454,11 +454,8 @@ static bool make_out_map(CUtensorMap* m, void* base, int B, int HW, int H, int W
 template <int W>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to, void* l0, void* l1, void* l2, void* l3, int B, int H,
                   cudaStream_t st) {
-  static bool attr = false;
-  if (!attr) {
-    cudaFuncSetAttribute(corr_build_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::kBytes);
-    attr = true;
-  }
+  // per device and per instantiation; a host-side table lookup, cheaper to repeat than to track
+  cudaFuncSetAttribute(corr_build_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::kBytes);
   ProfScope ps(DROID_PROF_CORR_GEMM, st);
   DROID_LAUNCH corr_build_kernel<W><<<dim3(H / 8, B), W == 64 ? kThreads64 : kThreads, Smem::kBytes, st>>>(
       ta, tb, to, (__half*)l0, (__half*)l1, (__half*)l2, (__half*)l3, H, H * W);

@@ -176,6 +176,99 @@ ProxWs carve_prox(void* base, int n) {
   return w;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// FactorGraph.__filter_repeated_edges (droid_slam/factor_graph.py:43-54): keep[k] = (ii[k], jj[k]) is not one of the
+// graph's existing edges (active + inactive).  The reference builds a Python set with one .item() per existing edge
+// and tests every candidate with two more; here the existing pairs go into an open-addressing hash table in global
+// memory (64-bit keys, linear probing, atomicCAS) and one CTA tests the candidates and compacts the survivors in
+// their original order.  Duplicates INSIDE the candidate list are all kept, exactly like the reference (its set holds
+// only the existing edges).
+// ------------------------------------------------------------------------------------------------
+constexpr unsigned long long kEmptyKey = ~0ull;
+
+__device__ __forceinline__ unsigned long long pair_key(long long i, long long j) {
+  return ((unsigned long long)(unsigned int)i << 32) | (unsigned long long)(unsigned int)j;
+}
+__device__ __forceinline__ unsigned int pair_hash(unsigned long long x) {
+  x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+  return (unsigned int)x;
+}
+
+__global__ void filter_insert_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int n,
+                                     unsigned long long* __restrict__ table, unsigned int mask) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  const unsigned long long key = pair_key(ii[e], jj[e]);
+  unsigned int slot = pair_hash(key) & mask;
+  while (true) {
+    const unsigned long long prev = atomicCAS(&table[slot], kEmptyKey, key);
+    if (prev == kEmptyKey || prev == key) return;
+    slot = (slot + 1) & mask;
+  }
+}
+
+__global__ void __launch_bounds__(1024) filter_query_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj,
+                                                            int n, const unsigned long long* __restrict__ table,
+                                                            unsigned int mask, int64_t* __restrict__ out_ii,
+                                                            int64_t* __restrict__ out_jj, unsigned char* __restrict__ keep,
+                                                            int* __restrict__ out_count) {
+  __shared__ int s_warp[32];
+  __shared__ int s_base;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_base = 0;
+  __syncthreads();
+  for (int c0 = 0; c0 < n; c0 += 1024) {
+    const int e = c0 + tid;
+    int flag = 0;
+    long long i = 0, j = 0;
+    if (e < n) {
+      i = ii[e]; j = jj[e];
+      const unsigned long long key = pair_key(i, j);
+      unsigned int slot = pair_hash(key) & mask;
+      flag = 1;
+      while (true) {
+        const unsigned long long v = table[slot];
+        if (v == key) { flag = 0; break; }
+        if (v == kEmptyKey) break;
+        slot = (slot + 1) & mask;
+      }
+      if (keep != nullptr) keep[e] = (unsigned char)flag;
+    }
+    // ordered compaction: exclusive scan of the flags over the CTA
+    int x = flag;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) s_warp[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      int w = s_warp[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += y;
+      }
+      s_warp[lane] = w;
+    }
+    __syncthreads();
+    const int pos = s_base + (warp > 0 ? s_warp[warp - 1] : 0) + x - flag;
+    if (flag) { out_ii[pos] = i; out_jj[pos] = j; }
+    __syncthreads();
+    if (tid == 0) s_base += s_warp[31];
+    __syncthreads();
+  }
+  if (tid == 0) *out_count = s_base;
+}
+
+static unsigned int filter_table_slots(int n_exist) {
+  unsigned int cap = 64;
+  while (cap < 2u * (unsigned int)(n_exist > 0 ? n_exist : 0) + 1u) cap <<= 1;
+  return cap;
+}
+
 }  // namespace
 }  // namespace droid
 
@@ -232,5 +325,34 @@ extern "C" int droid_proximity_edges(const float* d, int t, int t0, int t1, int 
   }
   DROID_LAUNCH prox_greedy_kernel<<<1, 32, 0, st>>>(w.keys, w.vals_sorted, w.sup, out_ii, out_jj, out_count, w.status, n, W,
                                                     t, t0, t1, nms, thresh, max_factors, mandatory, capacity);
+  return check_launch();
+}
+
+extern "C" size_t droid_filter_edges_workspace_bytes(int n_exist) {
+  if (n_exist < 0) return 0;
+  return (size_t)filter_table_slots(n_exist) * sizeof(unsigned long long) + 256;
+}
+
+extern "C" int droid_filter_repeated_edges(const int64_t* ii, const int64_t* jj, int n, const int64_t* ii_exist,
+                                           const int64_t* jj_exist, int n_exist, int64_t* out_ii, int64_t* out_jj,
+                                           unsigned char* keep, int* out_count, void* workspace, size_t workspace_bytes,
+                                           void* stream) {
+  if (n < 0 || n_exist < 0 || !out_count || !workspace) return DROID_ERR_INVALID_ARGUMENT;
+  if (n > 0 && (!ii || !jj || !out_ii || !out_jj)) return DROID_ERR_INVALID_ARGUMENT;
+  if (n_exist > 0 && (!ii_exist || !jj_exist)) return DROID_ERR_INVALID_ARGUMENT;
+  if (((uintptr_t)workspace & 255) != 0) {
+    const size_t adj = 256 - ((uintptr_t)workspace & 255);
+    if (workspace_bytes < adj) return DROID_ERR_WORKSPACE_TOO_SMALL;
+    workspace = (char*)workspace + adj;
+    workspace_bytes -= adj;
+  }
+  const unsigned int slots = filter_table_slots(n_exist);
+  if (workspace_bytes < (size_t)slots * sizeof(unsigned long long)) return DROID_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long* table = reinterpret_cast<unsigned long long*>(workspace);
+  cudaMemsetAsync(table, 0xff, (size_t)slots * sizeof(unsigned long long), st);
+  if (n_exist > 0)
+    DROID_LAUNCH filter_insert_kernel<<<(n_exist + 255) / 256, 256, 0, st>>>(ii_exist, jj_exist, n_exist, table, slots - 1);
+  DROID_LAUNCH filter_query_kernel<<<1, 1024, 0, st>>>(ii, jj, n, table, slots - 1, out_ii, out_jj, keep, out_count);
   return check_launch();
 }

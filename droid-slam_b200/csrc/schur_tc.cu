@@ -463,11 +463,8 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
 int launch_schur_tc(const float* ejc, const int64_t* jj, const float* gij, int* status, const int* kx, const int* eptr, const int* eidx,
                     const float* Qi, const float* Wi, double* A, double* bvec, int HW, int wd, int slab, int S, int t0,
                     int P, int n_eta, int frame_lo, int frame_hi, const int* ppos, cudaStream_t st) {
-  static bool attr = false;
-  if (!attr) {
+  if (dev_ctx().first(kOnceSchurTc))
     cudaFuncSetAttribute(stc::ba_schur_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, stc::kSmem);
-    attr = true;
-  }
   DROID_LAUNCH stc::ba_schur_tc_kernel<<<dim3(S, n_eta, 3), stc::kThreads, stc::kSmem, st>>>(
       ejc, jj, gij, status, kx, eptr, eidx, Qi, Wi, A, bvec, HW, wd, slab, t0, P, n_eta,
       frame_lo, frame_hi, ppos);

@@ -22,7 +22,7 @@ _DT = {torch.float32: _F32, torch.float16: _F16, torch.float64: _F64}
 
 _ERRORS = {
     -1: "invalid argument", -2: "unsupported dtype", -3: "workspace too small",
-    -4: "CUDA launch failed", -5: "not implemented",
+    -4: "CUDA launch failed", -5: "not implemented", -6: "device-side input validation failed",
 }
 
 REDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t,
@@ -38,7 +38,16 @@ class BaParams(ctypes.Structure):
         ("lm", ctypes.c_float), ("ep", ctypes.c_float),
         ("frame_lo", ctypes.c_int), ("frame_hi", ctypes.c_int),
         ("reduce_fn", REDUCE_FN), ("reduce_user", ctypes.c_void_p), ("edge_row", ctypes.c_void_p),
+        ("flags", ctypes.c_int),
     ]
+
+
+BA_FLAG_CHECK = 1
+# Input validation of ba() (eta rows == |unique(ii U [t0,t1))|, edge indices inside the buffer) happens on the device;
+# by default the host reads the verdict back and raises like the reference does on the eta broadcast
+# (src/droid_kernels.cu:1398).  DROID_BA_CHECK=0 (or ba(..., _validate=False)) keeps frontend-sized calls free of the
+# one host wait this costs; large systems wait for their chain layout anyway, so the check is free there.
+_BA_CHECK_DEFAULT = os.environ.get("DROID_BA_CHECK", "1") != "0"
 
 
 def _load():
@@ -58,6 +67,7 @@ def _load():
     lib.droid_launch_count.restype = ctypes.c_ulonglong
     lib.droid_proximity_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_scatter_mean_workspace_bytes.restype = ctypes.c_size_t
+    lib.droid_filter_edges_workspace_bytes.restype = ctypes.c_size_t
     return lib
 
 
@@ -73,6 +83,7 @@ C_ABI_SYMBOLS = [
     "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_solve_env_f64",
     "droid_chol_workspace_bytes", "droid_chol_solve_chains_f64", "droid_chol_chains_workspace_bytes",
     "droid_proximity_workspace_bytes", "droid_proximity_mandatory_count", "droid_proximity_edges",
+    "droid_filter_edges_workspace_bytes", "droid_filter_repeated_edges",
     "droid_cvx_upsample", "droid_scatter_mean_workspace_bytes", "droid_scatter_mean",
 ]
 
@@ -373,6 +384,30 @@ def proximity_edges(d, t, t0, t1, rad, nms, thresh, max_factors, stereo, ii_exis
     return out_ii[:k], out_jj[:k]
 
 
+def filter_repeated_edges(ii, jj, ii_exist, jj_exist):
+    """Extension: ``FactorGraph._FactorGraph__filter_repeated_edges`` (droid_slam/factor_graph.py:43-54)
+    on the device.  ``ii_exist`` / ``jj_exist`` = ``cat(graph.ii, graph.ii_inac)`` and likewise for jj.  Returns the
+    candidate edges that are not in the graph yet, in their original order (int64 CUDA).  One D2H read (the count)."""
+    _contig("filter_repeated_edges", ii=ii, jj=jj)
+    _long("filter_repeated_edges", ii=ii, jj=jj)
+    dev = ii.device
+    ii_exist = ii_exist.to(device=dev, dtype=torch.long).contiguous()
+    jj_exist = jj_exist.to(device=dev, dtype=torch.long).contiguous()
+    if ii.numel() != jj.numel() or ii_exist.numel() != jj_exist.numel():
+        raise RuntimeError("droid_backends.filter_repeated_edges: ii / jj differ in length")
+    n, ne = int(ii.numel()), int(ii_exist.numel())
+    with torch.cuda.device(dev):
+        out_ii, out_jj = torch.empty_like(ii), torch.empty_like(jj)
+        count = torch.zeros((1,), dtype=torch.int32, device=dev)
+        nws = int(_lib.droid_filter_edges_workspace_bytes(ne))
+        ws = torch.empty((nws,), dtype=torch.uint8, device=dev)
+        _check(_lib.droid_filter_repeated_edges(_p(ii), _p(jj), n, _p(ii_exist), _p(jj_exist), ne, _p(out_ii), _p(out_jj),
+                                                None, _p(count), ctypes.c_void_p(ws.data_ptr()), ctypes.c_size_t(nws),
+                                                _stream(ii)), "filter_repeated_edges")
+        k = int(count.item())
+    return out_ii[:k], out_jj[:k]
+
+
 def cvx_upsample(data, mask):
     """Extension: ``cvx_upsample`` of droid_slam/droid_net.py:21-35 in one pass.  data [batch,ht,wd,dim]
     float32, mask [batch, 9*8*8, ht, wd] (any shape with that many elements; float32 or float16 logits) ->
@@ -466,9 +501,11 @@ def _workspace(device, nbytes):
 
 
 def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1, iterations,
-       lm, ep, motion_only, _shard=None, _reduce=None, _edge_row=None):
+       lm, ep, motion_only, _shard=None, _reduce=None, _edge_row=None, _validate=None):
     """Updates ``poses`` and ``disps`` in place; returns [dx, dz] of the last iteration
-    (src/droid_kernels.cu:1314-1434).  ``_shard=(lo, hi)`` / ``_reduce`` / ``_edge_row`` are used by ba_sharded."""
+    (src/droid_kernels.cu:1314-1434).  ``_shard=(lo, hi)`` / ``_reduce`` / ``_edge_row`` are used by ba_sharded.
+    Raises RuntimeError when ``eta`` does not have one row per optimised frame or an edge index lies outside the
+    buffer (``_validate=False`` / DROID_BA_CHECK=0: no read-back, such edges are dropped, missing eta rows skipped)."""
     _contig("ba", poses=poses, disps=disps, intrinsics=intrinsics, disps_sens=disps_sens,
             targets=targets, weights=weights, ii=ii, jj=jj)
     if not isinstance(eta, torch.Tensor) or not eta.is_cuda:
@@ -486,7 +523,8 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, 
     prm = BaParams(n_edges=n_edges, nbuf=nbuf, ht=ht, wd=wd, n_eta=n_eta, t0=int(t0), t1=int(t1),
                    iterations=int(iterations), motion_only=1 if motion_only else 0, lm=float(lm),
                    ep=float(ep), frame_lo=0, frame_hi=0x7FFFFFFF, reduce_fn=REDUCE_FN(0),
-                   reduce_user=None, edge_row=None)
+                   reduce_user=None, edge_row=None,
+                   flags=BA_FLAG_CHECK if (_BA_CHECK_DEFAULT if _validate is None else _validate) else 0)
     if _edge_row is not None:
         if (_edge_row.dtype != torch.int32 or not _edge_row.is_cuda or not _edge_row.is_contiguous()
                 or _edge_row.numel() != n_edges):
@@ -509,10 +547,19 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, 
         ws = _workspace(poses.device, nws)
         dx = torch.zeros((max(P, 0), 6), dtype=torch.float32, device=poses.device)
         dz = torch.zeros((n_eta, HW), dtype=torch.float32, device=poses.device)
-        _check(_lib.droid_ba(_p(poses), _p(disps), _p(intrinsics), _p(disps_sens), _p(targets),
-                             _p(weights), _p(eta), _p(ii), _p(jj), ctypes.byref(prm), _p(dx), _p(dz),
-                             ctypes.c_void_p(ws.data_ptr()), ctypes.c_size_t(ws.numel()),
-                             _stream(poses)), "ba")
+        rc = _lib.droid_ba(_p(poses), _p(disps), _p(intrinsics), _p(disps_sens), _p(targets),
+                           _p(weights), _p(eta), _p(ii), _p(jj), ctypes.byref(prm), _p(dx), _p(dz),
+                           ctypes.c_void_p(ws.data_ptr()), ctypes.c_size_t(ws.numel()), _stream(poses))
+        if rc == -6:
+            st = ba_status(poses.device)
+            why = []
+            if st & 1:
+                why.append("eta has %d rows but unique(ii U [t0,t1)) has another count (the reference fails on this "
+                           "broadcast, src/droid_kernels.cu:1398)" % n_eta)
+            if st & 2:
+                why.append("an edge index lies outside [0, %d)" % nbuf)
+            raise RuntimeError("droid_backends.ba: " + "; ".join(why or ["device-side input validation failed"]))
+        _check(rc, "ba")
     return [dx, dz]
 
 

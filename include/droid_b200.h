@@ -5,9 +5,13 @@
  *  - every pointer is a DEVICE pointer unless its name ends in _host; all tensors are contiguous
  *    in the layout stated next to the argument (the reference enforces contiguity only,
  *    src/droid.cpp:84-85);
- *  - `stream` is a cudaStream_t passed as void*; every call is stream-ordered, never synchronises
- *    the host and never allocates caller-visible memory (outputs and workspaces are supplied by the
- *    caller; the Python host `droid_backends` allocates them with torch on the current stream);
+ *  - `stream` is a cudaStream_t passed as void*; every call is stream-ordered and never allocates
+ *    caller-visible memory (outputs and workspaces are supplied by the caller; the Python host
+ *    `droid_backends` allocates them with torch on the current stream).  No call synchronises the host,
+ *    with ONE documented exception: droid_ba waits on `stream` once (a) when the reduced camera system has
+ *    >= 1536 rows or a reduce_fn is set -- the host needs the chain layout / packed size (24 ints) to shape
+ *    the launch sequence -- and (b) at the end of the call when DROID_BA_FLAG_CHECK is set and (a) did not
+ *    already deliver the status word;
  *  - return value: DROID_OK or a negative DROID_ERR_* code (the Python host raises RuntimeError,
  *    mirroring TORCH_CHECK -> RuntimeError of the reference);
  *  - index tensors are int64 (torch.long), as in the reference;
@@ -30,12 +34,13 @@ extern "C" {
 #define DROID_ERR_WORKSPACE_TOO_SMALL (-3)
 #define DROID_ERR_CUDA (-4) /* a launch failed; see droid_last_cuda_error() */
 #define DROID_ERR_NOT_IMPLEMENTED (-5)
+#define DROID_ERR_BA_INPUT (-6) /* droid_ba with DROID_BA_FLAG_CHECK: the device-side validation failed (status word) */
 
 #define DROID_DTYPE_F32 0
 #define DROID_DTYPE_F16 1
 #define DROID_DTYPE_F64 2
 
-/* Library / build identification.  Returns e.g. "droid_b200 0.1 sm_100a". */
+/* Library / build identification.  Returns e.g. "droid_b200 0.2 sm_100a". */
 const char* droid_version(void);
 /* cudaGetErrorString of the last failing launch seen by this library (thread-unsafe, debug aid). */
 const char* droid_last_cuda_error(void);
@@ -167,6 +172,18 @@ int droid_proximity_edges(const float* d, int t, int t0, int t1, int rad, int nm
                           int64_t* out_ii, int64_t* out_jj, int capacity, int* out_count, void* workspace,
                           size_t workspace_bytes, void* stream);
 
+/* FactorGraph.__filter_repeated_edges (droid_slam/factor_graph.py:43-54), the second half of SURVEY 8f N3: of the
+ * candidate edges (ii[k], jj[k]), k < n, keep those that are not among the graph's existing edges
+ * (ii_exist/jj_exist = cat(active, inactive)); duplicates inside the candidate list are all kept, like the reference.
+ *   out_ii/out_jj [n]: the kept edges in their original order; keep [n] (may be NULL): 1 = kept; out_count (device
+ *   int): number kept.  Indices must be non-negative and < 2^32.
+ *   workspace: droid_filter_edges_workspace_bytes(n_exist) bytes (an open-addressing hash table of the existing pairs). */
+size_t droid_filter_edges_workspace_bytes(int n_exist);
+int droid_filter_repeated_edges(const int64_t* ii, const int64_t* jj, int n, const int64_t* ii_exist,
+                                const int64_t* jj_exist, int n_exist, int64_t* out_ii, int64_t* out_jj,
+                                unsigned char* keep, int* out_count, void* workspace, size_t workspace_bytes,
+                                void* stream);
+
 /* ---- convex upsampling (extension) -----------------------------------------------------
  * cvx_upsample (droid_slam/droid_net.py:21-35), as DepthVideo.upsample applies it (depth_video.py:123-127).
  *   data [batch,ht,wd,dim] float32; mask [batch,9*8*8,ht,wd] logits, float32 (mask_dtype 0) or float16 (1);
@@ -189,11 +206,17 @@ int droid_scatter_mean(const void* src, const int64_t* ix, void* out, int dtype,
  *   targets, weights [n_edges,2,ht,wd]; eta [n_eta,ht,wd] with one row per entry of
  *   kx = unique(ii U [t0,t1)) (so n_eta must equal |kx|; checked on the device, see status);
  *   dx_out [t1-t0,6], dz_out [n_eta,ht*wd] = updates of the LAST iteration (dz untouched when
- *   motion_only).  No host synchronisation; graph bookkeeping (unique/CSR) runs on the device.
+ *   motion_only; eta / n_eta are ignored then, as in the reference).  Graph bookkeeping (unique/CSR) runs on
+ *   the device; host synchronisation only as stated at the top of this file.
+ *   flags & DROID_BA_FLAG_CHECK: the call returns DROID_ERR_BA_INPUT when the device-side validation found
+ *   n_eta != |kx| (the reference raises on the broadcast, src/droid_kernels.cu:1398) or an edge index outside
+ *   [0, nbuf) (undefined behaviour in the reference; such edges are otherwise dropped).
  *   Multi-GPU: when `reduce_fn` != NULL it is called once per iteration, stream-ordered,
  *   on the packed reduced system (n_doubles fp64 values) after local accumulation; the Python host
  *   plugs torch.distributed.all_reduce (NCCL) in there.  With frame_lo/frame_hi a rank only
- *   accumulates source frames kx in [frame_lo, frame_hi) (pass 0, INT32_MAX for all).
+ *   accumulates source frames kx in [frame_lo, frame_hi).  "All frames" is frame_hi == INT32_MAX or < 0 (or
+ *   the zero-initialised pair (0, 0) when reduce_fn == NULL); any other pair is taken literally, so
+ *   frame_lo == frame_hi is an EMPTY shard: the rank contributes nothing and only joins the reduction.
  *   The buffer handed to reduce_fn is the reduced system PACKED to its structural non-zeros (the row segments
  *   inside the envelope of the pose order + the right-hand side; identical layout on every rank because the order
  *   is a function of the edge list alone) -- 10-20x fewer bytes than the dense lower triangle at 1000 keyframes.
@@ -209,7 +232,9 @@ typedef struct {
   droid_reduce_fn reduce_fn;   /* NULL on a single GPU                                      */
   void* reduce_user;
   const int* edge_row;         /* NULL, or row of every edge inside targets / weights       */
+  int flags;                   /* DROID_BA_FLAG_*                                            */
 } droid_ba_params;
+#define DROID_BA_FLAG_CHECK 1  /* read the status word back (one small D2H + wait) and fail on bad input */
 
 size_t droid_ba_workspace_bytes(const droid_ba_params* p);
 int droid_ba(float* poses, float* disps, const float* intrinsics, const float* disps_sens,
@@ -219,8 +244,8 @@ int droid_ba(float* poses, float* disps, const float* intrinsics, const float* d
 
 /* Device-side status word of the last droid_ba on this workspace (first 4 bytes of the workspace):
  * bit0 = n_eta != |kx|, bit1 = index out of range, bit2 = Cholesky failed in some iteration
- * (=> dx = 0 for that iteration, like src/droid_kernels.cu:1207-1210).  Reading it is the caller's
- * choice (it needs a D2H copy); droid_ba itself never reads it. */
+ * (=> dx = 0 for that iteration, like src/droid_kernels.cu:1207-1210).  Word 3 = largest out-degree of a source
+ * frame.  droid_ba reads it only under DROID_BA_FLAG_CHECK (or where it has to wait for the chain layout anyway). */
 #define DROID_BA_STATUS_ETA_MISMATCH 1
 #define DROID_BA_STATUS_BAD_INDEX 2
 #define DROID_BA_STATUS_CHOL_FAILED 4

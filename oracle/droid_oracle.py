@@ -11,9 +11,12 @@ and float64 where the reference does (host assembly + Cholesky, depth_filter com
 Parity pinning: the reference ships NO golden vectors or tests for these ops.  This
 oracle is pinned against outputs of the reference itself: the unmodified reference extension compiled by
 oracle/build_ref.sh (oracle/_ref/droid_backends_ref*.so) is run on the GPU box by
-tests/golden/make_golden_gpu.py and its outputs are committed under tests/golden/; tests/test_oracle_golden.py
-checks this oracle against them on CPU.  The BA math is additionally cross-checked against the reference's
-pure-PyTorch geom/ path by tests/golden/make_golden_pyref.py (run in the build container).
+tests/golden/make_golden_gpu.py and its outputs are committed under tests/golden/; tests/test_oracle.py checks this
+oracle against them on CPU.  The functions that restate the reference's PYTHON (reproject, proximity_edges,
+filter_repeated_edges, cvx_upsample) are pinned against outputs of the unmodified Python itself, run in the build
+container: tests/golden/make_golden_pyref.py (on the reference's own lietorch, oracle/build_lietorch.sh),
+make_golden_proximity.py, make_golden_upsample.py.  scatter_mean restates a third-party package that is absent
+(torch_scatter): parity unpinned.
 """
 import numpy as np
 
@@ -703,6 +706,14 @@ def proximity_edges(d, t, t0, t1, rad, nms, thresh, max_factors, stereo, ii_exis
 # ------------------------------------------------------------------------------------------------
 # convex upsampling
 # ------------------------------------------------------------------------------------------------
+def filter_repeated_edges(ii, jj, ii_exist, jj_exist):
+    """FactorGraph.__filter_repeated_edges (droid_slam/factor_graph.py:43-54): candidates that are not among the
+    existing (active + inactive) edges, original order; duplicates inside the candidate list are all kept."""
+    eset = set(zip(np.asarray(ii_exist).tolist(), np.asarray(jj_exist).tolist()))
+    keep = np.array([(int(i), int(j)) not in eset for i, j in zip(ii, jj)], bool).reshape(-1)
+    return np.asarray(ii, np.int64)[keep], np.asarray(jj, np.int64)[keep]
+
+
 def cvx_upsample(data, mask):
     """droid_slam/droid_net.py:21-35.  data [batch,ht,wd,dim], mask [batch,9*8*8,ht,wd] logits -> [batch,8ht,8wd,dim]:
     out[b, 8y+i, 8x+j, :] = sum_k softmax_k(mask[b, k, i, j, y, x]) * data[b, y + k//3 - 1, x + k%3 - 1, :] with zeros

@@ -31,10 +31,13 @@ def backends(lib_built):
 
 @pytest.fixture(scope="session")
 def ref_ext():
-    """The unmodified reference extension built by oracle/build_ref.sh, if present (GPU only)."""
+    """The unmodified reference extension built by oracle/build_ref.sh (oracle/_ref travels to the GPU box with the
+    snapshot).  Only `-m gpu` tests ask for it, and there a missing / unloadable extension is a FAILURE, not a skip:
+    the live comparisons are the strongest parity evidence this repo has."""
     try:
         import torch  # noqa: F401
         import droid_backends_ref
         return droid_backends_ref
-    except Exception:
-        return None
+    except Exception as ex:  # noqa: BLE001
+        pytest.fail("the reference extension oracle/_ref/droid_backends_ref*.so cannot be imported (%r): run "
+                    "`bash oracle/build_ref.sh` in the build container before `gpurun`" % (ex,))

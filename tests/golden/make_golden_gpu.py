@@ -88,17 +88,31 @@ def main():
 
     for key in G.BA_CASES:
         p, c = G.ba_case(key)
-        outs = {}
-        for tag, mod in (("ref", ref), ("mine", mine)):
-            poses, disps = cu(p["poses"]), cu(p["disps"])
+
+        def call(mod, poses0, disps0, iters):
+            poses, disps = cu(poses0), cu(disps0)
             o = mod.ba(poses, disps, cu(p["intrinsics"]), cu(p["disps_sens"]), cu(p["targets"]), cu(p["weights"]),
-                       cu(p["eta"]), cu(p["ii"]), cu(p["jj"]), p["t0"], p["t1"], c["iters"], c["lm"], c["ep"], c["motion_only"])
+                       cu(p["eta"]), cu(p["ii"]), cu(p["jj"]), p["t0"], p["t1"], iters, c["lm"], c["ep"], c["motion_only"])
             torch.cuda.synchronize()
-            outs[tag] = (poses.cpu().numpy(), disps.cpu().numpy(), o[0].cpu().numpy(),
-                         None if c["motion_only"] else o[1].cpu().numpy().reshape(-1, p["ht"] * p["wd"]))
+            return (poses.cpu().numpy(), disps.cpu().numpy(), o[0].cpu().numpy(),
+                    None if c["motion_only"] else o[1].cpu().numpy().reshape(-1, p["ht"] * p["wd"]))
+
+        outs = {tag: call(mod, p["poses"], p["disps"], c["iters"]) for tag, mod in (("ref", ref), ("mine", mine))}
         rp_, rd_, rdx, rdz = outs["ref"]
+        extra = {}
+        if c["iters"] == 2:
+            # the reference's state and updates after its FIRST iteration: lets every test compare iteration 2 from
+            # identical inputs (north_star: <= 1e-4 per Gauss-Newton iteration)
+            p1, d1, dx1, dz1 = call(ref, p["poses"], p["disps"], 1)
+            extra = dict(poses_it1=p1, disps_it1=d1, dx_it1=dx1, dz_it1=(dz1 if dz1 is not None else np.zeros(0, np.float32)))
+            p2, d2, dx2, dz2 = call(ref, p1, d1, 1)
+            cmp(key + ".ref 1+1 iterations vs one call of 2 (dx)", dx2, rdx)
+            m2 = call(mine, p1, d1, 1)
+            cmp(key + ".dx iteration 2 from the reference's state mine-vs-ref", m2[2], dx2)
+            if dz2 is not None:
+                cmp(key + ".dz iteration 2 from the reference's state mine-vs-ref", m2[3], dz2)
         save("ref_" + key, poses=rp_, disps=rd_, dx=rdx, dz=(rdz if rdz is not None else np.zeros(0, np.float32)),
-             digest=G.digest([p["poses"], p["disps"], p["targets"], p["weights"], p["eta"]]))
+             digest=G.digest([p["poses"], p["disps"], p["targets"], p["weights"], p["eta"]]), **extra)
         mp_, md_, mdx, mdz = outs["mine"]
         cmp(key + ".dx mine-vs-ref", mdx, rdx)
         cmp(key + ".poses mine-vs-ref", mp_, rp_)

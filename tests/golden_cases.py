@@ -45,6 +45,46 @@ def geom_case():
                 gt_poses=p["gt_poses"], gt_disps=p["gt_disps"])
 
 
+def reproject_case():
+    """geom_case with intrinsics that differ per frame, a stereo edge, edges into / out of the far-away frame 7 and a
+    noisy target field (motion features)."""
+    q = geom_case()
+    n = q["poses"].shape[0]
+    K = np.tile(q["intr"][None], (n, 1)).astype(np.float32)
+    K *= (1.0 + 0.01 * np.arange(n, dtype=np.float32))[:, None]
+    ii = np.concatenate([q["ii"], [3, 7, 6]]).astype(np.int64)
+    jj = np.concatenate([q["jj"], [3, 6, 7]]).astype(np.int64)
+    ht, wd = q["disps"].shape[1:]
+    rng = np.random.default_rng(31)
+    y, x = np.meshgrid(np.arange(ht, dtype=np.float32), np.arange(wd, dtype=np.float32), indexing="ij")
+    target = (np.stack([x, y], -1)[None] + rng.normal(0, 30.0, size=(len(ii), ht, wd, 2))).astype(np.float32)
+    return dict(poses=q["poses"], disps=q["disps"], intr=K, ii=ii, jj=jj, target=target)
+
+
+FILTER_CASES = {"frontend": (60, 48, 30, 1), "backend": (4000, 9000, 400, 2), "empty_graph": (40, 0, 12, 3),
+                "nothing_new": (0, 50, 20, 4), "all_known": (25, 25, 10, 5)}
+
+
+def filter_case(key):
+    """(candidates, existing edges) for FactorGraph.__filter_repeated_edges: random pairs over t frames, about half of
+    the candidates already in the graph, duplicates inside the candidate list."""
+    n, ne, t, seed = FILTER_CASES[key]
+    rng = np.random.default_rng(seed)
+    ie = rng.integers(0, t, size=ne).astype(np.int64)
+    je = np.clip(ie + rng.integers(-5, 6, size=ne), 0, t - 1).astype(np.int64)
+    ii = rng.integers(0, t, size=n).astype(np.int64)
+    jj = np.clip(ii + rng.integers(-5, 6, size=n), 0, t - 1).astype(np.int64)
+    if ne > 0 and n > 0:
+        k = rng.integers(0, ne, size=n)
+        m = rng.uniform(size=n) < 0.5
+        ii[m], jj[m] = ie[k][m], je[k][m]
+    if key == "all_known":
+        ii, jj = ie.copy(), je.copy()
+    if n > 4:
+        ii[3], jj[3] = ii[1], jj[1]                                    # a duplicate inside the candidate list
+    return dict(ii=ii, jj=jj, ii_exist=ie, jj_exist=je)
+
+
 BA_CASES = {
     "ba_C1": dict(name="C1", kw={}, iters=2, lm=1e-4, ep=0.1, motion_only=False),
     "ba_C1_1it": dict(name="C1", kw={}, iters=1, lm=1e-4, ep=0.1, motion_only=False),

@@ -110,6 +110,10 @@ def test_corr_index_pyramid_equals_levels(backends):
     fused = backends.corr_index_pyramid(vols, ct, 3)
     ref = torch.cat([backends.corr_index_forward(vols[l], ct / 2 ** l, 3)[0].view(B, 49, H, W) for l in range(4)], 1)
     assert torch.equal(fused, ref)
+    # and against the oracle on the same inputs (float16: bit-exact)
+    want = np.concatenate([O.corr_index_forward(vols[l].cpu().numpy(), (c / np.float32(2 ** l)).astype(np.float32), 3).reshape(B, 49, H, W)
+                           for l in range(4)], 1)
+    assert np.array_equal(fused.cpu().numpy(), want)
 
 
 # ---------------------------------------------------------------- altcorr ---------------------
@@ -140,6 +144,10 @@ def test_altcorr_indexed_equals_gathered(backends):
     a = backends.altcorr_forward_indexed(pyr, pyr, ii, jj, coords, 3)
     b, = backends.altcorr_forward(pyr[ii].float().contiguous(), pyr[jj].float().contiguous(), coords, 3)
     assert torch.equal(a, b)
+    # and against the oracle on the same (gathered, float32) inputs
+    f = pyr.float().cpu().numpy()
+    want = O.altcorr_forward(np.ascontiguousarray(f[p["ii"]]), np.ascontiguousarray(f[p["jj"]]), coords.cpu().numpy(), 3)
+    assert rel(a.cpu().numpy(), want) <= 1e-5
 
 
 def test_altcorr_backward(backends):
@@ -222,6 +230,20 @@ def test_reproject_matches_oracle(backends):
         backends.reproject(cu(poses), cu(disps), cu(intr), cu(ii), cu(jj))     # one intrinsics row per frame
 
 
+def test_reproject_matches_python_reference(backends):
+    """SURVEY 8f N1 against the reference ITSELF: stored outputs of the unmodified geom/projective_ops.py on the
+    reference's lietorch (tests/golden/ref_reproject.npz, tests/golden/make_golden_pyref.py)."""
+    import golden_cases as G
+    q = G.reproject_case()
+    ref = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_reproject.npz"))
+    assert str(ref["digest"]) == G.digest([q["poses"], q["disps"], q["intr"], q["target"]])
+    c, v, m = backends.reproject(cu(q["poses"]), cu(q["disps"]), cu(q["intr"]), cu(q["ii"]), cu(q["jj"]), cu(q["target"]))
+    scale = np.abs(ref["coords"]).max()
+    assert np.abs(c.cpu().numpy() - ref["coords"]).max() <= 1e-5 * scale
+    assert (v.cpu().numpy() != ref["valid"]).mean() <= 1e-4
+    assert np.abs(m.cpu().numpy() - ref["motn"]).max() <= 1e-5 * scale
+
+
 def test_frame_distance(backends):
     poses, disps, intr, ii, jj = geom_inputs()
     n = poses.shape[0]
@@ -236,6 +258,20 @@ def test_frame_distance(backends):
 
 
 def test_depth_filter_bit_exact(backends):
+    """Integer counts: bit-exact against the stored output of the unmodified reference extension
+    (tests/golden/ref_geom.npz) and against the oracle (which reproduces that output exactly, tests/test_oracle.py)."""
+    import golden_cases as G
+    q = G.geom_case()
+    ref = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_geom.npz"))
+    got = backends.depth_filter(cu(q["gt_poses"]), cu(q["gt_disps"]), cu(q["intr"]), cu(q["ix"]), cu(q["thresh"])).cpu().numpy()
+    assert np.array_equal(got, ref["counter"])
+    assert np.array_equal(got, O.depth_filter(q["gt_poses"], q["gt_disps"], q["intr"], q["ix"], q["thresh"]))
+    assert got.max() >= 3
+
+
+def test_depth_filter_frontend_window_against_oracle(backends):
+    """A 12-keyframe window: the numpy oracle evaluates the reprojection without FMA contraction, so a pixel whose
+    reprojection lands within one ulp of an integer may pick another bilinear cell -- at most 1e-4 of the pixels."""
     p = synth.make_ba_problem("C3", seed=3)
     poses, disps, intr = p["gt_poses"], p["gt_disps"], p["intrinsics"]
     ix = np.arange(12, dtype=np.int64)
@@ -243,7 +279,7 @@ def test_depth_filter_bit_exact(backends):
     ref = O.depth_filter(poses, disps, intr, ix, th)
     got = backends.depth_filter(cu(poses), cu(disps), cu(intr), cu(ix), cu(th)).cpu().numpy()
     assert got.min() >= 0 and got.max() <= 6 and ref.max() > 0
-    assert np.mean(got != ref) <= 1e-4   # identical up to float ties on the floor() of a reprojection
+    assert np.mean(got != ref) <= 1e-4
 
 
 # ---------------------------------------------------------------- dense BA --------------------
@@ -263,26 +299,45 @@ def oracle_ba(p, iterations=2, lm=1e-4, ep=0.1, motion_only=False):
     return poses, disps, dx, dz
 
 
+def check_per_iteration(backends, p, iters, lm, ep, motion_only=False, ref_step=None, tol=1e-4):
+    """north_star: pose / inverse-depth updates <= 1e-4 relative PER Gauss-Newton iteration.  Iteration k of the CUDA
+    path starts from the state the REFERENCE side (oracle or reference extension) left after iteration k-1, so every
+    iteration is compared on identical inputs instead of widening the bound for the second one."""
+    ref_step = ref_step or (lambda q: oracle_ba(q, 1, lm, ep, motion_only))
+    q = dict(p)
+    for it in range(iters):
+        rp, rd, rdx, rdz = ref_step(q)
+        gp, gd, gdx, gdz = run_ba(backends, q, 1, lm, ep, motion_only)
+        assert backends.ba_status() == 0
+        assert rel(gdx, rdx) <= tol, ("dx, iteration %d" % (it + 1), rel(gdx, rdx))
+        assert rel(gp, rp) <= 1e-5
+        if not motion_only:
+            assert rel(gdz.reshape(np.shape(rdz)), rdz) <= tol, ("dz, iteration %d" % (it + 1), rel(gdz.reshape(np.shape(rdz)), rdz))
+            assert rel(gd, rd) <= 1e-5
+        q = dict(q, poses=np.ascontiguousarray(rp), disps=np.ascontiguousarray(rd))
+    return q
+
+
 @pytest.mark.parametrize("name,kw", [("C1", {}), ("C3", {}), ("C1", dict(stereo=True, sensor=True)),
                                      ("C3", dict(nbuf=20))])
-@pytest.mark.parametrize("iters", [1, 2])
-def test_ba_matches_oracle(backends, name, kw, iters):
+def test_ba_matches_oracle(backends, name, kw):
     p = synth.make_ba_problem(name, **kw)
-    rp, rd, rdx, rdz = oracle_ba(p, iters)
-    gp, gd, gdx, gdz = run_ba(backends, p, iters)
-    assert backends.ba_status() == 0
-    # <= 1e-4 per Gauss-Newton iteration; iteration 2 starts from a state that already differs at 1e-6
-    assert rel(gdx, rdx) <= (1e-4 if iters == 1 else 5e-4) and rel(gdz, rdz) <= 1e-4
-    assert rel(gp, rp) <= 1e-5 and rel(gd, rd) <= 1e-5
+    q = check_per_iteration(backends, p, 2, 1e-4, 0.1)
+    # and the state after ONE call of two iterations against the oracle's state after its two
+    gp, gd, _, _ = run_ba(backends, p, 2)
+    assert rel(gp, q["poses"]) <= 1e-5 and rel(gd, q["disps"]) <= 1e-5
 
 
 def test_ba_motion_only(backends):
     p = synth.make_ba_problem("C3")
-    rp, rd, rdx, _ = oracle_ba(p, 2, motion_only=True)
-    gp, gd, gdx, _ = run_ba(backends, p, 2, motion_only=True)
-    assert rel(gdx, rdx) <= 5e-4 and rel(gp, rp) <= 1e-5
-    assert rel(run_ba(backends, p, 1, motion_only=True)[2], oracle_ba(p, 1, motion_only=True)[2]) <= 1e-4
+    q = check_per_iteration(backends, p, 2, 1e-4, 0.1, motion_only=True)
+    gp, gd, _, _ = run_ba(backends, p, 2, motion_only=True)
+    assert rel(gp, q["poses"]) <= 1e-5
     assert np.array_equal(gd, p["disps"])        # depths untouched
+    # the reference ignores eta when motion_only (src/droid_kernels.cu:1392-1395): a wrong row count is no error
+    r = dict(p, eta=np.ascontiguousarray(p["eta"][:3]))
+    hp, _, hdx, _ = run_ba(backends, r, 2, motion_only=True)
+    assert np.array_equal(hp, gp)
 
 
 def test_ba_backend_window_and_fixed_poses(backends):
@@ -291,10 +346,48 @@ def test_ba_backend_window_and_fixed_poses(backends):
     p["t0"] = 5
     kx = np.unique(np.concatenate([np.arange(p["t0"], p["t1"]), p["ii"]]))
     p["eta"] = np.ascontiguousarray(np.resize(p["eta"], (len(kx),) + p["eta"].shape[1:]))
-    rp, rd, rdx, rdz = oracle_ba(p, 2, lm=1e-5, ep=1e-2)
-    gp, gd, gdx, gdz = run_ba(backends, p, 2, lm=1e-5, ep=1e-2)
-    assert rel(gdx, rdx) <= 5e-4 and rel(gdz, rdz) <= 1e-4
+    check_per_iteration(backends, p, 2, 1e-5, 1e-2)
+    gp, _, _, _ = run_ba(backends, p, 2, lm=1e-5, ep=1e-2)
     assert np.array_equal(gp[:5], p["poses"][:5])
+
+
+def test_ba_input_validation_raises(backends):
+    """The reference fails on the eta broadcast when eta does not have one row per optimised frame
+    (src/droid_kernels.cu:1398) and has undefined behaviour for an edge index outside the buffer; here the device-side
+    validation is read back and raised (DROID_BA_FLAG_CHECK, the Python host's default)."""
+    p = synth.make_ba_problem("C3")
+    bad = dict(p, eta=np.ascontiguousarray(p["eta"][:-1]))
+    with pytest.raises(RuntimeError, match="eta"):
+        run_ba(backends, bad, 1)
+    jj = p["jj"].copy(); jj[3] = p["poses"].shape[0] + 5
+    with pytest.raises(RuntimeError, match="index"):
+        run_ba(backends, dict(p, jj=jj), 1)
+    # a long window takes the other read-back (chain layout): same errors, no extra wait
+    big = synth.make_ba_problem("C4", n_frames=280)
+    with pytest.raises(RuntimeError, match="eta"):
+        run_ba(backends, dict(big, eta=np.ascontiguousarray(big["eta"][:-2])), 1, lm=1e-5, ep=1e-2)
+    # opting out: no exception, the bad edge is dropped like every kernel drops it
+    poses, disps = cu(p["poses"]), cu(p["disps"])
+    backends.ba(poses, disps, cu(p["intrinsics"]), cu(p["disps_sens"]), cu(p["targets"]), cu(p["weights"]), cu(p["eta"]),
+                cu(p["ii"]), cu(jj), p["t0"], p["t1"], 1, 1e-4, 0.1, False, _validate=False)
+    assert backends.ba_status() & 2
+
+
+def test_ba_high_degree_frame_takes_the_tiled_schur_path(backends):
+    """A source frame with more edges than ba_schur_kernel can stage in shared memory (> ~190) used to be skipped
+    silently; it now goes through ba_schur_big_kernel.  8 frames, frame 3 carries 230 edges (its real neighbours
+    repeated -- duplicate edges are legal, the reference never de-duplicates inside ba)."""
+    p = synth.make_ba_problem("C1")
+    e = np.nonzero(p["ii"] == 3)[0]
+    rep = np.resize(e, 230 - len(e))
+    for k in ("ii", "jj", "targets", "weights"):
+        p[k] = np.ascontiguousarray(np.concatenate([p[k], p[k][rep]]))
+    p["weights"] = (p["weights"] * np.float32(0.05)).astype(np.float32)
+    assert int((p["ii"] == 3).sum()) == 230
+    rp, rd, rdx, rdz = oracle_ba(p, 1)
+    gp, gd, gdx, gdz = run_ba(backends, p, 1)
+    assert backends.ba_status() == 0
+    assert rel(gdx, rdx) <= 1e-4 and rel(gdz, rdz) <= 1e-4 and rel(gp, rp) <= 1e-5 and rel(gd, rd) <= 1e-5
 
 
 def test_ba_reduces_reprojection_error(backends):
@@ -351,7 +444,7 @@ def test_ba_pose_order_cache_follows_the_graph(backends):
     for k in ("ii", "jj", "targets", "weights"):
         q[k] = np.ascontiguousarray(p[k][perm])
     c = run_ba(backends, q, 1, lm=1e-5, ep=1e-2)                       # same problem, new signature
-    assert rel(c[2], a[2]) <= 2e-4 and rel(c[3], a[3]) <= 1e-4
+    assert rel(c[2], a[2]) <= 2e-4 and rel(c[3], a[3]) <= 1e-4     # another summation order of an ill-conditioned system
     # different graph, same shapes: the loop-closure edges are re-pointed, which changes the coupling structure
     r = dict(p)
     jj2 = p["jj"].copy()
@@ -586,22 +679,78 @@ def test_ba_two_shards_emulated_on_one_gpu(backends, name, kw, lm, ep):
 
 @pytest.mark.parametrize("key", sorted(__import__("golden_cases").BA_CASES))
 def test_ba_matches_reference_golden(backends, key):
-    """Against the stored outputs of the unmodified reference extension (tests/golden/ref_ba_*.npz)."""
+    """Against the stored outputs of the unmodified reference extension (tests/golden/ref_ba_*.npz), <= 1e-4 per
+    iteration: iteration 1 from the initial state, iteration 2 from the state the REFERENCE stored after its first."""
     import os
     import golden_cases as G
     p, c = G.ba_case(key)
     ref = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_" + key + ".npz"))
-    gp, gd, gdx, gdz = run_ba(backends, p, c["iters"], c["lm"], c["ep"], c["motion_only"])
-    assert rel(gdx, ref["dx"]) <= (1e-4 if c["iters"] == 1 else 5e-4)
+    mo = c["motion_only"]
+    hw = p["ht"] * p["wd"]
+    if c["iters"] == 2:
+        gp, gd, gdx, gdz = run_ba(backends, p, 1, c["lm"], c["ep"], mo)
+        assert rel(gdx, ref["dx_it1"]) <= 1e-4 and rel(gp, ref["poses_it1"]) <= 1e-5
+        if not mo:
+            assert rel(gdz.reshape(-1, hw), ref["dz_it1"]) <= 1e-4 and rel(gd, ref["disps_it1"]) <= 1e-5
+        p = dict(p, poses=ref["poses_it1"], disps=ref["disps_it1"])
+    gp, gd, gdx, gdz = run_ba(backends, p, 1, c["lm"], c["ep"], mo)
+    assert rel(gdx, ref["dx"]) <= 1e-4
     assert rel(gp, ref["poses"]) <= 1e-5
-    if not c["motion_only"]:
+    if not mo:
         assert rel(gdz.reshape(ref["dz"].shape), ref["dz"]) <= 1e-4 and rel(gd, ref["disps"]) <= 1e-5
 
 
+def test_ba_headline_parity_vs_reference_extension(backends, ref_ext):
+    """The configuration bench.py times (BASELINE configs[3]: 1000 keyframes, 20 862 edges, 40x64, lm=1e-5, ep=1e-2)
+    live against the UNMODIFIED reference extension on the same inputs: 4-chain + separator factorisation, three-CTA
+    edge-group Schur frames and the BFS pose order at the size no smaller test reaches.
+    Bound, per Gauss-Newton iteration (iteration 2 starts from the reference's state after its first): dx, dz <= 1e-4
+    relative -- or, because two float32 evaluations of this ill-conditioned system can be further from each other
+    than either is from the exact answer, no further from the float64 evaluation of the algorithm
+    (tests/golden/truth64_ba_C4_1000.npz, made by tests/golden/make_truth64_ba.py) than 2x the reference is.  The
+    measured figures are printed either way."""
+    p = synth.make_ba_problem("C4", n_frames=1000, knn=16)
+    assert len(p["ii"]) == 20862 and p["t1"] - p["t0"] == 999
+    dev = {k: cu(p[k]) for k in ("intrinsics", "disps_sens", "targets", "weights", "eta", "ii", "jj")}
+    hw = p["ht"] * p["wd"]
+
+    def call(mod, poses0, disps0, iters):
+        poses, disps = cu(poses0), cu(disps0)
+        dx, dz = mod.ba(poses, disps, dev["intrinsics"], dev["disps_sens"], dev["targets"], dev["weights"], dev["eta"],
+                        dev["ii"], dev["jj"], p["t0"], p["t1"], iters, 1e-5, 1e-2, False)
+        torch.cuda.synchronize()
+        return poses.cpu().numpy(), disps.cpu().numpy(), dx.cpu().numpy(), dz.cpu().numpy().reshape(-1, hw)
+
+    t64 = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "truth64_ba_C4_1000.npz"))
+    fr = t64["frames"]
+    r1 = call(ref_ext, p["poses"], p["disps"], 1)
+    g1 = call(backends, p["poses"], p["disps"], 1)
+    assert backends.ba_status() == 0 and len(backends.ba_chains()) >= 2
+    ref_x, got_x = rel(r1[2], t64["dx"]), rel(g1[2], t64["dx"])
+    ref_z, got_z = rel(r1[3][fr], t64["dz"]), rel(g1[3][fr], t64["dz"])
+    it1 = dict(dx=rel(g1[2], r1[2]), dz=rel(g1[3], r1[3]), poses=rel(g1[0], r1[0]), disps=rel(g1[1], r1[1]))
+    print("iteration 1  mine-vs-ref:", it1)
+    print("iteration 1  vs float64 truth: ref dx %.2e dz %.2e ; mine dx %.2e dz %.2e" % (ref_x, ref_z, got_x, got_z))
+    r2 = call(ref_ext, r1[0], r1[1], 1)
+    g2 = call(backends, r1[0], r1[1], 1)
+    it2 = dict(dx=rel(g2[2], r2[2]), dz=rel(g2[3], r2[3]), poses=rel(g2[0], r2[0]), disps=rel(g2[1], r2[1]))
+    print("iteration 2 (from the reference's state)  mine-vs-ref:", it2)
+    rr = call(ref_ext, p["poses"], p["disps"], 2)
+    gg = call(backends, p["poses"], p["disps"], 2)
+    whole = dict(dx=rel(gg[2], rr[2]), dz=rel(gg[3], rr[3]), poses=rel(gg[0], rr[0]), disps=rel(gg[1], rr[1]))
+    print("one call of 2 iterations  mine-vs-ref:", whole)
+    assert got_x <= max(1e-4, 2 * ref_x) and got_z <= max(1e-4, 2 * ref_z)
+    for it in (it1, it2):
+        assert it["dx"] <= 1e-4 or got_x <= max(1e-4, 2 * ref_x), it
+        assert it["dz"] <= 1e-4 or got_z <= max(1e-4, 2 * ref_z), it
+        assert it["poses"] <= 1e-5 and it["disps"] <= 1e-5, it
+    assert whole["poses"] <= 1e-5 and whole["disps"] <= 1e-5 and whole["dx"] <= 5e-4 and whole["dz"] <= 5e-4, whole
+
+
 def test_against_live_reference_extension(backends, ref_ext):
-    """When oracle/_ref holds the reference extension (built by oracle/build_ref.sh), compare live."""
-    if ref_ext is None:
-        pytest.skip("reference extension not built")
+    """Live against the unmodified reference extension (oracle/_ref, built by oracle/build_ref.sh; the fixture FAILS
+    when it cannot be imported).  Bit-exact: corr_index forward / backward (f32, f16), projmap, iproj, depth_filter,
+    frame_distance.  alt-corr <= 1e-5 (its float sums run over the channels in another order)."""
     import golden_cases as G
     for dt in (np.float32, np.float16):
         vol, c, g = G.corr_case(dt)
@@ -618,7 +767,34 @@ def test_against_live_reference_extension(backends, ref_ext):
                        ref_ext.depth_filter(GP, GD, K, cu(q["ix"]), cu(q["thresh"])))
     d1 = backends.frame_distance(P, D, K, cu(q["fa"]), cu(q["fb"]), 0.3)
     d2 = ref_ext.frame_distance(P, D, K, cu(q["fa"]), cu(q["fb"]), 0.3)
-    assert torch.equal(d1 == 1000.0, d2 == 1000.0) and rel(d1.cpu().numpy(), d2.cpu().numpy()) <= 1e-6
+    assert torch.equal(d1, d2), rel(d1.cpu().numpy(), d2.cpu().numpy())      # north_star: frame_distance bit-exact
+    f1, f2, coords, g = G.altcorr_case()
+    a, = backends.altcorr_forward(cu(f1), cu(f2), cu(coords), 3)
+    b, = ref_ext.altcorr_forward(cu(f1), cu(f2), cu(coords), 3)
+    assert rel(a.cpu().numpy(), b.cpu().numpy()) <= 1e-5
+    ga = backends.altcorr_backward(cu(f1), cu(f2), cu(coords), cu(g), 3)
+    gb = ref_ext.altcorr_backward(cu(f1), cu(f2), cu(coords), cu(g), 3)
+    assert rel(ga[0].cpu().numpy(), gb[0].cpu().numpy()) <= 1e-5 and rel(ga[1].cpu().numpy(), gb[1].cpu().numpy()) <= 1e-5
+    assert float(ga[2].abs().max()) == 0.0 and float(gb[2].abs().max()) == 0.0
+
+
+def test_frame_distance_bit_exact_at_backend_size(backends, ref_ext):
+    """frame_distance on the pair grid of a 250-keyframe backend graph (62 500 pairs, both the proximity call pattern
+    of factor_graph.py:305-316 and pairs that share a source frame in runs): every float bit-equal to the reference
+    extension, sentinels (1000.0) included."""
+    p = synth.make_ba_problem("C4", n_frames=250, knn=16)
+    n = 250
+    a, b = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    a, b = a.reshape(-1).astype(np.int64), b.reshape(-1).astype(np.int64)
+    P, D, K = cu(p["gt_poses"]), cu(p["gt_disps"]), cu(p["intrinsics"])
+    for beta in (0.3, 0.4):
+        d1 = backends.frame_distance(P, D, K, cu(a), cu(b), beta)
+        d2 = ref_ext.frame_distance(P, D, K, cu(a), cu(b), beta)
+        assert torch.equal(d1, d2), (beta, float((d1 != d2).float().mean()), rel(d1.cpu().numpy(), d2.cpu().numpy()))
+    assert bool((d2 == 1000.0).any()) and bool((d2 < 1000.0).any())
+    rng = np.random.default_rng(3)                                   # unsorted, repeated pairs
+    ia, ib = rng.integers(0, n, 5000), rng.integers(0, n, 5000)
+    assert torch.equal(backends.frame_distance(P, D, K, cu(ia), cu(ib), 0.3), ref_ext.frame_distance(P, D, K, cu(ia), cu(ib), 0.3))
 
 
 @pytest.mark.parametrize("key", sorted(__import__("proximity_cases").CASES))
@@ -636,6 +812,21 @@ def test_proximity_edges_bit_exact(backends, key):
     assert torch.equal(d, d0)                                           # the distances are the caller's
     assert ii.dtype == torch.long and np.array_equal(ii.cpu().numpy(), ref[key + "_ii"])
     assert np.array_equal(jj.cpu().numpy(), ref[key + "_jj"])
+
+
+@pytest.mark.parametrize("key", sorted(__import__("golden_cases").FILTER_CASES))
+def test_filter_repeated_edges_bit_exact(backends, key):
+    """SURVEY 8f N3, second half: FactorGraph.__filter_repeated_edges on the device against the output of the
+    UNMODIFIED method (tests/golden/ref_filter_edges.npz) and the restatement: same edges, same order."""
+    import golden_cases as G
+    c = G.filter_case(key)
+    ref = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_filter_edges.npz"))
+    assert str(ref[key + "_digest"]) == G.digest([c["ii"], c["jj"], c["ii_exist"], c["jj_exist"]])
+    ii, jj = backends.filter_repeated_edges(cu(c["ii"]), cu(c["jj"]), cu(c["ii_exist"]), cu(c["jj_exist"]))
+    assert ii.dtype == torch.long and np.array_equal(ii.cpu().numpy(), ref[key + "_ii"])
+    assert np.array_equal(jj.cpu().numpy(), ref[key + "_jj"])
+    oi, oj = O.filter_repeated_edges(c["ii"], c["jj"], c["ii_exist"], c["jj_exist"])
+    assert np.array_equal(ii.cpu().numpy(), oi) and np.array_equal(jj.cpu().numpy(), oj)
 
 
 def test_proximity_edges_large_graph_matches_oracle(backends):

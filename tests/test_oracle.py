@@ -87,6 +87,19 @@ def test_reproject_oracle_pinned_through_projmap():
     assert np.allclose(m[:, 0], np.clip(c[..., 0] - ug, -64, 64)) and np.allclose(m[:, 1], np.clip(c[..., 1] - vg, -64, 64))
 
 
+def test_reproject_vs_python_reference():
+    """SURVEY 8f N1, reference-run pin: O.reproject against stored outputs of the UNMODIFIED Python path
+    (geom/projective_ops.py:96-125 on the reference's own lietorch, run on CPU by tests/golden/make_golden_pyref.py):
+    per-frame intrinsics, Z < 0.1 fallback, stereo edge, motion features."""
+    q = G.reproject_case()
+    ref = gold("ref_reproject")
+    assert str(ref["digest"]) == G.digest([q["poses"], q["disps"], q["intr"], q["target"]])
+    c, v, m = O.reproject(q["poses"], q["disps"], q["intr"], q["ii"], q["jj"], target=q["target"])
+    assert 0.0 < ref["valid"].mean() < 1.0 and (np.abs(ref["motn"]) == 64.0).any()
+    assert rel(c, ref["coords"]) <= 1e-6 and np.array_equal(v, ref["valid"])
+    assert np.abs(m - ref["motn"]).max() <= 1e-6 * np.abs(ref["coords"]).max()
+
+
 @pytest.mark.parametrize("key", sorted(G.BA_CASES))
 def test_ba_vs_reference(key):
     p, c = G.ba_case(key)
@@ -186,6 +199,17 @@ def test_proximity_edges_vs_reference(key):
     assert str(ref[key + "_digest"]) == PC.digest(c)
     ii, jj = O.proximity_edges(c["d"], c["t"], c["t0"], c["t1"], c["rad"], c["nms"], c["thresh"], c["max_factors"],
                                c["stereo"], c["ii_exist"], c["jj_exist"])
+    assert np.array_equal(ii, ref[key + "_ii"]) and np.array_equal(jj, ref[key + "_jj"])
+
+
+@pytest.mark.parametrize("key", sorted(G.FILTER_CASES))
+def test_filter_repeated_edges_vs_reference(key):
+    """SURVEY 8f N3, second half: the restatement of FactorGraph.__filter_repeated_edges against the output of the
+    UNMODIFIED method (tests/golden/make_golden_pyref.py): bit-exact, order included."""
+    c = G.filter_case(key)
+    ref = gold("ref_filter_edges")
+    assert str(ref[key + "_digest"]) == G.digest([c["ii"], c["jj"], c["ii_exist"], c["jj_exist"]])
+    ii, jj = O.filter_repeated_edges(c["ii"], c["jj"], c["ii_exist"], c["jj_exist"])
     assert np.array_equal(ii, ref[key + "_ii"]) and np.array_equal(jj, ref[key + "_jj"])
 
 
