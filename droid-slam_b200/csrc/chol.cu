@@ -49,6 +49,10 @@ __device__ __forceinline__ double shfl_f64(double v, int src) {
   return __hiloint2double(__shfl_sync(0xffffffffu, __double2hiint(v), src),
                           __shfl_sync(0xffffffffu, __double2loint(v), src));
 }
+__device__ __forceinline__ double shfl_xor_f64(double v, int m) {
+  return __hiloint2double(__shfl_xor_sync(0xffffffffu, __double2hiint(v), m),
+                          __shfl_xor_sync(0xffffffffu, __double2loint(v), m));
+}
 
 // damp != 0: the Levenberg-Marquardt damping of ba (diag += ep + lm * diag, src/droid_kernels.cu:1197) is applied to the
 // copy in shared memory and *info is written in either case (0 / 1), so that ba needs neither a damping kernel nor a
@@ -194,19 +198,29 @@ __global__ void __launch_bounds__(160) chol_small_kernel(double* __restrict__ A,
 // blocked path.  Outer panels of PB = 128 columns (depth of the trailing update), each factorised as two
 // sub-panels of NB = 64 columns by chol_panel_kernel; then one trailing SYRK on all SMs.
 //
-// chol_panel_kernel: every CTA holds the 64 rows of the diagonal block (threads 0..63, redundantly in
-// every CTA) plus PR = 192 trailing rows (threads 64..255), ONE MATRIX ROW PER THREAD IN REGISTERS
-// (a[64]).  All rows run the same right-looking elimination in lockstep:
+// chol_panel_kernel<PRT>: every CTA holds the 64 rows of the diagonal block (threads 0..63, redundantly in
+// every CTA) plus PRT trailing rows (threads 64..), ONE MATRIX ROW PER THREAD IN REGISTERS (a[64]).  All rows
+// run the same right-looking elimination in lockstep:
 //     for c:  m = a[c] / d_c ;  a[q] -= m * col_c[q]  (q > c)
 // where col_c[q] = (un-normalised) entry (q, c) of the diagonal block, published through shared memory by
 // the diagonal rows one column ahead, with the reciprocal pivot computed by the publishing thread only.
 // One __syncthreads per column, no triangular-solve phase: the trailing rows finish together with the
-// 64x64 factorisation.  L = a[c] / sqrt(d_c) at the end.  If the sub-panel is the second half of its
-// outer panel (prev = 64), the rows first apply the update by the first half (a -= X_prev Xd_prev^T).
+// 64x64 factorisation.  L = a[c] / sqrt(d_c) at the end.
+//   * PRT = 64: the per-column cost of a CTA is the dependent pivot chain PLUS the fp64 issue of its rows' bulk
+//     update (rows x remaining columns / 64 lanes per clock); with 256 rows per CTA the bulk was as long as the
+//     chain (343 cycles per pivot), with 128 it hides behind it.  The panel kernels run a handful of CTAs
+//     (the rows inside the envelope), so three times as many CTAs cost nothing.
+//   * prev = 64 (second half of an outer panel): the rows first apply the rank-64 update of the first half to
+//     their 64 entries, a[c] -= sum_k L[r][j0-64+k] L[j0+c][j0-64+k], from two staged blocks -- this replaces a
+//     separate strip-SYRK launch (its own staging, C-tile round trip and two launch boundaries per 128 columns).
+//   * linv != nullptr: one extra CTA eliminates the rows of the 64x64 identity, which yields I L_KK^-T: the rows
+//     of the inverse transposed diagonal block.  The backward sweep then solves a block with a 64x64
+//     matrix-vector product instead of a 64-step dependent substitution.
 // The rhs (row n of A) is just one more trailing row, which is how L y = b gets solved for free.
 // ------------------------------------------------------------------------------------------------
 static constexpr int PB = 128;
-static constexpr int PR = 192;
+static constexpr int PRT = 64;                 // trailing rows per panel CTA
+static constexpr int kPanelThreads = 64 + PRT;
 #ifdef PANEL_TS
 __device__ long long g_ts[16];
 #define PTS(i) if (blockIdx.x == 0 && threadIdx.x == 0) g_ts[i] = clock64();
@@ -214,7 +228,8 @@ __device__ long long g_ts[16];
 #define PTS(i)
 #endif
 static constexpr int kRld = 66;   // staging row stride: even (16-byte rows for cp.async / LDS.128), 66*8 B spreads the banks
-static constexpr int kPanelSmem = (256 * kRld + 2 * 128 + 80 + 80 + 64) * (int)sizeof(double);
+static constexpr int kPanelSmem1 = (kPanelThreads * kRld + 2 * 128 + 80 + 80 + 64) * (int)sizeof(double);
+static constexpr int kPanelSmem2 = kPanelSmem1 + kPanelThreads * kRld * (int)sizeof(double);   // + the previous half
 
 // 1 / d without the IEEE fix-up of the compiler's division: MUFU seed (2^-23) and one third-order step,
 // e = 1 - d x0, x1 = x0 (1 + e + e^2): 4 dependent operations instead of 7, result within ~1 ulp.
@@ -286,47 +301,56 @@ struct Ranges {            // range c = [b[c], b[c+1]), c = 0..k; ranges 0..k-1 
   int b[kMaxChains + 2];
 };
 
-__global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__ A, int n, int j0, int jb,
-                                                            int* __restrict__ info,
-                                                            const int* __restrict__ hi64,
-                                                            int* __restrict__ arrive, int vec, int hole_lo,
-                                                            int hole_hi) {
+__global__ void __launch_bounds__(kPanelThreads, 1) chol_panel_kernel(double* __restrict__ A, int n, int j0, int jb,
+                                                                      int prev, int* __restrict__ info,
+                                                                      const int* __restrict__ hi64,
+                                                                      int* __restrict__ arrive, int vec, int hole_lo,
+                                                                      int hole_hi, double* __restrict__ linv) {
+  constexpr int NT = kPanelThreads;
+  constexpr int NW = NT / 32;                        // warps = rows staged per step
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* R = reinterpret_cast<double*>(smem_raw);  // [256][kRld] row staging
-  double* col = R + 256 * kRld;                      // [2][128]  published column (double-buffered, padded)
+  double* R = reinterpret_cast<double*>(smem_raw);  // [NT][kRld] row staging
+  double* col = R + NT * kRld;                       // [2][128]  published column (double-buffered, padded)
   double* inv = col + 256;                           // [80]      1 / pivot
   double* dv = inv + 80;                             // [80]      pivots
   double* rs = dv + 80;                              // [64]      1 / sqrt(pivot)
+  double* X = rs + 64;                               // [NT][kRld] the rows' entries in the previous 64 columns (prev only)
   const int tid = threadIdx.x;
-  const int trow0 = j0 + jb + blockIdx.x * PR;       // first trailing row of this CTA
+  // the last CTA of a launch with linv eliminates the identity instead of matrix rows
+  const bool ident = linv != nullptr && blockIdx.x == gridDim.x - 1;
+  const int trow0 = j0 + jb + blockIdx.x * PRT;      // first trailing row of this CTA
   // envelope: rows past hi64[] have no entry in these columns (and get none); the CTA holding the rhs row stays
-  if (hi64 != nullptr && blockIdx.x != 0 &&
-      ((trow0 > hi64[(j0 + jb - 1) >> 6] && trow0 + PR <= n) || (trow0 >= hole_lo && trow0 + PR <= hole_hi))) {
+  if (!ident && hi64 != nullptr && blockIdx.x != 0 &&
+      ((trow0 > hi64[(j0 + jb - 1) >> 6] && trow0 + PRT <= n) || (trow0 >= hole_lo && trow0 + PRT <= hole_hi))) {
     if (threadIdx.x == 0) atomicAdd(&arrive[j0 >> 6], 1);
     return;
   }
   auto row_of = [&](int t) { return t < 64 ? j0 + t : trow0 + t - 64; };
-  auto row_ok = [&](int t) { return t < 64 ? t < jb : (trow0 + t - 64) <= n; };
+  auto row_ok = [&](int t) { return t < 64 ? t < jb : (!ident && (trow0 + t - 64) <= n); };
 
   PTS(0)
   // stage: a warp-instruction moves 512 contiguous bytes of one row (16 B per lane) straight into shared memory
-  const int sr = tid >> 5, sc = (tid & 31) * 2;      // row within a group of 8, column pair
+  const int sr = tid >> 5, sc = (tid & 31) * 2;      // row within a group of NW, column pair
   if (vec && jb == 64) {
 #pragma unroll 8
-    for (int q = 0; q < 32; q++) {
-      const int t = q * 8 + sr;
+    for (int q = 0; q < NT / NW; q++) {
+      const int t = q * NW + sr;
       const unsigned dst = (unsigned)__cvta_generic_to_shared(R + t * kRld + sc);
       if (row_ok(t)) {
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(A + (size_t)row_of(t) * n + j0 + sc));
+        const double* src = A + (size_t)row_of(t) * n + j0 + sc;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
+        if (prev)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(X + t * kRld + sc)), "l"(src - prev));
       } else {
         *reinterpret_cast<double2*>(R + t * kRld + sc) = make_double2(0.0, 0.0);
+        if (prev) *reinterpret_cast<double2*>(X + t * kRld + sc) = make_double2(0.0, 0.0);
       }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
   } else {
-    for (int q = 0; q < 32; q++) {
-      const int t = q * 8 + sr;
+    for (int q = 0; q < NT / NW; q++) {
+      const int t = q * NW + sr;
       double2 v = make_double2(0.0, 0.0);
       if (row_ok(t)) {
         const double* src = A + (size_t)row_of(t) * n + j0 + sc;
@@ -348,6 +372,32 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
     const double2 v = *reinterpret_cast<const double2*>(R + tid * kRld + c);
     a[c] = v.x; a[c + 1] = v.y;
   }
+  if (prev) {
+    // a[c] -= sum_k L[r][k] L[j0 + c][k] over the previous 64 columns: own row from X[tid], the multiplier rows are
+    // the diagonal rows' entries X[0..63] (broadcast reads); 8 k at a time, 64 independent accumulators
+    const double* xr = X + tid * kRld;
+#pragma unroll 1
+    for (int k0 = 0; k0 < 64; k0 += 8) {
+      double x[8];
+#pragma unroll
+      for (int u = 0; u < 8; u += 2) {
+        const double2 v = *reinterpret_cast<const double2*>(xr + k0 + u);
+        x[u] = v.x; x[u + 1] = v.y;
+      }
+#pragma unroll
+      for (int c = 0; c < 64; c++) {
+        const double* d = X + c * kRld + k0;
+        double acc = a[c];
+#pragma unroll
+        for (int u = 0; u < 8; u += 2) {
+          const double2 w = *reinterpret_cast<const double2*>(d + u);
+          acc = fma(-x[u], w.x, acc);
+          acc = fma(-x[u + 1], w.y, acc);
+        }
+        a[c] = acc;
+      }
+    }
+  }
   if (tid < 64) {   // diagonal block: lower triangle only, partial block padded with I
 #pragma unroll
     for (int c = 0; c < 64; c++) {
@@ -356,6 +406,9 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
     }
     col[tid] = a[0];
     if (tid == 0) { inv[0] = rcp_fast(a[0]); dv[0] = a[0]; }
+  } else if (ident) {
+#pragma unroll
+    for (int c = 0; c < 64; c++) a[c] = (c == tid - 64) ? 1.0 : 0.0;
   }
   double qq = a[0] * a[0];
   PTS(1)
@@ -368,6 +421,16 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
     rs[tid] = 1.0 / sqrt(d);
   }
   __syncthreads();
+  if (ident) {      // rows of I L^-T: row i = tid - 64 of the inverse transposed diagonal block (the jb real rows only:
+                    // the rows behind a partial block belong to the next range)
+    if (tid >= 64 && tid - 64 < jb) {
+      double* dst = linv + (size_t)(j0 + tid - 64) * 64;
+#pragma unroll
+      for (int c = 0; c < 64; c += 2)
+        *reinterpret_cast<double2*>(dst + c) = make_double2(a[c] * rs[c], a[c + 1] * rs[c + 1]);
+    }
+    return;
+  }
 #pragma unroll
   for (int c = 0; c < 64; c += 2)
     *reinterpret_cast<double2*>(R + tid * kRld + c) = make_double2(a[c] * rs[c], a[c + 1] * rs[c + 1]);
@@ -379,8 +442,8 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
   __syncthreads();
   if (vec && jb == 64) {
 #pragma unroll 8
-    for (int q = 0; q < 32; q++) {
-      const int t = q * 8 + sr;
+    for (int q = 0; q < NT / NW; q++) {
+      const int t = q * NW + sr;
       if (!row_ok(t)) continue;
       if (t < 64 && (blockIdx.x != 0 || sc > t)) continue;   // the diagonal block is written once, lower part
       const double2 v = *reinterpret_cast<const double2*>(R + t * kRld + sc);
@@ -389,8 +452,8 @@ __global__ void __launch_bounds__(256, 1) chol_panel_kernel(double* __restrict__
       else *reinterpret_cast<double2*>(dst) = v;
     }
   } else {
-    for (int q = 0; q < 32; q++) {
-      const int t = q * 8 + sr;
+    for (int q = 0; q < NT / NW; q++) {
+      const int t = q * NW + sr;
       if (!row_ok(t)) continue;
       double* dst = A + (size_t)row_of(t) * n + j0 + sc;
 #pragma unroll
@@ -783,17 +846,22 @@ __global__ void __launch_bounds__(256) chol_bwd_gemv_kernel(double* __restrict__
 // ------------------------------------------------------------------------------------------------
 static constexpr int kBwdPersistMax = kCholChainsMaxRows;
 static constexpr int kBwdPThreads = 512;
-static size_t bwd_persist_smem(int n) { return ((size_t)n + 64 + 2 * 64 * 64 + 64 + 64) * sizeof(double); }
+static constexpr int kBwdLd = 66;     // row stride of a staged 64x64 block (16-byte rows, spreads the banks)
+static size_t bwd_persist_smem(int n) { return ((size_t)n + 64 + 2 * 64 * kBwdLd + 64 + 64) * sizeof(double); }
 
 // One CTA sweeps one range (rows [b[c], b[c+1]), blocks of 64 rows counted from the range start).  The separator
 // (c0 = k, one CTA) goes first and also subtracts its rows' contributions from the y entries of all chains; the
 // chains (c0 = 0, k CTAs) then run concurrently, each touching only its own columns.
+// linv: rows of the inverse transposed diagonal blocks (written by the panel kernels' identity CTA): x_blk = L^-T y_blk
+// is then a 64x64 matrix-vector product (8 threads per row + a 3-step shuffle reduction) instead of a 64-step chain of
+// dependent shuffle + DFMA; without it the block is solved by in-warp back-substitution on the diagonal block itself.
 __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(double* __restrict__ A, int n,
                                                                            const int* __restrict__ lo64,
-                                                                           const Ranges rg, int c0) {
+                                                                           const Ranges rg, int c0,
+                                                                           const double* __restrict__ linv) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* Dsm = reinterpret_cast<double*>(smem_raw);      // [2][64][64]
-  double* xs = Dsm + 2 * 64 * 64;                          // [64]
+  double* Dsm = reinterpret_cast<double*>(smem_raw);      // [2][64][kBwdLd]
+  double* xs = Dsm + 2 * 64 * kBwdLd;                      // [64]
   double* rinv = xs + 64;                                  // [64]
   double* ys = rinv + 64;                                  // [n (+pad)]
   const int tid = threadIdx.x;
@@ -807,11 +875,17 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
   const int nblk = (rend - rbeg + 63) >> 6;
   auto load_diag = [&](int blk, int buf) {
     const int o = rbeg + (blk << 6), jb = min(64, rend - o);
-    double* D = Dsm + buf * 4096;
+    double* D = Dsm + buf * 64 * kBwdLd;
     for (int e = tid; e < 64 * 32; e += kBwdPThreads) {
       const int r = e >> 5, c = 2 * (e & 31);
-      double* dst = D + r * 64 + c;
-      if (r < jb && c <= r) {
+      double* dst = D + r * kBwdLd + c;
+      if (linv != nullptr) {
+        if (r < jb) {
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(linv + (size_t)(o + r) * 64 + c));
+        } else {
+          dst[0] = 0.0; dst[1] = 0.0;
+        }
+      } else if (r < jb && c <= r) {
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(A + (size_t)(o + r) * n + o + c));
       } else {
         dst[0] = 0.0; dst[1] = 0.0;
@@ -823,36 +897,57 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
   for (int i = ylo + tid; i < rend; i += kBwdPThreads) ys[i] = y[i];
   for (int blk = nblk - 1; blk >= 0; blk--) {
     const int o = rbeg + (blk << 6), jb = min(64, rend - o);
-    double* D = Dsm + (blk & 1) * 4096;
+    double* D = Dsm + (blk & 1) * 64 * kBwdLd;
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();                                       // diagonal block landed; previous update of ys complete
     if (blk > 0) load_diag(blk - 1, (blk - 1) & 1);
-    if (tid < 64) rinv[tid] = tid < jb ? 1.0 / D[tid * 64 + tid] : 0.0;
-    __syncthreads();
-    // scale column c of the strictly lower part and y_c by 1 / L[c][c]
-    for (int e = tid; e < 64 * 64; e += kBwdPThreads) {
-      const int r = e >> 6, c = e & 63;
-      if (c < r) D[e] *= rinv[c];
-    }
-    if (tid < 64) xs[tid] = tid < jb ? ys[o + tid] * rinv[tid] : 0.0;
-    __syncthreads();
-    if (tid < 32) {
-      double x0 = xs[tid], x1 = xs[tid + 32];
+    if (linv != nullptr) {
+      // x[i] = sum_{c >= i} (L^-T)[i][c] y[c]
+      const int i = tid >> 3, part = tid & 7;
+      double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-      for (int c = 63; c >= 0; c--) {
-        const double xc = shfl_f64(c >= 32 ? x1 : x0, c & 31);
-        if (c >= 32) {
-          if (tid < (c & 31)) x1 = fma(-D[c * 64 + tid + 32], xc, x1);
-          x0 = fma(-D[c * 64 + tid], xc, x0);
-        } else if (tid < c) {
-          x0 = fma(-D[c * 64 + tid], xc, x0);
-        }
+      for (int c = part; c < 64; c += 16) {
+        s0 = fma(D[i * kBwdLd + c], (c < jb) ? ys[o + c] : 0.0, s0);
+        s1 = fma(D[i * kBwdLd + c + 8], (c + 8 < jb) ? ys[o + c + 8] : 0.0, s1);
       }
-      xs[tid] = x0; xs[tid + 32] = x1;
-      if (tid < jb) ys[o + tid] = x0;
-      if (tid + 32 < jb) ys[o + tid + 32] = x1;
+      double s = s0 + s1;
+      s += shfl_xor_f64(s, 1);
+      s += shfl_xor_f64(s, 2);
+      s += shfl_xor_f64(s, 4);
+      __syncthreads();                                     // every thread has read ys[o ..]
+      if (part == 0) {
+        xs[i] = (i < jb) ? s : 0.0;
+        if (i < jb) ys[o + i] = s;
+      }
+      __syncthreads();
+    } else {
+      if (tid < 64) rinv[tid] = tid < jb ? 1.0 / D[tid * kBwdLd + tid] : 0.0;
+      __syncthreads();
+      // scale column c of the strictly lower part and y_c by 1 / L[c][c]
+      for (int e = tid; e < 64 * 64; e += kBwdPThreads) {
+        const int r = e >> 6, c = e & 63;
+        if (c < r) D[r * kBwdLd + c] *= rinv[c];
+      }
+      if (tid < 64) xs[tid] = tid < jb ? ys[o + tid] * rinv[tid] : 0.0;
+      __syncthreads();
+      if (tid < 32) {
+        double x0 = xs[tid], x1 = xs[tid + 32];
+#pragma unroll
+        for (int c = 63; c >= 0; c--) {
+          const double xc = shfl_f64(c >= 32 ? x1 : x0, c & 31);
+          if (c >= 32) {
+            if (tid < (c & 31)) x1 = fma(-D[c * kBwdLd + tid + 32], xc, x1);
+            x0 = fma(-D[c * kBwdLd + tid], xc, x0);
+          } else if (tid < c) {
+            x0 = fma(-D[c * kBwdLd + tid], xc, x0);
+          }
+        }
+        xs[tid] = x0; xs[tid + 32] = x1;
+        if (tid < jb) ys[o + tid] = x0;
+        if (tid + 32 < jb) ys[o + tid + 32] = x1;
+      }
+      __syncthreads();
     }
-    __syncthreads();
     // y[c] -= sum_r L[o + r][c] x[r] for the columns left of the block, range by range
     const int bl0 = o >> 6, bl1 = (o + jb - 1) >> 6;      // the (absolute) 64-blocks of lo64 these rows fall into
     for (int sg = sg0; sg <= rc; sg++) {
@@ -937,10 +1032,15 @@ static size_t chol_ws_ints(int n, int k) {
   return (size_t)(k + 1) * (3 * nb + 1);   // panel check-in counters | hi64 | lo64, per range
 }
 
+static size_t chol_ws_head(int n, int nchains) {
+  return (256 + chol_ws_ints(n, nchains > 0 ? nchains : 0) * sizeof(int) + 255) / 256 * 256;
+}
+// rows of the inverse transposed 64x64 diagonal blocks, one row of 64 doubles per matrix row
+static size_t chol_ws_linv(int n) { return ((size_t)(n > 0 ? n : 0) * 64 * sizeof(double) + 255) / 256 * 256; }
+
 extern "C" size_t droid_chol_chains_workspace_bytes(int n, int nchains, int sep_rows) {
-  const size_t head = (256 + chol_ws_ints(n, nchains > 0 ? nchains : 0) * sizeof(int) + 255) / 256 * 256;
   const size_t scr = nchains > 1 ? (size_t)(nchains - 1) * (size_t)(sep_rows + 1) * (size_t)sep_rows * sizeof(double) : 0;
-  return head + scr;
+  return chol_ws_head(n, nchains) + chol_ws_linv(n) + scr;
 }
 
 extern "C" size_t droid_chol_workspace_bytes(int n) { return droid_chol_chains_workspace_bytes(n, 0, 0); }
@@ -1001,7 +1101,7 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
   constexpr int kSyrk128 = (2 * 2 * 16 * (128 + 2) + 128 * 128) * (int)sizeof(double);
   constexpr int kSyrk64 = (2 * 2 * 16 * (64 + 2) + 64 * 64) * (int)sizeof(double);
   if (dc.first(kOnceChol)) {
-    cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmem);
+    cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmem2);
     cudaFuncSetAttribute(chol_bwd_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem);
     cudaFuncSetAttribute(chol_syrk_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
     cudaFuncSetAttribute(chol_syrk_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSyrk128);
@@ -1052,9 +1152,12 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
   }
   double* scr = nullptr;
   const size_t scr_stride = (size_t)(seprows + 1) * (size_t)seprows;
+  // the backward sweep of envelope / chain systems runs in one persistent CTA per range and takes the diagonal blocks'
+  // inverses from the panel kernels (dense systems of this size keep the multi-CTA sweep: 0.9 vs 2.0 ms at n = 5994)
+  const bool persist_bwd = vec && firstc_dev != nullptr && n <= kBwdPersistMax;
+  double* linv = persist_bwd ? reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(workspace) + chol_ws_head(n, nchains)) : nullptr;
   if (nchains > 1) {
-    const size_t head = (256 + chol_ws_ints(n, nchains) * sizeof(int) + 255) / 256 * 256;
-    scr = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(workspace) + head);
+    scr = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(workspace) + chol_ws_head(n, nchains) + chol_ws_linv(n));
     cudaMemsetAsync(scr, 0, (size_t)(nchains - 1) * scr_stride * sizeof(double), st);
   }
   // Look-ahead: while the bulk of trailing update J runs on the chain's main stream, a second (high-priority) stream
@@ -1086,11 +1189,15 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
     for (int j0 = J; j0 < J + kb; j0 += NB) {
       const int jb = (J + kb - j0) < NB ? (J + kb - j0) : NB;
       const int rem_rows = n + 1 - (j0 + jb);  // >= 1 (the rhs row)
-      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PR - 1) / PR, 256, kPanelSmem, ps>>>(
-          A, n, j0, jb, info_dev, hi64 ? cs.hi64 : nullptr, cs.arrive, vec ? 1 : 0, cs.ca.hole_lo, cs.ca.hole_hi);
+      // second half of the outer panel: the rank-64 update by the first half is applied by the panel kernel itself
+      const bool fused = j0 > J && vec && jb == NB;
+      DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PRT - 1) / PRT + (linv ? 1 : 0), kPanelThreads,
+                                       fused ? kPanelSmem2 : kPanelSmem1, ps>>>(
+          A, n, j0, jb, fused ? NB : 0, info_dev, hi64 ? cs.hi64 : nullptr, cs.arrive, vec ? 1 : 0, cs.ca.hole_lo,
+          cs.ca.hole_hi, linv);
       const int rest = J + kb - (j0 + jb);     // columns of this outer panel still to factorise
-      if (rest > 0) {
-        // rank-64 update of the panel's remaining columns only (64x64 tiles of one block column, all SMs)
+      if (rest > 0 && !(vec && rest == NB)) {
+        // (only when the next sub-panel cannot fuse it) rank-64 update of the panel's remaining columns
         const int t64 = (rem_rows + 63) / 64;
         if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest, hi64 ? cs.hi64 : nullptr, cs.ca, 1 << 30, 0);
         else DROID_LAUNCH chol_syrk_kernel<64, false><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest, hi64 ? cs.hi64 : nullptr, cs.ca, 1 << 30, 0);
@@ -1197,11 +1304,10 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
     close_range(cs);
   }
   ProfScope psb(DROID_PROF_CHOL_BWD, st);
-  // (dense systems of this size keep the multi-CTA sweep: 0.9 ms vs 2.0 ms for one CTA at n = 5994)
-  if (vec && lo64 != nullptr && n <= kBwdPersistMax) {
-    DROID_LAUNCH chol_bwd_persist_kernel<<<1, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg, nchains);
+  if (persist_bwd) {
+    DROID_LAUNCH chol_bwd_persist_kernel<<<1, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg, nchains, linv);
     if (nchains > 0)
-      DROID_LAUNCH chol_bwd_persist_kernel<<<nchains, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg, 0);
+      DROID_LAUNCH chol_bwd_persist_kernel<<<nchains, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg, 0, linv);
     return check_launch();
   }
   for (int J0 = ((n - 1) / SB) * SB; J0 >= 0; J0 -= SB) {
