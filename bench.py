@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--frames", type=int, default=1000, help="keyframes of the C4 problem (default = BASELINE 1000)")
     ap.add_argument("--knn", type=int, default=16, help="proximity edges per keyframe (16 -> ~20k edges)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-frames", type=int, default=64, help="keyframes of the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-frames", type=int, default=48, help="keyframes of the bounded CPU-baseline sample")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the live comparison with the reference extension")
     ap.add_argument("--no-extra", action="store_true", help="skip the corr-lookup / frontend-window side metrics")
@@ -588,12 +588,15 @@ def extra_metrics(dev, hbm_peak, peaks):
     d = {k: torch.from_numpy(np.ascontiguousarray(p[k])).to(dev) for k in KEYS}
     p0, d0 = d["poses"].clone(), d["disps"].clone()
 
-    def fba(mod):
+    def fba(mod, **kw):
         d["poses"].copy_(p0); d["disps"].copy_(d0)
         mod.ba(d["poses"], d["disps"], d["intrinsics"], d["disps_sens"], d["targets"], d["weights"], d["eta"],
-               d["ii"], d["jj"], p["t0"], p["t1"], 2, 1e-4, 0.1, False)
+               d["ii"], d["jj"], p["t0"], p["t1"], 2, 1e-4, 0.1, False, **kw)
     t = timeit(lambda: fba(B), n=50)
-    out["frontend_ba"] = {"us_per_call": t * 1e6, "calls_per_s": 1.0 / t,
+    tn = timeit(lambda: fba(B, _validate=False), n=50)
+    out["frontend_ba"] = {"us_per_call": t * 1e6, "calls_per_s": 1.0 / t, "us_per_call_unvalidated": tn * 1e6,
+                          "note": "default call: the device-side input validation is read back (one host wait); "
+                                  "unvalidated = DROID_BA_CHECK=0, fully stream-ordered like round 1",
                           "workload": "C3 frontend window: 12 keyframes, 60 edges, 48x64, ba(iterations=2, lm=1e-4, ep=0.1)"}
     try:
         import droid_backends_ref as R
@@ -700,11 +703,62 @@ def altcorr_and_geometry_metrics(dev, hbm_peak, timeit):
 
 # ------------------------------------------------------------------------------------------------
 def cpu_baseline(args, frames=None):
-    """The numpy oracle (oracle/droid_oracle.py, a port of src/droid_kernels.cu) timed on the host on a
-    BOUNDED sample: one Gauss-Newton iteration of the C4 problem cut to `frames` keyframes.  Linear
-    extrapolation to the full edge count (optimistic for the CPU: the dense solve grows cubically)."""
-    import droid_oracle as O
+    """The reference's OWN CPU implementation of the path, timed on this box's host cores on a bounded sample:
+    droid_slam/geom/ba.py:31-106 (BA) + geom/chol.py:46-73 + geom/projective_ops.py:96-125 on the reference's
+    vendored lietorch (CPU build, oracle/build_lietorch.sh), the unmodified Python staged under oracle/_ref/pyref and
+    loaded by oracle/pyref.py.  Two samples: BASELINE configs[0] as it is (8 frames, 24 edges, 48x64; all cores and
+    1 core) and the headline problem cut to `frames` keyframes -- the dense Schur solve of geom/chol.py needs
+    P*M*6*HW*4 bytes for E (61 GB at 1000 keyframes), so the full size cannot run; `value` scales the cut linearly by
+    edges (optimistic for the CPU).  Falls back to the numpy port of the CUDA op when the staged reference is missing."""
     frames = frames or args.cpu_frames
+    try:
+        import pyref
+        import synth
+        ok, why = pyref.available()
+        if not ok:
+            raise ImportError(why)
+        import droid_backends as B
+        ns = pyref.load(B, cpu=True)
+        SE3 = ns.lietorch.SE3
+
+        def run_ba(p, nthreads, reps):
+            torch.set_num_threads(nthreads)
+            n = p["poses"].shape[0]
+            poses = SE3(torch.from_numpy(p["poses"])[None])
+            disps = torch.from_numpy(p["disps"])[None]
+            intr = torch.from_numpy(np.tile(p["intrinsics"][None], (n, 1)))[None]
+            ii, jj = torch.from_numpy(p["ii"]), torch.from_numpy(p["jj"])
+            target = torch.from_numpy(p["targets"]).permute(0, 2, 3, 1)[None].contiguous()
+            weight = torch.from_numpy(p["weights"]).permute(0, 2, 3, 1)[None].contiguous()
+            kx = torch.unique(ii)
+            eta = torch.from_numpy(p["eta"])[None][:, :len(kx)]
+            ns.ba.BA(target, weight, eta, poses, disps, intr, ii, jj, fixedp=p["t0"])      # warm-up
+            ts = []
+            for _ in range(reps):
+                t = time.perf_counter()
+                ns.ba.BA(target, weight, eta, poses, disps, intr, ii, jj, fixedp=p["t0"])
+                ts.append(time.perf_counter() - t)
+            return float(np.median(ts))
+        cores = os.cpu_count() or 1
+        c1 = synth.make_ba_problem("C1")
+        t_c1_all, t_c1_one = run_ba(c1, cores, 5), run_ba(c1, 1, 5)
+        q = problem(frames, args.knn)
+        threads = cores if t_c1_all <= t_c1_one else 1            # lietorch's OpenMP + torch threads can oversubscribe
+        dt = run_ba(q, threads, 2)
+        torch.set_num_threads(cores)
+        full = problem_edges(args.frames, args.knn)
+        scale = len(q["ii"]) / float(full)
+        return {"value": (1.0 / dt) * scale, "unit": "iters/s", "cores": threads, "kind": "reference",
+                "sample": "the reference's pure-PyTorch BA (droid_slam/geom/ba.py + chol.py + projective_ops.py on its own "
+                          "lietorch, CPU) on the C4 problem cut to %d keyframes / %d edges: %.2f s per Gauss-Newton "
+                          "iteration on %d thread(s); value = that rate scaled linearly by edges to %d edges (the full "
+                          "size needs 61 GB for the dense E of geom/chol.py)" % (frames, len(q["ii"]), dt, threads, full),
+                "sample_seconds": dt, "host_cores": cores,
+                "config0": {"workload": "BASELINE configs[0]: 8 frames, 24 edges, 48x64, one BA iteration",
+                            "ms_all_cores": t_c1_all * 1e3, "ms_one_core": t_c1_one * 1e3, "cores": cores}}
+    except Exception as ex:                                        # noqa: BLE001
+        note = "staged Python reference unavailable (%r): numpy port timed instead" % (ex,)
+    import droid_oracle as O
     q = problem(frames, args.knn)
     t = time.perf_counter()
     O.ba(q["poses"].copy(), q["disps"].copy(), q["intrinsics"], q["disps_sens"], q["targets"], q["weights"],
@@ -712,7 +766,7 @@ def cpu_baseline(args, frames=None):
     dt = time.perf_counter() - t
     full = problem_edges(args.frames, args.knn)
     scale = len(q["ii"]) / float(full)
-    return {"value": (1.0 / dt) * scale, "unit": "iters/s", "cores": 1, "kind": "port",
+    return {"value": (1.0 / dt) * scale, "unit": "iters/s", "cores": 1, "kind": "port", "note": note,
             "sample": "1 Gauss-Newton iteration of the C4 problem cut to %d keyframes / %d edges took %.2f s on 1 thread "
                       "(numpy port of src/droid_kernels.cu); value = that rate scaled linearly by edges to %d edges"
                       % (frames, len(q["ii"]), dt, full),

@@ -68,6 +68,7 @@ def _load():
     lib.droid_proximity_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_scatter_mean_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_filter_edges_workspace_bytes.restype = ctypes.c_size_t
+    lib.droid_frame_distance_workspace_bytes.restype = ctypes.c_size_t
     return lib
 
 
@@ -79,7 +80,7 @@ C_ABI_SYMBOLS = [
     "droid_version", "droid_last_cuda_error", "droid_launch_count", "droid_prof_enable", "droid_prof_read", "droid_corr_index_forward", "droid_corr_index_backward",
     "droid_corr_index_pyramid", "droid_altcorr_forward", "droid_altcorr_backward",
     "droid_altcorr_forward_indexed", "droid_corr_build", "droid_corr_build_workspace_bytes",
-    "droid_frame_distance", "droid_projmap", "droid_reproject", "droid_iproj", "droid_depth_filter",
+    "droid_frame_distance", "droid_frame_distance_workspace_bytes", "droid_frame_distance_ws", "droid_projmap", "droid_reproject", "droid_iproj", "droid_depth_filter",
     "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_solve_env_f64",
     "droid_chol_workspace_bytes", "droid_chol_solve_chains_f64", "droid_chol_chains_workspace_bytes",
     "droid_proximity_workspace_bytes", "droid_proximity_mandatory_count", "droid_proximity_edges",
@@ -286,7 +287,8 @@ def corr_build(fmap1, fmap2, num_levels=4):
 # ------------------------------------------------------------------------------------------------
 # geometry                                                   reference: src/droid.cpp:120-166,220-234
 # ------------------------------------------------------------------------------------------------
-def frame_distance(poses, disps, intrinsics, ii, jj, beta):
+def frame_distance(poses, disps, intrinsics, ii, jj, beta, _plain=False):
+    """``_plain=True`` calls the workspace-free C entry point (droid_frame_distance); same bits, slower."""
     _contig("frame_distance", poses=poses, disps=disps, intrinsics=intrinsics, ii=ii, jj=jj)
     _long("frame_distance", ii=ii, jj=jj)
     for t in (poses, disps, intrinsics):
@@ -295,9 +297,15 @@ def frame_distance(poses, disps, intrinsics, ii, jj, beta):
     ht, wd = disps.shape[1], disps.shape[2]
     with torch.cuda.device(poses.device):
         dist = torch.empty((n,), dtype=torch.float32, device=poses.device)
-        _check(_lib.droid_frame_distance(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj),
-                                         _p(dist), n, ht, wd, ctypes.c_float(beta), _stream(poses)),
-               "frame_distance")
+        if _plain:
+            _check(_lib.droid_frame_distance(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj), _p(dist), n, ht, wd,
+                                             ctypes.c_float(beta), _stream(poses)), "frame_distance")
+            return dist
+        nws = int(_lib.droid_frame_distance_workspace_bytes(ht, wd))
+        ws = torch.empty((nws,), dtype=torch.uint8, device=poses.device)
+        _check(_lib.droid_frame_distance_ws(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj), _p(dist), n, ht, wd,
+                                            ctypes.c_float(beta), ctypes.c_void_p(ws.data_ptr()), ctypes.c_size_t(nws),
+                                            _stream(poses)), "frame_distance")
     return dist
 
 

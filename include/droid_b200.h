@@ -128,6 +128,14 @@ int droid_frame_distance(const float* poses, const float* disps, const float* in
                          const int64_t* ii, const int64_t* jj, float* dist, int n, int ht, int wd,
                          float beta, void* stream);
 
+/* Same result, bit for bit, with the pair-independent per-pixel work (normalised image coordinates, the `total`
+ * reduction) done once per call in a small workspace instead of once per pixel-pair: what the Python host calls.
+ *   workspace: droid_frame_distance_workspace_bytes(ht, wd) bytes of device memory, 16-byte aligned. */
+size_t droid_frame_distance_workspace_bytes(int ht, int wd);
+int droid_frame_distance_ws(const float* poses, const float* disps, const float* intrinsics,
+                            const int64_t* ii, const int64_t* jj, float* dist, int n, int ht, int wd,
+                            float beta, void* workspace, size_t workspace_bytes, void* stream);
+
 /* projmap (src/droid.cpp:139-154, src/droid_kernels.cu:427-516,1463-1488).
  *   coords [n,ht,wd,3] (channel 2 = 0), valid [n,ht,wd,1]; both fully written. */
 int droid_projmap(const float* poses, const float* disps, const float* intrinsics,

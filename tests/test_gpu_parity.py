@@ -791,6 +791,7 @@ def test_frame_distance_bit_exact_at_backend_size(backends, ref_ext):
         d1 = backends.frame_distance(P, D, K, cu(a), cu(b), beta)
         d2 = ref_ext.frame_distance(P, D, K, cu(a), cu(b), beta)
         assert torch.equal(d1, d2), (beta, float((d1 != d2).float().mean()), rel(d1.cpu().numpy(), d2.cpu().numpy()))
+        assert torch.equal(backends.frame_distance(P, D, K, cu(a), cu(b), beta, _plain=True), d2)   # workspace-free entry
     assert bool((d2 == 1000.0).any()) and bool((d2 < 1000.0).any())
     rng = np.random.default_rng(3)                                   # unsorted, repeated pairs
     ia, ib = rng.integers(0, n, 5000), rng.integers(0, n, 5000)
