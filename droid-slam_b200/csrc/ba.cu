@@ -694,54 +694,60 @@ __device__ __forceinline__ void scatter_edge_value(double* __restrict__ A, doubl
 // pixel is owned by one thread => no atomics there).
 // ------------------------------------------------------------------------------------------------
 static constexpr int kSlabMax = 3072;
-static constexpr int kMetaChunk = 32;  // edges of one source frame staged in shared memory at a time
+static constexpr int kMetaChunk = 24;  // edges of one source frame staged in shared memory at a time
 
-__global__ void __launch_bounds__(kThreads) ba_accum_kernel(
+// Every thread owns NPIX pixels of the frame (p0 + tid + 256 m): their inverse depth, normalised image coordinates and
+// the running depth terms C, bz live in REGISTERS for the whole edge loop, the loop over them is fully unrolled (so the
+// loads and the packed-E_j stores of an edge are a per-edge base pointer + an immediate), and the per-pixel arithmetic
+// uses the structure of the Jacobian rows
+//     Jj_u = fx [hd, 0, -xd hd, -xd yd, 1 + xd^2, -yd],   Jj_v = fy [0, hd, -yd hd, -(1 + yd^2), xd yd, xd]
+// (xd, yd, hd = x/z, y/z, h/z): Hjj(1,0) vanishes identically, ten entries get one product and ten get two -- 30 FMAs
+// for the Hessian and 10 for the gradient instead of 42 + 12 plus the products with the structural zeros, which the
+// compiler may not drop without fast-math.  The first version (64-bit index arithmetic and a software-prefetch state
+// machine per pixel-edge, depth terms read-modify-written in shared memory) issued 294 instructions per pixel-edge,
+// this one ~150.
+template <int NPIX>
+__global__ void __launch_bounds__(kThreads, NPIX >= 4 ? 2 : 3) ba_accum_kernel(
     const float* __restrict__ disps, const float* __restrict__ intrinsics,
     const float* __restrict__ disps_sens, const float* __restrict__ targets,
     const float* __restrict__ weights, const float* __restrict__ eta,
     const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, const float* __restrict__ gij,
     const int* __restrict__ status, const int* __restrict__ kx, const int* __restrict__ eptr,
     const int* __restrict__ eidx, float* __restrict__ Qo, float* __restrict__ Wo,
-    double* __restrict__ A, double* __restrict__ bvec, int HW, int wd, int slab, int t0, int P,
+    double* __restrict__ A, double* __restrict__ bvec, int HW, int wd, int t0, int P,
     int n_eta, int motion_only, int frame_lo, int frame_hi, const int* __restrict__ ppos,
     float* __restrict__ ejc, const int* __restrict__ edge_row) {
-  // per pixel of the slab (dynamic shared memory, 5 x slab floats): C and bz sums, inverse depth and the normalised
-  // image coordinates -- the last three are the same for every edge of the frame, so the row/column split of the
-  // pixel index (an integer division) and the two float divisions by fx, fy are paid once per pixel, not per pixel-edge
-  extern __shared__ __align__(16) float accum_dyn[];
-  float* Cs = accum_dyn;
-  float* Bs = Cs + slab;
-  float* Ds = Bs + slab;
-  float* Xs = Ds + slab;
-  float* Ys = Xs + slab;
-  __shared__ float red[kThreads / 32][32];
-  __shared__ float s_sum[32];      // Hjj (21, lower triangle row-major) | vj (6)
+  __shared__ float part[kMetaChunk][kThreads / 32][32];   // per edge of the chunk and warp: Hjj (21, lower triangle row-major) | vj (6)
+  __shared__ float s_sum[kMetaChunk][32];
+  __shared__ int s_e[kMetaChunk];
+  __shared__ int s_jx[kMetaChunk];
+  __shared__ int s_row[kMetaChunk];
+  __shared__ __align__(16) float s_g[kMetaChunk][kEdgeStride];
   const int m = blockIdx.y;
   const int M = status[1];
   if (m >= M || (!motion_only && m >= n_eta)) return;   // eta has no say when motion_only (the reference ignores it)
   const int k = kx[m];
   if (k < frame_lo || k >= frame_hi) return;
-  const int p0 = blockIdx.x * slab;
-  const int p1 = min(HW, p0 + slab);
-  if (p0 >= p1) return;
+  const int p0 = blockIdx.x * (kThreads * NPIX);
+  if (p0 >= HW) return;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const Intr K = {intrinsics[0], intrinsics[1], intrinsics[2], intrinsics[3]};
+  const float fx2 = K.fx * K.fx, fy2 = K.fy * K.fy;
   const int n6 = 6 * P;
   const float* __restrict__ dmap = disps + (size_t)k * HW;
-  for (int p = tid; p < p1 - p0; p += kThreads) {
-    Cs[p] = 0.f; Bs[p] = 0.f; Ds[p] = dmap[p0 + p];
-    const int pi = (p0 + p) / wd, pj = (p0 + p) - pi * wd;
-    Xs[p] = ((float)pj - K.cx) / K.fx;
-    Ys[p] = ((float)pi - K.cy) / K.fy;
+  const int pbase = p0 + tid;
+  float px[NPIX], py[NPIX], pd[NPIX], Cs[NPIX], Bs[NPIX];
+#pragma unroll
+  for (int q = 0; q < NPIX; q++) {
+    const int p = pbase + q * kThreads;
+    const bool ok = p < HW;
+    const int pi = (ok ? p : 0) / wd, pj = (ok ? p : 0) - pi * wd;
+    px[q] = ((float)pj - K.cx) / K.fx;
+    py[q] = ((float)pi - K.cy) / K.fy;
+    pd[q] = ok ? dmap[p] : 1.f;
+    Cs[q] = 0.f; Bs[q] = 0.f;
   }
-  __syncthreads();
   const int e0 = eptr[m], e1 = eptr[m + 1];
-  // Edge metadata (edge id, target frame, relative pose, N) is staged in shared memory in chunks, and the four
-  // input values of the NEXT (edge, pixel) item are fetched before the current item is processed.
-  __shared__ int s_e[kMetaChunk];
-  __shared__ int s_jx[kMetaChunk];
-  __shared__ __align__(16) float s_g[kMetaChunk][kEdgeStride];
   for (int eb = e0; eb < e1; eb += kMetaChunk) {
     const int nE = min(kMetaChunk, e1 - eb);
     __syncthreads();
@@ -749,17 +755,28 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
       const int e = eidx[eb + i];
       s_e[i] = e;
       s_jx[i] = (int)jj[e];
+      s_row[i] = edge_row ? edge_row[e] : e;
     }
     for (int i = tid; i < nE * kEdgeStride; i += kThreads)
       s_g[i / kEdgeStride][i % kEdgeStride] = gij[(size_t)eidx[eb + i / kEdgeStride] * kEdgeStride + i % kEdgeStride];
     __syncthreads();
-    float n_tu = 0.f, n_tv = 0.f, n_wu = 0.f, n_wv = 0.f;
-    auto fetch = [&](int ei_, int p_) {
-      const size_t base = (size_t)(edge_row ? edge_row[s_e[ei_]] : s_e[ei_]) * 2 * HW + p_;
-      n_tu = __ldg(targets + base); n_tv = __ldg(targets + base + HW);
-      n_wu = __ldg(weights + base); n_wv = __ldg(weights + base + HW);
+    // targets / weights of the NEXT edge are fetched before the block reduction of the current one, so the loads are
+    // in flight across its two barriers
+    float ntu[NPIX], ntv[NPIX], nwu[NPIX], nwv[NPIX];
+    auto fetch = [&](int ei_) {
+      const float* __restrict__ pt = targets + (size_t)s_row[ei_] * 2 * HW + pbase;
+      const float* __restrict__ pw = weights + (size_t)s_row[ei_] * 2 * HW + pbase;
+#pragma unroll
+      for (int q = 0; q < NPIX; q++) {
+        const bool ok = pbase + q * kThreads < HW;
+        ntu[q] = ok ? __ldg(pt + q * kThreads) : 0.f;
+        ntv[q] = ok ? __ldg(pt + HW + q * kThreads) : 0.f;
+        nwu[q] = ok ? __ldg(pw + q * kThreads) : 0.f;
+        nwv[q] = ok ? __ldg(pw + HW + q * kThreads) : 0.f;
+      }
     };
-    if (p0 + tid < p1) fetch(0, p0 + tid);
+    constexpr bool kPrefetch = NPIX <= 6;   // beyond that the second set of input registers would spill
+    if (kPrefetch) fetch(0);
     for (int ei = 0; ei < nE; ei++) {
       const int jx = s_jx[ei];
       const bool stereo = (jx == k);
@@ -770,92 +787,136 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
         g.t[0] = ga.x; g.t[1] = ga.y; g.t[2] = ga.z;
         g.q[0] = ga.w; g.q[1] = gb.x; g.q[2] = gb.y; g.q[3] = gb.z;
       }
+      // per-edge base pointer; everything below is base + immediate
+      float* __restrict__ pe = ejc + (size_t)s_e[ei] * kEjComp * HW + pbase;
       float acc[32];
 #pragma unroll
       for (int l = 0; l < 32; l++) acc[l] = 0.f;
-      for (int p = p0 + tid; p < p1; p += kThreads) {
-        const float tu = n_tu, tv = n_tv, wu = n_wu, wv = n_wv;
-        {
-          int pn = p + kThreads, ein = ei;
-          if (pn >= p1) { pn = p0 + tid; ein = ei + 1; }
-          if (ein < nE) fetch(ein, pn);
-        }
-        PixLinJ L;
-        linearise_j_xy(g, K, Xs[p - p0], Ys[p - p0], Ds[p - p0], tu, tv, wu, wv, stereo, L);
-        // depth terms (:320-321, :353-354)
-        float c = L.wu_d * L.Jz_u * L.Jz_u;
-        float bz = L.wu_d * L.ru * L.Jz_u;
-        c += L.wv_d * L.Jz_v * L.Jz_v;
-        bz += L.wv_d * L.rv * L.Jz_v;
-        Cs[p - p0] += c;
-        Bs[p - p0] += bz;
-        if (!motion_only) {   // E_j for the Schur pass (streaming stores, read once by another kernel)
-          float pk[5];
-          ej_pack(L, K, pk);
-          float* dst = ejc + (size_t)s_e[ei] * kEjComp * HW + p;
+      float tu[NPIX], tv[NPIX], wu[NPIX], wv[NPIX];
 #pragma unroll
-          for (int q = 0; q < kEjComp; q++) __stcg(dst + (size_t)q * HW, pk[q]);
+      if (!kPrefetch) fetch(ei);
+#pragma unroll
+      for (int q = 0; q < NPIX; q++) { tu[q] = ntu[q]; tv[q] = ntv[q]; wu[q] = nwu[q]; wv[q] = nwv[q]; }
+      if (kPrefetch && ei + 1 < nE) fetch(ei + 1);
+#pragma unroll
+      for (int q = 0; q < NPIX; q++) {
+        const bool ok = pbase + q * kThreads < HW;
+        float Xi[4] = {px[q], py[q], 1.f, pd[q]}, Xj[4];
+        act_se3(g.t, g.q, Xi, Xj);
+        const float X = Xj[0], Y = Xj[1], h = Xj[3];
+        const bool behind = Xj[2] < DROID_MIN_DEPTH;
+        // the reference divides in double and rounds to float (:305); the IEEE-rounded float reciprocal is the same
+        // value except for double-rounding ties (~2^-29 of the inputs)
+        const float D = behind ? 0.0f : __frcp_rn(Xj[2]);
+        const float wud = behind ? 0.0f : (float)(.001 * (double)wu[q]);
+        const float wvd = behind ? 0.0f : (float)(.001 * (double)wv[q]);
+        const float fxd = K.fx * D, fyd = K.fy * D;
+        const float ru = tu[q] - (fxd * X + K.cx);                   // (:307-308)
+        const float rv = tv[q] - (fyd * Y + K.cy);
+        const float xd = X * D, yd = Y * D, hd = h * D;
+        const float Jzu = fxd * fmaf(-g.t[2], xd, g.t[0]);          // fx (t0 d - t2 x d^2)  (:319)
+        const float Jzv = fyd * fmaf(-g.t[2], yd, g.t[1]);
+        const float wuJ = wud * Jzu, wvJ = wvd * Jzv;
+        // depth terms (:320-321, :353-354)
+        Cs[q] += wuJ * Jzu + wvJ * Jzv;
+        Bs[q] += wuJ * ru + wvJ * rv;
+        if (!motion_only && ok) {   // packed E_j for the Schur and depth-update passes (streaming stores)
+          __stcg(pe + q * kThreads, stereo ? 0.f : wuJ * K.fx);
+          __stcg(pe + (size_t)HW + q * kThreads, stereo ? 0.f : wvJ * K.fy);
+          __stcg(pe + 2 * (size_t)HW + q * kThreads, xd);
+          __stcg(pe + 3 * (size_t)HW + q * kThreads, yd);
+          __stcg(pe + 4 * (size_t)HW + q * kThreads, hd);
         }
         if (!stereo) {
-          int l = 0;
-#pragma unroll
-          for (int n = 0; n < 6; n++) {
-            const float wju = L.wu * L.Jj_u[n], wjv = L.wv * L.Jj_v[n];
-#pragma unroll
-            for (int q = 0; q <= n; q++) { acc[l] += wju * L.Jj_u[q]; acc[l] += wjv * L.Jj_v[q]; l++; }
-          }
-          const float wr = L.wu * L.ru, wr2 = L.wv * L.rv;
-#pragma unroll
-          for (int n = 0; n < 6; n++) { acc[21 + n] += wr * L.Jj_u[n]; acc[21 + n] += wr2 * L.Jj_v[n]; }
+          const float xy = xd * yd;
+          const float j2u = -xd * hd, j3u = -xy, j4u = fmaf(xd, xd, 1.f), j5u = -yd;
+          const float j2v = -yd * hd, j3v = -fmaf(yd, yd, 1.f);
+          const float a = wud * fx2, b = wvd * fy2;
+          const float a0 = a * hd, a2 = a * j2u, a3 = a * j3u, a4 = a * j4u, a5 = a * j5u;
+          const float b1 = b * hd, b2 = b * j2v, b3 = b * j3v, b4 = b * xy, b5 = b * xd;
+          // Hjj lower triangle, row-major: l = n (n + 1) / 2 + q
+          acc[0] = fmaf(a0, hd, acc[0]);                                           // (0,0)
+          acc[2] = fmaf(b1, hd, acc[2]);                                           // (1,1)   (1,0) == 0
+          acc[3] = fmaf(a2, hd, acc[3]);                                           // (2,0)
+          acc[4] = fmaf(b2, hd, acc[4]);                                           // (2,1)
+          acc[5] = fmaf(a2, j2u, fmaf(b2, j2v, acc[5]));                           // (2,2)
+          acc[6] = fmaf(a3, hd, acc[6]);                                           // (3,0)
+          acc[7] = fmaf(b3, hd, acc[7]);                                           // (3,1)
+          acc[8] = fmaf(a3, j2u, fmaf(b3, j2v, acc[8]));                           // (3,2)
+          acc[9] = fmaf(a3, j3u, fmaf(b3, j3v, acc[9]));                           // (3,3)
+          acc[10] = fmaf(a4, hd, acc[10]);                                         // (4,0)
+          acc[11] = fmaf(b4, hd, acc[11]);                                         // (4,1)
+          acc[12] = fmaf(a4, j2u, fmaf(b4, j2v, acc[12]));                         // (4,2)
+          acc[13] = fmaf(a4, j3u, fmaf(b4, j3v, acc[13]));                         // (4,3)
+          acc[14] = fmaf(a4, j4u, fmaf(b4, xy, acc[14]));                          // (4,4)
+          acc[15] = fmaf(a5, hd, acc[15]);                                         // (5,0)
+          acc[16] = fmaf(b5, hd, acc[16]);                                         // (5,1)
+          acc[17] = fmaf(a5, j2u, fmaf(b5, j2v, acc[17]));                         // (5,2)
+          acc[18] = fmaf(a5, j3u, fmaf(b5, j3v, acc[18]));                         // (5,3)
+          acc[19] = fmaf(a5, j4u, fmaf(b5, xy, acc[19]));                          // (5,4)
+          acc[20] = fmaf(a5, j5u, fmaf(b5, xd, acc[20]));                          // (5,5)
+          const float cu = (wud * ru) * K.fx, cv = (wvd * rv) * K.fy;
+          acc[21] = fmaf(cu, hd, acc[21]);
+          acc[22] = fmaf(cv, hd, acc[22]);
+          acc[23] = fmaf(cu, j2u, fmaf(cv, j2v, acc[23]));
+          acc[24] = fmaf(cu, j3u, fmaf(cv, j3v, acc[24]));
+          acc[25] = fmaf(cu, j4u, fmaf(cv, xy, acc[25]));
+          acc[26] = fmaf(cu, j5u, fmaf(cv, xd, acc[26]));
         }
       }
+      // warp-level sums only (transposing butterfly: lane l ends with value l); the sum over the warps and the
+      // scatter into the system wait until the whole chunk of edges is done -- no CTA barrier per edge
       if (!stereo) {
         transpose_reduce32(acc, lane);
-        red[warp][lane] = acc[0];
-        __syncthreads();
-        if (tid < 32) {
-          float sum = 0.f;
-#pragma unroll
-          for (int w = 0; w < kThreads / 32; w++) sum += red[w][tid];
-          s_sum[tid] = sum;
-        }
-        __syncthreads();
-        if (tid < 90) {
-          const float* N = &s_g[ei][8];
-          auto Hjj = [&](int a, int b) { return a >= b ? s_sum[a * (a + 1) / 2 + b] : s_sum[b * (b + 1) / 2 + a]; };
-          float val = 0.f;
-          if (tid < 78) {
-            int n = (int)((sqrtf(8.f * tid + 1.f) - 1.f) * 0.5f);
-            while ((n + 1) * (n + 2) / 2 <= tid) n++;
-            while (n * (n + 1) / 2 > tid) n--;
-            const int mm = tid - n * (n + 1) / 2;
-            if (n < 6) {                 // Hii[n][mm] = sum_ab N[n][a] Hjj[a][b] N[mm][b]
-              for (int a = 0; a < 6; a++) {
-                float t = 0.f;
-                for (int b = 0; b < 6; b++) t = fmaf(Hjj(a, b), N[mm * 6 + b], t);
-                val = fmaf(N[n * 6 + a], t, val);
-              }
-            } else if (mm >= 6) {        // Hjj
-              val = Hjj(n - 6, mm - 6);
-            } else {                     // Hji[n-6][mm] = sum_b Hjj[n-6][b] N[mm][b]
-              for (int b = 0; b < 6; b++) val = fmaf(Hjj(n - 6, b), N[mm * 6 + b], val);
-            }
-          } else if (tid < 84) {         // vi = N vj
-            for (int a = 0; a < 6; a++) val = fmaf(N[(tid - 78) * 6 + a], s_sum[21 + a], val);
-          } else {
-            val = s_sum[21 + tid - 84];
-          }
-          int pi = k - t0, pj = jx - t0;
-          if (pi < 0 || pi >= P) pi = -1;
-          if (pj < 0 || pj >= P) pj = -1;
-          if (ppos != nullptr) {   // position in the (re-ordered) reduced system
-            if (pi >= 0) pi = ppos[pi];
-            if (pj >= 0) pj = ppos[pj];
-          }
-          scatter_edge_value(A, bvec, n6, tid, val, pi, pj);
-        }
-        __syncthreads();
+        part[ei][warp][lane] = acc[0];
       }
+    }
+    __syncthreads();
+    for (int it = tid; it < nE * 32; it += kThreads) {
+      const int ei = it >> 5, l = it & 31;
+      float sum = 0.f;
+#pragma unroll
+      for (int w = 0; w < kThreads / 32; w++) sum += part[ei][w][l];
+      s_sum[ei][l] = sum;
+    }
+    __syncthreads();
+    for (int it = tid; it < nE * 90; it += kThreads) {
+      const int ei = it / 90, l = it - ei * 90;
+      const int jx = s_jx[ei];
+      if (jx == k) continue;                     // stereo edge: depth terms only (:323,:356)
+      const float* N = &s_g[ei][8];
+      const float* ss = s_sum[ei];
+      auto Hjj = [&](int a, int b) { return a >= b ? ss[a * (a + 1) / 2 + b] : ss[b * (b + 1) / 2 + a]; };
+      float val = 0.f;
+      if (l < 78) {
+        int n = (int)((sqrtf(8.f * l + 1.f) - 1.f) * 0.5f);
+        while ((n + 1) * (n + 2) / 2 <= l) n++;
+        while (n * (n + 1) / 2 > l) n--;
+        const int mm = l - n * (n + 1) / 2;
+        if (n < 6) {                 // Hii[n][mm] = sum_ab N[n][a] Hjj[a][b] N[mm][b]
+          for (int a = 0; a < 6; a++) {
+            float t = 0.f;
+            for (int b = 0; b < 6; b++) t = fmaf(Hjj(a, b), N[mm * 6 + b], t);
+            val = fmaf(N[n * 6 + a], t, val);
+          }
+        } else if (mm >= 6) {        // Hjj
+          val = Hjj(n - 6, mm - 6);
+        } else {                     // Hji[n-6][mm] = sum_b Hjj[n-6][b] N[mm][b]
+          for (int b = 0; b < 6; b++) val = fmaf(Hjj(n - 6, b), N[mm * 6 + b], val);
+        }
+      } else if (l < 84) {           // vi = N vj
+        for (int a = 0; a < 6; a++) val = fmaf(N[(l - 78) * 6 + a], ss[21 + a], val);
+      } else {
+        val = ss[21 + l - 84];
+      }
+      int pi = k - t0, pj = jx - t0;
+      if (pi < 0 || pi >= P) pi = -1;
+      if (pj < 0 || pj >= P) pj = -1;
+      if (ppos != nullptr) {   // position in the (re-ordered) reduced system
+        if (pi >= 0) pi = ppos[pi];
+        if (pj >= 0) pj = ppos[pj];
+      }
+      scatter_edge_value(A, bvec, n6, l, val, pi, pj);
     }
   }
   if (motion_only) return;
@@ -863,12 +924,16 @@ __global__ void __launch_bounds__(kThreads) ba_accum_kernel(
   const float alpha = 0.05f;
   const float* __restrict__ ds = disps_sens + (size_t)k * HW;
   const float* __restrict__ et = eta + (size_t)m * HW;
-  for (int p = p0 + tid; p < p1; p += kThreads) {
-    const float mk = ds[p] > 0.f ? 1.0f : 0.0f;
-    const float C = Cs[p - p0] + mk * alpha + (1 - mk) * et[p];
-    const float w = Bs[p - p0] - mk * alpha * (Ds[p - p0] - ds[p]);
-    Qo[(size_t)m * HW + p] = (float)(1.0 / (double)C);
-    Wo[(size_t)m * HW + p] = w;
+#pragma unroll
+  for (int q = 0; q < NPIX; q++) {
+    const int p = pbase + q * kThreads;
+    if (p < HW) {
+      const float mk = ds[p] > 0.f ? 1.0f : 0.0f;
+      const float C = Cs[q] + mk * alpha + (1 - mk) * et[p];
+      const float w = Bs[q] - mk * alpha * (pd[q] - ds[p]);
+      Qo[(size_t)m * HW + p] = (float)(1.0 / (double)C);
+      Wo[(size_t)m * HW + p] = w;
+    }
   }
 }
 
@@ -1461,7 +1526,6 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
 
   if (dc.first(kOnceBa)) {
     cudaFuncSetAttribute(ba_schur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSchurSmemBytes);
-    cudaFuncSetAttribute(ba_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * kSlabMax * (int)sizeof(float));
     cudaStreamCreateWithFlags(&dc.ba_s2, cudaStreamNonBlocking);
     cudaEventCreateWithFlags(&dc.ba_fork, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&dc.ba_join, cudaEventDisableTiming);
@@ -1511,10 +1575,38 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     if (p->n_edges > 0 && Mgrid > 0) {
       {
         ProfScope ps(DROID_PROF_BA_ACCUM, st);
-        DROID_LAUNCH ba_accum_kernel<<<dim3(S, Mgrid), kThreads, 5 * (size_t)slab * sizeof(float), st>>>(
-            disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, w.gij, w.status, w.kx,
-            w.eptr, w.eidx, w.Q, w.W, w.A, bvec, HW, p->wd, slab, p->t0, P, p->n_eta, p->motion_only,
-            frame_lo, frame_hi, ppos, w.ejc, p->edge_row);
+        // pixels per thread: the slab of the CUDA-core kernels rounded up to one of the instantiated sizes
+        // pixels per thread: as many as the slab of the CUDA-core kernels allows (fewer, smaller CTAs when few frames
+        // have to fill the SMs), at most 6 (the next edge's inputs are prefetched into a second register set), and
+        // among the candidates the one that wastes the fewest padded pixels (2560 = 2 x 5 x 256, 3072 = 2 x 6 x 256)
+        static const int npix_env = []() { const char* e = getenv("DROID_ACCUM_NPIX"); return e ? atoi(e) : 0; }();
+        int want = (slab + kThreads - 1) / kThreads;
+        if (npix_env > 0) {
+          want = npix_env;
+        } else {
+          const int cap = want < 6 ? want : 6;
+          int best = cap, best_waste = 1 << 30;
+          for (int np = cap; np >= (cap + 1) / 2 && np >= 1; np--) {
+            const int tile = kThreads * np;
+            const int waste = (HW + tile - 1) / tile * tile - HW;
+            if (waste < best_waste) { best_waste = waste; best = np; }
+          }
+          want = best;
+        }
+#define BA_ACCUM_LAUNCH(NP)                                                                                          \
+  DROID_LAUNCH ba_accum_kernel<NP><<<dim3((HW + kThreads * NP - 1) / (kThreads * NP), Mgrid), kThreads, 0, st>>>(    \
+      disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, w.gij, w.status, w.kx, w.eptr, w.eidx, w.Q, w.W, \
+      w.A, bvec, HW, p->wd, p->t0, P, p->n_eta, p->motion_only, frame_lo, frame_hi, ppos, w.ejc, p->edge_row)
+        if (want <= 1) BA_ACCUM_LAUNCH(1);
+        else if (want <= 2) BA_ACCUM_LAUNCH(2);
+        else if (want <= 3) BA_ACCUM_LAUNCH(3);
+        else if (want <= 4) BA_ACCUM_LAUNCH(4);
+        else if (want <= 5) BA_ACCUM_LAUNCH(5);
+        else if (want <= 6) BA_ACCUM_LAUNCH(6);
+        else if (want <= 8) BA_ACCUM_LAUNCH(8);
+        else if (want <= 10) BA_ACCUM_LAUNCH(10);
+        else BA_ACCUM_LAUNCH(12);
+#undef BA_ACCUM_LAUNCH
       }
       if (!p->motion_only) {
         ProfScope ps(DROID_PROF_BA_SCHUR, st);
