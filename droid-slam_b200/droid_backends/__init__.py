@@ -23,6 +23,7 @@ _DT = {torch.float32: _F32, torch.float16: _F16, torch.float64: _F64}
 _ERRORS = {
     -1: "invalid argument", -2: "unsupported dtype", -3: "workspace too small",
     -4: "CUDA launch failed", -5: "not implemented", -6: "device-side input validation failed",
+    -7: "size exceeds the built-in scratch of a no-alloc entry point",
 }
 
 REDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t,
@@ -80,7 +81,8 @@ C_ABI_SYMBOLS = [
     "droid_version", "droid_last_cuda_error", "droid_launch_count", "droid_prof_enable", "droid_prof_read", "droid_corr_index_forward", "droid_corr_index_backward",
     "droid_corr_index_pyramid", "droid_altcorr_forward", "droid_altcorr_backward",
     "droid_altcorr_forward_indexed", "droid_corr_build", "droid_corr_build_workspace_bytes",
-    "droid_frame_distance", "droid_frame_distance_workspace_bytes", "droid_frame_distance_ws", "droid_projmap", "droid_reproject", "droid_iproj", "droid_depth_filter",
+    "droid_frame_distance", "droid_frame_distance_workspace_bytes", "droid_frame_distance_ws",
+    "droid_frame_distance_noalloc_max_pixels", "droid_frame_distance_noalloc", "droid_projmap", "droid_reproject", "droid_iproj", "droid_depth_filter",
     "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_solve_env_f64",
     "droid_chol_workspace_bytes", "droid_chol_solve_chains_f64", "droid_chol_chains_workspace_bytes",
     "droid_proximity_workspace_bytes", "droid_proximity_mandatory_count", "droid_proximity_edges",

@@ -35,6 +35,7 @@ extern "C" {
 #define DROID_ERR_CUDA (-4) /* a launch failed; see droid_last_cuda_error() */
 #define DROID_ERR_NOT_IMPLEMENTED (-5)
 #define DROID_ERR_BA_INPUT (-6) /* droid_ba with DROID_BA_FLAG_CHECK: the device-side validation failed (status word) */
+#define DROID_ERR_STATIC_SCRATCH_TOO_SMALL (-7) /* a *_noalloc entry point: size beyond its built-in scratch */
 
 #define DROID_DTYPE_F32 0
 #define DROID_DTYPE_F16 1
@@ -135,6 +136,22 @@ size_t droid_frame_distance_workspace_bytes(int ht, int wd);
 int droid_frame_distance_ws(const float* poses, const float* disps, const float* intrinsics,
                             const int64_t* ii, const int64_t* jj, float* dist, int n, int ht, int wd,
                             float beta, void* workspace, size_t workspace_bytes, void* stream);
+
+/* frame_distance WITHOUT any allocation and without a caller-supplied workspace.  This entry point has NO
+ * counterpart in the reference: it was added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result, bit for
+ * bit, as droid_frame_distance / droid_frame_distance_ws.  The scratch of the workspace path lives in a file-scope
+ * static __device__ array of DROID_FRAME_DISTANCE_NOALLOC_MAX_PIXELS * 16 + 256 bytes (257 KB, held by every GPU
+ * that loads the library until exit); ht * wd beyond that maximum returns DROID_ERR_STATIC_SCRATCH_TOO_SMALL.  The
+ * call performs no cudaMalloc / cudaFree and calls no allocating library routine; the caller passes inputs and
+ * outputs as for droid_frame_distance.  All calls on a device SHARE the array (it keeps the last call's contents;
+ * every call rewrites all of what it reads, so nothing needs clearing): calls that overlap on the GPU -- different
+ * streams, or graphs replayed concurrently -- race on it and must be serialised by the caller. */
+#define DROID_FRAME_DISTANCE_NOALLOC_MAX_PIXELS 16384
+int droid_frame_distance_noalloc_max_pixels(void);
+int droid_frame_distance_noalloc(const float* poses, const float* disps, const float* intrinsics,
+                                 const int64_t* ii, const int64_t* jj, float* dist, int n, int ht, int wd,
+                                 float beta, void* stream);
 
 /* projmap (src/droid.cpp:139-154, src/droid_kernels.cu:427-516,1463-1488).
  *   coords [n,ht,wd,3] (channel 2 = 0), valid [n,ht,wd,1]; both fully written. */
