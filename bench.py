@@ -370,24 +370,37 @@ def run_b200(args, world, rank, local):
     traffic = {}
     try:
         if p["n"] == 1000 and len(p["ii"]) == 20862 and world == 1:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
     except Exception:
         traffic = {}
     for k in table:
         if k in traffic:
             table[k]["traffic"] = int(traffic[k])
+    # `roofline`: the dominant THROUGHPUT kernel (accumulation / Schur / depth update, whichever is longest in this run)
+    # against the roof that bounds it.  The longest PHASE is the fp64 factorisation, a latency chain with no bandwidth or
+    # flop roof to be a fraction of: it is reported beside it under roofline.longest_phase (ns per pivot) and in the table.
     dom = max((k for k in ("ba_accum", "ba_schur", "ba_update") if k in table), key=lambda k: table[k]["ms"])
+    longest = max(table, key=lambda k: table[k]["ms"])
+    iter_traffic = sum(int(traffic[k]) for k in ("ba_accum", "ba_schur", "ba_update") if k in traffic) if traffic else None
     roof = {"kernel": dom, "bound": table[dom]["bound"], "achieved": table[dom]["achieved"], "peak": table[dom]["peak"],
             "unit": table[dom]["unit"], "frac": table[dom]["frac"], "traffic": table[dom].get("traffic"),
             "traffic_source": traffic.get("source") if table[dom].get("traffic") else None,
             "peak_source": ("measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)") +
                            ("; tf32 = bf16_tflops / 2" if table[dom]["bound"] == "tensor" else ""),
-            "ms_per_launch": table[dom]["ms"], "phases": table,
+            "ms_per_launch": table[dom]["ms"],
+            "longest_phase": {"kernel": longest, "ms": table[longest]["ms"], "share_of_iteration": table[longest]["ms"] / (ms / iters),
+                              "bound": table[longest]["bound"],
+                              **({"ns_per_pivot": table[longest]["ns_per_pivot"]} if "ns_per_pivot" in table[longest] else {})},
+            "phases": table,
             # the whole Gauss-Newton iteration against SURVEY 8(d)'s compulsory traffic (1.0 GB at C4): what an ideal
-            # single-pass BA would be bound by; the Schur Gram product and the fp64 factorisation keep it far from that
-            "iteration": {"algorithmic_bytes": int(alg["iter_bytes"]), "ms": ms / iters,
+            # single-pass BA would be bound by; the Schur Gram product and the fp64 factorisation keep it far from that.
+            # dram_bytes = what the three streaming kernels really move per iteration (ncu), the packed E_j stream
+            # written once and read twice included
+            "iteration": {"algorithmic_bytes": int(alg["iter_bytes"]), "dram_bytes": iter_traffic, "ms": ms / iters,
                           "achieved": alg["iter_bytes"] / (ms / iters * 1e-3) / 1e9, "unit": "GB/s",
                           "frac": alg["iter_bytes"] / (ms / iters * 1e-3) / 1e9 / hbm_peak}}
+    if "ba_schur" in table:
+        table["ba_schur"]["issued_over_algorithmic_flops"] = alg["ba_schur_issued_flops"] / max(alg["ba_schur_flops"], 1)
     line = {
         "metric": "global BA iters/s @1000 KF", "value": value, "unit": "iters/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
