@@ -295,10 +295,11 @@ struct ChainArgs {
   double* scr;            // scratch for C[r][c], r >= sep and c >= sep (nullptr: update A in place)
   int lds;
 };
-static constexpr int kMaxChains = 8;
-struct Ranges {            // range c = [b[c], b[c+1]), c = 0..k; ranges 0..k-1 are the chains, range k the separator
-  int k;
-  int b[kMaxChains + 2];
+static constexpr int kMaxChains = 8;                  // ranges factorised concurrently (one pair of streams each)
+static constexpr int kMaxRanges = 2 * kMaxChains;     // chains + separators of all levels
+struct Ranges {            // range c = [b[c], b[c+1]), c = 0..k, in elimination-tree layout: all ranges of level 0 (the
+  int k;                   // chains), then level 1, ...; a range is coupled only to ranges of HIGHER levels
+  int b[kMaxRanges + 2];
 };
 
 __global__ void __launch_bounds__(kPanelThreads, 1) chol_panel_kernel(double* __restrict__ A, int n, int j0, int jb,
@@ -636,6 +637,11 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
       for (int b = 0; b < F * 4; b += 2) {
         const int c = (b >> 2) * 64 + ((b >> 1) & 1) * 32 + tx * 2;
         if (c > cmax || in_hole(c0 + c)) continue;
+        // Ranges of one level run concurrently and may enumerate the same tile of a higher-level block; structurally
+        // only one of them has a non-zero update for a given element (the other's operand rows are exactly zero), so
+        // an element whose update is exactly 0 is left alone instead of being written back unchanged (a lost update
+        // for the range that really changes it).
+        if (acc[a][b] == 0.0 && acc[a][b + 1] == 0.0) continue;
         double* d2 = c_ptr(i0 + r, c0 + c);
         if (c + 1 <= cmax) {
           *reinterpret_cast<double2*>(d2) = make_double2(cv[b] - acc[a][b], cv[b + 1] - acc[a][b + 1]);
@@ -652,7 +658,7 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
 #pragma unroll
       for (int b = 0; b < F * 4; b++) {
         const int c = (b >> 2) * 64 + ((b >> 1) & 1) * 32 + tx * 2 + (b & 1);
-        if (c <= cmax) dst[c] = cv[b] - acc[a][b];
+        if (c <= cmax && acc[a][b] != 0.0) dst[c] = cv[b] - acc[a][b];
       }
     }
   }
@@ -849,9 +855,12 @@ static constexpr int kBwdPThreads = 512;
 static constexpr int kBwdLd = 66;     // row stride of a staged 64x64 block (16-byte rows, spreads the banks)
 static size_t bwd_persist_smem(int n) { return ((size_t)n + 64 + 2 * 64 * kBwdLd + 64 + 64) * sizeof(double); }
 
-// One CTA sweeps one range (rows [b[c], b[c+1]), blocks of 64 rows counted from the range start).  The separator
-// (c0 = k, one CTA) goes first and also subtracts its rows' contributions from the y entries of all chains; the
-// chains (c0 = 0, k CTAs) then run concurrently, each touching only its own columns.
+// One CTA sweeps one range (rows [b[c], b[c+1]), blocks of 64 rows counted from the range start).  The launches go
+// down the elimination tree: the ranges of the top level first, the chains (level 0) last; the CTAs of one launch are
+// the ranges of one level (c0 = first range of the level) and run concurrently.  A range keeps its OWN part of y in
+// shared memory; the contributions of its rows to the y entries of the (lower-level) ranges they reach into go
+// straight to global memory -- structurally every such entry is touched by one range of the level only, and a
+// contribution that is exactly zero is not written, so that a block of rows shared by two ranges cannot lose an update.
 // linv: rows of the inverse transposed diagonal blocks (written by the panel kernels' identity CTA): x_blk = L^-T y_blk
 // is then a 64x64 matrix-vector product (8 threads per row + a 3-step shuffle reduction) instead of a 64-step chain of
 // dependent shuffle + DFMA; without it the block is solved by in-warp back-substitution on the diagonal block itself.
@@ -870,8 +879,8 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
   const int rc = c0 + blockIdx.x;                          // the range this CTA sweeps
   const int rbeg = rg.b[rc], rend = rg.b[rc + 1];
   if (rend <= rbeg) return;
-  const int sg0 = rc == rg.k ? 0 : rc;                     // column ranges its rows reach into: all / its own
-  const int ylo = rg.b[sg0];
+  const int sg0 = 0;                                       // column ranges its rows may reach into: every earlier one
+  const int ylo = rbeg;                                    // ys[] holds the own range only
   const int nblk = (rend - rbeg + 63) >> 6;
   auto load_diag = [&](int blk, int buf) {
     const int o = rbeg + (blk << 6), jb = min(64, rend - o);
@@ -966,7 +975,9 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
           s3 = fma(col[(size_t)(r + 3) * n], xs[r + 3], s3);
         }
         for (; r < jb; r++) s0 = fma(col[(size_t)r * n], xs[r], s0);
-        ys[c] -= (s0 + s1) + (s2 + s3);
+        const double sum = (s0 + s1) + (s2 + s3);
+        if (sg == rc) ys[c] -= sum;
+        else if (sum != 0.0) y[c] -= sum;
       }
     }
   }
@@ -1038,9 +1049,18 @@ static size_t chol_ws_head(int n, int nchains) {
 // rows of the inverse transposed 64x64 diagonal blocks, one row of 64 doubles per matrix row
 static size_t chol_ws_linv(int n) { return ((size_t)(n > 0 ? n : 0) * 64 * sizeof(double) + 255) / 256 * 256; }
 
+// scratch of the levels whose ranges run concurrently: one (S + 1) x S block per level, S = rows behind the level;
+// the blocks shrink from level to level, so twice the first one bounds their sum (checked at run time)
+extern "C" size_t droid_chol_tree_workspace_bytes(int n, int nranges, int sep_rows) {
+  const size_t scr = nranges > 2 ? 2 * (size_t)(sep_rows + 1) * (size_t)sep_rows * sizeof(double) : 0;
+  return chol_ws_head(n, nranges > 0 ? nranges - 1 : 0) + chol_ws_linv(n) + scr;
+}
+
+// chains + one flat separator: any chain may touch any separator row, so every chain but the first gets a PRIVATE
+// scratch copy of the separator block
 extern "C" size_t droid_chol_chains_workspace_bytes(int n, int nchains, int sep_rows) {
   const size_t scr = nchains > 1 ? (size_t)(nchains - 1) * (size_t)(sep_rows + 1) * (size_t)sep_rows * sizeof(double) : 0;
-  return chol_ws_head(n, nchains) + chol_ws_linv(n) + scr;
+  return chol_ws_head(n, nchains > 0 ? nchains : 0) + chol_ws_linv(n) + scr;
 }
 
 extern "C" size_t droid_chol_workspace_bytes(int n) { return droid_chol_chains_workspace_bytes(n, 0, 0); }
@@ -1078,18 +1098,50 @@ struct ChainState {
 };
 }  // namespace
 
+static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_dev, int nranges,
+                                const int* range_end, int nlevels, const int* level_first, int* info_dev,
+                                void* workspace, size_t workspace_bytes, void* stream, bool private_scr);
+
 extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const int* firstc_dev, int nchains,
                                            const int* chain_end, int* info_dev, void* workspace,
                                            size_t workspace_bytes, void* stream) {
+  if (nchains < 0 || nchains > kMaxChains || (nchains > 0 && (!chain_end || !firstc_dev))) return DROID_ERR_INVALID_ARGUMENT;
+  // chains + ONE separator = a two-level tree (a single range when there are no chains)
+  int range_end[kMaxChains + 1], level_first[3] = {0, nchains, nchains + 1};
+  for (int c = 0; c < nchains; c++) range_end[c] = chain_end[c];
+  range_end[nchains] = n;
+  if (nchains == 0) { level_first[1] = 1; }
+  return chol_solve_tree_impl(A, b, n, firstc_dev, nchains + 1, range_end, nchains == 0 ? 1 : 2, level_first, info_dev,
+                              workspace, workspace_bytes, stream, true);
+}
+
+extern "C" int droid_chol_solve_tree_f64(double* A, double* b, int n, const int* firstc_dev, int nranges,
+                                         const int* range_end, int nlevels, const int* level_first, int* info_dev,
+                                         void* workspace, size_t workspace_bytes, void* stream) {
+  return chol_solve_tree_impl(A, b, n, firstc_dev, nranges, range_end, nlevels, level_first, info_dev, workspace,
+                              workspace_bytes, stream, false);
+}
+
+// private_scr: every range of a level but the first accumulates its updates of the rows behind the level in a scratch
+// copy of its own (general coupling); otherwise ranges at odd positions share ONE copy per level (path structure).
+static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_dev, int nranges,
+                                const int* range_end, int nlevels, const int* level_first, int* info_dev,
+                                void* workspace, size_t workspace_bytes, void* stream, bool private_scr) {
   if (n < 0 || !info_dev) return DROID_ERR_INVALID_ARGUMENT;
   if (n == 0) return DROID_OK;
   if (!A || !b) return DROID_ERR_INVALID_ARGUMENT;
   if (b != A + (size_t)n * n) return DROID_ERR_INVALID_ARGUMENT;  // rhs must be row n of A
-  if (nchains < 0 || nchains > kMaxChains || (nchains > 0 && (!chain_end || !firstc_dev))) return DROID_ERR_INVALID_ARGUMENT;
+  if (nranges < 1 || nranges > kMaxRanges || !range_end || nlevels < 1 || nlevels > nranges || !level_first ||
+      (nranges > 1 && !firstc_dev))
+    return DROID_ERR_INVALID_ARGUMENT;
+  if (level_first[0] != 0 || level_first[nlevels] != nranges || range_end[nranges - 1] != n) return DROID_ERR_INVALID_ARGUMENT;
+  for (int l = 0; l < nlevels; l++)
+    if (level_first[l + 1] <= level_first[l] || level_first[l + 1] - level_first[l] > kMaxChains) return DROID_ERR_INVALID_ARGUMENT;
+  const int nchains = nranges - 1;      // ranges besides the last one (sizes the per-range tables: nchains + 1 entries)
   cudaStream_t st = (cudaStream_t)stream;
   cudaMemsetAsync(info_dev, 0, sizeof(int), st);
   if (n <= kSmallMax) {
-    if (nchains > 0) return DROID_ERR_INVALID_ARGUMENT;
+    if (nranges > 1) return DROID_ERR_INVALID_ARGUMENT;
     if (dev_ctx().first(kOnceCholSmall))
       cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmemMax);
     const size_t smem = chol_small_smem(n);
@@ -1125,20 +1177,30 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
   }
   const bool vec = (n % 2 == 0) && (((uintptr_t)A & 15) == 0);
   const int nb = (n + 63) / 64;
-  // ranges: chains [chain_end[c-1], chain_end[c]) and the separator [chain_end[nchains-1], n)
+  // ranges in elimination-tree layout: range r = [range_end[r-1], range_end[r]), levels = runs of consecutive ranges
   Ranges rg;
   rg.k = nchains;
   rg.b[0] = 0;
-  for (int c = 0; c < nchains; c++) {
-    const int e = chain_end[c];
-    if (e <= rg.b[c] || e >= n || (e & 1)) return DROID_ERR_INVALID_ARGUMENT;
+  for (int c = 0; c < nranges; c++) {
+    const int e = range_end[c];
+    if (e <= rg.b[c] || e > n || (e & 1 && e != n)) return DROID_ERR_INVALID_ARGUMENT;
     rg.b[c + 1] = e;
   }
-  rg.b[nchains + 1] = n;
-  const int sep = rg.b[nchains], seprows = n - sep;
-  if (nchains > 0 && (!vec || n > kBwdPersistMax)) return DROID_ERR_INVALID_ARGUMENT;
-  if (!workspace || workspace_bytes < droid_chol_chains_workspace_bytes(n, nchains, nchains > 1 ? seprows : 0))
-    return DROID_ERR_WORKSPACE_TOO_SMALL;
+  const int sep = nlevels > 1 ? rg.b[level_first[1]] : n, seprows = n - sep;   // rows behind level 0
+  if (nranges > 1 && (!vec || n > kBwdPersistMax)) return DROID_ERR_INVALID_ARGUMENT;
+  const size_t ws_head = chol_ws_head(n, nchains) + chol_ws_linv(n);
+  if (!workspace || workspace_bytes < ws_head) return DROID_ERR_WORKSPACE_TOO_SMALL;
+  // scratch blocks of every level that has more than one range and something behind it: one (shared by the ranges at
+  // odd positions) or one per range but the first
+  size_t scr_off[kMaxRanges + 1] = {}, scr_stride[kMaxRanges + 1] = {}, scr_total = 0;
+  for (int l = 0; l + 1 < nlevels; l++) {
+    scr_off[l] = scr_total;
+    const size_t S = (size_t)(n - rg.b[level_first[l + 1]]);
+    const int cnt = level_first[l + 1] - level_first[l];
+    scr_stride[l] = (S + 1) * S;
+    if (cnt > 1) scr_total += (private_scr ? (size_t)(cnt - 1) : 1) * scr_stride[l];
+  }
+  if (workspace_bytes < ws_head + scr_total * sizeof(double)) return DROID_ERR_WORKSPACE_TOO_SMALL;
   // Envelope variant: the launches keep their dense shapes (the host never learns the band structure), CTAs whose
   // rows or columns lie outside the envelope return at once.  64x64 tiles throughout: the active window is narrow.
   int* arrive = reinterpret_cast<int*>(workspace);
@@ -1151,14 +1213,13 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
     DROID_LAUNCH chol_env_kernel<<<1, 1024, 0, st>>>(firstc_dev, n, rg, hi64, lo64);
   }
   double* scr = nullptr;
-  const size_t scr_stride = (size_t)(seprows + 1) * (size_t)seprows;
   // the backward sweep of envelope / chain systems runs in one persistent CTA per range and takes the diagonal blocks'
   // inverses from the panel kernels (dense systems of this size keep the multi-CTA sweep: 0.9 vs 2.0 ms at n = 5994)
   const bool persist_bwd = vec && firstc_dev != nullptr && n <= kBwdPersistMax;
   double* linv = persist_bwd ? reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(workspace) + chol_ws_head(n, nchains)) : nullptr;
-  if (nchains > 1) {
+  if (scr_total > 0) {
     scr = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(workspace) + chol_ws_head(n, nchains) + chol_ws_linv(n));
-    cudaMemsetAsync(scr, 0, (size_t)(nchains - 1) * scr_stride * sizeof(double), st);
+    cudaMemsetAsync(scr, 0, scr_total * sizeof(double), st);
   }
   // Look-ahead: while the bulk of trailing update J runs on the chain's main stream, a second (high-priority) stream
   // updates the next panel's 128 columns first and factorises them, so the serial panel chain hides behind the
@@ -1245,14 +1306,21 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
       if (cs.prof) prof_mark(DROID_PROF_CHOL_SYRK, false, m);
     }
   };
-  auto open_range = [&](ChainState& cs, int c, cudaStream_t m, ChainCtx* cx, bool prof) {
+  // range c at position `idx` of level `lv`: it must leave alone the later ranges of its own level (the hole) and sends
+  // its updates of everything behind the level either to A (even idx) or to the level's scratch block (odd idx): two
+  // ranges of the same parity never touch the same higher-level block (neighbours in the path order alternate)
+  auto open_range = [&](ChainState& cs, int c, int lv, int idx, cudaStream_t m, ChainCtx* cx, bool prof) {
     cs.J = rg.b[c]; cs.Jend = rg.b[c + 1];
     cs.main = m; cs.cx = cx; cs.prof = prof;
     cs.finished = cs.J >= cs.Jend;
-    cs.ca.hole_lo = cs.ca.hole_hi = 0; cs.ca.sep = sep; cs.ca.scr = nullptr; cs.ca.lds = seprows;
-    if (c < nchains) {
-      cs.ca.hole_lo = rg.b[c + 1]; cs.ca.hole_hi = sep;
-      if (c > 0) cs.ca.scr = scr + (size_t)(c - 1) * scr_stride;
+    const int behind = lv + 1 < nlevels ? rg.b[level_first[lv + 1]] : n;     // first row behind this level
+    cs.ca.hole_lo = cs.ca.hole_hi = 0; cs.ca.sep = behind; cs.ca.scr = nullptr; cs.ca.lds = n - behind;
+    if (lv + 1 < nlevels) {
+      cs.ca.hole_lo = rg.b[c + 1]; cs.ca.hole_hi = behind;
+      if (scr != nullptr && level_first[lv + 1] - level_first[lv] > 1) {
+        if (private_scr) { if (idx > 0) cs.ca.scr = scr + scr_off[lv] + (size_t)(idx - 1) * scr_stride[lv]; }
+        else if (idx & 1) cs.ca.scr = scr + scr_off[lv];
+      }
     }
     cs.hi64 = hi64 ? hi64 + (size_t)c * nb : nullptr;
     cs.arrive = arrive + (size_t)c * (nb + 1);
@@ -1270,44 +1338,48 @@ extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const in
       cs.on_side = false;
     }
   };
-  if (nchains > 0) {
+  for (int lv = 0; lv < nlevels; lv++) {
+    const int r_lo = level_first[lv], cnt = level_first[lv + 1] - r_lo;
     ChainState cs[kMaxChains];
+    if (cnt == 1) {
+      open_range(cs[0], r_lo, lv, 0, st, &ctx[0], true);
+      while (!cs[0].finished) step(cs[0]);
+      close_range(cs[0]);
+      continue;
+    }
     cudaEventRecord(ev_start, st);
-    for (int c = 0; c < nchains; c++) {
+    for (int c = 0; c < cnt; c++) {
       cudaStream_t m = c == 0 ? st : ctx[c].main;
       if (c > 0) cudaStreamWaitEvent(m, ev_start, 0);
-      open_range(cs[c], c, m, &ctx[c], c == 0);
+      open_range(cs[c], r_lo + c, lv, c, m, &ctx[c], c == 0);
     }
-    // the chains' launches are issued round-robin so that all of them are in flight from the start
+    // the ranges' launches are issued round-robin so that all of them are in flight from the start
     for (bool any = true; any;) {
       any = false;
-      for (int c = 0; c < nchains; c++) {
+      for (int c = 0; c < cnt; c++) {
         if (cs[c].finished) continue;
         step(cs[c]);
         any = true;
       }
     }
-    for (int c = 0; c < nchains; c++) {
+    for (int c = 0; c < cnt; c++) {
       close_range(cs[c]);
       if (c > 0) {
         cudaEventRecord(ctx[c].done, cs[c].main);
         cudaStreamWaitEvent(st, ctx[c].done, 0);
       }
     }
-    if (nchains > 1)
-      DROID_LAUNCH chol_merge_kernel<<<seprows + 1, 256, 0, st>>>(A, n, sep, scr, nchains - 1, scr_stride, seprows);
-  }
-  {
-    ChainState cs;
-    open_range(cs, nchains, st, &ctx[0], true);
-    while (!cs.finished) step(cs);
-    close_range(cs);
+    if (lv + 1 < nlevels && scr != nullptr) {
+      const int behind = rg.b[level_first[lv + 1]];
+      DROID_LAUNCH chol_merge_kernel<<<n - behind + 1, 256, 0, st>>>(A, n, behind, scr + scr_off[lv], private_scr ? cnt - 1 : 1,
+                                                                       scr_stride[lv], n - behind);
+    }
   }
   ProfScope psb(DROID_PROF_CHOL_BWD, st);
   if (persist_bwd) {
-    DROID_LAUNCH chol_bwd_persist_kernel<<<1, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg, nchains, linv);
-    if (nchains > 0)
-      DROID_LAUNCH chol_bwd_persist_kernel<<<nchains, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg, 0, linv);
+    for (int lv = nlevels - 1; lv >= 0; lv--)
+      DROID_LAUNCH chol_bwd_persist_kernel<<<level_first[lv + 1] - level_first[lv], kBwdPThreads, bwd_persist_smem(n), st>>>(
+          A, n, lo64, rg, level_first[lv], linv);
     return check_launch();
   }
   for (int J0 = ((n - 1) / SB) * SB; J0 >= 0; J0 -= SB) {

@@ -64,6 +64,7 @@ def _load():
     lib.droid_ba_workspace_bytes.argtypes = [ctypes.POINTER(BaParams)]
     lib.droid_chol_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_chol_chains_workspace_bytes.restype = ctypes.c_size_t
+    lib.droid_chol_tree_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_corr_build_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_launch_count.restype = ctypes.c_ulonglong
     lib.droid_proximity_workspace_bytes.restype = ctypes.c_size_t
@@ -85,6 +86,7 @@ C_ABI_SYMBOLS = [
     "droid_frame_distance_noalloc_max_pixels", "droid_frame_distance_noalloc", "droid_projmap", "droid_reproject", "droid_iproj", "droid_depth_filter",
     "droid_ba_workspace_bytes", "droid_ba", "droid_chol_solve_f64", "droid_chol_solve_env_f64",
     "droid_chol_workspace_bytes", "droid_chol_solve_chains_f64", "droid_chol_chains_workspace_bytes",
+    "droid_chol_solve_tree_f64", "droid_chol_tree_workspace_bytes",
     "droid_proximity_workspace_bytes", "droid_proximity_mandatory_count", "droid_proximity_edges",
     "droid_filter_edges_workspace_bytes", "droid_filter_repeated_edges",
     "droid_cvx_upsample", "droid_scatter_mean_workspace_bytes", "droid_scatter_mean",
@@ -595,6 +597,29 @@ def ba_chains(device=None):
     if st[8] != 0x0b200c0d:
         return []
     return st[19:19 + st[18]]
+
+
+def chol_solve_tree(A, b, first, range_end, level_first):
+    """Extension (tests/bench): droid_chol_solve_tree_f64 -- SPD solve over an elimination tree of column ranges.
+    first: CUDA int32 [len(range_end), n]; range_end / level_first: lists of ints (see include/droid_b200.h)."""
+    n = A.shape[0]
+    nr, nl = len(range_end), len(level_first) - 1
+    if first.dtype != torch.int32 or first.numel() != nr * n or not first.is_cuda:
+        raise RuntimeError("first must be a CUDA int32 tensor of len(range_end) * n entries")
+    with torch.cuda.device(A.device):
+        buf = torch.empty((n * n + n,), dtype=torch.float64, device=A.device)
+        buf[: n * n] = A.reshape(-1)
+        buf[n * n:] = b.reshape(-1)
+        info = torch.zeros((1,), dtype=torch.int32, device=A.device)
+        sep_rows = n - int(range_end[level_first[1] - 1]) if nl > 1 else 0
+        wsb = int(_lib.droid_chol_tree_workspace_bytes(n, nr, sep_rows))
+        ws = torch.empty((wsb,), dtype=torch.uint8, device=A.device)
+        ends = (ctypes.c_int * nr)(*[int(e) for e in range_end])
+        lf = (ctypes.c_int * (nl + 1))(*[int(e) for e in level_first])
+        _check(_lib.droid_chol_solve_tree_f64(_p(buf), ctypes.c_void_p(buf.data_ptr() + 8 * n * n), n, _p(first.contiguous()),
+                                              nr, ends, nl, lf, _p(info), _p(ws), ctypes.c_size_t(wsb), _stream(A)),
+               "chol_solve_tree")
+    return buf[n * n:].clone(), info
 
 
 def chol_solve(A, b, first=None, chain_end=None):

@@ -304,6 +304,23 @@ int droid_chol_solve_chains_f64(double* A, double* b, int n, const int* firstc_d
                                 void* stream);
 size_t droid_chol_chains_workspace_bytes(int n, int nchains, int sep_rows);
 
+/* The general form: an ELIMINATION TREE of column ranges (nested dissection).  The columns split into nranges ranges
+ * [range_end[r-1], range_end[r]) (host array, even increasing values, range_end[nranges-1] = n), laid out level by
+ * level: level l holds the ranges level_first[l] .. level_first[l+1]-1 (host array of nlevels + 1 entries,
+ * level_first[0] = 0, level_first[nlevels] = nranges, at most 8 ranges per level).  Ranges of one level are
+ * structurally decoupled from each other and are factorised CONCURRENTLY; a range is coupled only to ranges of higher
+ * levels, and two ranges of one level whose positions in the level have the same parity must not be coupled to the same
+ * higher-level range (true for the separators of a path graph in path order: neighbours alternate).  The levels are
+ * factorised one after the other; the backward sweep walks them in reverse.  firstc_dev as above, one row of n entries
+ * per range.  Chains + one separator is the two-level case; the reduced camera system of a long trajectory uses
+ * log2(chains) + 1 levels, which shortens the serial pivot chain from (chain + all separators) to
+ * (chain + one separator per level).
+ * workspace: droid_chol_tree_workspace_bytes(n, nranges, n - range_end[level_first[1] - 1]) bytes. */
+int droid_chol_solve_tree_f64(double* A, double* b, int n, const int* firstc_dev, int nranges, const int* range_end,
+                              int nlevels, const int* level_first, int* info_dev, void* workspace,
+                              size_t workspace_bytes, void* stream);
+size_t droid_chol_tree_workspace_bytes(int n, int nranges, int sep_rows);
+
 #ifdef __cplusplus
 }
 #endif

@@ -578,6 +578,93 @@ def test_chol_solve_chains(backends, n, ends, bw):
         assert int(info.item()) != 0
 
 
+def tree_system(k, seed, chain_rows=(120, 330), sep_rows=(40, 100), bw=48):
+    """SPD matrix with the structure of a long trajectory's reduced camera system: a PATH c0 - t0 - c1 - t1 - ... of k
+    banded chains and k - 1 separators (t_j couples to the tail of c_j and the head of c_{j+1}), permuted into
+    elimination-tree layout: the chains, then the separators level by level (level of t_j = 1 + trailing zeros of
+    j + 1, path order inside a level).  The row envelopes come from the non-zero pattern of the exact factor itself.
+    Returns A, b, firstc [nranges, n] int32, range_end, level_first."""
+    rng = np.random.default_rng(seed)
+    cl = [2 * int(rng.integers(chain_rows[0] // 2, chain_rows[1] // 2)) for _ in range(k)]
+    sl = [2 * int(rng.integers(sep_rows[0] // 2, sep_rows[1] // 2)) for _ in range(k - 1)]
+    # path order: blocks and their extents
+    blocks, pos = [], 0
+    for j in range(k):
+        blocks.append(("c", j, pos, cl[j])); pos += cl[j]
+        if j < k - 1:
+            blocks.append(("t", j, pos, sl[j])); pos += sl[j]
+    n = pos
+    M = np.zeros((n, n))
+    ext = {(kind, j): (o, ln) for kind, j, o, ln in blocks}
+    for j in range(k):
+        o, ln = ext[("c", j)]
+        for r in range(o, o + ln):
+            f = max(o, r - bw)
+            M[r, f:r] = rng.normal(size=r - f) * 0.1 * (rng.uniform(size=r - f) < 0.7)
+    for j in range(k - 1):
+        o, ln = ext[("t", j)]
+        M[o:o + ln, o:o + ln] += np.tril(rng.normal(size=(ln, ln)) * 0.1, -1)
+        oc, lc = ext[("c", j)]
+        w = min(bw, lc)
+        M[o:o + ln, oc + lc - w:oc + lc] = rng.normal(size=(ln, w)) * 0.1 * (rng.uniform(size=(ln, w)) < 0.6)
+        oc, lc = ext[("c", j + 1)]
+        w = min(bw, lc)
+        M[oc:oc + w, o:o + ln] = rng.normal(size=(w, ln)) * 0.1 * (rng.uniform(size=(w, ln)) < 0.6)   # upper part: mirrored below
+    M = np.tril(M) + np.tril(M.T, -1)
+    M = M + M.T
+    M += np.diag(np.abs(M).sum(1) * 0.6 + 1.0)
+    # layout: chains (the last one reversed, like ba_order_kernel), then separators by level
+    lev = lambda j: 1 + (((j + 1) & -(j + 1)).bit_length() - 1)
+    nlev = 1 + max([lev(j) for j in range(k - 1)], default=0)
+    order, range_end, level_first = [], [], [0]
+    for j in range(k):
+        o, ln = ext[("c", j)]
+        idx = list(range(o, o + ln))
+        order += idx[::-1] if (j == k - 1 and k > 1) else idx
+        range_end.append(len(order))
+    level_first.append(k)
+    for L in range(1, nlev):
+        for j in range(k - 1):
+            if lev(j) == L:
+                o, ln = ext[("t", j)]
+                order += list(range(o, o + ln)); range_end.append(len(order))
+        level_first.append(len(range_end))
+    P = np.array(order)
+    A = M[np.ix_(P, P)]
+    Lf = np.linalg.cholesky(A)
+    nz = np.abs(Lf) > 0
+    NONE = np.iinfo(np.int32).max
+    b0 = [0] + range_end
+    firstc = np.full((len(range_end), n), NONE, np.int64)
+    for c in range(len(range_end)):
+        sub = nz[:, b0[c]:b0[c + 1]]
+        has = sub.any(axis=1)
+        firstc[c, has] = b0[c] + sub[has].argmax(axis=1)
+    return A, rng.normal(size=n), firstc.astype(np.int32), range_end, level_first
+
+
+@pytest.mark.parametrize("k,seed", [(2, 1), (3, 2), (4, 3), (6, 4), (8, 5), (8, 6)])
+def test_chol_solve_tree(backends, k, seed):
+    """droid_chol_solve_tree_f64 (nested dissection): the ranges of a level are factorised concurrently, even / odd
+    positions into A / the level's scratch block, levels one after the other, backward sweep in reverse.  Same answer
+    as the dense solve, the same BITS on every run, and an indefinite pivot in any range of any level is reported."""
+    A, b, firstc, range_end, level_first = tree_system(k, seed)
+    n = A.shape[0]
+    want = np.linalg.solve(A, b)
+    x, info = backends.chol_solve_tree(cu(A), cu(b), cu(firstc), range_end, level_first)
+    assert int(info.item()) == 0
+    assert rel(x.cpu().numpy(), want) <= 1e-10, (k, len(level_first) - 1, rel(x.cpu().numpy(), want))
+    for _ in range(3):
+        x2, _ = backends.chol_solve_tree(cu(A), cu(b), cu(firstc), range_end, level_first)
+        assert torch.equal(x, x2)
+    b0 = [0] + list(range_end)
+    for r in (0, len(range_end) // 2, len(range_end) - 1):
+        bad = (b0[r] + b0[r + 1]) // 2
+        A2 = A.copy(); A2[bad, bad] = -5.0 * n
+        _, info = backends.chol_solve_tree(cu(A2), cu(b), cu(firstc), range_end, level_first)
+        assert int(info.item()) != 0
+
+
 @pytest.mark.parametrize("knn", [8, 14, 22])
 def test_ba_tensor_core_schur_matches_cuda_core_kernel(knn):
     """The 3xTF32 tcgen05 Schur kernel (default for frames with <= 31 edges) against the fp32 CUDA-core kernel
