@@ -23,7 +23,12 @@
 namespace droid {
 
 static constexpr int kThreads = 256;
-static constexpr int kBaMaxChains = 4;      // concurrent elimination chains of the reduced camera system
+static constexpr int kBaMaxChains = 8;      // concurrent elimination chains of the reduced camera system
+static constexpr int kBaMaxRanges = 2 * kBaMaxChains - 1;   // chains + the separators between them (elimination tree)
+// layout of the tree in the status block, relative to sig = status + 8 (ba_order_kernel writes, the host reads):
+//   sig[10] = number of ranges (0: one chain), sig[11] = number of levels, sig[12 .. 12 + ranges) = end row of every
+//   range, sig[28 .. 28 + levels] = first range of every level
+static constexpr int kSigRanges = 10, kSigLevels = 11, kSigRangeEnd = 12, kSigLevelFirst = 28;
 static constexpr int kBaChainMinRows = 1536;   // smaller systems are factorised as one chain
 static constexpr int kHW_ACC = 96;  // 78 Hessian + 12 gradient values per edge, padded to 96
 
@@ -44,7 +49,7 @@ struct BaWs {
   float* W;        // [n_eta][HW]
   float* dx;       // [P][6]
   int* ppos;       // [P]   free pose -> position in the reduced system (fill-reducing order)
-  int* first;      // [(kBaMaxChains + 1) * 6P]  row envelopes of the reduced system per column range (chol.cu: firstc)
+  int* first;      // [kBaMaxRanges * 6P]  row envelopes of the reduced system per column range (chol.cu: firstc)
   int* oscr;       // [6P + 2 nbuf + 16] scratch of ba_order_kernel
   double* A;       // [6P*6P + 6P]  dense system, b appended
   void* chol;      // workspace of the factorisation
@@ -54,8 +59,8 @@ struct BaWs {
   size_t total;
 };
 
-static constexpr int kPackSegs = kBaMaxChains + 1;
-static constexpr int kPackTotalWord = 18 + 1 + kBaMaxChains + 1;   // status word behind the chain layout (status[18..])
+static constexpr int kPackSegs = 8;         // a top-level separator row: 2 chains + 2 separators per lower level + its own block
+static constexpr int kPackTotalWord = 8 + 36;   // status word behind the tree layout (status[18 .. 43])
 
 static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -82,7 +87,7 @@ static BaWs carve(void* base, const droid_ba_params* p, size_t chol_bytes) {
   w.W = (float*)take((size_t)(p->n_eta > 0 ? p->n_eta : 1) * HW * sizeof(float));
   w.dx = (float*)take((n6 > 0 ? n6 : 1) * sizeof(float));
   w.ppos = (int*)take((n6 > 0 ? n6 : 1) * sizeof(int));
-  w.first = (int*)take((size_t)(kBaMaxChains + 1) * (n6 > 0 ? n6 : 1) * sizeof(int));
+  w.first = (int*)take((size_t)kBaMaxRanges * (n6 > 0 ? n6 : 1) * sizeof(int));
   w.oscr = (int*)take((6 * (n6 / 6) + 2 * (size_t)p->nbuf + 16) * sizeof(int));
   w.A = (double*)take((n6 * n6 + n6 + 1) * sizeof(double));
   w.chol = take(chol_bytes);
@@ -391,7 +396,7 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
           cstart = lvl[best + 1];
           prev = best;
         }
-        if (ok && (P - cstart < 22 || 6 * sepf > (6 * P) / 4)) ok = false;
+        if (ok && (P - cstart < 22 || 3 * sepf > P)) ok = false;   // at most a third of the poses in separators
         if (ok) nch = k;
       }
     }
@@ -404,8 +409,13 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
     for (int f = tid; f < P; f += 1024) ppos[f] = use_bfs ? pos[f] : f;
     for (int r = tid; r < 6 * P; r += 1024) first[r] = 6 * en[r / 6];
   } else {
-    // new position of BFS position q: chains first (the last one reversed), then the separator levels
+    // new position of BFS position q: chains first (the last one reversed), then the separators, grouped by their level
+    // in the elimination tree.  The separators form a path t_0 .. t_{nch-2} (t_m lies between chains m and m + 1);
+    // nested dissection of a path: t_m has level 1 + (trailing zeros of m + 1), so the odd-numbered ones go first
+    // (mutually decoupled once the chains are gone), then every second of the rest, ... -- log2(nch) levels instead of
+    // nch - 1 separators in a row.  Inside a level: path order.
     int cs[kBaMaxChains], ce[kBaMaxChains], nbeg[kBaMaxChains + 1], ss[kBaMaxChains], sbeg[kBaMaxChains];
+    int slev[kBaMaxChains], srank[kBaMaxChains], nlev = 1;
     {
       int c0 = 0, acc = 0;
       for (int c = 0; c < nch; c++) {
@@ -416,7 +426,11 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
         if (c + 1 < nch) { ss[c] = lvl[s_sepl[c]]; c0 = lvl[s_sepl[c] + 1]; }
       }
       nbeg[nch] = acc;                                           // first separator position
-      for (int m = 0; m + 1 < nch; m++) { sbeg[m] = acc; acc += lvl[s_sepl[m] + 1] - ss[m]; }
+      for (int m = 0; m + 1 < nch; m++) { slev[m] = 1 + __ffs(m + 1) - 1; nlev = max(nlev, slev[m] + 1); }
+      int rank = 0;
+      for (int L = 1; L < nlev; L++)
+        for (int m = 0; m + 1 < nch; m++)
+          if (slev[m] == L) { srank[m] = rank++; sbeg[m] = acc; acc += lvl[s_sepl[m] + 1] - ss[m]; }
     }
     auto newpos = [&](int q) {
       for (int c = 0; c < nch; c++)
@@ -459,12 +473,39 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
       }
       __syncthreads();
     }
-    for (int r = tid; r < n6; r += 1024) first[(size_t)nch * n6 + r] = r >= 6 * sep0 ? 6 * sep0 : 0x7fffffff;
-    if (tid <= nch && tid > 0) sig[10 + tid] = 6 * nbeg[tid];     // chain ends; the last one = first separator row
+    // separator ranges: a separator's own rows are dense in its block; of the other separators only its PARENTS in the
+    // elimination tree -- the nearest separators of a higher level on either side along the path, index (m + 1) -/+
+    // 2^(level - 1) -- have (fill) entries in its columns
+    for (int m = 0; m + 1 < nch; m++) {
+      const int ri = nch + srank[m];
+      const int lo = sbeg[m], hi = sbeg[m] + (lvl[s_sepl[m] + 1] - ss[m]);
+      const int step = 1 << (slev[m] - 1);
+      const int pl = (m + 1) - step - 1, pr = (m + 1) + step - 1;          // parents (separator indices), if they exist
+      const int pl_lo = pl >= 0 ? sbeg[pl] : -1, pl_hi = pl >= 0 ? sbeg[pl] + (lvl[s_sepl[pl] + 1] - ss[pl]) : -1;
+      const int pr_lo = pr + 1 < nch ? sbeg[pr] : -1, pr_hi = pr + 1 < nch ? sbeg[pr] + (lvl[s_sepl[pr] + 1] - ss[pr]) : -1;
+      for (int r = tid; r < n6; r += 1024) {
+        const int q = r / 6;
+        const bool in = (q >= lo && q < hi) || (q >= pl_lo && q < pl_hi) || (q >= pr_lo && q < pr_hi);
+        first[(size_t)ri * n6 + r] = in ? 6 * lo : 0x7fffffff;
+      }
+    }
+    if (tid == 0) {
+      const int nr = 2 * nch - 1;
+      sig[kSigLevels] = nlev;
+      for (int c = 0; c < nch; c++) sig[kSigRangeEnd + c] = 6 * nbeg[c + 1];
+      for (int m = 0; m + 1 < nch; m++) sig[kSigRangeEnd + nch + srank[m]] = 6 * (sbeg[m] + (lvl[s_sepl[m] + 1] - ss[m]));
+      sig[kSigLevelFirst] = 0;
+      int cnt = nch;
+      for (int L = 1; L < nlev; L++) {
+        sig[kSigLevelFirst + L] = cnt;
+        for (int m = 0; m + 1 < nch; m++) cnt += slev[m] == L;
+      }
+      sig[kSigLevelFirst + nlev] = nr;
+    }
   }
   __syncthreads();
   if (tid == 0) {
-    sig[10] = nch;
+    sig[kSigRanges] = nch > 0 ? 2 * nch - 1 : 0;
     sig[1] = (int)(hsh & 0xffffffffull); sig[2] = (int)(hsh >> 32);
     sig[3] = n_edges; sig[4] = nbuf; sig[5] = t0; sig[6] = P; sig[7] = lay0; sig[9] = lay1;
     __threadfence();
@@ -488,10 +529,10 @@ __global__ void __launch_bounds__(1024) ba_pack_plan_kernel(const int* __restric
   __shared__ int s_warp[32];
   __shared__ int s_base;
   const int tid = threadIdx.x;
-  const int nch = sig[10];
-  int ends[kBaMaxChains + 1];
-  for (int c = 0; c < kBaMaxChains; c++) ends[c] = c < nch ? sig[11 + c] : 0;
-  const int sep0 = nch > 0 ? ends[nch - 1] : 0;
+  // ranges of the elimination tree (none: one range with the plain row envelope first[r])
+  const int nr = sig[kSigRanges];
+  int ends[kBaMaxRanges + 1];
+  for (int c = 0; c < kBaMaxRanges; c++) ends[c] = c < nr ? sig[kSigRangeEnd + c] : 0;
   if (tid == 0) s_base = 0;
   __syncthreads();
   for (int r0 = 0; r0 < n6; r0 += 1024) {
@@ -500,23 +541,24 @@ __global__ void __launch_bounds__(1024) ba_pack_plan_kernel(const int* __restric
     if (r < n6) {
       int* sg = seg + (size_t)r * kPackSegs * 2;
       for (int c = 0; c < kPackSegs; c++) { sg[2 * c] = 0; sg[2 * c + 1] = 0; }
-      if (nch == 0) {
+      if (nr == 0) {
         int f = first[r];
         if (f < 0 || f > r) f = r;
         sg[0] = f; sg[1] = r - f + 1;
-      } else if (r < sep0) {
-        int c = 0;
-        while (c + 1 < nch && r >= ends[c]) c++;
-        int f = first[(size_t)c * n6 + r];
-        if (f < 0 || f > r) f = r;
-        sg[0] = f; sg[1] = r - f + 1;
       } else {
-        for (int c = 0; c < nch; c++) {
+        // own range R: [first, r]; every earlier range the row reaches into: [first, end of that range)
+        int R = 0;
+        while (R + 1 < nr && r >= ends[R]) R++;
+        int ns = 0;
+        for (int c = 0; c < R && ns < kPackSegs - 1; c++) {
           const int f = first[(size_t)c * n6 + r];
           const int lo = c > 0 ? ends[c - 1] : 0;
-          if (f >= lo && f < ends[c]) { sg[2 * c] = f; sg[2 * c + 1] = ends[c] - f; }
+          if (f >= lo && f < ends[c]) { sg[2 * ns] = f; sg[2 * ns + 1] = ends[c] - f; ns++; }
         }
-        sg[2 * nch] = sep0; sg[2 * nch + 1] = r - sep0 + 1;
+        int f = first[(size_t)R * n6 + r];
+        const int lo = R > 0 ? ends[R - 1] : 0;
+        if (f < lo || f > r) f = r;
+        sg[2 * ns] = f; sg[2 * ns + 1] = r - f + 1;
       }
       for (int c = 0; c < kPackSegs; c++) len += sg[2 * c + 1];
     }
@@ -1402,7 +1444,7 @@ using namespace droid;
 // chains are only used when the separator holds at most a quarter of the rows (ba_order_kernel)
 static size_t ba_chol_bytes(int n6) {
   if (n6 < kBaChainMinRows || n6 > kCholChainsMaxRows) return droid_chol_workspace_bytes(n6);
-  return droid_chol_chains_workspace_bytes(n6, kBaMaxChains, n6 / 4 + 8);
+  return droid_chol_tree_workspace_bytes(n6, kBaMaxRanges, n6 / 3 + 8);
 }
 
 // The shard of source frames a call works on: [lo, hi).  "All frames" is frame_hi == INT32_MAX or < 0, or the
@@ -1493,8 +1535,8 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
     return v < 2 ? 0 : (v > kBaMaxChains ? kBaMaxChains : v);
   }();
   const int kreq = (ordered && n6 >= kBaChainMinRows && n6 <= kCholChainsMaxRows) ? chains_req : 0;
-  int nchains = 0;
-  int chain_end[kBaMaxChains] = {};
+  int nranges = 0, nlevels = 0;        // elimination tree of the reduced system (0 ranges: one chain)
+  int range_end[kBaMaxRanges + 1] = {}, level_first[kBaMaxRanges + 2] = {};
   int pack_total = -1;          // multi-GPU: doubles of the packed system (without the rhs); -1 = sum the dense buffer
   int max_deg = p->n_edges;     // upper bound until the device's figure is known
   bool status_read = false;
@@ -1510,15 +1552,22 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
       status_read = true;
       max_deg = h_ints[3];
       if (check) { if (int rc = status_error()) return rc; }
-      const int* h_split = h_ints + 18;
+      const int* h_sig = h_ints + 8;
       if (kreq > 0) {
-        nchains = h_split[0];
-        if (nchains < 0 || nchains > kBaMaxChains) return DROID_ERR_CUDA;
-        for (int c = 0; c < nchains; c++) chain_end[c] = h_split[1 + c];
-        if (nchains > 0 && n6 - chain_end[nchains - 1] > n6 / 4 + 8) return DROID_ERR_CUDA;
+        nranges = h_sig[kSigRanges];
+        if (nranges < 0 || nranges > kBaMaxRanges) return DROID_ERR_CUDA;
+        if (nranges > 0) {
+          nlevels = h_sig[kSigLevels];
+          if (nlevels < 2 || nlevels > nranges) return DROID_ERR_CUDA;
+          for (int c = 0; c < nranges; c++) range_end[c] = h_sig[kSigRangeEnd + c];
+          for (int l = 0; l <= nlevels; l++) level_first[l] = h_sig[kSigLevelFirst + l];
+          if (range_end[nranges - 1] != n6 || level_first[0] != 0 || level_first[nlevels] != nranges ||
+              n6 - range_end[level_first[1] - 1] > n6 / 3 + 8)
+            return DROID_ERR_CUDA;
+        }
       }
       if (packed) {
-        pack_total = h_split[kPackTotalWord - 18];
+        pack_total = h_ints[kPackTotalWord];
         if (pack_total < n6 || (size_t)pack_total > (size_t)n6 * (n6 + 1) / 2) return DROID_ERR_CUDA;
       }
     }
@@ -1663,8 +1712,11 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
         rc = launch_chol_small_damped(w.A, n6, p->lm, p->ep, w.status + 2, st);
       } else {
         DROID_LAUNCH ba_damp_kernel<<<(n6 + 127) / 128, 128, 0, st>>>(w.A, n6, p->lm, p->ep);
-        rc = droid_chol_solve_chains_f64(w.A, bvec, n6, first, nchains, chain_end, w.status + 2, w.chol, chol_bytes,
-                                         stream);
+        if (nranges > 0)
+          rc = droid_chol_solve_tree_f64(w.A, bvec, n6, first, nranges, range_end, nlevels, level_first, w.status + 2,
+                                         w.chol, chol_bytes, stream);
+        else
+          rc = droid_chol_solve_chains_f64(w.A, bvec, n6, first, 0, nullptr, w.status + 2, w.chol, chol_bytes, stream);
       }
       if (rc != DROID_OK) return rc;
     }

@@ -13,6 +13,7 @@
 // Failure (non-positive or NaN pivot) sets *info != 0; the caller zeroes dx like the reference
 // (src/droid_kernels.cu:1207-1210).  No host synchronisation anywhere.
 #include "common.cuh"
+#include <cstdio>
 #include <cstdlib>
 
 namespace droid {
@@ -294,7 +295,19 @@ struct ChainArgs {
   int sep;                // first separator row
   double* scr;            // scratch for C[r][c], r >= sep and c >= sep (nullptr: update A in place)
   int lds;
+  const int* lo64r;       // lo64 of this range (INT_MAX = the 64-row block has no entry in the range's columns), or nullptr
 };
+
+// do the rows [r_lo, r_hi] have an entry in the range's columns LEFT OF col_end (the range whose lo64 row is lo64r)?
+// Rows whose envelope starts further right are still structurally zero in the panel being eliminated -- e.g. the rows
+// of the separator a chain meets at its END, during all but the chain's last panels.  (Row n, the rhs: always.)
+__device__ __forceinline__ bool rows_touched(const int* __restrict__ lo64r, int n, int r_lo, int r_hi, int col_end) {
+  if (lo64r == nullptr || r_hi >= n) return true;
+  for (int b = r_lo >> 6; b <= r_hi >> 6; b++)
+    if (lo64r[b] < col_end) return true;
+  return false;
+}
+
 static constexpr int kMaxChains = 8;                  // ranges factorised concurrently (one pair of streams each)
 static constexpr int kMaxRanges = 2 * kMaxChains;     // chains + separators of all levels
 struct Ranges {            // range c = [b[c], b[c+1]), c = 0..k, in elimination-tree layout: all ranges of level 0 (the
@@ -306,7 +319,8 @@ __global__ void __launch_bounds__(kPanelThreads, 1) chol_panel_kernel(double* __
                                                                       int prev, int* __restrict__ info,
                                                                       const int* __restrict__ hi64,
                                                                       int* __restrict__ arrive, int vec, int hole_lo,
-                                                                      int hole_hi, double* __restrict__ linv) {
+                                                                      int hole_hi, double* __restrict__ linv,
+                                                                      const int* __restrict__ lo64r) {
   constexpr int NT = kPanelThreads;
   constexpr int NW = NT / 32;                        // warps = rows staged per step
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -322,7 +336,8 @@ __global__ void __launch_bounds__(kPanelThreads, 1) chol_panel_kernel(double* __
   const int trow0 = j0 + jb + blockIdx.x * PRT;      // first trailing row of this CTA
   // envelope: rows past hi64[] have no entry in these columns (and get none); the CTA holding the rhs row stays
   if (!ident && hi64 != nullptr && blockIdx.x != 0 &&
-      ((trow0 > hi64[(j0 + jb - 1) >> 6] && trow0 + PRT <= n) || (trow0 >= hole_lo && trow0 + PRT <= hole_hi))) {
+      ((trow0 > hi64[(j0 + jb - 1) >> 6] && trow0 + PRT <= n) || (trow0 >= hole_lo && trow0 + PRT <= hole_hi) ||
+       !rows_touched(lo64r, n, trow0, trow0 + PRT - 1, j0 + jb))) {
     if (threadIdx.x == 0) atomicAdd(&arrive[j0 >> 6], 1);
     return;
   }
@@ -332,12 +347,17 @@ __global__ void __launch_bounds__(kPanelThreads, 1) chol_panel_kernel(double* __
   PTS(0)
   // stage: a warp-instruction moves 512 contiguous bytes of one row (16 B per lane) straight into shared memory
   const int sr = tid >> 5, sc = (tid & 31) * 2;      // row within a group of NW, column pair
-  if (vec && jb == 64) {
+  const bool vecp = vec && (jb & 1) == 0;            // 16-byte accesses also for a partial (even) sub-panel
+  if (vecp) {
 #pragma unroll 8
     for (int q = 0; q < NT / NW; q++) {
       const int t = q * NW + sr;
       const unsigned dst = (unsigned)__cvta_generic_to_shared(R + t * kRld + sc);
-      if (row_ok(t)) {
+      if (row_ok(t) && sc >= jb) {      // columns behind a partial sub-panel: zero; the previous half is whole
+        *reinterpret_cast<double2*>(R + t * kRld + sc) = make_double2(0.0, 0.0);
+        if (prev)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(X + t * kRld + sc)), "l"(A + (size_t)row_of(t) * n + j0 + sc - prev));
+      } else if (row_ok(t)) {
         const double* src = A + (size_t)row_of(t) * n + j0 + sc;
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
         if (prev)
@@ -441,11 +461,11 @@ __global__ void __launch_bounds__(kPanelThreads, 1) chol_panel_kernel(double* __
     while (*cnt < (int)gridDim.x - 1) {}
   }
   __syncthreads();
-  if (vec && jb == 64) {
+  if (vecp) {
 #pragma unroll 8
     for (int q = 0; q < NT / NW; q++) {
       const int t = q * NW + sr;
-      if (!row_ok(t)) continue;
+      if (!row_ok(t) || sc >= jb) continue;
       if (t < 64 && (blockIdx.x != 0 || sc > t)) continue;   // the diagonal block is written once, lower part
       const double2 v = *reinterpret_cast<const double2*>(R + t * kRld + sc);
       double* dst = A + (size_t)row_of(t) * n + j0 + sc;
@@ -516,6 +536,8 @@ __global__ void __launch_bounds__(256, TM == 128 ? 1 : 2)
     if (c0 > hi || (i0 > hi && i0 + rows <= n)) return;
   }
   if ((i0 >= ca.hole_lo && i0 + rows <= ca.hole_hi) || (c0 >= ca.hole_lo && c0 + cols <= ca.hole_hi)) return;
+  // rows or columns (as rows of the factor) without an entry in this range's columns: nothing to subtract
+  if (!rows_touched(ca.lo64r, n, i0, i0 + rows - 1, J + kb) || !rows_touched(ca.lo64r, n, c0, c0 + cols - 1, J + kb)) return;
   auto in_hole = [&](int g) { return g >= ca.hole_lo && g < ca.hole_hi; };
   // C element (gr, gc), gc even: in A, or in the chain's scratch copy of the separator block
   auto c_ptr = [&](int gr, int gc) -> double* {
@@ -879,7 +901,7 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
   const int rc = c0 + blockIdx.x;                          // the range this CTA sweeps
   const int rbeg = rg.b[rc], rend = rg.b[rc + 1];
   if (rend <= rbeg) return;
-  const int sg0 = 0;                                       // column ranges its rows may reach into: every earlier one
+  const int sg0 = rc;                                      // own columns only; the lower ranges: chol_bwd_wide_kernel
   const int ylo = rbeg;                                    // ys[] holds the own range only
   const int nblk = (rend - rbeg + 63) >> 6;
   auto load_diag = [&](int blk, int buf) {
@@ -985,6 +1007,46 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
   for (int i = ylo + tid; i < rend; i += kBwdPThreads) y[i] = ys[i];
 }
 
+// Second half of the backward sweep of a level above the chains: once the level's own x is known (kernel above), its
+// rows' contributions to the y entries of all LOWER ranges, y[c] -= sum_r L[r][c] x[r], are one wide matrix-vector
+// product with no dependency chain -- spread over the whole GPU instead of being walked by the one persistent CTA of the
+// range (a top-level separator row reaches into two whole chains and four lower separators: ~2000 columns).
+// grid = (64-column tiles of [0, first row of the level), ranges of the level); thread = one column, 4 row groups.
+__global__ void __launch_bounds__(256) chol_bwd_wide_kernel(double* __restrict__ A, int n, const int* __restrict__ lo64,
+                                                            const Ranges rg, int c0) {
+  __shared__ double part[4][64];
+  const int rc = c0 + blockIdx.y;
+  const int rbeg = rg.b[rc], rend = rg.b[rc + 1];
+  const int c = blockIdx.x * 64 + (threadIdx.x & 63), g = threadIdx.x >> 6;
+  const int nb64 = (n + 63) >> 6;
+  const double* __restrict__ y = A + (size_t)n * n;
+  // the range the tile's columns lie in (tiles may straddle two ranges: resolved per column)
+  int sg = 0;
+  while (sg < rc && c >= rg.b[sg + 1]) sg++;
+  double s0 = 0.0, s1 = 0.0;
+  if (c < rg.b[c0] && sg < rc) {
+    const int* lo = lo64 + (size_t)sg * nb64;
+    for (int r0 = rbeg + 16 * g; r0 < rend; r0 += 64) {          // row group g takes 16 rows of every 64
+      const int r1 = min(r0 + 16, rend);
+      // rows whose 64-block has nothing at or left of this column in range sg are structurally zero here
+      if (min(lo[r0 >> 6], lo[(r1 - 1) >> 6]) > c) continue;
+      int r = r0;
+#pragma unroll 4
+      for (; r + 1 < r1; r += 2) {
+        s0 = fma(A[(size_t)r * n + c], y[r], s0);
+        s1 = fma(A[(size_t)(r + 1) * n + c], y[r + 1], s1);
+      }
+      if (r < r1) s0 = fma(A[(size_t)r * n + c], y[r], s0);
+    }
+  }
+  part[g][threadIdx.x & 63] = s0 + s1;
+  __syncthreads();
+  if (threadIdx.x < 64 && c < rg.b[c0] && sg < rc) {
+    const double sum = (part[0][threadIdx.x] + part[1][threadIdx.x]) + (part[2][threadIdx.x] + part[3][threadIdx.x]);
+    if (sum != 0.0) A[(size_t)n * n + c] -= sum;      // structurally one range of the level per column: no race
+  }
+}
+
 // Envelope summary per 64-block and range.  firstc[c * n + r] = first structurally non-zero column of row r inside
 // range c (fill-in of a Cholesky factor stays inside these per-range row envelopes); a value
 // outside [b[c], min(r, b[c+1] - 1)] means "row r has nothing in range c", except in the row's own range, where it is
@@ -993,31 +1055,30 @@ __global__ void __launch_bounds__(kBwdPThreads, 1) chol_bwd_persist_kernel(doubl
 //   lo64[c * nb + blk] = first column of range c used by the rows of block blk  (INT_MAX: none)
 __global__ void __launch_bounds__(1024) chol_env_kernel(const int* __restrict__ firstc, int n, const Ranges rg,
                                                         int* __restrict__ hi64, int* __restrict__ lo64) {
+  // one CTA per range (the tree of a long trajectory has 15 of them)
   const int nb = (n + 63) >> 6;
-  for (int e = threadIdx.x; e < (rg.k + 1) * nb; e += 1024) {
-    const int c = e / nb, blk = e - c * nb;
-    hi64[e] = min(64 * blk + 63, rg.b[c + 1] - 1);
-    lo64[e] = 0x7fffffff;
+  const int c = blockIdx.x;
+  int* __restrict__ hi = hi64 + (size_t)c * nb;
+  int* __restrict__ lo = lo64 + (size_t)c * nb;
+  for (int blk = threadIdx.x; blk < nb; blk += 1024) {
+    hi[blk] = min(64 * blk + 63, rg.b[c + 1] - 1);
+    lo[blk] = 0x7fffffff;
   }
   __syncthreads();
-  for (int e = threadIdx.x; e < (rg.k + 1) * n; e += 1024) {
-    const int c = e / n, r = e - c * n;
-    int f = firstc[e];
+  for (int r = threadIdx.x; r < n; r += 1024) {
+    int f = firstc[(size_t)c * n + r];
     const int top = min(r, rg.b[c + 1] - 1);
     if (r >= rg.b[c] && r < rg.b[c + 1]) f = max(rg.b[c], min(f, r));   // own range: at least the diagonal
     else if (f < rg.b[c] || f > top) continue;
-    atomicMax(&hi64[c * nb + (f >> 6)], r);
-    atomicMin(&lo64[c * nb + (r >> 6)], f);
+    atomicMax(&hi[f >> 6], r);
+    atomicMin(&lo[r >> 6], f);
   }
   __syncthreads();
-  if (threadIdx.x <= rg.k) {
-    const int c = threadIdx.x;
-    if (rg.b[c + 1] > rg.b[c]) {
-      int run = 0;
-      for (int blk = rg.b[c] >> 6; blk <= (rg.b[c + 1] - 1) >> 6; blk++) {
-        run = max(run, hi64[c * nb + blk]);
-        hi64[c * nb + blk] = run;
-      }
+  if (threadIdx.x == 0 && rg.b[c + 1] > rg.b[c]) {
+    int run = 0;
+    for (int blk = rg.b[c] >> 6; blk <= (rg.b[c + 1] - 1) >> 6; blk++) {
+      run = max(run, hi[blk]);
+      hi[blk] = run;
     }
   }
 }
@@ -1139,6 +1200,9 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
     if (level_first[l + 1] <= level_first[l] || level_first[l + 1] - level_first[l] > kMaxChains) return DROID_ERR_INVALID_ARGUMENT;
   const int nchains = nranges - 1;      // ranges besides the last one (sizes the per-range tables: nchains + 1 entries)
   cudaStream_t st = (cudaStream_t)stream;
+  static const bool trace0 = []() { const char* e = getenv("DROID_CHOL_TRACE"); return e && e[0] == '1'; }();
+  cudaEvent_t tev0 = nullptr;
+  if (trace0) { cudaEventCreate(&tev0); cudaEventRecord(tev0, st); }
   cudaMemsetAsync(info_dev, 0, sizeof(int), st);
   if (n <= kSmallMax) {
     if (nranges > 1) return DROID_ERR_INVALID_ARGUMENT;
@@ -1210,7 +1274,7 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
   if (firstc_dev != nullptr) {
     hi64 = arrive + (size_t)(nchains + 1) * (nb + 1);
     lo64 = hi64 + (size_t)(nchains + 1) * nb;
-    DROID_LAUNCH chol_env_kernel<<<1, 1024, 0, st>>>(firstc_dev, n, rg, hi64, lo64);
+    DROID_LAUNCH chol_env_kernel<<<nchains + 1, 1024, 0, st>>>(firstc_dev, n, rg, hi64, lo64);
   }
   double* scr = nullptr;
   // the backward sweep of envelope / chain systems runs in one persistent CTA per range and takes the diagonal blocks'
@@ -1251,13 +1315,13 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
       const int jb = (J + kb - j0) < NB ? (J + kb - j0) : NB;
       const int rem_rows = n + 1 - (j0 + jb);  // >= 1 (the rhs row)
       // second half of the outer panel: the rank-64 update by the first half is applied by the panel kernel itself
-      const bool fused = j0 > J && vec && jb == NB;
+      const bool fused = j0 > J && vec && (jb & 1) == 0;
       DROID_LAUNCH chol_panel_kernel<<<(rem_rows + PRT - 1) / PRT + (linv ? 1 : 0), kPanelThreads,
                                        fused ? kPanelSmem2 : kPanelSmem1, ps>>>(
           A, n, j0, jb, fused ? NB : 0, info_dev, hi64 ? cs.hi64 : nullptr, cs.arrive, vec ? 1 : 0, cs.ca.hole_lo,
-          cs.ca.hole_hi, linv);
+          cs.ca.hole_hi, linv, cs.ca.lo64r);
       const int rest = J + kb - (j0 + jb);     // columns of this outer panel still to factorise
-      if (rest > 0 && !(vec && rest == NB)) {
+      if (rest > 0 && !(vec && rest <= NB && (rest & 1) == 0)) {
         // (only when the next sub-panel cannot fuse it) rank-64 update of the panel's remaining columns
         const int t64 = (rem_rows + 63) / 64;
         if (vec) DROID_LAUNCH chol_syrk_kernel<64, true><<<t64, 256, kSyrk64, ps>>>(A, n, j0, jb, rest, hi64 ? cs.hi64 : nullptr, cs.ca, 1 << 30, 0);
@@ -1323,6 +1387,7 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
       }
     }
     cs.hi64 = hi64 ? hi64 + (size_t)c * nb : nullptr;
+    cs.ca.lo64r = lo64 ? lo64 + (size_t)c * nb : nullptr;
     cs.arrive = arrive + (size_t)c * (nb + 1);
     const int r0 = cs.J + PB;
     cs.on_side = vec && r0 + PB <= cs.Jend && n + 1 - r0 >= 4 * PB;
@@ -1338,9 +1403,22 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
       cs.on_side = false;
     }
   };
+  // DROID_CHOL_TRACE=1: device time of every stage of the solve (events on the caller's stream; synchronises; debug aid)
+  static const bool trace = []() { const char* e = getenv("DROID_CHOL_TRACE"); return e && e[0] == '1'; }();
+  cudaEvent_t tev[2 * kMaxRanges + 8];
+  const char* tname[2 * kMaxRanges + 8];
+  int ntev = 0;
+  auto tmark = [&](const char* what) {
+    if (!trace) return;
+    cudaEventCreate(&tev[ntev]);
+    cudaEventRecord(tev[ntev], st);
+    tname[ntev++] = what;
+  };
+  if (trace) { tev[ntev] = tev0; tname[ntev++] = "set-up (memsets, envelope summary)"; }
   for (int lv = 0; lv < nlevels; lv++) {
     const int r_lo = level_first[lv], cnt = level_first[lv + 1] - r_lo;
     ChainState cs[kMaxChains];
+    tmark("level: factorise");
     if (cnt == 1) {
       open_range(cs[0], r_lo, lv, 0, st, &ctx[0], true);
       while (!cs[0].finished) step(cs[0]);
@@ -1369,6 +1447,7 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
         cudaStreamWaitEvent(st, ctx[c].done, 0);
       }
     }
+    tmark("level: join + merge");
     if (lv + 1 < nlevels && scr != nullptr) {
       const int behind = rg.b[level_first[lv + 1]];
       DROID_LAUNCH chol_merge_kernel<<<n - behind + 1, 256, 0, st>>>(A, n, behind, scr + scr_off[lv], private_scr ? cnt - 1 : 1,
@@ -1377,9 +1456,24 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
   }
   ProfScope psb(DROID_PROF_CHOL_BWD, st);
   if (persist_bwd) {
-    for (int lv = nlevels - 1; lv >= 0; lv--)
-      DROID_LAUNCH chol_bwd_persist_kernel<<<level_first[lv + 1] - level_first[lv], kBwdPThreads, bwd_persist_smem(n), st>>>(
-          A, n, lo64, rg, level_first[lv], linv);
+    for (int lv = nlevels - 1; lv >= 0; lv--) {
+      const int cnt = level_first[lv + 1] - level_first[lv];
+      tmark("backward: level");
+      DROID_LAUNCH chol_bwd_persist_kernel<<<cnt, kBwdPThreads, bwd_persist_smem(n), st>>>(A, n, lo64, rg, level_first[lv], linv);
+      if (lv > 0)
+        DROID_LAUNCH chol_bwd_wide_kernel<<<dim3((rg.b[level_first[lv]] + 63) / 64, cnt), 256, 0, st>>>(A, n, lo64, rg,
+                                                                                                       level_first[lv]);
+    }
+    if (trace) {
+      tmark("end");
+      cudaStreamSynchronize(st);
+      for (int i = 0; i + 1 < ntev; i++) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, tev[i], tev[i + 1]);
+        fprintf(stderr, "[chol trace] %-40s %8.1f us\n", tname[i], ms * 1e3f);
+      }
+      for (int i = 0; i < ntev; i++) cudaEventDestroy(tev[i]);
+    }
     return check_launch();
   }
   for (int J0 = ((n - 1) / SB) * SB; J0 >= 0; J0 -= SB) {

@@ -585,18 +585,26 @@ def ba_status(device=None):
     return int(ws[off:off + 4].view(torch.int32).item())
 
 
-def ba_chains(device=None):
-    """Chain layout the last large ba() on this device factorised its reduced camera system with: a list of the chain
-    end rows (empty = one chain).  Forces a D2H copy; debug / test aid."""
+def ba_tree(device=None):
+    """Elimination tree the last large ba() on this device factorised its reduced camera system with:
+    (range_end, level_first) as droid_chol_solve_tree_f64 takes them, ([], []) for a single chain.  Forces a D2H copy;
+    debug / test aid."""
     device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     ws = _ws_cache.get((device.type, device.index))
     if ws is None:
-        return []
+        return [], []
     off = (-ws.data_ptr()) % 256
     st = ws[off:off + 256].view(torch.int32).cpu().tolist()
-    if st[8] != 0x0b200c0d:
-        return []
-    return st[19:19 + st[18]]
+    if st[8] != 0x0b200c0d or st[18] <= 0:
+        return [], []
+    nr, nl = st[18], st[19]
+    return st[20:20 + nr], st[36:36 + nl + 1]
+
+
+def ba_chains(device=None):
+    """End rows of the chains (the level-0 ranges of ba_tree; the last one = first separator row); empty = one chain."""
+    range_end, level_first = ba_tree(device)
+    return range_end[:level_first[1]] if level_first else []
 
 
 def chol_solve_tree(A, b, first, range_end, level_first):

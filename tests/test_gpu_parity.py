@@ -518,13 +518,14 @@ def test_ba_chains_match_single_chain_factorisation(backends, frames):
     ) % (os.path.join(ROOT, "droid-slam_b200"), os.path.join(ROOT, "oracle"), frames)
     out = {}
     with tempfile.TemporaryDirectory() as td:
-        for k in ("4", "2", "0"):
+        for k in ("8", "4", "2", "0"):
             f = os.path.join(td, "o%s.npz" % k)
             subprocess.check_call([sys.executable, "-c", code, f], env=dict(os.environ, DROID_BA_CHAINS=k))
             out[k] = dict(np.load(f))
     assert len(out["0"]["chains"]) == 0 and len(out["2"]["chains"]) == 2 and len(out["4"]["chains"]) >= 2
     print("chain ends:", out["4"]["chains"], out["2"]["chains"])
-    for k in ("4", "2"):
+    print("chain ends (8 requested):", out["8"]["chains"])
+    for k in ("8", "4", "2"):
         for key, tol in (("dx", 2e-5), ("dz", 2e-5), ("po", 1e-5), ("di", 1e-5)):
             assert rel(out[k][key], out["0"][key]) <= tol, (k, key, rel(out[k][key], out["0"][key]))
 

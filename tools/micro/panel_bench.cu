@@ -21,7 +21,7 @@ int main() {
         cudaMemset(arrive, 0, 4096);
         cudaEventRecord(e0);
         droid::chol_panel_kernel<<<ncta, droid::kPanelThreads, prev ? droid::kPanelSmem2 : droid::kPanelSmem1>>>(
-            A, n, j0, jb, prev, info, nullptr, arrive, 1, 0, 0, linv);
+            A, n, j0, jb, prev, info, nullptr, arrive, 1, 0, 0, linv, nullptr);
         cudaEventRecord(e1); cudaEventSynchronize(e1);
         float ms; cudaEventElapsedTime(&ms, e0, e1);
         if (ms < best) best = ms;
