@@ -24,7 +24,7 @@ namespace droid {
 
 static constexpr int kThreads = 256;
 static constexpr int kBaMaxChains = 8;      // concurrent elimination chains of the reduced camera system
-static constexpr int kBaMaxRanges = 2 * kBaMaxChains - 1;   // chains + the separators between them (elimination tree)
+static constexpr int kBaMaxRanges = 2 * kBaMaxChains;   // chains + the separators between them + the cut (elimination tree)
 // layout of the tree in the status block, relative to sig = status + 8 (ba_order_kernel writes, the host reads):
 //   sig[10] = number of ranges (0: one chain), sig[11] = number of levels, sig[12 .. 12 + ranges) = end row of every
 //   range, sig[28 .. 28 + levels] = first range of every level
@@ -288,60 +288,163 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
             sig[3] == n_edges && sig[4] == nbuf && sig[5] == t0 && sig[6] == P && sig[7] == lay0 && sig[9] == lay1;
   __syncthreads();
   if (s_hit) return;
-  for (int f = tid; f < P; f += 1024) { pos[f] = -1; cur[f] = 0; cand[f] = 0; }
-  for (int m = tid; m < nbuf; m += 1024) starhit[m] = 0;
-  if (tid == 0) { s_placed = 0; s_nlev = 0; }
-  __syncthreads();
-  while (true) {
-    if (tid == 0) s_seed = 0x7fffffff;
-    __syncthreads();
-    int best = 0x7fffffff;
-    for (int f = tid; f < P; f += 1024)
-      if (pos[f] < 0) { best = f; break; }
-    if (best != 0x7fffffff) atomicMin(&s_seed, best);
-    __syncthreads();
-    const int seed = s_seed;
-    if (seed == 0x7fffffff) break;
-    if (tid == 0) { pos[seed] = s_placed; cur[seed] = 1; lvl[s_nlev] = s_placed; s_nlev = s_nlev + 1; s_placed = s_placed + 1; }
+  __shared__ int s_first_seed, s_cut, s_root, s_cnt[2];
+  // breadth-first levels over the poses with pos == -1 (pos == -2: taken out of the graph); first_seed >= 0 starts
+  // the first component there
+  auto bfs = [&](int first_seed) {
+    for (int f = tid; f < P; f += 1024) { cur[f] = 0; cand[f] = 0; }
+    for (int m = tid; m < nbuf; m += 1024) starhit[m] = 0;
+    if (tid == 0) { s_placed = 0; s_nlev = 0; s_first_seed = first_seed; }
     __syncthreads();
     while (true) {
+      if (tid == 0) s_seed = 0x7fffffff;
+      __syncthreads();
+      int best = 0x7fffffff;
+      for (int f = tid; f < P; f += 1024)
+        if (pos[f] == -1) { best = f; break; }
+      if (best != 0x7fffffff) atomicMin(&s_seed, best);
+      __syncthreads();
+      const int seed = s_first_seed >= 0 ? s_first_seed : s_seed;
+      __syncthreads();
+      if (seed == 0x7fffffff) break;
+      if (tid == 0) { s_first_seed = -1; pos[seed] = s_placed; cur[seed] = 1; lvl[s_nlev] = s_placed; s_nlev = s_nlev + 1; s_placed = s_placed + 1; }
+      __syncthreads();
+      while (true) {
+        for (int e = tid; e < n_edges; e += 1024) {
+          const long long i = ii[e], j = jj[e];
+          if (!valid(i, j)) continue;
+          const int a = (int)i - t0, b = (int)j - t0;
+          if ((a >= 0 && a < P && cur[a]) || (b >= 0 && b < P && cur[b])) starhit[kmap[i]] = 1;
+        }
+        __syncthreads();
+        for (int e = tid; e < n_edges; e += 1024) {
+          const long long i = ii[e], j = jj[e];
+          if (!valid(i, j) || !starhit[kmap[i]]) continue;
+          const int a = (int)i - t0, b = (int)j - t0;
+          if (a >= 0 && a < P && pos[a] == -1) cand[a] = 1;
+          if (b >= 0 && b < P && pos[b] == -1) cand[b] = 1;
+        }
+        __syncthreads();
+        for (int m = tid; m < nbuf; m += 1024) starhit[m] = 0;
+        for (int f = tid; f < P; f += 1024) cur[f] = 0;
+        __syncthreads();
+        const int base = s_placed;
+        int placed = 0;
+        for (int c0 = 0; c0 < P; c0 += 1024) {
+          const int f = c0 + tid;
+          const int flag = (f < P && cand[f]) ? 1 : 0;
+          int total;
+          const int ex = block_scan_excl_1024(flag, s_warp, &total);
+          if (flag) { pos[f] = base + placed + ex; cur[f] = 1; cand[f] = 0; }
+          placed += total;
+        }
+        __syncthreads();
+        if (tid == 0) {
+          s_placed = base + placed;
+          if (placed > 0) { lvl[s_nlev] = base; s_nlev = s_nlev + 1; }
+        }
+        __syncthreads();
+        if (placed == 0) break;
+      }
+    }
+  };
+  // Two attempts.  attempt 0 (long trajectories only): CUT the graph open first.  A trajectory that revisits places is
+  // ring-like, and the levels of a breadth-first search on a ring are two fronts travelling in opposite directions:
+  // twice the bandwidth, and every level separator is two fronts thick.  So: one search, take ONE connected component
+  // of its middle level as the cut S0 (removing it opens the ring), search again from a pose next to the cut on the
+  // graph without S0 -- single fronts -- and put S0 last, as the root of the elimination tree.  The structure the
+  // factorisation then relies on (S0 is coupled to the first and the last chain only) is verified below; if it does
+  // not hold, or the middle level is one piece (an open trajectory), attempt 1 is the plain search.
+  int cutn = 0, Pe = P, nch = 0;
+  bool use_bfs = false;
+  __shared__ int s_bad;
+  for (int attempt = (kreq >= 2 ? 0 : 1); attempt < 2; attempt++) {
+    for (int f = tid; f < P; f += 1024) pos[f] = -1;
+    if (tid == 0) s_cut = 0;
+    __syncthreads();
+    bfs(-1);
+    cutn = 0;
+    if (attempt == 0) {
+    if (s_nlev < 12) continue;
+    // connected components of the middle level (coupling = membership of a common star): min-label propagation
+    const int Lm = s_nlev / 2, l0 = lvl[Lm], l1 = lvl[Lm + 1];
+    __syncthreads();
+    int* label = cand;
+    for (int f = tid; f < P; f += 1024) label[f] = (pos[f] >= l0 && pos[f] < l1) ? f : 0x7fffffff;
+    __syncthreads();
+    for (int it = 0; it < 12; it++) {
+      for (int m = tid; m < nbuf; m += 1024) starmin[m] = 0x7fffffff;
+      __syncthreads();
       for (int e = tid; e < n_edges; e += 1024) {
         const long long i = ii[e], j = jj[e];
         if (!valid(i, j)) continue;
-        const int a = (int)i - t0, b = (int)j - t0;
-        if ((a >= 0 && a < P && cur[a]) || (b >= 0 && b < P && cur[b])) starhit[kmap[i]] = 1;
+        const int a = (int)i - t0, b = (int)j - t0, m = kmap[i];
+        if (a >= 0 && a < P && label[a] != 0x7fffffff) atomicMin(&starmin[m], label[a]);
+        if (b >= 0 && b < P && label[b] != 0x7fffffff) atomicMin(&starmin[m], label[b]);
       }
       __syncthreads();
       for (int e = tid; e < n_edges; e += 1024) {
         const long long i = ii[e], j = jj[e];
-        if (!valid(i, j) || !starhit[kmap[i]]) continue;
-        const int a = (int)i - t0, b = (int)j - t0;
-        if (a >= 0 && a < P && pos[a] < 0) cand[a] = 1;
-        if (b >= 0 && b < P && pos[b] < 0) cand[b] = 1;
+        if (!valid(i, j)) continue;
+        const int a = (int)i - t0, b = (int)j - t0, sm = starmin[kmap[i]];
+        if (a >= 0 && a < P && label[a] != 0x7fffffff) atomicMin(&label[a], sm);
+        if (b >= 0 && b < P && label[b] != 0x7fffffff) atomicMin(&label[b], sm);
       }
       __syncthreads();
-      for (int m = tid; m < nbuf; m += 1024) starhit[m] = 0;
-      for (int f = tid; f < P; f += 1024) cur[f] = 0;
-      __syncthreads();
-      const int base = s_placed;
+    }
+    if (tid == 0) { s_root = 0x7fffffff; s_cnt[0] = 0; s_cnt[1] = 0; }
+    __syncthreads();
+    for (int f = tid; f < P; f += 1024)
+      if (label[f] != 0x7fffffff) atomicMin(&s_root, label[f]);
+    __syncthreads();
+    for (int f = tid; f < P; f += 1024)
+      if (label[f] != 0x7fffffff) atomicAdd(&s_cnt[label[f] == s_root ? 0 : 1], 1);
+    __syncthreads();
+    if (s_cnt[0] == 0 || s_cnt[1] == 0) continue;                 // one piece: nothing to cut
+    const int root = s_root;
+    cutn = s_cnt[0];
+    // take S0 out, find the poses next to it, search again from the first of them
+    for (int f = tid; f < P; f += 1024) { pos[f] = (label[f] == root) ? -2 : -1; env[f] = 0; }
+    for (int m = tid; m < nbuf; m += 1024) starhit[m] = 0;
+    if (tid == 0) s_seed = 0x7fffffff;
+    __syncthreads();
+    for (int e = tid; e < n_edges; e += 1024) {
+      const long long i = ii[e], j = jj[e];
+      if (!valid(i, j)) continue;
+      const int a = (int)i - t0, b = (int)j - t0;
+      if ((a >= 0 && a < P && pos[a] == -2) || (b >= 0 && b < P && pos[b] == -2)) starhit[kmap[i]] = 1;
+    }
+    __syncthreads();
+    for (int e = tid; e < n_edges; e += 1024) {
+      const long long i = ii[e], j = jj[e];
+      if (!valid(i, j) || !starhit[kmap[i]]) continue;
+      const int a = (int)i - t0, b = (int)j - t0;
+      if (a >= 0 && a < P && pos[a] == -1) atomicMin(&s_seed, a);
+      if (b >= 0 && b < P && pos[b] == -1) atomicMin(&s_seed, b);
+    }
+    __syncthreads();
+    const int seed2 = s_seed;
+    __syncthreads();
+    if (seed2 == 0x7fffffff) { cutn = 0; continue; }
+    bfs(seed2);
+    // S0 goes behind everything else, in pose order
+    {
+      const int base = P - cutn;
       int placed = 0;
       for (int c0 = 0; c0 < P; c0 += 1024) {
         const int f = c0 + tid;
-        const int flag = (f < P && cand[f]) ? 1 : 0;
+        const int flag = (f < P && pos[f] == -2) ? 1 : 0;
         int total;
         const int ex = block_scan_excl_1024(flag, s_warp, &total);
-        if (flag) { pos[f] = base + placed + ex; cur[f] = 1; cand[f] = 0; }
+        if (flag) pos[f] = base + placed + ex;
         placed += total;
       }
+      if (tid == 0) s_cut = cutn;
       __syncthreads();
-      if (tid == 0) {
-        s_placed = base + placed;
-        if (placed > 0) { lvl[s_nlev] = base; s_nlev = s_nlev + 1; }
-      }
-      __syncthreads();
-      if (placed == 0) break;
     }
-  }
+    }  // (attempt 0: the cut)
+    cutn = s_cut;
+    Pe = P - cutn;
   // envelopes + profiles of both orders
   for (int pass = 0; pass < 2; pass++) {
     int* en = pass == 0 ? env : cand;
@@ -370,7 +473,7 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
     atomicAdd(&s_prof[pass], acc);
     __syncthreads();
   }
-  const bool use_bfs = s_prof[1] * 10ull < s_prof[0] * 7ull;
+  use_bfs = s_prof[1] * 10ull < s_prof[0] * 7ull;
   // Chains (long trajectories): every BFS level is a separator of the star graph (the members of a star lie in two
   // adjacent levels), so k - 1 levels near the quantiles of the order cut it into k mutually decoupled chains.  The
   // chains are eliminated concurrently and the separator levels last (chol.cu: droid_chol_solve_chains_f64); the
@@ -378,13 +481,17 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
   if (tid == 0) {
     int nch = 0;
     const int nlev = s_nlev;
-    lvl[nlev] = P;
+    lvl[nlev] = Pe;                                              // (the cut, if any, lies behind the last level)
     if (use_bfs) {
       for (int k = min(kreq, kBaMaxChains); k >= 2 && nch == 0; k--) {
+        // with the cut the path closes into a ring: the first and the last range of EVERY level both hang on the cut,
+        // so they must sit at positions of opposite parity (A / scratch) -- true for powers of two (level sizes k,
+        // k/2, k/4, ..., 1)
+        if (cutn > 0 && (k & (k - 1))) continue;
         bool ok = true;
         int prev = -1, sepf = 0, cstart = 0;
         for (int m = 1; m < k && ok; m++) {
-          const int target = (int)((long long)P * m / k);
+          const int target = (int)((long long)Pe * m / k);
           int best = -1, bestd = 0x7fffffff;
           for (int L = prev + 2; L <= nlev - 2; L++) {          // a level on either side stays with the chains
             const int d = abs((lvl[L] + lvl[L + 1]) / 2 - target);
@@ -396,14 +503,40 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
           cstart = lvl[best + 1];
           prev = best;
         }
-        if (ok && (P - cstart < 22 || 3 * sepf > P)) ok = false;   // at most a third of the poses in separators
+        if (ok && (Pe - cstart < 22 || 3 * (sepf + cutn) > P)) ok = false;   // at most a third of the poses in separators
         if (ok) nch = k;
       }
     }
     s_nch = nch;
   }
   __syncthreads();
-  const int nch = s_nch;
+  nch = s_nch;
+    if (attempt == 1 || cutn == 0) break;
+    // attempt 0: the cut must be coupled (share a star) with poses of the first and the last chain only
+    if (nch >= 2) {
+      const int c0_end = lvl[s_sepl[0]], cl_beg = lvl[s_sepl[nch - 2] + 1];
+      for (int m = tid; m < nbuf; m += 1024) starhit[m] = 0;
+      if (tid == 0) s_bad = 0;
+      __syncthreads();
+      for (int e = tid; e < n_edges; e += 1024) {
+        const long long i = ii[e], j = jj[e];
+        if (!valid(i, j)) continue;
+        const int a = (int)i - t0, b = (int)j - t0;
+        if ((a >= 0 && a < P && pos[a] >= Pe) || (b >= 0 && b < P && pos[b] >= Pe)) starhit[kmap[i]] = 1;
+      }
+      __syncthreads();
+      for (int e = tid; e < n_edges; e += 1024) {
+        const long long i = ii[e], j = jj[e];
+        if (!valid(i, j) || !starhit[kmap[i]]) continue;
+        const int a = (int)i - t0, b = (int)j - t0;
+        if (a >= 0 && a < P && pos[a] >= c0_end && pos[a] < cl_beg) s_bad = 1;
+        if (b >= 0 && b < P && pos[b] >= c0_end && pos[b] < cl_beg) s_bad = 1;
+      }
+      __syncthreads();
+      if (!s_bad) break;
+    }
+    __syncthreads();
+  }
   if (nch == 0) {
     const int* en = use_bfs ? cand : env;
     for (int f = tid; f < P; f += 1024) ppos[f] = use_bfs ? pos[f] : f;
@@ -420,7 +553,7 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
       int c0 = 0, acc = 0;
       for (int c = 0; c < nch; c++) {
         cs[c] = c0;
-        ce[c] = c + 1 < nch ? lvl[s_sepl[c]] : P;
+        ce[c] = c + 1 < nch ? lvl[s_sepl[c]] : Pe;
         nbeg[c] = acc;
         acc += ce[c] - cs[c];
         if (c + 1 < nch) { ss[c] = lvl[s_sepl[c]]; c0 = lvl[s_sepl[c] + 1]; }
@@ -485,13 +618,18 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
       const int pr_lo = pr + 1 < nch ? sbeg[pr] : -1, pr_hi = pr + 1 < nch ? sbeg[pr] + (lvl[s_sepl[pr] + 1] - ss[pr]) : -1;
       for (int r = tid; r < n6; r += 1024) {
         const int q = r / 6;
-        const bool in = (q >= lo && q < hi) || (q >= pl_lo && q < pl_hi) || (q >= pr_lo && q < pr_hi);
+        // a separator without a parent on one side hangs on the cut there (the cut closes the path into a ring)
+        const bool in = (q >= lo && q < hi) || (q >= pl_lo && q < pl_hi) || (q >= pr_lo && q < pr_hi) ||
+                        (cutn > 0 && q >= Pe && (pl < 0 || pr + 1 >= nch));
         first[(size_t)ri * n6 + r] = in ? 6 * lo : 0x7fffffff;
       }
     }
+    if (cutn > 0)      // the cut: the last range, a dense block, the root of the tree
+      for (int r = tid; r < n6; r += 1024) first[(size_t)(2 * nch - 1) * n6 + r] = r >= 6 * Pe ? 6 * Pe : 0x7fffffff;
     if (tid == 0) {
-      const int nr = 2 * nch - 1;
-      sig[kSigLevels] = nlev;
+      const int nr = 2 * nch - 1 + (cutn > 0 ? 1 : 0);
+      if (cutn > 0) { sig[kSigRangeEnd + nr - 1] = 6 * P; }
+      sig[kSigLevels] = nlev + (cutn > 0 ? 1 : 0);
       for (int c = 0; c < nch; c++) sig[kSigRangeEnd + c] = 6 * nbeg[c + 1];
       for (int m = 0; m + 1 < nch; m++) sig[kSigRangeEnd + nch + srank[m]] = 6 * (sbeg[m] + (lvl[s_sepl[m] + 1] - ss[m]));
       sig[kSigLevelFirst] = 0;
@@ -500,12 +638,13 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
         sig[kSigLevelFirst + L] = cnt;
         for (int m = 0; m + 1 < nch; m++) cnt += slev[m] == L;
       }
-      sig[kSigLevelFirst + nlev] = nr;
+      sig[kSigLevelFirst + nlev] = 2 * nch - 1;
+      if (cutn > 0) sig[kSigLevelFirst + nlev + 1] = nr;
     }
   }
   __syncthreads();
   if (tid == 0) {
-    sig[kSigRanges] = nch > 0 ? 2 * nch - 1 : 0;
+    sig[kSigRanges] = nch > 0 ? 2 * nch - 1 + (cutn > 0 ? 1 : 0) : 0;
     sig[1] = (int)(hsh & 0xffffffffull); sig[2] = (int)(hsh >> 32);
     sig[3] = n_edges; sig[4] = nbuf; sig[5] = t0; sig[6] = P; sig[7] = lay0; sig[9] = lay1;
     __threadfence();

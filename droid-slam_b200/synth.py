@@ -116,7 +116,7 @@ def edges_global(Rs, ts, rad=2, knn=8, max_factors=None):
     return [p[0] for p in pairs], [p[1] for p in pairs]
 
 
-def make_ba_problem(name="C1", seed=1234, n_frames=None, stereo=False, sensor=False, nbuf=None, knn=8):
+def make_ba_problem(name="C1", seed=1234, n_frames=None, stereo=False, sensor=False, nbuf=None, knn=8, loop=None):
     """Returns a dict of float32/int64 numpy arrays: poses, disps, intrinsics, disps_sens, targets,
     weights, eta, ii, jj, t0, t1 (+ gt_poses, gt_disps).  C4 with n_frames=1000, knn=16 is the
     BASELINE.json backend configuration: 1000 keyframes, 20 862 edges (~20k), 40x64."""
@@ -137,7 +137,7 @@ def make_ba_problem(name="C1", seed=1234, n_frames=None, stereo=False, sensor=Fa
     elif name == "C4":    # backend: n_frames KF (default 1000), ~20 edges per KF, 40x64
         n = n_frames or 1000
         ht, wd, intr = 40, 64, EUROC_INTR
-        loop = 250
+        loop = loop or 250          # keyframes per lap (a larger value than n_frames: an open trajectory, no loop closures)
         ii = jj = None
     else:
         raise ValueError(name)
