@@ -473,7 +473,9 @@ __global__ void __launch_bounds__(1024) ba_order_kernel(const int64_t* __restric
     atomicAdd(&s_prof[pass], acc);
     __syncthreads();
   }
-  use_bfs = s_prof[1] * 10ull < s_prof[0] * 7ull;
+  // (long systems: the levels are also what the chains are cut from, so the breadth-first order is taken as soon as it
+  //  is not clearly worse than the natural one -- an open trajectory is banded already, but one chain)
+  use_bfs = s_prof[1] * 10ull < s_prof[0] * 7ull || (kreq >= 2 && s_prof[1] * 10ull <= s_prof[0] * 12ull);
   // Chains (long trajectories): every BFS level is a separator of the star graph (the members of a star lie in two
   // adjacent levels), so k - 1 levels near the quantiles of the order cut it into k mutually decoupled chains.  The
   // chains are eliminated concurrently and the separator levels last (chol.cu: droid_chol_solve_chains_f64); the
