@@ -14,6 +14,7 @@
 // (src/droid_kernels.cu:1207-1210).  No host synchronisation anywhere.
 #include "common.cuh"
 #include <cstdio>
+#include <cstring>
 #include <cstdlib>
 
 namespace droid {
@@ -1145,77 +1146,10 @@ int droid::launch_chol_small_damped(double* A, int n, float lm, float ep, int* i
   return check_launch();
 }
 
-namespace {
-using ChainCtx = droid::ChainStreams;
-struct ChainState {
-  int J, Jend;
-  bool on_side, finished;
-  cudaStream_t main;
-  ChainCtx* cx;
-  ChainArgs ca;
-  const int* hi64;
-  int* arrive;
-  bool prof;
-};
-}  // namespace
-
-static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_dev, int nranges,
-                                const int* range_end, int nlevels, const int* level_first, int* info_dev,
-                                void* workspace, size_t workspace_bytes, void* stream, bool private_scr);
-
-extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const int* firstc_dev, int nchains,
-                                           const int* chain_end, int* info_dev, void* workspace,
-                                           size_t workspace_bytes, void* stream) {
-  if (nchains < 0 || nchains > kMaxChains || (nchains > 0 && (!chain_end || !firstc_dev))) return DROID_ERR_INVALID_ARGUMENT;
-  // chains + ONE separator = a two-level tree (a single range when there are no chains)
-  int range_end[kMaxChains + 1], level_first[3] = {0, nchains, nchains + 1};
-  for (int c = 0; c < nchains; c++) range_end[c] = chain_end[c];
-  range_end[nchains] = n;
-  if (nchains == 0) { level_first[1] = 1; }
-  return chol_solve_tree_impl(A, b, n, firstc_dev, nchains + 1, range_end, nchains == 0 ? 1 : 2, level_first, info_dev,
-                              workspace, workspace_bytes, stream, true);
-}
-
-extern "C" int droid_chol_solve_tree_f64(double* A, double* b, int n, const int* firstc_dev, int nranges,
-                                         const int* range_end, int nlevels, const int* level_first, int* info_dev,
-                                         void* workspace, size_t workspace_bytes, void* stream) {
-  return chol_solve_tree_impl(A, b, n, firstc_dev, nranges, range_end, nlevels, level_first, info_dev, workspace,
-                              workspace_bytes, stream, false);
-}
-
-// private_scr: every range of a level but the first accumulates its updates of the rows behind the level in a scratch
-// copy of its own (general coupling); otherwise ranges at odd positions share ONE copy per level (path structure).
-static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_dev, int nranges,
-                                const int* range_end, int nlevels, const int* level_first, int* info_dev,
-                                void* workspace, size_t workspace_bytes, void* stream, bool private_scr) {
-  if (n < 0 || !info_dev) return DROID_ERR_INVALID_ARGUMENT;
-  if (n == 0) return DROID_OK;
-  if (!A || !b) return DROID_ERR_INVALID_ARGUMENT;
-  if (b != A + (size_t)n * n) return DROID_ERR_INVALID_ARGUMENT;  // rhs must be row n of A
-  if (nranges < 1 || nranges > kMaxRanges || !range_end || nlevels < 1 || nlevels > nranges || !level_first ||
-      (nranges > 1 && !firstc_dev))
-    return DROID_ERR_INVALID_ARGUMENT;
-  if (level_first[0] != 0 || level_first[nlevels] != nranges || range_end[nranges - 1] != n) return DROID_ERR_INVALID_ARGUMENT;
-  for (int l = 0; l < nlevels; l++)
-    if (level_first[l + 1] <= level_first[l] || level_first[l + 1] - level_first[l] > kMaxChains) return DROID_ERR_INVALID_ARGUMENT;
-  const int nchains = nranges - 1;      // ranges besides the last one (sizes the per-range tables: nchains + 1 entries)
-  cudaStream_t st = (cudaStream_t)stream;
-  static const bool trace0 = []() { const char* e = getenv("DROID_CHOL_TRACE"); return e && e[0] == '1'; }();
-  cudaEvent_t tev0 = nullptr;
-  if (trace0) { cudaEventCreate(&tev0); cudaEventRecord(tev0, st); }
-  cudaMemsetAsync(info_dev, 0, sizeof(int), st);
-  if (n <= kSmallMax) {
-    if (nranges > 1) return DROID_ERR_INVALID_ARGUMENT;
-    if (dev_ctx().first(kOnceCholSmall))
-      cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmemMax);
-    const size_t smem = chol_small_smem(n);
-    DROID_LAUNCH chol_small_kernel<<<1, ((n + 1 + 31) / 32) * 32, smem, st>>>(A, n, info_dev, 0, 0.f, 0.f);
-    return check_launch();
-  }
-  DevCtx& dc = dev_ctx();
-  std::lock_guard<std::recursive_mutex> call_lock(dc.call);   // the side streams / events below are shared per device
-  constexpr int kSyrk128 = (2 * 2 * 16 * (128 + 2) + 128 * 128) * (int)sizeof(double);
-  constexpr int kSyrk64 = (2 * 2 * 16 * (64 + 2) + 64 * 64) * (int)sizeof(double);
+static constexpr int kSyrk128 = (2 * 2 * 16 * (128 + 2) + 128 * 128) * (int)sizeof(double);
+static constexpr int kSyrk64 = (2 * 2 * 16 * (64 + 2) + 64 * 64) * (int)sizeof(double);
+// once per device: shared-memory opt-ins, the pairs of streams and the events of the concurrent ranges
+static void chol_setup(DevCtx& dc) {
   if (dc.first(kOnceChol)) {
     cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPanelSmem2);
     cudaFuncSetAttribute(chol_bwd_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem);
@@ -1239,6 +1173,175 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
     }
     cudaEventCreateWithFlags(&dc.chol_start, cudaEventDisableTiming);
   }
+}
+
+namespace {
+using ChainCtx = droid::ChainStreams;
+struct ChainState {
+  int J, Jend;
+  bool on_side, finished;
+  bool r_recorded;          // cx->r was recorded by THIS range (an event of an earlier call must not be waited on in a capture)
+  cudaStream_t main;
+  ChainCtx* cx;
+  ChainArgs ca;
+  const int* hi64;
+  int* arrive;
+  bool prof;
+};
+}  // namespace
+
+static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_dev, int nranges,
+                                const int* range_end, int nlevels, const int* level_first, int* info_dev,
+                                void* workspace, size_t workspace_bytes, void* stream, bool private_scr);
+static int chol_solve_tree_enqueue(double* A, double* b, int n, const int* firstc_dev, int nranges,
+                                   const int* range_end, int nlevels, const int* level_first, int* info_dev,
+                                   void* workspace, size_t workspace_bytes, void* stream, bool private_scr,
+                                   bool capturing);
+
+extern "C" int droid_chol_solve_chains_f64(double* A, double* b, int n, const int* firstc_dev, int nchains,
+                                           const int* chain_end, int* info_dev, void* workspace,
+                                           size_t workspace_bytes, void* stream) {
+  if (nchains < 0 || nchains > kMaxChains || (nchains > 0 && (!chain_end || !firstc_dev))) return DROID_ERR_INVALID_ARGUMENT;
+  // chains + ONE separator = a two-level tree (a single range when there are no chains)
+  int range_end[kMaxChains + 1], level_first[3] = {0, nchains, nchains + 1};
+  for (int c = 0; c < nchains; c++) range_end[c] = chain_end[c];
+  range_end[nchains] = n;
+  if (nchains == 0) { level_first[1] = 1; }
+  return chol_solve_tree_impl(A, b, n, firstc_dev, nchains + 1, range_end, nchains == 0 ? 1 : 2, level_first, info_dev,
+                              workspace, workspace_bytes, stream, true);
+}
+
+extern "C" int droid_chol_solve_tree_f64(double* A, double* b, int n, const int* firstc_dev, int nranges,
+                                         const int* range_end, int nlevels, const int* level_first, int* info_dev,
+                                         void* workspace, size_t workspace_bytes, void* stream) {
+  return chol_solve_tree_impl(A, b, n, firstc_dev, nranges, range_end, nlevels, level_first, info_dev, workspace,
+                              workspace_bytes, stream, false);
+}
+
+// private_scr: every range of a level but the first accumulates its updates of the rows behind the level in a scratch
+// copy of its own (general coupling); otherwise ranges at odd positions share ONE copy per level (path structure).
+// ------------------------------------------------------------------------------------------------
+// The tree solve as a CUDA GRAPH.  A solve over 8 chains is ~400 small launches on 16 streams with ~250 event
+// operations between them; one host thread needs ~13 us per chain step for that, which with 8 chains in flight is more
+// than a step takes on the device (the chains were launch-bound: 117 us per 128 columns instead of 70).  The launch
+// sequence depends only on (n, tree layout) and the pointers, so it is captured once -- on an internal stream, the
+// caller's may be the legacy default stream, which cannot be captured -- and replayed with one cudaGraphLaunch into
+// the caller's stream.  A few graphs are kept per device (the backend alternates between at most a couple of layouts).
+// DROID_CHOL_GRAPH=0 or DROID_CHOL_TRACE=1: direct launches.
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct GraphKey {
+  const void *A, *firstc, *info, *ws;
+  size_t ws_bytes;
+  int n, nranges, nlevels, priv;
+  int range_end[kMaxRanges], level_first[kMaxRanges + 1];
+};
+struct GraphEntry {
+  GraphKey key;
+  cudaGraphExec_t exec = nullptr;
+  unsigned long long launches = 0, stamp = 0;
+  bool unusable = false;            // capture failed for this key once: do not try again
+};
+constexpr int kGraphSlots = 4;
+GraphEntry g_graphs[64][kGraphSlots];
+unsigned long long g_graph_clock = 0;
+}  // namespace
+
+static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_dev, int nranges,
+                                const int* range_end, int nlevels, const int* level_first, int* info_dev,
+                                void* workspace, size_t workspace_bytes, void* stream, bool private_scr) {
+  static const bool graph_on = []() { const char* e = getenv("DROID_CHOL_GRAPH"); return !(e && e[0] == '0'); }();
+  static const bool trace_env = []() { const char* e = getenv("DROID_CHOL_TRACE"); return e && e[0] == '1'; }();
+  if (!graph_on || trace_env || nranges < 3 || nranges > kMaxRanges || nlevels < 1 || nlevels > nranges || !range_end ||
+      !level_first || n <= kSmallMax)
+    return chol_solve_tree_enqueue(A, b, n, firstc_dev, nranges, range_end, nlevels, level_first, info_dev, workspace,
+                                   workspace_bytes, stream, private_scr, false);
+  DevCtx& dc = dev_ctx();
+  std::lock_guard<std::recursive_mutex> call_lock(dc.call);
+  GraphKey key;
+  memset(&key, 0, sizeof(key));
+  key.A = A; key.firstc = firstc_dev; key.info = info_dev; key.ws = workspace; key.ws_bytes = workspace_bytes;
+  key.n = n; key.nranges = nranges; key.nlevels = nlevels; key.priv = private_scr ? 1 : 0;
+  for (int c = 0; c < nranges; c++) key.range_end[c] = range_end[c];
+  for (int l = 0; l <= nlevels; l++) key.level_first[l] = level_first[l];
+  GraphEntry* slots = g_graphs[dc.device & 63];
+  GraphEntry* hit = nullptr;
+  GraphEntry* victim = &slots[0];
+  for (int i = 0; i < kGraphSlots; i++) {
+    if ((slots[i].exec != nullptr || slots[i].unusable) && memcmp(&slots[i].key, &key, sizeof(key)) == 0) hit = &slots[i];
+    if (slots[i].stamp < victim->stamp) victim = &slots[i];
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (hit == nullptr) {
+    chol_setup(dc);
+    cudaStream_t origin = dc.chain[0].main;
+    if (victim->exec != nullptr) { cudaGraphExecDestroy(victim->exec); victim->exec = nullptr; }
+    victim->key = key; victim->unusable = true; victim->launches = 0;
+    hit = victim;
+    const unsigned long long count0 = g_launch_count.load();
+    if (cudaStreamBeginCapture(origin, cudaStreamCaptureModeRelaxed) == cudaSuccess) {
+      const int rc = chol_solve_tree_enqueue(A, b, n, firstc_dev, nranges, range_end, nlevels, level_first, info_dev,
+                                             workspace, workspace_bytes, origin, private_scr, true);
+      cudaGraph_t g = nullptr;
+      const cudaError_t e = cudaStreamEndCapture(origin, &g);
+      if (rc == DROID_OK && e == cudaSuccess && g != nullptr) {
+        cudaGraphExec_t exec = nullptr;
+        if (cudaGraphInstantiate(&exec, g, 0) == cudaSuccess && exec != nullptr) {
+          hit->exec = exec; hit->unusable = false;
+          hit->launches = g_launch_count.load() - count0;
+        }
+      }
+      if (g != nullptr) cudaGraphDestroy(g);
+      if (rc != DROID_OK && (rc == DROID_ERR_INVALID_ARGUMENT || rc == DROID_ERR_WORKSPACE_TOO_SMALL)) {
+        cudaGetLastError();
+        g_launch_count.store(count0);
+        return rc;                                  // the caller's mistake, not the capture's
+      }
+    }
+    cudaGetLastError();
+    g_launch_count.store(count0);                   // captured, not launched
+  }
+  hit->stamp = ++g_graph_clock;
+  if (hit->exec == nullptr)                          // capture not possible here: direct launches
+    return chol_solve_tree_enqueue(A, b, n, firstc_dev, nranges, range_end, nlevels, level_first, info_dev, workspace,
+                                   workspace_bytes, stream, private_scr, false);
+  if (cudaGraphLaunch(hit->exec, st) != cudaSuccess) { g_last_error = cudaGetLastError(); return DROID_ERR_CUDA; }
+  g_launch_count += hit->launches;
+  return DROID_OK;
+}
+
+static int chol_solve_tree_enqueue(double* A, double* b, int n, const int* firstc_dev, int nranges,
+                                   const int* range_end, int nlevels, const int* level_first, int* info_dev,
+                                   void* workspace, size_t workspace_bytes, void* stream, bool private_scr,
+                                   bool capturing) {
+  if (n < 0 || !info_dev) return DROID_ERR_INVALID_ARGUMENT;
+  if (n == 0) return DROID_OK;
+  if (!A || !b) return DROID_ERR_INVALID_ARGUMENT;
+  if (b != A + (size_t)n * n) return DROID_ERR_INVALID_ARGUMENT;  // rhs must be row n of A
+  if (nranges < 1 || nranges > kMaxRanges || !range_end || nlevels < 1 || nlevels > nranges || !level_first ||
+      (nranges > 1 && !firstc_dev))
+    return DROID_ERR_INVALID_ARGUMENT;
+  if (level_first[0] != 0 || level_first[nlevels] != nranges || range_end[nranges - 1] != n) return DROID_ERR_INVALID_ARGUMENT;
+  for (int l = 0; l < nlevels; l++)
+    if (level_first[l + 1] <= level_first[l] || level_first[l + 1] - level_first[l] > kMaxChains) return DROID_ERR_INVALID_ARGUMENT;
+  const int nchains = nranges - 1;      // ranges besides the last one (sizes the per-range tables: nchains + 1 entries)
+  cudaStream_t st = (cudaStream_t)stream;
+  static const bool trace_env = []() { const char* e = getenv("DROID_CHOL_TRACE"); return e && e[0] == '1'; }();
+  const bool trace0 = trace_env && !capturing;
+  cudaEvent_t tev0 = nullptr;
+  if (trace0) { cudaEventCreate(&tev0); cudaEventRecord(tev0, st); }
+  cudaMemsetAsync(info_dev, 0, sizeof(int), st);
+  if (n <= kSmallMax) {
+    if (nranges > 1) return DROID_ERR_INVALID_ARGUMENT;
+    if (dev_ctx().first(kOnceCholSmall))
+      cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmallSmemMax);
+    const size_t smem = chol_small_smem(n);
+    DROID_LAUNCH chol_small_kernel<<<1, ((n + 1 + 31) / 32) * 32, smem, st>>>(A, n, info_dev, 0, 0.f, 0.f);
+    return check_launch();
+  }
+  DevCtx& dc = dev_ctx();
+  std::lock_guard<std::recursive_mutex> call_lock(dc.call);   // the side streams / events below are shared per device
+  chol_setup(dc);
   const bool vec = (n % 2 == 0) && (((uintptr_t)A & 15) == 0);
   const int nb = (n + 63) / 64;
   // ranges in elimination-tree layout: range r = [range_end[r-1], range_end[r]), levels = runs of consecutive ranges
@@ -1347,7 +1450,7 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
     if (cs.on_side) {
       const bool big = hi == nullptr && t128 * (t128 + 1) / 2 >= dc.sm_count;
       cudaEventRecord(cx.p, cx.side);
-      cudaStreamWaitEvent(cx.side, cx.r, 0);    // R(J-1) (no-op for the first panel)
+      if (cs.r_recorded) cudaStreamWaitEvent(cx.side, cx.r, 0);    // R(J-1)
       if (big) DROID_LAUNCH chol_syrk_kernel<128, true><<<t128, 256, kSyrk128, cx.side>>>(A, n, J, kb, PB, hi, cs.ca, 1 << 30, 0);
       else DROID_LAUNCH chol_syrk_kernel<64, true><<<2 * t64, 256, kSyrk64, cx.side>>>(A, n, J, kb, PB, hi, cs.ca, na, nskip);
       cudaStreamWaitEvent(m, cx.p, 0);
@@ -1358,6 +1461,7 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
         if (cs.prof) prof_mark(DROID_PROF_CHOL_SYRK, false, m);
       }
       cudaEventRecord(cx.r, m);
+      cs.r_recorded = true;
     } else {
       if (cs.prof) prof_mark(DROID_PROF_CHOL_SYRK, true, m);
       if (hi == nullptr && t128 * (t128 + 1) / 2 >= dc.sm_count) {
@@ -1375,7 +1479,7 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
   // ranges of the same parity never touch the same higher-level block (neighbours in the path order alternate)
   auto open_range = [&](ChainState& cs, int c, int lv, int idx, cudaStream_t m, ChainCtx* cx, bool prof) {
     cs.J = rg.b[c]; cs.Jend = rg.b[c + 1];
-    cs.main = m; cs.cx = cx; cs.prof = prof;
+    cs.main = m; cs.cx = cx; cs.prof = prof && !capturing; cs.r_recorded = false;
     cs.finished = cs.J >= cs.Jend;
     const int behind = lv + 1 < nlevels ? rg.b[level_first[lv + 1]] : n;     // first row behind this level
     cs.ca.hole_lo = cs.ca.hole_hi = 0; cs.ca.sep = behind; cs.ca.scr = nullptr; cs.ca.lds = n - behind;
@@ -1404,7 +1508,7 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
     }
   };
   // DROID_CHOL_TRACE=1: device time of every stage of the solve (events on the caller's stream; synchronises; debug aid)
-  static const bool trace = []() { const char* e = getenv("DROID_CHOL_TRACE"); return e && e[0] == '1'; }();
+  const bool trace = trace0;
   cudaEvent_t tev[2 * kMaxRanges + 8];
   const char* tname[2 * kMaxRanges + 8];
   int ntev = 0;
@@ -1454,7 +1558,8 @@ static int chol_solve_tree_impl(double* A, double* b, int n, const int* firstc_d
                                                                        scr_stride[lv], n - behind);
     }
   }
-  ProfScope psb(DROID_PROF_CHOL_BWD, st);
+  if (!capturing) prof_mark(DROID_PROF_CHOL_BWD, true, st);
+  struct BwdEnd { bool on; cudaStream_t s; ~BwdEnd() { if (on) prof_mark(DROID_PROF_CHOL_BWD, false, s); } } bwd_end{!capturing, st};
   if (persist_bwd) {
     for (int lv = nlevels - 1; lv >= 0; lv--) {
       const int cnt = level_first[lv + 1] - level_first[lv];
