@@ -338,6 +338,9 @@ def run_b200(args, world, rank, local):
     per_phase = {k: {"ms_per_launch": v[0] / max(v[1], 1), "launches": v[1], "share": v[0] / ms}
                  for k, v in phases.items() if v[1] > 0}
     tf32_peak = float(peaks.get("bf16_tflops", 1590.0)) / 2.0          # tcgen05 kind::tf32 runs at half the bf16 rate
+    if world > 1:                      # the algorithmic bytes / flops below are the whole job's: so is the roof
+        hbm_peak *= world
+        tf32_peak *= world
     ms_of = lambda k: per_phase[k]["ms_per_launch"] if k in per_phase else float("nan")   # noqa: E731
     # per-phase table: every throughput kernel against the roof that bounds it
     table = {}
@@ -386,7 +389,8 @@ def run_b200(args, world, rank, local):
             "unit": table[dom]["unit"], "frac": table[dom]["frac"], "traffic": table[dom].get("traffic"),
             "traffic_source": traffic.get("source") if table[dom].get("traffic") else None,
             "peak_source": ("measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md)") +
-                           ("; tf32 = bf16_tflops / 2" if table[dom]["bound"] == "tensor" else ""),
+                           ("; tf32 = bf16_tflops / 2" if table[dom]["bound"] == "tensor" else "") +
+                           ("; x %d GPUs (achieved is the whole job's)" % world if world > 1 else ""),
             "ms_per_launch": table[dom]["ms"],
             "longest_phase": {"kernel": longest, "ms": table[longest]["ms"], "share_of_iteration": table[longest]["ms"] / (ms / iters),
                               "bound": table[longest]["bound"],
@@ -447,7 +451,12 @@ def parity_check(B, p, d, poses0, disps0, dev, world, rank, bounds):
     if world > 1:
         if rank == 0:
             single = call(B.ba)
-            out["sharded_vs_single_gpu"] = {"dx": rel(mine[2], single[2]), "dz": rel(mine[3], single[3]),
+            # ba_sharded returns the depth step of the rank's OWN source frames (the depth maps are all-gathered)
+            kx = torch.unique(d["ii"])
+            own = ((kx >= bounds[0]) & (kx < bounds[1]))[:, None]
+            hw = mine[3].numel() // kx.numel()
+            own = own.expand(-1, hw).reshape(-1)
+            out["sharded_vs_single_gpu"] = {"dx": rel(mine[2], single[2]), "dz": rel(mine[3][own], single[3][own]),
                                             "poses": rel(mine[0], single[0]), "disps": rel(mine[1], single[1])}
             mine = single
     if rank != 0:
@@ -464,7 +473,7 @@ def parity_check(B, p, d, poses0, disps0, dev, world, rank, bounds):
         out["ok"] = None
     if "sharded_vs_single_gpu" in out:
         v = out["sharded_vs_single_gpu"]
-        out["sharded_ok"] = bool(v["poses"] <= 1e-5 and v["disps"] <= 1e-5 and v["dx"] <= 5e-4)
+        out["sharded_ok"] = bool(v["poses"] <= 1e-5 and v["disps"] <= 1e-5 and v["dx"] <= 5e-4 and v["dz"] <= 5e-4)
     return out
 
 

@@ -21,16 +21,16 @@
 //    therefore starts a fresh accumulator, and the chunks are summed with ordinary fp32 adds in registers.
 //
 // Warp roles (512 threads, one CTA per SM, CTA = (pixel slab, source frame, pair of edge groups)):
-//   warps 0-7   builders: stream the packed E_j of every (pixel, edge) (left behind by ba_accum_kernel), stage the
-//               chunk's F as plain fp32 in shared memory, then re-pack it (split + 16-byte stores) into the canonical
-//               MN-major UMMA layout for 32-bit operands (SWIZZLE_128B_BASE32B);
+//   warps 0-7   builders: stream the packed E_j of every (pixel, edge) (left behind by ba_accum_kernel) into
+//               registers one pass ahead, unpack, scale by sqrt(Q), split into tf32 hi + lo and store straight into
+//               the K-major UMMA operand tiles (SWIZZLE_128B, one 16-byte store per row and array; no fp32 staging);
 //   warp 13     one thread issues the 12 tcgen05.mma of a chunk into TMEM accumulator (chunk & 3);
 //   warps 8-11, 14-15  drainers: TMEM -> registers, fp32 accumulation of half a row of G per thread;
 //   epilogue    (all warps) G goes to shared memory, the source pose's rows are derived from it, and everything is
 //               subtracted from the dense reduced system with fp64 atomics, lanes along a row (same block placement
 //               rules as flush_block in ba.cu).
-// Operand stages, fp32 staging and TMEM accumulators are all double-buffered: building chunk c+1, the MMAs of chunk c
-// and the drain of chunk c-1 overlap.
+// Four operand stages and four TMEM accumulators: building chunk c+1, the MMAs of chunk c and the drain of chunk c-1
+// overlap.
 #include <cstdint>
 
 #include "ba_lin.cuh"
