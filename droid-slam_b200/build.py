@@ -13,7 +13,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 OBJDIR = os.path.join(HERE, "build")
 LIB = os.path.join(LIBDIR, "libdroid_b200.so")
-SOURCES = ["runtime.cu", "geom.cu", "corr_lookup.cu", "altcorr.cu", "ba.cu", "schur_tc.cu", "chol.cu", "corr_build.cu", "edges.cu", "upsample.cu", "scatter.cu"]
+SOURCES = ["runtime.cu", "geom.cu", "corr_lookup.cu", "altcorr.cu", "altcorr_tc.cu", "ba.cu", "schur_tc.cu", "chol.cu", "corr_build.cu", "edges.cu", "upsample.cu", "scatter.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",

@@ -49,7 +49,8 @@ template <typename TF, int CPL /*channels per lane, multiple of 4*/>
 __global__ void __launch_bounds__(256) altcorr_fwd_r3_kernel(
     const TF* __restrict__ f1_base, const TF* __restrict__ f2_base, const int64_t* __restrict__ ii,
     const int64_t* __restrict__ jj, const float* __restrict__ coords, float* __restrict__ out, int N,
-    int HW1, int H2, int W2, int C) {
+    int HW1, int H2, int W2, int C, const int* __restrict__ only_if) {
+  if (only_if && *only_if == 0) return;      // the tensor-core kernel (altcorr_tc.cu) has done the work
   __shared__ float taps[8][64];
   __shared__ float stage[49][8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -66,7 +67,7 @@ __global__ void __launch_bounds__(256) altcorr_fwd_r3_kernel(
     const float fx0 = floorf(x0), fy0 = floorf(y0);
     dx = x0 - fx0;
     dy = y0 - fy0;
-    const int xs = (int)fx0 - 3, ys = (int)fy0 - 3;
+    const int xs = window_origin(fx0, 3), ys = window_origin(fy0, 3);
     const TF* f1 = f1_base + (i1 * HW1 + pix) * (size_t)C + lane * CPL;
     const TF* f2 = f2_base + i2 * ((size_t)H2 * W2) * C + lane * CPL;
     float4 a[CPL / 4];
@@ -134,7 +135,7 @@ __global__ void __launch_bounds__(256) altcorr_fwd_generic_kernel(
   const float x0 = cp[0], y0 = cp[1];
   const float fx0 = floorf(x0), fy0 = floorf(y0);
   const float dx = x0 - fx0, dy = y0 - fy0;
-  const int xs = (int)fx0 - r, ys = (int)fy0 - r;
+  const int xs = window_origin(fx0, r), ys = window_origin(fy0, r);
   const float* f1 = f1_base + ((size_t)b * HW1 + pix) * (size_t)C;
   const float* f2 = f2_base + (size_t)b * ((size_t)H2 * W2) * C;
   for (int iy = 0; iy < rt; iy++)
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__(256) altcorr_bwd_kernel(
   const float x0 = cp[0], y0 = cp[1];
   const float fx0 = floorf(x0), fy0 = floorf(y0);
   const float dx = x0 - fx0, dy = y0 - fy0;
-  const int xs = (int)fx0 - r, ys = (int)fy0 - r;
+  const int xs = window_origin(fx0, r), ys = window_origin(fy0, r);
   const float* gp = cg + ((size_t)b * N + n) * rd * rd * HW1 + pix;
   // per-tap gradient, reference order (:242-252): nw, ne, sw, se
   for (int t = lane; t < rt * rt; t += 32) {
@@ -214,9 +215,26 @@ __global__ void __launch_bounds__(256) altcorr_bwd_kernel(
   }
 }
 
+// altcorr_tc.cu
+bool altcorr_tc_supported(int B, int N, int H1, int W1, int H2, int W2, int C, int radius, size_t frames1, size_t frames2);
+int altcorr_tc_forward(const void* f1, const void* f2, const int64_t* ii, const int64_t* jj, const float* coords, float* out,
+                       const int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int H2, int W2,
+                       int C, int radius, cudaStream_t st);
+int altcorr_tc_convert(const float* f1, const float* f2, void* f1h, void* f2h, int* flag, size_t n1, size_t n2,
+                       cudaStream_t st);
+
+static bool tc_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("DROID_ALTCORR_TC");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
+// `only_if` (may be null): device flag; the CUDA-core kernel runs only when it is non-zero.
 static int fwd_common(const void* f1, const void* f2, const int64_t* ii, const int64_t* jj,
                       const float* coords, float* out, int dtype, int B, int N, int H1, int W1,
-                      int H2, int W2, int C, int radius, cudaStream_t st) {
+                      int H2, int W2, int C, int radius, cudaStream_t st, const int* only_if = nullptr) {
   const int HW1 = H1 * W1;
   if (N > 65535 || B > 65535) return DROID_ERR_INVALID_ARGUMENT;
   dim3 grid((HW1 + 7) / 8, N, B);
@@ -226,7 +244,7 @@ static int fwd_common(const void* f1, const void* f2, const int64_t* ii, const i
 #define ALT_LAUNCH(TF, CPL)                                                                     \
   DROID_LAUNCH altcorr_fwd_r3_kernel<TF, CPL><<<grid, 256, 0, st>>>(reinterpret_cast<const TF*>(f1),          \
                                                         reinterpret_cast<const TF*>(f2), ii, jj, \
-                                                        coords, out, N, HW1, H2, W2, C)
+                                                        coords, out, N, HW1, H2, W2, C, only_if)
     if (dtype == DROID_DTYPE_F32) {
       if (C == 128) ALT_LAUNCH(float, 4);
       else if (C == 256) ALT_LAUNCH(float, 8);
@@ -243,7 +261,7 @@ static int fwd_common(const void* f1, const void* f2, const int64_t* ii, const i
     return check_launch();
   }
 generic:
-  if (dtype != DROID_DTYPE_F32 || ii || jj) return DROID_ERR_UNSUPPORTED_DTYPE;
+  if (dtype != DROID_DTYPE_F32 || ii || jj || only_if) return DROID_ERR_UNSUPPORTED_DTYPE;
   {
     const int rt = 2 * radius + 2;
     size_t smem = (size_t)8 * rt * rt * sizeof(float);
@@ -271,6 +289,46 @@ extern "C" int droid_altcorr_forward(const void* fmap1, const void* fmap2, const
                     N, H1, W1, H2, W2, C, radius, (cudaStream_t)stream);
 }
 
+// Workspace of droid_altcorr_forward_ws: fp16 copies of both maps + the exactness flag; 0 = shape not covered by the
+// tensor-core kernel (the call then behaves exactly like droid_altcorr_forward).
+extern "C" size_t droid_altcorr_forward_workspace_bytes(int B, int N, int H1, int W1, int H2, int W2, int C, int radius) {
+  if (B <= 0 || N <= 0 || H1 <= 0 || W1 <= 0 || H2 <= 0 || W2 <= 0) return 0;
+  if (!tc_enabled() || !altcorr_tc_supported(B, N, H1, W1, H2, W2, C, radius, (size_t)B, (size_t)B)) return 0;
+  const size_t n1 = (size_t)B * H1 * W1 * C, n2 = (size_t)B * H2 * W2 * C;
+  return 256 + ((n1 * 2 + 255) & ~(size_t)255) + ((n2 * 2 + 255) & ~(size_t)255) + 256;
+}
+
+extern "C" int droid_altcorr_forward_ws(const void* fmap1, const void* fmap2, const float* coords, void* out,
+                                        int dtype, int B, int N, int H1, int W1, int H2, int W2, int C, int radius,
+                                        void* workspace, size_t workspace_bytes, void* stream) {
+  if (B < 0 || N < 0 || H1 <= 0 || W1 <= 0 || H2 <= 0 || W2 <= 0 || C <= 0 || radius < 0)
+    return DROID_ERR_INVALID_ARGUMENT;
+  if (B == 0 || N == 0) return DROID_OK;
+  if (!fmap1 || !fmap2 || !coords || !out) return DROID_ERR_INVALID_ARGUMENT;
+  if (dtype != DROID_DTYPE_F32) return DROID_ERR_UNSUPPORTED_DTYPE;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t need = droid_altcorr_forward_workspace_bytes(B, N, H1, W1, H2, W2, C, radius);
+  const bool aligned = (((uintptr_t)fmap1 | (uintptr_t)fmap2 | (uintptr_t)workspace) & 15) == 0;
+  if (need && workspace && workspace_bytes >= need && aligned) {
+    const size_t n1 = (size_t)B * H1 * W1 * C, n2 = (size_t)B * H2 * W2 * C;
+    unsigned char* w = reinterpret_cast<unsigned char*>(workspace);
+    int* flag = reinterpret_cast<int*>(w);
+    void* f1h = w + 256;
+    void* f2h = w + 256 + ((n1 * 2 + 255) & ~(size_t)255);
+    int rc = altcorr_tc_convert(reinterpret_cast<const float*>(fmap1), reinterpret_cast<const float*>(fmap2), f1h, f2h,
+                                flag, n1, n2, st);
+    if (rc != DROID_OK) return rc;
+    rc = altcorr_tc_forward(f1h, f2h, nullptr, nullptr, coords, reinterpret_cast<float*>(out), flag, (size_t)B, (size_t)B,
+                            B, N, H1, W1, H2, W2, C, radius, st);
+    if (rc == DROID_OK)      // behind it, gated on the flag: the CUDA-core kernel for inputs that are not fp16 values
+      return fwd_common(fmap1, fmap2, nullptr, nullptr, coords, reinterpret_cast<float*>(out), dtype, B, N, H1, W1, H2,
+                        W2, C, radius, st, flag);
+    if (rc != DROID_ERR_NOT_IMPLEMENTED) return rc;
+  }
+  return fwd_common(fmap1, fmap2, nullptr, nullptr, coords, reinterpret_cast<float*>(out), dtype, B, N, H1, W1, H2, W2,
+                    C, radius, st);
+}
+
 extern "C" int droid_altcorr_forward_indexed(const void* pyr0, const void* pyrL, const int64_t* ii,
                                              const int64_t* jj, const float* coords, float* out,
                                              int dtype, int F, int B, int N, int H1, int W1, int H2,
@@ -280,6 +338,11 @@ extern "C" int droid_altcorr_forward_indexed(const void* pyr0, const void* pyrL,
   if (B == 0 || N == 0) return DROID_OK;
   if (!pyr0 || !pyrL || !ii || !jj || !coords || !out) return DROID_ERR_INVALID_ARGUMENT;
   if (C != 128 && C != 256) return DROID_ERR_INVALID_ARGUMENT;
+  if (dtype == DROID_DTYPE_F16 && tc_enabled()) {
+    const int rc = altcorr_tc_forward(pyr0, pyrL, ii, jj, coords, out, nullptr, (size_t)F, (size_t)F, B, N, H1, W1, H2,
+                                      W2, C, radius, (cudaStream_t)stream);
+    if (rc != DROID_ERR_NOT_IMPLEMENTED) return rc;
+  }
   return fwd_common(pyr0, pyrL, ii, jj, coords, out, dtype, B, N, H1, W1, H2, W2, C, radius,
                     (cudaStream_t)stream);
 }

@@ -142,8 +142,8 @@ __device__ __forceinline__ void lookup_load_r3(const T* __restrict__ vol, int b,
   const int row = threadIdx.x & 7;
   const float fx0 = floorf(x0), fy0 = floorf(y0);
   R.dx = x0 - fx0; R.dy = y0 - fy0;
-  const int xs = (int)fx0 - 3;
-  const int ys = (int)fy0 - 3 + row;
+  const int xs = window_origin(fx0, 3);
+  const int ys = window_origin(fy0, 3) + row;
   const bool rv = pv && ys >= 0 && ys < H2;
   if (rv) {
     const T* rowp = vol + ((size_t)b * HW1 + pix) * ((size_t)H2 * W2) + (size_t)ys * W2;
@@ -319,7 +319,7 @@ __global__ void __launch_bounds__(256) corr_index_fwd_generic_kernel(
   const float y0 = coords[((size_t)b * 2 + 1) * HW1 + pix];
   const float fx0 = floorf(x0), fy0 = floorf(y0);
   const float dx = x0 - fx0, dy = y0 - fy0;
-  const int xs = (int)fx0 - r, ys = (int)fy0 - r;
+  const int xs = window_origin(fx0, r), ys = window_origin(fy0, r);
   const T w00 = Arith<T>::wcast((1.0f - dx) * (1.0f - dy));
   const T w01 = Arith<T>::wcast((1.0f - dx) * dy);
   const T w10 = Arith<T>::wcast(dx * (1.0f - dy));
@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(256) corr_index_bwd_kernel(const float* __rest
   const float y0 = coords[((size_t)b * 2 + 1) * HW1 + pix];
   const float fx0 = floorf(x0), fy0 = floorf(y0);
   const float dx = x0 - fx0, dy = y0 - fy0;
-  const int xs = (int)fx0 - r, ys = (int)fy0 - r;
+  const int xs = window_origin(fx0, r), ys = window_origin(fy0, r);
   const T w00 = Arith<T>::wcast((1.0f - dx) * (1.0f - dy));
   const T w01 = Arith<T>::wcast((1.0f - dx) * dy);
   const T w10 = Arith<T>::wcast(dx * (1.0f - dy));

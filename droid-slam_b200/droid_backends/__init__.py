@@ -71,6 +71,7 @@ def _load():
     lib.droid_scatter_mean_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_filter_edges_workspace_bytes.restype = ctypes.c_size_t
     lib.droid_frame_distance_workspace_bytes.restype = ctypes.c_size_t
+    lib.droid_altcorr_forward_workspace_bytes.restype = ctypes.c_size_t
     return lib
 
 
@@ -80,7 +81,8 @@ __version__ = _lib.droid_version().decode()
 # names every build of the library must export (checked by tests/test_abi.py against the header)
 C_ABI_SYMBOLS = [
     "droid_version", "droid_last_cuda_error", "droid_launch_count", "droid_prof_enable", "droid_prof_read", "droid_corr_index_forward", "droid_corr_index_backward",
-    "droid_corr_index_pyramid", "droid_altcorr_forward", "droid_altcorr_backward",
+    "droid_corr_index_pyramid", "droid_altcorr_forward", "droid_altcorr_forward_ws",
+    "droid_altcorr_forward_workspace_bytes", "droid_altcorr_backward",
     "droid_altcorr_forward_indexed", "droid_corr_build", "droid_corr_build_workspace_bytes",
     "droid_frame_distance", "droid_frame_distance_workspace_bytes", "droid_frame_distance_ws",
     "droid_frame_distance_noalloc_max_pixels", "droid_frame_distance_noalloc", "droid_projmap", "droid_reproject", "droid_iproj", "droid_depth_filter",
@@ -209,7 +211,8 @@ def corr_index_pyramid(volumes, coords, radius=3):
 # ------------------------------------------------------------------------------------------------
 # alt correlation                                            reference: src/droid.cpp:193-217
 # ------------------------------------------------------------------------------------------------
-def altcorr_forward(fmap1, fmap2, coords, radius):
+def altcorr_forward(fmap1, fmap2, coords, radius, _plain=False):
+    """``_plain`` (tests): the entry point without a workspace, i.e. always the CUDA-core kernel."""
     _contig("altcorr_forward", fmap1=fmap1, fmap2=fmap2, coords=coords)
     _dtype("altcorr_forward", fmap1, (torch.float32,))
     _dtype("altcorr_forward", fmap2, (torch.float32,))
@@ -220,8 +223,13 @@ def altcorr_forward(fmap1, fmap2, coords, radius):
     rd = 2 * radius + 1
     with torch.cuda.device(fmap1.device):
         out = torch.empty((B, N, rd * rd, H, W), dtype=fmap1.dtype, device=fmap1.device)
-        _check(_lib.droid_altcorr_forward(_p(fmap1), _p(fmap2), _p(coords), _p(out), _F32, B, N, H1,
-                                          W1, H2, W2, C, int(radius), _stream(fmap1)),
+        # tensor-core path (altcorr_tc.cu): fp16 copies of the maps + an exactness flag live in a workspace; the
+        # CUDA-core kernel behind it takes over on the device when the maps are not fp16 values
+        nws = 0 if _plain else int(_lib.droid_altcorr_forward_workspace_bytes(B, N, H1, W1, H2, W2, C, int(radius)))
+        ws = _workspace(fmap1.device, nws, "altcorr") if nws else None
+        _check(_lib.droid_altcorr_forward_ws(_p(fmap1), _p(fmap2), _p(coords), _p(out), _F32, B, N, H1,
+                                             W1, H2, W2, C, int(radius), _p(ws) if nws else None,
+                                             ctypes.c_size_t(ws.numel() if nws else 0), _stream(fmap1)),
                "altcorr_forward")
     return [out]
 
@@ -503,8 +511,8 @@ def depth_filter(poses, disps, intrinsics, ix, thresh):
 _ws_cache = {}
 
 
-def _workspace(device, nbytes):
-    key = (device.type, device.index)
+def _workspace(device, nbytes, tag="ba"):
+    key = (device.type, device.index, tag)
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty((int(nbytes * 1.25) + 1024,), dtype=torch.uint8, device=device)

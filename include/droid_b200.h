@@ -97,6 +97,18 @@ int droid_altcorr_forward(const void* fmap1, const void* fmap2, const float* coo
                           int dtype, int B, int N, int H1, int W1, int H2, int W2, int C,
                           int radius, void* stream);
 
+/* The same op with a caller-supplied workspace (droid_altcorr_forward_workspace_bytes; 0 = not needed for this shape),
+ * which unlocks the tensor-core kernel (csrc/altcorr_tc.cu: radius 3, C = 128, W2 <= 64): both maps are copied to fp16
+ * in the workspace with a round-trip check -- AltCorrBlock hands `.float()` copies of an fp16 pyramid
+ * (droid_slam/modules/corr.py:96-120), so the copy is exact -- and correlated with tcgen05.mma; when a value is not an
+ * fp16 number a device-side flag routes the call to the CUDA-core kernel instead, without a host round trip.  Same
+ * result contract as droid_altcorr_forward (<= 1e-5 of the largest value).  This is the entry point the Python
+ * host's altcorr_forward binds. */
+int droid_altcorr_forward_ws(const void* fmap1, const void* fmap2, const float* coords, void* out,
+                             int dtype, int B, int N, int H1, int W1, int H2, int W2, int C,
+                             int radius, void* workspace, size_t workspace_bytes, void* stream);
+size_t droid_altcorr_forward_workspace_bytes(int B, int N, int H1, int W1, int H2, int W2, int C, int radius);
+
 /* Replaces altcorr_backward (src/droid.cpp:205-217, src/altcorr_kernel.cu:152-286,321-356); f32 only
  * like the reference.  fmap1_grad/fmap2_grad fully written; coords_grad [B,N,H1,W1,2] is all zero
  * (the reference never writes it). */
@@ -108,6 +120,7 @@ int droid_altcorr_backward(const float* fmap1, const float* fmap2, const float* 
 /* Indexed alt-correlation: same result as altcorr_forward on
  * fmap1 = pyr0[ii], fmap2 = pyrL[jj] (modules/corr.py:106-125) without the gathered copies.
  *   pyr0 [F,H1,W1,C], pyrL [F,H2,W2,C] dtype; ii,jj [B] int64; output f32. */
+/* fp16 pyramids with C = 128 and W2 <= 64 take the tensor-core kernel (TMA straight from the pyramid, no copies). */
 int droid_altcorr_forward_indexed(const void* pyr0, const void* pyrL, const int64_t* ii,
                                   const int64_t* jj, const float* coords, float* out, int dtype,
                                   int F, int B, int N, int H1, int W1, int H2, int W2, int C,

@@ -150,6 +150,87 @@ def test_altcorr_indexed_equals_gathered(backends):
     assert rel(a.cpu().numpy(), want) <= 1e-5
 
 
+def _tc_case(n_edges, ht, wd, seed, scramble):
+    """fp16 pyramid of an AltCorrBlock (modules/corr.py:91-104: /4 and avg_pool2d in half, channel-last) + coordinates:
+    smooth flow with 3 % far outliers, and optionally pixels with arbitrary / extreme / non-finite coordinates."""
+    p = synth.make_corr_problem(n_edges, ht, wd, 128, seed=seed, oob_frac=0.03)
+    f = cu(p["fmaps"]) / 4.0
+    pyr = []
+    for _ in range(4):
+        pyr.append(f.permute(0, 2, 3, 1).contiguous())
+        f = torch.nn.functional.avg_pool2d(f, 2, stride=2)
+    coords = p["coords"].transpose(0, 2, 3, 1)[:, None].copy()          # [E, 1, H, W, 2]
+    if scramble:
+        rng = np.random.default_rng(seed)
+        m = rng.uniform(size=coords.shape[:4]) < 0.2
+        coords[m] = rng.uniform(-12, max(ht, wd) + 12, size=(int(m.sum()), 2)).astype(np.float32)
+        coords[0, 0, 0, 0] = (1e30, 3.0); coords[0, 0, 0, 1] = (-1e30, -1e30); coords[0, 0, 0, 2] = (2.5, 3.0e9)
+        coords[0, 0, 1, 0] = (-3.0, -3.0); coords[0, 0, 1, 1] = (wd + 2.999, ht + 2.999); coords[0, 0, 1, 2] = (wd + 3.0, 5.0)
+    return p, pyr, cu(np.ascontiguousarray(coords))
+
+
+@pytest.mark.parametrize("ht,wd,n_edges,scramble", [(40, 64, 6, False), (40, 64, 5, True), (48, 64, 3, True),
+                                                     (24, 40, 4, True), (18, 22, 4, True)])
+def test_altcorr_tensor_core_path(backends, ht, wd, n_edges, scramble):
+    """altcorr_tc.cu (tcgen05 GEMM + in-CTA window sampling) against the CUDA-core kernel and the oracle: every level of
+    the pyramid, through the indexed fp16 entry point (TMA straight from the pyramid) and through the drop-in fp32
+    signature (fp16 copies + exactness flag).  Sizes: EuRoC / TartanAir grids (256-pixel CTAs exactly), 24x40 (960 =
+    3.75 CTAs, rows of 40 / 20 / 10 / 5 pixels) and 18x22 (odd rows, level widths 22 / 11 / 5 / 2)."""
+    p, pyr, coords = _tc_case(n_edges, ht, wd, 7 + ht, scramble)
+    ii, jj = cu(p["ii"]), cu(p["jj"])
+    for l in range(4):
+        c = (coords / 2 ** l).contiguous()
+        f1, f2 = pyr[0][ii].float().contiguous(), pyr[l][jj].float().contiguous()
+        plain, = backends.altcorr_forward(f1, f2, c, 3, _plain=True)              # CUDA-core kernel
+        tc, = backends.altcorr_forward(f1, f2, c, 3)                              # fp32 signature -> fp16 copies -> tcgen05
+        ix = backends.altcorr_forward_indexed(pyr[0], pyr[l], ii, jj, c, 3)       # fp16 pyramid -> tcgen05
+        fin = torch.isfinite(plain)
+        assert torch.equal(fin, torch.isfinite(tc)) and torch.equal(fin, torch.isfinite(ix))
+        scale = float(plain[fin].abs().max())
+        assert float((tc[fin] - plain[fin]).abs().max()) <= 1e-5 * scale, l
+        assert torch.equal(tc[fin], ix[fin]), l
+        if l in (0, 3) and n_edges <= 5:
+            cn = c.cpu().numpy().copy()
+            want = O.altcorr_forward(f1.cpu().numpy(), f2.cpu().numpy(), np.clip(cn, -1e6, 1e6), 3)
+            ok = fin.cpu().numpy() & np.isfinite(want)
+            assert np.abs(tc.cpu().numpy()[ok] - want[ok]).max() <= 1e-5 * scale
+    # two samples per pixel (stereo: coords [B, 2, H, W, 2])
+    c2 = torch.cat([coords, coords + 0.37], 1).contiguous()
+    a, = backends.altcorr_forward(pyr[0][ii].float().contiguous(), pyr[0][jj].float().contiguous(), c2, 3)
+    b, = backends.altcorr_forward(pyr[0][ii].float().contiguous(), pyr[0][jj].float().contiguous(), c2, 3, _plain=True)
+    fin = torch.isfinite(b)
+    assert float((a[fin] - b[fin]).abs().max()) <= 1e-5 * float(b[fin].abs().max())
+
+
+def test_altcorr_real_fp32_features_fall_back_on_the_device(backends):
+    """Feature maps that are NOT fp16 values: the pre-pass raises the flag, the tensor-core kernel exits, the CUDA-core
+    kernel behind it produces the result -- bit-identical to the entry point without a workspace."""
+    p, pyr, coords = _tc_case(4, 40, 64, 3, True)
+    ii, jj = cu(p["ii"]), cu(p["jj"])
+    f1 = (pyr[0][ii].float() * 1.0001).contiguous()
+    f2 = pyr[0][jj].float().contiguous()
+    a, = backends.altcorr_forward(f1, f2, coords, 3)
+    b, = backends.altcorr_forward(f1, f2, coords, 3, _plain=True)
+    fin = torch.isfinite(b)
+    assert torch.equal(a[fin], b[fin]) and torch.equal(fin, torch.isfinite(a))
+    f2n = f2.clone(); f2n[1, 3, 5, 7] = float("nan")            # a NaN feature is "not an fp16 value" as well
+    a, = backends.altcorr_forward(pyr[0][ii].float().contiguous(), f2n, coords, 3)
+    b, = backends.altcorr_forward(pyr[0][ii].float().contiguous(), f2n, coords, 3, _plain=True)
+    assert torch.equal(torch.isnan(a), torch.isnan(b)) and torch.equal(a[~torch.isnan(b)], b[~torch.isnan(b)])
+
+
+def test_altcorr_tensor_core_vs_reference_extension(backends, ref_ext):
+    """The unmodified reference op on the same fp16-valued maps at the backend's size (40x64, 4 levels)."""
+    p, pyr, coords = _tc_case(8, 40, 64, 21, False)
+    ii, jj = cu(p["ii"]), cu(p["jj"])
+    for l in range(4):
+        c = (coords / 2 ** l).contiguous()
+        f1, f2 = pyr[0][ii].float().contiguous(), pyr[l][jj].float().contiguous()
+        a, = backends.altcorr_forward(f1, f2, c, 3)
+        b, = ref_ext.altcorr_forward(f1, f2, c, 3)
+        assert rel(a.cpu().numpy(), b.cpu().numpy()) <= 1e-5, l
+
+
 def test_altcorr_backward(backends):
     p = synth.make_corr_problem(2, 8, 16, 64, seed=7, oob_frac=0.05, dtype=np.float32)
     f = (p["fmaps"] / 4.0).astype(np.float32).transpose(0, 2, 3, 1)
