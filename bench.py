@@ -673,9 +673,14 @@ def altcorr_and_geometry_metrics(dev, hbm_peak, timeit):
                 "algorithmic_bytes": int(by), "flops": int(flops)}
     wl = "%d edges (8 source frames of a 250-keyframe backend graph), %dx%d, C=128, 4 levels, radius 3" % (Bn, H, W)
     t = timeit(lambda: [B.altcorr_forward(f1, f2[l], cl[l], r) for l in range(4)], n=10)
-    out["altcorr_forward"] = dict(rec(t, by32), workload=wl + "; drop-in signature, float32 gathered copies, 4 calls")
+    out["altcorr_forward"] = dict(rec(t, by32), workload=wl + "; drop-in signature, float32 gathered copies, 4 calls (fp16 copies + exactness flag, then the tensor-core kernel)")
     t = timeit(lambda: [B.altcorr_forward_indexed(pyr[0], pyr[l], ii, jj, cl[l], r) for l in range(4)], n=10)
     out["altcorr_forward_indexed"] = dict(rec(t, by16), workload=wl + "; float16 pyramid indexed by (ii, jj), no gathered copies, 4 calls")
+    t = timeit(lambda: B.altcorr_pyramid_indexed(pyr, ii, jj, coords, r), n=10)
+    out["altcorr_pyramid_indexed"] = dict(rec(t, by16), workload=wl + "; float16 pyramid, all 4 levels in ONE launch (tcgen05 GEMM of 128 "
+                                          "source pixels against the target rows their windows touch, sampled from TMEM)",
+                                          bound="latency per CTA (prologue -> TMA -> MMA -> TMEM read -> 196 stores per pixel); "
+                                                "HBM floor = the 321 MB of output")
     t = timeit(lambda: [B.altcorr_forward(pyr[0][ii].float(), pyr[l][jj].float(), cl[l], r) for l in range(4)], n=10)
     out["altcorr_forward_with_gathers"] = {"us": t * 1e6, "workload": wl + "; as AltCorrBlock.corr_fn calls it: pyramid[l][:, jj].float() gathers + the op"}
     if R is not None:
@@ -683,6 +688,7 @@ def altcorr_and_geometry_metrics(dev, hbm_peak, timeit):
         out["altcorr_forward_reference_ext"] = rec(t, by32)
         out["altcorr_forward"]["speedup_vs_reference_ext"] = out["altcorr_forward_reference_ext"]["us"] / out["altcorr_forward"]["us"]
         out["altcorr_forward_indexed"]["speedup_vs_reference_ext"] = out["altcorr_forward_reference_ext"]["us"] / out["altcorr_forward_indexed"]["us"]
+        out["altcorr_pyramid_indexed"]["speedup_vs_reference_ext"] = out["altcorr_forward_reference_ext"]["us"] / out["altcorr_pyramid_indexed"]["us"]
     del f1, f2, pyr, coords, cl
 
     # ---- frame_distance: every pair of a 1000-keyframe video, one direction (the caller averages two calls)

@@ -220,6 +220,10 @@ bool altcorr_tc_supported(int B, int N, int H1, int W1, int H2, int W2, int C, i
 int altcorr_tc_forward(const void* f1, const void* f2, const int64_t* ii, const int64_t* jj, const float* coords, float* out,
                        const int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int H2, int W2,
                        int C, int radius, cudaStream_t st);
+int altcorr_tc_forward_levels(const void* f1, const void* const* f2, const int* H2, const int* W2, const float* cscale,
+                              int nlev, const int64_t* ii, const int64_t* jj, const float* coords, float* out,
+                              const int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int C,
+                              int radius, cudaStream_t st);
 int altcorr_tc_convert(const float* f1, const float* f2, void* f1h, void* f2h, int* flag, size_t n1, size_t n2,
                        cudaStream_t st);
 
@@ -345,6 +349,32 @@ extern "C" int droid_altcorr_forward_indexed(const void* pyr0, const void* pyrL,
   }
   return fwd_common(pyr0, pyrL, ii, jj, coords, out, dtype, B, N, H1, W1, H2, W2, C, radius,
                     (cudaStream_t)stream);
+}
+
+extern "C" int droid_altcorr_pyramid_indexed(const void* const* pyr_host, int num_levels, const int64_t* ii,
+                                            const int64_t* jj, const float* coords, float* out, int dtype, int F,
+                                            int B, int N, int H1, int W1, int C, int radius, void* stream) {
+  if (F <= 0 || B < 0 || N < 0 || H1 <= 0 || W1 <= 0 || C <= 0 || radius != 3 || num_levels < 1 || num_levels > 4 ||
+      !pyr_host)
+    return DROID_ERR_INVALID_ARGUMENT;
+  if (B == 0 || N == 0) return DROID_OK;
+  if (!ii || !jj || !coords || !out) return DROID_ERR_INVALID_ARGUMENT;
+  int H2[4], W2[4];
+  float cs[4];
+  for (int l = 0; l < num_levels; l++) {
+    if (!pyr_host[l]) return DROID_ERR_INVALID_ARGUMENT;
+    H2[l] = H1 >> l;
+    W2[l] = W1 >> l;
+    cs[l] = 1.0f / (float)(1 << l);
+    if (H2[l] <= 0 || W2[l] <= 0) return DROID_ERR_INVALID_ARGUMENT;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == DROID_DTYPE_F16 && tc_enabled()) {
+    const int rc = altcorr_tc_forward_levels(pyr_host[0], pyr_host, H2, W2, cs, num_levels, ii, jj, coords, out, nullptr,
+                                             (size_t)F, (size_t)F, B, N, H1, W1, C, radius, st);
+    if (rc != DROID_ERR_NOT_IMPLEMENTED) return rc;
+  }
+  return DROID_ERR_NOT_IMPLEMENTED;   // the Python host then loops over droid_altcorr_forward_indexed
 }
 
 extern "C" int droid_altcorr_backward(const float* fmap1, const float* fmap2, const float* coords,

@@ -30,6 +30,8 @@
 #include <cuda.h>
 #include <cuda_fp16.h>
 
+#include <cstring>
+
 #include "common.cuh"
 
 namespace droid {
@@ -37,14 +39,14 @@ namespace atc {
 
 static constexpr int kC = 128;
 static constexpr int kTileM = 128;                   // source pixels per A tile = TMEM lanes
-static constexpr int kTiles = 2;                     // A tiles per CTA
+static constexpr int kTiles = 1;                     // A tiles per CTA
 static constexpr int kN = 64;                        // target pixels per chunk = accumulator columns
 static constexpr int kSlots = 4;                     // accumulators per tile
 static constexpr int kASlab = kTileM * 128;          // 64 channels (128 B) x 128 rows
 static constexpr int kATile = 2 * kASlab;            // 32 KB
 static constexpr int kBSlab = kN * 128;              // 8 KB
 static constexpr int kBStage = 2 * kBSlab;           // 16 KB
-static constexpr int kBStages = 5;
+static constexpr int kBStages = 2;
 static constexpr int kRowLd = 68;                    // floats per staging row (64 + pad: conflict-free 16-byte stores)
 static constexpr int kStageWarp = 32 * kRowLd * 4;   // 8704 B per sampler warp
 static constexpr int kSamplers = 4 * kTiles;         // sampler warps
@@ -54,6 +56,7 @@ static constexpr int kBOff = kTiles * kATile;                     // 64 KB
 static constexpr int kStOff = kBOff + kBStages * kBStage;         // +80 KB
 static constexpr int kBarOff = kStOff + kSamplers * kStageWarp;   // +68 KB
 static constexpr int kSmem = kBarOff + 512 + 1024;
+static constexpr int kTmemCols = kTiles * kSlots * kN;   // 256 / 512: a power of two
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -121,13 +124,50 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-// f1 rows: [frames1 * HW1][128] fp16, f2 rows: [frames2 * H2 * W2][128] fp16 (channel-last), through TMA.
-// grid = (ceil(HW1 / 256), N, B).  `skip_if` (may be null): a device flag; non-zero = leave everything to the
-// CUDA-core kernel launched behind this one.
-__global__ void __launch_bounds__(kThreads, 1)
-altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, const float* __restrict__ coords,
-                  float* __restrict__ out, const int* __restrict__ skip_if, int N, int HW1, int H2, int W2, int Rh) {
+static constexpr int kMaxLevels = 4;
+
+// Everything the kernel needs about the target side: one tensor map and one geometry per pyramid level.
+struct Params {
+  CUtensorMap a;                    // f1 rows: [frames1 * HW1][128] fp16
+  CUtensorMap b[kMaxLevels];        // f2 rows of level l: [frames2 * H2 * W2][128] fp16 (channel-last)
+  int H2[kMaxLevels], W2[kMaxLevels];
+  int Rh[kMaxLevels];               // whole image rows per chunk = 64 / W2
+  float cscale[kMaxLevels];         // coordinates of level l = coords * cscale (2^-l: exact, = coords / 2^l of corr.py:116)
+  int nlev;
+};
+
+// The lookup window of one pixel at one level: integer origin, the valid taps of a window row, the chunks it touches.
+struct Window {
+  int xs, ys, c_lo, c_hi;           // c_lo > c_hi: no tap inside the image
+  unsigned colmask;
+  float dx, dy;
+};
+__device__ __forceinline__ Window make_window(float x, float y, int H2, int W2, int Rh, bool live) {
+  Window w;
+  const float fx0 = floorf(x), fy0 = floorf(y);
+  w.dx = x - fx0;
+  w.dy = y - fy0;
+  w.xs = window_origin(fx0, 3);
+  w.ys = window_origin(fy0, 3);
+  w.colmask = 0;
+#pragma unroll
+  for (int ix = 0; ix < 8; ix++) w.colmask |= ((unsigned)(w.xs + ix) < (unsigned)W2) ? (1u << ix) : 0u;
+  const int r_lo = max(w.ys, 0), r_hi = min(w.ys + 7, H2 - 1);
+  w.c_lo = 1;
+  w.c_hi = 0;
+  if (live && w.colmask && r_lo <= r_hi) {
+    w.c_lo = r_lo / Rh;
+    w.c_hi = r_hi / Rh;
+  }
+  return w;
+}
+
+// grid = (ceil(HW1 / 256), N, B).  out [B, N, nlev * 49, HW1].  `skip_if` (may be null): a device flag; non-zero =
+// leave everything to the CUDA-core kernel launched behind this one.
+__global__ void __launch_bounds__(kThreads, kTiles == 1 ? 2 : 1)
+altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ ii, const int64_t* __restrict__ jj,
+                  const float* __restrict__ coords, float* __restrict__ out, const int* __restrict__ skip_if, int N,
+                  int HW1) {
   if (skip_if && *skip_if) return;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -138,14 +178,19 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* acc_full = b_empty + kBStages;               // [kTiles * kSlots]
   uint64_t* acc_empty = acc_full + kTiles * kSlots;      // [kTiles * kSlots]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + kTiles * kSlots);
-  int* crange = reinterpret_cast<int*>(tmem_slot + 2);   // [2]: first / last chunk any pixel of the CTA needs
+  int* crange = reinterpret_cast<int*>(tmem_slot + 2);   // [2 * nlev]: first / last chunk of a level any pixel of the CTA needs
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.z, n = blockIdx.y;
   const int pix0 = blockIdx.x * (kTiles * kTileM);
-  const int nchunks = (H2 + Rh - 1) / Rh;
+  const int nlev = P.nlev;
 
-  if (threadIdx.x == 0) {
+  // The producer thread sets up the barriers and starts the A tiles at once: they do not depend on the chunk ranges
+  // computed below, and their latency (frame index -> TMA -> HBM) otherwise sits on every CTA's critical path.
+  int fr2 = 0;
+  if (threadIdx.x == kSamplers * 32) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&P.a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&P.b[0]) : "memory");
     mbar_init(a_full, 1);
     for (int i = 0; i < kBStages; i++) {
       mbar_init(b_full + i, 1);
@@ -155,84 +200,81 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_init(acc_full + i, 1);
       mbar_init(acc_empty + i, 4);                       // one arrival per sampler warp of the tile
     }
-    crange[0] = nchunks;
-    crange[1] = -1;
+    for (int l = 0; l < kMaxLevels; l++) {
+      crange[2 * l] = 1 << 30;
+      crange[2 * l + 1] = -1;
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    const int fr1 = ii ? (int)ii[b] : b;
+    fr2 = jj ? (int)jj[b] : b;
+    mbar_expect_tx(a_full, kTiles * kATile);
+    for (int t = 0; t < kTiles; t++)
+      for (int ks = 0; ks < 2; ks++)
+        tma_load_2d(smem + kAOff + t * kATile + ks * kASlab, &P.a, a_full, ks * 64, fr1 * HW1 + pix0 + t * kTileM);
   }
   if (warp == kSamplers) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   __syncthreads();
 
-  // ---- every sampler thread: its pixel, its window, the chunks it needs ----
+  // ---- every sampler thread: its pixel and, per level, the chunks its window touches ----
   const int tile = warp >> 2, q = warp & 3;
   const int pix = pix0 + tile * kTileM + q * 32 + lane;
   bool live = false;
-  int xs = 0, ys = 0, c_lo = 1, c_hi = 0;
-  unsigned colmask = 0;
-  float dx = 0.f, dy = 0.f;
+  float x0 = 0.f, y0 = 0.f;
   if (warp < kSamplers) {
     live = pix < HW1;
     if (live) {
       const float2 xy = __ldg(reinterpret_cast<const float2*>(coords + (((size_t)b * N + n) * HW1 + pix) * 2));
-      const float fx0 = floorf(xy.x), fy0 = floorf(xy.y);
-      dx = xy.x - fx0;
-      dy = xy.y - fy0;
-      // same integer window origin as the CUDA-core kernel; far-away (or non-finite) coordinates are pinned to a
-      // window that lies outside every image instead of overflowing
-      xs = window_origin(fx0, 3);
-      ys = window_origin(fy0, 3);
+      x0 = xy.x;
+      y0 = xy.y;
+    }
+    for (int l = 0; l < nlev; l++) {
+      const Window w = make_window(x0 * P.cscale[l], y0 * P.cscale[l], P.H2[l], P.W2[l], P.Rh[l], live);
+      int lo = w.c_lo <= w.c_hi ? w.c_lo : (1 << 30), hi = w.c_lo <= w.c_hi ? w.c_hi : -1;
 #pragma unroll
-      for (int ix = 0; ix < 8; ix++) colmask |= ((unsigned)(xs + ix) < (unsigned)W2) ? (1u << ix) : 0u;
-      const int r_lo = max(ys, 0), r_hi = min(ys + 7, H2 - 1);
-      if (colmask && r_lo <= r_hi) {
-        c_lo = r_lo / Rh;
-        c_hi = r_hi / Rh;
+      for (int o = 16; o; o >>= 1) {
+        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
       }
-    }
-    int lo = c_lo <= c_hi ? c_lo : nchunks, hi = c_lo <= c_hi ? c_hi : -1;
-#pragma unroll
-    for (int o = 16; o; o >>= 1) {
-      lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-      hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-    }
-    if (lane == 0 && hi >= 0) {
-      atomicMin(crange, lo);
-      atomicMax(crange + 1, hi);
+      if (lane == 0 && hi >= 0) {
+        atomicMin(crange + 2 * l, lo);
+        atomicMax(crange + 2 * l + 1, hi);
+      }
     }
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const int cmin = crange[0], cmax = crange[1];          // cmax < cmin: nothing to correlate (all windows outside)
-  const int ncta = cmax - cmin + 1;
+  int total = 0;                                          // chunks of all levels; cmax < cmin: nothing to correlate
+  for (int l = 0; l < nlev; l++) total += max(crange[2 * l + 1] - crange[2 * l] + 1, 0);
 
   if (warp == kSamplers) {
     // ---------------- TMA producer ----------------
-    if (lane == 0 && ncta > 0) {
-      const int fr1 = ii ? (int)ii[b] : b, fr2 = jj ? (int)jj[b] : b;
-      mbar_expect_tx(a_full, kTiles * kATile);
-      for (int t = 0; t < kTiles; t++)
-        for (int ks = 0; ks < 2; ks++)
-          tma_load_2d(smem + kAOff + t * kATile + ks * kASlab, &tmA, a_full, ks * 64, fr1 * HW1 + pix0 + t * kTileM);
-      const int row0 = fr2 * H2 * W2;
-      for (int it = 0; it < ncta; it++) {
-        const int s = it % kBStages;
-        if (it >= kBStages) mbar_wait(b_empty + s, ((it / kBStages) - 1) & 1);
-        mbar_expect_tx(b_full + s, kBStage);
-        for (int ks = 0; ks < 2; ks++)
-          tma_load_2d(smem + kBOff + s * kBStage + ks * kBSlab, &tmB, b_full + s, ks * 64, row0 + (cmin + it) * Rh * W2);
+    if (lane == 0 && total == 0) mbar_wait(a_full, 0);   // nothing to correlate: the A tiles must still have landed
+    if (lane == 0 && total > 0) {
+      int it = 0;
+      for (int l = 0; l < nlev; l++) {
+        const int row0 = fr2 * P.H2[l] * P.W2[l], step = P.Rh[l] * P.W2[l];
+        for (int c = crange[2 * l]; c <= crange[2 * l + 1]; c++, it++) {
+          const int s = it % kBStages;
+          if (it >= kBStages) mbar_wait(b_empty + s, ((it / kBStages) - 1) & 1);
+          mbar_expect_tx(b_full + s, kBStage);
+          for (int ks = 0; ks < 2; ks++)
+            tma_load_2d(smem + kBOff + s * kBStage + ks * kBSlab, &P.b[l], b_full + s, ks * 64, row0 + c * step);
+        }
       }
     }
     __syncwarp();
   } else if (warp == kSamplers + 1) {
     // ---------------- MMA issuer ----------------
-    if (lane == 0 && ncta > 0) {
+    if (lane == 0 && total > 0) {
       const uint32_t idesc = umma_idesc();
       mbar_wait(a_full, 0);
-      for (int it = 0; it < ncta; it++) {
+      for (int it = 0; it < total; it++) {
         const int s = it % kBStages, slot = it & (kSlots - 1);
         mbar_wait(b_full + s, (it / kBStages) & 1);
         const uint32_t bs = smem_u32(smem + kBOff + s * kBStage);
@@ -254,58 +296,64 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     __syncwarp();
   } else {
     // ---------------- samplers ----------------
-    float taps[64];
-#pragma unroll
-    for (int i = 0; i < 64; i++) taps[i] = 0.f;
     float* mine = reinterpret_cast<float*>(smem + kStOff + warp * kStageWarp) + lane * kRowLd;
-    for (int it = 0; it < ncta; it++) {
-      const int c = cmin + it, slot = it & (kSlots - 1);
-      const int h0 = c * Rh;
-      const bool need = c >= c_lo && c <= c_hi;
-      mbar_wait(acc_full + tile * kSlots + slot, (it / kSlots) & 1);
-      tc_fence_after();
-      const bool any = __any_sync(0xffffffffu, need);
-      if (any) {
-        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (tile * kSlots + slot) * kN;
+    int it = 0;
+    for (int l = 0; l < nlev; l++) {
+      const int H2 = P.H2[l], W2 = P.W2[l], Rh = P.Rh[l];
+      const Window w = make_window(x0 * P.cscale[l], y0 * P.cscale[l], H2, W2, Rh, live);
+      float taps[64];
 #pragma unroll
-        for (int h = 0; h < 2; h++) {
-          uint32_t r[32];
-          tmem_ld32(taddr + h * 32, r);
+      for (int i = 0; i < 64; i++) taps[i] = 0.f;
+      for (int c = crange[2 * l]; c <= crange[2 * l + 1]; c++, it++) {
+        const int slot = it & (kSlots - 1);
+        const int h0 = c * Rh;
+        const bool need = c >= w.c_lo && c <= w.c_hi;
+        mbar_wait(acc_full + tile * kSlots + slot, (it / kSlots) & 1);
+        tc_fence_after();
+        if (__any_sync(0xffffffffu, need)) {
+          const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (tile * kSlots + slot) * kN;
+          uint32_t r[64];
+          tmem_ld32(taddr, r);                       // both halves in flight, one wait
+          tmem_ld32(taddr + 32, r + 32);
           tmem_ld_wait();
-          uint4* dst = reinterpret_cast<uint4*>(mine + h * 32);
+          uint4* dst = reinterpret_cast<uint4*>(mine);
 #pragma unroll
-          for (int j = 0; j < 8; j++) dst[j] = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+          for (int j = 0; j < 16; j++) dst[j] = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
         }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(acc_empty + tile * kSlots + slot);
-      if (need) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_empty + tile * kSlots + slot);
+        if (need) {
+          // window rows iy with first <= iy < first + cnt lie in this chunk (and inside the image)
+          const int first = max(max(h0, 0) - w.ys, 0);
+          const int cnt = max(min(min(h0 + Rh, H2) - w.ys, 8) - first, 0);
+          const float* row0 = mine + (w.ys - h0) * W2 + w.xs;
 #pragma unroll
-        for (int iy = 0; iy < 8; iy++) {
-          const int h2 = ys + iy;
-          if (h2 >= h0 && h2 < h0 + Rh && h2 < H2 && h2 >= 0) {
-            const float* row = mine + (h2 - h0) * W2 + xs;
+          for (int iy = 0; iy < 8; iy++) {
+            if ((unsigned)(iy - first) < (unsigned)cnt) {
+              const float* row = row0 + iy * W2;
 #pragma unroll
-            for (int ix = 0; ix < 8; ix++)
-              if (colmask & (1u << ix)) taps[iy * 8 + ix] = row[ix];
+              for (int ix = 0; ix < 8; ix++)
+                if (w.colmask & (1u << ix)) taps[iy * 8 + ix] = row[ix];
+            }
           }
         }
       }
-    }
-    if (live) {
-      const float wse = (1 - dy) * (1 - dx), wsw = (1 - dy) * dx, wne = dy * (1 - dx), wnw = dy * dx;
-      float* ob = out + ((size_t)b * N + n) * 49 * HW1 + pix;
+      if (live) {
+        const float dx = w.dx, dy = w.dy;
+        const float wse = (1 - dy) * (1 - dx), wsw = (1 - dy) * dx, wne = dy * (1 - dx), wnw = dy * dx;
+        float* ob = out + (((size_t)b * N + n) * nlev + l) * 49 * HW1 + pix;
 #pragma unroll
-      for (int ixo = 0; ixo < 7; ixo++) {
+        for (int ixo = 0; ixo < 7; ixo++) {
 #pragma unroll
-        for (int iyo = 0; iyo < 7; iyo++) {      // channel = iy + 7 * ix (src/altcorr_kernel.cu:102-105)
-          const int t = iyo * 8 + ixo;
-          float acc = taps[t] * wse;
-          acc = fmaf(taps[t + 1], wsw, acc);
-          acc = fmaf(taps[t + 8], wne, acc);
-          acc = fmaf(taps[t + 9], wnw, acc);
-          __stcs(ob + (size_t)(iyo + 7 * ixo) * HW1, acc);
+          for (int iyo = 0; iyo < 7; iyo++) {      // channel = iy + 7 * ix (src/altcorr_kernel.cu:102-105)
+            const int t = iyo * 8 + ixo;
+            float acc = taps[t] * wse;
+            acc = fmaf(taps[t + 1], wsw, acc);
+            acc = fmaf(taps[t + 8], wne, acc);
+            acc = fmaf(taps[t + 9], wnw, acc);
+            __stcs(ob + (size_t)(iyo + 7 * ixo) * HW1, acc);
+          }
         }
       }
     }
@@ -313,7 +361,7 @@ altcorr_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   tc_fence_before();
   __syncthreads();
   if (warp == kSamplers) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
   }
 }
 
@@ -373,26 +421,44 @@ bool altcorr_tc_supported(int B, int N, int H1, int W1, int H2, int W2, int C, i
   return r1 < (1u << 31) && r2 < (1u << 31);
 }
 
-// Enqueue the tensor-core forward.  f1 / f2: fp16 channel-last maps of `frames1` / `frames2` frames; ii / jj may be
-// null (frame = b).  Returns DROID_ERR_NOT_IMPLEMENTED if the shape is not covered (nothing enqueued then).
-int altcorr_tc_forward(const void* f1, const void* f2, const int64_t* ii, const int64_t* jj, const float* coords, float* out,
-                       const int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int H2, int W2,
-                       int C, int radius, cudaStream_t st) {
-  if (!altcorr_tc_supported(B, N, H1, W1, H2, W2, C, radius, frames1, frames2)) return DROID_ERR_NOT_IMPLEMENTED;
-  if (((uintptr_t)f1 & 15) || ((uintptr_t)f2 & 15) || ((uintptr_t)coords & 7)) return DROID_ERR_NOT_IMPLEMENTED;
+// Enqueue the tensor-core forward over `nlev` pyramid levels in ONE launch.  f1: fp16 channel-last maps of `frames1`
+// frames; f2[l]: level l of `frames2` frames, H2[l] x W2[l]; coordinates are multiplied by cscale[l] for level l;
+// ii / jj may be null (frame = b); out [B, N, nlev * 49, H1, W1].  Returns DROID_ERR_NOT_IMPLEMENTED if a shape is not
+// covered (nothing enqueued then).
+int altcorr_tc_forward_levels(const void* f1, const void* const* f2, const int* H2, const int* W2, const float* cscale,
+                              int nlev, const int64_t* ii, const int64_t* jj, const float* coords, float* out,
+                              const int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int C,
+                              int radius, cudaStream_t st) {
+  if (nlev < 1 || nlev > atc::kMaxLevels) return DROID_ERR_NOT_IMPLEMENTED;
+  if (((uintptr_t)f1 & 15) || ((uintptr_t)coords & 7)) return DROID_ERR_NOT_IMPLEMENTED;
   const int HW1 = H1 * W1;
-  CUtensorMap ta, tb;
-  if (!atc::make_map(&ta, f1, frames1 * (size_t)HW1, atc::kTileM) ||
-      !atc::make_map(&tb, f2, frames2 * (size_t)H2 * W2, atc::kN))
-    return DROID_ERR_NOT_IMPLEMENTED;
+  atc::Params P;
+  memset(&P, 0, sizeof(P));
+  P.nlev = nlev;
+  if (!atc::make_map(&P.a, f1, frames1 * (size_t)HW1, atc::kTileM)) return DROID_ERR_NOT_IMPLEMENTED;
+  for (int l = 0; l < nlev; l++) {
+    if (!altcorr_tc_supported(B, N, H1, W1, H2[l], W2[l], C, radius, frames1, frames2)) return DROID_ERR_NOT_IMPLEMENTED;
+    if (((uintptr_t)f2[l] & 15) || !atc::make_map(&P.b[l], f2[l], frames2 * (size_t)H2[l] * W2[l], atc::kN))
+      return DROID_ERR_NOT_IMPLEMENTED;
+    P.H2[l] = H2[l];
+    P.W2[l] = W2[l];
+    P.Rh[l] = atc::kN / W2[l];
+    P.cscale[l] = cscale[l];
+  }
   DevCtx& dc = dev_ctx();
   if (dc.first(kOnceAltcorrTc))
     cudaFuncSetAttribute(atc::altcorr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::kSmem);
-  const int Rh = atc::kN / W2;                         // whole image rows per chunk
   dim3 grid((HW1 + atc::kTiles * atc::kTileM - 1) / (atc::kTiles * atc::kTileM), N, B);
-  DROID_LAUNCH atc::altcorr_tc_kernel<<<grid, atc::kThreads, atc::kSmem, st>>>(ta, tb, ii, jj, coords, out, skip_if, N, HW1,
-                                                                             H2, W2, Rh);
+  DROID_LAUNCH atc::altcorr_tc_kernel<<<grid, atc::kThreads, atc::kSmem, st>>>(P, ii, jj, coords, out, skip_if, N, HW1);
   return check_launch();
+}
+
+int altcorr_tc_forward(const void* f1, const void* f2, const int64_t* ii, const int64_t* jj, const float* coords, float* out,
+                       const int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int H2, int W2,
+                       int C, int radius, cudaStream_t st) {
+  const float one = 1.f;
+  return altcorr_tc_forward_levels(f1, &f2, &H2, &W2, &one, 1, ii, jj, coords, out, skip_if, frames1, frames2, B, N, H1, W1,
+                                   C, radius, st);
 }
 
 // fp32 -> fp16 copies of both maps into `f1h` / `f2h`, *flag = 1 if any value is not exactly a half.

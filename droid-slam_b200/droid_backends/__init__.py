@@ -82,7 +82,7 @@ __version__ = _lib.droid_version().decode()
 C_ABI_SYMBOLS = [
     "droid_version", "droid_last_cuda_error", "droid_launch_count", "droid_prof_enable", "droid_prof_read", "droid_corr_index_forward", "droid_corr_index_backward",
     "droid_corr_index_pyramid", "droid_altcorr_forward", "droid_altcorr_forward_ws",
-    "droid_altcorr_forward_workspace_bytes", "droid_altcorr_backward",
+    "droid_altcorr_forward_workspace_bytes", "droid_altcorr_backward", "droid_altcorr_pyramid_indexed",
     "droid_altcorr_forward_indexed", "droid_corr_build", "droid_corr_build_workspace_bytes",
     "droid_frame_distance", "droid_frame_distance_workspace_bytes", "droid_frame_distance_ws",
     "droid_frame_distance_noalloc_max_pixels", "droid_frame_distance_noalloc", "droid_projmap", "droid_reproject", "droid_iproj", "droid_depth_filter",
@@ -270,6 +270,36 @@ def altcorr_forward_indexed(pyr0, pyrl, ii, jj, coords, radius=3):
                                                   C, int(radius), _stream(pyr0)),
                "altcorr_forward_indexed")
     return out
+
+
+def altcorr_pyramid_indexed(pyramid, ii, jj, coords, radius=3):
+    """Extension: every level of an AltCorrBlock in ONE launch == torch.cat([altcorr_forward(pyramid[0][ii].float(),
+    pyramid[l][jj].float(), coords / 2**l, r) for l], dim=2) (modules/corr.py:106-125).  pyramid[l]: [F, H>>l, W>>l, C]
+    float16, channel-last; coords [B, S, H, W, 2] at level 0; returns [B, S, L*(2r+1)^2, H, W] float32.  Shapes the
+    tensor-core kernel does not cover fall back to one altcorr_forward_indexed call per level."""
+    L = len(pyramid)
+    _contig("altcorr_pyramid_indexed", ii=ii, jj=jj, coords=coords, **{"level%d" % i: v for i, v in enumerate(pyramid)})
+    _long("altcorr_pyramid_indexed", ii=ii, jj=jj)
+    p0 = pyramid[0]
+    _dtype("altcorr_pyramid_indexed", p0, (torch.float32, torch.float16))
+    F, H1, W1, C = p0.shape
+    B, N, H, W, _ = coords.shape
+    for l, v in enumerate(pyramid):
+        if v.dtype != p0.dtype or tuple(v.shape) != (F, H1 >> l, W1 >> l, C):
+            raise RuntimeError("droid_backends.altcorr_pyramid_indexed: bad level %d" % l)
+    rd = 2 * radius + 1
+    with torch.cuda.device(p0.device):
+        if p0.dtype == torch.float16 and 1 <= L <= 4:
+            out = torch.empty((B, N, L * rd * rd, H, W), dtype=torch.float32, device=p0.device)
+            ptrs = (ctypes.c_void_p * L)(*[v.data_ptr() for v in pyramid])
+            rc = _lib.droid_altcorr_pyramid_indexed(ptrs, L, _p(ii), _p(jj), _p(coords), _p(out), _DT[p0.dtype], F, B,
+                                                    N, H1, W1, C, int(radius), _stream(p0))
+            if rc == 0:
+                return out
+            if rc != -5:                                   # DROID_ERR_NOT_IMPLEMENTED: shape not covered
+                _check(rc, "altcorr_pyramid_indexed")
+        return torch.cat([altcorr_forward_indexed(p0, pyramid[l], ii, jj, (coords / 2 ** l).contiguous(), radius)
+                          for l in range(L)], dim=2)
 
 
 def corr_build(fmap1, fmap2, num_levels=4):

@@ -126,6 +126,15 @@ int droid_altcorr_forward_indexed(const void* pyr0, const void* pyrL, const int6
                                   int F, int B, int N, int H1, int W1, int H2, int W2, int C,
                                   int radius, void* stream);
 
+/* Every level of an AltCorrBlock in one launch (extension; droid_slam/modules/corr.py:106-125 is four calls + cat):
+ *   pyr_host[l]: device pointer of level l, [F, H1>>l, W1>>l, C] channel-last; coords [B,N,H1,W1,2] at LEVEL 0 (divided
+ *   by 2^l inside, exactly as corr.py:116); out [B, N, num_levels*49, H1, W1] f32, level l at channels 49 l .. 49 l + 48.
+ * Tensor-core kernel only (f16, C = 128, radius 3, W1 <= 64, num_levels <= 4): DROID_ERR_NOT_IMPLEMENTED otherwise --
+ * the caller then uses droid_altcorr_forward_indexed per level (the Python host does). */
+int droid_altcorr_pyramid_indexed(const void* const* pyr_host, int num_levels, const int64_t* ii,
+                                  const int64_t* jj, const float* coords, float* out, int dtype, int F, int B,
+                                  int N, int H1, int W1, int C, int radius, void* stream);
+
 /* ---- all-pairs correlation volume + pyramid (tcgen05/TMEM GEMM) -------------------------------
  * Replaces CorrBlock.corr + 3x avg_pool2d (droid_slam/modules/corr.py:24-38,63-71).
  *   fmap1,fmap2 [B,C,HW] f16 (C=128), UNSCALED (the /4 on each side is applied inside, in f16,

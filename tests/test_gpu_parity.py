@@ -194,6 +194,11 @@ def test_altcorr_tensor_core_path(backends, ht, wd, n_edges, scramble):
             want = O.altcorr_forward(f1.cpu().numpy(), f2.cpu().numpy(), np.clip(cn, -1e6, 1e6), 3)
             ok = fin.cpu().numpy() & np.isfinite(want)
             assert np.abs(tc.cpu().numpy()[ok] - want[ok]).max() <= 1e-5 * scale
+    # all levels in one launch == the per-level calls, bit for bit (same kernel, same chunk order per level)
+    fused = backends.altcorr_pyramid_indexed(pyr, ii, jj, coords, 3)
+    each = torch.cat([backends.altcorr_forward_indexed(pyr[0], pyr[l], ii, jj, (coords / 2 ** l).contiguous(), 3) for l in range(4)], 2)
+    fin = torch.isfinite(each)
+    assert fused.shape == each.shape and torch.equal(fin, torch.isfinite(fused)) and torch.equal(fused[fin], each[fin])
     # two samples per pixel (stereo: coords [B, 2, H, W, 2])
     c2 = torch.cat([coords, coords + 0.37], 1).contiguous()
     a, = backends.altcorr_forward(pyr[0][ii].float().contiguous(), pyr[0][jj].float().contiguous(), c2, 3)
