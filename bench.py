@@ -606,6 +606,7 @@ def extra_metrics(dev, hbm_peak, peaks):
         out.update(altcorr_and_geometry_metrics(dev, hbm_peak, timeit))
     except Exception as ex:                                        # noqa: BLE001
         out["altcorr_geometry_error"] = repr(ex)
+    out["frontend_driver"] = frontend_driver_metric()
     p = synth.make_ba_problem("C3")
     d = {k: torch.from_numpy(np.ascontiguousarray(p[k])).to(dev) for k in KEYS}
     p0, d0 = d["poses"].clone(), d["disps"].clone()
@@ -627,6 +628,32 @@ def extra_metrics(dev, hbm_peak, peaks):
     except Exception:
         pass
     return out
+
+
+def frontend_driver_metric(frames=48):
+    """BASELINE's "frontend fps", through the reference's OWN DroidFrontend (unmodified droid_slam/*.py staged under
+    oracle/_ref/pyref) on a synthetic stream of `frames` keyframes with a random-init DroidNet: the same Python with
+    `droid_backends` bound to the reference extension and to this repo's module.  Runs tools/run_reference_drivers.py in a
+    child process (a measurement tool: the only place besides cpu_baseline where bench.py touches oracle/); DESIGN.md 5.1
+    holds the 100-keyframe run and the 1000-keyframe backend run of the same tool."""
+    import subprocess
+    tool = os.path.join(ROOT, "tools", "run_reference_drivers.py")
+    try:
+        r = subprocess.run([sys.executable, tool, "frontend", "--frames", str(frames), "--arms", "reference,drop-in"],
+                           capture_output=True, text=True, timeout=420)
+        if r.returncode != 0:
+            return {"unavailable": (r.stderr or r.stdout).strip().splitlines()[-1][:300] if (r.stderr or r.stdout) else "rc %d" % r.returncode}
+        res = json.loads(r.stdout[r.stdout.index("{"):])
+        out = {"workload": "DroidFrontend.__call__ per keyframe (edge selection + 6 FactorGraph.update: corr lookup, update operator, "
+                           "ba on the window), %d keyframes 40x64 at 1/8, random-init DroidNet in PyTorch" % frames}
+        for arm, a in res["arms"].items():
+            out[arm] = {"keyframes_per_s": a["keyframes_per_s"], "droid_backends_ms": a["droid_backends_ms"],
+                        "ba_ms": a["droid_backends_calls"].get("ba", {}).get("ms"), "finite": a["finite"]}
+            if "vs_reference" in a:
+                out[arm]["vs_reference"] = a["vs_reference"]
+        return out
+    except Exception as ex:                                        # noqa: BLE001
+        return {"unavailable": repr(ex)[:300]}
 
 
 def altcorr_and_geometry_metrics(dev, hbm_peak, timeit):

@@ -339,12 +339,12 @@ def frame_distance(poses, disps, intrinsics, ii, jj, beta, _plain=False):
     ht, wd = disps.shape[1], disps.shape[2]
     with torch.cuda.device(poses.device):
         dist = torch.empty((n,), dtype=torch.float32, device=poses.device)
-        if _plain:
+        if _plain or n <= 256:      # few pairs (the frontend's keyframe test): one launch, no per-call table, same bits
             _check(_lib.droid_frame_distance(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj), _p(dist), n, ht, wd,
                                              ctypes.c_float(beta), _stream(poses)), "frame_distance")
             return dist
         nws = int(_lib.droid_frame_distance_workspace_bytes(ht, wd))
-        ws = torch.empty((nws,), dtype=torch.uint8, device=poses.device)
+        ws = _workspace(poses.device, nws, "frame_distance")
         _check(_lib.droid_frame_distance_ws(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj), _p(dist), n, ht, wd,
                                             ctypes.c_float(beta), ctypes.c_void_p(ws.data_ptr()), ctypes.c_size_t(nws),
                                             _stream(poses)), "frame_distance")

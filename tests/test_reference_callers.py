@@ -76,6 +76,16 @@ def test_alt_corr_block_through_reference_python(backends, ref_ext, ref_py):
     assert a.shape == (1, 10, 4 * 49, 40, 64)
     assert rel(a, b) <= 1e-5
 
+    # the one-launch binding INTEGRATION.md proposes for corr_fn: the reference's own pyramid, every level at once
+    import pyref
+    pyref.use(ref_py, ref_ext)
+    blk = ref_py.corr.AltCorrBlock(fmaps)
+    want = blk(coords, ii, jj)                                                # unmodified reference, reference extension
+    pyref.use(ref_py, backends)
+    got = backends.altcorr_pyramid_indexed([p[0] for p in blk.pyramid], ii, jj, coords[0][:, None].contiguous(), 3)
+    assert got.shape == (10, 1, 4 * 49, 40, 64)
+    assert rel(got[:, 0], want[0]) <= 1e-5
+
     f1 = (fmaps[0, ii].float() / 4).permute(0, 2, 3, 1).contiguous().requires_grad_(True)
     f2 = (fmaps[0, jj].float() / 4).permute(0, 2, 3, 1).contiguous().requires_grad_(True)
     c5 = coords[0][:, None].contiguous()
