@@ -616,7 +616,7 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, 
 def ba_status(device=None):
     """Device-side status word of the last ba() on this device (forces a D2H copy; debug aid)."""
     device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
-    ws = _ws_cache.get((device.type, device.index))
+    ws = _ws_cache.get((device.type, device.index, "ba"))
     if ws is None:
         return 0
     off = (-ws.data_ptr()) % 256
@@ -628,7 +628,7 @@ def ba_tree(device=None):
     (range_end, level_first) as droid_chol_solve_tree_f64 takes them, ([], []) for a single chain.  Forces a D2H copy;
     debug / test aid."""
     device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
-    ws = _ws_cache.get((device.type, device.index))
+    ws = _ws_cache.get((device.type, device.index, "ba"))
     if ws is None:
         return [], []
     off = (-ws.data_ptr()) % 256
