@@ -73,15 +73,15 @@ class Timed:
         return out
 
 
-def fill_video(ns, p, n, buffer, seed=0):
+def fill_video(ns, p, n, buffer, seed=0, stereo=False):
     ht, wd = p["ht"], p["wd"]
-    v = ns.depth_video.DepthVideo(image_size=[8 * ht, 8 * wd], buffer=buffer)
+    v = ns.depth_video.DepthVideo(image_size=[8 * ht, 8 * wd], buffer=buffer, stereo=stereo)
     v.poses[:n] = torch.from_numpy(p["poses"][:n]).to(DEV)
     v.disps[:n] = torch.from_numpy(p["disps"][:n]).to(DEV)
     v.intrinsics[:] = torch.from_numpy(p["intrinsics"]).to(DEV)
     v.tstamp[:n] = torch.arange(n, device=DEV, dtype=torch.float)
     g = torch.Generator(device=DEV).manual_seed(seed)
-    v.fmaps[:n] = torch.randn((n, 1, 128, ht, wd), generator=g, device=DEV).half()
+    v.fmaps[:n] = torch.randn((n, 2 if stereo else 1, 128, ht, wd), generator=g, device=DEV).half()
     v.nets[:n] = torch.tanh(torch.randn((n, 128, ht, wd), generator=g, device=DEV)).half()
     v.inps[:n] = torch.relu(torch.randn((n, 128, ht, wd), generator=g, device=DEV)).half()
     v.counter.value = n
@@ -144,10 +144,11 @@ def run_arm(kind, arm, ns, net, p, args, ref_mod):
             return r
         if kind == "backend":
             n = args.frames
-            v = fill_video(ns, p, n, n + 8)
+            v = fill_video(ns, p, n, n + 8, stereo=args.stereo)
             a = types.SimpleNamespace(beta=0.3, backend_thresh=22.0, backend_radius=2, backend_nms=3)
             with torch.no_grad():                          # the body of DroidBackend.__call__ (droid_backend.py:24-40), phase by phase
-                timed("normalize", v.normalize)
+                if not v.stereo:                            # droid_backend.py:28-29
+                    timed("normalize", v.normalize)
                 g = timed("graph", lambda: ns.factor_graph.FactorGraph(v, net.update, corr_impl="alt", max_factors=16 * n))
                 timed("add_proximity_factors", lambda: g.add_proximity_factors(rad=a.backend_radius, nms=a.backend_nms,
                                                                               thresh=a.backend_thresh, beta=a.beta))
@@ -159,8 +160,8 @@ def run_arm(kind, arm, ns, net, p, args, ref_mod):
             fe_mod = importlib.import_module("droid_frontend")
             a = types.SimpleNamespace(warmup=8, beta=0.3, frontend_nms=1, keyframe_thresh=0.0, frontend_window=25,
                                       frontend_thresh=16.0, frontend_radius=2)
-            full = fill_video(ns, p, n, n + 8)
-            v = ns.depth_video.DepthVideo(image_size=[8 * p["ht"], 8 * p["wd"]], buffer=n + 8)
+            full = fill_video(ns, p, n, n + 8, stereo=args.stereo)
+            v = ns.depth_video.DepthVideo(image_size=[8 * p["ht"], 8 * p["wd"]], buffer=n + 8, stereo=args.stereo)
             v.intrinsics[:] = full.intrinsics
             fe = fe_mod.DroidFrontend(net, v, a)
 
@@ -194,6 +195,7 @@ def main():
     ap.add_argument("--frames", type=int, default=500)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--arms", default="reference,drop-in,integrated")
+    ap.add_argument("--stereo", action="store_true", help="rig of two cameras (BASELINE configs[4]): fmaps of both, (i, i) edges")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
     ok, why = pyref.available()
@@ -204,10 +206,10 @@ def main():
     ns = pyref.load(B)
     torch.manual_seed(0)
     net = ns.droid_net.DroidNet().to(DEV).eval()
-    p = synth.make_ba_problem("C4", n_frames=max(args.frames, 16), knn=16)
-    res = {"kind": args.kind, "frames": args.frames, "image": "%dx%d at 1/8" % (p["ht"], p["wd"]), "arms": {}}
+    p = synth.make_ba_problem("C4", n_frames=max(args.frames, 16), knn=16)      # EuRoC shape: 40x64 at 1/8
+    res = {"kind": args.kind, "frames": args.frames, "stereo": bool(args.stereo), "image": "%dx%d at 1/8" % (p["ht"], p["wd"]), "arms": {}}
     for arm in args.arms.split(","):
-        run_arm(args.kind, arm, ns, net, p, types.SimpleNamespace(frames=min(args.frames, 40), steps=1), R)   # warm-up (cuDNN, allocator)
+        run_arm(args.kind, arm, ns, net, p, types.SimpleNamespace(frames=min(args.frames, 40), steps=1, stereo=args.stereo), R)   # warm-up (cuDNN, allocator)
         res["arms"][arm] = run_arm(args.kind, arm, ns, net, p, args, R)
     states = {arm: r.pop("_state") for arm, r in res["arms"].items()}
     ref = res["arms"].get("reference")
