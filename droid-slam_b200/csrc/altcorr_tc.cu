@@ -40,23 +40,30 @@ namespace atc {
 static constexpr int kC = 128;
 static constexpr int kTileM = 128;                   // source pixels per A tile = TMEM lanes
 static constexpr int kTiles = 1;                     // A tiles per CTA
-static constexpr int kN = 64;                        // target pixels per chunk = accumulator columns
 static constexpr int kSlots = 4;                     // accumulators per tile
 static constexpr int kASlab = kTileM * 128;          // 64 channels (128 B) x 128 rows
 static constexpr int kATile = 2 * kASlab;            // 32 KB
-static constexpr int kBSlab = kN * 128;              // 8 KB
-static constexpr int kBStage = 2 * kBSlab;           // 16 KB
 static constexpr int kBStages = 2;
-static constexpr int kRowLd = 68;                    // floats per staging row (64 + pad: conflict-free 16-byte stores)
-static constexpr int kStageWarp = 32 * kRowLd * 4;   // 8704 B per sampler warp
 static constexpr int kSamplers = 4 * kTiles;         // sampler warps
 static constexpr int kThreads = 32 * (kSamplers + 2);
 static constexpr int kAOff = 0;
-static constexpr int kBOff = kTiles * kATile;                     // 64 KB
-static constexpr int kStOff = kBOff + kBStages * kBStage;         // +80 KB
-static constexpr int kBarOff = kStOff + kSamplers * kStageWarp;   // +68 KB
-static constexpr int kSmem = kBarOff + 512 + 1024;
-static constexpr int kTmemCols = kTiles * kSlots * kN;   // 256 / 512: a power of two
+static constexpr int kBOff = kTiles * kATile;
+// Everything that depends on the accumulator width NC = target pixels per chunk: 64 (image rows of up to 64 pixels:
+// 100 KB of shared memory and 256 TMEM columns per CTA, two CTAs per SM) or 128 (rows of up to 128 pixels, e.g. the
+// 73-pixel rows of a 16:9 video at 1/8 resolution: 164 KB and 512 columns, one CTA per SM).
+template <int NC>
+struct Cfg {
+  static constexpr int kN = NC;
+  static constexpr int kBSlab = NC * 128;                            // 64 channels x NC rows
+  static constexpr int kBStage = 2 * kBSlab;
+  static constexpr int kRowLd = NC + 4;                              // floats per staging row (pad: conflict-free 16-byte stores)
+  static constexpr int kStageWarp = 32 * kRowLd * 4;
+  static constexpr int kStOff = kBOff + kBStages * kBStage;
+  static constexpr int kBarOff = kStOff + kSamplers * kStageWarp;
+  static constexpr int kSmem = kBarOff + 512 + 1024;
+  static constexpr int kTmemCols = kTiles * kSlots * NC;             // 256 / 512: a power of two
+  static constexpr int kCtasPerSm = NC == 64 && kTiles == 1 ? 2 : 1;
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -96,9 +103,9 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
   d |= (uint64_t)2 << 61;                  // SWIZZLE_128B
   return d;
 }
-// instruction descriptor, kind::f16: D = f32, A = B = f16, both K-major, M = 128, N = 64
-__device__ __forceinline__ uint32_t umma_idesc() {
-  return (1u << 4) | ((uint32_t)(kN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+// instruction descriptor, kind::f16: D = f32, A = B = f16, both K-major, M = 128, N = n
+__device__ __forceinline__ uint32_t umma_idesc(int n) {
+  return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
 }
 __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
   asm volatile(
@@ -164,11 +171,15 @@ __device__ __forceinline__ Window make_window(float x, float y, int H2, int W2, 
 
 // grid = (ceil(HW1 / 256), N, B).  out [B, N, nlev * 49, HW1].  `skip_if` (may be null): a device flag; non-zero =
 // leave everything to the CUDA-core kernel launched behind this one.
-__global__ void __launch_bounds__(kThreads, kTiles == 1 ? 2 : 1)
+template <int NC>
+__global__ void __launch_bounds__(kThreads, Cfg<NC>::kCtasPerSm)
 altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ ii, const int64_t* __restrict__ jj,
                   const float* __restrict__ coords, float* __restrict__ out, const int* __restrict__ skip_if, int N,
                   int HW1) {
   if (skip_if && *skip_if) return;
+  using C = Cfg<NC>;
+  constexpr int kN = C::kN, kBSlab = C::kBSlab, kBStage = C::kBStage, kRowLd = C::kRowLd, kStageWarp = C::kStageWarp;
+  constexpr int kStOff = C::kStOff, kBarOff = C::kBarOff, kTmemCols = C::kTmemCols;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kBarOff);
@@ -272,7 +283,7 @@ altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ 
   } else if (warp == kSamplers + 1) {
     // ---------------- MMA issuer ----------------
     if (lane == 0 && total > 0) {
-      const uint32_t idesc = umma_idesc();
+      const uint32_t idesc = umma_idesc(kN);
       mbar_wait(a_full, 0);
       for (int it = 0; it < total; it++) {
         const int s = it % kBStages, slot = it & (kSlots - 1);
@@ -312,13 +323,16 @@ altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ 
         tc_fence_after();
         if (__any_sync(0xffffffffu, need)) {
           const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + (tile * kSlots + slot) * kN;
-          uint32_t r[64];
-          tmem_ld32(taddr, r);                       // both halves in flight, one wait
-          tmem_ld32(taddr + 32, r + 32);
-          tmem_ld_wait();
-          uint4* dst = reinterpret_cast<uint4*>(mine);
 #pragma unroll
-          for (int j = 0; j < 16; j++) dst[j] = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+          for (int h = 0; h < kN / 64; h++) {          // 64 columns at a time: two loads in flight, one wait
+            uint32_t r[64];
+            tmem_ld32(taddr + 64 * h, r);
+            tmem_ld32(taddr + 64 * h + 32, r + 32);
+            tmem_ld_wait();
+            uint4* dst = reinterpret_cast<uint4*>(mine + 64 * h);
+#pragma unroll
+            for (int j = 0; j < 16; j++) dst[j] = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+          }
         }
         tc_fence_before();
         __syncwarp();
@@ -413,9 +427,9 @@ static bool make_map(CUtensorMap* m, const void* base, size_t rows, int box_rows
 
 }  // namespace atc
 
-// True if the tensor-core kernel covers this shape (fp16 maps, 128 channels, radius 3, image rows of <= 64 pixels).
+// True if the tensor-core kernel covers this shape (fp16 maps, 128 channels, radius 3, image rows of <= 128 pixels).
 bool altcorr_tc_supported(int B, int N, int H1, int W1, int H2, int W2, int C, int radius, size_t frames1, size_t frames2) {
-  if (C != atc::kC || radius != 3 || W2 > atc::kN || W2 <= 0 || H2 <= 0) return false;
+  if (C != atc::kC || radius != 3 || W2 > 128 || W2 <= 0 || H2 <= 0) return false;
   if (B > 65535 || N > 65535) return false;
   const size_t r1 = frames1 * (size_t)H1 * W1, r2 = frames2 * (size_t)H2 * W2;
   return r1 < (1u << 31) && r2 < (1u << 31);
@@ -436,20 +450,29 @@ int altcorr_tc_forward_levels(const void* f1, const void* const* f2, const int* 
   memset(&P, 0, sizeof(P));
   P.nlev = nlev;
   if (!atc::make_map(&P.a, f1, frames1 * (size_t)HW1, atc::kTileM)) return DROID_ERR_NOT_IMPLEMENTED;
+  int wmax = 0;
+  for (int l = 0; l < nlev; l++) wmax = W2[l] > wmax ? W2[l] : wmax;
+  const int nc = wmax <= 64 ? 64 : 128;                 // accumulator width: the widest level decides
   for (int l = 0; l < nlev; l++) {
     if (!altcorr_tc_supported(B, N, H1, W1, H2[l], W2[l], C, radius, frames1, frames2)) return DROID_ERR_NOT_IMPLEMENTED;
-    if (((uintptr_t)f2[l] & 15) || !atc::make_map(&P.b[l], f2[l], frames2 * (size_t)H2[l] * W2[l], atc::kN))
+    if (((uintptr_t)f2[l] & 15) || !atc::make_map(&P.b[l], f2[l], frames2 * (size_t)H2[l] * W2[l], nc))
       return DROID_ERR_NOT_IMPLEMENTED;
     P.H2[l] = H2[l];
     P.W2[l] = W2[l];
-    P.Rh[l] = atc::kN / W2[l];
+    P.Rh[l] = nc / W2[l];
     P.cscale[l] = cscale[l];
   }
   DevCtx& dc = dev_ctx();
-  if (dc.first(kOnceAltcorrTc))
-    cudaFuncSetAttribute(atc::altcorr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::kSmem);
+  if (dc.first(kOnceAltcorrTc)) {
+    cudaFuncSetAttribute(atc::altcorr_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::Cfg<64>::kSmem);
+    cudaFuncSetAttribute(atc::altcorr_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::Cfg<128>::kSmem);
+  }
   dim3 grid((HW1 + atc::kTiles * atc::kTileM - 1) / (atc::kTiles * atc::kTileM), N, B);
-  DROID_LAUNCH atc::altcorr_tc_kernel<<<grid, atc::kThreads, atc::kSmem, st>>>(P, ii, jj, coords, out, skip_if, N, HW1);
+  if (nc == 64) {
+    DROID_LAUNCH atc::altcorr_tc_kernel<64><<<grid, atc::kThreads, atc::Cfg<64>::kSmem, st>>>(P, ii, jj, coords, out, skip_if, N, HW1);
+  } else {
+    DROID_LAUNCH atc::altcorr_tc_kernel<128><<<grid, atc::kThreads, atc::Cfg<128>::kSmem, st>>>(P, ii, jj, coords, out, skip_if, N, HW1);
+  }
   return check_launch();
 }
 

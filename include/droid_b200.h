@@ -98,7 +98,7 @@ int droid_altcorr_forward(const void* fmap1, const void* fmap2, const float* coo
                           int radius, void* stream);
 
 /* The same op with a caller-supplied workspace (droid_altcorr_forward_workspace_bytes; 0 = not needed for this shape),
- * which unlocks the tensor-core kernel (csrc/altcorr_tc.cu: radius 3, C = 128, W2 <= 64): both maps are copied to fp16
+ * which unlocks the tensor-core kernel (csrc/altcorr_tc.cu: radius 3, C = 128, W2 <= 128): both maps are copied to fp16
  * in the workspace with a round-trip check -- AltCorrBlock hands `.float()` copies of an fp16 pyramid
  * (droid_slam/modules/corr.py:96-120), so the copy is exact -- and correlated with tcgen05.mma; when a value is not an
  * fp16 number a device-side flag routes the call to the CUDA-core kernel instead, without a host round trip.  Same
@@ -120,7 +120,7 @@ int droid_altcorr_backward(const float* fmap1, const float* fmap2, const float* 
 /* Indexed alt-correlation: same result as altcorr_forward on
  * fmap1 = pyr0[ii], fmap2 = pyrL[jj] (modules/corr.py:106-125) without the gathered copies.
  *   pyr0 [F,H1,W1,C], pyrL [F,H2,W2,C] dtype; ii,jj [B] int64; output f32. */
-/* fp16 pyramids with C = 128 and W2 <= 64 take the tensor-core kernel (TMA straight from the pyramid, no copies). */
+/* fp16 pyramids with C = 128 and W2 <= 128 take the tensor-core kernel (TMA straight from the pyramid, no copies). */
 int droid_altcorr_forward_indexed(const void* pyr0, const void* pyrL, const int64_t* ii,
                                   const int64_t* jj, const float* coords, float* out, int dtype,
                                   int F, int B, int N, int H1, int W1, int H2, int W2, int C,
@@ -129,7 +129,7 @@ int droid_altcorr_forward_indexed(const void* pyr0, const void* pyrL, const int6
 /* Every level of an AltCorrBlock in one launch (extension; droid_slam/modules/corr.py:106-125 is four calls + cat):
  *   pyr_host[l]: device pointer of level l, [F, H1>>l, W1>>l, C] channel-last; coords [B,N,H1,W1,2] at LEVEL 0 (divided
  *   by 2^l inside, exactly as corr.py:116); out [B, N, num_levels*49, H1, W1] f32, level l at channels 49 l .. 49 l + 48.
- * Tensor-core kernel only (f16, C = 128, radius 3, W1 <= 64, num_levels <= 4): DROID_ERR_NOT_IMPLEMENTED otherwise --
+ * Tensor-core kernel only (f16, C = 128, radius 3, W1 <= 128, num_levels <= 4): DROID_ERR_NOT_IMPLEMENTED otherwise --
  * the caller then uses droid_altcorr_forward_indexed per level (the Python host does). */
 int droid_altcorr_pyramid_indexed(const void* const* pyr_host, int num_levels, const int64_t* ii,
                                   const int64_t* jj, const float* coords, float* out, int dtype, int F, int B,

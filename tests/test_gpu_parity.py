@@ -170,14 +170,16 @@ def _tc_case(n_edges, ht, wd, seed, scramble):
 
 
 @pytest.mark.parametrize("ht,wd,n_edges,scramble", [(40, 64, 6, False), (40, 64, 5, True), (48, 64, 3, True),
-                                                     (24, 40, 4, True), (18, 22, 4, True), (16, 80, 3, True)])
+                                                     (24, 40, 4, True), (18, 22, 4, True), (16, 80, 3, True), (41, 73, 3, True),
+                                                     (16, 136, 2, True)])
 def test_altcorr_tensor_core_path(backends, ht, wd, n_edges, scramble):
     """altcorr_tc.cu (tcgen05 GEMM + in-CTA window sampling) against the CUDA-core kernel and the oracle: every level of
     the pyramid, through the indexed fp16 entry point (TMA straight from the pyramid) and through the drop-in fp32
     signature (fp16 copies + exactness flag).  Sizes: EuRoC / TartanAir grids (256-pixel CTAs exactly), 24x40 (960 =
-    3.75 CTAs, rows of 40 / 20 / 10 / 5 pixels), 18x22 (odd rows, level widths 22 / 11 / 5 / 2) and 16x80 (level 0 is
-    wider than a 64-column accumulator: that level takes the CUDA-core kernel, the others the tensor cores, and the
-    one-launch pyramid call falls back to per-level calls in the Python host)."""
+    3.75 CTAs, rows of 40 / 20 / 10 / 5 pixels), 18x22 (odd rows, level widths 22 / 11 / 5 / 2), 16x80 and 41x73 (a 16:9
+    video at 1/8 resolution: rows wider than 64 pixels take the 128-column instantiation) and 16x136 (level 0 wider than
+    any accumulator: that level takes the CUDA-core kernel, the others the tensor cores, and the one-launch pyramid
+    call falls back to per-level calls in the Python host)."""
     p, pyr, coords = _tc_case(n_edges, ht, wd, 7 + ht, scramble)
     ii, jj = cu(p["ii"]), cu(p["jj"])
     for l in range(4):
