@@ -116,7 +116,8 @@ def edges_global(Rs, ts, rad=2, knn=8, max_factors=None):
     return [p[0] for p in pairs], [p[1] for p in pairs]
 
 
-def make_ba_problem(name="C1", seed=1234, n_frames=None, stereo=False, sensor=False, nbuf=None, knn=8, loop=None):
+def make_ba_problem(name="C1", seed=1234, n_frames=None, stereo=False, sensor=False, nbuf=None, knn=8, loop=None,
+                    shape=None):
     """Returns a dict of float32/int64 numpy arrays: poses, disps, intrinsics, disps_sens, targets,
     weights, eta, ii, jj, t0, t1 (+ gt_poses, gt_disps).  C4 with n_frames=1000, knn=16 is the
     BASELINE.json backend configuration: 1000 keyframes, 20 862 edges (~20k), 40x64."""
@@ -143,6 +144,9 @@ def make_ba_problem(name="C1", seed=1234, n_frames=None, stereo=False, sensor=Fa
         raise ValueError(name)
     if n_frames is not None and name != "C4":
         raise ValueError("n_frames only applies to C4")
+    if shape is not None:      # another grid (e.g. 41x73: a 16:9 video at 1/8 resolution); intrinsics scaled along
+        intr = intr * np.array([shape[1] / wd, shape[0] / ht, shape[1] / wd, shape[0] / ht])
+        ht, wd = int(shape[0]), int(shape[1])
     Rs, ts = trajectory(n, loop=loop)
     if ii is None:
         ii, jj = edges_global(Rs, ts, rad=2, knn=knn, max_factors=None)

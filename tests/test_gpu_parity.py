@@ -347,6 +347,32 @@ def test_frame_distance(backends):
     assert np.all(got[a == b] == 0.0)          # frame_distance(i, i) == 0
 
 
+@pytest.mark.parametrize("shape", [(41, 73), (25, 35)])
+def test_geometry_ops_odd_image_sizes(backends, ref_ext, shape):
+    """frame_distance / projmap / iproj / depth_filter / reproject on grids that are not 48x64 / 40x64 (pixel count not a
+    multiple of 4 or of the CTA size), against the live reference extension: frame_distance and the depth_filter counts
+    bit for bit, the float outputs to 1e-5."""
+    p = synth.make_ba_problem("C4", n_frames=24, shape=shape)
+    P, D, K = cu(p["gt_poses"]), cu(p["gt_disps"]), cu(p["intrinsics"])
+    n = 24
+    a, b = torch.meshgrid(torch.arange(n, device="cuda"), torch.arange(n, device="cuda"), indexing="ij")
+    a, b = a.reshape(-1).contiguous(), b.reshape(-1).contiguous()
+    for x, y in ((a, b), (a[:7].contiguous(), b[:7].contiguous())):     # table-driven kernel and the few-pairs entry point
+        assert torch.equal(backends.frame_distance(P, D, K, x, y, 0.3), ref_ext.frame_distance(P, D, K, x, y, 0.3))
+    ii, jj = cu(p["ii"]), cu(p["jj"])
+    c, v = backends.projmap(P, D, K, ii, jj)
+    rc, rv = ref_ext.projmap(P, D, K, ii, jj)
+    assert rel(c.cpu().numpy(), rc.cpu().numpy()) <= 1e-5 and torch.equal(v, rv)
+    assert rel(backends.iproj(P, D, K).cpu().numpy(), ref_ext.iproj(P, D, K).cpu().numpy()) <= 1e-5
+    ix = torch.arange(n, device="cuda")
+    th = torch.full((n,), 0.05, device="cuda")
+    assert torch.equal(backends.depth_filter(P, D, K, ix, th), ref_ext.depth_filter(P, D, K, ix, th))
+    Kf = K[None].repeat(n, 1).contiguous()
+    want_c, want_v = O.reproject(p["gt_poses"], p["gt_disps"], Kf.cpu().numpy(), p["ii"], p["jj"])[:2]
+    got_c, got_v = backends.reproject(P, D, Kf, ii, jj)
+    assert float(np.abs(got_c.cpu().numpy() - want_c).max()) <= 1e-5 * float(np.abs(want_c).max())
+
+
 def test_depth_filter_bit_exact(backends):
     """Integer counts: bit-exact against the stored output of the unmodified reference extension
     (tests/golden/ref_geom.npz) and against the oracle (which reproduces that output exactly, tests/test_oracle.py)."""
@@ -439,6 +465,17 @@ def test_ba_backend_window_and_fixed_poses(backends):
     check_per_iteration(backends, p, 2, 1e-5, 1e-2)
     gp, _, _, _ = run_ba(backends, p, 2, lm=1e-5, ep=1e-2)
     assert np.array_equal(gp[:5], p["poses"][:5])
+
+
+@pytest.mark.parametrize("shape", [(41, 73), (25, 35), (6, 9)])
+def test_ba_odd_image_sizes(backends, shape):
+    """Grids whose pixel count is not a multiple of 4 (16:9 videos at 1/8 resolution, tiny maps): no kernel may assume
+    48x64 / 40x64 -- the tensor-core Schur builders move 4 pixels per access and hand such frames to the CUDA-core
+    kernel, the accumulation slabs end mid-vector."""
+    p = synth.make_ba_problem("C1", shape=shape)
+    check_per_iteration(backends, p, 2, 1e-4, 0.1)
+    q = synth.make_ba_problem("C4", n_frames=40, shape=shape)
+    check_per_iteration(backends, q, 2, 1e-5, 1e-2)
 
 
 def test_ba_input_validation_raises(backends):
