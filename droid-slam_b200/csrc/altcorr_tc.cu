@@ -196,6 +196,17 @@ altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ 
   const int pix0 = blockIdx.x * (kTiles * kTileM);
   const int nlev = P.nlev;
 
+  // every sampler thread: its pixel; the coordinate load is in flight while the barriers / TMEM are set up
+  const int tile = warp >> 2, q = warp & 3;
+  const int pix = pix0 + tile * kTileM + q * 32 + lane;
+  const bool live = warp < kSamplers && pix < HW1;
+  float x0 = 0.f, y0 = 0.f;
+  if (live) {
+    const float2 xy = __ldg(reinterpret_cast<const float2*>(coords + (((size_t)b * N + n) * HW1 + pix) * 2));
+    x0 = xy.x;
+    y0 = xy.y;
+  }
+
   // The producer thread sets up the barriers and starts the A tiles at once: they do not depend on the chunk ranges
   // computed below, and their latency (frame index -> TMA -> HBM) otherwise sits on every CTA's critical path.
   int fr2 = 0;
@@ -230,18 +241,8 @@ altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ 
   }
   __syncthreads();
 
-  // ---- every sampler thread: its pixel and, per level, the chunks its window touches ----
-  const int tile = warp >> 2, q = warp & 3;
-  const int pix = pix0 + tile * kTileM + q * 32 + lane;
-  bool live = false;
-  float x0 = 0.f, y0 = 0.f;
+  // ---- per level, the chunks the pixel's window touches ----
   if (warp < kSamplers) {
-    live = pix < HW1;
-    if (live) {
-      const float2 xy = __ldg(reinterpret_cast<const float2*>(coords + (((size_t)b * N + n) * HW1 + pix) * 2));
-      x0 = xy.x;
-      y0 = xy.y;
-    }
     for (int l = 0; l < nlev; l++) {
       const Window w = make_window(x0 * P.cscale[l], y0 * P.cscale[l], P.H2[l], P.W2[l], P.Rh[l], live);
       int lo = w.c_lo <= w.c_hi ? w.c_lo : (1 << 30), hi = w.c_lo <= w.c_hi ? w.c_hi : -1;
