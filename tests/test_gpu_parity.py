@@ -478,6 +478,39 @@ def test_ba_odd_image_sizes(backends, shape):
     check_per_iteration(backends, q, 2, 1e-5, 1e-2)
 
 
+def _random_ba_problem(seed):
+    """A random small problem with the reference's degrees of freedom exercised at once: grid size, window [t0, t1) that
+    does not start at 1, edges into fixed poses, duplicate and one-directional edges, a frame
+    whose weights are all zero, stereo (i, i) edges, sensor depths, a pose buffer longer than the trajectory."""
+    rng = np.random.default_rng(1000 + seed)
+    ht, wd = int(rng.integers(5, 14)) * 2 + int(rng.integers(0, 2)), int(rng.integers(6, 20)) * 2 + int(rng.integers(0, 2))
+    n = int(rng.integers(6, 15))
+    p = synth.make_ba_problem("C4", n_frames=n, knn=int(rng.integers(0, 4)), shape=(ht, wd), seed=seed,
+                              stereo=bool(seed % 3 == 0), sensor=bool(seed % 2), nbuf=n + int(rng.integers(0, 5)))
+    ii, jj = p["ii"], p["jj"]
+    keep = rng.uniform(size=len(ii)) > 0.15                      # drop edges at random: one-directional pairs appear
+    keep |= np.abs(ii - jj) == 1                                 # ... but the graph stays connected
+    dup = rng.integers(0, len(ii), size=3)                       # and repeat a few (legal: the reference never de-duplicates)
+    sel = np.concatenate([np.nonzero(keep)[0], dup])
+    for k in ("ii", "jj", "targets", "weights"):
+        p[k] = np.ascontiguousarray(p[k][sel])
+    z = int(rng.integers(0, n))
+    p["weights"][p["ii"] == z] = 0.0                             # a source frame that contributes nothing but eta
+    p["t0"] = int(rng.integers(1, 4))
+    p["t1"] = int(max(p["ii"].max(), p["jj"].max())) + 1         # as every reference caller does (an edge into a frame >= t1
+                                                                 # indexes the reference's block matrix out of range)
+    kx = np.unique(np.concatenate([np.arange(p["t0"], p["t1"]), p["ii"]]))
+    p["eta"] = np.ascontiguousarray(np.resize(p["eta"], (len(kx),) + p["eta"].shape[1:]))
+    return p
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_ba_random_small_problems(backends, seed):
+    p = _random_ba_problem(seed)
+    motion_only = seed % 4 == 3
+    check_per_iteration(backends, p, 2, 1e-4, 0.1, motion_only=motion_only)
+
+
 def test_ba_input_validation_raises(backends):
     """The reference fails on the eta broadcast when eta does not have one row per optimised frame
     (src/droid_kernels.cu:1398) and has undefined behaviour for an edge index outside the buffer; here the device-side
