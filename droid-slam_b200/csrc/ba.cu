@@ -1804,7 +1804,7 @@ extern "C" int droid_ba(float* poses, float* disps, const float* intrinsics, con
         // rest.  The two kernels touch disjoint frames, so the CUDA-core one runs on a second stream: its few, long
         // CTAs start first and the tensor-core CTAs fill the SMs around them instead of waiting for its tail.
         static const bool tc_on = []() { const char* e = getenv("DROID_SCHUR_TC"); return !(e && e[0] == '0'); }();
-        const bool use_tc = tc_on && (HW % 4 == 0);      // the tensor-core builders move 4 pixels per 16-byte access
+        const bool use_tc = tc_on;
         const int tc_max_d = use_tc ? kSchurTcMaxDeg + 1 : 0;
         // once the device's maximum out-degree is known (large systems), kernels without a frame to work on are not launched
         const bool need_cc = !status_read || max_deg + 1 > tc_max_d;

@@ -145,6 +145,7 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 // (the conversion instruction runs at a fraction of the ALU rate and made the pack pass cost as much as the MMAs)
 __device__ __forceinline__ uint32_t tf32_rna(float x) { return (__float_as_uint(x) + 0x1000u) & 0xFFFFE000u; }
 
+template <bool kVec>
 __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
     const float* __restrict__ ejc, const int64_t* __restrict__ jj, const float* __restrict__ gij, int* __restrict__ status,
     const int* __restrict__ kx, const int* __restrict__ eptr, const int* __restrict__ eidx,
@@ -263,12 +264,26 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
     constexpr int kMaxI = (kSchurTcMaxU + 7) / 8;     // edges per thread
     float4 r_c[kMaxI][kEjComp];
     float4 n_q = make_float4(0.f, 0.f, 0.f, 0.f), n_w = n_q;
+    // grids whose pixel count is not a multiple of 4 (41x73, ...): planes start at odd offsets and the last group of a
+    // frame is partial, so the 16-byte loads become four masked scalar ones (pixels >= p1 read as zero -> zero rows)
+    auto ld4 = [&](const float* src, int p, bool stream) {
+      float4 v;
+      if constexpr (kVec) {
+        v = stream ? __ldcs(reinterpret_cast<const float4*>(src)) : __ldg(reinterpret_cast<const float4*>(src));
+      } else {
+        v.x = p + 0 < p1 ? __ldg(src + 0) : 0.f;
+        v.y = p + 1 < p1 ? __ldg(src + 1) : 0.f;
+        v.z = p + 2 < p1 ? __ldg(src + 2) : 0.f;
+        v.w = p + 3 < p1 ? __ldg(src + 3) : 0.f;
+      }
+      return v;
+    };
     auto fetch = [&](int it, int p, bool ok) {
       const int i = slice + 8 * it;
       if (ok && i < nu) {
         const float* src = ejc + (size_t)s_e[i] * kEjComp * HW + p;
 #pragma unroll
-        for (int q = 0; q < kEjComp; q++) r_c[it][q] = __ldcs(reinterpret_cast<const float4*>(src + (size_t)q * HW));
+        for (int q = 0; q < kEjComp; q++) r_c[it][q] = ld4(src + (size_t)q * HW, p, true);
         if (p + kTB < p1) {      // and the pass after that on its way into L2
 #pragma unroll
           for (int q = 0; q < kEjComp; q++) asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (size_t)q * HW + kTB));
@@ -276,8 +291,8 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
       }
     };
     auto fetch_pix = [&](int p, bool ok) {
-      n_q = ok ? __ldg(reinterpret_cast<const float4*>(Qi + (size_t)m * HW + p)) : make_float4(0.f, 0.f, 0.f, 0.f);
-      if (slice == 7) n_w = ok ? __ldg(reinterpret_cast<const float4*>(Wi + (size_t)m * HW + p)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      n_q = ok ? ld4(Qi + (size_t)m * HW + p, p, false) : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (slice == 7) n_w = ok ? ld4(Wi + (size_t)m * HW + p, p, false) : make_float4(0.f, 0.f, 0.f, 0.f);
     };
     // 16-byte store of 4 pixels of one row: hi and lo parts at byte offset `off` of the stage's two arrays
     auto put_row = [&](int off, float x0, float x1, float x2, float x3) {
@@ -463,11 +478,17 @@ __global__ void __launch_bounds__(kThreads, 1) ba_schur_tc_kernel(
 int launch_schur_tc(const float* ejc, const int64_t* jj, const float* gij, int* status, const int* kx, const int* eptr, const int* eidx,
                     const float* Qi, const float* Wi, double* A, double* bvec, int HW, int wd, int slab, int S, int t0,
                     int P, int n_eta, int frame_lo, int frame_hi, const int* ppos, cudaStream_t st) {
-  if (dev_ctx().first(kOnceSchurTc))
-    cudaFuncSetAttribute(stc::ba_schur_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, stc::kSmem);
-  DROID_LAUNCH stc::ba_schur_tc_kernel<<<dim3(S, n_eta, 3), stc::kThreads, stc::kSmem, st>>>(
-      ejc, jj, gij, status, kx, eptr, eidx, Qi, Wi, A, bvec, HW, wd, slab, t0, P, n_eta,
-      frame_lo, frame_hi, ppos);
+  if (dev_ctx().first(kOnceSchurTc)) {
+    cudaFuncSetAttribute(stc::ba_schur_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, stc::kSmem);
+    cudaFuncSetAttribute(stc::ba_schur_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, stc::kSmem);
+  }
+  if ((HW & 3) == 0) {
+    DROID_LAUNCH stc::ba_schur_tc_kernel<true><<<dim3(S, n_eta, 3), stc::kThreads, stc::kSmem, st>>>(
+        ejc, jj, gij, status, kx, eptr, eidx, Qi, Wi, A, bvec, HW, wd, slab, t0, P, n_eta, frame_lo, frame_hi, ppos);
+  } else {     // pixel count not a multiple of 4: masked scalar loads in the builders
+    DROID_LAUNCH stc::ba_schur_tc_kernel<false><<<dim3(S, n_eta, 3), stc::kThreads, stc::kSmem, st>>>(
+        ejc, jj, gij, status, kx, eptr, eidx, Qi, Wi, A, bvec, HW, wd, slab, t0, P, n_eta, frame_lo, frame_hi, ppos);
+  }
   return check_launch();
 }
 
