@@ -218,14 +218,13 @@ __global__ void __launch_bounds__(256) altcorr_bwd_kernel(
 // altcorr_tc.cu
 bool altcorr_tc_supported(int B, int N, int H1, int W1, int H2, int W2, int C, int radius, size_t frames1, size_t frames2);
 int altcorr_tc_forward(const void* f1, const void* f2, const int64_t* ii, const int64_t* jj, const float* coords, float* out,
-                       const int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int H2, int W2,
-                       int C, int radius, cudaStream_t st);
+                       int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int H2, int W2,
+                       int C, int radius, cudaStream_t st, bool f1_is_f32);
 int altcorr_tc_forward_levels(const void* f1, const void* const* f2, const int* H2, const int* W2, const float* cscale,
                               int nlev, const int64_t* ii, const int64_t* jj, const float* coords, float* out,
-                              const int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int C,
-                              int radius, cudaStream_t st);
-int altcorr_tc_convert(const float* f1, const float* f2, void* f1h, void* f2h, int* flag, size_t n1, size_t n2,
-                       cudaStream_t st);
+                              int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int C,
+                              int radius, cudaStream_t st, bool f1_is_f32);
+int altcorr_tc_convert(const float* src, void* dst, int* flag, size_t n, cudaStream_t st);
 
 static bool tc_enabled() {
   static const bool on = [] {
@@ -293,13 +292,13 @@ extern "C" int droid_altcorr_forward(const void* fmap1, const void* fmap2, const
                     N, H1, W1, H2, W2, C, radius, (cudaStream_t)stream);
 }
 
-// Workspace of droid_altcorr_forward_ws: fp16 copies of both maps + the exactness flag; 0 = shape not covered by the
+// Workspace of droid_altcorr_forward_ws: an fp16 copy of the target map + the exactness flag; 0 = shape not covered by the
 // tensor-core kernel (the call then behaves exactly like droid_altcorr_forward).
 extern "C" size_t droid_altcorr_forward_workspace_bytes(int B, int N, int H1, int W1, int H2, int W2, int C, int radius) {
   if (B <= 0 || N <= 0 || H1 <= 0 || W1 <= 0 || H2 <= 0 || W2 <= 0) return 0;
   if (!tc_enabled() || !altcorr_tc_supported(B, N, H1, W1, H2, W2, C, radius, (size_t)B, (size_t)B)) return 0;
-  const size_t n1 = (size_t)B * H1 * W1 * C, n2 = (size_t)B * H2 * W2 * C;
-  return 256 + ((n1 * 2 + 255) & ~(size_t)255) + ((n2 * 2 + 255) & ~(size_t)255) + 256;
+  const size_t n2 = (size_t)B * H2 * W2 * C;
+  return 256 + ((n2 * 2 + 255) & ~(size_t)255) + 256;
 }
 
 extern "C" int droid_altcorr_forward_ws(const void* fmap1, const void* fmap2, const float* coords, void* out,
@@ -314,16 +313,16 @@ extern "C" int droid_altcorr_forward_ws(const void* fmap1, const void* fmap2, co
   const size_t need = droid_altcorr_forward_workspace_bytes(B, N, H1, W1, H2, W2, C, radius);
   const bool aligned = (((uintptr_t)fmap1 | (uintptr_t)fmap2 | (uintptr_t)workspace) & 15) == 0;
   if (need && workspace && workspace_bytes >= need && aligned) {
-    const size_t n1 = (size_t)B * H1 * W1 * C, n2 = (size_t)B * H2 * W2 * C;
+    const size_t n2 = (size_t)B * H2 * W2 * C;
     unsigned char* w = reinterpret_cast<unsigned char*>(workspace);
     int* flag = reinterpret_cast<int*>(w);
-    void* f1h = w + 256;
-    void* f2h = w + 256 + ((n1 * 2 + 255) & ~(size_t)255);
-    int rc = altcorr_tc_convert(reinterpret_cast<const float*>(fmap1), reinterpret_cast<const float*>(fmap2), f1h, f2h,
-                                flag, n1, n2, st);
+    void* f2h = w + 256;
+    // the target map is copied to fp16 here (every CTA of an edge re-reads it); the source map is converted tile by
+    // tile inside the kernel.  Both raise the flag on a value that is not an fp16 number.
+    int rc = altcorr_tc_convert(reinterpret_cast<const float*>(fmap2), f2h, flag, n2, st);
     if (rc != DROID_OK) return rc;
-    rc = altcorr_tc_forward(f1h, f2h, nullptr, nullptr, coords, reinterpret_cast<float*>(out), flag, (size_t)B, (size_t)B,
-                            B, N, H1, W1, H2, W2, C, radius, st);
+    rc = altcorr_tc_forward(fmap1, f2h, nullptr, nullptr, coords, reinterpret_cast<float*>(out), flag, (size_t)B, (size_t)B,
+                            B, N, H1, W1, H2, W2, C, radius, st, true);
     if (rc == DROID_OK)      // behind it, gated on the flag: the CUDA-core kernel for inputs that are not fp16 values
       return fwd_common(fmap1, fmap2, nullptr, nullptr, coords, reinterpret_cast<float*>(out), dtype, B, N, H1, W1, H2,
                         W2, C, radius, st, flag);
@@ -344,7 +343,7 @@ extern "C" int droid_altcorr_forward_indexed(const void* pyr0, const void* pyrL,
   if (C != 128 && C != 256) return DROID_ERR_INVALID_ARGUMENT;
   if (dtype == DROID_DTYPE_F16 && tc_enabled()) {
     const int rc = altcorr_tc_forward(pyr0, pyrL, ii, jj, coords, out, nullptr, (size_t)F, (size_t)F, B, N, H1, W1, H2,
-                                      W2, C, radius, (cudaStream_t)stream);
+                                      W2, C, radius, (cudaStream_t)stream, false);
     if (rc != DROID_ERR_NOT_IMPLEMENTED) return rc;
   }
   return fwd_common(pyr0, pyrL, ii, jj, coords, out, dtype, B, N, H1, W1, H2, W2, C, radius,
@@ -371,7 +370,7 @@ extern "C" int droid_altcorr_pyramid_indexed(const void* const* pyr_host, int nu
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == DROID_DTYPE_F16 && tc_enabled()) {
     const int rc = altcorr_tc_forward_levels(pyr_host[0], pyr_host, H2, W2, cs, num_levels, ii, jj, coords, out, nullptr,
-                                             (size_t)F, (size_t)F, B, N, H1, W1, C, radius, st);
+                                             (size_t)F, (size_t)F, B, N, H1, W1, C, radius, st, false);
     if (rc != DROID_ERR_NOT_IMPLEMENTED) return rc;
   }
   return DROID_ERR_NOT_IMPLEMENTED;   // the Python host then loops over droid_altcorr_forward_indexed

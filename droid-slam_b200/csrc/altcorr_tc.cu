@@ -171,12 +171,15 @@ __device__ __forceinline__ Window make_window(float x, float y, int H2, int W2, 
 
 // grid = (ceil(HW1 / 256), N, B).  out [B, N, nlev * 49, HW1].  `skip_if` (may be null): a device flag; non-zero =
 // leave everything to the CUDA-core kernel launched behind this one.
-template <int NC>
+// A32: the source map arrives as fp32 (`f1_32`: [B][HW1][128], the drop-in signature) and the sampler warps convert
+// their A tile to fp16 themselves -- with the same round-trip check as the pre-pass, raising `flag` -- instead of a
+// TMA load from an fp16 copy: the copy of f1 (3/4 of the conversion traffic over a pyramid) is never made.
+template <int NC, bool A32>
 __global__ void __launch_bounds__(kThreads, Cfg<NC>::kCtasPerSm)
 altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ ii, const int64_t* __restrict__ jj,
-                  const float* __restrict__ coords, float* __restrict__ out, const int* __restrict__ skip_if, int N,
-                  int HW1) {
-  if (skip_if && *skip_if) return;
+                  const float* __restrict__ coords, float* __restrict__ out, int* __restrict__ flag, int N,
+                  int HW1, const float* __restrict__ f1_32) {
+  if (flag && *reinterpret_cast<volatile int*>(flag)) return;
   using C = Cfg<NC>;
   constexpr int kN = C::kN, kBSlab = C::kBSlab, kBStage = C::kBStage, kRowLd = C::kRowLd, kStageWarp = C::kStageWarp;
   constexpr int kStOff = C::kStOff, kBarOff = C::kBarOff, kTmemCols = C::kTmemCols;
@@ -213,7 +216,7 @@ altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ 
   if (threadIdx.x == kSamplers * 32) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&P.a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&P.b[0]) : "memory");
-    mbar_init(a_full, 1);
+    mbar_init(a_full, A32 ? kSamplers : 1);
     for (int i = 0; i < kBStages; i++) {
       mbar_init(b_full + i, 1);
       mbar_init(b_empty + i, 1);
@@ -227,12 +230,14 @@ altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ 
       crange[2 * l + 1] = -1;
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    const int fr1 = ii ? (int)ii[b] : b;
     fr2 = jj ? (int)jj[b] : b;
-    mbar_expect_tx(a_full, kTiles * kATile);
-    for (int t = 0; t < kTiles; t++)
-      for (int ks = 0; ks < 2; ks++)
-        tma_load_2d(smem + kAOff + t * kATile + ks * kASlab, &P.a, a_full, ks * 64, fr1 * HW1 + pix0 + t * kTileM);
+    if constexpr (!A32) {
+      const int fr1 = ii ? (int)ii[b] : b;
+      mbar_expect_tx(a_full, kTiles * kATile);
+      for (int t = 0; t < kTiles; t++)
+        for (int ks = 0; ks < 2; ks++)
+          tma_load_2d(smem + kAOff + t * kATile + ks * kASlab, &P.a, a_full, ks * 64, fr1 * HW1 + pix0 + t * kTileM);
+    }
   }
   if (warp == kSamplers) {
     __syncwarp();
@@ -241,6 +246,33 @@ altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ 
   }
   __syncthreads();
 
+  if constexpr (A32) {
+    // fp32 A tile -> fp16, K-major SWIZZLE_128B: a warp converts 32 rows, one row (512 bytes) per step, lane l the
+    // channels 4l .. 4l + 3 = half of the 16-byte unit (l & 15) >> 1 of K slab l >> 4
+    if (warp < kSamplers) {
+      const float* src = f1_32 + ((size_t)(ii ? (size_t)ii[b] : (size_t)b) * HW1 + pix0 + tile * kTileM) * kC + 4 * lane;
+      unsigned char* dstA = smem + kAOff + tile * kATile + (lane >> 4) * kASlab + ((lane & 1) << 3);
+      const int unit = (lane & 15) >> 1;
+      bool bad = false;
+#pragma unroll 8
+      for (int i = 0; i < 32; i++) {
+        const int r = q * 32 + i;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (pix0 + tile * kTileM + r < HW1) v = __ldg(reinterpret_cast<const float4*>(src + (size_t)r * kC));
+        const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
+        const float2 f0 = __half22float2(h0), f1v = __half22float2(h1);
+        bad |= !(f0.x == v.x && f0.y == v.y && f1v.x == v.z && f1v.y == v.w);
+        uint2 o;
+        o.x = *reinterpret_cast<const uint32_t*>(&h0);
+        o.y = *reinterpret_cast<const uint32_t*>(&h1);
+        *reinterpret_cast<uint2*>(dstA + r * 128 + ((unit ^ (r & 7)) << 4)) = o;
+      }
+      if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(flag, 1);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(a_full);
+    }
+  }
   // ---- per level, the chunks the pixel's window touches ----
   if (warp < kSamplers) {
     for (int l = 0; l < nlev; l++) {
@@ -266,7 +298,7 @@ altcorr_tc_kernel(const __grid_constant__ Params P, const int64_t* __restrict__ 
 
   if (warp == kSamplers) {
     // ---------------- TMA producer ----------------
-    if (lane == 0 && total == 0) mbar_wait(a_full, 0);   // nothing to correlate: the A tiles must still have landed
+    if (!A32 && lane == 0 && total == 0) mbar_wait(a_full, 0);   // nothing to correlate: the A tiles must still have landed
     if (lane == 0 && total > 0) {
       int it = 0;
       for (int l = 0; l < nlev; l++) {
@@ -442,15 +474,16 @@ bool altcorr_tc_supported(int B, int N, int H1, int W1, int H2, int W2, int C, i
 // covered (nothing enqueued then).
 int altcorr_tc_forward_levels(const void* f1, const void* const* f2, const int* H2, const int* W2, const float* cscale,
                               int nlev, const int64_t* ii, const int64_t* jj, const float* coords, float* out,
-                              const int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int C,
-                              int radius, cudaStream_t st) {
+                              int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int C,
+                              int radius, cudaStream_t st, bool f1_is_f32) {
+  if (f1_is_f32 && !skip_if) return DROID_ERR_INVALID_ARGUMENT;      // the in-kernel conversion reports through the flag
   if (nlev < 1 || nlev > atc::kMaxLevels) return DROID_ERR_NOT_IMPLEMENTED;
   if (((uintptr_t)f1 & 15) || ((uintptr_t)coords & 7)) return DROID_ERR_NOT_IMPLEMENTED;
   const int HW1 = H1 * W1;
   atc::Params P;
   memset(&P, 0, sizeof(P));
   P.nlev = nlev;
-  if (!atc::make_map(&P.a, f1, frames1 * (size_t)HW1, atc::kTileM)) return DROID_ERR_NOT_IMPLEMENTED;
+  if (!f1_is_f32 && !atc::make_map(&P.a, f1, frames1 * (size_t)HW1, atc::kTileM)) return DROID_ERR_NOT_IMPLEMENTED;
   int wmax = 0;
   for (int l = 0; l < nlev; l++) wmax = W2[l] > wmax ? W2[l] : wmax;
   const int nc = wmax <= 64 ? 64 : 128;                 // accumulator width: the widest level decides
@@ -465,35 +498,38 @@ int altcorr_tc_forward_levels(const void* f1, const void* const* f2, const int* 
   }
   DevCtx& dc = dev_ctx();
   if (dc.first(kOnceAltcorrTc)) {
-    cudaFuncSetAttribute(atc::altcorr_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::Cfg<64>::kSmem);
-    cudaFuncSetAttribute(atc::altcorr_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::Cfg<128>::kSmem);
+    cudaFuncSetAttribute(atc::altcorr_tc_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::Cfg<64>::kSmem);
+    cudaFuncSetAttribute(atc::altcorr_tc_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::Cfg<128>::kSmem);
+    cudaFuncSetAttribute(atc::altcorr_tc_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::Cfg<64>::kSmem);
+    cudaFuncSetAttribute(atc::altcorr_tc_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::Cfg<128>::kSmem);
   }
   dim3 grid((HW1 + atc::kTiles * atc::kTileM - 1) / (atc::kTiles * atc::kTileM), N, B);
+  const float* f32 = f1_is_f32 ? reinterpret_cast<const float*>(f1) : nullptr;
+#define ATC_LAUNCH(NC, A32) \
+  DROID_LAUNCH atc::altcorr_tc_kernel<NC, A32><<<grid, atc::kThreads, atc::Cfg<NC>::kSmem, st>>>(P, ii, jj, coords, out, skip_if, N, HW1, f32)
   if (nc == 64) {
-    DROID_LAUNCH atc::altcorr_tc_kernel<64><<<grid, atc::kThreads, atc::Cfg<64>::kSmem, st>>>(P, ii, jj, coords, out, skip_if, N, HW1);
+    if (f1_is_f32) ATC_LAUNCH(64, true); else ATC_LAUNCH(64, false);
   } else {
-    DROID_LAUNCH atc::altcorr_tc_kernel<128><<<grid, atc::kThreads, atc::Cfg<128>::kSmem, st>>>(P, ii, jj, coords, out, skip_if, N, HW1);
+    if (f1_is_f32) ATC_LAUNCH(128, true); else ATC_LAUNCH(128, false);
   }
+#undef ATC_LAUNCH
   return check_launch();
 }
 
 int altcorr_tc_forward(const void* f1, const void* f2, const int64_t* ii, const int64_t* jj, const float* coords, float* out,
-                       const int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int H2, int W2,
-                       int C, int radius, cudaStream_t st) {
+                       int* skip_if, size_t frames1, size_t frames2, int B, int N, int H1, int W1, int H2, int W2,
+                       int C, int radius, cudaStream_t st, bool f1_is_f32) {
   const float one = 1.f;
   return altcorr_tc_forward_levels(f1, &f2, &H2, &W2, &one, 1, ii, jj, coords, out, skip_if, frames1, frames2, B, N, H1, W1,
-                                   C, radius, st);
+                                   C, radius, st, f1_is_f32);
 }
 
-// fp32 -> fp16 copies of both maps into `f1h` / `f2h`, *flag = 1 if any value is not exactly a half.
-int altcorr_tc_convert(const float* f1, const float* f2, void* f1h, void* f2h, int* flag, size_t n1, size_t n2,
-                       cudaStream_t st) {
+// fp32 -> fp16 copy of a map into `dst`, *flag = 0 first, then 1 if any value is not exactly a half.
+int altcorr_tc_convert(const float* src, void* dst, int* flag, size_t n, cudaStream_t st) {
   cudaMemsetAsync(flag, 0, sizeof(int), st);
-  const size_t a = n1 / 4, c = n2 / 4;
+  const size_t a = n / 4;
   DROID_LAUNCH atc::to_half_checked_kernel<<<(unsigned)std::min<size_t>((a + 255) / 256, 148 * 16), 256, 0, st>>>(
-      reinterpret_cast<const float4*>(f1), reinterpret_cast<uint2*>(f1h), a, flag);
-  DROID_LAUNCH atc::to_half_checked_kernel<<<(unsigned)std::min<size_t>((c + 255) / 256, 148 * 16), 256, 0, st>>>(
-      reinterpret_cast<const float4*>(f2), reinterpret_cast<uint2*>(f2h), c, flag);
+      reinterpret_cast<const float4*>(src), reinterpret_cast<uint2*>(dst), a, flag);
   return check_launch();
 }
 

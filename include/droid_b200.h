@@ -98,12 +98,12 @@ int droid_altcorr_forward(const void* fmap1, const void* fmap2, const float* coo
                           int radius, void* stream);
 
 /* The same op with a caller-supplied workspace (droid_altcorr_forward_workspace_bytes; 0 = not needed for this shape),
- * which unlocks the tensor-core kernel (csrc/altcorr_tc.cu: radius 3, C = 128, W2 <= 128): both maps are copied to fp16
- * in the workspace with a round-trip check -- AltCorrBlock hands `.float()` copies of an fp16 pyramid
- * (droid_slam/modules/corr.py:96-120), so the copy is exact -- and correlated with tcgen05.mma; when a value is not an
- * fp16 number a device-side flag routes the call to the CUDA-core kernel instead, without a host round trip.  Same
- * result contract as droid_altcorr_forward (<= 1e-5 of the largest value).  This is the entry point the Python
- * host's altcorr_forward binds. */
+ * which unlocks the tensor-core kernel (csrc/altcorr_tc.cu: radius 3, C = 128, W2 <= 128): the target map is copied to
+ * fp16 in the workspace and the source map is converted tile by tile inside the kernel, both with a round-trip check --
+ * AltCorrBlock hands `.float()` copies of an fp16 pyramid (droid_slam/modules/corr.py:96-120), so the conversion is
+ * exact -- and correlated with tcgen05.mma; when a value is not an fp16 number a device-side flag routes the call to the
+ * CUDA-core kernel instead, without a host round trip.  Same result contract as droid_altcorr_forward (<= 1e-5 of the
+ * largest value).  This is the entry point the Python host's altcorr_forward binds. */
 int droid_altcorr_forward_ws(const void* fmap1, const void* fmap2, const float* coords, void* out,
                              int dtype, int B, int N, int H1, int W1, int H2, int W2, int C,
                              int radius, void* workspace, size_t workspace_bytes, void* stream);
