@@ -4,7 +4,7 @@
   drop-in     the same unmodified Python with `droid_backends` bound to THIS repo's module (nothing else changes)
   integrated  drop-in + the bindings INTEGRATION.md proposes for the rows of SURVEY 8f (AltCorrBlock.corr_fn ->
               altcorr_pyramid_indexed, the edge selection of add_proximity_factors -> proximity_edges,
-              __filter_repeated_edges -> filter_repeated_edges)
+              __filter_repeated_edges -> filter_repeated_edges, DepthVideo.reproject -> reproject)
 
 backend:  droid_slam/droid_backend.py DroidBackend.__call__ (BASELINE configs[3]): FactorGraph(corr_impl="alt"),
           add_proximity_factors over all keyframe pairs, update_lowmem(steps): per step reproject, ~n/8 chunks of
@@ -113,6 +113,15 @@ def integrate(ns, Bm):
         return Bm.filter_repeated_edges(ii.contiguous(), jj.contiguous(), torch.cat([self.ii, self.ii_inac]),
                                         torch.cat([self.jj, self.jj_inac]))
 
+    dv = ns.depth_video
+    old_reproject = dv.DepthVideo.reproject
+
+    def reproject(self, ii, jj):                            # depth_video.py:139-147
+        ii, jj = dv.DepthVideo.format_indicies(ii, jj)
+        coords, valid = Bm.reproject(self.poses, self.disps, self.intrinsics, ii.contiguous(), jj.contiguous())
+        return coords[None], valid[None]
+
+    dv.DepthVideo.reproject = reproject
     old_filter = fg.FactorGraph._FactorGraph__filter_repeated_edges
     corr.AltCorrBlock.corr_fn = corr_fn
     fg.FactorGraph.add_proximity_factors = add_proximity_factors
@@ -122,6 +131,7 @@ def integrate(ns, Bm):
         corr.AltCorrBlock.corr_fn = old_corr_fn
         fg.FactorGraph.add_proximity_factors = old_prox
         fg.FactorGraph._FactorGraph__filter_repeated_edges = old_filter
+        dv.DepthVideo.reproject = old_reproject
     return undo
 
 
