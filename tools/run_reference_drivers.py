@@ -4,7 +4,8 @@
   drop-in     the same unmodified Python with `droid_backends` bound to THIS repo's module (nothing else changes)
   integrated  drop-in + the bindings INTEGRATION.md proposes for the rows of SURVEY 8f (AltCorrBlock.corr_fn ->
               altcorr_pyramid_indexed, the edge selection of add_proximity_factors -> proximity_edges,
-              __filter_repeated_edges -> filter_repeated_edges, DepthVideo.reproject -> reproject)
+              __filter_repeated_edges -> filter_repeated_edges, DepthVideo.reproject -> reproject,
+              CorrBlock.__init__ / __call__ -> corr_build / corr_index_pyramid)
 
 backend:  droid_slam/droid_backend.py DroidBackend.__call__ (BASELINE configs[3]): FactorGraph(corr_impl="alt"),
           add_proximity_factors over all keyframe pairs, update_lowmem(steps): per step reproject, ~n/8 chunks of
@@ -113,6 +114,22 @@ def integrate(ns, Bm):
         return Bm.filter_repeated_edges(ii.contiguous(), jj.contiguous(), torch.cat([self.ii, self.ii_inac]),
                                         torch.cat([self.jj, self.jj_inac]))
 
+    old_cb_init, old_cb_call = corr.CorrBlock.__init__, corr.CorrBlock.__call__
+
+    def cb_init(self, fmap1, fmap2, num_levels=4, radius=3):   # modules/corr.py:24-38,63-71: matmul + 3 avg_pool2d
+        H, W = fmap1.shape[-2:]
+        if num_levels != 4 or fmap1.dtype != torch.float16 or H % 8 or W % 16 or W > 64:
+            return old_cb_init(self, fmap1, fmap2, num_levels, radius)
+        self.num_levels, self.radius = num_levels, radius
+        self.corr_pyramid = Bm.corr_build(fmap1.contiguous(), fmap2.contiguous())
+
+    def cb_call(self, coords):                              # modules/corr.py:40-50: 4 lookups + cat
+        batch, num, ht, wd, _ = coords.shape
+        c = coords.permute(0, 1, 4, 2, 3).contiguous().view(batch * num, 2, ht, wd)
+        vols = [v.contiguous() for v in self.corr_pyramid]
+        return Bm.corr_index_pyramid(vols, c, self.radius).view(batch, num, -1, ht, wd)
+
+    corr.CorrBlock.__init__, corr.CorrBlock.__call__ = cb_init, cb_call
     dv = ns.depth_video
     old_reproject = dv.DepthVideo.reproject
 
@@ -132,6 +149,7 @@ def integrate(ns, Bm):
         fg.FactorGraph.add_proximity_factors = old_prox
         fg.FactorGraph._FactorGraph__filter_repeated_edges = old_filter
         dv.DepthVideo.reproject = old_reproject
+        corr.CorrBlock.__init__, corr.CorrBlock.__call__ = old_cb_init, old_cb_call
     return undo
 
 
