@@ -647,13 +647,14 @@ def extra_metrics(dev, hbm_peak, peaks):
 def frontend_driver_metric(frames=48):
     """BASELINE's "frontend fps", through the reference's OWN DroidFrontend (unmodified droid_slam/*.py staged under
     oracle/_ref/pyref) on a synthetic stream of `frames` keyframes with a random-init DroidNet: the same Python with
-    `droid_backends` bound to the reference extension and to this repo's module.  Runs tools/run_reference_drivers.py in a
+    `droid_backends` bound to the reference extension, to this repo's module (drop-in) and to this repo's module plus the
+    bindings INTEGRATION.md proposes for the rows of SURVEY 8f (integrated).  Runs tools/run_reference_drivers.py in a
     child process (a measurement tool: the only place besides cpu_baseline where bench.py touches oracle/); DESIGN.md 5.1
     holds the 100-keyframe run and the 1000-keyframe backend run of the same tool."""
     import subprocess
     tool = os.path.join(ROOT, "tools", "run_reference_drivers.py")
     try:
-        r = subprocess.run([sys.executable, tool, "frontend", "--frames", str(frames), "--arms", "reference,drop-in"],
+        r = subprocess.run([sys.executable, tool, "frontend", "--frames", str(frames), "--arms", "reference,drop-in,integrated"],
                            capture_output=True, text=True, timeout=420)
         if r.returncode != 0:
             return {"unavailable": (r.stderr or r.stdout).strip().splitlines()[-1][:300] if (r.stderr or r.stdout) else "rc %d" % r.returncode}
