@@ -990,9 +990,11 @@ __global__ void __launch_bounds__(kThreads, NPIX >= 4 ? 2 : 3) ba_accum_kernel(
         const bool behind = Xj[2] < DROID_MIN_DEPTH;
         // the reference divides in double and rounds to float (:305); the IEEE-rounded float reciprocal is the same
         // value except for double-rounding ties (~2^-29 of the inputs)
-        const float D = behind ? 0.0f : __frcp_rn(Xj[2]);
-        const float wud = behind ? 0.0f : (float)(.001 * (double)wu[q]);
-        const float wvd = behind ? 0.0f : (float)(.001 * (double)wv[q]);
+        // branch-free (bit masks, not a divergent block per pixel: the five pixels of a thread interleave)
+        const unsigned keep = behind ? 0u : 0xffffffffu;
+        const float D = __uint_as_float(__float_as_uint(rcp_depth(Xj[2])) & keep);
+        const float wud = __uint_as_float(__float_as_uint((float)(.001 * (double)wu[q])) & keep);
+        const float wvd = __uint_as_float(__float_as_uint((float)(.001 * (double)wv[q])) & keep);
         const float fxd = K.fx * D, fyd = K.fy * D;
         const float ru = tu[q] - (fxd * X + K.cx);                   // (:307-308)
         const float rv = tv[q] - (fyd * Y + K.cy);
@@ -1003,12 +1005,20 @@ __global__ void __launch_bounds__(kThreads, NPIX >= 4 ? 2 : 3) ba_accum_kernel(
         // depth terms (:320-321, :353-354)
         Cs[q] += wuJ * Jzu + wvJ * Jzv;
         Bs[q] += wuJ * ru + wvJ * rv;
-        if (!motion_only && ok) {   // packed E_j for the Schur and depth-update passes (streaming stores)
-          __stcg(pe + q * kThreads, stereo ? 0.f : wuJ * K.fx);
-          __stcg(pe + (size_t)HW + q * kThreads, stereo ? 0.f : wvJ * K.fy);
-          __stcg(pe + 2 * (size_t)HW + q * kThreads, xd);
-          __stcg(pe + 3 * (size_t)HW + q * kThreads, yd);
-          __stcg(pe + 4 * (size_t)HW + q * kThreads, hd);
+        {   // packed E_j for the Schur and depth-update passes: five predicated streaming stores, no branch
+          const float e0 = stereo ? 0.f : wuJ * K.fx, e1 = stereo ? 0.f : wvJ * K.fy;
+          float* p0 = pe + q * kThreads;
+          asm volatile(
+              "{\n\t.reg .pred p;\n\t"
+              "setp.ne.b32 p, %11, 0;\n\t"
+              "@p st.global.cg.f32 [%0], %5;\n\t"
+              "@p st.global.cg.f32 [%1], %6;\n\t"
+              "@p st.global.cg.f32 [%2], %7;\n\t"
+              "@p st.global.cg.f32 [%3], %8;\n\t"
+              "@p st.global.cg.f32 [%4], %9;\n\t}"
+              ::"l"(p0), "l"(p0 + (size_t)HW), "l"(p0 + 2 * (size_t)HW), "l"(p0 + 3 * (size_t)HW), "l"(p0 + 4 * (size_t)HW),
+                "f"(e0), "f"(e1), "f"(xd), "f"(yd), "f"(hd), "r"(0), "r"((int)(!motion_only && ok))
+              : "memory");
         }
         if (!stereo) {
           const float xy = xd * yd;

@@ -59,7 +59,7 @@ __device__ __forceinline__ void linearise_j_xy(const SE3& g, const Intr& K, floa
   const bool behind = Xj[2] < DROID_MIN_DEPTH;
   // the reference divides in double and rounds to float (:305); the IEEE-rounded float reciprocal is the same value
   // except for double-rounding ties (~2^-29 of the inputs) and keeps the slow fp64 pipe off the critical chain
-  const float d = behind ? 0.0f : __frcp_rn(Xj[2]);
+  const float d = behind ? 0.0f : rcp_depth(Xj[2]);
   const float d2 = d * d;
   L.wu_d = behind ? 0.0f : (float)(.001 * (double)wru);
   L.wv_d = behind ? 0.0f : (float)(.001 * (double)wrv);
