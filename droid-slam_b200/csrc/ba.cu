@@ -1020,7 +1020,7 @@ __global__ void __launch_bounds__(kThreads, NPIX >= 4 ? 2 : 3) ba_accum_kernel(
                 "f"(e0), "f"(e1), "f"(xd), "f"(yd), "f"(hd), "r"(0), "r"((int)(!motion_only && ok))
               : "memory");
         }
-        if (!stereo) {
+        {   // (for a stereo edge these sums are never read -- depth terms only, :323,:356 -- so no branch per pixel)
           const float xy = xd * yd;
           const float j2u = -xd * hd, j3u = -xy, j4u = fmaf(xd, xd, 1.f), j5u = -yd;
           const float j2v = -yd * hd, j3v = -fmaf(yd, yd, 1.f);
