@@ -49,13 +49,19 @@ template <typename TF, int CPL /*channels per lane, multiple of 4*/>
 __global__ void __launch_bounds__(256) altcorr_fwd_r3_kernel(
     const TF* __restrict__ f1_base, const TF* __restrict__ f2_base, const int64_t* __restrict__ ii,
     const int64_t* __restrict__ jj, const float* __restrict__ coords, float* __restrict__ out, int N,
-    int HW1, int H2, int W2, int C, const int* __restrict__ only_if) {
-  if (only_if && *only_if == 0) return;      // the tensor-core kernel (altcorr_tc.cu) has done the work
+    int HW1, int H2, int W2, int C, const int* __restrict__ only_if, int nstrips, int B) {
+  // Gated launch (`only_if` set; behind the tensor-core kernel of altcorr_tc.cu): a small 1-D grid whose CTAs walk over
+  // all (b, n, strip) units -- when the flag is clear, which is the normal case, a few hundred CTAs exit instead of
+  // tens of thousands (45 us per launch at 160 edges).  Plain launch: one unit per CTA, 3-D grid.
+  if (only_if && *only_if == 0) return;      // the tensor-core kernel has done the work
   __shared__ float taps[8][64];
   __shared__ float stage[49][8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int b = blockIdx.z, n = blockIdx.y;
-  const int pix0 = blockIdx.x * 8;
+  const long long total = only_if ? (long long)nstrips * N * B : 1;
+  for (long long unit = only_if ? blockIdx.x : 0; unit < total; unit += gridDim.x) {
+  const int b = only_if ? (int)(unit / ((long long)nstrips * N)) : blockIdx.z;
+  const int n = only_if ? (int)((unit / nstrips) % N) : blockIdx.y;
+  const int pix0 = (only_if ? (int)(unit % nstrips) : blockIdx.x) * 8;
   const int pix = pix0 + warp;
   const bool pv = pix < HW1;
   const size_t i1 = ii ? (size_t)ii[b] : (size_t)b;
@@ -116,6 +122,8 @@ __global__ void __launch_bounds__(256) altcorr_fwd_r3_kernel(
   for (int e = threadIdx.x; e < 49 * 8; e += 256) {
     const int c = e >> 3, p = e & 7;
     if (pix0 + p < HW1) ob[(size_t)c * HW1 + pix0 + p] = stage[c][p];
+  }
+  __syncthreads();      // `stage` / `taps` are reused by the next unit
   }
 }
 
@@ -244,10 +252,12 @@ static int fwd_common(const void* f1, const void* f2, const int64_t* ii, const i
   const int esz = dtype == DROID_DTYPE_F16 ? 2 : 4;
   const bool aligned = ((uintptr_t)f1 % (4 * esz) == 0) && ((uintptr_t)f2 % (4 * esz) == 0);
   if (radius == 3 && aligned && (C == 128 || C == 256 || (C == 384 && dtype == DROID_DTYPE_F32))) {
+    const int nstrips = (HW1 + 7) / 8;
+    const dim3 g = only_if ? dim3((unsigned)std::min<long long>((long long)nstrips * N * B, 148 * 8)) : grid;
 #define ALT_LAUNCH(TF, CPL)                                                                     \
-  DROID_LAUNCH altcorr_fwd_r3_kernel<TF, CPL><<<grid, 256, 0, st>>>(reinterpret_cast<const TF*>(f1),          \
+  DROID_LAUNCH altcorr_fwd_r3_kernel<TF, CPL><<<g, 256, 0, st>>>(reinterpret_cast<const TF*>(f1),          \
                                                         reinterpret_cast<const TF*>(f2), ii, jj, \
-                                                        coords, out, N, HW1, H2, W2, C, only_if)
+                                                        coords, out, N, HW1, H2, W2, C, only_if, nstrips, B)
     if (dtype == DROID_DTYPE_F32) {
       if (C == 128) ALT_LAUNCH(float, 4);
       else if (C == 256) ALT_LAUNCH(float, 8);
