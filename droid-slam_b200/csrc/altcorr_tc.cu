@@ -6,27 +6,29 @@
 //
 // Why a GEMM: every source pixel needs 64 dot products of 128 channels against an 8x8 window of the target frame,
 // and the windows of neighbouring pixels overlap almost entirely.  The CUDA-core kernel re-reads a 256 / 512-byte row
-// per tap (27 instructions per tap, 6.6 TFLOP/s).  Here a CTA takes 256 source pixels (two 128-row A tiles, loaded
-// once) and sweeps the target frame in chunks of 64 pixels (whole image rows): D = A B^T (128 x 64, K = 128, kind::f16,
-// fp32 accumulation in TMEM) holds the correlation of every source pixel of the tile with every target pixel of the
-// chunk, and each source pixel picks the taps of its own window out of its accumulator row.  Only the chunks some
-// pixel of the CTA needs are computed: for a smooth flow field that is the window rows of four image rows (~14 of 40
-// rows), for arbitrary coordinates the whole frame -- the result never depends on it.
+// per tap (27 instructions per tap, 6.6 TFLOP/s).  Here a CTA takes 128 source pixels (one A tile, loaded once) and
+// sweeps the target level in chunks of NC = 64 or 128 pixels (whole image rows): D = A B^T (128 x NC, K = 128,
+// kind::f16, fp32 accumulation in TMEM) holds the correlation of every source pixel of the tile with every target
+// pixel of the chunk, and each source pixel picks the taps of its own window out of its accumulator row.  Only the
+// chunks some pixel of the CTA needs are computed: for a smooth flow field the window rows of two image rows (~9-12 of
+// 40 rows), for arbitrary coordinates the whole frame -- the result never depends on it.  Up to four pyramid levels
+// run in one launch (the chunk stream continues across levels; level l + 1 is multiplied while level l is sampled).
 // fp16 products are exact in fp32 and K = 128 is 8 chained MMAs, so the values agree with the fp32 FMA chain of the
 // CUDA-core kernel to ~1e-7 of the largest value (the reference's own bar for the lookups is 1e-5).
 //
-// Warp roles (320 threads, one CTA per SM):
-//   warps 0-3 / 4-7  samplers of A tile 0 / 1: thread = TMEM lane = source pixel.  Per chunk: accumulator row -> registers
-//                    (tcgen05.ld) -> the thread's own row of a shared staging buffer -> the taps of the window rows
-//                    that lie in the chunk, into registers with static indices; chunks no lane of the warp needs are
-//                    only acknowledged.  After the last chunk: bilinear weights, 49 coalesced stores per pixel;
-//   warp 8           TMA producer: the two A tiles once, then the B chunks through a 5-stage ring (two 64-channel
-//                    K slabs per stage, 128-byte swizzle);
-//   warp 9           MMA issuer: 2 x 8 tcgen05.mma per chunk into accumulator (tile, chunk & 3); TMEM = 2 x 4 x 64 columns.
+// Warp roles (192 threads; NC = 64: 100 KB of shared memory, 256 TMEM columns, two CTAs per SM):
+//   warps 0-3  samplers: thread = TMEM lane = source pixel.  Per chunk: accumulator row -> registers (tcgen05.ld) ->
+//              the thread's own row of a shared staging buffer -> the taps of the window rows that lie in the chunk,
+//              into registers with static indices; chunks no lane of the warp needs are only acknowledged.  After the
+//              last chunk of a level: bilinear weights, 49 coalesced stores per pixel;
+//   warp 4     TMA producer: the A tile at kernel entry, then the B chunks through a 2-stage ring (two 64-channel
+//              K slabs per stage, 128-byte swizzle);
+//   warp 5     MMA issuer: 8 tcgen05.mma per chunk into accumulator (chunk & 3); TMEM = 4 x NC columns.
 //
-// The fp32 entry point (the drop-in signature) converts both feature maps to fp16 in a pre-pass that also checks that
-// every value survives the round trip; if one does not (a caller that feeds real fp32 features), a device-side flag
-// makes this kernel exit at once and the CUDA-core kernel, launched behind it, do the work -- no host round trip.
+// The fp32 entry point (the drop-in signature) copies the TARGET map to fp16 in a pre-pass and converts the SOURCE map
+// tile by tile inside this kernel (template flag A32), both with a round-trip check; if a value is not an fp16 number
+// (a caller that feeds real fp32 features) a device-side flag makes the remaining CTAs exit and the CUDA-core kernel,
+// launched behind it, redo the call -- no host round trip.
 #include <cuda.h>
 #include <cuda_fp16.h>
 
